@@ -1,0 +1,206 @@
+/*
+ * vsnray_b200.h -- C ABI of libvsnray_b200.so: the B200 (sm_100a) ray-query hot path.
+ *
+ * The reference (tu500/visionaray) has no FFI; its hot path is C++ templates instantiated in
+ * the caller's translation unit.  The entry points below are what the host adaptor headers
+ * (include/visionaray_b200/) bind in place of those template instantiations.  Each one cites the
+ * reference interface it replaces (paths relative to /root/reference/include/visionaray/).
+ *
+ * Conventions: plain pointers and sizes only; every call returns 0 (VSB_OK) or a negative
+ * vsb_* code / positive cudaError_t; vsb_strerror() describes either.  There is no CPU
+ * fallback: without a CUDA device every compute entry point fails with VSB_ERR_NO_DEVICE.
+ * Calls on one context are serialised by the caller (the reference's frame() is not
+ * re-entrant either, detail/cuda_sched.inl:307-320).
+ */
+#ifndef VSNRAY_B200_H
+#define VSNRAY_B200_H 1
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---- data layouts (the reference's memory layouts are the ABI) ---- */
+
+/* basic_ray<float>: math/ray.h; vec3 is 16-byte aligned (math/detail/vector3f.inl:12). 32 B. */
+typedef struct vsb_ray {
+    float ori[3]; float pad0;
+    float dir[3]; float pad1;
+} vsb_ray;
+
+/* basic_triangle<3,float,unsigned>: math/triangle.h + math/primitive.h. 64 B. */
+typedef struct vsb_triangle {
+    uint32_t geom_id; uint32_t prim_id; uint32_t pad0[2];
+    float v1[3]; float pad1;
+    float e1[3]; float pad2;
+    float e2[3]; float pad3;
+} vsb_triangle;
+
+/* basic_sphere<float,unsigned>: math/sphere.h. 48 B. */
+typedef struct vsb_sphere {
+    uint32_t geom_id; uint32_t prim_id; uint32_t pad0[2];
+    float center[3]; float pad1;
+    float radius; float pad2[3];
+} vsb_sphere;
+
+/* bvh_node: bvh.h:52-119. inner <=> num_prims == 0; children at first, first+1. 32 B. */
+typedef struct vsb_bvh_node {
+    float    bbox_min[3];
+    uint32_t first;        /* first_child (inner) | first_prim (leaf, index into indices[]) */
+    float    bbox_max[3];
+    uint32_t num_prims;
+} vsb_bvh_node;
+
+/* hit_record_bvh<ray, BVH, hit_record<ray, primitive<unsigned>>>:
+ * math/intersect.h:88-115 + detail/bvh/hit_record.h:30-46 (isect_pos is not produced by the
+ * reference's intersect() either, math/intersect.h:257).  A miss has hit=0, t=FLT_MAX. 32 B. */
+typedef struct vsb_hit {
+    int32_t  hit;
+    uint32_t prim_id;
+    uint32_t geom_id;
+    float    t;
+    float    u;
+    float    v;
+    uint32_t prim_list_index;   /* primitive_list_index: position in indices[] */
+    uint32_t pad;
+} vsb_hit;
+
+/* plastic<float> / matte<float> parameters (material.h, detail/material/{plastic,matte}.inl),
+ * flattened; the adaptor fills it through the reference's getters. 64 B. */
+typedef struct vsb_material {
+    float ca[3]; float ka;
+    float cd[3]; float kd;
+    float cs[3]; float ks;
+    float spec_exp; int32_t kind;   /* VSB_MAT_PLASTIC | VSB_MAT_MATTE */
+    float pad[2];
+} vsb_material;
+
+/* point_light<float> (point_light.h:58-64). 48 B. */
+typedef struct vsb_point_light {
+    float pos[3]; float kl;
+    float cl[3];  float att_const;
+    float att_lin; float att_quad; float pad[2];
+} vsb_point_light;
+
+enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1 };
+enum { VSB_PRIM_TRIANGLE = 0, VSB_PRIM_SPHERE = 1 };
+enum { VSB_KERNEL_SIMPLE = 0, VSB_KERNEL_WHITTED = 1, VSB_KERNEL_AO = 2, VSB_KERNEL_PATHTRACING = 3 };
+enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2 };
+
+/* traversal engine: the wide quantised BVH8 (default, fast) or the reference-order BVH2 walk
+ * (bit-exact with detail/bvh/intersect.inl:35-134 including tie order and any-hit winner). */
+enum { VSB_TRAVERSE_WIDE = 0, VSB_TRAVERSE_EXACT = 1 };
+
+/* where the caller's buffers live */
+enum { VSB_MEM_DEVICE = 0, VSB_MEM_HOST = 1 };
+
+enum {
+    VSB_OK = 0,
+    VSB_ERR_NO_DEVICE   = -1,
+    VSB_ERR_BAD_ARG     = -2,
+    VSB_ERR_BAD_TREE    = -3,
+    VSB_ERR_NOT_INIT    = -4,
+    VSB_ERR_UNSUPPORTED = -5
+};
+
+/* Kernel + scheduler parameters of one frame() call.  Mirrors what cuda_sched<R>::frame()
+ * passes to render<<<>>> (detail/cuda_sched.inl:60-99,259-266) plus the fields of
+ * kernel_params (kernels.h:94-319) the built-in kernels read.  The first block is shared
+ * field-for-field with the oracle (oracle/vsnray_oracle.h: vso_frame_params). */
+typedef struct vsb_frame_params {
+    int32_t  kernel;          /* VSB_KERNEL_* */
+    int32_t  pixel_sampler;   /* VSB_PS_* (sched_common.h:29-52) */
+    int32_t  width, height;
+    float    eye[4], center[4], up[4];   /* pinhole camera (camera.h) */
+    float    fovy, aspect;               /* fovy in radians */
+    uint32_t frame_num, seed;
+    uint32_t num_bounces;
+    float    epsilon;
+    float    bg[4];
+    float    ambient[4];
+    int32_t  ao_samples;
+    float    ao_radius;
+    int32_t  n_lights, n_materials;
+} vsb_frame_params;
+
+typedef struct vsb_frame_desc {
+    vsb_frame_params p;
+    /* camera basis as cuda_sched_impl_frame computes it on the host
+     * (detail/cuda_sched.inl:259-266); filled by vsb_camera_basis() */
+    float    cam_eye[4], cam_u[4], cam_v[4], cam_w[4];
+    int32_t  scissor[4];                 /* x, y, w, h; (0,0,width,height) = whole image */
+    const float*           normals;      /* per-face normals, 16 B each, indexed by prim_id
+                                            (normals_per_face_binding, get_normal.h:28-37) */
+    const vsb_material*    materials;    /* indexed by geom_id */
+    const vsb_point_light* lights;
+    void*    color;                      /* PF_RGBA32F, buffer[y*width+x] (pixel_access.h:38-58) */
+    void*    depth;                      /* reserved (PF_DEPTH32F); may be NULL */
+    int32_t  mem;                        /* VSB_MEM_*: where normals/materials/lights/color live */
+    int32_t  traverse;                   /* VSB_TRAVERSE_* */
+    /* image-space tile partition for multi-GPU (64x64 tiles, tile k -> rank k % nranks);
+     * nranks <= 1 renders everything.  With nranks > 1 `color` is the rank's compact tile
+     * buffer (tiles_of_rank * 64*64 pixels), see vsb_tiles_of_rank(). */
+    int32_t  tile_rank, tile_nranks;
+    uint64_t* ray_count;                 /* optional device/host counter: rays traced this frame */
+} vsb_frame_desc;
+
+typedef struct vsb_scene vsb_scene;
+
+/* ---- context ---- */
+int  vsb_init(int device);                       /* cudaSetDevice + stream/queue state */
+int  vsb_shutdown(void);
+const char* vsb_strerror(int code);
+int  vsb_version(void);
+int  vsb_device_sm_count(int* out);
+
+/* ---- scene: replaces cuda_index_bvh<P>(index_bvh<P> const&) upload (bvh.h:344-350,446-447)
+ * and the .ref() it hands to kernels (bvh.h:364-376).  indices == NULL means a non-index
+ * bvh (bvh_t, primitive(i) = prims[i], bvh.h:177-180).  The tree is validated, uploaded and
+ * re-encoded on the GPU into the wide quantised BVH8. ---- */
+int  vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
+                      const vsb_bvh_node* nodes, size_t n_nodes,
+                      const uint32_t* indices, size_t n_indices,
+                      vsb_scene** out);
+int  vsb_scene_destroy(vsb_scene* s);
+/* diagnostics: out[0]=wide nodes, out[1]=wide node bytes, out[2]=leaf prim records,
+ * out[3]=prim record bytes, out[4]=bvh2 max depth, out[5]=bvh2 nodes */
+int  vsb_scene_stats(const vsb_scene* s, uint64_t* out, int n);
+/* copy the re-encoded wide nodes back to the host (property tests of the re-encode) */
+int  vsb_scene_download_wide(const vsb_scene* s, void* nodes_out, size_t node_bytes_cap,
+                             void* prims_out, size_t prim_bytes_cap);
+
+/* ---- ray queries over a list of rays: replaces closest_hit()/any_hit() over
+ * [prims.begin, prims.end) (detail/traverse_linear.inl:186-318) -> intersect<Traversal>()
+ * (detail/bvh/intersect.inl:35-134).  scenes[0..n_scenes) mirrors the range of bvh refs.
+ * max_t_per_ray may be NULL (then max_t applies to all rays; FLT_MAX = unbounded). ---- */
+int  vsb_closest_hit(const vsb_scene* const* scenes, int n_scenes,
+                     const vsb_ray* rays, size_t n_rays, float max_t, const float* max_t_per_ray,
+                     vsb_hit* hits, int mem, int traverse, void* cuda_stream);
+int  vsb_any_hit(const vsb_scene* const* scenes, int n_scenes,
+                 const vsb_ray* rays, size_t n_rays, float max_t, const float* max_t_per_ray,
+                 vsb_hit* hits, int mem, int traverse, void* cuda_stream);
+
+/* ---- frame: replaces cuda_sched<R>::frame(kernel, sched_params, frame_num)
+ * (detail/cuda_sched.h:24-40, detail/cuda_sched.inl:307-320) for the built-in kernels
+ * simple / whitted / pathtracing (detail/*.inl) and the AO kernel of
+ * src/examples/ao/main.cpp:183-246. ---- */
+int  vsb_camera_basis(vsb_frame_desc* d);        /* fills cam_eye/u/v/w from p.eye/center/up/fovy/aspect */
+int  vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb_frame_desc* d, void* cuda_stream);
+int  vsb_tiles_of_rank(int width, int height, int rank, int nranks, int* n_tiles);
+/* scatter rank-major gathered tile buffers (nranks * tiles_per_rank_padded * 4096 px) into a
+ * row-major RGBA32F image: the de-interleave step after the NCCL all-gather. device pointers. */
+int  vsb_deinterleave_tiles(const void* gathered, int width, int height, int nranks,
+                            int tiles_per_rank_padded, void* image, void* cuda_stream);
+
+/* ---- timing helper for the harness: average device time (ms) of the last query/frame
+ * kernels, measured with CUDA events on the stream they were launched on ---- */
+int  vsb_last_kernel_ms(float* ms);
+int  vsb_launch_count(uint64_t* n);              /* number of kernels this library launched */
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* VSNRAY_B200_H */

@@ -1,0 +1,392 @@
+// TEST / BASELINE INFRASTRUCTURE -- frame() half of oracle/ref_harness.cpp.
+// Calls the reference's kernel functors and schedulers; copies nothing from them.
+
+namespace
+{
+
+// Mirrors vsb_frame_params in include/vsnray_b200.h (field for field).
+struct frame_params
+{
+    int32_t  kernel;          // 0 simple, 1 whitted, 2 ao, 3 pathtracing
+    int32_t  pixel_sampler;   // 0 uniform, 1 jittered, 2 jittered_blend
+    int32_t  width, height;
+    float    eye[4], center[4], up[4];
+    float    fovy, aspect;    // radians
+    uint32_t frame_num, seed;
+    uint32_t num_bounces;
+    float    epsilon;
+    float    bg[4];
+    float    ambient[4];
+    int32_t  ao_samples;
+    float    ao_radius;
+    int32_t  n_lights, n_materials;
+};
+
+struct scene_host
+{
+    tri_ref_t ref;
+    aligned_vector<vec3> normals;
+    aligned_vector<plastic<float>> plastics;
+    aligned_vector<matte<float>> mattes;
+    aligned_vector<point_light<float>> lights;
+};
+
+inline spectrum<float> spec3(float const* c) { return spectrum<float>(from_rgb(c[0], c[1], c[2])); }
+
+void fill_scene(scene_host& s, frame_params const& fp, float const* normals16, size_t n_normals,
+                mat_pod const* mats, light_pod const* lights)
+{
+    s.normals.resize(n_normals);
+    for (size_t i = 0; i < n_normals; ++i)
+        s.normals[i] = vec3(normals16[i * 4], normals16[i * 4 + 1], normals16[i * 4 + 2]);
+    for (int i = 0; i < fp.n_materials; ++i)
+    {
+        plastic<float> p;
+        p.set_ca(spec3(mats[i].ca)); p.set_ka(mats[i].ka);
+        p.set_cd(spec3(mats[i].cd)); p.set_kd(mats[i].kd);
+        p.set_cs(spec3(mats[i].cs)); p.set_ks(mats[i].ks);
+        p.set_specular_exp(mats[i].spec_exp);
+        s.plastics.push_back(p);
+        matte<float> m;
+        m.set_ca(spec3(mats[i].ca)); m.set_ka(mats[i].ka);
+        m.set_cd(spec3(mats[i].cd)); m.set_kd(mats[i].kd);
+        s.mattes.push_back(m);
+    }
+    for (int i = 0; i < fp.n_lights; ++i)
+    {
+        point_light<float> l;
+        l.set_cl(vec3(lights[i].cl[0], lights[i].cl[1], lights[i].cl[2]));
+        l.set_kl(lights[i].kl);
+        l.set_position(vec3(lights[i].pos[0], lights[i].pos[1], lights[i].pos[2]));
+        l.set_constant_attenuation(lights[i].att_const);
+        l.set_linear_attenuation(lights[i].att_lin);
+        l.set_quadratic_attenuation(lights[i].att_quad);
+        s.lights.push_back(l);
+    }
+}
+
+camera make_cam(frame_params const& fp)
+{
+    camera cam;
+    cam.perspective(fp.fovy, fp.aspect, 0.001f, 1000.0f);
+    cam.look_at(vec3(fp.eye[0], fp.eye[1], fp.eye[2]),
+                vec3(fp.center[0], fp.center[1], fp.center[2]),
+                vec3(fp.up[0], fp.up[1], fp.up[2]));
+    return cam;
+}
+
+// The AO kernel of src/examples/ao/main.cpp:183-246, instantiated through the reference's
+// own closest_hit / any_hit / get_normal / make_orthonormal_basis / cosine_sample_hemisphere.
+template <typename R>
+struct ao_kernel
+{
+    using S = typename R::scalar_type;
+    using C = vector<4, S>;
+    using V = vector<3, S>;
+
+    tri_ref_t const* begin;
+    tri_ref_t const* end;
+    vec3 const* normals;
+    vec4 bg;
+    int samples;
+    float radius;
+
+    template <typename Sampler>
+    result_record<S> operator()(R ray, Sampler& samp) const
+    {
+        result_record<S> result;
+        result.color = C(bg);
+        auto hit_rec = closest_hit(ray, begin, end);
+        result.hit = hit_rec.hit;
+        if (any(hit_rec.hit))
+        {
+            hit_rec.isect_pos = ray.ori + ray.dir * hit_rec.t;
+            result.isect_pos  = hit_rec.isect_pos;
+            V clr(1.0);
+            auto n = get_normal(normals, hit_rec, index_bvh<tri_t>{}, normals_per_face_binding{});
+            V u, v, w = n;
+            make_orthonormal_basis(u, v, w);
+            S rad = radius;
+            for (int i = 0; i < samples; ++i)
+            {
+                auto sp = cosine_sample_hemisphere(samp.next(), samp.next());
+                auto dir = normalize(sp.x * u + sp.y * v + sp.z * w);
+                R ao_ray;
+                ao_ray.ori = hit_rec.isect_pos + dir * S(1E-3f);
+                ao_ray.dir = dir;
+                auto ao_rec = any_hit(ao_ray, begin, end, rad);
+                clr = select(ao_rec.hit, clr - V(S(1.0f / samples)), clr);
+            }
+            result.color = select(hit_rec.hit, C(clr, S(1.0)), result.color);
+        }
+        return result;
+    }
+};
+
+template <typename K>
+struct no_sampler_adapter
+{
+    K k;
+    template <typename R, typename Sampler>
+    auto operator()(R ray, Sampler&) const -> decltype(k(ray)) { return k(ray); }
+};
+
+// Scalar per-pixel driver with the deterministic sampler: the PARITY frame oracle.
+template <typename K>
+void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, float* basis_out)
+{
+    auto cam = make_cam(fp);
+    // host-side basis, as the reference schedulers compute it (detail/tiled_sched.inl:296-304)
+    auto f = normalize(cam.eye() - cam.center());
+    auto s = normalize(cross(cam.up(), f));
+    auto u = cross(f, s);
+    vec3 eye   = cam.eye();
+    vec3 cam_u = s * tan(cam.fovy() / 2.0f) * cam.aspect();
+    vec3 cam_v = u * tan(cam.fovy() / 2.0f);
+    vec3 cam_w = -f;
+    if (basis_out)
+    {
+        float b[12] = { eye.x, eye.y, eye.z, cam_u.x, cam_u.y, cam_u.z, cam_v.x, cam_v.y, cam_v.z, cam_w.x, cam_w.y, cam_w.z };
+        std::memcpy(basis_out, b, sizeof(b));
+    }
+    size_t w = fp.width, h = fp.height;
+    parallel_for(w * h, nthreads, [&](size_t b, size_t e)
+    {
+        for (size_t i = b; i < e; ++i)
+        {
+            unsigned x = unsigned(i % w), y = unsigned(i / w);
+            det_sampler samp((uint32_t)i, fp.frame_num, fp.seed);
+            float px = float(x), py = float(y);
+            if (fp.pixel_sampler != 0)
+            {
+                // jittered: detail/sched_common.h:197-217
+                float jx = samp.next() - 0.5f;
+                float jy = samp.next() - 0.5f;
+                px += jx; py += jy;
+            }
+            ray_t r = detail::make_primary_ray_impl<ray_t>(px, py, w, h, eye, cam_u, cam_v, cam_w);
+            auto res = kernel(r, samp);
+            vec4 c = res.color;
+            float* dst = rgba + i * 4;
+            if (fp.pixel_sampler == 2)
+            {
+                // jittered_blend: detail/sched_common.h:516-528
+                float alpha = 1.0f / float(fp.frame_num);
+                dst[0] = c.x * alpha + dst[0] * (1.0f - alpha);
+                dst[1] = c.y * alpha + dst[1] * (1.0f - alpha);
+                dst[2] = c.z * alpha + dst[2] * (1.0f - alpha);
+                dst[3] = c.w * alpha + dst[3] * (1.0f - alpha);
+            }
+            else
+            {
+                dst[0] = c.x; dst[1] = c.y; dst[2] = c.z; dst[3] = c.w;
+            }
+        }
+    });
+}
+
+// tiled_sched<R>::frame() driver: the TIMED CPU baseline (and, for RNG-free kernels with the
+// uniform pixel sampler, a second frame oracle).  Returns seconds for `reps` frames (best).
+template <typename R, typename K, typename PS>
+double tiled_frame(K kernel, PS ps, frame_params const& fp, float* rgba, int nthreads, int reps, int warmup)
+{
+    static tiled_sched<R>* sched = nullptr;
+    static int sched_threads = 0;
+    if (!sched || sched_threads != nthreads)
+    {
+        delete sched;
+        sched = new tiled_sched<R>((unsigned)nthreads);
+        sched_threads = nthreads;
+        // workers must reach their condvar wait before the first notify
+        std::this_thread::sleep_for(std::chrono::milliseconds(200));
+    }
+    simple_buffer_rt<PF_RGBA32F, PF_UNSPECIFIED> rt;
+    rt.resize(fp.width, fp.height);
+    auto cam = make_cam(fp);
+    cam.set_viewport(0, 0, fp.width, fp.height);
+    auto sparams = make_sched_params(ps, cam, rt);
+    double best = 1e30;
+    for (int i = 0; i < warmup + reps; ++i)
+    {
+        auto t0 = std::chrono::steady_clock::now();
+        sched->frame(kernel, sparams, fp.frame_num);
+        auto t1 = std::chrono::steady_clock::now();
+        double dt = std::chrono::duration<double>(t1 - t0).count();
+        if (i >= warmup && dt < best) best = dt;
+    }
+    if (rgba) std::memcpy(rgba, rt.color(), sizeof(float) * 4 * size_t(fp.width) * fp.height);
+    return best;
+}
+
+template <typename R>
+struct ao_tiled_adapter
+{
+    ao_kernel<R> k;
+    template <typename Sampler>
+    auto operator()(R ray, Sampler& s) const -> decltype(k(ray, s)) { return k(ray, s); }
+};
+
+} // namespace
+
+extern "C"
+{
+
+// mode 0: scalar parity driver (deterministic sampler) -> returns 0.0
+// mode 1: tiled_sched<simd::ray8> (AVX2) timed; returns best seconds over reps
+// mode 2: tiled_sched<ray> scalar timed
+double ref_frame(void const* fp_, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                 uint32_t const* indices, size_t n_idx, float const* normals16,
+                 void const* mats_, void const* lights_, float* rgba, int nthreads,
+                 int mode, int reps, int warmup, float* basis_out)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    scene_host s{ make_ref<tri_t>(prims, n_prims, nodes, n_nodes, indices, n_idx) };
+    fill_scene(s, fp, normals16, n_prims, (mat_pod const*)mats_, (light_pod const*)lights_);
+    bool use_matte = fp.n_materials > 0 && ((mat_pod const*)mats_)[0].kind == 1;
+
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+
+    auto lb = s.lights.data();
+    auto le = s.lights.data() + s.lights.size();
+    tri_ref_t const* pb = &s.ref;
+    tri_ref_t const* pe = &s.ref + 1;
+
+#define VSB_DISPATCH(KERNEL_EXPR, IS_RNG)                                                          \
+    do {                                                                                           \
+        auto k__ = KERNEL_EXPR;                                                                    \
+        if (mode == 0) { scalar_frame(k__, fp, rgba, nthreads, basis_out); return 0.0; }           \
+    } while (0)
+
+    if (fp.kernel == 2)
+    {
+        if (mode == 0)
+        {
+            ao_kernel<ray_t> k{ pb, pe, s.normals.data(), bg, fp.ao_samples, fp.ao_radius };
+            scalar_frame(k, fp, rgba, nthreads, basis_out);
+            return 0.0;
+        }
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+        if (mode == 1)
+        {
+            ao_tiled_adapter<simd::ray8> k{ { pb, pe, s.normals.data(), bg, fp.ao_samples, fp.ao_radius } };
+            return tiled_frame<simd::ray8>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+        }
+#endif
+        ao_tiled_adapter<ray_t> k{ { pb, pe, s.normals.data(), bg, fp.ao_samples, fp.ao_radius } };
+        return tiled_frame<ray_t>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+    }
+
+    // built-in kernels: plastic or matte material list
+    auto run = [&](auto kparams) -> double
+    {
+        using KP = decltype(kparams);
+        if (fp.kernel == 0)
+        {
+            simple::kernel<KP> k{ kparams };
+            if (mode == 0) { scalar_frame(no_sampler_adapter<simple::kernel<KP>>{ k }, fp, rgba, nthreads, basis_out); return 0.0; }
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+            if (mode == 1) return tiled_frame<simd::ray8>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+#endif
+            return tiled_frame<ray_t>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+        }
+        else if (fp.kernel == 1)
+        {
+            whitted::kernel<KP> k{ kparams };
+            if (mode == 0) { scalar_frame(no_sampler_adapter<whitted::kernel<KP>>{ k }, fp, rgba, nthreads, basis_out); return 0.0; }
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+            if (mode == 1) return tiled_frame<simd::ray8>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+#endif
+            return tiled_frame<ray_t>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+        }
+        else
+        {
+            pathtracing::kernel<KP> k{ kparams };
+            if (mode == 0) { scalar_frame(k, fp, rgba, nthreads, basis_out); return 0.0; }
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+            if (mode == 1) return tiled_frame<simd::ray8>(k, pixel_sampler::jittered_blend_type{}, fp, rgba, nthreads, reps, warmup);
+#endif
+            return tiled_frame<ray_t>(k, pixel_sampler::jittered_blend_type{}, fp, rgba, nthreads, reps, warmup);
+        }
+    };
+#undef VSB_DISPATCH
+
+    if (use_matte)
+    {
+        return run(make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(),
+                                      s.mattes.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb));
+    }
+    return run(make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(),
+                                  s.plastics.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb));
+}
+
+// Timed ray-list baseline: simd::ray8 packets of 8 consecutive rays, all threads.
+// Returns best seconds over reps.  hits_out may be NULL.
+double ref_query_timed(int any, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                       uint32_t const* indices, size_t n_idx, void const* rays, size_t n_rays,
+                       float max_t, int nthreads, int reps, int warmup, uint64_t* n_hits_out)
+{
+    auto ref = make_ref<tri_t>(prims, n_prims, nodes, n_nodes, indices, n_idx);
+    auto r = reinterpret_cast<ray_t const*>(rays);
+    double best = 1e30;
+    std::atomic<uint64_t> hits(0);
+    for (int it = 0; it < warmup + reps; ++it)
+    {
+        hits = 0;
+        auto t0 = std::chrono::steady_clock::now();
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+        size_t n_packets = n_rays / 8;
+        parallel_for(n_packets, nthreads, [&](size_t b, size_t e)
+        {
+            uint64_t local = 0;
+            for (size_t p = b; p < e; ++p)
+            {
+                std::array<ray_t, 8> rs;
+                for (int k = 0; k < 8; ++k) rs[k] = r[p * 8 + k];
+                simd::ray8 r8 = simd::pack(rs);
+                default_intersector isect;
+                if (any)
+                {
+                    auto hr = any_hit(r8, &ref, &ref + 1, simd::float8(max_t), isect);
+                    local += (uint64_t)__builtin_popcount((unsigned)_mm256_movemask_ps(hr.hit.f));
+                }
+                else
+                {
+                    auto hr = closest_hit(r8, &ref, &ref + 1, isect);
+                    local += (uint64_t)__builtin_popcount((unsigned)_mm256_movemask_ps(hr.hit.f));
+                }
+            }
+            hits += local;
+        });
+#else
+        parallel_for(n_rays, nthreads, [&](size_t b, size_t e)
+        {
+            uint64_t local = 0;
+            for (size_t i = b; i < e; ++i)
+            {
+                default_intersector isect;
+                if (any) local += any_hit(r[i], &ref, &ref + 1, max_t, isect).hit ? 1 : 0;
+                else     local += closest_hit(r[i], &ref, &ref + 1, isect).hit ? 1 : 0;
+            }
+            hits += local;
+        });
+#endif
+        auto t1 = std::chrono::steady_clock::now();
+        double dt = std::chrono::duration<double>(t1 - t0).count();
+        if (it >= warmup && dt < best) best = dt;
+    }
+    if (n_hits_out) *n_hits_out = hits.load();
+    return best;
+}
+
+int ref_simd_width()
+{
+#if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
+    return 8;
+#else
+    return 1;
+#endif
+}
+
+} // extern "C"

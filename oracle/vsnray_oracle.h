@@ -1,0 +1,106 @@
+/*
+ * vsnray_oracle.h -- TEST INFRASTRUCTURE ONLY.  Plain-C CPU restatement of the reference's
+ * ray-query hot path (tu500/visionaray @ 175062fa).  Only tests/, __graft_entry__.smoke() and
+ * bench.py's cpu_baseline / --impl reference legs may load this library, and only as the
+ * checker or the reported CPU baseline -- never as part of the product path.
+ *
+ * Parity status: PINNED.  The restatement is checked bit-for-bit (hit, ids, t, u, v,
+ * primitive_list_index) against the reference's own headers compiled here
+ * (oracle/_ref/libvsnray_ref.so, -ffp-contract=off) by tests/test_oracle_vs_ref.py, against
+ * the reference's known-answer test test/unittests/get_normal.cpp:17-75, and against golden
+ * vectors generated from the reference (tests/golden/, generator tests/golden/make_golden.py).
+ *
+ * Each function cites the reference file:line it follows (paths relative to
+ * /root/reference/include/visionaray/).
+ */
+#ifndef VSNRAY_ORACLE_H
+#define VSNRAY_ORACLE_H 1
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Same layouts as include/vsnray_b200.h (kept separate so the oracle has no dependency on
+ * the product headers). */
+typedef struct { float ori[3]; float pad0; float dir[3]; float pad1; } vso_ray;
+typedef struct { uint32_t geom_id, prim_id, pad0[2]; float v1[3], pad1, e1[3], pad2, e2[3], pad3; } vso_triangle;
+typedef struct { uint32_t geom_id, prim_id, pad0[2]; float center[3], pad1, radius, pad2[3]; } vso_sphere;
+typedef struct { float bbox_min[3]; uint32_t first; float bbox_max[3]; uint32_t num_prims; } vso_bvh_node;
+typedef struct { int32_t hit; uint32_t prim_id, geom_id; float t, u, v; uint32_t prim_list_index, pad; } vso_hit;
+typedef struct { float ca[3], ka, cd[3], kd, cs[3], ks, spec_exp; int32_t kind; float pad[2]; } vso_material;
+typedef struct { float pos[3], kl, cl[3], att_const, att_lin, att_quad, pad[2]; } vso_point_light;
+
+typedef struct {
+    int32_t  kernel;          /* 0 simple, 1 whitted, 2 ao, 3 pathtracing */
+    int32_t  pixel_sampler;   /* 0 uniform, 1 jittered, 2 jittered_blend */
+    int32_t  width, height;
+    float    eye[4], center[4], up[4];
+    float    fovy, aspect;
+    uint32_t frame_num, seed;
+    uint32_t num_bounces;
+    float    epsilon;
+    float    bg[4];
+    float    ambient[4];
+    int32_t  ao_samples;
+    float    ao_radius;
+    int32_t  n_lights, n_materials;
+} vso_frame_params;
+
+typedef struct {
+    int prim_kind;                 /* 0 triangles, 1 spheres */
+    const void* prims; size_t n_prims;
+    const vso_bvh_node* nodes; size_t n_nodes;
+    const uint32_t* indices; size_t n_indices;   /* NULL: primitive(i) = prims[i] (bvh.h:177-180) */
+} vso_bvh;
+
+/* per-ray-batch visit counters for the roofline denominator:
+ * counters[0] += inner-node steps (each reads both 32-B children), counters[1] += leaf
+ * primitives tested, counters[2] += rays */
+typedef struct { uint64_t n_inner, n_prim, n_rays, n_hits; } vso_counters;
+
+/* primitives (math/intersect.h) */
+void vso_intersect_triangle(const vso_ray* r, const vso_triangle* tri, vso_hit* out);
+void vso_intersect_sphere(const vso_ray* r, const vso_sphere* s, vso_hit* out);
+int  vso_intersect_aabb(const vso_ray* r, const float bmin[3], const float bmax[3],
+                        const float inv_dir[3], float* tnear, float* tfar);
+
+/* intersect<ClosestHit|AnyHit>(ray, bvh, isect, max_t) -- detail/bvh/intersect.inl:35-134 */
+void vso_intersect_bvh(int any, const vso_ray* r, const vso_bvh* b, float max_t, vso_hit* out,
+                       vso_counters* c);
+
+/* closest_hit()/any_hit() over a ray list (detail/traverse_linear.inl:186-318, one bvh) */
+void vso_query(int any, const vso_bvh* b, const vso_ray* rays, size_t n_rays, float max_t,
+               const float* max_t_per_ray, vso_hit* hits, vso_counters* counters, int nthreads);
+
+/* brute force over all primitives in list order (detail/traverse_linear.inl:26-63); used to
+ * classify t-ties */
+void vso_query_brute(int any, int prim_kind, const void* prims, size_t n_prims,
+                     const vso_ray* rays, size_t n_rays, float max_t, vso_hit* hits, int nthreads);
+
+/* camera basis (detail/cuda_sched.inl:259-266) and primary ray (detail/sched_common.h:130-150) */
+void vso_camera_basis(const vso_frame_params* p, float eye[3], float u[3], float v[3], float w[3]);
+void vso_primary_ray(float x, float y, int width, int height, const float eye[3],
+                     const float cu[3], const float cv[3], const float cw[3], vso_ray* out);
+
+/* deterministic counter-based sampler shared by oracle, reference harness and CUDA kernels */
+uint32_t vso_sampler_init(uint32_t pixel, uint32_t frame, uint32_t seed);
+float    vso_sampler_next(uint32_t* state);
+
+/* frame(): per pixel ray-gen + kernel + store/blend (detail/sched_common.h:361-528 and
+ * detail/{simple,whitted,pathtracing}.inl, src/examples/ao/main.cpp:183-246).
+ * rgba: width*height*4 floats, row-major, y up.  counters may be NULL. */
+void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals16,
+               const vso_material* mats, const vso_point_light* lights, float* rgba,
+               vso_counters* counters, int nthreads);
+
+/* max depth of the BVH2 (root = depth 1); the reference's traversal stack holds 31 entries
+ * (detail/stack.h:39-47, detail/bvh/intersect.inl:60) */
+int vso_bvh_max_depth(const vso_bvh* b);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,387 @@
+/*
+ * vsnray_oracle_frame.c -- TEST INFRASTRUCTURE ONLY (see vsnray_oracle.h).
+ *
+ * Scalar restatement of the frame() path: per pixel ray generation, the built-in kernels
+ * (simple / whitted / pathtracing) with the plastic / matte + point-light subset, the AO
+ * kernel of src/examples/ao/main.cpp, and the store / blend rules.  Paths cited are relative
+ * to /root/reference/include/visionaray/.  Shading uses libm (tanf/powf/sinf/cosf), so frame
+ * parity is a tolerance (1/255 per channel), not bit-exactness; the ray queries inside go
+ * through vso_intersect_bvh and are bit-exact.
+ */
+#define _GNU_SOURCE 1
+#include "vsnray_oracle.h"
+
+#include <float.h>
+#include <math.h>
+#include <pthread.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define VSO_PI      3.14159265358979323846f
+#define VSO_TWO_PI  6.28318530717958647692f
+#define VSO_INV_PI  0.31830988618379067154f
+
+typedef struct { float x, y, z; } v3;
+
+static inline v3 v3m(float x, float y, float z) { v3 r = { x, y, z }; return r; }
+static inline v3 add(v3 a, v3 b) { return v3m(a.x + b.x, a.y + b.y, a.z + b.z); }
+static inline v3 sub(v3 a, v3 b) { return v3m(a.x - b.x, a.y - b.y, a.z - b.z); }
+static inline v3 mul(v3 a, v3 b) { return v3m(a.x * b.x, a.y * b.y, a.z * b.z); }
+static inline v3 scale(v3 a, float s) { return v3m(a.x * s, a.y * s, a.z * s); }
+static inline v3 neg(v3 a) { return v3m(-a.x, -a.y, -a.z); }
+static inline float dot(v3 a, v3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+static inline v3 cross(v3 u, v3 v)
+{
+    return v3m(u.y * v.z - u.z * v.y, u.z * v.x - u.x * v.z, u.x * v.y - u.y * v.x);
+}
+static inline v3 normalize(v3 v) { return scale(v, 1.0f / sqrtf(dot(v, v))); }
+static inline float length(v3 v) { return sqrtf(dot(v, v)); }
+static inline v3 ld3(const float* p) { return v3m(p[0], p[1], p[2]); }
+static inline float fmax0(float x) { return 0.0f < x ? x : 0.0f; }   /* max(0, x) */
+
+/* math/detail/vector.inl:685-688 */
+static inline v3 reflect(v3 i, v3 n) { return sub(scale(n, 2.0f * dot(n, i)), i); }
+/* math/detail/vector.inl:674-681 */
+static inline v3 faceforward(v3 n, v3 i, v3 nref) { return dot(nref, i) < 0.0f ? neg(n) : n; }
+
+typedef struct
+{
+    const vso_frame_params* p;
+    const vso_bvh* b;
+    const float* normals;
+    const vso_material* mats;
+    const vso_point_light* lights;
+    float* rgba;
+    float eye[3], cu[3], cv[3], cw[3];
+} frame_ctx;
+
+static void closest(const frame_ctx* f, v3 o, v3 d, vso_hit* h, vso_counters* c)
+{
+    vso_ray r = { { o.x, o.y, o.z }, 0.0f, { d.x, d.y, d.z }, 0.0f };
+    vso_intersect_bvh(0, &r, f->b, FLT_MAX, h, c);
+}
+
+static int occluded(const frame_ctx* f, v3 o, v3 d, float max_t, vso_counters* c)
+{
+    vso_ray r = { { o.x, o.y, o.z }, 0.0f, { d.x, d.y, d.z }, 0.0f };
+    vso_hit h;
+    vso_intersect_bvh(1, &r, f->b, max_t, &h, c);
+    return h.hit;
+}
+
+/* point_light::intensity -- detail/point_light.inl:11-27 */
+static v3 light_intensity(const vso_point_light* l, v3 pos)
+{
+    float dist = length(sub(ld3(l->pos), pos));
+    float att = 1.0f / (l->att_const + l->att_lin * dist + l->att_quad * dist * dist);
+    return scale(scale(ld3(l->cl), l->kl), att);
+}
+
+/* lambertian::f -- brdf.h:33-41 */
+static v3 lambert_f(const vso_material* m) { return scale(scale(ld3(m->cd), m->kd), VSO_INV_PI); }
+
+/* blinn::f (plastic's specular lobe, material.h:322-323) -- brdf.h:107-119 */
+static v3 blinn_f(const vso_material* m, v3 n, v3 wo, v3 wi)
+{
+    v3 h = normalize(add(wo, wi));
+    float hdotn = fmax0(dot(h, n));
+    v3 spec = scale(ld3(m->cs), m->ks);
+    float sat = dot(wi, h);
+    sat = sat < 0.0f ? 0.0f : (sat > 1.0f ? 1.0f : sat);
+    float sch = powf(1.0f - sat, 5.0f);
+    v3 schlick = add(spec, scale(sub(v3m(1.0f, 1.0f, 1.0f), spec), sch));
+    float nfactor = (m->spec_exp + 2.0f) / (8.0f * VSO_PI);
+    return scale(scale(schlick, nfactor), powf(hdotn, m->spec_exp));
+}
+
+/* plastic::shade -- detail/material/plastic.inl:18-37; matte::shade -- matte.inl:18-39 */
+static v3 shade(const vso_material* m, const vso_point_light* l, v3 pos, v3 n, v3 wo, v3 wi)
+{
+    float ndotl = fmax0(dot(n, wi));
+    v3 f = lambert_f(m);
+    if (m->kind == 0) f = add(f, blinn_f(m, n, wo, wi));
+    return scale(mul(scale(f, VSO_PI), light_intensity(l, pos)), ndotl);
+}
+
+static v3 rgb_of_rgba(const float c[4]) { return v3m(c[0] * c[3], c[1] * c[3], c[2] * c[3]); }   /* from_rgba, detail/spectrum.inl:375-378 */
+
+/* simple::kernel -- detail/simple.inl:25-75 */
+static void kernel_simple(const frame_ctx* f, v3 o, v3 d, float out[4], vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    vso_hit h;
+    closest(f, o, d, &h, c);
+    if (!h.hit) { memcpy(out, p->bg, 16); return; }
+    v3 pos = add(o, scale(d, h.t));
+    const vso_material* m = &f->mats[h.geom_id];
+    v3 n = ld3(f->normals + 4 * (size_t)h.prim_id);   /* normals[hr.prim_id], get_normal.h:28-37 */
+    v3 shaded = mul(scale(ld3(m->ca), m->ka), rgb_of_rgba(p->ambient));
+    v3 view = neg(d);
+    n = faceforward(n, view, n);
+    for (int i = 0; i < p->n_lights; ++i)
+    {
+        v3 wi = normalize(sub(ld3(f->lights[i].pos), pos));
+        shaded = add(shaded, shade(m, &f->lights[i], pos, n, view, wi));
+    }
+    out[0] = shaded.x; out[1] = shaded.y; out[2] = shaded.z; out[3] = 1.0f;
+}
+
+/* whitted::kernel -- detail/whitted.inl:227-323; specular_bounce :79-110 (plastic: kr 0.1,
+ * matte: kr 0) */
+static void kernel_whitted(const frame_ctx* f, v3 o, v3 d, float out[4], vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    vso_hit h;
+    closest(f, o, d, &h, c);
+    if (!h.hit) { memcpy(out, p->bg, 16); return; }
+
+    v3 color = v3m(0.0f, 0.0f, 0.0f);
+    unsigned depth = 0;
+    float throughput = 1.0f;
+    while (h.hit && throughput > p->epsilon && depth++ < p->num_bounces)
+    {
+        v3 pos = add(o, scale(d, h.t));
+        const vso_material* m = &f->mats[h.geom_id];
+        v3 sn = ld3(f->normals + 4 * (size_t)h.prim_id);
+        v3 shaded = mul(scale(ld3(m->ca), m->ka), rgb_of_rgba(p->ambient));
+        v3 view = neg(d);
+        v3 n = faceforward(sn, view, sn);
+        for (int i = 0; i < p->n_lights; ++i)
+        {
+            v3 lpos = ld3(f->lights[i].pos);
+            v3 wi = normalize(sub(lpos, pos));
+            v3 so = add(pos, scale(wi, p->epsilon));
+            float ld = length(sub(pos, lpos));
+            if (!occluded(f, so, wi, ld, c))
+                shaded = add(shaded, shade(m, &f->lights[i], pos, n, view, wi));
+        }
+        color = add(color, scale(shaded, throughput));
+
+        float kr = (m->kind == 0) ? 0.1f : 0.0f;
+        if (kr > 0.0f)
+        {
+            v3 dir = reflect(view, sn);
+            o = add(pos, scale(dir, p->epsilon));
+            d = dir;
+            closest(f, o, d, &h, c);
+        }
+        throughput *= kr;
+    }
+    out[0] = color.x; out[1] = color.y; out[2] = color.z; out[3] = 1.0f;
+}
+
+/* make_orthonormal_basis -- math/detail/vector3.inl:357-367 */
+static void ortho_basis(v3* u, v3* v, v3 w)
+{
+    if (fabsf(w.x) > fabsf(w.y)) *v = normalize(v3m(-w.z, 0.0f, w.x));
+    else                         *v = normalize(v3m(0.0f, w.z, -w.y));
+    *u = cross(*v, w);
+}
+
+/* cosine_sample_hemisphere -- sampling.h:61-71 */
+static v3 cosine_sample_hemisphere(float u1, float u2)
+{
+    float r = sqrtf(u1);
+    float theta = VSO_TWO_PI * u2;
+    float x = r * cosf(theta);
+    float y = r * sinf(theta);
+    float z = sqrtf(fmax0(1.0f - u1));
+    return v3m(x, y, z);
+}
+
+/* AO kernel -- src/examples/ao/main.cpp:183-246 (no faceforward; offset 1e-3 along dir) */
+static void kernel_ao(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, float out[4], vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    vso_hit h;
+    closest(f, o, d, &h, c);
+    if (!h.hit) { memcpy(out, p->bg, 16); return; }
+    v3 pos = add(o, scale(d, h.t));
+    v3 w = ld3(f->normals + 4 * (size_t)h.prim_id);
+    v3 u, v;
+    ortho_basis(&u, &v, w);
+    float clr = 1.0f;
+    float dec = 1.0f / (float)p->ao_samples;
+    for (int i = 0; i < p->ao_samples; ++i)
+    {
+        float u1 = vso_sampler_next(samp);
+        float u2 = vso_sampler_next(samp);
+        v3 sp = cosine_sample_hemisphere(u1, u2);
+        v3 dir = normalize(add(add(scale(u, sp.x), scale(v, sp.y)), scale(w, sp.z)));
+        v3 ao_o = add(pos, scale(dir, 1E-3f));
+        if (occluded(f, ao_o, dir, p->ao_radius, c)) clr = clr - dec;
+    }
+    out[0] = clr; out[1] = clr; out[2] = clr; out[3] = 1.0f;
+}
+
+/* lambertian::sample_f -- brdf.h:43-61 */
+static v3 lambert_sample(const vso_material* m, v3 n, v3* wi, float* pdf, uint32_t* samp)
+{
+    v3 u, v;
+    ortho_basis(&u, &v, n);
+    float u1 = vso_sampler_next(samp);
+    float u2 = vso_sampler_next(samp);
+    v3 sp = cosine_sample_hemisphere(u1, u2);
+    *wi = normalize(add(add(scale(u, sp.x), scale(v, sp.y)), scale(n, sp.z)));
+    *pdf = dot(n, *wi) * VSO_INV_PI;
+    return lambert_f(m);
+}
+
+/* blinn::sample_f -- brdf.h:121-150 */
+static v3 blinn_sample(const vso_material* m, v3 n, v3 wo, v3* wi, float* pdf, uint32_t* samp)
+{
+    float u1 = vso_sampler_next(samp);
+    float u2 = vso_sampler_next(samp);
+    float e = m->spec_exp;
+    float costheta = powf(u1, 1.0f / (e + 1.0f));
+    float sintheta = sqrtf(fmax0(1.0f - costheta * costheta));
+    float phi = u2 * VSO_TWO_PI;
+    v3 u, v;
+    ortho_basis(&u, &v, n);
+    v3 h = normalize(add(add(scale(u, sintheta * cosf(phi)), scale(v, sintheta * sinf(phi))), scale(n, costheta)));
+    *wi = reflect(wo, h);
+    float vdoth = dot(wo, h);
+    *pdf = ((e + 1.0f) * powf(costheta, e)) / (2.0f * VSO_PI * 4.0f * vdoth);
+    return blinn_f(m, n, wo, *wi);
+}
+
+/* plastic::sample_impl -- detail/material/plastic.inl:186-229; matte::sample_impl -- matte.inl:147-155 */
+static v3 material_sample(const vso_material* m, v3 n, v3 wo, v3* wi, float* pdf, uint32_t* samp)
+{
+    if (m->kind == 1) return lambert_sample(m, n, wi, pdf, samp);
+    float prob_diff = ((m->cd[0] + m->cd[1] + m->cd[2]) / 3.0f) * m->kd;
+    float prob_spec = ((m->cs[0] + m->cs[1] + m->cs[2]) / 3.0f) * m->ks;
+    if (prob_diff == 0.0f && prob_spec == 0.0f) { prob_diff = 0.5f; prob_spec = 0.5f; }
+    prob_diff = prob_diff / (prob_diff + prob_spec);
+    float u = vso_sampler_next(samp);
+    if (u < prob_diff) return lambert_sample(m, n, wi, pdf, samp);
+    return blinn_sample(m, n, wo, wi, pdf, samp);
+}
+
+/* pathtracing::kernel -- detail/pathtracing.inl:29-121 (no emissive materials in the subset) */
+static void kernel_pathtracing(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, float out[4], vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    int active = 1, result_hit = 0;
+    v3 dst = v3m(1.0f, 1.0f, 1.0f);
+    for (unsigned bounce = 0; bounce < p->num_bounces; ++bounce)
+    {
+        vso_hit h;
+        closest(f, o, d, &h, c);
+        if (active && !h.hit) dst = mul(dst, rgb_of_rgba(p->ambient));
+        active = active && h.hit;
+        if (!active) break;
+        if (bounce == 0) result_hit = h.hit;
+
+        v3 view = neg(d);
+        const vso_material* m = &f->mats[h.geom_id];
+        v3 sn = ld3(f->normals + 4 * (size_t)h.prim_id);
+        v3 n = faceforward(sn, view, sn);
+        v3 refl; float pdf = 0.0f;
+        v3 src = material_sample(m, n, view, &refl, &pdf, samp);
+        int zero_pdf = pdf <= 0.0f;
+        src = scale(src, dot(n, refl) / pdf);
+        if (!zero_pdf) dst = mul(dst, src);
+        else           dst = v3m(0.0f, 0.0f, 0.0f);
+        active = active && !zero_pdf;
+        if (!active) break;
+        v3 pos = add(o, scale(d, h.t));
+        o = add(pos, scale(refl, p->epsilon));
+        d = refl;
+    }
+    if (active) dst = v3m(0.0f, 0.0f, 0.0f);
+    if (result_hit) { out[0] = dst.x; out[1] = dst.y; out[2] = dst.z; out[3] = 1.0f; }
+    else memcpy(out, p->bg, 16);
+}
+
+typedef struct { frame_ctx* f; size_t b, e; vso_counters c; } frame_job;
+
+static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    size_t w = (size_t)p->width;
+    for (size_t i = b; i < e; ++i)
+    {
+        unsigned x = (unsigned)(i % w), y = (unsigned)(i / w);
+        uint32_t samp = vso_sampler_init((uint32_t)i, p->frame_num, p->seed);
+        float px = (float)x, py = (float)y;
+        if (p->pixel_sampler != 0)
+        {
+            /* jittered: detail/sched_common.h:197-217 */
+            float jx = vso_sampler_next(&samp) - 0.5f;
+            float jy = vso_sampler_next(&samp) - 0.5f;
+            px += jx; py += jy;
+        }
+        vso_ray r;
+        vso_primary_ray(px, py, p->width, p->height, f->eye, f->cu, f->cv, f->cw, &r);
+        v3 o = ld3(r.ori), d = ld3(r.dir);
+        float col[4];
+        switch (p->kernel)
+        {
+        case 0: kernel_simple(f, o, d, col, c); break;
+        case 1: kernel_whitted(f, o, d, col, c); break;
+        case 2: kernel_ao(f, o, d, &samp, col, c); break;
+        default: kernel_pathtracing(f, o, d, &samp, col, c); break;
+        }
+        float* dst = f->rgba + i * 4;
+        if (p->pixel_sampler == 2)
+        {
+            /* jittered_blend: detail/sched_common.h:516-528 */
+            float alpha = 1.0f / (float)p->frame_num;
+            for (int k = 0; k < 4; ++k) dst[k] = col[k] * alpha + dst[k] * (1.0f - alpha);
+        }
+        else
+        {
+            /* uniform / jittered store: detail/pixel_access.h:38-58 */
+            for (int k = 0; k < 4; ++k) dst[k] = col[k];
+        }
+    }
+}
+
+typedef struct { frame_ctx* f; size_t n; size_t* next; pthread_mutex_t* mu; vso_counters c; } fworker;
+
+static void* fworker_main(void* q)
+{
+    fworker* w = (fworker*)q;
+    for (;;)
+    {
+        size_t b;
+        pthread_mutex_lock(w->mu);
+        b = *w->next; *w->next += 1024;
+        pthread_mutex_unlock(w->mu);
+        if (b >= w->n) break;
+        size_t e = b + 1024 < w->n ? b + 1024 : w->n;
+        frame_range(w->f, b, e, &w->c);
+    }
+    return NULL;
+}
+
+void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals16,
+               const vso_material* mats, const vso_point_light* lights, float* rgba,
+               vso_counters* counters, int nthreads)
+{
+    frame_ctx f;
+    memset(&f, 0, sizeof(f));
+    f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights; f.rgba = rgba;
+    vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
+    if (nthreads < 1) nthreads = 1;
+    if (nthreads > 256) nthreads = 256;
+    size_t n = (size_t)p->width * (size_t)p->height, next = 0;
+    pthread_mutex_t mu = PTHREAD_MUTEX_INITIALIZER;
+    fworker* ws = (fworker*)calloc((size_t)nthreads, sizeof(fworker));
+    pthread_t* ts = (pthread_t*)calloc((size_t)nthreads, sizeof(pthread_t));
+    for (int i = 0; i < nthreads; ++i) { ws[i].f = &f; ws[i].n = n; ws[i].next = &next; ws[i].mu = &mu; }
+    if (nthreads == 1) fworker_main(&ws[0]);
+    else
+    {
+        for (int i = 0; i < nthreads; ++i) pthread_create(&ts[i], NULL, fworker_main, &ws[i]);
+        for (int i = 0; i < nthreads; ++i) pthread_join(ts[i], NULL);
+    }
+    if (counters)
+        for (int i = 0; i < nthreads; ++i)
+        {
+            counters->n_inner += ws[i].c.n_inner; counters->n_prim += ws[i].c.n_prim;
+            counters->n_rays += ws[i].c.n_rays;   counters->n_hits += ws[i].c.n_hits;
+        }
+    free(ws); free(ts);
+}
