@@ -1,0 +1,174 @@
+"""TEST INFRASTRUCTURE ONLY -- ctypes bindings of the CPU oracle.
+
+* ``oracle/libvsnray_oracle.so``         plain-C restatement (vsnray_oracle.c), built anywhere.
+* ``oracle/_ref/libvsnray_ref.so``       the UNMODIFIED reference headers behind ref_harness.cpp,
+  parity build (-ffp-contract=off); prebuilt in the build container, travels to the GPU box.
+* ``oracle/_ref/libvsnray_ref_fast.so``  same, -O3 -mavx2 -mfma: the timed CPU baseline.
+
+Only tests/, __graft_entry__.smoke() and bench.py (cpu_baseline / --impl reference) may import
+this module.  The product package (visionaray_b200/) never does.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+HIT_DTYPE = np.dtype(
+    [("hit", "<i4"), ("prim_id", "<u4"), ("geom_id", "<u4"), ("t", "<f4"), ("u", "<f4"), ("v", "<f4"),
+     ("prim_list_index", "<u4"), ("pad", "<u4")]
+)
+
+
+class Bvh(C.Structure):
+    _fields_ = [("prim_kind", C.c_int), ("prims", C.c_void_p), ("n_prims", C.c_size_t),
+                ("nodes", C.c_void_p), ("n_nodes", C.c_size_t), ("indices", C.c_void_p), ("n_indices", C.c_size_t)]
+
+
+class Counters(C.Structure):
+    _fields_ = [("n_inner", C.c_uint64), ("n_prim", C.c_uint64), ("n_rays", C.c_uint64), ("n_hits", C.c_uint64)]
+
+
+def _p(a):
+    return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
+
+
+_oracle = None
+_ref = {}
+
+
+def oracle_lib():
+    global _oracle
+    if _oracle is None:
+        path = os.path.join(_HERE, "libvsnray_oracle.so")
+        if not os.path.exists(path):
+            raise RuntimeError(f"{path} missing: run `make -C oracle oracle` (or __graft_entry__.build())")
+        lib = C.CDLL(path)
+        vp, sz = C.c_void_p, C.c_size_t
+        lib.vso_query.argtypes = [C.c_int, C.POINTER(Bvh), vp, sz, C.c_float, vp, vp, C.POINTER(Counters), C.c_int]
+        lib.vso_query_brute.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, C.c_float, vp, C.c_int]
+        lib.vso_frame.argtypes = [vp, C.POINTER(Bvh), vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
+        lib.vso_camera_basis.argtypes = [vp, vp, vp, vp, vp]
+        lib.vso_bvh_max_depth.argtypes = [C.POINTER(Bvh)]
+        lib.vso_sampler_init.restype = C.c_uint32
+        lib.vso_sampler_init.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
+        lib.vso_sampler_next.restype = C.c_float
+        lib.vso_sampler_next.argtypes = [C.POINTER(C.c_uint32)]
+        _oracle = lib
+    return _oracle
+
+
+def ref_available(fast: bool = False) -> bool:
+    return os.path.exists(os.path.join(_HERE, "_ref", "libvsnray_ref_fast.so" if fast else "libvsnray_ref.so"))
+
+
+def ref_lib(fast: bool = False):
+    key = bool(fast)
+    if key not in _ref:
+        path = os.path.join(_HERE, "_ref", "libvsnray_ref_fast.so" if fast else "libvsnray_ref.so")
+        lib = C.CDLL(path)
+        vp, sz = C.c_void_p, C.c_size_t
+        lib.ref_layout.argtypes = [C.POINTER(C.c_int)]
+        for f in (lib.ref_build_triangles, lib.ref_build_spheres):
+            f.argtypes = [vp, sz, C.c_int, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        lib.ref_query.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, vp, vp, C.c_int]
+        lib.ref_frame.restype = C.c_double
+        lib.ref_frame.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+        lib.ref_query_timed.restype = C.c_double
+        lib.ref_query_timed.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int,
+                                        C.POINTER(C.c_uint64)]
+        _ref[key] = lib
+    return _ref[key]
+
+
+def make_bvh(scene) -> Bvh:
+    """scene: visionaray_b200.scenes.HostScene (kept alive by the caller)."""
+    b = Bvh()
+    b.prim_kind = scene.prim_kind
+    b.prims = scene.prims.ctypes.data
+    b.n_prims = scene.prims.shape[0]
+    b.nodes = scene.nodes.ctypes.data
+    b.n_nodes = scene.nodes.shape[0]
+    b.indices = scene.indices.ctypes.data if scene.indices is not None else None
+    b.n_indices = scene.indices.shape[0] if scene.indices is not None else 0
+    return b
+
+
+def oracle_query(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_per_ray=None, nthreads=0,
+                 counters=None):
+    hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+    b = make_bvh(scene)
+    c = counters if counters is not None else Counters()
+    oracle_lib().vso_query(int(any_hit), C.byref(b), _p(rays), rays.shape[0], max_t, _p(max_t_per_ray), _p(hits),
+                           C.byref(c), nthreads or (os.cpu_count() or 1))
+    return hits
+
+
+def oracle_brute(scene, rays, any_hit=False, max_t=3.4028234663852886e38, nthreads=0):
+    hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+    oracle_lib().vso_query_brute(int(any_hit), scene.prim_kind, _p(scene.prims), scene.prims.shape[0], _p(rays),
+                                 rays.shape[0], max_t, _p(hits), nthreads or (os.cpu_count() or 1))
+    return hits
+
+
+def oracle_frame(scene, fp, materials, lights, rgba=None, nthreads=0, counters=None):
+    w, h = fp.width, fp.height
+    if rgba is None:
+        rgba = np.zeros((h, w, 4), dtype=np.float32)
+    b = make_bvh(scene)
+    c = counters if counters is not None else Counters()
+    oracle_lib().vso_frame(C.byref(fp), C.byref(b), _p(scene.normals), _p(materials), _p(lights), _p(rgba),
+                           C.byref(c), nthreads or (os.cpu_count() or 1))
+    return rgba
+
+
+def oracle_max_depth(scene) -> int:
+    b = make_bvh(scene)
+    return int(oracle_lib().vso_bvh_max_depth(C.byref(b)))
+
+
+def ref_build(prim_kind, prims, spatial_splits=False):
+    lib = ref_lib()
+    n = prims.shape[0]
+    nodes = np.zeros(max(2 * n - 1, 1) * (4 if spatial_splits else 1), dtype=np.dtype(
+        [("bbox_min", "<f4", (3,)), ("first", "<u4"), ("bbox_max", "<f4", (3,)), ("num_prims", "<u4")]))
+    idx = np.zeros(max(n, 1) * (4 if spatial_splits else 1), dtype=np.uint32)
+    nn, ni = C.c_size_t(0), C.c_size_t(0)
+    f = lib.ref_build_triangles if prim_kind == 0 else lib.ref_build_spheres
+    rc = f(_p(prims), n, int(spatial_splits), _p(nodes), nodes.shape[0], C.byref(nn), _p(idx), idx.shape[0], C.byref(ni))
+    if rc != 0:
+        raise RuntimeError("ref_build: capacity")
+    return nodes[: nn.value].copy(), idx[: ni.value].copy()
+
+
+def ref_query(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_per_ray=None, nthreads=0):
+    hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+    ref_lib().ref_query(scene.prim_kind, int(any_hit), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes),
+                        scene.nodes.shape[0], _p(scene.indices), scene.indices.shape[0], _p(rays), rays.shape[0],
+                        max_t, _p(max_t_per_ray), _p(hits), nthreads or (os.cpu_count() or 1))
+    return hits
+
+
+def ref_frame(scene, fp, materials, lights, rgba=None, nthreads=0, mode=0, reps=1, warmup=0, fast=False):
+    """mode 0: scalar parity driver; 1: tiled_sched<ray8>; 2: tiled_sched<ray>. Returns (rgba, seconds)."""
+    w, h = fp.width, fp.height
+    if rgba is None:
+        rgba = np.zeros((h, w, 4), dtype=np.float32)
+    basis = np.zeros(12, dtype=np.float32)
+    secs = ref_lib(fast).ref_frame(C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes),
+                                   scene.nodes.shape[0], _p(scene.indices), scene.indices.shape[0], _p(scene.normals),
+                                   _p(materials), _p(lights), _p(rgba), nthreads or (os.cpu_count() or 1), mode, reps,
+                                   warmup, _p(basis))
+    return rgba, secs, basis
+
+
+def ref_query_timed(scene, rays, any_hit=False, max_t=3.4028234663852886e38, nthreads=0, reps=1, warmup=0):
+    nh = C.c_uint64(0)
+    secs = ref_lib(True).ref_query_timed(int(any_hit), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes),
+                                         scene.nodes.shape[0], _p(scene.indices), scene.indices.shape[0], _p(rays),
+                                         rays.shape[0], max_t, nthreads or (os.cpu_count() or 1), reps, warmup,
+                                         C.byref(nh))
+    return secs, nh.value

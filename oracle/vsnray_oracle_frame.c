@@ -204,8 +204,11 @@ static void kernel_ao(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, float out[
     float dec = 1.0f / (float)p->ao_samples;
     for (int i = 0; i < p->ao_samples; ++i)
     {
-        float u1 = vso_sampler_next(samp);
+        /* cosine_sample_hemisphere(samp.next(), samp.next()): the argument evaluation order is
+         * unspecified in C++; g++ (the compiler the reference is built with here) evaluates
+         * right to left, so the FIRST draw is u2.  Pinned by tests/test_oracle_vs_ref.py. */
         float u2 = vso_sampler_next(samp);
+        float u1 = vso_sampler_next(samp);
         v3 sp = cosine_sample_hemisphere(u1, u2);
         v3 dir = normalize(add(add(scale(u, sp.x), scale(v, sp.y)), scale(w, sp.z)));
         v3 ao_o = add(pos, scale(dir, 1E-3f));
@@ -219,8 +222,8 @@ static v3 lambert_sample(const vso_material* m, v3 n, v3* wi, float* pdf, uint32
 {
     v3 u, v;
     ortho_basis(&u, &v, n);
+    float u2 = vso_sampler_next(samp);   /* right-to-left argument evaluation, see kernel_ao */
     float u1 = vso_sampler_next(samp);
-    float u2 = vso_sampler_next(samp);
     v3 sp = cosine_sample_hemisphere(u1, u2);
     *wi = normalize(add(add(scale(u, sp.x), scale(v, sp.y)), scale(n, sp.z)));
     *pdf = dot(n, *wi) * VSO_INV_PI;

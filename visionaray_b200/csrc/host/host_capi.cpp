@@ -1,0 +1,86 @@
+// host_capi.cpp -- extern "C" wrappers around the host C++ layer (scene generators, binned-SAH
+// builder) for the Python harness (tests/, bench.py).  Built into libvsnray_b200_host.so.
+// Pure host code: no CUDA, no oracle.
+
+#include <cstdint>
+#include <cstring>
+#include <vector>
+
+#include "visionaray_b200/bvh.h"
+#include "scenes.h"
+
+using namespace visionaray_b200;
+
+extern "C"
+{
+
+// kind: 1 uv_sphere(a=slices, b=stacks), 2 displaced_grid(a=n, seed), 3 cube_field(a=n_cubes, seed),
+//       5 soup(a=n, seed, s=fparam)
+// returns the number of triangles; writes up to cap triangles (64 B each) when out != NULL
+size_t vsbh_gen_triangles(int kind, long a, long b, uint64_t seed, float fparam, void* out, size_t cap)
+{
+    std::vector<scenes::triangle> tris;
+    switch (kind)
+    {
+    case 1: scenes::uv_sphere(tris, int(a), int(b), fparam > 0.0f ? fparam : 1.0f); break;
+    case 2: scenes::displaced_grid(tris, int(a), seed, fparam > 0.0f ? fparam : 0.15f); break;
+    case 3: scenes::cube_field(tris, int(a), seed); break;
+    case 5: scenes::soup(tris, size_t(a), seed, fparam > 0.0f ? fparam : 0.004f); break;
+    default: return 0;
+    }
+    if (out && cap >= tris.size()) std::memcpy(out, tris.data(), tris.size() * sizeof(scenes::triangle));
+    return tris.size();
+}
+
+size_t vsbh_gen_spheres(size_t n, uint64_t seed, float r_lo, float r_hi, void* out)
+{
+    std::vector<scenes::sphere> s;
+    scenes::sphere_cloud(s, n, seed, r_lo, r_hi);
+    std::memcpy(out, s.data(), n * sizeof(scenes::sphere));
+    return n;
+}
+
+void vsbh_gen_random_rays(void* out, size_t n, uint64_t seed, float lo, float hi)
+{
+    scenes::random_rays(reinterpret_cast<ray*>(out), n, seed, lo, hi);
+}
+
+void vsbh_face_normals(const void* tris, size_t n, void* normals16)
+{
+    auto t = reinterpret_cast<scenes::triangle const*>(tris);
+    auto o = reinterpret_cast<vec3*>(normals16);
+    for (size_t i = 0; i < n; ++i) o[i] = normalize(cross(t[i].e1, t[i].e2));
+}
+
+// build<index_bvh<P>>(); prim_kind 0 triangles, 1 spheres.  nodes_out needs 2n-1 entries,
+// idx_out n entries.
+int vsbh_build_bvh(int prim_kind, const void* prims, size_t n, void* nodes_out, size_t nodes_cap,
+                   size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx)
+{
+    try
+    {
+        if (prim_kind == 0)
+        {
+            auto t = build<index_bvh<basic_triangle<3, float>>>(reinterpret_cast<basic_triangle<3, float> const*>(prims), n);
+            *n_nodes = t.num_nodes(); *n_idx = t.num_indices();
+            if (*n_nodes > nodes_cap || *n_idx > idx_cap) return 1;
+            std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
+            std::memcpy(idx_out, t.indices().data(), *n_idx * sizeof(uint32_t));
+        }
+        else
+        {
+            auto t = build<index_bvh<basic_sphere<float>>>(reinterpret_cast<basic_sphere<float> const*>(prims), n);
+            *n_nodes = t.num_nodes(); *n_idx = t.num_indices();
+            if (*n_nodes > nodes_cap || *n_idx > idx_cap) return 1;
+            std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
+            std::memcpy(idx_out, t.indices().data(), *n_idx * sizeof(uint32_t));
+        }
+    }
+    catch (...)
+    {
+        return 2;
+    }
+    return 0;
+}
+
+} // extern "C"
