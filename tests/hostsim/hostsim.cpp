@@ -1,0 +1,111 @@
+// TEST-ONLY: host instantiation of the product's host/device headers (csrc/*.cuh) so that the
+// BVH2 -> BVH8 collapse, the quantised slab test and both traversal loops can be checked on
+// the CPU in the no-GPU test tier.  libvsnray_b200.so does not contain or export any of this.
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+
+#include "../../visionaray_b200/csrc/bvh8_traverse.cuh"
+#include "../../visionaray_b200/csrc/bvh2_exact.cuh"
+
+using namespace vsb;
+
+namespace
+{
+struct Alloc
+{
+    uint32_t* counter;
+    uint32_t operator()(uint32_t n) { uint32_t r = *counter; *counter += n; return r; }
+};
+
+struct HostWide
+{
+    std::vector<Node80> nodes;
+    std::vector<uint8_t> prims;
+    int prim_kind;
+    int levels;
+};
+}
+
+extern "C"
+{
+
+void* hs_build(int prim_kind, const void* prims, size_t n_prims, const void* nodes2, size_t n_nodes2,
+               const uint32_t* indices, size_t n_idx)
+{
+    (void)n_prims;
+    auto* w = new HostWide();
+    w->prim_kind = prim_kind;
+    const Node32* n2 = reinterpret_cast<const Node32*>(nodes2);
+    size_t n_list = indices ? n_idx : n_prims;
+    w->nodes.resize(n_nodes2 ? n_nodes2 : 1);
+    std::vector<uint32_t> leaf_list(n_list + 1);
+    std::vector<WideTask> cur(1), next(n_nodes2 + 1);
+    cur[0].bvh2_node = 0; cur[0].wide_index = 0;
+    uint32_t node_count = 1, prim_count = 0;
+    w->levels = 0;
+    while (!cur.empty())
+    {
+        uint32_t task_count = 0;
+        Alloc an{ &node_count }, ap{ &prim_count }, at{ &task_count };
+        for (auto const& t : cur) collapse_node(t, n2, w->nodes.data(), leaf_list.data(), next.data(), an, ap, at);
+        cur.assign(next.begin(), next.begin() + task_count);
+        ++w->levels;
+    }
+    w->nodes.resize(node_count);
+    size_t rec = prim_kind == 0 ? sizeof(TriRec) : sizeof(SphRec);
+    w->prims.resize((size_t)prim_count * rec + 16);
+    for (uint32_t i = 0; i < prim_count; ++i) make_prim_record(prim_kind, prims, indices, leaf_list[i], w->prims.data(), i);
+    return w;
+}
+
+void hs_free(void* h) { delete reinterpret_cast<HostWide*>(h); }
+
+void hs_stats(void* h, uint64_t* out)
+{
+    auto* w = reinterpret_cast<HostWide*>(h);
+    out[0] = w->nodes.size();
+    out[1] = w->prims.size() / (w->prim_kind == 0 ? sizeof(TriRec) : sizeof(SphRec));
+    out[2] = (uint64_t)w->levels;
+}
+
+const void* hs_nodes(void* h) { return reinterpret_cast<HostWide*>(h)->nodes.data(); }
+const void* hs_prims(void* h) { return reinterpret_cast<HostWide*>(h)->prims.data(); }
+
+void hs_query_wide(void* h, int any, const void* rays, size_t n_rays, float max_t, const float* max_t_per_ray, void* hits)
+{
+    auto* w = reinterpret_cast<HostWide*>(h);
+    WideScene s{ w->nodes.data(), w->prims.data(), w->prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    Hit32* out = reinterpret_cast<Hit32*>(hits);
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        RayCtx rc;
+        ray_ctx_init(rc, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz);
+        HitReg b;
+        float mt = max_t_per_ray ? max_t_per_ray[i] : max_t;
+        if (any) trace_wide<true>(s, rc, mt, b); else trace_wide<false>(s, rc, mt, b);
+        out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
+        out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
+    }
+}
+
+void hs_query_exact(int prim_kind, int any, const void* prims, const void* nodes2, const uint32_t* indices,
+                    const void* rays, size_t n_rays, float max_t, const float* max_t_per_ray, void* hits)
+{
+    ExactScene s{ reinterpret_cast<const Node32*>(nodes2), prims, indices, prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    Hit32* out = reinterpret_cast<Hit32*>(hits);
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        HitReg b;
+        float mt = max_t_per_ray ? max_t_per_ray[i] : max_t;
+        if (any) trace_exact<true>(s, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz, mt, b);
+        else     trace_exact<false>(s, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz, mt, b);
+        out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
+        out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
+    }
+}
+
+} // extern "C"
