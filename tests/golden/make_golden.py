@@ -1,0 +1,50 @@
+"""Generates tests/golden/*.npz FROM THE REFERENCE ITSELF (oracle/_ref/libvsnray_ref.so, i.e. the
+unmodified headers under /root/reference/include compiled by oracle/Makefile).  Run in the
+build container only:   python tests/golden/make_golden.py
+The fixtures pin the oracle restatement where /root/reference is absent (the GPU box).
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+
+from oracle import bindings as O  # noqa: E402
+from visionaray_b200 import scenes as S  # noqa: E402
+
+FLT_MAX = 3.4028234663852886e38
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def main():
+    assert O.ref_available(), "oracle/_ref missing: run `make -C oracle ref` where /root/reference exists"
+    out = {}
+    tris = S.gen_triangles(5, 600, 0, 21, 0.08)                 # small soup
+    sph = S.gen_spheres(300, 22, 0.02, 0.12)
+    for key, kind, prims, lo, hi in (("tri", 0, tris, -0.2, 1.2), ("sph", 1, sph, -1.3, 1.3)):
+        nodes, idx = O.ref_build(kind, prims)                    # the REFERENCE builder
+        sc = S.HostScene(kind, prims, nodes, idx, None, key)
+        rays = S.random_rays(2000, 23, lo, hi)
+        out[f"{key}_prims"] = prims
+        out[f"{key}_nodes"] = nodes.view(np.uint8)
+        out[f"{key}_indices"] = idx
+        out[f"{key}_rays"] = rays
+        out[f"{key}_closest"] = O.ref_query(sc, rays, False, FLT_MAX).view(np.uint8)
+        out[f"{key}_any"] = O.ref_query(sc, rays, True, 0.4).view(np.uint8)
+    np.savez_compressed(os.path.join(HERE, "golden_queries.npz"), **out)
+
+    sc = S.make_scene("cfg1_sphere", 0.01)
+    eye = (0.0, 0.0, 3.0)
+    frames = {}
+    for kernel, ps, mat in ((0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 2, 1)):
+        fp = S.frame_params(kernel, 32, 24, eye, (0, 0, 0), pixel_sampler=ps, ambient=(1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0))
+        img, _, _ = O.ref_frame(sc, fp, S.default_material(mat), S.point_light(eye), mode=0)
+        frames[f"k{kernel}"] = img
+    np.savez_compressed(os.path.join(HERE, "golden_frames.npz"), **frames)
+    print("wrote golden_queries.npz, golden_frames.npz")
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,172 @@
+"""Python mirror of the host adaptor above the C ABI (include/vsnray_b200.h).
+
+Names follow the reference's domain: a `Scene` is what `cuda_index_bvh<P>(index_bvh<P> const&)`
+produces (bvh.h:344-350) -- the uploaded tree, re-encoded on the GPU into the wide BVH8;
+`closest_hit` / `any_hit` replace the calls of detail/traverse_linear.inl:186-318 over a ray list;
+`frame` replaces `cuda_sched<R>::frame()` (detail/cuda_sched.inl:307-320) for the built-in kernels.
+
+Every call goes through libvsnray_b200.so.  There is no CPU fallback; errors raise RuntimeError
+(the reference's convention for the path is std::runtime_error at setup).
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _native as N
+
+FLT_MAX = 3.4028234663852886e38
+TRAVERSE_WIDE, TRAVERSE_EXACT = 0, 1
+MEM_DEVICE, MEM_HOST = 0, 1
+KERNEL_SIMPLE, KERNEL_WHITTED, KERNEL_AO, KERNEL_PATHTRACING = 0, 1, 2, 3
+PS_UNIFORM, PS_JITTERED, PS_JITTERED_BLEND = 0, 1, 2
+TILE = 64
+
+
+def _check(rc: int, what: str):
+    if rc != 0:
+        msg = N.cuda_lib().vsb_strerror(rc).decode()
+        raise RuntimeError(f"{what} failed: {msg} ({rc})")
+
+
+def init(device: int = 0):
+    _check(N.cuda_lib().vsb_init(device), "vsb_init")
+
+
+def shutdown():
+    N.cuda_lib().vsb_shutdown()
+
+
+def sm_count() -> int:
+    n = C.c_int(0)
+    _check(N.cuda_lib().vsb_device_sm_count(C.byref(n)), "vsb_device_sm_count")
+    return n.value
+
+
+def launch_count() -> int:
+    n = C.c_uint64(0)
+    N.cuda_lib().vsb_launch_count(C.byref(n))
+    return n.value
+
+
+def last_kernel_ms() -> float:
+    ms = C.c_float(0)
+    _check(N.cuda_lib().vsb_last_kernel_ms(C.byref(ms)), "vsb_last_kernel_ms")
+    return ms.value
+
+
+class Scene:
+    """Device-resident scene: reference-layout BVH2 (exact traversal) + re-encoded BVH8."""
+
+    def __init__(self, host_scene):
+        self.host = host_scene
+        h = C.c_void_p(0)
+        idx = host_scene.indices
+        _check(N.cuda_lib().vsb_scene_create(
+            host_scene.prim_kind, N.ptr(host_scene.prims), host_scene.prims.shape[0],
+            N.ptr(host_scene.nodes), host_scene.nodes.shape[0],
+            N.ptr(idx) if idx is not None else None, idx.shape[0] if idx is not None else 0, C.byref(h)),
+            "vsb_scene_create")
+        self.handle = h
+
+    def stats(self) -> dict:
+        out = (C.c_uint64 * 7)()
+        _check(N.cuda_lib().vsb_scene_stats(self.handle, out, 7), "vsb_scene_stats")
+        keys = ["wide_nodes", "wide_node_bytes", "wide_prims", "wide_prim_bytes", "bvh2_depth", "bvh2_nodes", "wide_levels"]
+        return dict(zip(keys, [int(v) for v in out]))
+
+    def download_wide(self):
+        st = self.stats()
+        nodes = np.zeros((st["wide_nodes"], 20), dtype=np.uint32)
+        prims = np.zeros(st["wide_prim_bytes"] // 4, dtype=np.uint32)
+        _check(N.cuda_lib().vsb_scene_download_wide(self.handle, N.ptr(nodes), nodes.nbytes, N.ptr(prims), prims.nbytes),
+               "vsb_scene_download_wide")
+        return nodes, prims
+
+    def close(self):
+        if self.handle:
+            N.cuda_lib().vsb_scene_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _scene_array(scenes):
+    arr = (C.c_void_p * len(scenes))(*[s.handle for s in scenes])
+    return arr
+
+
+def _query(fn, scenes, rays, max_t, max_t_per_ray, hits, traverse, stream):
+    """rays / hits: numpy arrays (host memory, copies inside the call) or torch CUDA tensors."""
+    if isinstance(scenes, Scene):
+        scenes = [scenes]
+    arr = _scene_array(scenes)
+    if isinstance(rays, np.ndarray):
+        n = rays.shape[0]
+        if hits is None:
+            hits = np.zeros(n, dtype=N.HIT_DTYPE)
+        mt = N.ptr(max_t_per_ray) if max_t_per_ray is not None else None
+        _check(fn(arr, len(scenes), N.ptr(rays), n, max_t, mt, N.ptr(hits), MEM_HOST, traverse, stream), fn.__name__)
+        return hits
+    import torch
+
+    n = rays.shape[0]
+    if hits is None:
+        hits = torch.empty((n, 8), dtype=torch.int32, device=rays.device)
+    mt = C.c_void_p(max_t_per_ray.data_ptr()) if max_t_per_ray is not None else None
+    _check(fn(arr, len(scenes), C.c_void_p(rays.data_ptr()), n, max_t, mt, C.c_void_p(hits.data_ptr()), MEM_DEVICE,
+              traverse, stream), fn.__name__)
+    return hits
+
+
+def closest_hit(scenes, rays, max_t=FLT_MAX, max_t_per_ray=None, hits=None, traverse=TRAVERSE_WIDE, stream=None):
+    return _query(N.cuda_lib().vsb_closest_hit, scenes, rays, max_t, max_t_per_ray, hits, traverse, stream)
+
+
+def any_hit(scenes, rays, max_t=FLT_MAX, max_t_per_ray=None, hits=None, traverse=TRAVERSE_WIDE, stream=None):
+    return _query(N.cuda_lib().vsb_any_hit, scenes, rays, max_t, max_t_per_ray, hits, traverse, stream)
+
+
+def tiles_of_rank(width, height, rank, nranks) -> int:
+    n = C.c_int(0)
+    _check(N.cuda_lib().vsb_tiles_of_rank(width, height, rank, nranks, C.byref(n)), "vsb_tiles_of_rank")
+    return n.value
+
+
+def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
+          tile_nranks=0, ray_count=None, stream=None):
+    """One frame() call.  numpy arrays -> host buffers (H2D/D2H inside the call, returns with
+    pixels in place); torch CUDA tensors -> device buffers (asynchronous on `stream`)."""
+    if isinstance(scenes, Scene):
+        scenes = [scenes]
+    d = N.FrameDesc()
+    d.p = fp
+    _check(N.cuda_lib().vsb_camera_basis(C.byref(d)), "vsb_camera_basis")
+    d.scissor[0], d.scissor[1], d.scissor[2], d.scissor[3] = 0, 0, fp.width, fp.height
+    host = isinstance(color, np.ndarray)
+
+    def p(a):
+        if a is None:
+            return None
+        return a.ctypes.data if isinstance(a, np.ndarray) else a.data_ptr()
+
+    d.normals, d.materials, d.lights, d.color = p(normals), p(materials), p(lights), p(color)
+    d.depth = None
+    d.mem = MEM_HOST if host else MEM_DEVICE
+    d.traverse = traverse
+    d.tile_rank, d.tile_nranks = tile_rank, tile_nranks
+    d.ray_count = p(ray_count)
+    _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), stream), "vsb_frame")
+    return color
+
+
+def deinterleave_tiles(gathered, width, height, nranks, tiles_per_rank_padded, image, stream=None):
+    _check(N.cuda_lib().vsb_deinterleave_tiles(C.c_void_p(gathered.data_ptr()), width, height, nranks,
+                                               tiles_per_rank_padded, C.c_void_p(image.data_ptr()), stream),
+           "vsb_deinterleave_tiles")
+    return image

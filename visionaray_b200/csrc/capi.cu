@@ -1,0 +1,292 @@
+// capi.cu -- the C ABI of libvsnray_b200.so (include/vsnray_b200.h) over the sm_100a kernels.
+// No CPU fallback exists in this library: without a CUDA device vsb_init() fails and every
+// compute entry point returns VSB_ERR_NOT_INIT.
+
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <utility>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/vsnray_b200.h"
+#include "kernels.cuh"
+
+#include "capi_scene.inl"
+
+namespace
+{
+
+static_assert(sizeof(vsb_ray) == 32 && sizeof(vsb_hit) == 32 && sizeof(vsb_bvh_node) == 32, "ABI layouts");
+static_assert(sizeof(vsb_triangle) == 64 && sizeof(vsb_sphere) == 48, "ABI layouts");
+static_assert(sizeof(vsb_material) == 64 && sizeof(vsb_point_light) == 48, "ABI layouts");
+static_assert(sizeof(vsb_frame_params) == sizeof(vsb::FrameParams), "frame params layout");
+static_assert(sizeof(vsb::Material) == 64 && sizeof(vsb::PointLight) == 48, "device layouts");
+static_assert(sizeof(vsb::Node80) == 80 && sizeof(vsb::TriRec) == 48 && sizeof(vsb::SphRec) == 32, "wide layouts");
+
+const int BLOCK = 128;
+
+int upload_scene_table(const vsb_scene* const* scenes, int n_scenes, cudaStream_t st)
+{
+    if (!scenes || n_scenes < 1 || n_scenes > MAX_SCENES) return VSB_ERR_BAD_ARG;
+    vsb::DeviceScene tab[MAX_SCENES];
+    for (int i = 0; i < n_scenes; ++i)
+    {
+        if (!scenes[i]) return VSB_ERR_BAD_ARG;
+        tab[i] = scenes[i]->dev;
+    }
+    VSB_CUDA(cudaMemcpyAsync(g.d_scenes, tab, sizeof(vsb::DeviceScene) * n_scenes, cudaMemcpyHostToDevice, st));
+    return VSB_OK;
+}
+
+template <typename K>
+int grid_for(K kernel, unsigned long long work_items_of_32)
+{
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
+    unsigned long long want = (work_items_of_32 + (BLOCK / 32) - 1) / (BLOCK / 32);
+    unsigned long long full = (unsigned long long)per_sm * (unsigned long long)g.sm_count;   // whole waves of resident CTAs
+    unsigned long long grid = want < full ? want : full;
+    return (int)(grid < 1 ? 1 : grid);
+}
+
+int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_ray* rays, size_t n_rays,
+              float max_t, const float* max_t_per_ray, vsb_hit* hits, int mem, int traverse, void* cuda_stream)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (n_rays == 0) return VSB_OK;
+    if (!rays || !hits) return VSB_ERR_BAD_ARG;
+    if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT) return VSB_ERR_BAD_ARG;
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
+
+    const float4* d_rays = reinterpret_cast<const float4*>(rays);
+    uint4* d_hits = reinterpret_cast<uint4*>(hits);
+    const float* d_mt = max_t_per_ray;
+    if (mem == VSB_MEM_HOST)
+    {
+        void *a, *b, *c = nullptr;
+        rc = stage(0, n_rays * sizeof(vsb_ray), &a); if (rc) return rc;
+        rc = stage(1, n_rays * sizeof(vsb_hit), &b); if (rc) return rc;
+        VSB_CUDA(cudaMemcpyAsync(a, rays, n_rays * sizeof(vsb_ray), cudaMemcpyHostToDevice, st));
+        if (max_t_per_ray)
+        {
+            rc = stage(2, n_rays * sizeof(float), &c); if (rc) return rc;
+            VSB_CUDA(cudaMemcpyAsync(c, max_t_per_ray, n_rays * sizeof(float), cudaMemcpyHostToDevice, st));
+        }
+        d_rays = reinterpret_cast<const float4*>(a); d_hits = reinterpret_cast<uint4*>(b); d_mt = reinterpret_cast<const float*>(c);
+    }
+    else if (mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+
+    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, sizeof(unsigned long long), st));
+    const unsigned long long warps = ((unsigned long long)n_rays + 31ull) / 32ull;
+    const bool exact = traverse == VSB_TRAVERSE_EXACT;
+    VSB_CUDA(cudaEventRecord(g.ev0, st));
+#define VSB_LAUNCH_QUERY(ANY, EXACT)                                                                       \
+    vsb::query_kernel<ANY, EXACT><<<grid_for(vsb::query_kernel<ANY, EXACT>, warps), BLOCK, 0, st>>>(       \
+        g.d_scenes, n_scenes, d_rays, (unsigned long long)n_rays, max_t, d_mt, d_hits, g.d_work)
+    if (any) { if (exact) VSB_LAUNCH_QUERY(true, true); else VSB_LAUNCH_QUERY(true, false); }
+    else     { if (exact) VSB_LAUNCH_QUERY(false, true); else VSB_LAUNCH_QUERY(false, false); }
+#undef VSB_LAUNCH_QUERY
+    ++g.launches;
+    VSB_CUDA(cudaGetLastError());
+    VSB_CUDA(cudaEventRecord(g.ev1, st));
+    if (mem == VSB_MEM_HOST)
+    {
+        VSB_CUDA(cudaMemcpyAsync(hits, d_hits, n_rays * sizeof(vsb_hit), cudaMemcpyDeviceToHost, st));
+        VSB_CUDA(cudaStreamSynchronize(st));
+    }
+    return VSB_OK;
+}
+
+} // namespace
+
+extern "C" int vsb_version(void) { return 100; }
+
+extern "C" const char* vsb_strerror(int code)
+{
+    switch (code)
+    {
+    case VSB_OK: return "ok";
+    case VSB_ERR_NO_DEVICE: return "no CUDA device (this library has no CPU fallback)";
+    case VSB_ERR_BAD_ARG: return "bad argument";
+    case VSB_ERR_BAD_TREE: return "malformed or too deep BVH";
+    case VSB_ERR_NOT_INIT: return "vsb_init() has not succeeded";
+    case VSB_ERR_UNSUPPORTED: return "unsupported";
+    default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
+    }
+}
+
+extern "C" int vsb_closest_hit(const vsb_scene* const* scenes, int n_scenes, const vsb_ray* rays, size_t n_rays,
+                               float max_t, const float* max_t_per_ray, vsb_hit* hits, int mem, int traverse, void* cuda_stream)
+{
+    return run_query(false, scenes, n_scenes, rays, n_rays, max_t, max_t_per_ray, hits, mem, traverse, cuda_stream);
+}
+
+extern "C" int vsb_any_hit(const vsb_scene* const* scenes, int n_scenes, const vsb_ray* rays, size_t n_rays,
+                           float max_t, const float* max_t_per_ray, vsb_hit* hits, int mem, int traverse, void* cuda_stream)
+{
+    return run_query(true, scenes, n_scenes, rays, n_rays, max_t, max_t_per_ray, hits, mem, traverse, cuda_stream);
+}
+
+// Host-side camera basis, exactly the arithmetic of cuda_sched_impl_frame
+// (detail/cuda_sched.inl:259-266); this TU is built with -Xcompiler -ffp-contract=off.
+extern "C" int vsb_camera_basis(vsb_frame_desc* d)
+{
+    if (!d) return VSB_ERR_BAD_ARG;
+    const vsb_frame_params& p = d->p;
+    auto norm = [](const float v[3], float o[3])
+    {
+        float s = 1.0f / std::sqrt(v[0] * v[0] + v[1] * v[1] + v[2] * v[2]);
+        o[0] = v[0] * s; o[1] = v[1] * s; o[2] = v[2] * s;
+    };
+    auto cross = [](const float u[3], const float v[3], float o[3])
+    {
+        float x = u[1] * v[2] - u[2] * v[1], y = u[2] * v[0] - u[0] * v[2], z = u[0] * v[1] - u[1] * v[0];
+        o[0] = x; o[1] = y; o[2] = z;
+    };
+    float dd[3] = { p.eye[0] - p.center[0], p.eye[1] - p.center[1], p.eye[2] - p.center[2] };
+    float f[3], c[3], s[3], u[3];
+    norm(dd, f);
+    cross(p.up, f, c);
+    norm(c, s);
+    cross(f, s, u);
+    const float th = std::tan(p.fovy / 2.0f);
+    for (int i = 0; i < 3; ++i)
+    {
+        d->cam_eye[i] = p.eye[i];
+        d->cam_u[i] = s[i] * th * p.aspect;
+        d->cam_v[i] = u[i] * th;
+        d->cam_w[i] = -f[i];
+    }
+    d->cam_eye[3] = d->cam_u[3] = d->cam_v[3] = d->cam_w[3] = 0.0f;
+    return VSB_OK;
+}
+
+extern "C" int vsb_tiles_of_rank(int width, int height, int rank, int nranks, int* n_tiles)
+{
+    if (!n_tiles || width < 1 || height < 1 || nranks < 1 || rank < 0 || rank >= nranks) return VSB_ERR_BAD_ARG;
+    const int tiles = ((width + VSB_TILE - 1) / VSB_TILE) * ((height + VSB_TILE - 1) / VSB_TILE);
+    *n_tiles = (tiles - rank + nranks - 1) / nranks;   // tiles k with k % nranks == rank
+    return VSB_OK;
+}
+
+extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb_frame_desc* d, void* cuda_stream)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!d || !d->color) return VSB_ERR_BAD_ARG;
+    const vsb_frame_params& p = d->p;
+    if (p.width < 1 || p.height < 1 || p.kernel < 0 || p.kernel > 3 || p.pixel_sampler < 0 || p.pixel_sampler > 2) return VSB_ERR_BAD_ARG;
+    if (p.pixel_sampler == VSB_PS_JITTERED_BLEND && p.frame_num == 0) return VSB_ERR_BAD_ARG;
+    if (p.kernel != VSB_KERNEL_AO && (!d->materials || p.n_materials < 1)) return VSB_ERR_BAD_ARG;
+    if (!d->normals) return VSB_ERR_BAD_ARG;
+    if (p.n_lights > 0 && !d->lights && p.kernel <= VSB_KERNEL_WHITTED) return VSB_ERR_BAD_ARG;
+    for (int i = 0; i < n_scenes; ++i) if (!scenes || !scenes[i] || scenes[i]->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
+
+    vsb::FrameLaunch fl;
+    std::memset(&fl, 0, sizeof(fl));
+    std::memcpy(&fl.ctx.p, &p, sizeof(p));
+    for (int i = 0; i < 3; ++i) { fl.ctx.eye[i] = d->cam_eye[i]; fl.ctx.cu[i] = d->cam_u[i]; fl.ctx.cv[i] = d->cam_v[i]; fl.ctx.cw[i] = d->cam_w[i]; }
+    const int nranks = d->tile_nranks > 1 ? d->tile_nranks : 1;
+    const int rank = d->tile_nranks > 1 ? d->tile_rank : 0;
+    if (rank < 0 || rank >= nranks) return VSB_ERR_BAD_ARG;
+    fl.tile_rank = rank; fl.tile_nranks = d->tile_nranks > 1 ? nranks : 0;
+    fl.tiles_x = (p.width + VSB_TILE - 1) / VSB_TILE; fl.tiles_y = (p.height + VSB_TILE - 1) / VSB_TILE;
+    vsb_tiles_of_rank(p.width, p.height, rank, nranks, &fl.n_owned_tiles);
+    std::memcpy(fl.scissor, d->scissor, sizeof(fl.scissor));
+    if (fl.scissor[2] <= 0 || fl.scissor[3] <= 0) { fl.scissor[0] = 0; fl.scissor[1] = 0; fl.scissor[2] = p.width; fl.scissor[3] = p.height; }
+    fl.scenes = g.d_scenes; fl.n_scenes = n_scenes;
+
+    const size_t n_normals = scenes[0]->n_prims;
+    const size_t color_px = nranks > 1 ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
+    unsigned long long* d_ray_count = nullptr;
+    if (d->mem == VSB_MEM_HOST)
+    {
+        void *a, *b = nullptr, *c = nullptr, *e;
+        rc = stage(3, n_normals * 16, &a); if (rc) return rc;
+        VSB_CUDA(cudaMemcpyAsync(a, d->normals, n_normals * 16, cudaMemcpyHostToDevice, st));
+        rc = stage(4, (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64 + (size_t)(p.n_lights > 0 ? p.n_lights : 1) * 48 + 64, &b); if (rc) return rc;
+        if (d->materials) VSB_CUDA(cudaMemcpyAsync(b, d->materials, (size_t)p.n_materials * 64, cudaMemcpyHostToDevice, st));
+        c = (char*)b + (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64;
+        if (d->lights && p.n_lights > 0) VSB_CUDA(cudaMemcpyAsync(c, d->lights, (size_t)p.n_lights * 48, cudaMemcpyHostToDevice, st));
+        rc = stage(5, color_px * 16 + 16, &e); if (rc) return rc;
+        if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
+            VSB_CUDA(cudaMemcpyAsync(e, d->color, color_px * 16, cudaMemcpyHostToDevice, st));   // progressive state lives with the caller
+        fl.ctx.normals = reinterpret_cast<const float4*>(a);
+        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(b);
+        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(c);
+        fl.color = reinterpret_cast<float4*>(e);
+        if (d->ray_count) d_ray_count = g.d_work + 1;
+    }
+    else
+    {
+        fl.ctx.normals = reinterpret_cast<const float4*>(d->normals);
+        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(d->materials);
+        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(d->lights);
+        fl.color = reinterpret_cast<float4*>(d->color);
+        d_ray_count = reinterpret_cast<unsigned long long*>(d->ray_count);
+    }
+    fl.ray_count = d_ray_count;
+
+    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 2 * sizeof(unsigned long long), st));
+    const unsigned long long packets = (unsigned long long)fl.n_owned_tiles * VSB_PACKETS_PER_TILE;
+    const bool exact = d->traverse == VSB_TRAVERSE_EXACT;
+    VSB_CUDA(cudaEventRecord(g.ev0, st));
+#define VSB_LAUNCH_FRAME(K, EXACT)                                                                         \
+    vsb::frame_kernel<K, EXACT><<<grid_for(vsb::frame_kernel<K, EXACT>, packets), BLOCK, 0, st>>>(fl, g.d_work)
+    switch (p.kernel * 2 + (exact ? 1 : 0))
+    {
+    case 0: VSB_LAUNCH_FRAME(0, false); break;
+    case 1: VSB_LAUNCH_FRAME(0, true); break;
+    case 2: VSB_LAUNCH_FRAME(1, false); break;
+    case 3: VSB_LAUNCH_FRAME(1, true); break;
+    case 4: VSB_LAUNCH_FRAME(2, false); break;
+    case 5: VSB_LAUNCH_FRAME(2, true); break;
+    case 6: VSB_LAUNCH_FRAME(3, false); break;
+    default: VSB_LAUNCH_FRAME(3, true); break;
+    }
+#undef VSB_LAUNCH_FRAME
+    ++g.launches;
+    VSB_CUDA(cudaGetLastError());
+    VSB_CUDA(cudaEventRecord(g.ev1, st));
+    if (d->mem == VSB_MEM_HOST)
+    {
+        VSB_CUDA(cudaMemcpyAsync(d->color, fl.color, color_px * 16, cudaMemcpyDeviceToHost, st));
+        if (d->ray_count) VSB_CUDA(cudaMemcpyAsync(d->ray_count, d_ray_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+        VSB_CUDA(cudaStreamSynchronize(st));   // host-visible target: frame() returns with pixels in place
+    }
+    return VSB_OK;
+}
+
+extern "C" int vsb_deinterleave_tiles(const void* gathered, int width, int height, int nranks,
+                                      int tiles_per_rank_padded, void* image, void* cuda_stream)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!gathered || !image || width < 1 || height < 1 || nranks < 1) return VSB_ERR_BAD_ARG;
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    dim3 block(32, 8), grid((width + 31) / 32, (height + 7) / 8);
+    vsb::deinterleave_kernel<<<grid, block, 0, st>>>(reinterpret_cast<const float4*>(gathered), width, height, nranks,
+                                                      tiles_per_rank_padded, reinterpret_cast<float4*>(image));
+    ++g.launches;
+    VSB_CUDA(cudaGetLastError());
+    return VSB_OK;
+}
+
+extern "C" int vsb_last_kernel_ms(float* ms)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!ms) return VSB_ERR_BAD_ARG;
+    VSB_CUDA(cudaEventSynchronize(g.ev1));
+    VSB_CUDA(cudaEventElapsedTime(ms, g.ev0, g.ev1));
+    return VSB_OK;
+}
+
+extern "C" int vsb_launch_count(uint64_t* n)
+{
+    if (!n) return VSB_ERR_BAD_ARG;
+    *n = g.launches;
+    return VSB_OK;
+}

@@ -1,0 +1,307 @@
+// capi_scene.inl -- context + scene half of capi.cu (included there).
+
+namespace
+{
+
+struct Context
+{
+    bool         inited = false;
+    int          device = -1;
+    int          sm_count = 0;
+    cudaStream_t stream = nullptr;          // internal stream for uploads / encode
+    cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    unsigned long long* d_work = nullptr;   // persistent-kernel work counter
+    vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
+    void*        staging[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
+    size_t       staging_cap[6] = { 0, 0, 0, 0, 0, 0 };
+    float        last_ms = 0.0f;
+    unsigned long long launches = 0;
+};
+
+const int MAX_SCENES = 16;
+Context g;
+
+#define VSB_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (int)e__; } while (0)
+
+int require_init()
+{
+    if (!g.inited) return VSB_ERR_NOT_INIT;
+    return VSB_OK;
+}
+
+// grow-only device staging buffer for host-memory callers
+int stage(int slot, size_t bytes, void** out)
+{
+    if (bytes > g.staging_cap[slot])
+    {
+        if (g.staging[slot]) cudaFree(g.staging[slot]);
+        g.staging[slot] = nullptr; g.staging_cap[slot] = 0;
+        size_t cap = bytes + bytes / 4 + 256;
+        VSB_CUDA(cudaMalloc(&g.staging[slot], cap));
+        g.staging_cap[slot] = cap;
+    }
+    *out = g.staging[slot];
+    return VSB_OK;
+}
+
+} // namespace
+
+struct vsb_scene
+{
+    int      prim_kind = 0;
+    size_t   n_prims = 0, n_nodes2 = 0, n_idx = 0;
+    void*    d_prims = nullptr;          // reference layout (exact traversal)
+    vsb::Node32* d_nodes2 = nullptr;
+    uint32_t* d_indices = nullptr;       // NULL for a non-index bvh
+    vsb::Node80* d_wide = nullptr;
+    void*    d_wide_prims = nullptr;
+    uint32_t n_wide = 0, n_wide_prims = 0;
+    int      levels = 0, depth2 = 0;
+    vsb::DeviceScene dev;
+};
+
+namespace
+{
+
+// Host validation of the incoming BVH2 (the reference only asserts, bvh.h:74,86,112): every
+// node reachable exactly once, children adjacent and in range, leaf ranges inside indices[],
+// indices inside prims[].  Returns max depth (root = 1) or a negative error.
+int validate_tree(const vsb_bvh_node* nodes, size_t n_nodes, const uint32_t* indices, size_t n_idx,
+                  size_t n_prims, bool* big_leaves)
+{
+    if (n_nodes == 0) return VSB_ERR_BAD_TREE;
+    std::vector<uint8_t> seen(n_nodes, 0);
+    std::vector<std::pair<uint32_t, int>> st;
+    st.push_back({ 0u, 1 });
+    int maxd = 0;
+    size_t visited = 0;
+    *big_leaves = false;
+    const size_t list_len = indices ? n_idx : n_prims;
+    while (!st.empty())
+    {
+        auto cur = st.back(); st.pop_back();
+        uint32_t i = cur.first; int d = cur.second;
+        if (i >= n_nodes || seen[i]) return VSB_ERR_BAD_TREE;
+        seen[i] = 1; ++visited;
+        if (d > maxd) maxd = d;
+        const vsb_bvh_node& n = nodes[i];
+        if (n.num_prims == 0)
+        {
+            if ((size_t)n.first + 1 >= n_nodes || n.first == 0) return VSB_ERR_BAD_TREE;
+            st.push_back({ n.first, d + 1 });
+            st.push_back({ n.first + 1, d + 1 });
+        }
+        else
+        {
+            if ((size_t)n.first + n.num_prims > list_len) return VSB_ERR_BAD_TREE;
+            if (n.num_prims > 4) *big_leaves = true;
+            if (indices)
+                for (uint32_t k = 0; k < n.num_prims; ++k)
+                    if (indices[n.first + k] >= n_prims) return VSB_ERR_BAD_TREE;
+        }
+    }
+    (void)visited;
+    return maxd;
+}
+
+// Leaves with more than 4 primitives (degenerate centroids or SAH "leaf is cheaper",
+// detail/bvh/sah.h:677-762) are split into chains of virtual BVH2 nodes that keep the parent
+// bounds, so that the collapse can assume <= 4 primitives per leaf.  Only the copy used for
+// the wide encode is changed; the exact traversal keeps the caller's tree.
+void normalise_leaves(std::vector<vsb_bvh_node>& nodes)
+{
+    for (size_t i = 0; i < nodes.size(); ++i)
+    {
+        vsb_bvh_node n = nodes[i];
+        if (n.num_prims <= 4) continue;
+        uint32_t half = n.num_prims / 2;
+        vsb_bvh_node a = n, b = n;
+        a.num_prims = half;
+        b.first = n.first + half; b.num_prims = n.num_prims - half;
+        n.first = (uint32_t)nodes.size(); n.num_prims = 0;
+        nodes[i] = n;
+        nodes.push_back(a);
+        nodes.push_back(b);   // revisited later by this same loop if still > 4
+    }
+}
+
+} // namespace
+
+extern "C" int vsb_init(int device)
+{
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || count == 0) return VSB_ERR_NO_DEVICE;
+    if (device < 0 || device >= count) return VSB_ERR_BAD_ARG;
+    if (g.inited && g.device == device) return VSB_OK;
+    if (g.inited) vsb_shutdown();
+    VSB_CUDA(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    VSB_CUDA(cudaGetDeviceProperties(&prop, device));
+    g.device = device;
+    g.sm_count = prop.multiProcessorCount;
+    VSB_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    VSB_CUDA(cudaEventCreate(&g.ev0));
+    VSB_CUDA(cudaEventCreate(&g.ev1));
+    VSB_CUDA(cudaMalloc(&g.d_work, 64));
+    VSB_CUDA(cudaMalloc(&g.d_scenes, sizeof(vsb::DeviceScene) * MAX_SCENES));
+    g.inited = true;
+    return VSB_OK;
+}
+
+extern "C" int vsb_shutdown(void)
+{
+    if (!g.inited) return VSB_OK;
+    cudaSetDevice(g.device);
+    cudaDeviceSynchronize();
+    for (int i = 0; i < 6; ++i) { if (g.staging[i]) cudaFree(g.staging[i]); g.staging[i] = nullptr; g.staging_cap[i] = 0; }
+    if (g.d_work) cudaFree(g.d_work);
+    if (g.d_scenes) cudaFree(g.d_scenes);
+    if (g.ev0) cudaEventDestroy(g.ev0);
+    if (g.ev1) cudaEventDestroy(g.ev1);
+    if (g.stream) cudaStreamDestroy(g.stream);
+    g = Context();
+    return VSB_OK;
+}
+
+extern "C" int vsb_device_sm_count(int* out)
+{
+    int rc = require_init(); if (rc) return rc;
+    *out = g.sm_count;
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_destroy(vsb_scene* s)
+{
+    if (!s) return VSB_OK;
+    if (s->d_prims) cudaFree(s->d_prims);
+    if (s->d_nodes2) cudaFree(s->d_nodes2);
+    if (s->d_indices) cudaFree(s->d_indices);
+    if (s->d_wide) cudaFree(s->d_wide);
+    if (s->d_wide_prims) cudaFree(s->d_wide_prims);
+    delete s;
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
+                                const vsb_bvh_node* nodes, size_t n_nodes,
+                                const uint32_t* indices, size_t n_indices, vsb_scene** out)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!prims || !nodes || !out || n_prims == 0 || n_nodes == 0) return VSB_ERR_BAD_ARG;
+    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE) return VSB_ERR_BAD_ARG;
+    if (n_nodes >= 0x7fffffffull || n_prims >= 0x7fffffffull) return VSB_ERR_UNSUPPORTED;
+
+    bool big = false;
+    const int depth = validate_tree(nodes, n_nodes, indices, n_indices, n_prims, &big);
+    if (depth < 0) return depth;
+    if (depth > VSB_EXACT_STACK - 1 || depth > VSB_STACK_SIZE - 1) return VSB_ERR_BAD_TREE;
+
+    vsb_scene* s = new vsb_scene();
+    s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_nodes2 = n_nodes; s->n_idx = indices ? n_indices : 0;
+    s->depth2 = depth;
+    const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
+    const size_t rec_bytes = prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
+    const size_t list_len = indices ? n_indices : n_prims;
+
+#define VSB_SCENE_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { vsb_scene_destroy(s); return (int)e__; } } while (0)
+    VSB_SCENE_CUDA(cudaMalloc(&s->d_prims, n_prims * prim_bytes));
+    VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_nodes2, n_nodes * sizeof(vsb::Node32)));
+    if (indices) VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_indices, n_indices * sizeof(uint32_t)));
+    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_prims, prims, n_prims * prim_bytes, cudaMemcpyHostToDevice, g.stream));
+    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_nodes2, nodes, n_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice, g.stream));
+    if (indices) VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_indices, indices, n_indices * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
+
+    // BVH2 used for the encode: the caller's tree, or a normalised copy when it has big leaves
+    vsb::Node32* d_enc_nodes = s->d_nodes2;
+    size_t n_enc_nodes = n_nodes;
+    vsb::Node32* d_norm = nullptr;
+    if (big)
+    {
+        std::vector<vsb_bvh_node> norm(nodes, nodes + n_nodes);
+        normalise_leaves(norm);
+        n_enc_nodes = norm.size();
+        VSB_SCENE_CUDA(cudaMalloc((void**)&d_norm, n_enc_nodes * sizeof(vsb::Node32)));
+        VSB_SCENE_CUDA(cudaMemcpy(d_norm, norm.data(), n_enc_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice));
+        d_enc_nodes = d_norm;
+    }
+
+    // GPU re-encode, level by level
+    uint32_t* d_leaf_list = nullptr; vsb::WideTask* d_tasks[2] = { nullptr, nullptr }; uint32_t* d_counters = nullptr;
+    const size_t wide_cap = n_enc_nodes;   // a wide node consumes >= 1 BVH2 inner node
+    cudaError_t err = cudaSuccess;
+    auto cleanup = [&]()
+    {
+        if (d_leaf_list) cudaFree(d_leaf_list);
+        if (d_tasks[0]) cudaFree(d_tasks[0]);
+        if (d_tasks[1]) cudaFree(d_tasks[1]);
+        if (d_counters) cudaFree(d_counters);
+        if (d_norm) cudaFree(d_norm);
+    };
+#define VSB_ENC_CUDA(expr) do { err = (expr); if (err != cudaSuccess) { cleanup(); vsb_scene_destroy(s); return (int)err; } } while (0)
+    VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, wide_cap * sizeof(vsb::Node80)));
+    VSB_ENC_CUDA(cudaMalloc((void**)&d_leaf_list, (list_len + 1) * sizeof(uint32_t)));
+    VSB_ENC_CUDA(cudaMalloc((void**)&d_tasks[0], (wide_cap + 1) * sizeof(vsb::WideTask)));
+    VSB_ENC_CUDA(cudaMalloc((void**)&d_tasks[1], (wide_cap + 1) * sizeof(vsb::WideTask)));
+    VSB_ENC_CUDA(cudaMalloc((void**)&d_counters, 4 * sizeof(uint32_t)));
+    {
+        vsb::WideTask root; root.bvh2_node = 0; root.wide_index = 0;
+        uint32_t init[4] = { 1u, 0u, 0u, 0u };
+        VSB_ENC_CUDA(cudaMemcpyAsync(d_tasks[0], &root, sizeof(root), cudaMemcpyHostToDevice, g.stream));
+        VSB_ENC_CUDA(cudaMemcpyAsync(d_counters, init, sizeof(init), cudaMemcpyHostToDevice, g.stream));
+    }
+    uint32_t n_tasks = 1; int cur = 0; s->levels = 0;
+    uint32_t counters[4] = { 1u, 0u, 0u, 0u };
+    while (n_tasks > 0)
+    {
+        VSB_ENC_CUDA(cudaMemsetAsync(d_counters + 2, 0, sizeof(uint32_t), g.stream));
+        vsb::encode_level_kernel<<<(n_tasks + 127) / 128, 128, 0, g.stream>>>(
+            d_tasks[cur], n_tasks, d_enc_nodes, s->d_wide, d_leaf_list, d_tasks[cur ^ 1], d_counters);
+        ++g.launches;
+        VSB_ENC_CUDA(cudaGetLastError());
+        VSB_ENC_CUDA(cudaMemcpyAsync(counters, d_counters, sizeof(counters), cudaMemcpyDeviceToHost, g.stream));
+        VSB_ENC_CUDA(cudaStreamSynchronize(g.stream));
+        n_tasks = counters[2];
+        cur ^= 1;
+        ++s->levels;
+        if (s->levels > 256) { cleanup(); vsb_scene_destroy(s); return VSB_ERR_BAD_TREE; }
+    }
+    s->n_wide = counters[0];
+    s->n_wide_prims = counters[1];
+    if (s->n_wide_prims != list_len || s->levels > VSB_STACK_SIZE - 2) { cleanup(); vsb_scene_destroy(s); return VSB_ERR_BAD_TREE; }
+    VSB_ENC_CUDA(cudaMalloc(&s->d_wide_prims, (size_t)s->n_wide_prims * rec_bytes + 64));
+    vsb::fill_prims_kernel<<<(s->n_wide_prims + 255) / 256, 256, 0, g.stream>>>(
+        prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims);
+    ++g.launches;
+    VSB_ENC_CUDA(cudaGetLastError());
+    VSB_ENC_CUDA(cudaStreamSynchronize(g.stream));
+    cleanup();
+
+    s->dev.wide.nodes = s->d_wide; s->dev.wide.prims = s->d_wide_prims; s->dev.wide.prim_kind = prim_kind;
+    s->dev.exact.nodes = s->d_nodes2; s->dev.exact.prims = s->d_prims; s->dev.exact.indices = s->d_indices;
+    s->dev.exact.prim_kind = prim_kind;
+    *out = s;
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_stats(const vsb_scene* s, uint64_t* out, int n)
+{
+    if (!s || !out) return VSB_ERR_BAD_ARG;
+    uint64_t v[6] = { s->n_wide, (uint64_t)s->n_wide * sizeof(vsb::Node80), s->n_wide_prims,
+                      (uint64_t)s->n_wide_prims * (s->prim_kind == 0 ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec)),
+                      (uint64_t)s->depth2, (uint64_t)s->n_nodes2 };
+    for (int i = 0; i < n && i < 6; ++i) out[i] = v[i];
+    if (n > 6) out[6] = (uint64_t)s->levels;
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_download_wide(const vsb_scene* s, void* nodes_out, size_t node_bytes_cap,
+                                       void* prims_out, size_t prim_bytes_cap)
+{
+    if (!s) return VSB_ERR_BAD_ARG;
+    const size_t nb = (size_t)s->n_wide * sizeof(vsb::Node80);
+    const size_t pb = (size_t)s->n_wide_prims * (s->prim_kind == 0 ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec));
+    if (nodes_out) { if (node_bytes_cap < nb) return VSB_ERR_BAD_ARG; VSB_CUDA(cudaMemcpy(nodes_out, s->d_wide, nb, cudaMemcpyDeviceToHost)); }
+    if (prims_out) { if (prim_bytes_cap < pb) return VSB_ERR_BAD_ARG; VSB_CUDA(cudaMemcpy(prims_out, s->d_wide_prims, pb, cudaMemcpyDeviceToHost)); }
+    return VSB_OK;
+}
