@@ -151,6 +151,7 @@ typedef struct vsb_scene vsb_scene;
 /* ---- context ---- */
 int  vsb_init(int device);                       /* cudaSetDevice + stream/queue state */
 int  vsb_shutdown(void);
+int  vsb_sync(void);                             /* wait for the library's own stream (calls made with cuda_stream == NULL) */
 const char* vsb_strerror(int code);
 int  vsb_version(void);
 int  vsb_device_sm_count(int* out);

@@ -66,7 +66,7 @@ class FrameDesc(C.Structure):
 
 # every symbol include/vsnray_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
-    "vsb_init", "vsb_shutdown", "vsb_strerror", "vsb_version", "vsb_device_sm_count",
+    "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count",
     "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_last_kernel_ms", "vsb_launch_count",
@@ -130,6 +130,7 @@ def host_lib() -> C.CDLL:
         lib.vsbh_gen_spheres.argtypes = [sz, C.c_uint64, C.c_float, C.c_float, vp]
         lib.vsbh_gen_random_rays.argtypes = [vp, sz, C.c_uint64, C.c_float, C.c_float]
         lib.vsbh_face_normals.argtypes = [vp, sz, vp]
+        lib.vsbh_primary_rays.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, vp]
         lib.vsbh_build_bvh.argtypes = [C.c_int, vp, sz, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
         _host_lib = lib
     return _host_lib

@@ -38,6 +38,11 @@ def shutdown():
     N.cuda_lib().vsb_shutdown()
 
 
+def sync():
+    """Wait for everything the library queued on its own stream."""
+    _check(N.cuda_lib().vsb_sync(), "vsb_sync")
+
+
 def sm_count() -> int:
     n = C.c_int(0)
     _check(N.cuda_lib().vsb_device_sm_count(C.byref(n)), "vsb_device_sm_count")

@@ -164,6 +164,13 @@ extern "C" int vsb_shutdown(void)
     return VSB_OK;
 }
 
+extern "C" int vsb_sync(void)
+{
+    int rc = require_init(); if (rc) return rc;
+    VSB_CUDA(cudaStreamSynchronize(g.stream));
+    return VSB_OK;
+}
+
 extern "C" int vsb_device_sm_count(int* out)
 {
     int rc = require_init(); if (rc) return rc;

@@ -8,6 +8,7 @@
 
 #include "visionaray_b200/bvh.h"
 #include "scenes.h"
+#include "../shade.cuh"   // host instantiation of primary_ray() (same single-rounding arithmetic as the kernels)
 
 using namespace visionaray_b200;
 
@@ -81,6 +82,27 @@ int vsbh_build_bvh(int prim_kind, const void* prims, size_t n, void* nodes_out, 
         return 2;
     }
     return 0;
+}
+
+// Primary rays of a width x height pinhole frame, uniform pixel sampler, in pixel order
+// (ray i = pixel (i % width, i / width)); basis = eye, u, v, w as vsb_camera_basis() fills them
+// (4 floats each).  Same arithmetic as the frame kernels' ray generation
+// (detail/sched_common.h:130-150), so a ray list made here equals the rays a frame traces.
+void vsbh_primary_rays(const float* eye, const float* cu, const float* cv, const float* cw, int width, int height, void* out)
+{
+    vsb::FrameCtx f;
+    std::memset(&f, 0, sizeof(f));
+    f.p.width = width; f.p.height = height;
+    for (int i = 0; i < 3; ++i) { f.eye[i] = eye[i]; f.cu[i] = cu[i]; f.cv[i] = cv[i]; f.cw[i] = cw[i]; }
+    vsb::Ray32* r = reinterpret_cast<vsb::Ray32*>(out);
+    for (int y = 0; y < height; ++y)
+        for (int x = 0; x < width; ++x)
+        {
+            vsb::V3 o, d;
+            vsb::primary_ray(f, (float)x, (float)y, o, d);
+            vsb::Ray32& q = r[(size_t)y * width + x];
+            q.ox = o.x; q.oy = o.y; q.oz = o.z; q.pad0 = 0.0f; q.dx = d.x; q.dy = d.y; q.dz = d.z; q.pad1 = 0.0f;
+        }
 }
 
 } // extern "C"
