@@ -132,18 +132,22 @@ typedef struct vsb_frame_desc {
     float    cam_eye[4], cam_u[4], cam_v[4], cam_w[4];
     int32_t  scissor[4];                 /* x, y, w, h; (0,0,width,height) = whole image */
     const float*           normals;      /* per-face normals, 16 B each, indexed by prim_id
-                                            (normals_per_face_binding, get_normal.h:28-37) */
+                                            (normals_per_face_binding, get_normal.h:28-37); NULL = the
+                                            normals attached to scenes[0] by vsb_scene_set_normals() */
     const vsb_material*    materials;    /* indexed by geom_id */
     const vsb_point_light* lights;
     void*    color;                      /* PF_RGBA32F, buffer[y*width+x] (pixel_access.h:38-58) */
     void*    depth;                      /* reserved (PF_DEPTH32F); may be NULL */
-    int32_t  mem;                        /* VSB_MEM_*: where normals/materials/lights/color live */
+    int32_t  mem;                        /* VSB_MEM_*: where color / ray_count live (the render target) */
     int32_t  traverse;                   /* VSB_TRAVERSE_* */
     /* image-space tile partition for multi-GPU (64x64 tiles, tile k -> rank k % nranks);
      * nranks <= 1 renders everything.  With nranks > 1 `color` is the rank's compact tile
      * buffer (tiles_of_rank * 64*64 pixels), see vsb_tiles_of_rank(). */
     int32_t  tile_rank, tile_nranks;
-    uint64_t* ray_count;                 /* optional device/host counter: rays traced this frame */
+    uint64_t* ray_count;                 /* optional counter (same memory as color): += rays traced (device),
+                                            = rays traced this frame (host) */
+    int32_t  params_mem;                 /* VSB_MEM_*: where materials / lights (and normals, if given) live */
+    int32_t  reserved;
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;
@@ -165,6 +169,9 @@ int  vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
                       const uint32_t* indices, size_t n_indices,
                       vsb_scene** out);
 int  vsb_scene_destroy(vsb_scene* s);
+/* per-face normals kept on the device with the scene (what a cuda_sched user holds in a thrust
+ * device_vector and hands to make_kernel_params, src/viewer/viewer.cpp:507-521); n = n_prims */
+int  vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem);
 /* diagnostics: out[0]=wide nodes, out[1]=wide node bytes, out[2]=leaf prim records,
  * out[3]=prim record bytes, out[4]=bvh2 max depth, out[5]=bvh2 nodes */
 int  vsb_scene_stats(const vsb_scene* s, uint64_t* out, int n);

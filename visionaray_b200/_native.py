@@ -61,13 +61,14 @@ class FrameDesc(C.Structure):
         ("color", C.c_void_p), ("depth", C.c_void_p),
         ("mem", C.c_int32), ("traverse", C.c_int32), ("tile_rank", C.c_int32), ("tile_nranks", C.c_int32),
         ("ray_count", C.c_void_p),
+        ("params_mem", C.c_int32), ("reserved", C.c_int32),
     ]
 
 
 # every symbol include/vsnray_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count",
-    "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_stats", "vsb_scene_download_wide",
+    "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
@@ -102,6 +103,7 @@ def cuda_lib() -> C.CDLL:
         lib.vsb_device_sm_count.argtypes = [C.POINTER(C.c_int)]
         lib.vsb_scene_create.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, C.POINTER(vp)]
         lib.vsb_scene_destroy.argtypes = [vp]
+        lib.vsb_scene_set_normals.argtypes = [vp, vp, sz, C.c_int]
         lib.vsb_scene_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
         lib.vsb_scene_download_wide.argtypes = [vp, vp, sz, vp, sz]
         for f in (lib.vsb_closest_hit, lib.vsb_any_hit):

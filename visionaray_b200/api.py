@@ -74,6 +74,16 @@ class Scene:
             N.ptr(idx) if idx is not None else None, idx.shape[0] if idx is not None else 0, C.byref(h)),
             "vsb_scene_create")
         self.handle = h
+        if host_scene.normals is not None:
+            self.set_normals(host_scene.normals)
+
+    def set_normals(self, normals):
+        """Per-face normals (n_prims x 4 float32) kept on the device with the scene."""
+        if isinstance(normals, np.ndarray):
+            p, n, mem = N.ptr(normals), normals.shape[0], MEM_HOST
+        else:
+            p, n, mem = C.c_void_p(normals.data_ptr()), normals.shape[0], MEM_DEVICE
+        _check(N.cuda_lib().vsb_scene_set_normals(self.handle, p, n, mem), "vsb_scene_set_normals")
 
     def stats(self) -> dict:
         out = (C.c_uint64 * 7)()
@@ -145,8 +155,10 @@ def tiles_of_rank(width, height, rank, nranks) -> int:
 
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
           tile_nranks=0, ray_count=None, stream=None):
-    """One frame() call.  numpy arrays -> host buffers (H2D/D2H inside the call, returns with
-    pixels in place); torch CUDA tensors -> device buffers (asynchronous on `stream`)."""
+    """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
+    the call, returns with pixels in place); torch CUDA tensor -> device render target
+    (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
+    normals attached to the scene) are host or device buffers independently of the target."""
     if isinstance(scenes, Scene):
         scenes = [scenes]
     d = N.FrameDesc()
@@ -163,6 +175,11 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.normals, d.materials, d.lights, d.color = p(normals), p(materials), p(lights), p(color)
     d.depth = None
     d.mem = MEM_HOST if host else MEM_DEVICE
+    params = [a for a in (normals, materials, lights) if a is not None]
+    kinds = {isinstance(a, np.ndarray) for a in params}
+    if len(kinds) > 1:
+        raise ValueError("normals / materials / lights must all be host arrays or all device tensors")
+    d.params_mem = MEM_HOST if (not kinds or kinds.pop()) else MEM_DEVICE
     d.traverse = traverse
     d.tile_rank, d.tile_nranks = tile_rank, tile_nranks
     d.ray_count = p(ray_count)

@@ -180,7 +180,6 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     if (p.width < 1 || p.height < 1 || p.kernel < 0 || p.kernel > 3 || p.pixel_sampler < 0 || p.pixel_sampler > 2) return VSB_ERR_BAD_ARG;
     if (p.pixel_sampler == VSB_PS_JITTERED_BLEND && p.frame_num == 0) return VSB_ERR_BAD_ARG;
     if (p.kernel != VSB_KERNEL_AO && (!d->materials || p.n_materials < 1)) return VSB_ERR_BAD_ARG;
-    if (!d->normals) return VSB_ERR_BAD_ARG;
     if (p.n_lights > 0 && !d->lights && p.kernel <= VSB_KERNEL_WHITTED) return VSB_ERR_BAD_ARG;
     for (int i = 0; i < n_scenes; ++i) if (!scenes || !scenes[i] || scenes[i]->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
@@ -203,29 +202,44 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     const size_t n_normals = scenes[0]->n_prims;
     const size_t color_px = nranks > 1 ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
     unsigned long long* d_ray_count = nullptr;
-    if (d->mem == VSB_MEM_HOST)
+    if (d->mem != VSB_MEM_HOST && d->mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    if (d->params_mem != VSB_MEM_HOST && d->params_mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    if (!d->normals && !scenes[0]->d_normals) return VSB_ERR_BAD_ARG;
+    fl.ctx.normals = d->normals ? reinterpret_cast<const float4*>(d->normals) : scenes[0]->d_normals;
+    if (d->params_mem == VSB_MEM_HOST)
     {
-        void *a, *b = nullptr, *c = nullptr, *e;
-        rc = stage(3, n_normals * 16, &a); if (rc) return rc;
-        VSB_CUDA(cudaMemcpyAsync(a, d->normals, n_normals * 16, cudaMemcpyHostToDevice, st));
+        // small per-frame parameter block: materials | lights (what cuda_sched copies as kernel
+        // arguments, detail/cuda_sched.inl:60-99); explicit normals ride along when given
+        void *a, *b = nullptr, *c = nullptr;
+        if (d->normals)
+        {
+            rc = stage(3, n_normals * 16, &a); if (rc) return rc;
+            VSB_CUDA(cudaMemcpyAsync(a, d->normals, n_normals * 16, cudaMemcpyHostToDevice, st));
+            fl.ctx.normals = reinterpret_cast<const float4*>(a);
+        }
         rc = stage(4, (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64 + (size_t)(p.n_lights > 0 ? p.n_lights : 1) * 48 + 64, &b); if (rc) return rc;
         if (d->materials) VSB_CUDA(cudaMemcpyAsync(b, d->materials, (size_t)p.n_materials * 64, cudaMemcpyHostToDevice, st));
         c = (char*)b + (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64;
         if (d->lights && p.n_lights > 0) VSB_CUDA(cudaMemcpyAsync(c, d->lights, (size_t)p.n_lights * 48, cudaMemcpyHostToDevice, st));
+        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(b);
+        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(c);
+    }
+    else
+    {
+        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(d->materials);
+        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(d->lights);
+    }
+    if (d->mem == VSB_MEM_HOST)
+    {
+        void* e;
         rc = stage(5, color_px * 16 + 16, &e); if (rc) return rc;
         if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
             VSB_CUDA(cudaMemcpyAsync(e, d->color, color_px * 16, cudaMemcpyHostToDevice, st));   // progressive state lives with the caller
-        fl.ctx.normals = reinterpret_cast<const float4*>(a);
-        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(b);
-        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(c);
         fl.color = reinterpret_cast<float4*>(e);
         if (d->ray_count) d_ray_count = g.d_work + 1;
     }
     else
     {
-        fl.ctx.normals = reinterpret_cast<const float4*>(d->normals);
-        fl.ctx.materials = reinterpret_cast<const vsb::Material*>(d->materials);
-        fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(d->lights);
         fl.color = reinterpret_cast<float4*>(d->color);
         d_ray_count = reinterpret_cast<unsigned long long*>(d->ray_count);
     }

@@ -55,6 +55,7 @@ struct vsb_scene
     uint32_t* d_indices = nullptr;       // NULL for a non-index bvh
     vsb::Node80* d_wide = nullptr;
     void*    d_wide_prims = nullptr;
+    float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
     uint32_t n_wide = 0, n_wide_prims = 0;
     int      levels = 0, depth2 = 0;
     vsb::DeviceScene dev;
@@ -186,6 +187,7 @@ extern "C" int vsb_scene_destroy(vsb_scene* s)
     if (s->d_indices) cudaFree(s->d_indices);
     if (s->d_wide) cudaFree(s->d_wide);
     if (s->d_wide_prims) cudaFree(s->d_wide_prims);
+    if (s->d_normals) cudaFree(s->d_normals);
     delete s;
     return VSB_OK;
 }
@@ -288,6 +290,18 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
     s->dev.exact.nodes = s->d_nodes2; s->dev.exact.prims = s->d_prims; s->dev.exact.indices = s->d_indices;
     s->dev.exact.prim_kind = prim_kind;
     *out = s;
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!s || !normals16 || n != s->n_prims) return VSB_ERR_BAD_ARG;
+    if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    if (!s->d_normals) VSB_CUDA(cudaMalloc((void**)&s->d_normals, n * 16));
+    VSB_CUDA(cudaMemcpyAsync(s->d_normals, normals16, n * 16,
+                             mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, g.stream));
+    VSB_CUDA(cudaStreamSynchronize(g.stream));
     return VSB_OK;
 }
 
