@@ -258,7 +258,9 @@ def run_gpu(args):
 
     tiles = api.tiles_of_rank(w, h, rank, world)
     per = max(api.tiles_of_rank(w, h, r, world) for r in range(world))
-    main = torch.cuda.current_stream()
+    # a real (non-legacy) stream: the C ABI treats a NULL stream as "the library's own stream"
+    main = torch.cuda.Stream()
+    torch.cuda.set_stream(main)
     if world > 1:
         tile_buf = [torch.zeros((per, api.TILE * api.TILE, 4), dtype=torch.float32, device="cuda") for _ in range(2)]
         gathered = torch.zeros((world, per, api.TILE * api.TILE, 4), dtype=torch.float32, device="cuda")
