@@ -416,13 +416,157 @@ def run_gpu(args):
     return 0
 
 
+def run_gpu_raylist(args):
+    """cfg5: incoherent random-ray stress.  Rays uniform in the unit cube with uniform directions
+    vs the triangle soup, processed in batches of 2^24; a step = one vsb_closest_hit (or
+    vsb_any_hit with --any) pass over one batch.  N > 1: every rank gets its own batches
+    (contiguous chunks of the global ray list, different seeds), no collective."""
+    import torch
+    import torch.distributed as dist
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the ray-query path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from visionaray_b200 import api, scenes as S
+
+    api.init(local_rank)
+    t0 = time.time()
+    sc = S.make_scene("cfg5_soup", args.scale)
+    build_s = time.time() - t0
+    dev = api.Scene(sc)
+    stats = dev.stats()
+    n_batch = args.batch
+    n_bufs = 4                                            # rotate batches: 4 x (512 MiB rays + 512 MiB hits) >> L2
+    main = torch.cuda.Stream()
+    torch.cuda.set_stream(main)
+    rays_h = [S.random_rays(n_batch, 600 + 16 * rank + i) for i in range(n_bufs)]
+    d_rays = [torch.from_numpy(r).cuda() for r in rays_h]
+    d_hits = [torch.empty((n_batch, 8), dtype=torch.int32, device="cuda") for _ in range(n_bufs)]
+    fn = api.any_hit if args.any else api.closest_hit
+    trav = api.TRAVERSE_EXACT if args.traverse == "exact" else api.TRAVERSE_WIDE
+    k = [0]
+
+    def step():
+        i = k[0] % n_bufs
+        k[0] += 1
+        fn(dev, d_rays[i], hits=d_hits[i], traverse=trav, stream=main.cuda_stream)
+
+    def fence():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        step()
+    fence()
+    launches0 = api.launch_count()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    time.sleep(0.25)
+    fence()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tw0 = time.time()
+    e0.record(main)
+    for _ in range(args.steps):
+        step()
+    e1.record(main)
+    fence()
+    tw1 = time.time()
+    t = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    clk = clocks.stop(tw0, tw1)
+    launches = (api.launch_count() - launches0) * world
+    value = n_batch * args.steps * world / (ms_total * 1e-3) / 1e6
+    kms = []
+    for _ in range(args.steps):
+        step()
+        kms.append(api.last_kernel_ms())
+    fence()
+    kernel_ms = float(np.mean(kms))
+    hit_frac = float((d_hits[0][:, 0] != 0).float().mean().item())
+
+    # e2e: host ray list in, host hit records out (pinned), H2D + D2H inside the call
+    n_e2e = min(n_batch, 1 << 22)
+    h_rays = torch.from_numpy(rays_h[0][:n_e2e].copy()).pin_memory().numpy()
+    h_hits = torch.zeros((n_e2e, 8), dtype=torch.int32).pin_memory().numpy().view(api.N.HIT_DTYPE).reshape(-1)
+    fn(dev, h_rays, hits=h_hits, traverse=trav)
+    fence()
+    e2e_steps = max(1, min(args.steps, 5))
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        fn(dev, h_rays, hits=h_hits, traverse=trav)
+    fence()
+    te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = n_e2e * e2e_steps * world / float(te.item()) / 1e6
+
+    if rank == 0:
+        from oracle import bindings as O              # checker / CPU baseline only
+        peak, peak_src = measured_peak_gbs()
+        sample = rays_h[0][:200_000]
+        c = O.Counters()
+        t0 = time.perf_counter()
+        O.oracle_query(sc, sample, bool(args.any), counters=c)
+        port_s = time.perf_counter() - t0
+        n_inner, n_prim = c.n_inner / c.n_rays, c.n_prim / c.n_rays
+        b_ray = 64.0 * n_inner + 68.0 * n_prim + 64.0
+        achieved = b_ray * n_batch / (kernel_ms * 1e-3) / 1e9
+        cpu = None
+        if world == 1 and not args.no_cpu:
+            cores = os.cpu_count() or 1
+            if O.ref_available(fast=True):
+                nref = 2_000_000
+                secs, _ = O.ref_query_timed(sc, rays_h[0][:nref], bool(args.any), nthreads=cores, reps=2, warmup=1)
+                cpu = {"value": nref / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "reference",
+                       "sample": f"{nref} rays of the same list, scalar closest_hit()/any_hit() of the unmodified headers on {cores} std::threads, best of 2"}
+            else:
+                cpu = {"value": 200_000 / port_s / 1e6, "unit": "Mrays/s", "cores": cores, "kind": "port",
+                       "sample": "200000 rays of the same list, scalar C port, pthreads"}
+        line = {
+            "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": f"incoherent random rays vs {sc.n_prims}-tri soup, {'any' if args.any else 'closest'}-hit, "
+                                   f"batches of {n_batch} rays per GPU", "traverse": args.traverse, "scale": args.scale,
+                       "l2": f"{n_bufs} rotating ray/hit batches ({n_bufs * n_batch * 64 >> 20} MiB) + scene "
+                             f"{(stats['wide_node_bytes'] + stats['wide_prim_bytes']) >> 20} MiB, all > 126 MB L2",
+                       "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "bvh2_depth": stats["bvh2_depth"],
+                       "host_build_s": build_s, "hit_fraction": hit_frac},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": "query_kernel", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
+                         "n_inner_per_ray": n_inner, "n_prim_per_ray": n_prim, "peak_source": peak_src,
+                         "roofline_mrays_s": peak * 1e9 / b_ray / 1e6},
+            "cpu_baseline": cpu,
+            "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": n_e2e * 32 * world,
+                    "d2h_bytes_per_step": n_e2e * 32 * world, "steps": e2e_steps, "rays_per_step": n_e2e},
+            "gpu_launches": int(launches), "clocks": clk,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    dev.close()
+    return 0
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS))
+    ap.add_argument("--workload", default="cfg2", choices=sorted(WORKLOADS) + ["cfg5"])
+    ap.add_argument("--any", action="store_true", help="cfg5: any-hit instead of closest-hit")
+    ap.add_argument("--batch", type=int, default=1 << 24, help="cfg5: rays per batch")
     ap.add_argument("--traverse", default="wide", choices=["wide", "exact"])
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
@@ -430,6 +574,8 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
+    if args.workload == "cfg5":
+        return run_gpu_raylist(args)
     return run_gpu(args)
 
 

@@ -78,7 +78,8 @@ _host_lib = None
 
 
 def cuda_lib_path() -> str:
-    return os.path.join(LIB_DIR, "libvsnray_b200.so")
+    # VSB_CUDA_LIB: developer hook to load a tuning variant of the same library (tools/build_variant.sh)
+    return os.environ.get("VSB_CUDA_LIB") or os.path.join(LIB_DIR, "libvsnray_b200.so")
 
 
 def host_lib_path() -> str:

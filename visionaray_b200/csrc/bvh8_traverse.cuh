@@ -35,18 +35,25 @@ VSB_HD void ray_ctx_init(RayCtx& r, float ox, float oy, float oz, float dx, floa
 
 struct NodeRegs { uint32_t w[20]; };
 
-VSB_HD void load_node(const Node80* __restrict__ nodes, uint32_t idx, NodeRegs& n)
+// Loads n16 (2, 3 or 5) 128-bit words of a 16-byte aligned record: a BVH8 node (5), a leaf-order
+// triangle (3) or sphere (2).  One code path for nodes and primitives, so a warp whose lanes are
+// in different phases still issues all its loads together.
+VSB_HD void load_record(const void* __restrict__ addr, int n16, NodeRegs& n)
 {
 #if defined(__CUDA_ARCH__)
-    const uint4* p = reinterpret_cast<const uint4*>(nodes + idx);   // 80 B records, 16-B aligned
-    uint4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2), d = __ldg(p + 3), e = __ldg(p + 4);
+    const uint4* p = reinterpret_cast<const uint4*>(addr);
+    const uint4 a = __ldg(p), b = __ldg(p + 1);
+    uint4 c = make_uint4(0u, 0u, 0u, 0u), d = c, e = c;
+    if (n16 > 2) c = __ldg(p + 2);
+    if (n16 > 3) { d = __ldg(p + 3); e = __ldg(p + 4); }
     n.w[0] = a.x; n.w[1] = a.y; n.w[2] = a.z; n.w[3] = a.w;
     n.w[4] = b.x; n.w[5] = b.y; n.w[6] = b.z; n.w[7] = b.w;
     n.w[8] = c.x; n.w[9] = c.y; n.w[10] = c.z; n.w[11] = c.w;
     n.w[12] = d.x; n.w[13] = d.y; n.w[14] = d.z; n.w[15] = d.w;
     n.w[16] = e.x; n.w[17] = e.y; n.w[18] = e.z; n.w[19] = e.w;
 #else
-    memcpy(n.w, nodes[idx].w, sizeof(n.w));
+    for (int i = 0; i < 20; ++i) n.w[i] = 0u;
+    memcpy(n.w, addr, (size_t)n16 * 16u);
 #endif
 }
 
@@ -111,46 +118,32 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit)
     return hitmask;
 }
 
-// is_closer(hr, result, max_t): update_if.h:50-56,75-79.  `limit` = min(result.t, max_t).
-VSB_HD void test_prim(const WideScene& s, uint32_t index, const RayCtx& r, HitReg& best, float& limit)
+// Primitive test on a loaded leaf-order record + is_closer(hr, result, max_t)
+// (update_if.h:50-56,75-79).  `limit` = min(result.t, max_t).
+VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg& best, float& limit)
 {
-    if (s.prim_kind == 0)
+    if (prim_kind == 0)
     {
-#if defined(__CUDA_ARCH__)
-        const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const TriRec*>(s.prims) + index);
-        const float4 a = __ldg(p), b = __ldg(p + 1), c = __ldg(p + 2);
-#else
-        const TriRec& tr = reinterpret_cast<const TriRec*>(s.prims)[index];
-        struct f4 { float x, y, z, w; };
-        const f4 a = { tr.v1x, tr.v1y, tr.v1z, u2f(tr.prim_id) }, b = { tr.e1x, tr.e1y, tr.e1z, u2f(tr.geom_id) },
-                 c = { tr.e2x, tr.e2y, tr.e2z, u2f(tr.list_index) };
-#endif
+        // TriRec: v1 | prim_id, e1 | geom_id, e2 | list_index
         float t, u, v;
-        if (isect_triangle(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, a.x, a.y, a.z, b.x, b.y, b.z, c.x, c.y, c.z, t, u, v)
+        if (isect_triangle(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]),
+                           u2f(n.w[4]), u2f(n.w[5]), u2f(n.w[6]), u2f(n.w[8]), u2f(n.w[9]), u2f(n.w[10]), t, u, v)
             && t >= 0.0f && t < limit)
         {
             best.t = t; best.u = u; best.v = v; best.hit = 1;
-            best.prim_id = f2u(a.w); best.geom_id = f2u(b.w); best.list_index = f2u(c.w);
+            best.prim_id = n.w[3]; best.geom_id = n.w[7]; best.list_index = n.w[11];
             limit = t;
         }
     }
     else
     {
-#if defined(__CUDA_ARCH__)
-        const float4* p = reinterpret_cast<const float4*>(reinterpret_cast<const SphRec*>(s.prims) + index);
-        const float4 a = __ldg(p);
-        const uint4 b = __ldg(reinterpret_cast<const uint4*>(p + 1));
-#else
-        const SphRec& sr = reinterpret_cast<const SphRec*>(s.prims)[index];
-        struct f4 { float x, y, z, w; }; struct u4 { uint32_t x, y, z, w; };
-        const f4 a = { sr.cx, sr.cy, sr.cz, sr.radius };
-        const u4 b = { sr.prim_id, sr.geom_id, sr.list_index, 0u };
-#endif
+        // SphRec: center, radius | prim_id, geom_id, list_index, pad
         float t;
-        if (isect_sphere(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, a.x, a.y, a.z, a.w, t) && t >= 0.0f && t < limit)
+        if (isect_sphere(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]), u2f(n.w[3]), t)
+            && t >= 0.0f && t < limit)
         {
             best.t = t; best.u = 0.0f; best.v = 0.0f; best.hit = 1;
-            best.prim_id = b.x; best.geom_id = b.y; best.list_index = b.z;
+            best.prim_id = n.w[4]; best.geom_id = n.w[5]; best.list_index = n.w[6];
             limit = t;
         }
     }
@@ -158,57 +151,93 @@ VSB_HD void test_prim(const WideScene& s, uint32_t index, const RayCtx& r, HitRe
 
 #define VSB_STACK_SIZE 48
 
-// Single-ray traversal.  ANY = any-hit (first accepted hit terminates, exit_traversal.h:49-57).
-// Stack entries: (base index, mask): node groups carry hit bits in 24..31 and the node's imask
-// in 0..7; primitive groups carry one bit per primitive in 0..23.
+// Per-ray traversal state.  Stack entries are node GROUPS (base index, mask): hit bits in
+// 24..31 (already permuted by the ray octant: highest set bit = nearest child) and the node's
+// inner mask in 0..7.  The primitive group (one bit per primitive in 0..23) is never stacked.
+struct TravState
+{
+    uint32_t ng_base, ng_mask;      // current node group
+    uint32_t pg_base, pg_mask;      // current primitive group
+    int      sp;
+    uint32_t stack_b[VSB_STACK_SIZE], stack_m[VSB_STACK_SIZE];
+};
+
+VSB_HD void trav_begin(TravState& t)
+{
+    // the root is "inner child at bit 31" of a virtual group with child_base 0 and imask 0
+    t.ng_base = 0u; t.ng_mask = 0x80000000u;
+    t.pg_base = 0u; t.pg_mask = 0u;
+    t.sp = 0;
+}
+
+// One traversal step of one ray: EITHER one primitive test (while the lane has primitives
+// pending) OR one node visit.  A warp whose lanes are in different phases issues all record
+// loads together (load_record) and then runs the primitive test and the node test once each,
+// every lane doing useful work in one of them -- instead of a per-lane loop over a leaf's
+// primitives that runs at the occupancy of its longest leaf (measured: 3.5 of 32 lanes).
+// Invariant on entry: pg_mask != 0 or the node group has hit bits.  Returns false when the ray
+// is finished (stack empty, or `any` and a hit was accepted: exit_traversal.h:49-57).
+VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg& best, float& limit, bool any)
+{
+    const bool prim_mode = t.pg_mask != 0u;
+    const char* addr;
+    int n16;
+    if (prim_mode)
+    {
+        const int bit = find_msb(t.pg_mask);
+        t.pg_mask &= ~(1u << bit);
+        const uint32_t index = t.pg_base + (uint32_t)bit;
+        n16 = s.prim_kind == 0 ? 3 : 2;
+        addr = reinterpret_cast<const char*>(s.prims) + (size_t)index * (size_t)(n16 * 16);
+    }
+    else
+    {
+        const int bit = find_msb(t.ng_mask);
+        t.ng_mask &= ~(1u << bit);
+        const uint32_t imask = t.ng_mask & 0xffu;
+        const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xffu)) & 7u;
+        const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
+        n16 = 5;
+        addr = reinterpret_cast<const char*>(s.nodes + (t.ng_base + rel));
+        if (t.ng_mask & 0xff000000u) { t.stack_b[t.sp] = t.ng_base; t.stack_m[t.sp] = t.ng_mask; ++t.sp; }
+    }
+
+    NodeRegs n;
+    load_record(addr, n16, n);
+
+    if (prim_mode)
+    {
+        test_prim(s.prim_kind, n, r, best, limit);
+        if (any && best.hit) return false;
+        if (t.pg_mask) return true;
+    }
+    else
+    {
+        const uint32_t hm = test_node(n, r, limit);
+        t.ng_base = n.w[4]; t.ng_mask = (hm & 0xff000000u) | (n.w[3] >> 24);
+        t.pg_base = n.w[5]; t.pg_mask = hm & 0x00ffffffu;
+        if (t.pg_mask) return true;
+    }
+
+    // no primitives pending: the next step is a node visit; pop when this group is used up
+    if ((t.ng_mask & 0xff000000u) == 0u)
+    {
+        if (t.sp == 0) return false;
+        --t.sp;
+        t.ng_base = t.stack_b[t.sp]; t.ng_mask = t.stack_m[t.sp];
+    }
+    return true;
+}
+
+// Single-ray traversal (sequential form of the loop the kernels run warp-synchronously).
 template <bool ANY>
 VSB_HD void trace_wide(const WideScene& s, const RayCtx& r, float max_t, HitReg& best)
 {
     hit_reset(best);
     float limit = max_t;
-    uint32_t stack_b[VSB_STACK_SIZE], stack_m[VSB_STACK_SIZE];
-    int sp = 0;
-    uint32_t ng_base = 0u, ng_mask = 0x80000000u;   // root: one "inner child" at bit 31, imask bit 0..7 unused
-    // the root is addressed as child_base 0 + popc(imask below slot) = 0: give it imask = 0
-    uint32_t pg_base = 0u, pg_mask = 0u;
-
-    for (;;)
-    {
-        if (ng_mask & 0xff000000u)
-        {
-            const int bit = find_msb(ng_mask);
-            ng_mask &= ~(1u << bit);
-            const uint32_t base = ng_base, imask = ng_mask & 0xffu;
-            if (ng_mask & 0xff000000u) { stack_b[sp] = ng_base; stack_m[sp] = ng_mask; ++sp; }
-            const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xffu)) & 7u;
-            const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
-            NodeRegs n;
-            load_node(s.nodes, base + rel, n);
-            const uint32_t hm = test_node(n, r, limit);
-            ng_base = n.w[4]; ng_mask = (hm & 0xff000000u) | (n.w[3] >> 24);
-            pg_base = n.w[5]; pg_mask = hm & 0x00ffffffu;
-        }
-        else
-        {
-            pg_base = ng_base; pg_mask = ng_mask;
-            ng_base = 0u; ng_mask = 0u;
-        }
-
-        while (pg_mask)
-        {
-            const int bit = find_msb(pg_mask);
-            pg_mask &= ~(1u << bit);
-            test_prim(s, pg_base + (uint32_t)bit, r, best, limit);
-            if (ANY && best.hit) return;
-        }
-
-        if ((ng_mask & 0xff000000u) == 0u)
-        {
-            if (sp == 0) break;
-            --sp;
-            ng_base = stack_b[sp]; ng_mask = stack_m[sp];
-        }
-    }
+    TravState t;
+    trav_begin(t);
+    while (trav_step(s, r, t, best, limit, ANY)) { }
 }
 
 } // namespace vsb

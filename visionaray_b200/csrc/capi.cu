@@ -40,15 +40,37 @@ int upload_scene_table(const vsb_scene* const* scenes, int n_scenes, cudaStream_
     return VSB_OK;
 }
 
+// grid = resident CTAs per SM x SM count (persistent warps pull work from the queue), capped by the
+// number of warps the work can feed
 template <typename K>
-int grid_for(K kernel, unsigned long long work_items_of_32)
+int grid_for(K kernel, size_t smem, unsigned long long items, unsigned chunk)
 {
     int per_sm = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BLOCK, 0) != cudaSuccess || per_sm < 1) per_sm = 4;
-    unsigned long long want = (work_items_of_32 + (BLOCK / 32) - 1) / (BLOCK / 32);
-    unsigned long long full = (unsigned long long)per_sm * (unsigned long long)g.sm_count;   // whole waves of resident CTAs
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, BLOCK, smem) != cudaSuccess || per_sm < 1) per_sm = 4;
+    const unsigned long long chunks = (items + chunk - 1) / chunk;
+    unsigned long long want = (chunks + (BLOCK / 32) - 1) / (BLOCK / 32);
+    unsigned long long full = (unsigned long long)per_sm * (unsigned long long)g.sm_count;
     unsigned long long grid = want < full ? want : full;
     return (int)(grid < 1 ? 1 : grid);
+}
+
+// tuning constants of the persistent loop (kernels.cuh): lanes that must be idle before the
+// continuations / refill run
+#ifndef VSB_QUERY_SERVICE_MIN
+#define VSB_QUERY_SERVICE_MIN 4
+#endif
+#ifndef VSB_FRAME_SERVICE_MIN
+#define VSB_FRAME_SERVICE_MIN 8
+#endif
+
+template <typename Program, bool EXACT, int SERVICE_MIN>
+cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
+{
+    auto kernel = vsb::trace_kernel<Program, EXACT, SERVICE_MIN>;
+    const size_t smem = (size_t)Program::STATE_WORDS * BLOCK * sizeof(uint32_t);
+    const int grid = grid_for(kernel, smem, tl.n_items, tl.chunk);
+    kernel<<<grid, BLOCK, smem, st>>>(tl, prog);
+    return cudaGetLastError();
 }
 
 int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_ray* rays, size_t n_rays,
@@ -80,15 +102,21 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
     else if (mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
 
     VSB_CUDA(cudaMemsetAsync(g.d_work, 0, sizeof(unsigned long long), st));
-    const unsigned long long warps = ((unsigned long long)n_rays + 31ull) / 32ull;
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
+    vsb::RayListProgram prog;
+    prog.rays = d_rays; prog.max_t_per_ray = d_mt; prog.max_t = max_t; prog.hits = d_hits; prog.any = any ? 1 : 0;
+    vsb::TraceLaunch tl;
+    tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_rays;
+    tl.work_counter = g.d_work; tl.ray_count = nullptr;
+    {
+        // chunk: ~16 reservations per resident warp, 32..256 rays
+        unsigned long long per = (unsigned long long)n_rays / ((unsigned long long)g.sm_count * 32ull * 16ull);
+        per = (per / 32ull) * 32ull;
+        tl.chunk = (unsigned)(per < 32ull ? 32ull : (per > 256ull ? 256ull : per));
+    }
     VSB_CUDA(cudaEventRecord(g.ev0, st));
-#define VSB_LAUNCH_QUERY(ANY, EXACT)                                                                       \
-    vsb::query_kernel<ANY, EXACT><<<grid_for(vsb::query_kernel<ANY, EXACT>, warps), BLOCK, 0, st>>>(       \
-        g.d_scenes, n_scenes, d_rays, (unsigned long long)n_rays, max_t, d_mt, d_hits, g.d_work)
-    if (any) { if (exact) VSB_LAUNCH_QUERY(true, true); else VSB_LAUNCH_QUERY(true, false); }
-    else     { if (exact) VSB_LAUNCH_QUERY(false, true); else VSB_LAUNCH_QUERY(false, false); }
-#undef VSB_LAUNCH_QUERY
+    if (exact) VSB_CUDA((launch_trace<vsb::RayListProgram, true, VSB_QUERY_SERVICE_MIN>(prog, tl, st)));
+    else       VSB_CUDA((launch_trace<vsb::RayListProgram, false, VSB_QUERY_SERVICE_MIN>(prog, tl, st)));
     ++g.launches;
     VSB_CUDA(cudaGetLastError());
     VSB_CUDA(cudaEventRecord(g.ev1, st));
@@ -185,7 +213,8 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
-    vsb::FrameLaunch fl;
+    struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles;
+             unsigned long long* ray_count; } fl;
     std::memset(&fl, 0, sizeof(fl));
     std::memcpy(&fl.ctx.p, &p, sizeof(p));
     for (int i = 0; i < 3; ++i) { fl.ctx.eye[i] = d->cam_eye[i]; fl.ctx.cu[i] = d->cam_u[i]; fl.ctx.cv[i] = d->cam_v[i]; fl.ctx.cw[i] = d->cam_w[i]; }
@@ -197,7 +226,6 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     vsb_tiles_of_rank(p.width, p.height, rank, nranks, &fl.n_owned_tiles);
     std::memcpy(fl.scissor, d->scissor, sizeof(fl.scissor));
     if (fl.scissor[2] <= 0 || fl.scissor[3] <= 0) { fl.scissor[0] = 0; fl.scissor[1] = 0; fl.scissor[2] = p.width; fl.scissor[3] = p.height; }
-    fl.scenes = g.d_scenes; fl.n_scenes = n_scenes;
 
     const size_t n_normals = scenes[0]->n_prims;
     const size_t color_px = nranks > 1 ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
@@ -246,21 +274,26 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     fl.ray_count = d_ray_count;
 
     VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 2 * sizeof(unsigned long long), st));
-    const unsigned long long packets = (unsigned long long)fl.n_owned_tiles * VSB_PACKETS_PER_TILE;
     const bool exact = d->traverse == VSB_TRAVERSE_EXACT;
+    vsb::TraceLaunch tl;
+    tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
+    tl.n_items = (unsigned long long)fl.n_owned_tiles * VSB_TILE * VSB_TILE;
+    tl.chunk = VSB_FRAME_CHUNK; tl.work_counter = g.d_work; tl.ray_count = fl.ray_count;
     VSB_CUDA(cudaEventRecord(g.ev0, st));
-#define VSB_LAUNCH_FRAME(K, EXACT)                                                                         \
-    vsb::frame_kernel<K, EXACT><<<grid_for(vsb::frame_kernel<K, EXACT>, packets), BLOCK, 0, st>>>(fl, g.d_work)
-    switch (p.kernel * 2 + (exact ? 1 : 0))
+#define VSB_LAUNCH_FRAME(K)                                                                                  \
+    do {                                                                                                     \
+        vsb::FrameProgram<K> prog;                                                                           \
+        prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
+        prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true, VSB_FRAME_SERVICE_MIN>(prog, tl, st)));  \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false, VSB_FRAME_SERVICE_MIN>(prog, tl, st))); \
+    } while (0)
+    switch (p.kernel)
     {
-    case 0: VSB_LAUNCH_FRAME(0, false); break;
-    case 1: VSB_LAUNCH_FRAME(0, true); break;
-    case 2: VSB_LAUNCH_FRAME(1, false); break;
-    case 3: VSB_LAUNCH_FRAME(1, true); break;
-    case 4: VSB_LAUNCH_FRAME(2, false); break;
-    case 5: VSB_LAUNCH_FRAME(2, true); break;
-    case 6: VSB_LAUNCH_FRAME(3, false); break;
-    default: VSB_LAUNCH_FRAME(3, true); break;
+    case 0: VSB_LAUNCH_FRAME(0); break;
+    case 1: VSB_LAUNCH_FRAME(1); break;
+    case 2: VSB_LAUNCH_FRAME(2); break;
+    default: VSB_LAUNCH_FRAME(3); break;
     }
 #undef VSB_LAUNCH_FRAME
     ++g.launches;

@@ -2,8 +2,12 @@
 //
 //  encode_level_kernel   BVH2 -> BVH8 collapse, one thread per wide node of the current level
 //  fill_prims_kernel     leaf-order primitive records (removes the indices[] indirection)
-//  query_kernel          persistent warps over a ray list: closest_hit / any_hit
-//  frame_kernel          persistent warps over 8x4-pixel packets: ray gen + kernel + store/blend
+//  trace_kernel<Program> persistent warps running ONE warp-synchronous traversal loop; lanes are
+//                        refilled individually (ray compaction): a lane whose ray finishes runs
+//                        its program's continuation (write the hit / shade / next bounce / next
+//                        pixel) while the other lanes keep their rays.  Programs: RayListProgram
+//                        (closest_hit / any_hit over a ray list) and the frame programs of
+//                        shade.cuh (simple / whitted / ao / pathtracing: ray gen + kernel + store)
 //  deinterleave_kernel   rank-major tile buffers -> row-major image (after the NCCL all-gather)
 //
 // Grids are sized as (resident CTAs per SM) x (SM count) and every warp pulls work from a
@@ -52,181 +56,181 @@ __global__ void fill_prims_kernel(int prim_kind, const void* __restrict__ prims,
     make_prim_record(prim_kind, prims, indices, leaf_list[i], out, i);
 }
 
-// ---- ray list ----------------------------------------------------------------------------------
+// ---- the persistent trace kernel ----------------------------------------------------------------
+//
+// Work items (rays of a list, pixels of a frame) are handed out in two levels: a warp reserves a
+// CHUNK of consecutive items with one atomicAdd and then refills idle lanes from its chunk with
+// ballot/popc arithmetic only.  Lane states:
+//   TRAVERSING  the lane owns a ray and takes one trav_step() per loop iteration
+//   WAITING     its ray finished; the program's done() continuation has not run yet
+//   EMPTY       no work item; wants one from the chunk
+//   DEAD        no work item and the queue is exhausted
+// The continuations and the refill ("service") run only when at least SERVICE_MIN lanes are not
+// traversing (or nobody is), so that shading / ray setup code is not executed for one lane at a
+// time: this bounds both the idle lanes (< SERVICE_MIN / 32) and the per-ray service overhead.
 
-template <bool ANY, bool EXACT>
-__device__ __forceinline__ void trace_one(const DeviceScene& s, float ox, float oy, float oz,
-                                          float dx, float dy, float dz, float max_t, HitReg& h)
-{
-    if (EXACT)
-    {
-        trace_exact<ANY>(s.exact, ox, oy, oz, dx, dy, dz, max_t, h);
-    }
-    else
-    {
-        RayCtx rc;
-        ray_ctx_init(rc, ox, oy, oz, dx, dy, dz);
-        trace_wide<ANY>(s.wide, rc, max_t, h);
-    }
-}
+enum { LANE_TRAVERSING = 0, LANE_WAITING = 1, LANE_EMPTY = 2, LANE_DEAD = 3 };
 
-// is_closer + update_if merge over the range of bvhs (detail/traverse_linear.inl:106-127):
-// each bvh is traversed from scratch, then merged with strict '<'.
-template <bool ANY, bool EXACT>
-__device__ __forceinline__ void trace_scenes(const DeviceScene* __restrict__ scenes, int n_scenes,
-                                             float ox, float oy, float oz, float dx, float dy, float dz,
-                                             float max_t, HitReg& best)
-{
-    trace_one<ANY, EXACT>(scenes[0], ox, oy, oz, dx, dy, dz, max_t, best);
-    for (int k = 1; k < n_scenes; ++k)
-    {
-        if (ANY && best.hit) return;
-        HitReg h;
-        trace_one<ANY, EXACT>(scenes[k], ox, oy, oz, dx, dy, dz, max_t, h);
-        if (h.hit && h.t >= 0.0f && h.t < best.t && h.t < max_t) best = h;
-    }
-}
-
-template <bool ANY, bool EXACT>
-__global__ void __launch_bounds__(128)
-query_kernel(const DeviceScene* __restrict__ scenes, int n_scenes, const float4* __restrict__ rays,
-             unsigned long long n_rays, float max_t, const float* __restrict__ max_t_per_ray,
-             uint4* __restrict__ hits, unsigned long long* work_counter)
-{
-    const unsigned lane = threadIdx.x & 31u;
-    for (;;)
-    {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd(work_counter, 32ull);
-        base = __shfl_sync(0xffffffffu, base, 0);
-        if (base >= n_rays) break;
-        const unsigned long long i = base + lane;
-        if (i < n_rays)
-        {
-            const float4 o = __ldg(rays + 2 * i), d = __ldg(rays + 2 * i + 1);
-            const float mt = max_t_per_ray ? __ldg(max_t_per_ray + i) : max_t;
-            HitReg h;
-            trace_scenes<ANY, EXACT>(scenes, n_scenes, o.x, o.y, o.z, d.x, d.y, d.z, mt, h);
-            uint4 a, b;
-            a.x = (uint32_t)h.hit; a.y = h.prim_id; a.z = h.geom_id; a.w = __float_as_uint(h.t);
-            b.x = __float_as_uint(h.u); b.y = __float_as_uint(h.v); b.z = h.list_index; b.w = 0u;
-            hits[2 * i] = a;
-            hits[2 * i + 1] = b;
-        }
-        __syncwarp();
-    }
-}
-
-// ---- frame -------------------------------------------------------------------------------------
-
-struct FrameLaunch
-{
-    FrameCtx ctx;
-    int scissor[4];
-    float4* color;
-    int tile_rank, tile_nranks;
-    int tiles_x, tiles_y;            // 64x64 tiles
-    int n_owned_tiles;               // tiles this rank renders
-    unsigned long long* ray_count;   // may be NULL
-    const DeviceScene* scenes;
-    int n_scenes;
-};
-
-template <bool EXACT>
-struct Tracer
+struct TraceLaunch
 {
     const DeviceScene* scenes;
     int n_scenes;
-    unsigned n_rays;
-    __device__ void closest(V3 o, V3 d, HitReg& h)
-    {
-        ++n_rays;
-        trace_scenes<false, EXACT>(scenes, n_scenes, o.x, o.y, o.z, d.x, d.y, d.z, FLT_MAX, h);
-    }
-    __device__ bool occluded(V3 o, V3 d, float max_t)
-    {
-        ++n_rays;
-        HitReg h;
-        trace_scenes<true, EXACT>(scenes, n_scenes, o.x, o.y, o.z, d.x, d.y, d.z, max_t, h);
-        return h.hit != 0;
-    }
+    unsigned long long n_items;
+    unsigned chunk;                       // items per warp reservation (multiple of 32)
+    unsigned long long* work_counter;
+    unsigned long long* ray_count;        // optional: += rays traced
 };
 
-#define VSB_TILE 64
-#define VSB_PACKETS_PER_TILE ((VSB_TILE / 8) * (VSB_TILE / 4))
+#define VSB_BLOCK 128
 
-template <int KERNEL, bool EXACT>
-__global__ void __launch_bounds__(128)
-frame_kernel(const FrameLaunch fl, unsigned long long* work_counter)
+template <typename Program, bool EXACT, int SERVICE_MIN>
+__global__ void __launch_bounds__(VSB_BLOCK)
+trace_kernel(const TraceLaunch tl, const Program prog)
 {
+    extern __shared__ uint32_t lane_store_raw[];
     const unsigned lane = threadIdx.x & 31u;
-    const FrameCtx& f = fl.ctx;
-    Tracer<EXACT> tr{ fl.scenes, fl.n_scenes, 0u };
-    const unsigned long long n_packets = (unsigned long long)fl.n_owned_tiles * VSB_PACKETS_PER_TILE;
-    const int nr = fl.tile_nranks > 1 ? fl.tile_nranks : 1;
-    const int rk = fl.tile_nranks > 1 ? fl.tile_rank : 0;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    typename Program::Lane L(lane_store_raw, threadIdx.x);
+
+    unsigned long long chunk_next = 0, chunk_end = 0;     // warp-uniform
+    bool exhausted = false;                               // warp-uniform
+    int state = LANE_EMPTY;
+    unsigned n_rays = 0;
+
+    RayCtx rc; rc.ox = rc.oy = rc.oz = rc.dx = rc.dy = rc.dz = 0.0f; rc.ix = rc.iy = rc.iz = 0.0f; rc.octinv4 = 0u;
+    HitReg best; hit_reset(best);
+    float limit = 0.0f, ray_max_t = 0.0f;
+    bool any = false;
+    int scene_i = 0;
+    WideScene sc = tl.scenes[0].wide;
+    TravState t; trav_begin(t);
+    RayReq req;
+
     for (;;)
     {
-        unsigned long long pk = 0;
-        if (lane == 0) pk = atomicAdd(work_counter, 1ull);
-        pk = __shfl_sync(0xffffffffu, pk, 0);
-        if (pk >= n_packets) break;
-        const int local_tile = (int)(pk / VSB_PACKETS_PER_TILE);
-        const int in_tile = (int)(pk % VSB_PACKETS_PER_TILE);
-        const int tile = local_tile * nr + rk;                   // interleaved: tile k -> rank k % nranks
-        const int tx = tile % fl.tiles_x, ty = tile / fl.tiles_x;
-        const int px = in_tile % (VSB_TILE / 8), py = in_tile / (VSB_TILE / 8);
-        const int lx = px * 8 + (int)(lane & 7u), ly = py * 4 + (int)(lane >> 3);
-        const int x = tx * VSB_TILE + lx, y = ty * VSB_TILE + ly;
-        const bool inside = x < f.p.width && y < f.p.height &&
-                            x >= fl.scissor[0] && y >= fl.scissor[1] &&
-                            x < fl.scissor[0] + fl.scissor[2] && y < fl.scissor[1] + fl.scissor[3];
-        if (inside)
+        const unsigned not_trav = __ballot_sync(0xffffffffu, state == LANE_WAITING || state == LANE_EMPTY);
+        const unsigned trav = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);
+        if (not_trav != 0u && (__popc(not_trav) >= SERVICE_MIN || trav == 0u))
         {
-            const uint32_t pixel = (uint32_t)y * (uint32_t)f.p.width + (uint32_t)x;
-            uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
-            float fx = (float)x, fy = (float)y;
-            if (f.p.pixel_sampler != 0)
+            // ---- continuations of finished rays ----
+            bool start = false;
+            if (state == LANE_WAITING)
             {
-                // jittered (detail/sched_common.h:197-217)
-                const float jx = rn_sub(sampler_next(samp), 0.5f);
-                const float jy = rn_sub(sampler_next(samp), 0.5f);
-                fx = rn_add(fx, jx); fy = rn_add(fy, jy);
+                if (prog.done(L, best, rc.ox, rc.oy, rc.oz, rc.dx, rc.dy, rc.dz, req)) start = true;
+                else state = LANE_EMPTY;
             }
-            V3 o, d;
-            primary_ray(f, fx, fy, o, d);
-            float col[4];
-            if (KERNEL == 0)      kernel_simple(f, tr, o, d, col);
-            else if (KERNEL == 1) kernel_whitted(f, tr, o, d, col);
-            else if (KERNEL == 2) kernel_ao(f, tr, o, d, samp, col);
-            else                  kernel_pathtracing(f, tr, o, d, samp, col);
-
-            const size_t dst = fl.tile_nranks > 1
-                ? (size_t)local_tile * (VSB_TILE * VSB_TILE) + (size_t)ly * VSB_TILE + (size_t)lx
-                : (size_t)pixel;
-            float4 c = make_float4(col[0], col[1], col[2], col[3]);
-            if (f.p.pixel_sampler == 2)
+            // ---- refill empty lanes from the warp's chunk ----
+            unsigned empty = __ballot_sync(0xffffffffu, state == LANE_EMPTY);
+            while (empty != 0u && !exhausted)
             {
-                // jittered_blend (detail/sched_common.h:516-528)
-                const float alpha = rn_div(1.0f, (float)f.p.frame_num);
-                const float ia = rn_sub(1.0f, alpha);
-                const float4 old = fl.color[dst];
-                c.x = rn_add(rn_mul(c.x, alpha), rn_mul(old.x, ia));
-                c.y = rn_add(rn_mul(c.y, alpha), rn_mul(old.y, ia));
-                c.z = rn_add(rn_mul(c.z, alpha), rn_mul(old.z, ia));
-                c.w = rn_add(rn_mul(c.w, alpha), rn_mul(old.w, ia));
+                if (chunk_next >= chunk_end)
+                {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(tl.work_counter, (unsigned long long)tl.chunk);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base >= tl.n_items) { exhausted = true; break; }
+                    chunk_next = base;
+                    chunk_end = base + tl.chunk < tl.n_items ? base + tl.chunk : tl.n_items;
+                }
+                const unsigned long long item = chunk_next + (unsigned long long)__popc(empty & lt_mask);
+                if (state == LANE_EMPTY && item < chunk_end)
+                {
+                    // begin() may reject the item (pixel outside the image / scissor): lane stays EMPTY
+                    if (prog.begin(L, item, req)) { start = true; state = LANE_WAITING; }
+                }
+                const unsigned long long taken = (unsigned long long)__popc(empty);
+                chunk_next = chunk_next + taken < chunk_end ? chunk_next + taken : chunk_end;
+                empty = __ballot_sync(0xffffffffu, state == LANE_EMPTY);
             }
-            fl.color[dst] = c;
+            if (exhausted && state == LANE_EMPTY) state = LANE_DEAD;
+            if (start)
+            {
+                ++n_rays;
+                any = req.any; ray_max_t = req.max_t; limit = req.max_t;
+                hit_reset(best);
+                if (EXACT) { rc.ox = req.ox; rc.oy = req.oy; rc.oz = req.oz; rc.dx = req.dx; rc.dy = req.dy; rc.dz = req.dz; }
+                else ray_ctx_init(rc, req.ox, req.oy, req.oz, req.dx, req.dy, req.dz);
+                scene_i = 0;
+                if (tl.n_scenes > 1) sc = tl.scenes[0].wide;
+                trav_begin(t);
+                state = LANE_TRAVERSING;
+            }
+            if (__all_sync(0xffffffffu, state == LANE_DEAD)) break;
         }
-        __syncwarp();
+
+        if (state == LANE_TRAVERSING)
+        {
+            if (EXACT)
+            {
+                // reference-order BVH2 walk (blocking); over the range of bvhs as
+                // detail/traverse_linear.inl:106-127: each bvh from scratch, merged with strict '<'
+                for (int k = 0; k < tl.n_scenes; ++k)
+                {
+                    HitReg h;
+                    if (any) trace_exact<true>(tl.scenes[k].exact, rc.ox, rc.oy, rc.oz, rc.dx, rc.dy, rc.dz, ray_max_t, h);
+                    else     trace_exact<false>(tl.scenes[k].exact, rc.ox, rc.oy, rc.oz, rc.dx, rc.dy, rc.dz, ray_max_t, h);
+                    if (k == 0) best = h;
+                    else if (h.hit && h.t >= 0.0f && h.t < best.t && h.t < ray_max_t) best = h;
+                    if (any && best.hit) break;
+                }
+                state = LANE_WAITING;
+            }
+            else if (!trav_step(sc, rc, t, best, limit, any))
+            {
+                // this bvh is finished: next bvh of the range (same best / limit == strict '<' merge)
+                if (!(any && best.hit) && ++scene_i < tl.n_scenes)
+                {
+                    sc = tl.scenes[scene_i].wide;
+                    trav_begin(t);
+                }
+                else state = LANE_WAITING;
+            }
+        }
     }
-    if (fl.ray_count)
+
+    if (tl.ray_count)
     {
-        unsigned n = tr.n_rays;
+        unsigned n = n_rays;
         for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
-        if (lane == 0 && n) atomicAdd(fl.ray_count, (unsigned long long)n);
+        if (lane == 0 && n) atomicAdd(tl.ray_count, (unsigned long long)n);
     }
 }
+
+// ---- ray list program: closest_hit()/any_hit() over a ray list ----------------------------------
+struct RayListProgram
+{
+    const float4* rays;
+    const float*  max_t_per_ray;
+    float         max_t;
+    uint4*        hits;
+    int           any;
+
+    struct Lane
+    {
+        unsigned long long item;
+        __device__ Lane(uint32_t*, unsigned) : item(0) {}
+    };
+    static constexpr int STATE_WORDS = 0;
+
+    __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
+    {
+        L.item = item;
+        const float4 o = __ldg(rays + 2 * item), d = __ldg(rays + 2 * item + 1);
+        req.ox = o.x; req.oy = o.y; req.oz = o.z; req.dx = d.x; req.dy = d.y; req.dz = d.z;
+        req.max_t = max_t_per_ray ? __ldg(max_t_per_ray + item) : max_t;
+        req.any = any != 0;
+        return true;
+    }
+    __device__ bool done(Lane& L, const HitReg& h, float, float, float, float, float, float, RayReq&) const
+    {
+        uint4 a, b;
+        a.x = (uint32_t)h.hit; a.y = h.prim_id; a.z = h.geom_id; a.w = __float_as_uint(h.t);
+        b.x = __float_as_uint(h.u); b.y = __float_as_uint(h.v); b.z = h.list_index; b.w = 0u;
+        hits[2 * L.item] = a;
+        hits[2 * L.item + 1] = b;
+        return false;
+    }
+};
 
 // gathered: [rank][tiles_per_rank_padded][64*64] float4 -> image[y*width + x]
 __global__ void deinterleave_kernel(const float4* __restrict__ gathered, int width, int height, int nranks,

@@ -174,137 +174,318 @@ VSB_HD V3 material_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, ui
     return blinn_sample(m, n, wo, wi, pdf, samp);
 }
 
-// ---- the kernels; Tracer provides closest(o, d, hit) and occluded(o, d, max_t) ------------------
+// ---- frame programs ------------------------------------------------------------------------------
+//
+// The built-in kernels as CONTINUATIONS around the persistent traversal loop (kernels.cuh,
+// trace_kernel): begin() turns a pixel into its primary ray, done() receives the finished ray's hit
+// record and either emits the next ray of that pixel (shadow ray, reflection, AO sample, path
+// bounce) or writes the pixel and frees the lane.  Per-pixel state lives in shared memory
+// (structure-of-arrays, one column per thread), not in registers, so the traversal loop keeps its
+// register budget.  The arithmetic and the order of random draws are those of the reference
+// kernels, statement for statement.
 
-template <typename Tracer>
-VSB_HD void kernel_simple(const FrameCtx& f, Tracer& tr, V3 o, V3 d, float out[4])
+#if defined(__CUDACC__)
+
+#define VSB_TILE 64
+#define VSB_FRAME_CHUNK 64          // one 8x8 pixel block per warp reservation
+
+// a ray handed to the traversal loop by a program
+struct RayReq
 {
-    HitReg h;
-    tr.closest(o, d, h);
-    if (!h.hit) { out[0] = f.p.bg[0]; out[1] = f.p.bg[1]; out[2] = f.p.bg[2]; out[3] = f.p.bg[3]; return; }
-    const V3 pos = vadd(o, vscale(d, h.t));
-    const Material m = f.materials[h.geom_id];
-    const float4 nn = f.normals[h.prim_id];
-    V3 n = v3(nn.x, nn.y, nn.z);
-    const float aw = f.p.ambient[3];
-    V3 shaded = v3(m.ca[0] * m.ka * (f.p.ambient[0] * aw), m.ca[1] * m.ka * (f.p.ambient[1] * aw), m.ca[2] * m.ka * (f.p.ambient[2] * aw));
-    const V3 view = vneg(d);
-    n = vfaceforward(n, view, n);
-    for (int i = 0; i < f.p.n_lights; ++i)
+    float ox, oy, oz, dx, dy, dz;
+    float max_t;
+    bool  any;
+};
+
+struct FrameLane
+{
+    uint32_t* base;
+    __device__ FrameLane(uint32_t* raw, unsigned tid) : base(raw + tid) {}
+    __device__ float&    f(int k) { return reinterpret_cast<float*>(base)[k * 128]; }
+    __device__ uint32_t& u(int k) { return base[k * 128]; }
+    __device__ V3   ld(int k) { return v3(f(k), f(k + 1), f(k + 2)); }
+    __device__ void st(int k, V3 a) { f(k) = a.x; f(k + 1) = a.y; f(k + 2) = a.z; }
+};
+
+enum { W_DST = 0, W_SAMP = 1, W_PHASE = 2, W_K = 3 };
+enum { PH_PRIMARY = 0, PH_BOUNCE = 1, PH_SHADOW = 2 };
+
+template <int KERNEL>
+struct FrameProgram
+{
+    FrameCtx ctx;
+    int scissor[4];
+    float4* color;
+    int tile_rank, tile_nranks;      // tile_nranks == 0: single rank, row-major target
+    int tiles_x;
+
+    using Lane = FrameLane;
+    static constexpr int STATE_WORDS = KERNEL == 1 ? 20 : (KERNEL == 0 ? 3 : 9);
+
+    __device__ void closest(RayReq& r, V3 o, V3 d) const
     {
-        const PointLight l = f.lights[i];
-        const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
-        const V3 c = shade_light(m, l, pos, n, view, wi);
-        shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
+        r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.max_t = FLT_MAX; r.any = false;
     }
-    out[0] = shaded.x; out[1] = shaded.y; out[2] = shaded.z; out[3] = 1.0f;
-}
-
-template <typename Tracer>
-VSB_HD void kernel_whitted(const FrameCtx& f, Tracer& tr, V3 o, V3 d, float out[4])
-{
-    HitReg h;
-    tr.closest(o, d, h);
-    if (!h.hit) { out[0] = f.p.bg[0]; out[1] = f.p.bg[1]; out[2] = f.p.bg[2]; out[3] = f.p.bg[3]; return; }
-    V3 color = v3(0.0f, 0.0f, 0.0f);
-    unsigned depth = 0;
-    float throughput = 1.0f;
-    const float aw = f.p.ambient[3];
-    while (h.hit && throughput > f.p.epsilon && depth++ < f.p.num_bounces)
+    __device__ void occlusion(RayReq& r, V3 o, V3 d, float max_t) const
     {
+        r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.max_t = max_t; r.any = true;
+    }
+
+    // pixel_access::store / blend (detail/pixel_access.h:38-58, detail/sched_common.h:516-528)
+    __device__ void finish(Lane& L, float r, float g, float b, float a) const
+    {
+        const size_t dst = L.u(W_DST);
+        float4 c = make_float4(r, g, b, a);
+        if (ctx.p.pixel_sampler == 2)
+        {
+            const float alpha = rn_div(1.0f, (float)ctx.p.frame_num);
+            const float ia = rn_sub(1.0f, alpha);
+            const float4 old = color[dst];
+            c.x = rn_add(rn_mul(c.x, alpha), rn_mul(old.x, ia));
+            c.y = rn_add(rn_mul(c.y, alpha), rn_mul(old.y, ia));
+            c.z = rn_add(rn_mul(c.z, alpha), rn_mul(old.z, ia));
+            c.w = rn_add(rn_mul(c.w, alpha), rn_mul(old.w, ia));
+        }
+        color[dst] = c;
+    }
+    __device__ void finish_bg(Lane& L) const { finish(L, ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3]); }
+
+    __device__ V3 ambient_term(const Material& m) const
+    {
+        const float aw = ctx.p.ambient[3];
+        return v3(m.ca[0] * m.ka * (ctx.p.ambient[0] * aw), m.ca[1] * m.ka * (ctx.p.ambient[1] * aw), m.ca[2] * m.ka * (ctx.p.ambient[2] * aw));
+    }
+    __device__ V3 face_normal(uint32_t prim_id) const
+    {
+        const float4 nn = __ldg(ctx.normals + prim_id);
+        return v3(nn.x, nn.y, nn.z);
+    }
+
+    // item -> pixel: 64x64 tiles (tile k of the frame belongs to rank k % nranks), 8x8 blocks inside
+    __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
+    {
+        const FrameCtx& f = ctx;
+        const int nr = tile_nranks > 1 ? tile_nranks : 1;
+        const int rk = tile_nranks > 1 ? tile_rank : 0;
+        const int local_tile = (int)(item / (VSB_TILE * VSB_TILE));
+        const int in_tile = (int)(item % (VSB_TILE * VSB_TILE));
+        const int block = in_tile / 64, p = in_tile % 64;
+        const int lx = (block % 8) * 8 + (p & 7), ly = (block / 8) * 8 + (p >> 3);
+        const int tile = local_tile * nr + rk;
+        const int x = (tile % tiles_x) * VSB_TILE + lx, y = (tile / tiles_x) * VSB_TILE + ly;
+        const bool inside = x < f.p.width && y < f.p.height && x >= scissor[0] && y >= scissor[1] &&
+                            x < scissor[0] + scissor[2] && y < scissor[1] + scissor[3];
+        if (!inside) return false;
+        const uint32_t pixel = (uint32_t)y * (uint32_t)f.p.width + (uint32_t)x;
+        L.u(W_DST) = tile_nranks > 1 ? (uint32_t)(local_tile * (VSB_TILE * VSB_TILE) + ly * VSB_TILE + lx) : pixel;
+        uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
+        float fx = (float)x, fy = (float)y;
+        if (f.p.pixel_sampler != 0)
+        {
+            // jittered (detail/sched_common.h:197-217)
+            const float jx = rn_sub(sampler_next(samp), 0.5f);
+            const float jy = rn_sub(sampler_next(samp), 0.5f);
+            fx = rn_add(fx, jx); fy = rn_add(fy, jy);
+        }
+        L.u(W_SAMP) = samp;
+        L.u(W_PHASE) = PH_PRIMARY;
+        V3 o, d;
+        primary_ray(f, fx, fy, o, d);
+        if (KERNEL == 1)
+        {
+            L.st(W_K + 0, v3(0.0f, 0.0f, 0.0f));     // color
+            L.f(W_K + 6) = 1.0f;                     // throughput
+            L.u(W_K + 7) = 0u;                       // depth
+        }
+        if (KERNEL == 3)
+        {
+            L.st(W_K + 0, v3(1.0f, 1.0f, 1.0f));     // dst
+            L.u(W_K + 3) = 0u;                       // bounce
+            L.u(W_K + 4) = 0u;                       // result.hit
+            if (f.p.num_bounces == 0u) { finish_bg(L); return false; }
+        }
+        closest(req, o, d);
+        return true;
+    }
+
+    __device__ bool done(Lane& L, const HitReg& h, float ox, float oy, float oz, float dx, float dy, float dz, RayReq& req) const
+    {
+        const V3 o = v3(ox, oy, oz), d = v3(dx, dy, dz);
+        if (KERNEL == 0) return done_simple(L, h, o, d);
+        if (KERNEL == 1) return done_whitted(L, h, o, d, req);
+        if (KERNEL == 2) return done_ao(L, h, o, d, req);
+        return done_pathtracing(L, h, o, d, req);
+    }
+
+    // simple::kernel -- detail/simple.inl:25-75
+    __device__ bool done_simple(Lane& L, const HitReg& h, V3 o, V3 d) const
+    {
+        const FrameCtx& f = ctx;
+        if (!h.hit) { finish_bg(L); return false; }
         const V3 pos = vadd(o, vscale(d, h.t));
         const Material m = f.materials[h.geom_id];
-        const float4 nn = f.normals[h.prim_id];
-        const V3 sn = v3(nn.x, nn.y, nn.z);
-        V3 shaded = v3(m.ca[0] * m.ka * (f.p.ambient[0] * aw), m.ca[1] * m.ka * (f.p.ambient[1] * aw), m.ca[2] * m.ka * (f.p.ambient[2] * aw));
+        V3 n = face_normal(h.prim_id);
+        V3 shaded = ambient_term(m);
         const V3 view = vneg(d);
-        const V3 n = vfaceforward(sn, view, sn);
+        n = vfaceforward(n, view, n);
         for (int i = 0; i < f.p.n_lights; ++i)
         {
             const PointLight l = f.lights[i];
-            const V3 lpos = ld3(l.pos);
-            const V3 wi = vnormalize(vsub(lpos, pos));
-            const V3 so = vadd(pos, vscale(wi, f.p.epsilon));
-            const float ld = vlength(vsub(pos, lpos));
-            if (!tr.occluded(so, wi, ld))
+            const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
+            const V3 c = shade_light(m, l, pos, n, view, wi);
+            shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
+        }
+        finish(L, shaded.x, shaded.y, shaded.z, 1.0f);
+        return false;
+    }
+
+    // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
+    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16
+    __device__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
+    {
+        const FrameCtx& f = ctx;
+        const uint32_t phase = L.u(W_PHASE);
+        V3 pos, view, shaded;
+        uint32_t prim_id, geom_id, light;
+        if (phase == PH_SHADOW)
+        {
+            pos = L.ld(W_K + 9); view = L.ld(W_K + 12); shaded = L.ld(W_K + 3);
+            prim_id = L.u(W_K + 15); geom_id = L.u(W_K + 16); light = L.u(W_K + 8);
+            if (!h.hit)
             {
+                const Material m = f.materials[geom_id];
+                const PointLight l = f.lights[light];
+                const V3 sn = face_normal(prim_id);
+                const V3 n = vfaceforward(sn, view, sn);
+                const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
                 const V3 c = shade_light(m, l, pos, n, view, wi);
                 shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
             }
+            ++light;
         }
+        else
+        {
+            if (phase == PH_PRIMARY && !h.hit) { finish_bg(L); return false; }
+            // while (hit && throughput > epsilon && depth++ < num_bounces)
+            const float throughput = L.f(W_K + 6);
+            bool go = h.hit && throughput > f.p.epsilon;
+            if (go) { const uint32_t depth = L.u(W_K + 7); go = depth < f.p.num_bounces; L.u(W_K + 7) = depth + 1u; }
+            if (!go) { const V3 c = L.ld(W_K + 0); finish(L, c.x, c.y, c.z, 1.0f); return false; }
+            pos = vadd(o, vscale(d, h.t));
+            view = vneg(d);
+            prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
+            shaded = ambient_term(f.materials[geom_id]);
+            L.st(W_K + 9, pos); L.st(W_K + 12, view); L.u(W_K + 15) = prim_id; L.u(W_K + 16) = geom_id;
+        }
+        if ((int)light < f.p.n_lights)
+        {
+            const V3 lpos = ld3(f.lights[light].pos);
+            const V3 wi = vnormalize(vsub(lpos, pos));
+            occlusion(req, vadd(pos, vscale(wi, f.p.epsilon)), wi, vlength(vsub(pos, lpos)));
+            L.st(W_K + 3, shaded); L.u(W_K + 8) = light; L.u(W_PHASE) = PH_SHADOW;
+            return true;
+        }
+        const float throughput = L.f(W_K + 6);
+        V3 color = L.ld(W_K + 0);
         color = v3(color.x + shaded.x * throughput, color.y + shaded.y * throughput, color.z + shaded.z * throughput);
-        const float kr = (m.kind == 0) ? 0.1f : 0.0f;   // specular_bounce, detail/whitted.inl:79-110
+        const float kr = (f.materials[geom_id].kind == 0) ? 0.1f : 0.0f;   // specular_bounce, detail/whitted.inl:79-110
         if (kr > 0.0f)
         {
-            const V3 dir = vreflect(view, sn);
-            o = vadd(pos, vscale(dir, f.p.epsilon));
-            d = dir;
-            tr.closest(o, d, h);
+            const V3 dir = vreflect(view, face_normal(prim_id));
+            closest(req, vadd(pos, vscale(dir, f.p.epsilon)), dir);
+            L.st(W_K + 0, color); L.f(W_K + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
+            return true;
         }
-        throughput = rn_mul(throughput, kr);
+        finish(L, color.x, color.y, color.z, 1.0f);    // throughput * 0 ends the loop
+        return false;
     }
-    out[0] = color.x; out[1] = color.y; out[2] = color.z; out[3] = 1.0f;
-}
 
-template <typename Tracer>
-VSB_HD void kernel_ao(const FrameCtx& f, Tracer& tr, V3 o, V3 d, uint32_t& samp, float out[4])
-{
-    HitReg h;
-    tr.closest(o, d, h);
-    if (!h.hit) { out[0] = f.p.bg[0]; out[1] = f.p.bg[1]; out[2] = f.p.bg[2]; out[3] = f.p.bg[3]; return; }
-    const V3 pos = vadd(o, vscale(d, h.t));
-    const float4 nn = f.normals[h.prim_id];
-    const V3 w = v3(nn.x, nn.y, nn.z);
-    V3 u, v;
-    ortho_basis(u, v, w);
-    float clr = 1.0f;
-    const float dec = 1.0f / (float)f.p.ao_samples;
-    for (int i = 0; i < f.p.ao_samples; ++i)
+    // AO kernel -- src/examples/ao/main.cpp:183-246.  State: pos 0..2, prim_id 3, clr 4, i 5
+    __device__ bool done_ao(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
-        const float u2 = sampler_next(samp);   // right-to-left argument evaluation (see above)
-        const float u1 = sampler_next(samp);
-        const V3 dir = hemisphere_dir(u, v, w, cosine_sample_hemisphere(u1, u2));
-        const V3 ao_o = vadd(pos, vscale(dir, 1E-3f));
-        if (tr.occluded(ao_o, dir, f.p.ao_radius)) clr = rn_sub(clr, dec);
+        const FrameCtx& f = ctx;
+        V3 pos; uint32_t prim_id, i; float clr;
+        if (L.u(W_PHASE) == PH_PRIMARY)
+        {
+            if (!h.hit) { finish_bg(L); return false; }
+            pos = vadd(o, vscale(d, h.t));
+            prim_id = h.prim_id; clr = 1.0f; i = 0u;
+            L.st(W_K + 0, pos); L.u(W_K + 3) = prim_id; L.u(W_PHASE) = PH_SHADOW;
+        }
+        else
+        {
+            pos = L.ld(W_K + 0); prim_id = L.u(W_K + 3); clr = L.f(W_K + 4); i = L.u(W_K + 5);
+            if (h.hit) clr = rn_sub(clr, 1.0f / (float)f.p.ao_samples);
+            ++i;
+        }
+        if ((int)i < f.p.ao_samples)
+        {
+            const V3 w = face_normal(prim_id);
+            V3 u, v;
+            ortho_basis(u, v, w);
+            uint32_t samp = L.u(W_SAMP);
+            const float u2 = sampler_next(samp);   // right-to-left argument evaluation (see lambert_sample)
+            const float u1 = sampler_next(samp);
+            L.u(W_SAMP) = samp;
+            const V3 dir = hemisphere_dir(u, v, w, cosine_sample_hemisphere(u1, u2));
+            occlusion(req, vadd(pos, vscale(dir, 1E-3f)), dir, f.p.ao_radius);
+            L.f(W_K + 4) = clr; L.u(W_K + 5) = i;
+            return true;
+        }
+        finish(L, clr, clr, clr, 1.0f);
+        return false;
     }
-    out[0] = clr; out[1] = clr; out[2] = clr; out[3] = 1.0f;
-}
 
-template <typename Tracer>
-VSB_HD void kernel_pathtracing(const FrameCtx& f, Tracer& tr, V3 o, V3 d, uint32_t& samp, float out[4])
-{
-    bool active = true, result_hit = false;
-    V3 dst = v3(1.0f, 1.0f, 1.0f);
-    const float aw = f.p.ambient[3];
-    for (unsigned bounce = 0; bounce < f.p.num_bounces; ++bounce)
+    // pathtracing::kernel -- detail/pathtracing.inl:29-121.  State: dst 0..2, bounce 3, result.hit 4
+    __device__ bool done_pathtracing(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
-        HitReg h;
-        tr.closest(o, d, h);
-        if (active && !h.hit) dst = v3(dst.x * (f.p.ambient[0] * aw), dst.y * (f.p.ambient[1] * aw), dst.z * (f.p.ambient[2] * aw));
-        active = active && h.hit;
-        if (!active) break;
-        if (bounce == 0) result_hit = true;
-        const V3 view = vneg(d);
-        const Material m = f.materials[h.geom_id];
-        const float4 nn = f.normals[h.prim_id];
-        const V3 sn = v3(nn.x, nn.y, nn.z);
-        const V3 n = vfaceforward(sn, view, sn);
-        V3 refl = v3(0.0f, 0.0f, 0.0f);
-        float pdf = 0.0f;
-        V3 src = material_sample(m, n, view, refl, pdf, samp);
-        const bool zero_pdf = pdf <= 0.0f;
-        const float w = vdot(n, refl) / pdf;
-        if (!zero_pdf) dst = v3(dst.x * (src.x * w), dst.y * (src.y * w), dst.z * (src.z * w));
-        else           dst = v3(0.0f, 0.0f, 0.0f);
-        active = active && !zero_pdf;
-        if (!active) break;
-        const V3 pos = vadd(o, vscale(d, h.t));
-        o = vadd(pos, vscale(refl, f.p.epsilon));
-        d = refl;
+        const FrameCtx& f = ctx;
+        V3 dst = L.ld(W_K + 0);
+        uint32_t bounce = L.u(W_K + 3);
+        bool result_hit = L.u(W_K + 4) != 0u;
+        const float aw = f.p.ambient[3];
+        bool finished = false;
+        if (!h.hit)
+        {
+            dst = v3(dst.x * (f.p.ambient[0] * aw), dst.y * (f.p.ambient[1] * aw), dst.z * (f.p.ambient[2] * aw));
+            finished = true;
+        }
+        else
+        {
+            if (bounce == 0u) result_hit = true;
+            const V3 view = vneg(d);
+            const Material m = f.materials[h.geom_id];
+            const V3 sn = face_normal(h.prim_id);
+            const V3 n = vfaceforward(sn, view, sn);
+            V3 refl = v3(0.0f, 0.0f, 0.0f);
+            float pdf = 0.0f;
+            uint32_t samp = L.u(W_SAMP);
+            const V3 src = material_sample(m, n, view, refl, pdf, samp);
+            L.u(W_SAMP) = samp;
+            if (pdf <= 0.0f) { dst = v3(0.0f, 0.0f, 0.0f); finished = true; }
+            else
+            {
+                const float w = vdot(n, refl) / pdf;
+                dst = v3(dst.x * (src.x * w), dst.y * (src.y * w), dst.z * (src.z * w));
+                ++bounce;
+                if (bounce >= f.p.num_bounces) { dst = v3(0.0f, 0.0f, 0.0f); finished = true; }   // still active after the last bounce
+                else
+                {
+                    const V3 pos = vadd(o, vscale(d, h.t));
+                    closest(req, vadd(pos, vscale(refl, f.p.epsilon)), refl);
+                }
+            }
+        }
+        if (finished)
+        {
+            if (result_hit) finish(L, dst.x, dst.y, dst.z, 1.0f); else finish_bg(L);
+            return false;
+        }
+        L.st(W_K + 0, dst); L.u(W_K + 3) = bounce; L.u(W_K + 4) = result_hit ? 1u : 0u;
+        return true;
     }
-    if (active) dst = v3(0.0f, 0.0f, 0.0f);
-    if (result_hit) { out[0] = dst.x; out[1] = dst.y; out[2] = dst.z; out[3] = 1.0f; }
-    else { out[0] = f.p.bg[0]; out[1] = f.p.bg[1]; out[2] = f.p.bg[2]; out[3] = f.p.bg[3]; }
-}
+};
+
+#endif // __CUDACC__
 
 } // namespace vsb
