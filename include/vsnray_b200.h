@@ -159,6 +159,10 @@ int  vsb_sync(void);                             /* wait for the library's own s
 const char* vsb_strerror(int code);
 int  vsb_version(void);
 int  vsb_device_sm_count(int* out);
+/* scheduling knobs of the persistent traversal kernel: "query_service_min", "frame_service_min"
+ * (idle lanes of a warp before finished rays are serviced / refilled, 1..32) and "phase_min"
+ * (node/primitive phase vote threshold).  Results do not depend on them. */
+int  vsb_tune(const char* key, int value);
 
 /* ---- scene: replaces cuda_index_bvh<P>(index_bvh<P> const&) upload (bvh.h:344-350,446-447)
  * and the .ref() it hands to kernels (bvh.h:364-376).  indices == NULL means a non-index

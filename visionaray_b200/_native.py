@@ -67,7 +67,7 @@ class FrameDesc(C.Structure):
 
 # every symbol include/vsnray_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
-    "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count",
+    "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
     "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_last_kernel_ms", "vsb_launch_count",
@@ -102,6 +102,12 @@ def cuda_lib() -> C.CDLL:
         lib.vsb_strerror.restype = C.c_char_p
         lib.vsb_strerror.argtypes = [C.c_int]
         lib.vsb_device_sm_count.argtypes = [C.POINTER(C.c_int)]
+        lib.vsb_tune.argtypes = [C.c_char_p, C.c_int]
+        for kv in os.environ.get("VSB_TUNE", "").split(","):      # e.g. VSB_TUNE=frame_service_min=32,phase_min=8
+            if "=" in kv:
+                k, v = kv.split("=")
+                if lib.vsb_tune(k.strip().encode(), int(v)) != 0:
+                    raise RuntimeError(f"VSB_TUNE: bad setting {kv!r}")
         lib.vsb_scene_create.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, C.POINTER(vp)]
         lib.vsb_scene_destroy.argtypes = [vp]
         lib.vsb_scene_set_normals.argtypes = [vp, vp, sz, C.c_int]

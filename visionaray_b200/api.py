@@ -43,6 +43,10 @@ def sync():
     _check(N.cuda_lib().vsb_sync(), "vsb_sync")
 
 
+def tune(key: str, value: int):
+    _check(N.cuda_lib().vsb_tune(key.encode(), int(value)), "vsb_tune")
+
+
 def sm_count() -> int:
     n = C.c_int(0)
     _check(N.cuda_lib().vsb_device_sm_count(C.byref(n)), "vsb_device_sm_count")

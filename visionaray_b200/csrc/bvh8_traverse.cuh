@@ -177,6 +177,8 @@ VSB_HD void trav_begin(TravState& t)
 // primitives that runs at the occupancy of its longest leaf (measured: 3.5 of 32 lanes).
 // Invariant on entry: pg_mask != 0 or the node group has hit bits.  Returns false when the ray
 // is finished (stack empty, or `any` and a hit was accepted: exit_traversal.h:49-57).
+VSB_HD bool trav_prim_mode(const TravState& t) { return t.pg_mask != 0u; }
+
 VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg& best, float& limit, bool any)
 {
     const bool prim_mode = t.pg_mask != 0u;
@@ -209,6 +211,19 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
     {
         test_prim(s.prim_kind, n, r, best, limit);
         if (any && best.hit) return false;
+#if defined(__CUDA_ARCH__)
+        // coherent leaves: while (nearly) all lanes that entered this primitive phase still have
+        // primitives, keep testing in a tight loop instead of paying a full step per primitive
+        const int n_enter = __popc(__activemask());
+        while (t.pg_mask && __popc(__activemask()) * 8 >= n_enter * 7)
+        {
+            const int bit = find_msb(t.pg_mask);
+            t.pg_mask &= ~(1u << bit);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(t.pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
+            test_prim(s.prim_kind, n, r, best, limit);
+            if (any && best.hit) return false;
+        }
+#endif
         if (t.pg_mask) return true;
     }
     else

@@ -54,19 +54,17 @@ int grid_for(K kernel, size_t smem, unsigned long long items, unsigned chunk)
     return (int)(grid < 1 ? 1 : grid);
 }
 
-// tuning constants of the persistent loop (kernels.cuh): lanes that must be idle before the
-// continuations / refill run
-#ifndef VSB_QUERY_SERVICE_MIN
-#define VSB_QUERY_SERVICE_MIN 4
-#endif
-#ifndef VSB_FRAME_SERVICE_MIN
-#define VSB_FRAME_SERVICE_MIN 8
-#endif
+// tuning knobs of the persistent loop (kernels.cuh), settable through vsb_tune():
+//   query_service_min / frame_service_min  lanes that must be idle before continuations + refill run
+//   phase_min                              phase vote threshold
+// frame_service_min 0 = per kernel: 32 (warp-wide lockstep; measured best for the coherent simple /
+// whitted / AO frames) or 16 (path tracing, whose bounces decorrelate the lanes)
+int g_query_service_min = 4, g_frame_service_min = 0, g_phase_min = 1;
 
-template <typename Program, bool EXACT, int SERVICE_MIN>
+template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
 {
-    auto kernel = vsb::trace_kernel<Program, EXACT, SERVICE_MIN>;
+    auto kernel = vsb::trace_kernel<Program, EXACT>;
     const size_t smem = (size_t)Program::STATE_WORDS * BLOCK * sizeof(uint32_t);
     const int grid = grid_for(kernel, smem, tl.n_items, tl.chunk);
     kernel<<<grid, BLOCK, smem, st>>>(tl, prog);
@@ -108,6 +106,7 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_rays;
     tl.work_counter = g.d_work; tl.ray_count = nullptr;
+    tl.service_min = g_query_service_min; tl.phase_min = g_phase_min;
     {
         // chunk: ~16 reservations per resident warp, 32..256 rays
         unsigned long long per = (unsigned long long)n_rays / ((unsigned long long)g.sm_count * 32ull * 16ull);
@@ -115,8 +114,8 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
         tl.chunk = (unsigned)(per < 32ull ? 32ull : (per > 256ull ? 256ull : per));
     }
     VSB_CUDA(cudaEventRecord(g.ev0, st));
-    if (exact) VSB_CUDA((launch_trace<vsb::RayListProgram, true, VSB_QUERY_SERVICE_MIN>(prog, tl, st)));
-    else       VSB_CUDA((launch_trace<vsb::RayListProgram, false, VSB_QUERY_SERVICE_MIN>(prog, tl, st)));
+    if (exact) VSB_CUDA((launch_trace<vsb::RayListProgram, true>(prog, tl, st)));
+    else       VSB_CUDA((launch_trace<vsb::RayListProgram, false>(prog, tl, st)));
     ++g.launches;
     VSB_CUDA(cudaGetLastError());
     VSB_CUDA(cudaEventRecord(g.ev1, st));
@@ -131,6 +130,16 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
 } // namespace
 
 extern "C" int vsb_version(void) { return 100; }
+
+extern "C" int vsb_tune(const char* key, int value)
+{
+    if (!key || value < 0 || value > 64) return VSB_ERR_BAD_ARG;
+    if (!std::strcmp(key, "query_service_min")) g_query_service_min = value;
+    else if (!std::strcmp(key, "frame_service_min")) g_frame_service_min = value;
+    else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
+    else return VSB_ERR_BAD_ARG;
+    return VSB_OK;
+}
 
 extern "C" const char* vsb_strerror(int code)
 {
@@ -279,14 +288,16 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
     tl.n_items = (unsigned long long)fl.n_owned_tiles * VSB_TILE * VSB_TILE;
     tl.chunk = VSB_FRAME_CHUNK; tl.work_counter = g.d_work; tl.ray_count = fl.ray_count;
+    tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel == VSB_KERNEL_PATHTRACING ? 16 : 32);
+    tl.phase_min = g_phase_min;
     VSB_CUDA(cudaEventRecord(g.ev0, st));
 #define VSB_LAUNCH_FRAME(K)                                                                                  \
     do {                                                                                                     \
         vsb::FrameProgram<K> prog;                                                                           \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
-        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true, VSB_FRAME_SERVICE_MIN>(prog, tl, st)));  \
-        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false, VSB_FRAME_SERVICE_MIN>(prog, tl, st))); \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true>(prog, tl, st)));  \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false>(prog, tl, st))); \
     } while (0)
     switch (p.kernel)
     {

@@ -65,9 +65,9 @@ __global__ void fill_prims_kernel(int prim_kind, const void* __restrict__ prims,
 //   WAITING     its ray finished; the program's done() continuation has not run yet
 //   EMPTY       no work item; wants one from the chunk
 //   DEAD        no work item and the queue is exhausted
-// The continuations and the refill ("service") run only when at least SERVICE_MIN lanes are not
+// The continuations and the refill ("service") run only when at least service_min lanes are not
 // traversing (or nobody is), so that shading / ray setup code is not executed for one lane at a
-// time: this bounds both the idle lanes (< SERVICE_MIN / 32) and the per-ray service overhead.
+// time: this bounds both the idle lanes (< service_min / 32) and the per-ray service overhead.
 
 enum { LANE_TRAVERSING = 0, LANE_WAITING = 1, LANE_EMPTY = 2, LANE_DEAD = 3 };
 
@@ -79,12 +79,33 @@ struct TraceLaunch
     unsigned chunk;                       // items per warp reservation (multiple of 32)
     unsigned long long* work_counter;
     unsigned long long* ray_count;        // optional: += rays traced
+    int service_min;                      // lanes that must be idle before continuations / refill run
+    int phase_min;                        // phase vote threshold (phase_runs)
 };
 
 #define VSB_BLOCK 128
+#ifndef VSB_MIN_BLOCKS
+#define VSB_MIN_BLOCKS 6     // <= 80 registers: 24 warps per SM (measured best of 5..8)
+#endif
 
-template <typename Program, bool EXACT, int SERVICE_MIN>
-__global__ void __launch_bounds__(VSB_BLOCK)
+// Phase vote among the traversing lanes of a warp (called by all of them): a lane is in
+// primitive phase or node phase (trav_prim_mode).  Both phases run in the same iteration when each
+// has at least `phase_min` lanes; otherwise only the majority phase runs and the minority lanes
+// wait one iteration, so neither the node test nor the primitive test is executed for a handful of
+// lanes.  Coherent packets stay in lockstep; incoherent warps gather lanes per phase.
+__device__ __forceinline__ bool phase_runs(int phase_min, bool prim_mode)
+{
+    if (phase_min <= 1) return true;
+    const unsigned m = __activemask();
+    const unsigned mp = __ballot_sync(m, prim_mode);
+    const int n_prim = __popc(mp), n_node = __popc(m) - n_prim;
+    const bool run_prim = n_prim >= phase_min || n_prim >= n_node;
+    const bool run_node = n_node >= phase_min || n_node > n_prim;
+    return prim_mode ? run_prim : run_node;
+}
+
+template <typename Program, bool EXACT>
+__global__ void __launch_bounds__(VSB_BLOCK, VSB_MIN_BLOCKS)
 trace_kernel(const TraceLaunch tl, const Program prog)
 {
     extern __shared__ uint32_t lane_store_raw[];
@@ -110,7 +131,7 @@ trace_kernel(const TraceLaunch tl, const Program prog)
     {
         const unsigned not_trav = __ballot_sync(0xffffffffu, state == LANE_WAITING || state == LANE_EMPTY);
         const unsigned trav = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);
-        if (not_trav != 0u && (__popc(not_trav) >= SERVICE_MIN || trav == 0u))
+        if (not_trav != 0u && (__popc(not_trav) >= tl.service_min || trav == 0u))
         {
             // ---- continuations of finished rays ----
             bool start = false;
@@ -175,6 +196,7 @@ trace_kernel(const TraceLaunch tl, const Program prog)
                 }
                 state = LANE_WAITING;
             }
+            else if (!phase_runs(tl.phase_min, trav_prim_mode(t))) { /* minority phase: wait for the lanes to gather */ }
             else if (!trav_step(sc, rc, t, best, limit, any))
             {
                 // this bvh is finished: next bvh of the range (same best / limit == strict '<' merge)
