@@ -1,0 +1,523 @@
+// visionaray_b200/scheduler.h -- host C++ adaptor of the drop-in boundary: the reference's
+// source-level contracts for the ray-query path, with the same names,
+// argument meaning and error behaviour, terminating in the C ABI of libvsnray_b200.so
+// (include/vsnray_b200.h).
+//
+//   reference (include/visionaray/...)                         here
+//   cuda_index_bvh<P>(index_bvh<P> const&)  bvh.h:344-350      b200_index_bvh<P>(index_bvh<P> const&)
+//   cuda_bvh<P>                             bvh.h:443-448      b200_bvh<P>
+//   tree.ref()                              bvh.h:364-376      b200_bvh_ref (POD handle)
+//   closest_hit / any_hit(ray, b, e[,max_t]) detail/traverse_linear.inl:186-318   same names (+ ray-list overloads)
+//   hit_record<ray, primitive<unsigned>>    math/intersect.h:88-115, detail/bvh/hit_record.h:30-46   hit_record
+//   pinhole_camera                          pinhole_camera.h   pinhole_camera
+//   plastic<T> / matte<T> / point_light<T>  material.h, point_light.h              same names
+//   make_kernel_params(...)                 kernels.h:328-509  same name (per-face normals overloads)
+//   simple/whitted/pathtracing::kernel<KP>  detail/*.inl       same names (+ ao::kernel, src/examples/ao)
+//   pixel_sampler::*_type                   detail/sched_common.h:29-52            same names
+//   make_sched_params(...)                  scheduler.h:164-242                    same name
+//   cuda_sched<R>::frame(K, SP, frame_num)  detail/cuda_sched.h:24-40              b200_sched<R>::frame
+//   gpu_buffer_rt / simple_buffer_rt        gpu_buffer_rt.h, simple_buffer_rt.h    same names
+//
+// Errors: the reference's path reports none (asserts only); setup errors are std::runtime_error
+// there.  Here every failing C-ABI call throws std::runtime_error with vsb_strerror().
+// User-defined kernel functors cannot cross the C ABI; they stay on the reference's own template
+// path (documented out of scope).
+#pragma once
+#ifndef VISIONARAY_B200_SCHEDULER_H
+#define VISIONARAY_B200_SCHEDULER_H 1
+
+#include <cstring>
+#include <stdexcept>
+#include <string>
+#include <type_traits>
+#include <vector>
+
+#include "../vsnray_b200.h"
+#include "bvh.h"
+#include "math.h"
+
+namespace visionaray_b200
+{
+
+namespace detail
+{
+inline void check(int rc, char const* what)
+{
+    if (rc != VSB_OK) throw std::runtime_error(std::string(what) + ": " + vsb_strerror(rc));
+}
+inline void ensure_init()
+{
+    static bool done = false;
+    if (!done) { check(vsb_init(0), "vsb_init"); done = true; }
+}
+template <typename P> struct prim_kind;
+template <> struct prim_kind<basic_triangle<3, float>> { static const int value = VSB_PRIM_TRIANGLE; };
+template <> struct prim_kind<basic_sphere<float>> { static const int value = VSB_PRIM_SPHERE; };
+} // namespace detail
+
+//-------------------------------------------------------------------------------------------------
+// Device BVH: upload + GPU re-encode (cuda_index_bvh<P> / cuda_bvh<P>, bvh.h:344-350,443-448)
+//
+
+struct b200_bvh_ref          // what .ref() hands to kernels; trivially copyable
+{
+    vsb_scene const* scene;
+};
+
+template <typename P, bool Indexed>
+class b200_bvh_base
+{
+public:
+    using primitive_type = P;
+    using bvh_ref = b200_bvh_ref;
+
+    b200_bvh_base() = default;
+    b200_bvh_base(b200_bvh_base const&) = delete;
+    b200_bvh_base& operator=(b200_bvh_base const&) = delete;
+    b200_bvh_base(b200_bvh_base&& o) noexcept : scene_(o.scene_), n_prims_(o.n_prims_), n_nodes_(o.n_nodes_) { o.scene_ = nullptr; }
+    b200_bvh_base& operator=(b200_bvh_base&& o) noexcept
+    {
+        if (this != &o) { reset(); scene_ = o.scene_; n_prims_ = o.n_prims_; n_nodes_ = o.n_nodes_; o.scene_ = nullptr; }
+        return *this;
+    }
+    ~b200_bvh_base() { reset(); }
+
+    bvh_ref ref() const { return bvh_ref{ scene_ }; }
+    size_t num_primitives() const { return n_prims_; }
+    size_t num_nodes() const { return n_nodes_; }
+
+    // per-face normals kept with the device tree (what viewer.cpp:507-521 keeps in a
+    // thrust::device_vector and hands to make_kernel_params)
+    void set_normals(vec3 const* normals, size_t count)
+    {
+        detail::check(vsb_scene_set_normals(scene_, reinterpret_cast<float const*>(normals), count, VSB_MEM_HOST), "vsb_scene_set_normals");
+    }
+
+protected:
+    void create(P const* prims, size_t np, bvh_node const* nodes, size_t nn, unsigned const* idx, size_t ni)
+    {
+        detail::ensure_init();
+        reset();
+        detail::check(vsb_scene_create(detail::prim_kind<P>::value, prims, np, reinterpret_cast<vsb_bvh_node const*>(nodes), nn,
+                                       idx, ni, &scene_), "vsb_scene_create");
+        n_prims_ = np; n_nodes_ = nn;
+    }
+    void reset() { if (scene_) { vsb_scene_destroy(scene_); scene_ = nullptr; } }
+
+    vsb_scene* scene_ = nullptr;
+    size_t n_prims_ = 0, n_nodes_ = 0;
+};
+
+template <typename P>
+class b200_index_bvh : public b200_bvh_base<P, true>
+{
+public:
+    b200_index_bvh() = default;
+    explicit b200_index_bvh(index_bvh<P> const& rhs)
+    {
+        this->create(rhs.primitives().data(), rhs.num_primitives(), rhs.nodes().data(), rhs.num_nodes(),
+                     rhs.indices().data(), rhs.num_indices());
+    }
+    // raw arrays in the reference's layouts (e.g. straight out of the reference's own index_bvh)
+    b200_index_bvh(P const* prims, size_t np, bvh_node const* nodes, size_t nn, unsigned const* idx, size_t ni)
+    {
+        this->create(prims, np, nodes, nn, idx, ni);
+    }
+};
+
+template <typename P>
+class b200_bvh : public b200_bvh_base<P, false>
+{
+public:
+    b200_bvh() = default;
+    explicit b200_bvh(bvh<P> const& rhs)
+    {
+        this->create(rhs.primitives().data(), rhs.num_primitives(), rhs.nodes().data(), rhs.num_nodes(), nullptr, 0);
+    }
+};
+
+//-------------------------------------------------------------------------------------------------
+// Ray queries (detail/traverse_linear.inl:186-318)
+//
+
+// hit_record_bvh<ray, BVH, hit_record<ray, primitive<unsigned>>>; same fields, same miss values
+struct hit_record
+{
+    int      hit;
+    unsigned prim_id;
+    unsigned geom_id;
+    float    t;
+    float    u;
+    float    v;
+    unsigned primitive_list_index;
+    unsigned pad_;
+    explicit operator bool() const { return hit != 0; }
+};
+static_assert(sizeof(hit_record) == sizeof(vsb_hit), "hit record layout");
+
+namespace detail
+{
+inline void query(bool any, b200_bvh_ref const* begin, b200_bvh_ref const* end, ray const* rays, size_t n,
+                  float max_t, float const* max_t_per_ray, hit_record* hits, int traverse)
+{
+    std::vector<vsb_scene const*> s;
+    for (auto it = begin; it != end; ++it) s.push_back(it->scene);
+    auto fn = any ? vsb_any_hit : vsb_closest_hit;
+    check(fn(s.data(), int(s.size()), reinterpret_cast<vsb_ray const*>(rays), n, max_t, max_t_per_ray,
+             reinterpret_cast<vsb_hit*>(hits), VSB_MEM_HOST, traverse, nullptr), any ? "vsb_any_hit" : "vsb_closest_hit");
+}
+} // namespace detail
+
+// single ray, as in the reference (one launch per call: for real work use the ray-list overloads)
+inline hit_record closest_hit(ray const& r, b200_bvh_ref const* begin, b200_bvh_ref const* end)
+{
+    hit_record h;
+    detail::query(false, begin, end, &r, 1, FLT_MAX, nullptr, &h, VSB_TRAVERSE_WIDE);
+    return h;
+}
+inline hit_record any_hit(ray const& r, b200_bvh_ref const* begin, b200_bvh_ref const* end, float max_t = FLT_MAX)
+{
+    hit_record h;
+    detail::query(true, begin, end, &r, 1, max_t, nullptr, &h, VSB_TRAVERSE_WIDE);
+    return h;
+}
+
+// ray lists (host memory): hits[i] = closest_hit(rays[i], begin, end)
+inline void closest_hit(ray const* rays, size_t n, b200_bvh_ref const* begin, b200_bvh_ref const* end, hit_record* hits,
+                        bool reference_order = false)
+{
+    detail::query(false, begin, end, rays, n, FLT_MAX, nullptr, hits, reference_order ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE);
+}
+inline void any_hit(ray const* rays, size_t n, b200_bvh_ref const* begin, b200_bvh_ref const* end, float max_t, hit_record* hits,
+                    bool reference_order = false)
+{
+    detail::query(true, begin, end, rays, n, max_t, nullptr, hits, reference_order ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE);
+}
+
+//-------------------------------------------------------------------------------------------------
+// Camera (camera.h:50-94), materials (material.h), point light (point_light.h)
+//
+
+class pinhole_camera
+{
+public:
+    void look_at(vec3 const& eye, vec3 const& center, vec3 const& up = vec3(0.0f, 1.0f, 0.0f)) { eye_ = eye; center_ = center; up_ = up; }
+    void perspective(float fovy, float aspect, float z_near, float z_far) { fovy_ = fovy; aspect_ = aspect; z_near_ = z_near; z_far_ = z_far; }
+    void set_viewport(recti const& viewport) { viewport_ = viewport; }
+    void set_viewport(int left, int bottom, int width, int height) { viewport_ = recti(left, bottom, width, height); }
+    recti get_viewport() const { return viewport_; }
+    float fovy() const { return fovy_; }
+    float aspect() const { return aspect_; }
+    float z_near() const { return z_near_; }
+    float z_far() const { return z_far_; }
+    vec3 const& eye() const { return eye_; }
+    vec3 const& center() const { return center_; }
+    vec3 const& up() const { return up_; }
+
+private:
+    vec3 eye_ = vec3(0.0f, 0.0f, 1.0f), center_ = vec3(0.0f), up_ = vec3(0.0f, 1.0f, 0.0f);
+    float fovy_ = 0.78539816f, aspect_ = 1.0f, z_near_ = 0.001f, z_far_ = 1000.0f;
+    recti viewport_ = recti(0, 0, 0, 0);
+};
+using camera = pinhole_camera;   // the reference's class name (camera.h)
+
+// plastic<T> / matte<T>: same getters/setters; flattened to vsb_material at frame() time
+template <typename T = float>
+class plastic
+{
+public:
+    void set_ca(vec3 const& c) { ca_ = c; } vec3 get_ca() const { return ca_; }
+    void set_cd(vec3 const& c) { cd_ = c; } vec3 get_cd() const { return cd_; }
+    void set_cs(vec3 const& c) { cs_ = c; } vec3 get_cs() const { return cs_; }
+    void set_ka(T k) { ka_ = k; } T get_ka() const { return ka_; }
+    void set_kd(T k) { kd_ = k; } T get_kd() const { return kd_; }
+    void set_ks(T k) { ks_ = k; } T get_ks() const { return ks_; }
+    void set_specular_exp(T e) { exp_ = e; } T get_specular_exp() const { return exp_; }
+    vsb_material flatten() const
+    {
+        vsb_material m; std::memset(&m, 0, sizeof(m));
+        for (int i = 0; i < 3; ++i) { m.ca[i] = ca_[i]; m.cd[i] = cd_[i]; m.cs[i] = cs_[i]; }
+        m.ka = ka_; m.kd = kd_; m.ks = ks_; m.spec_exp = exp_; m.kind = VSB_MAT_PLASTIC;
+        return m;
+    }
+private:
+    vec3 ca_ = vec3(0.0f), cd_ = vec3(0.0f), cs_ = vec3(0.0f);
+    T ka_ = T(0), kd_ = T(0), ks_ = T(0), exp_ = T(0);
+};
+
+template <typename T = float>
+class matte
+{
+public:
+    void set_ca(vec3 const& c) { ca_ = c; } vec3 get_ca() const { return ca_; }
+    void set_cd(vec3 const& c) { cd_ = c; } vec3 get_cd() const { return cd_; }
+    void set_ka(T k) { ka_ = k; } T get_ka() const { return ka_; }
+    void set_kd(T k) { kd_ = k; } T get_kd() const { return kd_; }
+    vsb_material flatten() const
+    {
+        vsb_material m; std::memset(&m, 0, sizeof(m));
+        for (int i = 0; i < 3; ++i) { m.ca[i] = ca_[i]; m.cd[i] = cd_[i]; }
+        m.ka = ka_; m.kd = kd_; m.kind = VSB_MAT_MATTE;
+        return m;
+    }
+private:
+    vec3 ca_ = vec3(0.0f), cd_ = vec3(0.0f);
+    T ka_ = T(0), kd_ = T(0);
+};
+
+template <typename T = float>
+class point_light
+{
+public:
+    vec3 position() const { return position_; }
+    void set_cl(vec3 const& cl) { cl_ = cl; }
+    void set_kl(T kl) { kl_ = kl; }
+    void set_position(vec3 const& pos) { position_ = pos; }
+    void set_constant_attenuation(T att) { att_const_ = att; }
+    void set_linear_attenuation(T att) { att_lin_ = att; }
+    void set_quadratic_attenuation(T att) { att_quad_ = att; }
+    vsb_point_light flatten() const
+    {
+        vsb_point_light l; std::memset(&l, 0, sizeof(l));
+        for (int i = 0; i < 3; ++i) { l.pos[i] = position_[i]; l.cl[i] = cl_[i]; }
+        l.kl = kl_; l.att_const = att_const_; l.att_lin = att_lin_; l.att_quad = att_quad_;
+        return l;
+    }
+private:
+    vec3 cl_ = vec3(1.0f), position_ = vec3(0.0f);
+    T kl_ = T(1), att_const_ = T(1), att_lin_ = T(0), att_quad_ = T(0);
+};
+
+//-------------------------------------------------------------------------------------------------
+// Kernel parameters and the built-in kernels (kernels.h:94-509, detail/{simple,whitted,pathtracing}.inl)
+//
+
+struct normals_per_face_binding {};
+
+template <typename Material>
+struct kernel_params
+{
+    b200_bvh_ref const* prims_begin;
+    b200_bvh_ref const* prims_end;
+    vec3 const* normals;             // host per-face normals, or nullptr = the normals attached to the device tree
+    Material const* materials;  size_t num_materials;     // indexed by geom_id
+    point_light<float> const* lights_begin; point_light<float> const* lights_end;
+    unsigned num_bounces;
+    float epsilon;
+    vec4 bg_color;
+    vec4 ambient_color;
+};
+
+// make_kernel_params(normals_per_face_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-409
+// `materials` is a contiguous container (std::vector<plastic<float>>, ...), as the reference's callers pass.
+template <typename Materials>
+auto make_kernel_params(normals_per_face_binding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
+                        Materials const& materials, point_light<float> const* lbegin, point_light<float> const* lend,
+                        unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
+                        vec4 const& ambient_color = vec4(0.0f))
+    -> kernel_params<typename std::decay<decltype(materials[0])>::type>
+{
+    using M = typename std::decay<decltype(materials[0])>::type;
+    return kernel_params<M>{ begin, end, normals, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color };
+}
+
+namespace simple      { template <typename KP> struct kernel { KP params; static const int id = VSB_KERNEL_SIMPLE; }; }
+namespace whitted     { template <typename KP> struct kernel { KP params; static const int id = VSB_KERNEL_WHITTED; }; }
+namespace pathtracing { template <typename KP> struct kernel { KP params; static const int id = VSB_KERNEL_PATHTRACING; }; }
+// the AO kernel of src/examples/ao/main.cpp:183-246 (a lambda there)
+namespace ao
+{
+template <typename KP> struct kernel { KP params; int num_samples; float radius; static const int id = VSB_KERNEL_AO; };
+}
+
+//-------------------------------------------------------------------------------------------------
+// Pixel samplers (detail/sched_common.h:29-52) and scheduler params (scheduler.h:23-242)
+//
+
+namespace pixel_sampler
+{
+struct uniform_type        { static const int id = VSB_PS_UNIFORM; };
+struct jittered_type       { static const int id = VSB_PS_JITTERED; };
+struct jittered_blend_type { static const int id = VSB_PS_JITTERED_BLEND; };
+}
+
+template <typename RT, typename PxSampler>
+struct sched_params
+{
+    using pixel_sampler_type = PxSampler;
+    pinhole_camera cam;
+    RT& rt;                    // must outlive frame(), as in the reference
+    recti scissor_box;
+};
+
+template <typename PxSampler, typename RT>
+sched_params<RT, PxSampler> make_sched_params(PxSampler, pinhole_camera const& cam, RT& rt)
+{
+    return sched_params<RT, PxSampler>{ cam, rt, recti(0, 0, int(rt.width()), int(rt.height())) };
+}
+template <typename RT>
+sched_params<RT, pixel_sampler::uniform_type> make_sched_params(pinhole_camera const& cam, RT& rt)
+{
+    return make_sched_params(pixel_sampler::uniform_type{}, cam, rt);
+}
+
+//-------------------------------------------------------------------------------------------------
+// Render targets (render_target.h:45-101, simple_buffer_rt.h:21-52, gpu_buffer_rt.h:16-48).
+// PF_RGBA32F colour, no depth (PF_UNSPECIFIED): buffer[y * width + x], y up, pitch = width.
+//
+
+enum pixel_format { PF_UNSPECIFIED = 0, PF_RGBA32F = 1 };
+
+template <pixel_format CF, pixel_format DF>
+struct render_target_ref
+{
+    vec4* color_; void* depth_; int width_, height_;
+    vec4* color() const { return color_; }
+    int width() const { return width_; }
+    int height() const { return height_; }
+};
+
+// host memory; frame() returns with the pixels in place (like tiled_sched into simple_buffer_rt)
+template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
+class simple_buffer_rt
+{
+    static_assert(CF == PF_RGBA32F && DF == PF_UNSPECIFIED, "the path writes RGBA32F colour only");
+public:
+    using color_type = vec4;
+    using ref_type = render_target_ref<CF, DF>;
+    static const int memory = VSB_MEM_HOST;
+
+    color_type* color() { return color_.data(); }
+    color_type const* color() const { return color_.data(); }
+    ref_type ref() { return ref_type{ color(), nullptr, int(width_), int(height_) }; }
+    void clear_color_buffer(vec4 const& c = vec4(0.0f)) { for (auto& p : color_) p = c; }
+    void begin_frame() {}
+    void end_frame() {}
+    void resize(size_t w, size_t h) { width_ = w; height_ = h; color_.assign(w * h, vec4(0.0f)); }
+    size_t width() const { return width_; }
+    size_t height() const { return height_; }
+private:
+    std::vector<vec4> color_;
+    size_t width_ = 0, height_ = 0;
+};
+template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
+using cpu_buffer_rt = simple_buffer_rt<CF, DF>;   // cpu_buffer_rt minus display_color_buffer() (GL: unavailable on this box)
+
+// device memory; frame() is asynchronous on the library's stream, as cuda_sched's launch is
+template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
+class gpu_buffer_rt
+{
+    static_assert(CF == PF_RGBA32F && DF == PF_UNSPECIFIED, "the path writes RGBA32F colour only");
+public:
+    using color_type = vec4;
+    using ref_type = render_target_ref<CF, DF>;
+    static const int memory = VSB_MEM_DEVICE;
+
+    gpu_buffer_rt() = default;
+    gpu_buffer_rt(gpu_buffer_rt const&) = delete;
+    gpu_buffer_rt& operator=(gpu_buffer_rt const&) = delete;
+    ~gpu_buffer_rt() { if (color_) vsb_device_free(color_); }
+
+    color_type* color() { return color_; }                      // DEVICE pointer
+    color_type const* color() const { return color_; }
+    ref_type ref() { return ref_type{ color_, nullptr, int(width_), int(height_) }; }
+    void clear_color_buffer(vec4 const& c = vec4(0.0f))
+    {
+        std::vector<vec4> tmp(width_ * height_, c);
+        detail::check(vsb_device_copy(color_, tmp.data(), tmp.size() * sizeof(vec4), VSB_MEM_DEVICE, VSB_MEM_HOST), "vsb_device_copy");
+    }
+    void begin_frame() {}
+    void end_frame() {}
+    void resize(size_t w, size_t h)
+    {
+        detail::ensure_init();
+        if (color_) { vsb_device_free(color_); color_ = nullptr; }
+        width_ = w; height_ = h;
+        void* p = nullptr;
+        detail::check(vsb_device_alloc(w * h * sizeof(vec4), &p), "vsb_device_alloc");
+        color_ = static_cast<vec4*>(p);
+        clear_color_buffer();
+    }
+    size_t width() const { return width_; }
+    size_t height() const { return height_; }
+    // read back (the reference's users go through GL or thrust copies)
+    void download(vec4* dst) const
+    {
+        detail::check(vsb_device_copy(dst, color_, width_ * height_ * sizeof(vec4), VSB_MEM_HOST, VSB_MEM_DEVICE), "vsb_device_copy");
+    }
+private:
+    vec4* color_ = nullptr;
+    size_t width_ = 0, height_ = 0;
+};
+
+//-------------------------------------------------------------------------------------------------
+// Scheduler: cuda_sched<R> (detail/cuda_sched.h:24-40).  frame() calls rt.begin_frame() first and
+// rt.end_frame() last (detail/cuda_sched.inl:309,319); kernel and sched_params are passed by
+// value; not re-entrant.
+//
+
+template <typename R = ray>
+class b200_sched
+{
+public:
+    b200_sched() = default;
+    explicit b200_sched(vec2ui) {}                    // block dims of cuda_sched: grids are sized by the library
+    b200_sched(unsigned, unsigned) {}
+
+    // image-space partition for multi-GPU: this process renders tiles k with k % nranks == rank
+    void set_tile_partition(int rank, int nranks) { tile_rank_ = rank; tile_nranks_ = nranks; }
+    void set_seed(unsigned seed) { seed_ = seed; }
+    void set_reference_order(bool on) { traverse_ = on ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE; }
+
+    template <typename K, typename SP>
+    void frame(K kernel, SP sparams, unsigned frame_num = 0)
+    {
+        detail::ensure_init();
+        sparams.rt.begin_frame();
+
+        auto const& kp = kernel.params;
+        vsb_frame_desc d; std::memset(&d, 0, sizeof(d));
+        d.p.kernel = K::id;
+        d.p.pixel_sampler = SP::pixel_sampler_type::id;
+        d.p.width = int(sparams.rt.width()); d.p.height = int(sparams.rt.height());
+        for (int i = 0; i < 3; ++i) { d.p.eye[i] = sparams.cam.eye()[i]; d.p.center[i] = sparams.cam.center()[i]; d.p.up[i] = sparams.cam.up()[i]; }
+        d.p.fovy = sparams.cam.fovy(); d.p.aspect = sparams.cam.aspect();
+        // jittered_blend: alpha = 1 / frame_num (detail/sched_common.h:516-528); the reference's
+        // callers count frames from 1 there
+        d.p.frame_num = frame_num; d.p.seed = seed_;
+        d.p.num_bounces = kp.num_bounces; d.p.epsilon = kp.epsilon;
+        std::memcpy(d.p.bg, kp.bg_color.data(), 16); std::memcpy(d.p.ambient, kp.ambient_color.data(), 16);
+        set_ao(d, kernel);
+        std::vector<vsb_material> mats(kp.num_materials);
+        for (size_t i = 0; i < kp.num_materials; ++i) mats[i] = kp.materials[i].flatten();
+        std::vector<vsb_point_light> lights;
+        for (auto l = kp.lights_begin; l != kp.lights_end; ++l) lights.push_back(l->flatten());
+        d.p.n_materials = int(mats.size()); d.p.n_lights = int(lights.size());
+        detail::check(vsb_camera_basis(&d), "vsb_camera_basis");
+        d.scissor[0] = sparams.scissor_box.x; d.scissor[1] = sparams.scissor_box.y;
+        d.scissor[2] = sparams.scissor_box.w; d.scissor[3] = sparams.scissor_box.h;
+        d.normals = reinterpret_cast<float const*>(kp.normals);
+        d.materials = mats.data(); d.lights = lights.data();
+        d.params_mem = VSB_MEM_HOST;
+        d.color = sparams.rt.color(); d.mem = std::remove_reference<decltype(sparams.rt)>::type::memory;
+        d.traverse = traverse_;
+        d.tile_rank = tile_rank_; d.tile_nranks = tile_nranks_;
+
+        std::vector<vsb_scene const*> scenes;
+        for (auto it = kp.prims_begin; it != kp.prims_end; ++it) scenes.push_back(it->scene);
+        detail::check(vsb_frame(scenes.data(), int(scenes.size()), &d, nullptr), "vsb_frame");
+
+        sparams.rt.end_frame();
+    }
+
+private:
+    template <typename K> static void set_ao(vsb_frame_desc&, K const&) {}
+    template <typename KP> static void set_ao(vsb_frame_desc& d, ao::kernel<KP> const& k) { d.p.ao_samples = k.num_samples; d.p.ao_radius = k.radius; }
+
+    int tile_rank_ = 0, tile_nranks_ = 0, traverse_ = VSB_TRAVERSE_WIDE;
+    unsigned seed_ = 1;
+};
+
+} // namespace visionaray_b200
+
+#endif // VISIONARAY_B200_SCHEDULER_H

@@ -206,6 +206,12 @@ int  vsb_tiles_of_rank(int width, int height, int rank, int nranks, int* n_tiles
 int  vsb_deinterleave_tiles(const void* gathered, int width, int height, int nranks,
                             int tiles_per_rank_padded, void* image, void* cuda_stream);
 
+/* ---- device memory helpers for host adaptors that own device render targets without linking the
+ * CUDA runtime themselves (gpu_buffer_rt, gpu_buffer_rt.h:16-48).  dst_mem / src_mem: VSB_MEM_* ---- */
+int  vsb_device_alloc(size_t bytes, void** out);
+int  vsb_device_free(void* p);
+int  vsb_device_copy(void* dst, const void* src, size_t bytes, int dst_mem, int src_mem);
+
 /* ---- timing helper for the harness: average device time (ms) of the last query/frame
  * kernels, measured with CUDA events on the stream they were launched on ---- */
 int  vsb_last_kernel_ms(float* ms);

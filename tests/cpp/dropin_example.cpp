@@ -1,0 +1,122 @@
+// dropin_example.cpp -- a reference-style program written against the host adaptor headers
+// (include/visionaray_b200/), i.e. what a user of tu500/visionaray's cuda_sched path writes after
+// switching.  Used by tests/test_dropin_cpp.py: it dumps hit records and frames
+// for the same seeded scene the Python tests regenerate and check against the oracle.
+//
+//   dropin_example <out_dir>      exit 0 ok, 2 known-answer failure, 3 no CUDA device / library error
+#include <cstdio>
+#include <fstream>
+#include <iostream>
+#include <vector>
+
+#include <visionaray_b200/scheduler.h>
+#include "../../visionaray_b200/csrc/host/scenes.h"
+
+namespace visionaray = visionaray_b200;      // the one-line switch
+using namespace visionaray;
+
+template <typename T>
+static void dump(std::string const& path, T const* p, size_t n)
+{
+    std::ofstream f(path, std::ios::binary);
+    f.write(reinterpret_cast<char const*>(p), std::streamsize(n * sizeof(T)));
+}
+
+int main(int argc, char** argv)
+{
+    std::string out = argc > 1 ? argv[1] : ".";
+    try
+    {
+        using triangle_type = basic_triangle<3, float>;
+
+        // --- GetNormal.BVH (test/unittests/get_normal.cpp:17-46) ---
+        {
+            std::vector<triangle_type> t(2);
+            t[0] = scenes::make_tri(vec3(-1, -1, 1), vec3(1, -1, 1), vec3(1, 1, 1), 0, 0);
+            t[1] = scenes::make_tri(vec3(1, -1, -1), vec3(-1, -1, -1), vec3(-1, 1, -1), 1, 1);
+            auto bvh = build<index_bvh<triangle_type>>(t.data(), t.size());
+            b200_index_bvh<triangle_type> d_bvh(bvh);
+            b200_bvh_ref refs[1] = { d_bvh.ref() };
+            ray r(vec3(0.5f, -0.5f, 2.0f), vec3(0.0f, 0.0f, -1.0f));
+            auto hr = closest_hit(r, refs, refs + 1);
+            if (!hr.hit || hr.t != 1.0f || hr.prim_id != 0) { std::cerr << "known-answer test failed\n"; return 2; }
+            if (any_hit(r, refs, refs + 1, 0.5f).hit) { std::cerr << "any_hit max_t failed\n"; return 2; }
+        }
+
+        // --- scene: UV sphere, binned-SAH index_bvh on the host, upload + GPU re-encode ---
+        std::vector<triangle_type> tris;
+        scenes::uv_sphere(tris, 50, 50, 1.0f);
+        auto bvh = build<index_bvh<triangle_type>>(tris.data(), tris.size());
+        std::vector<vec3> normals;
+        scenes::face_normals(normals, tris);
+        b200_index_bvh<triangle_type> d_bvh(bvh);
+        d_bvh.set_normals(normals.data(), normals.size());
+        b200_bvh_ref prims[1] = { d_bvh.ref() };
+
+        // --- ray list: closest_hit / any_hit ---
+        std::vector<ray> rays(20000);
+        scenes::random_rays(rays.data(), rays.size(), 3, -1.5f, 1.5f);
+        std::vector<hit_record> wide(rays.size()), exact(rays.size()), occ(rays.size());
+        closest_hit(rays.data(), rays.size(), prims, prims + 1, wide.data());
+        closest_hit(rays.data(), rays.size(), prims, prims + 1, exact.data(), true);
+        any_hit(rays.data(), rays.size(), prims, prims + 1, 0.5f, occ.data());
+        dump(out + "/hits_wide.bin", wide.data(), wide.size());
+        dump(out + "/hits_exact.bin", exact.data(), exact.size());
+        dump(out + "/hits_any.bin", occ.data(), occ.size());
+
+        // --- frame(): Whitted kernel, one point light at the eye, plastic material ---
+        int w = 160, h = 120;
+        pinhole_camera cam;
+        cam.look_at(vec3(0.0f, 0.0f, 3.0f), vec3(0.0f), vec3(0.0f, 1.0f, 0.0f));
+        cam.perspective(45.0f * 3.14159265358979323846f / 180.0f, float(w) / float(h), 0.001f, 1000.0f);
+        cam.set_viewport(0, 0, w, h);
+
+        std::vector<plastic<float>> materials(1);
+        materials[0].set_ca(vec3(0.2f)); materials[0].set_ka(1.0f);
+        materials[0].set_cd(vec3(0.8f)); materials[0].set_kd(1.0f);
+        materials[0].set_cs(vec3(0.1f)); materials[0].set_ks(1.0f);
+        materials[0].set_specular_exp(32.0f);
+        std::vector<point_light<float>> lights(1);
+        lights[0].set_position(vec3(0.0f, 0.0f, 3.0f));
+
+        auto kparams = make_kernel_params(normals_per_face_binding{}, prims, prims + 1, (vec3 const*)nullptr, materials,
+                                          lights.data(), lights.data() + lights.size(), 4, 1e-3f,
+                                          vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(0.0f));
+        whitted::kernel<decltype(kparams)> kernel{ kparams };
+
+        simple_buffer_rt<PF_RGBA32F, PF_UNSPECIFIED> host_rt;
+        host_rt.resize(w, h);
+        b200_sched<ray> sched;
+        auto sparams = make_sched_params(pixel_sampler::uniform_type{}, cam, host_rt);
+        sched.frame(kernel, sparams);
+        dump(out + "/frame_whitted.bin", host_rt.color(), size_t(w) * h);
+
+        gpu_buffer_rt<PF_RGBA32F, PF_UNSPECIFIED> dev_rt;
+        dev_rt.resize(w, h);
+        auto sparams_dev = make_sched_params(cam, dev_rt);
+        sched.frame(kernel, sparams_dev);
+        std::vector<vec4> back(size_t(w) * h);
+        dev_rt.download(back.data());
+        if (std::memcmp(back.data(), host_rt.color(), back.size() * sizeof(vec4)) != 0) { std::cerr << "gpu_buffer_rt != simple_buffer_rt\n"; return 2; }
+
+        // --- progressive path tracing: jittered_blend, frame_num = 1..3 ---
+        std::vector<matte<float>> mattes(1);
+        mattes[0].set_ca(vec3(0.2f)); mattes[0].set_ka(1.0f); mattes[0].set_cd(vec3(0.8f)); mattes[0].set_kd(1.0f);
+        auto kp2 = make_kernel_params(normals_per_face_binding{}, prims, prims + 1, (vec3 const*)nullptr, mattes,
+                                      lights.data(), lights.data() + lights.size(), 4, 1e-3f,
+                                      vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(1.0f));
+        pathtracing::kernel<decltype(kp2)> pt{ kp2 };
+        host_rt.clear_color_buffer();
+        auto sp2 = make_sched_params(pixel_sampler::jittered_blend_type{}, cam, host_rt);
+        for (unsigned frame_num = 1; frame_num <= 3; ++frame_num) sched.frame(pt, sp2, frame_num);
+        dump(out + "/frame_pt.bin", host_rt.color(), size_t(w) * h);
+
+        std::printf("dropin_example ok: %zu triangles, %zu nodes, %zu rays\n", tris.size(), bvh.num_nodes(), rays.size());
+        return 0;
+    }
+    catch (std::exception const& e)
+    {
+        std::cerr << "error: " << e.what() << "\n";
+        return 3;
+    }
+}

@@ -1,0 +1,60 @@
+"""The host C++ adaptor (include/visionaray_b200/scheduler.h): a reference-style program compiled
+with g++ against libvsnray_b200.so.  CPU tier: it builds, links, and fails loudly without a GPU.
+GPU tier: its hit records and frames match the oracle on the same seeded scene."""
+import os
+import subprocess
+import tempfile
+
+import numpy as np
+import pytest
+
+from conftest import classify_closest
+from oracle import bindings as O
+from visionaray_b200 import scenes as S
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+EXE = os.path.join(ROOT, "tests", "cpp", "dropin_example")
+
+
+def run(outdir):
+    env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "visionaray_b200", "lib") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
+    return subprocess.run([EXE, outdir], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+
+
+def test_builds_and_fails_loudly_without_gpu():
+    assert os.path.exists(EXE), "tests/cpp/dropin_example not built (__graft_entry__.build())"
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    with tempfile.TemporaryDirectory() as d:
+        r = run(d)
+    assert r.returncode == 3 and "no CUDA device" in r.stdout, r.stdout
+
+
+@pytest.mark.gpu
+def test_dropin_program_matches_oracle(gpu):
+    with tempfile.TemporaryDirectory() as d:
+        r = run(d)
+        assert r.returncode == 0, r.stdout
+        sc = S.make_scene("cfg1_sphere", (50 / 224) ** 2)     # uv_sphere(50, 50)
+        assert sc.n_prims == 2 * 50 * 49
+        rays = S.random_rays(20000, 3, -1.5, 1.5)
+        want = O.oracle_query(sc, rays, False)
+        exact = np.fromfile(os.path.join(d, "hits_exact.bin"), dtype=O.HIT_DTYPE)
+        wide = np.fromfile(os.path.join(d, "hits_wide.bin"), dtype=O.HIT_DTYPE)
+        occ = np.fromfile(os.path.join(d, "hits_any.bin"), dtype=O.HIT_DTYPE)
+        assert exact.tobytes() == want.tobytes()
+        assert classify_closest(want, wide)["bad"] == 0
+        assert (occ["hit"] == O.oracle_query(sc, rays, True, 0.5)["hit"]).all()
+        eye = (0.0, 0.0, 3.0)
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
+        ref = O.oracle_frame(sc, fp, S.default_material(0), S.point_light(eye))
+        img = np.fromfile(os.path.join(d, "frame_whitted.bin"), dtype=np.float32).reshape(120, 160, 4)
+        assert float((np.abs(img - ref).max(axis=2) > 1 / 255).mean()) <= 2e-4
+        acc = np.zeros((120, 160, 4), dtype=np.float32)
+        for frame_num in (1, 2, 3):
+            fp = S.frame_params(3, 160, 120, eye, (0, 0, 0), pixel_sampler=2, frame_num=frame_num, num_bounces=4, ambient=(1, 1, 1, 1))
+            O.oracle_frame(sc, fp, S.default_material(1), S.point_light(eye), rgba=acc)
+        pt = np.fromfile(os.path.join(d, "frame_pt.bin"), dtype=np.float32).reshape(120, 160, 4)
+        assert float((np.abs(pt - acc).max(axis=2) > 1 / 255).mean()) <= 5e-3

@@ -70,7 +70,7 @@ ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
     "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
-    "vsb_deinterleave_tiles", "vsb_last_kernel_ms", "vsb_launch_count",
+    "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
 
 _cuda_lib = None

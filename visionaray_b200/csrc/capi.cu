@@ -333,6 +333,31 @@ extern "C" int vsb_deinterleave_tiles(const void* gathered, int width, int heigh
     return VSB_OK;
 }
 
+extern "C" int vsb_device_alloc(size_t bytes, void** out)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!out || bytes == 0) return VSB_ERR_BAD_ARG;
+    VSB_CUDA(cudaMalloc(out, bytes));
+    return VSB_OK;
+}
+
+extern "C" int vsb_device_free(void* p)
+{
+    if (p) VSB_CUDA(cudaFree(p));
+    return VSB_OK;
+}
+
+extern "C" int vsb_device_copy(void* dst, const void* src, size_t bytes, int dst_mem, int src_mem)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!dst || !src) return VSB_ERR_BAD_ARG;
+    const cudaMemcpyKind kind = dst_mem == VSB_MEM_DEVICE ? (src_mem == VSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice)
+                                                          : (src_mem == VSB_MEM_DEVICE ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost);
+    VSB_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, g.stream));
+    VSB_CUDA(cudaStreamSynchronize(g.stream));
+    return VSB_OK;
+}
+
 extern "C" int vsb_last_kernel_ms(float* ms)
 {
     int rc = require_init(); if (rc) return rc;
