@@ -19,7 +19,7 @@ closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.j
 
 N > 1 (torchrun): the frame is partitioned into interleaved 64x64 tiles (tile k -> rank k % N), the
 scene is replicated, every step ends with one NCCL all-gather of the tile buffers + de-interleave.
-Weak scaling: the frame grows with N (4096^2 pixels per GPU).
+Weak scaling: the same view at sqrt(N) x the resolution per axis (4096^2 pixels per GPU).
 """
 from __future__ import annotations
 
@@ -114,18 +114,12 @@ def measured_peak_gbs():
 
 
 def frame_shape(wl: dict, n_gpus: int):
-    """Weak scaling: 4096^2 (base) pixels per GPU; the frame doubles in x, then y, ..."""
-    w, h = wl["w"], wl["h"]
-    k = 0
-    n = n_gpus
-    while n > 1:
-        if k % 2 == 0:
-            w *= 2
-        else:
-            h *= 2
-        n //= 2
-        k += 1
-    return w, h
+    """Weak scaling: the same view at sqrt(N) x the resolution per axis (rounded to whole 64-pixel
+    tiles), i.e. base-frame pixels per GPU and the same mix of sky / geometry / secondary rays."""
+    if n_gpus <= 1:
+        return wl["w"], wl["h"]
+    f = math.sqrt(n_gpus)
+    return int(round(wl["w"] * f / 64.0)) * 64, int(round(wl["h"] * f / 64.0)) * 64
 
 
 def make_frame_params(S, wl: dict, w: int, h: int, frame_num: int = 1):
