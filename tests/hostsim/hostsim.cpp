@@ -4,6 +4,7 @@
 #include <cstdint>
 #include <cstdlib>
 #include <cstring>
+#include <utility>
 #include <vector>
 
 #include "../../visionaray_b200/csrc/bvh8_traverse.cuh"
@@ -45,11 +46,32 @@ void* hs_build(int prim_kind, const void* prims, size_t n_prims, const void* nod
     cur[0].bvh2_node = 0; cur[0].wide_index = 0;
     uint32_t node_count = 1, prim_count = 0;
     w->levels = 0;
+    // collapse DP in post-order (sequential form of collapse_dp_kernel)
+    std::vector<CollapseCost> cost(n_nodes2);
+    std::vector<CollapseDec> dec(n_nodes2);
+    {
+        std::vector<std::pair<uint32_t, int>> st;
+        st.push_back({ 0u, 0 });
+        while (!st.empty())
+        {
+            auto cur_ = st.back(); st.pop_back();
+            const Node32& n = n2[cur_.first];
+            if (n.num_prims != 0) { dp_leaf(n, cost[cur_.first], dec[cur_.first]); continue; }
+            if (cur_.second == 0)
+            {
+                st.push_back({ cur_.first, 1 });
+                st.push_back({ n.first, 0 });
+                st.push_back({ n.first + 1, 0 });
+            }
+            else dp_inner(n, cost[n.first], cost[n.first + 1], cost[cur_.first], dec[cur_.first]);
+        }
+    }
+    const CollapseDec* decp = getenv("VSB_HOSTSIM_GREEDY") ? nullptr : dec.data();
     while (!cur.empty())
     {
         uint32_t task_count = 0;
         Alloc an{ &node_count }, ap{ &prim_count }, at{ &task_count };
-        for (auto const& t : cur) collapse_node(t, n2, w->nodes.data(), leaf_list.data(), next.data(), an, ap, at);
+        for (auto const& t : cur) collapse_node(t, n2, w->nodes.data(), leaf_list.data(), next.data(), an, ap, at, decp);
         cur.assign(next.begin(), next.begin() + task_count);
         ++w->levels;
     }

@@ -47,9 +47,9 @@ def check_wide_tree(sc, nodes, prims):
     meta, imask = d["meta"], d["imask"]
     count = meta >> 5
     ofs = meta & 31
-    is_inner = (count == 1) & (ofs >= 24)
-    # imask agrees with meta
-    assert ((np.packbits(is_inner[:, ::-1], axis=1)[:, 0]) == imask).all()
+    is_inner = ((imask[:, None] >> np.arange(8)[None, :]) & 1).astype(bool)
+    assert (meta[is_inner] == 0).all()                      # inner children carry no primitive bits
+    assert (count <= 4).all() and ((ofs + count)[count > 0] <= 32).all()
     seen_nodes = np.zeros(n, dtype=np.int64)
     seen_nodes[0] = 1
     # exact bounds of everything below each wide node (union of primitive bounds), bottom-up via
@@ -59,7 +59,7 @@ def check_wide_tree(sc, nodes, prims):
     for i in range(n - 1, -1, -1):
         rank = 0
         for s in range(8):
-            if meta[i, s] == 0:
+            if meta[i, s] == 0 and not is_inner[i, s]:
                 continue
             lo, hi = d["lo"][i, s], d["hi"][i, s]
             if is_inner[i, s]:

@@ -1,0 +1,32 @@
+#!/usr/bin/env python
+"""Instruction / stall-sample shares per code region of the trace kernel (file + line ranges)."""
+import csv, io, subprocess, sys
+def load(path):
+    out = subprocess.run(["ncu","-i",path,"--page","source","--print-source","cuda,sass","--csv"],stdout=subprocess.PIPE,text=True).stdout
+    rows=list(csv.reader(io.StringIO(out))); fname="";h=None;L=[]
+    for r in rows:
+        if len(r)==2 and r[0]=="File Path": fname=r[1].split("/")[-1]; continue
+        if len(r)>5 and r[0]=="Line No": h=r; continue
+        if h and len(r)==len(h) and r[0] not in("","Line No") and r[2]=="-": L.append((fname,int(r[0]),r))
+    return h,L
+def region(fn, ln, src):
+    if fn=="bvh8_traverse.cuh":
+        if "test_node" in src or 56<=ln<=118: return "node_test"
+        if 119<=ln<=150: return "prim_test"
+        if ln<56: return "ray_init/load_record"
+        return "trav_step control/stack"
+    if fn=="bvh8.cuh": return "node_test"
+    if fn=="vsb_common.cuh": return "prim_test / shading arithmetic"
+    if fn=="kernels.cuh": return "kernel loop (service, refill, program)"
+    if fn=="shade.cuh": return "shade programs"
+    return fn
+path=sys.argv[1]
+h,L=load(path)
+ii=h.index("Instructions Executed"); ti=h.index("Thread Instructions Executed"); si=h.index("# Samples")
+f=lambda v: float(v) if v not in("","-") else 0.0
+g={}
+for fn,ln,r in L:
+    a=g.setdefault(region(fn,ln,r[1]),[0,0,0]); a[0]+=f(r[ii]); a[1]+=f(r[ti]); a[2]+=f(r[si])
+T=sum(a[0] for a in g.values()); S=sum(a[2] for a in g.values())
+print(f"# {path}: warp instructions {T:.4g}")
+for k,a in sorted(g.items(), key=lambda x:-x[1][0]): print(f"  {k:40s} inst%={100*a[0]/T:5.1f} active_threads={a[1]/a[0] if a[0] else 0:5.1f} stall_samples%={100*a[2]/S:5.1f}")

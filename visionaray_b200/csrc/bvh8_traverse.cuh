@@ -57,10 +57,19 @@ VSB_HD void load_record(const void* __restrict__ addr, int n16, NodeRegs& n)
 #endif
 }
 
-// Tests the 8 children of a node against the ray; returns the hit mask: bits 24..31 = inner
-// children (bit = 24 + (slot ^ octinv), so the highest set bit is the nearest slot), bits
-// 0..23 = leaf primitives (one bit per primitive of every hit leaf child).
-VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit)
+// bit i of the result = bit (i ^ x) of h, for an 8-bit mask h and x in 0..7
+VSB_HD uint32_t perm_xor8(uint32_t h, uint32_t x)
+{
+    if (x & 1u) h = ((h & 0x55u) << 1) | ((h >> 1) & 0x55u);
+    if (x & 2u) h = ((h & 0x33u) << 2) | ((h >> 2) & 0x33u);
+    if (x & 4u) h = ((h & 0x0fu) << 4) | ((h >> 4) & 0x0fu);
+    return h;
+}
+
+// Tests the 8 children of a node against the ray.  Returns the node hit mask: bits 24..31 = inner
+// children (bit = 24 + (slot ^ octinv), so the highest set bit is the nearest slot); prim_hits
+// gets one bit per leaf primitive of every hit leaf child (up to 8 leaves x 4 primitives).
+VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
 {
     const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
     const uint32_t e = n.w[3];
@@ -85,7 +94,7 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit)
 
     // near/far planes by direction sign (selected once per node, not per child)
     const bool nx = r.ix < 0.0f, ny = r.iy < 0.0f, nz = r.iz < 0.0f;
-    uint32_t hitmask = 0;
+    uint32_t child_hits = 0u, ph = 0u;
 #pragma unroll
     for (int half = 0; half < 2; ++half)
     {
@@ -95,10 +104,6 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit)
         const uint32_t qnx = nx ? qhix : qlox, qfx = nx ? qlox : qhix;
         const uint32_t qny = ny ? qhiy : qloy, qfy = ny ? qloy : qhiy;
         const uint32_t qnz = nz ? qhiz : qloz, qfz = nz ? qloz : qhiz;
-        const uint32_t is_inner4 = (meta4 & (meta4 << 1)) & 0x10101010u;
-        const uint32_t inner_mask4 = (is_inner4 >> 4) * 0xffu;
-        const uint32_t bit_index4 = (meta4 ^ (r.octinv4 & inner_mask4)) & 0x1f1f1f1fu;
-        const uint32_t count4 = (meta4 >> 5) & 0x07070707u;
 #pragma unroll
         for (int k = 0; k < 4; ++k)
         {
@@ -110,12 +115,16 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit)
             const float tfz = fma_f(byte_as_unit_float(qfz, k), szs, ofz);
             const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, limit));
-            const uint32_t cnt = (count4 >> (8 * k)) & 0xffu;
-            const uint32_t pos = (bit_index4 >> (8 * k)) & 0xffu;
-            if (tmin <= tmax) hitmask |= bit_mask(pos, cnt);   // empty slots have cnt = 0
+            const uint32_t m = (meta4 >> (8 * k)) & 0xffu;       // leaf: count << 5 | offset; inner / empty: 0
+            if (tmin <= tmax)
+            {
+                child_hits |= 1u << (4 * half + k);
+                ph |= bit_mask(m & 31u, m >> 5);
+            }
         }
     }
-    return hitmask;
+    prim_hits = ph;
+    return perm_xor8(child_hits & (n.w[3] >> 24), r.octinv4 & 7u) << 24;
 }
 
 // Primitive test on a loaded leaf-order record + is_closer(hr, result, max_t)
@@ -153,14 +162,48 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
 
 // Per-ray traversal state.  Stack entries are node GROUPS (base index, mask): hit bits in
 // 24..31 (already permuted by the ray octant: highest set bit = nearest child) and the node's
-// inner mask in 0..7.  The primitive group (one bit per primitive in 0..23) is never stacked.
+// inner mask in 0..7.  The primitive group (base + one bit per primitive, 32 bits) is never stacked.
+#ifndef VSB_SHARED_STACK
+#define VSB_SHARED_STACK 16     // entries per thread kept in shared memory (device); deeper ones spill to local
+#endif
+#ifndef VSB_PREFETCH
+#define VSB_PREFETCH 0     // measured: no gain (the unified loads already overlap); kept as a switch
+#endif
+
 struct TravState
 {
     uint32_t ng_base, ng_mask;      // current node group
     uint32_t pg_base, pg_mask;      // current primitive group
     int      sp;
+#if defined(__CUDACC__)
+    uint32_t* sstack;               // this thread's column of the block's shared stack: entry k at [2k*128], [(2k+1)*128]
+    uint32_t stack_b[VSB_STACK_SIZE - VSB_SHARED_STACK], stack_m[VSB_STACK_SIZE - VSB_SHARED_STACK];
+#else
     uint32_t stack_b[VSB_STACK_SIZE], stack_m[VSB_STACK_SIZE];
+#endif
 };
+
+VSB_HD void stack_push(TravState& t, uint32_t b, uint32_t m)
+{
+#if defined(__CUDACC__)
+    if (t.sp < VSB_SHARED_STACK) { t.sstack[(2 * t.sp) * 128] = b; t.sstack[(2 * t.sp + 1) * 128] = m; }
+    else { t.stack_b[t.sp - VSB_SHARED_STACK] = b; t.stack_m[t.sp - VSB_SHARED_STACK] = m; }
+#else
+    t.stack_b[t.sp] = b; t.stack_m[t.sp] = m;
+#endif
+    ++t.sp;
+}
+
+VSB_HD void stack_pop(TravState& t, uint32_t& b, uint32_t& m)
+{
+    --t.sp;
+#if defined(__CUDACC__)
+    if (t.sp < VSB_SHARED_STACK) { b = t.sstack[(2 * t.sp) * 128]; m = t.sstack[(2 * t.sp + 1) * 128]; }
+    else { b = t.stack_b[t.sp - VSB_SHARED_STACK]; m = t.stack_m[t.sp - VSB_SHARED_STACK]; }
+#else
+    b = t.stack_b[t.sp]; m = t.stack_m[t.sp];
+#endif
+}
 
 VSB_HD void trav_begin(TravState& t)
 {
@@ -168,6 +211,24 @@ VSB_HD void trav_begin(TravState& t)
     t.ng_base = 0u; t.ng_mask = 0x80000000u;
     t.pg_base = 0u; t.pg_mask = 0u;
     t.sp = 0;
+}
+
+// Prefetch the leaf-order records of the primitives a node test selected (bits of `mask`, records
+// of `rec_bytes` starting at index `base`): they are tested over the next steps, and by then the
+// lines are in L1 instead of costing one exposed HBM/L2 round trip per primitive.
+VSB_HD void prefetch_prims(const void* prims, uint32_t base, uint32_t mask, uint32_t rec_bytes)
+{
+#if defined(__CUDA_ARCH__)
+    const uint32_t first = (uint32_t)(__ffs((int)mask) - 1), last = (uint32_t)find_msb(mask);
+    const char* a = reinterpret_cast<const char*>(prims) + (size_t)(base + first) * rec_bytes;
+    const char* e = reinterpret_cast<const char*>(prims) + (size_t)(base + last + 1u) * rec_bytes;
+    a = reinterpret_cast<const char*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
+#pragma unroll
+    for (int k = 0; k < 4; ++k)
+        if (a + 128 * k < e) asm volatile("prefetch.global.L1 [%0];" :: "l"(a + 128 * k));
+#else
+    (void)prims; (void)base; (void)mask; (void)rec_bytes;
+#endif
 }
 
 // One traversal step of one ray: EITHER one primitive test (while the lane has primitives
@@ -201,7 +262,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
         n16 = 5;
         addr = reinterpret_cast<const char*>(s.nodes + (t.ng_base + rel));
-        if (t.ng_mask & 0xff000000u) { t.stack_b[t.sp] = t.ng_base; t.stack_m[t.sp] = t.ng_mask; ++t.sp; }
+        if (t.ng_mask & 0xff000000u) stack_push(t, t.ng_base, t.ng_mask);
     }
 
     NodeRegs n;
@@ -228,18 +289,22 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
     }
     else
     {
-        const uint32_t hm = test_node(n, r, limit);
-        t.ng_base = n.w[4]; t.ng_mask = (hm & 0xff000000u) | (n.w[3] >> 24);
-        t.pg_base = n.w[5]; t.pg_mask = hm & 0x00ffffffu;
-        if (t.pg_mask) return true;
+        uint32_t ph;
+        const uint32_t nh = test_node(n, r, limit, ph);
+        t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
+        t.pg_base = n.w[5]; t.pg_mask = ph;
+        if (t.pg_mask)
+        {
+            if (VSB_PREFETCH) prefetch_prims(s.prims, t.pg_base, t.pg_mask, s.prim_kind == 0 ? 48u : 32u);
+            return true;
+        }
     }
 
     // no primitives pending: the next step is a node visit; pop when this group is used up
     if ((t.ng_mask & 0xff000000u) == 0u)
     {
         if (t.sp == 0) return false;
-        --t.sp;
-        t.ng_base = t.stack_b[t.sp]; t.ng_mask = t.stack_m[t.sp];
+        stack_pop(t, t.ng_base, t.ng_mask);
     }
     return true;
 }

@@ -9,6 +9,7 @@
 #include <vector>
 
 #include <cuda_runtime.h>
+#include <cub/device/device_radix_sort.cuh>
 
 #include "../../include/vsnray_b200.h"
 #include "kernels.cuh"
@@ -60,12 +61,14 @@ int grid_for(K kernel, size_t smem, unsigned long long items, unsigned chunk)
 // frame_service_min 0 = per kernel: 32 (warp-wide lockstep; measured best for the coherent simple /
 // whitted / AO frames) or 16 (path tracing, whose bounces decorrelate the lanes)
 int g_query_service_min = 4, g_frame_service_min = 0, g_phase_min = 1;
+// sort_rays: 1 = ray lists of >= 64 Ki rays are traced in coherence-sorted order (wide path), 0 = never
+int g_sort_rays = 1;
 
 template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
 {
     auto kernel = vsb::trace_kernel<Program, EXACT>;
-    const size_t smem = (size_t)Program::STATE_WORDS * BLOCK * sizeof(uint32_t);
+    const size_t smem = (size_t)(Program::STATE_WORDS + 2 * VSB_SHARED_STACK) * BLOCK * sizeof(uint32_t);
     const int grid = grid_for(kernel, smem, tl.n_items, tl.chunk);
     kernel<<<grid, BLOCK, smem, st>>>(tl, prog);
     return cudaGetLastError();
@@ -101,7 +104,32 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
 
     VSB_CUDA(cudaMemsetAsync(g.d_work, 0, sizeof(unsigned long long), st));
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
+    // coherence sort (order only: rays are gathered and hits scattered by index, so results land in
+    // the caller's order)
+    const uint32_t* d_order = nullptr;
+    if (g_sort_rays && !exact && n_rays >= (1u << 16) && n_rays < 0x7fffffffull)
+    {
+        void *k0, *k1, *i0, *i1, *tmp;
+        const uint32_t n = (uint32_t)n_rays;
+        rc = stage(6, (size_t)n * 4, &k0); if (rc) return rc;
+        rc = stage(7, (size_t)n * 4, &k1); if (rc) return rc;
+        rc = stage(8, (size_t)n * 4, &i0); if (rc) return rc;
+        rc = stage(9, (size_t)n * 4, &i1); if (rc) return rc;
+        size_t tmp_bytes = 0;
+        VSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, 27, st));
+        rc = stage(10, tmp_bytes, &tmp); if (rc) return rc;
+        const vsb_scene* s0 = scenes[0];
+        float3 lo = make_float3(s0->lo[0], s0->lo[1], s0->lo[2]);
+        float3 inv = make_float3(1.0f / fmaxf(s0->hi[0] - s0->lo[0], 1e-30f), 1.0f / fmaxf(s0->hi[1] - s0->lo[1], 1e-30f),
+                                 1.0f / fmaxf(s0->hi[2] - s0->lo[2], 1e-30f));
+        vsb::ray_key_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rays, n, lo, inv, (uint32_t*)k0, (uint32_t*)i0);
+        VSB_CUDA(cudaGetLastError());
+        VSB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, 27, st));
+        g.launches += 2;
+        d_order = (const uint32_t*)i1;
+    }
     vsb::RayListProgram prog;
+    prog.order = d_order;
     prog.rays = d_rays; prog.max_t_per_ray = d_mt; prog.max_t = max_t; prog.hits = d_hits; prog.any = any ? 1 : 0;
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_rays;
@@ -137,6 +165,8 @@ extern "C" int vsb_tune(const char* key, int value)
     if (!std::strcmp(key, "query_service_min")) g_query_service_min = value;
     else if (!std::strcmp(key, "frame_service_min")) g_frame_service_min = value;
     else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
+    else if (!std::strcmp(key, "sort_rays")) g_sort_rays = value;
+    else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
     else return VSB_ERR_BAD_ARG;
     return VSB_OK;
 }

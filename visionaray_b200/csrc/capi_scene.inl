@@ -12,13 +12,14 @@ struct Context
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     unsigned long long* d_work = nullptr;   // persistent-kernel work counter
     vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
-    void*        staging[6] = { nullptr, nullptr, nullptr, nullptr, nullptr, nullptr };
-    size_t       staging_cap[6] = { 0, 0, 0, 0, 0, 0 };
+    void*        staging[12] = {};
+    size_t       staging_cap[12] = {};
     float        last_ms = 0.0f;
     unsigned long long launches = 0;
 };
 
 const int MAX_SCENES = 16;
+int g_optimal_collapse = 1;     // vsb_tune("optimal_collapse", 0|1), read at vsb_scene_create
 Context g;
 
 #define VSB_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return (int)e__; } while (0)
@@ -58,6 +59,7 @@ struct vsb_scene
     float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
     uint32_t n_wide = 0, n_wide_prims = 0;
     int      levels = 0, depth2 = 0;
+    float    lo[3] = { 0, 0, 0 }, hi[3] = { 0, 0, 0 };   // root bounds
     vsb::DeviceScene dev;
 };
 
@@ -155,7 +157,7 @@ extern "C" int vsb_shutdown(void)
     if (!g.inited) return VSB_OK;
     cudaSetDevice(g.device);
     cudaDeviceSynchronize();
-    for (int i = 0; i < 6; ++i) { if (g.staging[i]) cudaFree(g.staging[i]); g.staging[i] = nullptr; g.staging_cap[i] = 0; }
+    for (int i = 0; i < 12; ++i) { if (g.staging[i]) cudaFree(g.staging[i]); g.staging[i] = nullptr; g.staging_cap[i] = 0; }
     if (g.d_work) cudaFree(g.d_work);
     if (g.d_scenes) cudaFree(g.d_scenes);
     if (g.ev0) cudaEventDestroy(g.ev0);
@@ -209,6 +211,7 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
     vsb_scene* s = new vsb_scene();
     s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_nodes2 = n_nodes; s->n_idx = indices ? n_indices : 0;
     s->depth2 = depth;
+    for (int i = 0; i < 3; ++i) { s->lo[i] = nodes[0].bbox_min[i]; s->hi[i] = nodes[0].bbox_max[i]; }
     const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
     const size_t rec_bytes = prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
     const size_t list_len = indices ? n_indices : n_prims;
@@ -237,6 +240,7 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
 
     // GPU re-encode, level by level
     uint32_t* d_leaf_list = nullptr; vsb::WideTask* d_tasks[2] = { nullptr, nullptr }; uint32_t* d_counters = nullptr;
+    uint32_t* d_parent = nullptr; uint32_t* d_arrived = nullptr; vsb::CollapseCost* d_cost = nullptr; vsb::CollapseDec* d_dec = nullptr;
     const size_t wide_cap = n_enc_nodes;   // a wide node consumes >= 1 BVH2 inner node
     cudaError_t err = cudaSuccess;
     auto cleanup = [&]()
@@ -246,6 +250,10 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
         if (d_tasks[1]) cudaFree(d_tasks[1]);
         if (d_counters) cudaFree(d_counters);
         if (d_norm) cudaFree(d_norm);
+        if (d_parent) cudaFree(d_parent);
+        if (d_arrived) cudaFree(d_arrived);
+        if (d_cost) cudaFree(d_cost);
+        if (d_dec) cudaFree(d_dec);
     };
 #define VSB_ENC_CUDA(expr) do { err = (expr); if (err != cudaSuccess) { cleanup(); vsb_scene_destroy(s); return (int)err; } } while (0)
     VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, wide_cap * sizeof(vsb::Node80)));
@@ -259,13 +267,27 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
         VSB_ENC_CUDA(cudaMemcpyAsync(d_tasks[0], &root, sizeof(root), cudaMemcpyHostToDevice, g.stream));
         VSB_ENC_CUDA(cudaMemcpyAsync(d_counters, init, sizeof(init), cudaMemcpyHostToDevice, g.stream));
     }
+    // optimal collapse: bottom-up DP over the BVH2 (g_optimal_collapse = 0: greedy largest-area-first)
+    if (g_optimal_collapse)
+    {
+        const uint32_t nn = (uint32_t)n_enc_nodes;
+        VSB_ENC_CUDA(cudaMalloc((void**)&d_parent, (size_t)nn * 4));
+        VSB_ENC_CUDA(cudaMalloc((void**)&d_arrived, (size_t)nn * 4));
+        VSB_ENC_CUDA(cudaMalloc((void**)&d_cost, (size_t)nn * sizeof(vsb::CollapseCost)));
+        VSB_ENC_CUDA(cudaMalloc((void**)&d_dec, (size_t)nn * sizeof(vsb::CollapseDec)));
+        VSB_ENC_CUDA(cudaMemsetAsync(d_arrived, 0, (size_t)nn * 4, g.stream));
+        vsb::bvh2_parents_kernel<<<(nn + 255) / 256, 256, 0, g.stream>>>(d_enc_nodes, nn, d_parent);
+        vsb::collapse_dp_kernel<<<(nn + 255) / 256, 256, 0, g.stream>>>(d_enc_nodes, nn, d_parent, d_arrived, d_cost, d_dec);
+        g.launches += 2;
+        VSB_ENC_CUDA(cudaGetLastError());
+    }
     uint32_t n_tasks = 1; int cur = 0; s->levels = 0;
     uint32_t counters[4] = { 1u, 0u, 0u, 0u };
     while (n_tasks > 0)
     {
         VSB_ENC_CUDA(cudaMemsetAsync(d_counters + 2, 0, sizeof(uint32_t), g.stream));
         vsb::encode_level_kernel<<<(n_tasks + 127) / 128, 128, 0, g.stream>>>(
-            d_tasks[cur], n_tasks, d_enc_nodes, s->d_wide, d_leaf_list, d_tasks[cur ^ 1], d_counters);
+            d_tasks[cur], n_tasks, d_enc_nodes, s->d_wide, d_leaf_list, d_tasks[cur ^ 1], d_counters, d_dec);
         ++g.launches;
         VSB_ENC_CUDA(cudaGetLastError());
         VSB_ENC_CUDA(cudaMemcpyAsync(counters, d_counters, sizeof(counters), cudaMemcpyDeviceToHost, g.stream));

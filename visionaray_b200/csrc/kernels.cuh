@@ -37,15 +37,55 @@ struct DeviceAlloc
     __device__ uint32_t operator()(uint32_t n) { return atomicAdd(counter, n); }
 };
 
+// parent[] of the BVH2 (the reference layout has child links only)
+__global__ void bvh2_parents_kernel(const Node32* __restrict__ nodes2, uint32_t n_nodes, uint32_t* __restrict__ parent)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    if (i == 0) parent[0] = 0xffffffffu;
+    const Node32 n = nodes2[i];
+    if (n.num_prims == 0) { parent[n.first] = i; parent[n.first + 1] = i; }
+}
+
+// Bottom-up collapse DP (bvh8.cuh): one thread per BVH2 leaf climbs towards the root; at every
+// inner node the first arriving thread stops, the second (both children done) evaluates the node.
+__global__ void collapse_dp_kernel(const Node32* __restrict__ nodes2, uint32_t n_nodes, const uint32_t* __restrict__ parent,
+                                   uint32_t* __restrict__ arrived, CollapseCost* cost, CollapseDec* dec)
+{
+    uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_nodes) return;
+    Node32 n = nodes2[i];
+    if (n.num_prims == 0) return;
+    CollapseCost c; CollapseDec d;
+    dp_leaf(n, c, d);
+    cost[i] = c; dec[i] = d;
+    for (;;)
+    {
+        const uint32_t p = parent[i];
+        if (p == 0xffffffffu) return;
+        __threadfence();
+        if (atomicAdd(arrived + p, 1u) == 0u) return;
+        __threadfence();
+        n = nodes2[p];
+        const volatile CollapseCost* vc = cost;
+        CollapseCost l, r;
+        for (int k = 0; k < 8; ++k) { l.c[k] = vc[n.first].c[k]; r.c[k] = vc[n.first + 1].c[k]; }
+        dp_inner(n, l, r, c, d);
+        cost[p] = c; dec[p] = d;
+        i = p;
+    }
+}
+
 // counters[0] = next free wide node, [1] = next free primitive slot, [2] = tasks emitted
 __global__ void encode_level_kernel(const WideTask* __restrict__ tasks, uint32_t n_tasks,
                                     const Node32* __restrict__ nodes2, Node80* out_nodes,
-                                    uint32_t* leaf_list, WideTask* next_tasks, uint32_t* counters)
+                                    uint32_t* leaf_list, WideTask* next_tasks, uint32_t* counters,
+                                    const CollapseDec* __restrict__ dec)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_tasks) return;
     DeviceAlloc an{ counters + 0 }, ap{ counters + 1 }, at{ counters + 2 };
-    collapse_node(tasks[i], nodes2, out_nodes, leaf_list, next_tasks, an, ap, at);
+    collapse_node(tasks[i], nodes2, out_nodes, leaf_list, next_tasks, an, ap, at, dec);
 }
 
 __global__ void fill_prims_kernel(int prim_kind, const void* __restrict__ prims, const uint32_t* __restrict__ indices,
@@ -111,7 +151,8 @@ trace_kernel(const TraceLaunch tl, const Program prog)
     extern __shared__ uint32_t lane_store_raw[];
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
-    typename Program::Lane L(lane_store_raw, threadIdx.x);
+    // shared memory: [32 stack words per thread][Program::STATE_WORDS per thread], column per thread
+    typename Program::Lane L(lane_store_raw + 2 * VSB_SHARED_STACK * VSB_BLOCK, threadIdx.x);
 
     unsigned long long chunk_next = 0, chunk_end = 0;     // warp-uniform
     bool exhausted = false;                               // warp-uniform
@@ -125,6 +166,7 @@ trace_kernel(const TraceLaunch tl, const Program prog)
     int scene_i = 0;
     WideScene sc = tl.scenes[0].wide;
     TravState t; trav_begin(t);
+    t.sstack = lane_store_raw + threadIdx.x;
     RayReq req;
 
     for (;;)
@@ -219,8 +261,37 @@ trace_kernel(const TraceLaunch tl, const Program prog)
 }
 
 // ---- ray list program: closest_hit()/any_hit() over a ray list ----------------------------------
+// Sort key of a ray for the coherence pre-pass of ray lists: direction octant (3 bits, major) and
+// a 24-bit Morton code of the origin inside the scene bounds (8 bits per axis).  Rays that are
+// neighbours after the sort start close together and head the same way, so the lanes of a warp
+// walk the same part of the tree (L1/L2 hits instead of HBM sector misses).
+__device__ __forceinline__ uint32_t morton_spread8(uint32_t v)
+{
+    v = (v | (v << 16)) & 0x030000FFu;
+    v = (v | (v << 8)) & 0x0300F00Fu;
+    v = (v | (v << 4)) & 0x030C30C3u;
+    v = (v | (v << 2)) & 0x09249249u;
+    return v;
+}
+
+__global__ void ray_key_kernel(const float4* __restrict__ rays, uint32_t n, float3 lo, float3 inv_extent,
+                               uint32_t* __restrict__ keys, uint32_t* __restrict__ index)
+{
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const float4 o = __ldg(rays + 2 * (size_t)i), d = __ldg(rays + 2 * (size_t)i + 1);
+    const float fx = fminf(fmaxf((o.x - lo.x) * inv_extent.x, 0.0f), 0.999f);
+    const float fy = fminf(fmaxf((o.y - lo.y) * inv_extent.y, 0.0f), 0.999f);
+    const float fz = fminf(fmaxf((o.z - lo.z) * inv_extent.z, 0.0f), 0.999f);
+    const uint32_t qx = (uint32_t)(fx * 256.0f), qy = (uint32_t)(fy * 256.0f), qz = (uint32_t)(fz * 256.0f);
+    const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
+    keys[i] = (oct << 24) | morton_spread8(qx) | (morton_spread8(qy) << 1) | (morton_spread8(qz) << 2);
+    index[i] = i;
+}
+
 struct RayListProgram
 {
+    const uint32_t* order;         // optional: item -> ray index (coherence sort); NULL = identity
     const float4* rays;
     const float*  max_t_per_ray;
     float         max_t;
@@ -236,6 +307,7 @@ struct RayListProgram
 
     __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
     {
+        if (order) item = __ldg(order + item);
         L.item = item;
         const float4 o = __ldg(rays + 2 * item), d = __ldg(rays + 2 * item + 1);
         req.ox = o.x; req.oy = o.y; req.oz = o.z; req.dx = d.x; req.dy = d.y; req.dz = d.z;

@@ -69,9 +69,9 @@ struct SphRec
 //  q0: origin p (3 x f32) | e_x e_y e_z imask (4 x u8; child box = p + q * 2^(e-127... see below))
 //  q1: child_base (u32) | prim_base (u32) | meta[0..7] (8 x u8)
 //  q2: qlo_x[8] | qlo_y[8]      q3: qlo_z[8] | qhi_x[8]      q4: qhi_y[8] | qhi_z[8]
-// meta[i]: 0 = empty slot; otherwise (count << 5) | bit_offset, where an inner child has
-// count = 1 and bit_offset = 24 + i, and a leaf child has count = 1..4 primitives starting at
-// bit_offset = offset of its first primitive relative to prim_base (0..23).  The exponents are
+// meta[i]: leaf child: (count << 5) | offset, count = 1..4 primitives starting at prim_base + offset
+// (offset 0..28: 8 leaves x 4 primitives = 32 bits of primitive hit mask); inner child (bit i of
+// imask set) or empty slot: 0.  The exponents are
 // biased float exponents: scale = bits_to_float(e << 23).
 struct Node80
 {
@@ -79,7 +79,7 @@ struct Node80
 };
 
 #define VSB_WIDE 8
-#define VSB_MAX_LEAF_BITS 24
+#define VSB_MAX_LEAF_BITS 32
 
 // ---- exact single-rounding arithmetic ---------------------------------------------------------
 #if defined(__CUDA_ARCH__)
