@@ -113,6 +113,15 @@ def measured_peak_gbs():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def measured_traffic(workload: str):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/), or None."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            return int(json.load(f)[workload]["bytes"])
+    except Exception:
+        return None
+
+
 def frame_shape(wl: dict, n_gpus: int):
     """Weak scaling: the same view at sqrt(N) x the resolution per axis (rounded to whole 64-pixel
     tiles), i.e. base-frame pixels per GPU and the same mix of sky / geometry / secondary rays."""
@@ -377,7 +386,8 @@ def run_gpu(args):
         b_ray, visit = algorithmic_bytes_per_ray(O, S, sc, wl, mats, lights)
         achieved = b_ray * rays_per_step_rank / (kernel_ms * 1e-3) / 1e9
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                    "traffic": None, "kernel": "frame_kernel", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
+                    "traffic": measured_traffic(args.workload) if world == 1 and args.scale == 1.0 else None,
+                    "kernel": "trace_kernel<FrameProgram>", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
                     "n_inner_per_ray": visit["n_inner"], "n_prim_per_ray": visit["n_prim"], "peak_source": peak_src,
                     "roofline_mrays_s": peak * 1e9 / b_ray / 1e6}
         cpu = None
@@ -536,7 +546,8 @@ def run_gpu_raylist(args):
                        "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "bvh2_depth": stats["bvh2_depth"],
                        "host_build_s": build_s, "hit_fraction": hit_frac},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": "query_kernel", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
+                         "traffic": measured_traffic("cfg5") if world == 1 and args.scale == 1.0 and not args.any else None,
+                         "kernel": "trace_kernel<RayListProgram>", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
                          "n_inner_per_ray": n_inner, "n_prim_per_ray": n_prim, "peak_source": peak_src,
                          "roofline_mrays_s": peak * 1e9 / b_ray / 1e6},
             "cpu_baseline": cpu,
