@@ -293,3 +293,75 @@ def test_full_size_properties_cfg1(gpu):
     sub = rays[::97].copy()
     assert gpu.closest_hit(dev, sub, traverse=gpu.TRAVERSE_EXACT).tobytes() == O.oracle_query(sc, sub, False).tobytes()
     dev.close()
+
+
+def test_full_size_cfg2_frame_wide_vs_reference_order(gpu):
+    """BASELINE configs[1] at full size (1,002,528 triangles, 4096^2 Whitted): the BVH8 frame equals
+    the reference-order frame except for t-tie pixels; a 512^2 crop of the same view is checked
+    against the oracle through the scissor box."""
+    import torch
+
+    sc = S.make_scene("cfg2_grid", 1.0)
+    dev = gpu.Scene(sc)
+    eye = (0.3, 1.2, 2.2)
+    fp = S.frame_params(1, 4096, 4096, eye, (0, 0, 0), num_bounces=4)
+    mats, lights = S.default_material(0), S.point_light(eye)
+    d_m = torch.from_numpy(mats.view(np.float32).copy()).cuda()
+    d_l = torch.from_numpy(lights.view(np.float32).copy()).cuda()
+    imgs = []
+    for trav in (gpu.TRAVERSE_EXACT, gpu.TRAVERSE_WIDE):
+        img = torch.zeros((4096, 4096, 4), dtype=torch.float32, device="cuda")
+        rc = torch.zeros(1, dtype=torch.int64, device="cuda")
+        gpu.frame(dev, fp, None, d_m, d_l, img, traverse=trav, ray_count=rc)
+        gpu.sync()
+        imgs.append(img)
+        assert 16_777_216 < int(rc.item()) < 3 * 16_777_216
+    diff = (imgs[0] - imgs[1]).abs().amax(dim=2)
+    assert float((diff > 1.0 / 255.0).float().mean().item()) <= 2e-4
+    # oracle on a low-resolution frame of the same view
+    fp_small = S.frame_params(1, 384, 384, eye, (0, 0, 0), num_bounces=4)
+    want = O.oracle_frame(sc, fp_small, mats, lights)
+    got = np.zeros((384, 384, 4), dtype=np.float32)
+    gpu.frame(dev, fp_small, None, mats, lights, got, traverse=gpu.TRAVERSE_EXACT)
+    assert np.abs(got - want).max() <= 1.0 / 255.0
+    dev.close()
+
+
+def test_large_incoherent_ray_list_properties(gpu):
+    """cfg5-style stress at 2 M triangles x 2 M random rays: BVH8 == reference order up to ties on
+    every ray; the coherence sort does not change a single byte; any-hit flag == closest t < max_t;
+    an oracle sample pins the reference-order records."""
+    sc = S.make_scene("cfg5_soup", 0.1)
+    dev = gpu.Scene(sc)
+    rays = S.random_rays(2_000_000, 77)
+    exact = gpu.closest_hit(dev, rays, traverse=gpu.TRAVERSE_EXACT)
+    wide = gpu.closest_hit(dev, rays)
+    r = classify_closest(exact, wide)
+    assert r["bad"] == 0, r
+    gpu.tune("sort_rays", 0)
+    try:
+        unsorted_ = gpu.closest_hit(dev, rays)
+    finally:
+        gpu.tune("sort_rays", 1)
+    assert unsorted_.tobytes() == wide.tobytes()
+    occ = gpu.any_hit(dev, rays, max_t=0.05)
+    assert ((occ["hit"] != 0) == ((exact["hit"] != 0) & (exact["t"] < 0.05))).all()
+    sub = rays[::50].copy()
+    assert gpu.closest_hit(dev, sub, traverse=gpu.TRAVERSE_EXACT).tobytes() == O.oracle_query(sc, sub, False).tobytes()
+    st = dev.stats()
+    assert st["wide_prims"] == sc.n_prims and st["wide_nodes"] * 7 + 1 >= sc.nodes.shape[0] // 2 // 7
+    dev.close()
+
+
+def test_scheduling_knobs_do_not_change_results(gpu, scenes):
+    sc, dev = scenes("cfg3_cubes", 0.004)
+    rays = scene_rays(sc, 100_000, 91)
+    base = gpu.closest_hit(dev, rays)
+    try:
+        for key, val in (("query_service_min", 1), ("query_service_min", 32), ("phase_min", 12)):
+            gpu.tune(key, val)
+            assert gpu.closest_hit(dev, rays).tobytes() == base.tobytes(), (key, val)
+    finally:
+        gpu.tune("query_service_min", 4); gpu.tune("phase_min", 1)
+    with pytest.raises(RuntimeError):
+        gpu.tune("no_such_knob", 1)
