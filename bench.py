@@ -259,31 +259,51 @@ def run_gpu(args):
     d_rays = torch.zeros(1, dtype=torch.int64, device="cuda")
     trav = api.TRAVERSE_EXACT if args.traverse == "exact" else api.TRAVERSE_WIDE
 
-    tiles = api.tiles_of_rank(w, h, rank, world)
     per = max(api.tiles_of_rank(w, h, r, world) for r in range(world))
     # a real (non-legacy) stream: the C ABI treats a NULL stream as "the library's own stream"
     main = torch.cuda.Stream()
     torch.cuda.set_stream(main)
-    if world > 1:
+    # N > 1, how the frame is assembled:
+    #   peer  (default) every rank stores its tiles straight into rank 0's frame over NVLink peer
+    #         memory (CUDA IPC) from inside the traversal kernel; a tiny all-reduce per step marks
+    #         completion.  No gather pass, no de-interleave.
+    #   nccl  compact tile buffers + all-gather + de-interleave on a side stream (also used for the
+    #         progressive path tracer, whose blend reads the previous frame locally)
+    mode = "single" if world == 1 else ("nccl" if (args.gather == "nccl" or wl["kernel"] == 3) else "peer")
+    image = None
+    if mode == "single":
+        image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    elif mode == "peer":
+        handle = [None]
+        if rank == 0:
+            frame_buf = api.DeviceBuffer(w * h * 16)
+            handle[0] = frame_buf.export()
+        dist.broadcast_object_list(handle, src=0)
+        if rank != 0:
+            frame_buf = api.DeviceBuffer.open(handle[0], w * h * 16)
+        done_flag = torch.zeros(1, dtype=torch.float32, device="cuda")
+    else:
         tile_buf = [torch.zeros((per, api.TILE * api.TILE, 4), dtype=torch.float32, device="cuda") for _ in range(2)]
         gathered = torch.zeros((world, per, api.TILE * api.TILE, 4), dtype=torch.float32, device="cuda")
         image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
         comm = torch.cuda.Stream()
         rendered = [torch.cuda.Event() for _ in range(2)]
         gathered_done = [torch.cuda.Event() for _ in range(2)]
-    else:
-        image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
 
     step_no = [0]
 
     def step():
-        """One frame: every rank renders its interleaved tiles; with N > 1 the tile buffers are
-        all-gathered over NVLink and de-interleaved on a side stream, overlapping the next frame."""
+        """One frame: every rank renders its interleaved tiles (see `mode`)."""
         k = step_no[0]
         step_no[0] += 1
         fp = make_frame_params(S, wl, w, h, frame_num=k + 1 if wl["kernel"] == 3 else 1)
-        if world == 1:
+        if mode == "single":
             api.frame(dev, fp, None, d_mats, d_lights, image, traverse=trav, ray_count=d_rays, stream=main.cuda_stream)
+            return
+        if mode == "peer":
+            api.frame(dev, fp, None, d_mats, d_lights, frame_buf, traverse=trav, tile_rank=rank, tile_nranks=world,
+                      ray_count=d_rays, stream=main.cuda_stream, tiles_in_place=True)
+            dist.all_reduce(done_flag)                 # frame k is complete on rank 0 once this returns on its stream
             return
         b = k & 1
         main.wait_event(gathered_done[b])          # buffer b was last read by the gather of frame k-2
@@ -315,7 +335,7 @@ def run_gpu(args):
     e0.record(main)
     for _ in range(args.steps):
         step()
-    if world > 1:
+    if mode == "nccl":
         main.wait_stream(comm)                      # the last gather belongs to the timed region
     e1.record(main)
     fence()
@@ -379,6 +399,25 @@ def run_gpu(args):
         h2d += n_px * 16 * world                                   # progressive state lives with the caller
     d2h = (n_px * 16 + 8) * world
 
+    # N > 1: the assembled frame on rank 0 equals the frame one GPU renders alone
+    verified = None
+    if world > 1 and wl["kernel"] != 3:
+        fence()
+        if rank == 0:
+            fp = make_frame_params(S, wl, w, h)
+            alone = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+            api.frame(dev, fp, None, d_mats, d_lights, alone, traverse=trav, stream=main.cuda_stream)
+            torch.cuda.synchronize()
+            if mode == "peer":
+                got = torch.empty_like(alone)
+                N_ = api.N.cuda_lib()
+                api._check(N_.vsb_device_copy(got.data_ptr(), frame_buf.data_ptr(), w * h * 16, 0, 0), "vsb_device_copy")
+                torch.cuda.synchronize()
+            else:
+                got = image
+            verified = bool(torch.equal(got, alone))
+        fence()
+
     line = None
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
@@ -404,7 +443,9 @@ def run_gpu(args):
             "config": {"workload": wl["desc"], "frame": [w, h], "rays_per_step": rays_total // args.steps,
                        "traverse": args.traverse, "scale": args.scale,
                        "partition": f"interleaved 64x64 tiles over {world} GPU(s), scene replicated"
-                                    + (", NCCL all-gather + de-interleave per frame on a side stream" if world > 1 else ""),
+                                    + {"single": "", "peer": ", tiles stored in place into rank 0's frame over NVLink peer memory (CUDA IPC) + 1 tiny all-reduce per frame",
+                                       "nccl": ", NCCL all-gather + de-interleave per frame on a side stream"}[mode],
+                       "assembled_frame_verified": verified,
                        "l2": f"framebuffer {w * h * 16 >> 20} MiB rewritten every step + scene {(stats['wide_node_bytes'] + stats['wide_prim_bytes']) >> 20} MiB (> 126 MB L2 together)",
                        "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "triangles": sc.n_prims},
             "roofline": roofline, "cpu_baseline": cpu,
@@ -575,6 +616,7 @@ def main():
     ap.add_argument("--traverse", default="wide", choices=["wide", "exact"])
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how the frame is assembled")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":

@@ -95,6 +95,7 @@ enum { VSB_TRAVERSE_WIDE = 0, VSB_TRAVERSE_EXACT = 1 };
 
 /* where the caller's buffers live */
 enum { VSB_MEM_DEVICE = 0, VSB_MEM_HOST = 1 };
+enum { VSB_TILES_COMPACT = 0, VSB_TILES_IN_PLACE = 1 };
 
 enum {
     VSB_OK = 0,
@@ -147,7 +148,10 @@ typedef struct vsb_frame_desc {
     uint64_t* ray_count;                 /* optional counter (same memory as color): += rays traced (device),
                                             = rays traced this frame (host) */
     int32_t  params_mem;                 /* VSB_MEM_*: where materials / lights (and normals, if given) live */
-    int32_t  reserved;
+    int32_t  tile_target;                /* with tile_nranks > 1: VSB_TILES_COMPACT (default) or VSB_TILES_IN_PLACE =
+                                            `color` is the whole row-major frame (width*height pixels), e.g. a peer
+                                            GPU's buffer opened with vsb_ipc_open(): the rank's tiles are stored
+                                            straight into it over NVLink, no gather pass (device memory, no blend) */
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;
@@ -211,6 +215,12 @@ int  vsb_deinterleave_tiles(const void* gathered, int width, int height, int nra
 int  vsb_device_alloc(size_t bytes, void** out);
 int  vsb_device_free(void* p);
 int  vsb_device_copy(void* dst, const void* src, size_t bytes, int dst_mem, int src_mem);
+
+/* ---- sharing a device buffer between the per-GPU processes of one node (CUDA IPC over
+ * NVLink/NVSwitch peer memory): export on the owner, open on the peers; handle = 64 bytes ---- */
+int  vsb_ipc_export(const void* dev_ptr, void* handle64);
+int  vsb_ipc_open(const void* handle64, void** out);
+int  vsb_ipc_close(void* p);
 
 /* ---- timing helper for the harness: average device time (ms) of the last query/frame
  * kernels, measured with CUDA events on the stream they were launched on ---- */

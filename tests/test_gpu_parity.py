@@ -271,6 +271,16 @@ def test_tile_partition_reassembles_the_frame(gpu, scenes):
     host = np.zeros((h, w, 4), dtype=np.float32)
     gpu.frame(dev, fp, sc.normals, mats, lights, host)
     assert np.array_equal(host, full.cpu().numpy())
+    # in-place tile target (what peers do over NVLink into rank 0's frame): each "rank" stores its
+    # tiles straight into the row-major image, here a raw library allocation
+    buf = gpu.DeviceBuffer(w * h * 16)
+    for r in range(nr):
+        gpu.frame(dev, fp, d_norm, d_m, d_l, buf, tile_rank=r, tile_nranks=nr, tiles_in_place=True)
+    gpu.sync()
+    got = buf.download(np.zeros((h, w, 4), dtype=np.float32))
+    assert np.array_equal(got, host)
+    assert len(buf.export()) == 64
+    buf.close()
 
 
 def test_full_size_properties_cfg1(gpu):

@@ -61,7 +61,7 @@ class FrameDesc(C.Structure):
         ("color", C.c_void_p), ("depth", C.c_void_p),
         ("mem", C.c_int32), ("traverse", C.c_int32), ("tile_rank", C.c_int32), ("tile_nranks", C.c_int32),
         ("ray_count", C.c_void_p),
-        ("params_mem", C.c_int32), ("reserved", C.c_int32),
+        ("params_mem", C.c_int32), ("tile_target", C.c_int32),
     ]
 
 
@@ -70,7 +70,7 @@ ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
     "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
-    "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_last_kernel_ms", "vsb_launch_count",
+    "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_ipc_export", "vsb_ipc_open", "vsb_ipc_close", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
 
 _cuda_lib = None
@@ -119,6 +119,12 @@ def cuda_lib() -> C.CDLL:
         lib.vsb_frame.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(FrameDesc), vp]
         lib.vsb_tiles_of_rank.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
         lib.vsb_deinterleave_tiles.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, vp, vp]
+        lib.vsb_device_alloc.argtypes = [sz, C.POINTER(vp)]
+        lib.vsb_device_free.argtypes = [vp]
+        lib.vsb_device_copy.argtypes = [vp, vp, sz, C.c_int, C.c_int]
+        lib.vsb_ipc_export.argtypes = [vp, vp]
+        lib.vsb_ipc_open.argtypes = [vp, C.POINTER(vp)]
+        lib.vsb_ipc_close.argtypes = [vp]
         lib.vsb_last_kernel_ms.argtypes = [C.POINTER(C.c_float)]
         lib.vsb_launch_count.argtypes = [C.POINTER(C.c_uint64)]
         _cuda_lib = lib

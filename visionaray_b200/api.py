@@ -157,8 +157,45 @@ def tiles_of_rank(width, height, rank, nranks) -> int:
     return n.value
 
 
+class DeviceBuffer:
+    """A raw device allocation of the library (cudaMalloc), shareable between the per-GPU processes
+    of a node through CUDA IPC: `export()` on the owner, `DeviceBuffer.open(handle)` on the peers."""
+
+    def __init__(self, nbytes: int = 0, ptr: int = 0, peer: bool = False):
+        self.nbytes, self.peer = nbytes, peer
+        if ptr:
+            self.ptr = ptr
+        else:
+            p = C.c_void_p(0)
+            _check(N.cuda_lib().vsb_device_alloc(nbytes, C.byref(p)), "vsb_device_alloc")
+            self.ptr = p.value
+
+    def data_ptr(self) -> int:
+        return self.ptr
+
+    def export(self) -> bytes:
+        h = C.create_string_buffer(64)
+        _check(N.cuda_lib().vsb_ipc_export(C.c_void_p(self.ptr), h), "vsb_ipc_export")
+        return h.raw
+
+    @staticmethod
+    def open(handle: bytes, nbytes: int = 0) -> "DeviceBuffer":
+        p = C.c_void_p(0)
+        _check(N.cuda_lib().vsb_ipc_open(C.create_string_buffer(handle, 64), C.byref(p)), "vsb_ipc_open")
+        return DeviceBuffer(nbytes, p.value, peer=True)
+
+    def download(self, out: np.ndarray):
+        _check(N.cuda_lib().vsb_device_copy(N.ptr(out), C.c_void_p(self.ptr), out.nbytes, MEM_HOST, MEM_DEVICE), "vsb_device_copy")
+        return out
+
+    def close(self):
+        if self.ptr:
+            (N.cuda_lib().vsb_ipc_close if self.peer else N.cuda_lib().vsb_device_free)(C.c_void_p(self.ptr))
+            self.ptr = 0
+
+
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
-          tile_nranks=0, ray_count=None, stream=None):
+          tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False):
     """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
     the call, returns with pixels in place); torch CUDA tensor -> device render target
     (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
@@ -186,6 +223,7 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.params_mem = MEM_HOST if (not kinds or kinds.pop()) else MEM_DEVICE
     d.traverse = traverse
     d.tile_rank, d.tile_nranks = tile_rank, tile_nranks
+    d.tile_target = 1 if tiles_in_place else 0
     d.ray_count = p(ray_count)
     _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), stream), "vsb_frame")
     return color

@@ -252,7 +252,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
-    struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles;
+    struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles, in_place;
              unsigned long long* ray_count; } fl;
     std::memset(&fl, 0, sizeof(fl));
     std::memcpy(&fl.ctx.p, &p, sizeof(p));
@@ -267,7 +267,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     if (fl.scissor[2] <= 0 || fl.scissor[3] <= 0) { fl.scissor[0] = 0; fl.scissor[1] = 0; fl.scissor[2] = p.width; fl.scissor[3] = p.height; }
 
     const size_t n_normals = scenes[0]->n_prims;
-    const size_t color_px = nranks > 1 ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
+    fl.in_place = (nranks > 1 && d->tile_target == VSB_TILES_IN_PLACE) ? 1 : 0;
+    if (fl.in_place && (d->mem != VSB_MEM_DEVICE || p.pixel_sampler == VSB_PS_JITTERED_BLEND)) return VSB_ERR_UNSUPPORTED;
+    const size_t color_px = (nranks > 1 && !fl.in_place) ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
     unsigned long long* d_ray_count = nullptr;
     if (d->mem != VSB_MEM_HOST && d->mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     if (d->params_mem != VSB_MEM_HOST && d->params_mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
@@ -326,6 +328,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         vsb::FrameProgram<K> prog;                                                                           \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
+        prog.in_place = fl.in_place;                                                                         \
         if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true>(prog, tl, st)));  \
         else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false>(prog, tl, st))); \
     } while (0)
@@ -385,6 +388,33 @@ extern "C" int vsb_device_copy(void* dst, const void* src, size_t bytes, int dst
                                                           : (src_mem == VSB_MEM_DEVICE ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost);
     VSB_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, g.stream));
     VSB_CUDA(cudaStreamSynchronize(g.stream));
+    return VSB_OK;
+}
+
+extern "C" int vsb_ipc_export(const void* dev_ptr, void* handle64)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!dev_ptr || !handle64) return VSB_ERR_BAD_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "ipc handle size");
+    cudaIpcMemHandle_t h;
+    VSB_CUDA(cudaIpcGetMemHandle(&h, const_cast<void*>(dev_ptr)));
+    std::memcpy(handle64, &h, 64);
+    return VSB_OK;
+}
+
+extern "C" int vsb_ipc_open(const void* handle64, void** out)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!handle64 || !out) return VSB_ERR_BAD_ARG;
+    cudaIpcMemHandle_t h;
+    std::memcpy(&h, handle64, 64);
+    VSB_CUDA(cudaIpcOpenMemHandle(out, h, cudaIpcMemLazyEnablePeerAccess));
+    return VSB_OK;
+}
+
+extern "C" int vsb_ipc_close(void* p)
+{
+    if (p) VSB_CUDA(cudaIpcCloseMemHandle(p));
     return VSB_OK;
 }
 

@@ -218,6 +218,7 @@ struct FrameProgram
     float4* color;
     int tile_rank, tile_nranks;      // tile_nranks == 0: single rank, row-major target
     int tiles_x;
+    int in_place;                    // tile_nranks > 1: store into the whole row-major frame (e.g. peer memory)
 
     using Lane = FrameLane;
     static constexpr int STATE_WORDS = KERNEL == 1 ? 20 : (KERNEL == 0 ? 3 : 9);
@@ -277,7 +278,7 @@ struct FrameProgram
                             x < scissor[0] + scissor[2] && y < scissor[1] + scissor[3];
         if (!inside) return false;
         const uint32_t pixel = (uint32_t)y * (uint32_t)f.p.width + (uint32_t)x;
-        L.u(W_DST) = tile_nranks > 1 ? (uint32_t)(local_tile * (VSB_TILE * VSB_TILE) + ly * VSB_TILE + lx) : pixel;
+        L.u(W_DST) = (tile_nranks > 1 && !in_place) ? (uint32_t)(local_tile * (VSB_TILE * VSB_TILE) + ly * VSB_TILE + lx) : pixel;
         uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
         float fx = (float)x, fy = (float)y;
         if (f.p.pixel_sampler != 0)
