@@ -166,6 +166,9 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
 #ifndef VSB_SHARED_STACK
 #define VSB_SHARED_STACK 16     // entries per thread kept in shared memory (device); deeper ones spill to local
 #endif
+#ifndef VSB_STEP_MODE
+#define VSB_STEP_MODE 0     // measured: chaining costs a second exposed latency per step (cfg5 +29 % time)
+#endif
 #ifndef VSB_PREFETCH
 #define VSB_PREFETCH 0     // measured: no gain (the unified loads already overlap); kept as a switch
 #endif
@@ -242,6 +245,55 @@ VSB_HD bool trav_prim_mode(const TravState& t) { return t.pg_mask != 0u; }
 
 VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg& best, float& limit, bool any)
 {
+    NodeRegs n;
+#if VSB_STEP_MODE == 1
+    // Mode 1 ("chained"): the primitive part runs first for the lanes with pending primitives; a lane
+    // that tests its LAST pending primitive falls through into the node part of the same step, so it
+    // does not spend a whole extra warp iteration before its next node visit.
+    if (t.pg_mask)
+    {
+        const int n16 = s.prim_kind == 0 ? 3 : 2;
+#if defined(__CUDA_ARCH__)
+        const int n_enter = __popc(__activemask());
+#endif
+        do
+        {
+            const int bit = find_msb(t.pg_mask);
+            t.pg_mask &= ~(1u << bit);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(t.pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
+            test_prim(s.prim_kind, n, r, best, limit);
+            if (any && best.hit) return false;
+        }
+#if defined(__CUDA_ARCH__)
+        while (t.pg_mask && __popc(__activemask()) * 8 >= n_enter * 7);     // coherent leaves: tight loop
+#else
+        while (false);
+#endif
+        if (t.pg_mask) return true;
+        if ((t.ng_mask & 0xff000000u) == 0u)
+        {
+            if (t.sp == 0) return false;
+            stack_pop(t, t.ng_base, t.ng_mask);
+        }
+    }
+    {
+        const int bit = find_msb(t.ng_mask);
+        t.ng_mask &= ~(1u << bit);
+        const uint32_t imask = t.ng_mask & 0xffu;
+        const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xffu)) & 7u;
+        const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
+        const char* addr = reinterpret_cast<const char*>(s.nodes + (t.ng_base + rel));
+        if (t.ng_mask & 0xff000000u) stack_push(t, t.ng_base, t.ng_mask);
+        load_record(addr, 5, n);
+        uint32_t ph;
+        const uint32_t nh = test_node(n, r, limit, ph);
+        t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
+        t.pg_base = n.w[5]; t.pg_mask = ph;
+        if (t.pg_mask) return true;
+    }
+#else
+    // Mode 0 ("unified loads"): a lane is in primitive phase or node phase for the whole step; all
+    // lanes issue their record loads together, then each test runs once.
     const bool prim_mode = t.pg_mask != 0u;
     const char* addr;
     int n16;
@@ -265,7 +317,6 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         if (t.ng_mask & 0xff000000u) stack_push(t, t.ng_base, t.ng_mask);
     }
 
-    NodeRegs n;
     load_record(addr, n16, n);
 
     if (prim_mode)
@@ -299,6 +350,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
             return true;
         }
     }
+#endif
 
     // no primitives pending: the next step is a node visit; pop when this group is used up
     if ((t.ng_mask & 0xff000000u) == 0u)
