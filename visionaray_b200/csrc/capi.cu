@@ -63,6 +63,9 @@ int grid_for(K kernel, size_t smem, unsigned long long items, unsigned chunk)
 int g_query_service_min = 4, g_frame_service_min = 0, g_phase_min = 1;
 // sort_rays: 1 = ray lists of >= 64 Ki rays are traced in coherence-sorted order (wide path), 0 = never
 int g_sort_rays = 1;
+// frame_bands: a host render target is traced in this many bands so that the D2H copy of one band
+// overlaps the tracing of the next (1 = off)
+int g_frame_bands = 2;     // measured on cfg2: 1: 11.7 ms, 2: 9.6 ms, 4: 9.7 ms per 4096^2 frame into pinned host memory
 
 template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
@@ -166,6 +169,7 @@ extern "C" int vsb_tune(const char* key, int value)
     else if (!std::strcmp(key, "frame_service_min")) g_frame_service_min = value;
     else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
     else if (!std::strcmp(key, "sort_rays")) g_sort_rays = value;
+    else if (!std::strcmp(key, "frame_bands")) g_frame_bands = value;
     else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
     else return VSB_ERR_BAD_ARG;
     return VSB_OK;
@@ -314,41 +318,77 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     }
     fl.ray_count = d_ray_count;
 
-    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 2 * sizeof(unsigned long long), st));
+    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 16 * sizeof(unsigned long long), st));
     const bool exact = d->traverse == VSB_TRAVERSE_EXACT;
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
-    tl.n_items = (unsigned long long)fl.n_owned_tiles * VSB_TILE * VSB_TILE;
-    tl.chunk = VSB_FRAME_CHUNK; tl.work_counter = g.d_work; tl.ray_count = fl.ray_count;
+    tl.chunk = VSB_FRAME_CHUNK; tl.ray_count = fl.ray_count;
     tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel == VSB_KERNEL_PATHTRACING ? 16 : 32);
     tl.phase_min = g_phase_min;
+
+    // Host render targets are rendered in bands of whole tile rows (row-major target) or tile ranges
+    // (compact tile buffer): the D2H copy of band i runs on the copy stream while band i+1 is traced.
+    const bool compact = nranks > 1 && !fl.in_place;
+    int n_bands = 1;
+    if (d->mem == VSB_MEM_HOST && fl.n_owned_tiles >= 256) n_bands = g_frame_bands < 1 ? 1 : (g_frame_bands > 8 ? 8 : g_frame_bands);
+    const int units = compact ? fl.n_owned_tiles : fl.tiles_y;               // what a band is made of
+    if (n_bands > units) n_bands = units;
+    const int per_band = (units + n_bands - 1) / n_bands;
+
     VSB_CUDA(cudaEventRecord(g.ev0, st));
+    for (int band = 0; band < n_bands; ++band)
+    {
+        const int u0 = band * per_band, u1 = (band + 1) * per_band < units ? (band + 1) * per_band : units;
+        if (u0 >= u1) break;
+        const int t0 = compact ? u0 : u0 * fl.tiles_x, t1 = compact ? u1 : u1 * fl.tiles_x;   // rank-local tile range
+        // (row-major multi-rank in-place targets are device memory: n_bands == 1 there, t0..t1 = all owned tiles)
+        const int tile_begin = n_bands == 1 ? 0 : t0;
+        const int tile_count = n_bands == 1 ? fl.n_owned_tiles : t1 - t0;
+        tl.n_items = (unsigned long long)tile_count * VSB_TILE * VSB_TILE;
+        tl.work_counter = n_bands == 1 ? g.d_work : g.d_work + 2 + band;
 #define VSB_LAUNCH_FRAME(K)                                                                                  \
     do {                                                                                                     \
         vsb::FrameProgram<K> prog;                                                                           \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
-        prog.in_place = fl.in_place;                                                                         \
-        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true>(prog, tl, st)));  \
-        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false>(prog, tl, st))); \
+        prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true>(prog, tl, st)));                       \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false>(prog, tl, st)));                      \
     } while (0)
-    switch (p.kernel)
-    {
-    case 0: VSB_LAUNCH_FRAME(0); break;
-    case 1: VSB_LAUNCH_FRAME(1); break;
-    case 2: VSB_LAUNCH_FRAME(2); break;
-    default: VSB_LAUNCH_FRAME(3); break;
-    }
+        switch (p.kernel)
+        {
+        case 0: VSB_LAUNCH_FRAME(0); break;
+        case 1: VSB_LAUNCH_FRAME(1); break;
+        case 2: VSB_LAUNCH_FRAME(2); break;
+        default: VSB_LAUNCH_FRAME(3); break;
+        }
 #undef VSB_LAUNCH_FRAME
-    ++g.launches;
-    VSB_CUDA(cudaGetLastError());
-    VSB_CUDA(cudaEventRecord(g.ev1, st));
+        ++g.launches;
+        VSB_CUDA(cudaGetLastError());
+        if (d->mem == VSB_MEM_HOST)
+        {
+            size_t px0, px1;
+            if (compact) { px0 = (size_t)t0 * VSB_TILE * VSB_TILE; px1 = (size_t)t1 * VSB_TILE * VSB_TILE; }
+            else
+            {
+                const size_t row0 = (size_t)u0 * VSB_TILE, row1 = (size_t)u1 * VSB_TILE < (size_t)p.height ? (size_t)u1 * VSB_TILE : (size_t)p.height;
+                px0 = row0 * (size_t)p.width; px1 = row1 * (size_t)p.width;
+            }
+            if (n_bands == 1) { px0 = 0; px1 = color_px; }
+            if (band == n_bands - 1) VSB_CUDA(cudaEventRecord(g.ev1, st));
+            VSB_CUDA(cudaEventRecord(g.band_done[band], st));
+            VSB_CUDA(cudaStreamWaitEvent(g.copy_stream, g.band_done[band], 0));
+            VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * 16, reinterpret_cast<const char*>(fl.color) + px0 * 16,
+                                     (px1 - px0) * 16, cudaMemcpyDeviceToHost, g.copy_stream));
+        }
+    }
     if (d->mem == VSB_MEM_HOST)
     {
-        VSB_CUDA(cudaMemcpyAsync(d->color, fl.color, color_px * 16, cudaMemcpyDeviceToHost, st));
         if (d->ray_count) VSB_CUDA(cudaMemcpyAsync(d->ray_count, d_ray_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
-        VSB_CUDA(cudaStreamSynchronize(st));   // host-visible target: frame() returns with pixels in place
+        VSB_CUDA(cudaStreamSynchronize(st));
+        VSB_CUDA(cudaStreamSynchronize(g.copy_stream));   // host-visible target: frame() returns with pixels in place
     }
+    else VSB_CUDA(cudaEventRecord(g.ev1, st));
     return VSB_OK;
 }
 

@@ -9,6 +9,8 @@ struct Context
     int          device = -1;
     int          sm_count = 0;
     cudaStream_t stream = nullptr;          // internal stream for uploads / encode
+    cudaStream_t copy_stream = nullptr;     // D2H of finished frame bands, overlapping the next band's kernel
+    cudaEvent_t  band_done[8] = {};
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     unsigned long long* d_work = nullptr;   // persistent-kernel work counter
     vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
@@ -144,9 +146,11 @@ extern "C" int vsb_init(int device)
     g.device = device;
     g.sm_count = prop.multiProcessorCount;
     VSB_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
+    VSB_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 8; ++i) VSB_CUDA(cudaEventCreateWithFlags(&g.band_done[i], cudaEventDisableTiming));
     VSB_CUDA(cudaEventCreate(&g.ev0));
     VSB_CUDA(cudaEventCreate(&g.ev1));
-    VSB_CUDA(cudaMalloc(&g.d_work, 64));
+    VSB_CUDA(cudaMalloc(&g.d_work, 16 * sizeof(unsigned long long)));   // [0] queue, [1] ray count, [2..9] band queues
     VSB_CUDA(cudaMalloc(&g.d_scenes, sizeof(vsb::DeviceScene) * MAX_SCENES));
     g.inited = true;
     return VSB_OK;
@@ -163,6 +167,8 @@ extern "C" int vsb_shutdown(void)
     if (g.ev0) cudaEventDestroy(g.ev0);
     if (g.ev1) cudaEventDestroy(g.ev1);
     if (g.stream) cudaStreamDestroy(g.stream);
+    if (g.copy_stream) cudaStreamDestroy(g.copy_stream);
+    for (int i = 0; i < 8; ++i) if (g.band_done[i]) cudaEventDestroy(g.band_done[i]);
     g = Context();
     return VSB_OK;
 }

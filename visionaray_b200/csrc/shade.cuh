@@ -187,7 +187,9 @@ VSB_HD V3 material_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, ui
 #if defined(__CUDACC__)
 
 #define VSB_TILE 64
-#define VSB_FRAME_CHUNK 64          // one 8x8 pixel block per warp reservation
+#ifndef VSB_FRAME_CHUNK
+#define VSB_FRAME_CHUNK 32          // half an 8x8 pixel block (8x4) per warp reservation: short tail per launch
+#endif
 
 // a ray handed to the traversal loop by a program
 struct RayReq
@@ -219,6 +221,7 @@ struct FrameProgram
     int tile_rank, tile_nranks;      // tile_nranks == 0: single rank, row-major target
     int tiles_x;
     int in_place;                    // tile_nranks > 1: store into the whole row-major frame (e.g. peer memory)
+    int tile_begin;                  // first rank-local tile of this launch (host targets are rendered in bands)
 
     using Lane = FrameLane;
     static constexpr int STATE_WORDS = KERNEL == 1 ? 20 : (KERNEL == 0 ? 3 : 9);
@@ -268,7 +271,7 @@ struct FrameProgram
         const FrameCtx& f = ctx;
         const int nr = tile_nranks > 1 ? tile_nranks : 1;
         const int rk = tile_nranks > 1 ? tile_rank : 0;
-        const int local_tile = (int)(item / (VSB_TILE * VSB_TILE));
+        const int local_tile = tile_begin + (int)(item / (VSB_TILE * VSB_TILE));
         const int in_tile = (int)(item % (VSB_TILE * VSB_TILE));
         const int block = in_tile / 64, p = in_tile % 64;
         const int lx = (block % 8) * 8 + (p & 7), ly = (block / 8) * 8 + (p >> 3);
