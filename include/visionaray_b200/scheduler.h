@@ -339,6 +339,11 @@ namespace pixel_sampler
 struct uniform_type        { static const int id = VSB_PS_UNIFORM; };
 struct jittered_type       { static const int id = VSB_PS_JITTERED; };
 struct jittered_blend_type { static const int id = VSB_PS_JITTERED_BLEND; };
+template <unsigned Num> struct ssaa_type
+{
+    static_assert(Num == 1 || Num == 2 || Num == 4 || Num == 8, "ssaa_type<1|2|4|8>");
+    static const int id = Num == 1 ? VSB_PS_UNIFORM : (Num == 2 ? VSB_PS_SSAA2 : (Num == 4 ? VSB_PS_SSAA4 : VSB_PS_SSAA8));
+};
 }
 
 template <typename RT, typename PxSampler>

@@ -87,7 +87,8 @@ typedef struct vsb_point_light {
 enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1 };
 enum { VSB_PRIM_TRIANGLE = 0, VSB_PRIM_SPHERE = 1 };
 enum { VSB_KERNEL_SIMPLE = 0, VSB_KERNEL_WHITTED = 1, VSB_KERNEL_AO = 2, VSB_KERNEL_PATHTRACING = 3 };
-enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2 };
+enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2,
+       VSB_PS_SSAA2 = 3, VSB_PS_SSAA4 = 4, VSB_PS_SSAA8 = 5 };   /* ssaa_type<2|4|8>, detail/sched_common.h:222-295,640-698 */
 
 /* traversal engine: the wide quantised BVH8 (default, fast) or the reference-order BVH2 walk
  * (bit-exact with detail/bvh/intersect.inl:35-134 including tie order and any-hit winner). */

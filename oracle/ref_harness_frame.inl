@@ -157,6 +157,37 @@ void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, f
             unsigned x = unsigned(i % w), y = unsigned(i / w);
             det_sampler samp((uint32_t)i, fp.frame_num, fp.seed);
             float px = float(x), py = float(y);
+            float* dst = rgba + i * 4;
+            if (fp.pixel_sampler >= 3)
+            {
+                // ssaa_type<N> with the reference's own ray generator: the N rays of
+                // make_primary_rays(ssaa_type<N>) (detail/sched_common.h:222-295), then clear +
+                // N x blend(src / N + dst) (detail/sched_common.h:640-698)
+                vec4 acc(0.0f);
+                auto run = [&](ray_t const& r, float alpha)
+                {
+                    auto res = kernel(r, samp);
+                    acc = res.color * alpha + acc * 1.0f;
+                };
+                random_sampler<float> unused;
+                if (fp.pixel_sampler == 3)
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<2>{}, unused, x, y, w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 2.0f);
+                }
+                else if (fp.pixel_sampler == 4)
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<4>{}, unused, x, y, w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 4.0f);
+                }
+                else
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<8>{}, unused, x, y, w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 8.0f);
+                }
+                dst[0] = acc.x; dst[1] = acc.y; dst[2] = acc.z; dst[3] = acc.w;
+                continue;
+            }
             if (fp.pixel_sampler != 0)
             {
                 // jittered: detail/sched_common.h:197-217
@@ -167,7 +198,6 @@ void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, f
             ray_t r = detail::make_primary_ray_impl<ray_t>(px, py, w, h, eye, cam_u, cam_v, cam_w);
             auto res = kernel(r, samp);
             vec4 c = res.color;
-            float* dst = rgba + i * 4;
             if (fp.pixel_sampler == 2)
             {
                 // jittered_blend: detail/sched_common.h:516-528
@@ -216,6 +246,19 @@ double tiled_frame(K kernel, PS ps, frame_params const& fp, float* rgba, int nth
     }
     if (rgba) std::memcpy(rgba, rt.color(), sizeof(float) * 4 * size_t(fp.width) * fp.height);
     return best;
+}
+
+// uniform or ssaa_type<N> by fp.pixel_sampler (RNG-free kernels: tiled_sched itself is the oracle)
+template <typename R, typename K>
+double tiled_frame_ps(K kernel, frame_params const& fp, float* rgba, int nthreads, int reps, int warmup)
+{
+    switch (fp.pixel_sampler)
+    {
+    case 3: return tiled_frame<R>(kernel, pixel_sampler::ssaa_type<2>{}, fp, rgba, nthreads, reps, warmup);
+    case 4: return tiled_frame<R>(kernel, pixel_sampler::ssaa_type<4>{}, fp, rgba, nthreads, reps, warmup);
+    case 5: return tiled_frame<R>(kernel, pixel_sampler::ssaa_type<8>{}, fp, rgba, nthreads, reps, warmup);
+    default: return tiled_frame<R>(kernel, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+    }
 }
 
 template <typename R>
@@ -287,18 +330,18 @@ double ref_frame(void const* fp_, void const* prims, size_t n_prims, void const*
             simple::kernel<KP> k{ kparams };
             if (mode == 0) { scalar_frame(no_sampler_adapter<simple::kernel<KP>>{ k }, fp, rgba, nthreads, basis_out); return 0.0; }
 #if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
-            if (mode == 1) return tiled_frame<simd::ray8>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+            if (mode == 1) return tiled_frame_ps<simd::ray8>(k, fp, rgba, nthreads, reps, warmup);
 #endif
-            return tiled_frame<ray_t>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+            return tiled_frame_ps<ray_t>(k, fp, rgba, nthreads, reps, warmup);
         }
         else if (fp.kernel == 1)
         {
             whitted::kernel<KP> k{ kparams };
             if (mode == 0) { scalar_frame(no_sampler_adapter<whitted::kernel<KP>>{ k }, fp, rgba, nthreads, basis_out); return 0.0; }
 #if VSNRAY_SIMD_ISA_GE(VSNRAY_SIMD_ISA_AVX)
-            if (mode == 1) return tiled_frame<simd::ray8>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+            if (mode == 1) return tiled_frame_ps<simd::ray8>(k, fp, rgba, nthreads, reps, warmup);
 #endif
-            return tiled_frame<ray_t>(k, pixel_sampler::uniform_type{}, fp, rgba, nthreads, reps, warmup);
+            return tiled_frame_ps<ray_t>(k, fp, rgba, nthreads, reps, warmup);
         }
         else
         {

@@ -35,7 +35,7 @@ typedef struct { float pos[3], kl, cl[3], att_const, att_lin, att_quad, pad[2]; 
 
 typedef struct {
     int32_t  kernel;          /* 0 simple, 1 whitted, 2 ao, 3 pathtracing */
-    int32_t  pixel_sampler;   /* 0 uniform, 1 jittered, 2 jittered_blend */
+    int32_t  pixel_sampler;   /* 0 uniform, 1 jittered, 2 jittered_blend, 3/4/5 ssaa 2x/4x/8x */
     int32_t  width, height;
     float    eye[4], center[4], up[4];
     float    fovy, aspect;

@@ -299,6 +299,32 @@ static void kernel_pathtracing(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, f
 
 typedef struct { frame_ctx* f; size_t b, e; vso_counters c; } frame_job;
 
+/* SSAA sample positions: detail/sched_common.h:222-295 (0.1825 in the 8x table is the reference's) */
+static void ssaa_offset(int num, int k, float* dx, float* dy)
+{
+    static const float o4x[4] = { -0.125f, 0.375f, 0.125f, -0.375f }, o4y[4] = { -0.375f, -0.125f, 0.375f, 0.125f };
+    static const float o8x[8] = { -0.125f, 0.375f, -0.375f, 0.125f, -0.125f, 0.375f, -0.375f, 0.125f };
+    static const float o8y[8] = { -0.4375f, -0.3125f, -0.1875f, -0.0625f, 0.0625f, 0.1825f, 0.3125f, 0.4375f };
+    if (num == 2) { *dx = k == 0 ? -0.25f : 0.25f; *dy = *dx; }
+    else if (num == 4) { *dx = o4x[k]; *dy = o4y[k]; }
+    else { *dx = o8x[k]; *dy = o8y[k]; }
+}
+
+static void run_kernel(const frame_ctx* f, float px, float py, uint32_t* samp, float col[4], vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    vso_ray r;
+    vso_primary_ray(px, py, p->width, p->height, f->eye, f->cu, f->cv, f->cw, &r);
+    v3 o = ld3(r.ori), d = ld3(r.dir);
+    switch (p->kernel)
+    {
+    case 0: kernel_simple(f, o, d, col, c); break;
+    case 1: kernel_whitted(f, o, d, col, c); break;
+    case 2: kernel_ao(f, o, d, samp, col, c); break;
+    default: kernel_pathtracing(f, o, d, samp, col, c); break;
+    }
+}
+
 static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
 {
     const vso_frame_params* p = f->p;
@@ -308,6 +334,23 @@ static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
         unsigned x = (unsigned)(i % w), y = (unsigned)(i / w);
         uint32_t samp = vso_sampler_init((uint32_t)i, p->frame_num, p->seed);
         float px = (float)x, py = (float)y;
+        float* dst = f->rgba + i * 4;
+        float col[4];
+        if (p->pixel_sampler >= 3)
+        {
+            /* ssaa_type<N>: clear, then N x blend(src / N + dst): detail/sched_common.h:640-698 */
+            const int num = 2 << (p->pixel_sampler - 3);
+            const float alpha = 1.0f / (float)num;
+            for (int k = 0; k < 4; ++k) dst[k] = 0.0f;
+            for (int s = 0; s < num; ++s)
+            {
+                float dx, dy;
+                ssaa_offset(num, s, &dx, &dy);
+                run_kernel(f, px + dx, py + dy, &samp, col, c);
+                for (int k = 0; k < 4; ++k) dst[k] = col[k] * alpha + dst[k] * 1.0f;
+            }
+            continue;
+        }
         if (p->pixel_sampler != 0)
         {
             /* jittered: detail/sched_common.h:197-217 */
@@ -315,18 +358,7 @@ static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
             float jy = vso_sampler_next(&samp) - 0.5f;
             px += jx; py += jy;
         }
-        vso_ray r;
-        vso_primary_ray(px, py, p->width, p->height, f->eye, f->cu, f->cv, f->cw, &r);
-        v3 o = ld3(r.ori), d = ld3(r.dir);
-        float col[4];
-        switch (p->kernel)
-        {
-        case 0: kernel_simple(f, o, d, col, c); break;
-        case 1: kernel_whitted(f, o, d, col, c); break;
-        case 2: kernel_ao(f, o, d, &samp, col, c); break;
-        default: kernel_pathtracing(f, o, d, &samp, col, c); break;
-        }
-        float* dst = f->rgba + i * 4;
+        run_kernel(f, px, py, &samp, col, c);
         if (p->pixel_sampler == 2)
         {
             /* jittered_blend: detail/sched_common.h:516-528 */

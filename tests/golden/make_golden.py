@@ -42,6 +42,9 @@ def main():
         fp = S.frame_params(kernel, 32, 24, eye, (0, 0, 0), pixel_sampler=ps, ambient=(1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0))
         img, _, _ = O.ref_frame(sc, fp, S.default_material(mat), S.point_light(eye), mode=0)
         frames[f"k{kernel}"] = img
+    # ssaa_type<4> through the reference's own tiled_sched<simd::ray8> (RNG-free kernel)
+    fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=4)
+    frames["k1_ssaa4"], _, _ = O.ref_frame(sc, fp, S.default_material(0), S.point_light(eye), mode=1)
     np.savez_compressed(os.path.join(HERE, "golden_frames.npz"), **frames)
     print("wrote golden_queries.npz, golden_frames.npz")
 

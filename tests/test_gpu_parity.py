@@ -199,6 +199,7 @@ def test_golden_vectors_through_c_abi(gpu):
 
 FRAMES = [  # kernel, pixel sampler, material kind
     (0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 2, 1), (3, 1, 0),
+    (0, 3, 0), (1, 4, 0), (1, 5, 0), (2, 4, 0), (3, 3, 1),      # ssaa_type<2|4|8>
 ]
 
 

@@ -95,6 +95,29 @@ def test_oracle_frames_match_reference(kernel, ps, mat):
         assert np.abs(a - c).max() <= 1.0 / 255.0
 
 
+@pytest.mark.parametrize("kernel,ps", [(0, 3), (1, 4), (0, 5), (2, 4), (3, 3)])
+def test_oracle_ssaa_matches_reference(kernel, ps):
+    """ssaa_type<2|4|8> (detail/sched_common.h:222-295,640-698): the restatement against the reference's
+    own make_primary_rays(ssaa_type<N>) driven per pixel, and for the RNG-free kernels against the
+    reference's tiled_sched<ray8> with the ssaa pixel sampler."""
+    if not O.ref_available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    sc = S.make_scene("cfg2_grid", 0.01)
+    eye = (0.3, 1.2, 2.2)
+    fp = S.frame_params(kernel, 48, 40, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=(1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0))
+    mats, lights = S.default_material(1 if kernel == 3 else 0), S.point_light(eye)
+    a = O.oracle_frame(sc, fp, mats, lights)
+    b, _, _ = O.ref_frame(sc, fp, mats, lights, mode=0)
+    assert np.abs(a - b).max() <= 1e-6
+    if kernel in (0, 1):
+        c, _, _ = O.ref_frame(sc, fp, mats, lights, mode=1)
+        assert np.abs(a - c).max() <= 1.0 / 255.0
+    # supersampling really happened: differs from the uniform frame on edges
+    u = O.oracle_frame(sc, S.frame_params(kernel, 48, 40, eye, (0, 0, 0), pixel_sampler=0, num_bounces=4,
+                                          ambient=(1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0)), mats, lights)
+    assert np.abs(a - u).max() > 1e-3
+
+
 def test_golden_vectors():
     """Fixtures generated from the reference itself by tests/golden/make_golden.py."""
     path = os.path.join(GOLD, "golden_queries.npz")
@@ -117,6 +140,10 @@ def test_golden_vectors():
         fp = S.frame_params(kernel, 32, 24, eye, (0, 0, 0), pixel_sampler=ps, ambient=(1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0))
         img = O.oracle_frame(sc, fp, S.default_material(mat), S.point_light(eye))
         assert np.abs(img - fr[f"k{kernel}"]).max() <= 1e-6
+    if "k1_ssaa4" in fr:
+        fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=4)
+        img = O.oracle_frame(sc, fp, S.default_material(0), S.point_light(eye))
+        assert np.abs(img - fr["k1_ssaa4"]).max() <= 1.0 / 255.0     # generated by tiled_sched<simd::ray8> (packets)
 
 
 def test_brute_force_agrees_with_bvh():

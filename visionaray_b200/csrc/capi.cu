@@ -248,7 +248,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     int rc = require_init(); if (rc) return rc;
     if (!d || !d->color) return VSB_ERR_BAD_ARG;
     const vsb_frame_params& p = d->p;
-    if (p.width < 1 || p.height < 1 || p.kernel < 0 || p.kernel > 3 || p.pixel_sampler < 0 || p.pixel_sampler > 2) return VSB_ERR_BAD_ARG;
+    if (p.width < 1 || p.height < 1 || p.kernel < 0 || p.kernel > 3 || p.pixel_sampler < 0 || p.pixel_sampler > 5) return VSB_ERR_BAD_ARG;
     if (p.pixel_sampler == VSB_PS_JITTERED_BLEND && p.frame_num == 0) return VSB_ERR_BAD_ARG;
     if (p.kernel != VSB_KERNEL_AO && (!d->materials || p.n_materials < 1)) return VSB_ERR_BAD_ARG;
     if (p.n_lights > 0 && !d->lights && p.kernel <= VSB_KERNEL_WHITTED) return VSB_ERR_BAD_ARG;
@@ -346,21 +346,25 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         const int tile_count = n_bands == 1 ? fl.n_owned_tiles : t1 - t0;
         tl.n_items = (unsigned long long)tile_count * VSB_TILE * VSB_TILE;
         tl.work_counter = n_bands == 1 ? g.d_work : g.d_work + 2 + band;
-#define VSB_LAUNCH_FRAME(K)                                                                                  \
+#define VSB_LAUNCH_FRAME(K, SS)                                                                                \
     do {                                                                                                     \
-        vsb::FrameProgram<K> prog;                                                                           \
+        vsb::FrameProgram<K, SS> prog;                                                                       \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
-        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K>, true>(prog, tl, st)));                       \
-        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K>, false>(prog, tl, st)));                      \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, true>(prog, tl, st)));                   \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, st)));                  \
     } while (0)
-        switch (p.kernel)
+        switch (p.kernel * 2 + (p.pixel_sampler >= VSB_PS_SSAA2 ? 1 : 0))
         {
-        case 0: VSB_LAUNCH_FRAME(0); break;
-        case 1: VSB_LAUNCH_FRAME(1); break;
-        case 2: VSB_LAUNCH_FRAME(2); break;
-        default: VSB_LAUNCH_FRAME(3); break;
+        case 0: VSB_LAUNCH_FRAME(0, false); break;
+        case 1: VSB_LAUNCH_FRAME(0, true); break;
+        case 2: VSB_LAUNCH_FRAME(1, false); break;
+        case 3: VSB_LAUNCH_FRAME(1, true); break;
+        case 4: VSB_LAUNCH_FRAME(2, false); break;
+        case 5: VSB_LAUNCH_FRAME(2, true); break;
+        case 6: VSB_LAUNCH_FRAME(3, false); break;
+        default: VSB_LAUNCH_FRAME(3, true); break;
         }
 #undef VSB_LAUNCH_FRAME
         ++g.launches;

@@ -209,10 +209,13 @@ struct FrameLane
     __device__ void st(int k, V3 a) { f(k) = a.x; f(k + 1) = a.y; f(k + 2) = a.z; }
 };
 
-enum { W_DST = 0, W_SAMP = 1, W_PHASE = 2, W_K = 3 };
+// common words: destination index, sampler state, phase, pixel index, SSAA sub-sample index + accumulator
+enum { W_DST = 0, W_SAMP = 1, W_PHASE = 2, W_PIX = 3, W_SUB = 4, W_ACC = 5 };   // 3.. only with SSAA
 enum { PH_PRIMARY = 0, PH_BOUNCE = 1, PH_SHADOW = 2 };
 
-template <int KERNEL>
+// SSAA = true adds the sub-sample accumulator to the lane state and the resampling branch to
+// finish(); the common samplers run the leaner instantiation.
+template <int KERNEL, bool SSAA>
 struct FrameProgram
 {
     FrameCtx ctx;
@@ -224,7 +227,8 @@ struct FrameProgram
     int tile_begin;                  // first rank-local tile of this launch (host targets are rendered in bands)
 
     using Lane = FrameLane;
-    static constexpr int STATE_WORDS = KERNEL == 1 ? 20 : (KERNEL == 0 ? 3 : 9);
+    static constexpr int K0 = SSAA ? 9 : 3;      // first kernel-specific state word
+    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? 17 : (KERNEL == 0 ? 0 : 6));
 
     __device__ void closest(RayReq& r, V3 o, V3 d) const
     {
@@ -235,12 +239,70 @@ struct FrameProgram
         r.ox = o.x; r.oy = o.y; r.oz = o.z; r.dx = d.x; r.dy = d.y; r.dz = d.z; r.max_t = max_t; r.any = true;
     }
 
-    // pixel_access::store / blend (detail/pixel_access.h:38-58, detail/sched_common.h:516-528)
-    __device__ void finish(Lane& L, float r, float g, float b, float a) const
+    // SSAA sample positions: detail/sched_common.h:222-295 (the 8x table's 0.1825 is the reference's)
+    __device__ void ssaa_offset(int num, int k, float& dx, float& dy) const
+    {
+        if (num == 2) { dx = k == 0 ? -0.25f : 0.25f; dy = dx; return; }
+        if (num == 4)
+        {
+            const float ox[4] = { -0.125f, 0.375f, 0.125f, -0.375f }, oy[4] = { -0.375f, -0.125f, 0.375f, 0.125f };
+            dx = ox[k]; dy = oy[k]; return;
+        }
+        const float ox[8] = { -0.125f, 0.375f, -0.375f, 0.125f, -0.125f, 0.375f, -0.375f, 0.125f };
+        const float oy[8] = { -0.4375f, -0.3125f, -0.1875f, -0.0625f, 0.0625f, 0.1825f, 0.3125f, 0.4375f };
+        dx = ox[k]; dy = oy[k];
+    }
+
+    // per-sample kernel state + the primary ray of sub-sample k (k = 0 for the non-SSAA samplers)
+    __device__ void start_sample(Lane& L, float fx, float fy, RayReq& req) const
+    {
+        L.u(W_PHASE) = PH_PRIMARY;
+        if (KERNEL == 1)
+        {
+            L.st(K0 + 0, v3(0.0f, 0.0f, 0.0f));     // color
+            L.f(K0 + 6) = 1.0f;                     // throughput
+            L.u(K0 + 7) = 0u;                       // depth
+        }
+        if (KERNEL == 3)
+        {
+            L.st(K0 + 0, v3(1.0f, 1.0f, 1.0f));     // dst
+            L.u(K0 + 3) = 0u;                       // bounce
+            L.u(K0 + 4) = 0u;                       // result.hit
+        }
+        V3 o, d;
+        primary_ray(ctx, fx, fy, o, d);
+        closest(req, o, d);
+    }
+
+    // Pixel result of one kernel invocation.  uniform / jittered: store (detail/pixel_access.h:38-58);
+    // jittered_blend: dst = src/frame_num + dst (1 - 1/frame_num) (detail/sched_common.h:516-528);
+    // ssaa<N>: clear, then N x { dst = src/N + dst } (detail/sched_common.h:640-698) -- the
+    // accumulator lives in the lane state and the next sub-sample's primary ray is emitted.
+    // Returns true when the pixel continues with another ray (req).
+    __device__ bool finish(Lane& L, float r, float g, float b, float a, RayReq& req) const
     {
         const size_t dst = L.u(W_DST);
         float4 c = make_float4(r, g, b, a);
-        if (ctx.p.pixel_sampler == 2)
+        const int ps = ctx.p.pixel_sampler;
+        if (SSAA && ps >= 3)
+        {
+            const int num = 2 << (ps - 3);
+            const float alpha = rn_div(1.0f, (float)num);
+            c.x = rn_add(rn_mul(c.x, alpha), L.f(W_ACC + 0)); c.y = rn_add(rn_mul(c.y, alpha), L.f(W_ACC + 1));
+            c.z = rn_add(rn_mul(c.z, alpha), L.f(W_ACC + 2)); c.w = rn_add(rn_mul(c.w, alpha), L.f(W_ACC + 3));
+            const uint32_t k = L.u(W_SUB) + 1u;
+            if ((int)k < num)
+            {
+                L.f(W_ACC + 0) = c.x; L.f(W_ACC + 1) = c.y; L.f(W_ACC + 2) = c.z; L.f(W_ACC + 3) = c.w;
+                L.u(W_SUB) = k;
+                const uint32_t pixel = L.u(W_PIX);
+                float dx, dy;
+                ssaa_offset(num, (int)k, dx, dy);
+                start_sample(L, rn_add((float)(pixel % (uint32_t)ctx.p.width), dx), rn_add((float)(pixel / (uint32_t)ctx.p.width), dy), req);
+                return true;
+            }
+        }
+        else if (ps == 2)
         {
             const float alpha = rn_div(1.0f, (float)ctx.p.frame_num);
             const float ia = rn_sub(1.0f, alpha);
@@ -251,8 +313,9 @@ struct FrameProgram
             c.w = rn_add(rn_mul(c.w, alpha), rn_mul(old.w, ia));
         }
         color[dst] = c;
+        return false;
     }
-    __device__ void finish_bg(Lane& L) const { finish(L, ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3]); }
+    __device__ bool finish_bg(Lane& L, RayReq& req) const { return finish(L, ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3], req); }
 
     __device__ V3 ambient_term(const Material& m) const
     {
@@ -282,50 +345,51 @@ struct FrameProgram
         if (!inside) return false;
         const uint32_t pixel = (uint32_t)y * (uint32_t)f.p.width + (uint32_t)x;
         L.u(W_DST) = (tile_nranks > 1 && !in_place) ? (uint32_t)(local_tile * (VSB_TILE * VSB_TILE) + ly * VSB_TILE + lx) : pixel;
+        if (SSAA)
+        {
+            L.u(W_PIX) = pixel; L.u(W_SUB) = 0u;
+            L.f(W_ACC + 0) = 0.0f; L.f(W_ACC + 1) = 0.0f; L.f(W_ACC + 2) = 0.0f; L.f(W_ACC + 3) = 0.0f;
+        }
         uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
         float fx = (float)x, fy = (float)y;
-        if (f.p.pixel_sampler != 0)
+        if (f.p.pixel_sampler == 1 || f.p.pixel_sampler == 2)
         {
             // jittered (detail/sched_common.h:197-217)
             const float jx = rn_sub(sampler_next(samp), 0.5f);
             const float jy = rn_sub(sampler_next(samp), 0.5f);
             fx = rn_add(fx, jx); fy = rn_add(fy, jy);
         }
+        else if (SSAA && f.p.pixel_sampler >= 3)
+        {
+            float dx, dy;
+            ssaa_offset(2 << (f.p.pixel_sampler - 3), 0, dx, dy);
+            fx = rn_add(fx, dx); fy = rn_add(fy, dy);
+        }
         L.u(W_SAMP) = samp;
-        L.u(W_PHASE) = PH_PRIMARY;
-        V3 o, d;
-        primary_ray(f, fx, fy, o, d);
-        if (KERNEL == 1)
+        if (KERNEL == 3 && f.p.num_bounces == 0u)
         {
-            L.st(W_K + 0, v3(0.0f, 0.0f, 0.0f));     // color
-            L.f(W_K + 6) = 1.0f;                     // throughput
-            L.u(W_K + 7) = 0u;                       // depth
+            // no bounce is traced: every sample returns the background
+            color[L.u(W_DST)] = make_float4(f.p.bg[0], f.p.bg[1], f.p.bg[2], f.p.bg[3]);
+            return false;
         }
-        if (KERNEL == 3)
-        {
-            L.st(W_K + 0, v3(1.0f, 1.0f, 1.0f));     // dst
-            L.u(W_K + 3) = 0u;                       // bounce
-            L.u(W_K + 4) = 0u;                       // result.hit
-            if (f.p.num_bounces == 0u) { finish_bg(L); return false; }
-        }
-        closest(req, o, d);
+        start_sample(L, fx, fy, req);
         return true;
     }
 
     __device__ bool done(Lane& L, const HitReg& h, float ox, float oy, float oz, float dx, float dy, float dz, RayReq& req) const
     {
         const V3 o = v3(ox, oy, oz), d = v3(dx, dy, dz);
-        if (KERNEL == 0) return done_simple(L, h, o, d);
+        if (KERNEL == 0) return done_simple(L, h, o, d, req);
         if (KERNEL == 1) return done_whitted(L, h, o, d, req);
         if (KERNEL == 2) return done_ao(L, h, o, d, req);
         return done_pathtracing(L, h, o, d, req);
     }
 
     // simple::kernel -- detail/simple.inl:25-75
-    __device__ bool done_simple(Lane& L, const HitReg& h, V3 o, V3 d) const
+    __device__ bool done_simple(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
         const FrameCtx& f = ctx;
-        if (!h.hit) { finish_bg(L); return false; }
+        if (!h.hit) { return finish_bg(L, req); }
         const V3 pos = vadd(o, vscale(d, h.t));
         const Material m = f.materials[h.geom_id];
         V3 n = face_normal(h.prim_id);
@@ -339,8 +403,7 @@ struct FrameProgram
             const V3 c = shade_light(m, l, pos, n, view, wi);
             shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
         }
-        finish(L, shaded.x, shaded.y, shaded.z, 1.0f);
-        return false;
+        return finish(L, shaded.x, shaded.y, shaded.z, 1.0f, req);
     }
 
     // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
@@ -353,8 +416,8 @@ struct FrameProgram
         uint32_t prim_id, geom_id, light;
         if (phase == PH_SHADOW)
         {
-            pos = L.ld(W_K + 9); view = L.ld(W_K + 12); shaded = L.ld(W_K + 3);
-            prim_id = L.u(W_K + 15); geom_id = L.u(W_K + 16); light = L.u(W_K + 8);
+            pos = L.ld(K0 + 9); view = L.ld(K0 + 12); shaded = L.ld(K0 + 3);
+            prim_id = L.u(K0 + 15); geom_id = L.u(K0 + 16); light = L.u(K0 + 8);
             if (!h.hit)
             {
                 const Material m = f.materials[geom_id];
@@ -369,39 +432,38 @@ struct FrameProgram
         }
         else
         {
-            if (phase == PH_PRIMARY && !h.hit) { finish_bg(L); return false; }
+            if (phase == PH_PRIMARY && !h.hit) { return finish_bg(L, req); }
             // while (hit && throughput > epsilon && depth++ < num_bounces)
-            const float throughput = L.f(W_K + 6);
+            const float throughput = L.f(K0 + 6);
             bool go = h.hit && throughput > f.p.epsilon;
-            if (go) { const uint32_t depth = L.u(W_K + 7); go = depth < f.p.num_bounces; L.u(W_K + 7) = depth + 1u; }
-            if (!go) { const V3 c = L.ld(W_K + 0); finish(L, c.x, c.y, c.z, 1.0f); return false; }
+            if (go) { const uint32_t depth = L.u(K0 + 7); go = depth < f.p.num_bounces; L.u(K0 + 7) = depth + 1u; }
+            if (!go) { const V3 c = L.ld(K0 + 0); return finish(L, c.x, c.y, c.z, 1.0f, req); }
             pos = vadd(o, vscale(d, h.t));
             view = vneg(d);
             prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
             shaded = ambient_term(f.materials[geom_id]);
-            L.st(W_K + 9, pos); L.st(W_K + 12, view); L.u(W_K + 15) = prim_id; L.u(W_K + 16) = geom_id;
+            L.st(K0 + 9, pos); L.st(K0 + 12, view); L.u(K0 + 15) = prim_id; L.u(K0 + 16) = geom_id;
         }
         if ((int)light < f.p.n_lights)
         {
             const V3 lpos = ld3(f.lights[light].pos);
             const V3 wi = vnormalize(vsub(lpos, pos));
             occlusion(req, vadd(pos, vscale(wi, f.p.epsilon)), wi, vlength(vsub(pos, lpos)));
-            L.st(W_K + 3, shaded); L.u(W_K + 8) = light; L.u(W_PHASE) = PH_SHADOW;
+            L.st(K0 + 3, shaded); L.u(K0 + 8) = light; L.u(W_PHASE) = PH_SHADOW;
             return true;
         }
-        const float throughput = L.f(W_K + 6);
-        V3 color = L.ld(W_K + 0);
+        const float throughput = L.f(K0 + 6);
+        V3 color = L.ld(K0 + 0);
         color = v3(color.x + shaded.x * throughput, color.y + shaded.y * throughput, color.z + shaded.z * throughput);
         const float kr = (f.materials[geom_id].kind == 0) ? 0.1f : 0.0f;   // specular_bounce, detail/whitted.inl:79-110
         if (kr > 0.0f)
         {
             const V3 dir = vreflect(view, face_normal(prim_id));
             closest(req, vadd(pos, vscale(dir, f.p.epsilon)), dir);
-            L.st(W_K + 0, color); L.f(W_K + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
+            L.st(K0 + 0, color); L.f(K0 + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
             return true;
         }
-        finish(L, color.x, color.y, color.z, 1.0f);    // throughput * 0 ends the loop
-        return false;
+        return finish(L, color.x, color.y, color.z, 1.0f, req);    // throughput * 0 ends the loop
     }
 
     // AO kernel -- src/examples/ao/main.cpp:183-246.  State: pos 0..2, prim_id 3, clr 4, i 5
@@ -411,14 +473,14 @@ struct FrameProgram
         V3 pos; uint32_t prim_id, i; float clr;
         if (L.u(W_PHASE) == PH_PRIMARY)
         {
-            if (!h.hit) { finish_bg(L); return false; }
+            if (!h.hit) { return finish_bg(L, req); }
             pos = vadd(o, vscale(d, h.t));
             prim_id = h.prim_id; clr = 1.0f; i = 0u;
-            L.st(W_K + 0, pos); L.u(W_K + 3) = prim_id; L.u(W_PHASE) = PH_SHADOW;
+            L.st(K0 + 0, pos); L.u(K0 + 3) = prim_id; L.u(W_PHASE) = PH_SHADOW;
         }
         else
         {
-            pos = L.ld(W_K + 0); prim_id = L.u(W_K + 3); clr = L.f(W_K + 4); i = L.u(W_K + 5);
+            pos = L.ld(K0 + 0); prim_id = L.u(K0 + 3); clr = L.f(K0 + 4); i = L.u(K0 + 5);
             if (h.hit) clr = rn_sub(clr, 1.0f / (float)f.p.ao_samples);
             ++i;
         }
@@ -433,20 +495,19 @@ struct FrameProgram
             L.u(W_SAMP) = samp;
             const V3 dir = hemisphere_dir(u, v, w, cosine_sample_hemisphere(u1, u2));
             occlusion(req, vadd(pos, vscale(dir, 1E-3f)), dir, f.p.ao_radius);
-            L.f(W_K + 4) = clr; L.u(W_K + 5) = i;
+            L.f(K0 + 4) = clr; L.u(K0 + 5) = i;
             return true;
         }
-        finish(L, clr, clr, clr, 1.0f);
-        return false;
+        return finish(L, clr, clr, clr, 1.0f, req);
     }
 
     // pathtracing::kernel -- detail/pathtracing.inl:29-121.  State: dst 0..2, bounce 3, result.hit 4
     __device__ bool done_pathtracing(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
         const FrameCtx& f = ctx;
-        V3 dst = L.ld(W_K + 0);
-        uint32_t bounce = L.u(W_K + 3);
-        bool result_hit = L.u(W_K + 4) != 0u;
+        V3 dst = L.ld(K0 + 0);
+        uint32_t bounce = L.u(K0 + 3);
+        bool result_hit = L.u(K0 + 4) != 0u;
         const float aw = f.p.ambient[3];
         bool finished = false;
         if (!h.hit)
@@ -480,12 +541,8 @@ struct FrameProgram
                 }
             }
         }
-        if (finished)
-        {
-            if (result_hit) finish(L, dst.x, dst.y, dst.z, 1.0f); else finish_bg(L);
-            return false;
-        }
-        L.st(W_K + 0, dst); L.u(W_K + 3) = bounce; L.u(W_K + 4) = result_hit ? 1u : 0u;
+        if (finished) return result_hit ? finish(L, dst.x, dst.y, dst.z, 1.0f, req) : finish_bg(L, req);
+        L.st(K0 + 0, dst); L.u(K0 + 3) = bounce; L.u(K0 + 4) = result_hit ? 1u : 0u;
         return true;
     }
 };
