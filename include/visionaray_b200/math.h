@@ -49,6 +49,22 @@ struct alignas(16) vec4
     float const* data() const { return &x; }
 };
 
+// matrix<4,4,float> (math/matrix.h:74-130): four columns, 16 floats column-major; (row, col) access
+struct alignas(16) mat4
+{
+    float m[16];
+    mat4() = default;
+    explicit mat4(float const* d) { for (int i = 0; i < 16; ++i) m[i] = d[i]; }
+    mat4(float m00, float m10, float m20, float m30, float m01, float m11, float m21, float m31,
+         float m02, float m12, float m22, float m32, float m03, float m13, float m23, float m33)
+        : m{ m00, m10, m20, m30, m01, m11, m21, m31, m02, m12, m22, m32, m03, m13, m23, m33 } {}
+    static mat4 identity() { return mat4(1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1, 0, 0, 0, 0, 1); }
+    float&       operator()(size_t row, size_t col)       { return m[col * 4 + row]; }
+    float const& operator()(size_t row, size_t col) const { return m[col * 4 + row]; }
+    float*       data()       { return m; }
+    float const* data() const { return m; }
+};
+
 struct recti { int x, y, w, h; recti() = default; recti(int x_, int y_, int w_, int h_) : x(x_), y(y_), w(w_), h(h_) {} };
 
 // Operation order follows the reference (math/detail/vector3.inl:293-336) so that host-side

@@ -201,8 +201,28 @@ inline void any_hit(ray const* rays, size_t n, b200_bvh_ref const* begin, b200_b
 class pinhole_camera
 {
 public:
-    void look_at(vec3 const& eye, vec3 const& center, vec3 const& up = vec3(0.0f, 1.0f, 0.0f)) { eye_ = eye; center_ = center; up_ = up; }
-    void perspective(float fovy, float aspect, float z_near, float z_far) { fovy_ = fovy; aspect_ = aspect; z_near_ = z_near; z_far_ = z_far; }
+    // view / projection matrices as the reference camera keeps them (detail/camera.inl:10-65)
+    void look_at(vec3 const& eye, vec3 const& center, vec3 const& up = vec3(0.0f, 1.0f, 0.0f))
+    {
+        eye_ = eye; center_ = center; up_ = up;
+        vec3 f = normalize(eye - center);
+        vec3 s = normalize(cross(up, f));
+        vec3 u = cross(f, s);
+        view_ = mat4(s.x, u.x, f.x, 0.0f, s.y, u.y, f.y, 0.0f, s.z, u.z, f.z, 0.0f, -dot(eye, s), -dot(eye, u), -dot(eye, f), 1.0f);
+    }
+    void perspective(float fovy, float aspect, float z_near, float z_far)
+    {
+        fovy_ = fovy; aspect_ = aspect; z_near_ = z_near; z_far_ = z_far;
+        float f = 1.0f / std::tan(fovy * 0.5f);
+        for (int i = 0; i < 16; ++i) proj_.m[i] = 0.0f;
+        proj_(0, 0) = f / aspect;
+        proj_(1, 1) = f;
+        proj_(2, 2) = (z_far + z_near) / (z_near - z_far);
+        proj_(2, 3) = (2.0f * z_far * z_near) / (z_near - z_far);
+        proj_(3, 2) = -1.0f;
+    }
+    mat4 const& get_view_matrix() const { return view_; }
+    mat4 const& get_proj_matrix() const { return proj_; }
     void set_viewport(recti const& viewport) { viewport_ = viewport; }
     void set_viewport(int left, int bottom, int width, int height) { viewport_ = recti(left, bottom, width, height); }
     recti get_viewport() const { return viewport_; }
@@ -218,6 +238,7 @@ private:
     vec3 eye_ = vec3(0.0f, 0.0f, 1.0f), center_ = vec3(0.0f), up_ = vec3(0.0f, 1.0f, 0.0f);
     float fovy_ = 0.78539816f, aspect_ = 1.0f, z_near_ = 0.001f, z_far_ = 1000.0f;
     recti viewport_ = recti(0, 0, 0, 0);
+    mat4 view_ = mat4::identity(), proj_ = mat4::identity();
 };
 using camera = pinhole_camera;   // the reference's class name (camera.h)
 
@@ -366,18 +387,42 @@ sched_params<RT, pixel_sampler::uniform_type> make_sched_params(pinhole_camera c
     return make_sched_params(pixel_sampler::uniform_type{}, cam, rt);
 }
 
+// sched_params from view / projection matrices (scheduler.h:60-96, make_sched_params :205-242):
+// primary rays from the inverse matrices, and the only form that can fill a depth buffer
+template <typename RT, typename PxSampler>
+struct sched_params_matrix
+{
+    using pixel_sampler_type = PxSampler;
+    mat4 view_matrix, proj_matrix;
+    RT& rt;
+    recti scissor_box;
+};
+
+template <typename PxSampler, typename RT>
+sched_params_matrix<RT, PxSampler> make_sched_params(PxSampler, mat4 const& view_matrix, mat4 const& proj_matrix, RT& rt)
+{
+    return sched_params_matrix<RT, PxSampler>{ view_matrix, proj_matrix, rt, recti(0, 0, int(rt.width()), int(rt.height())) };
+}
+template <typename RT>
+sched_params_matrix<RT, pixel_sampler::uniform_type> make_sched_params(mat4 const& view_matrix, mat4 const& proj_matrix, RT& rt)
+{
+    return make_sched_params(pixel_sampler::uniform_type{}, view_matrix, proj_matrix, rt);
+}
+
 //-------------------------------------------------------------------------------------------------
 // Render targets (render_target.h:45-101, simple_buffer_rt.h:21-52, gpu_buffer_rt.h:16-48).
-// PF_RGBA32F colour, no depth (PF_UNSPECIFIED): buffer[y * width + x], y up, pitch = width.
+// PF_RGBA32F colour, depth PF_UNSPECIFIED (none) or PF_DEPTH32F: buffer[y * width + x], y up,
+// pitch = width.
 //
 
-enum pixel_format { PF_UNSPECIFIED = 0, PF_RGBA32F = 1 };
+enum pixel_format { PF_UNSPECIFIED = 0, PF_RGBA32F = 1, PF_DEPTH32F = 2 };
 
 template <pixel_format CF, pixel_format DF>
 struct render_target_ref
 {
-    vec4* color_; void* depth_; int width_, height_;
+    vec4* color_; float* depth_; int width_, height_;
     vec4* color() const { return color_; }
+    float* depth() const { return depth_; }
     int width() const { return width_; }
     int height() const { return height_; }
 };
@@ -386,23 +431,32 @@ struct render_target_ref
 template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
 class simple_buffer_rt
 {
-    static_assert(CF == PF_RGBA32F && DF == PF_UNSPECIFIED, "the path writes RGBA32F colour only");
+    static_assert(CF == PF_RGBA32F && (DF == PF_UNSPECIFIED || DF == PF_DEPTH32F), "the path writes RGBA32F colour and DEPTH32F depth");
 public:
     using color_type = vec4;
+    using depth_type = float;
     using ref_type = render_target_ref<CF, DF>;
     static const int memory = VSB_MEM_HOST;
 
     color_type* color() { return color_.data(); }
     color_type const* color() const { return color_.data(); }
-    ref_type ref() { return ref_type{ color(), nullptr, int(width_), int(height_) }; }
+    depth_type* depth() { return DF == PF_DEPTH32F ? depth_.data() : nullptr; }
+    depth_type const* depth() const { return DF == PF_DEPTH32F ? depth_.data() : nullptr; }
+    ref_type ref() { return ref_type{ color(), depth(), int(width_), int(height_) }; }
     void clear_color_buffer(vec4 const& c = vec4(0.0f)) { for (auto& p : color_) p = c; }
+    void clear_depth_buffer(float d = 1.0f) { for (auto& p : depth_) p = d; }
     void begin_frame() {}
     void end_frame() {}
-    void resize(size_t w, size_t h) { width_ = w; height_ = h; color_.assign(w * h, vec4(0.0f)); }
+    void resize(size_t w, size_t h)
+    {
+        width_ = w; height_ = h; color_.assign(w * h, vec4(0.0f));
+        if (DF == PF_DEPTH32F) depth_.assign(w * h, 0.0f);
+    }
     size_t width() const { return width_; }
     size_t height() const { return height_; }
 private:
     std::vector<vec4> color_;
+    std::vector<float> depth_;
     size_t width_ = 0, height_ = 0;
 };
 template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
@@ -412,20 +466,33 @@ using cpu_buffer_rt = simple_buffer_rt<CF, DF>;   // cpu_buffer_rt minus display
 template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
 class gpu_buffer_rt
 {
-    static_assert(CF == PF_RGBA32F && DF == PF_UNSPECIFIED, "the path writes RGBA32F colour only");
+    static_assert(CF == PF_RGBA32F && (DF == PF_UNSPECIFIED || DF == PF_DEPTH32F), "the path writes RGBA32F colour and DEPTH32F depth");
 public:
     using color_type = vec4;
+    using depth_type = float;
     using ref_type = render_target_ref<CF, DF>;
     static const int memory = VSB_MEM_DEVICE;
 
     gpu_buffer_rt() = default;
     gpu_buffer_rt(gpu_buffer_rt const&) = delete;
     gpu_buffer_rt& operator=(gpu_buffer_rt const&) = delete;
-    ~gpu_buffer_rt() { if (color_) vsb_device_free(color_); }
+    ~gpu_buffer_rt() { if (color_) vsb_device_free(color_); if (depth_) vsb_device_free(depth_); }
 
     color_type* color() { return color_; }                      // DEVICE pointer
     color_type const* color() const { return color_; }
-    ref_type ref() { return ref_type{ color_, nullptr, int(width_), int(height_) }; }
+    depth_type* depth() { return depth_; }                      // DEVICE pointer (null without a depth format)
+    depth_type const* depth() const { return depth_; }
+    ref_type ref() { return ref_type{ color_, depth_, int(width_), int(height_) }; }
+    void clear_depth_buffer(float d = 1.0f)
+    {
+        if (!depth_) return;
+        std::vector<float> tmp(width_ * height_, d);
+        detail::check(vsb_device_copy(depth_, tmp.data(), tmp.size() * sizeof(float), VSB_MEM_DEVICE, VSB_MEM_HOST), "vsb_device_copy");
+    }
+    void download_depth(float* dst) const
+    {
+        detail::check(vsb_device_copy(dst, depth_, width_ * height_ * sizeof(float), VSB_MEM_HOST, VSB_MEM_DEVICE), "vsb_device_copy");
+    }
     void clear_color_buffer(vec4 const& c = vec4(0.0f))
     {
         std::vector<vec4> tmp(width_ * height_, c);
@@ -442,6 +509,13 @@ public:
         detail::check(vsb_device_alloc(w * h * sizeof(vec4), &p), "vsb_device_alloc");
         color_ = static_cast<vec4*>(p);
         clear_color_buffer();
+        if (depth_) { vsb_device_free(depth_); depth_ = nullptr; }
+        if (DF == PF_DEPTH32F)
+        {
+            detail::check(vsb_device_alloc(w * h * sizeof(float), &p), "vsb_device_alloc");
+            depth_ = static_cast<float*>(p);
+            clear_depth_buffer(0.0f);
+        }
     }
     size_t width() const { return width_; }
     size_t height() const { return height_; }
@@ -452,6 +526,7 @@ public:
     }
 private:
     vec4* color_ = nullptr;
+    float* depth_ = nullptr;
     size_t width_ = 0, height_ = 0;
 };
 
@@ -485,8 +560,7 @@ public:
         d.p.kernel = K::id;
         d.p.pixel_sampler = SP::pixel_sampler_type::id;
         d.p.width = int(sparams.rt.width()); d.p.height = int(sparams.rt.height());
-        for (int i = 0; i < 3; ++i) { d.p.eye[i] = sparams.cam.eye()[i]; d.p.center[i] = sparams.cam.center()[i]; d.p.up[i] = sparams.cam.up()[i]; }
-        d.p.fovy = sparams.cam.fovy(); d.p.aspect = sparams.cam.aspect();
+        set_camera(d, sparams);
         // jittered_blend: alpha = 1 / frame_num (detail/sched_common.h:516-528); the reference's
         // callers count frames from 1 there
         d.p.frame_num = frame_num; d.p.seed = seed_;
@@ -498,13 +572,15 @@ public:
         std::vector<vsb_point_light> lights;
         for (auto l = kp.lights_begin; l != kp.lights_end; ++l) lights.push_back(l->flatten());
         d.p.n_materials = int(mats.size()); d.p.n_lights = int(lights.size());
-        detail::check(vsb_camera_basis(&d), "vsb_camera_basis");
+        if (d.camera_kind == VSB_CAM_BASIS) detail::check(vsb_camera_basis(&d), "vsb_camera_basis");
         d.scissor[0] = sparams.scissor_box.x; d.scissor[1] = sparams.scissor_box.y;
         d.scissor[2] = sparams.scissor_box.w; d.scissor[3] = sparams.scissor_box.h;
         d.normals = reinterpret_cast<float const*>(kp.normals);
         d.materials = mats.data(); d.lights = lights.data();
         d.params_mem = VSB_MEM_HOST;
-        d.color = sparams.rt.color(); d.mem = std::remove_reference<decltype(sparams.rt)>::type::memory;
+        d.color = sparams.rt.color();
+        d.depth = d.camera_kind == VSB_CAM_MATRIX ? sparams.rt.depth() : nullptr;   // the reference's depth path needs the matrices
+        d.mem = std::remove_reference<decltype(sparams.rt)>::type::memory;
         d.traverse = traverse_;
         d.tile_rank = tile_rank_; d.tile_nranks = tile_nranks_;
 
@@ -516,6 +592,17 @@ public:
     }
 
 private:
+    template <typename RT, typename PS> static void set_camera(vsb_frame_desc& d, sched_params<RT, PS> const& sp)
+    {
+        for (int i = 0; i < 3; ++i) { d.p.eye[i] = sp.cam.eye()[i]; d.p.center[i] = sp.cam.center()[i]; d.p.up[i] = sp.cam.up()[i]; }
+        d.p.fovy = sp.cam.fovy(); d.p.aspect = sp.cam.aspect();
+        d.camera_kind = VSB_CAM_BASIS;
+    }
+    template <typename RT, typename PS> static void set_camera(vsb_frame_desc& d, sched_params_matrix<RT, PS> const& sp)
+    {
+        d.camera_kind = VSB_CAM_MATRIX;
+        std::memcpy(d.view_matrix, sp.view_matrix.data(), 64); std::memcpy(d.proj_matrix, sp.proj_matrix.data(), 64);
+    }
     template <typename K> static void set_ao(vsb_frame_desc&, K const&) {}
     template <typename KP> static void set_ao(vsb_frame_desc& d, ao::kernel<KP> const& k) { d.p.ao_samples = k.num_samples; d.p.ao_radius = k.radius; }
 

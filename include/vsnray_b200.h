@@ -127,6 +127,8 @@ typedef struct vsb_frame_params {
     int32_t  n_lights, n_materials;
 } vsb_frame_params;
 
+enum { VSB_CAM_BASIS = 0, VSB_CAM_MATRIX = 1 };
+
 typedef struct vsb_frame_desc {
     vsb_frame_params p;
     /* camera basis as cuda_sched_impl_frame computes it on the host
@@ -139,7 +141,11 @@ typedef struct vsb_frame_desc {
     const vsb_material*    materials;    /* indexed by geom_id */
     const vsb_point_light* lights;
     void*    color;                      /* PF_RGBA32F, buffer[y*width+x] (pixel_access.h:38-58) */
-    void*    depth;                      /* reserved (PF_DEPTH32F); may be NULL */
+    void*    depth;                      /* PF_DEPTH32F, buffer[y*width+x], same memory (and tile layout) as color;
+                                            may be NULL.  depth = hit ? ((proj*view*isect_pos).z/w + 1)/2 : 1
+                                            (depth_transform, detail/sched_common.h:337-354,425); needs
+                                            camera_kind = VSB_CAM_MATRIX like the reference, whose depth
+                                            transform only exists for matrix sched_params */
     int32_t  mem;                        /* VSB_MEM_*: where color / ray_count live (the render target) */
     int32_t  traverse;                   /* VSB_TRAVERSE_* */
     /* image-space tile partition for multi-GPU (64x64 tiles, tile k -> rank k % nranks);
@@ -153,6 +159,12 @@ typedef struct vsb_frame_desc {
                                             `color` is the whole row-major frame (width*height pixels), e.g. a peer
                                             GPU's buffer opened with vsb_ipc_open(): the rank's tiles are stored
                                             straight into it over NVLink, no gather pass (device memory, no blend) */
+    /* sched_params built from matrices instead of a camera (make_sched_params(view, proj, rt),
+     * scheduler.h:60-96,205-242): rays come from the inverse matrices (detail/sched_common.h:152-178;
+     * the inverses are computed per frame on the host like detail/cuda_sched.inl:231-234).
+     * matrix<4,4,float> layout: 16 floats, column-major. */
+    int32_t  camera_kind;                /* VSB_CAM_BASIS (cam_eye/u/v/w above) or VSB_CAM_MATRIX */
+    float    view_matrix[16], proj_matrix[16];
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;

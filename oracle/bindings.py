@@ -52,6 +52,8 @@ def oracle_lib():
         lib.vso_query_brute.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, C.c_float, vp, C.c_int]
         lib.vso_frame.argtypes = [vp, C.POINTER(Bvh), vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
         lib.vso_camera_basis.argtypes = [vp, vp, vp, vp, vp]
+        lib.vso_frame_matrix.argtypes = [vp, vp, vp, C.POINTER(Bvh), vp, vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
+        lib.vso_mat4_inverse.argtypes = [vp, vp]
         lib.vso_bvh_max_depth.argtypes = [C.POINTER(Bvh)]
         lib.vso_sampler_init.restype = C.c_uint32
         lib.vso_sampler_init.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
@@ -77,6 +79,8 @@ def ref_lib(fast: bool = False):
         lib.ref_query.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, vp, vp, C.c_int]
         lib.ref_frame.restype = C.c_double
         lib.ref_frame.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
+        lib.ref_frame_matrix.argtypes = [vp, vp, vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, vp, C.c_int, vp]
+        lib.ref_camera_matrices.argtypes = [vp, C.c_float, C.c_float, vp, vp]
         lib.ref_query_timed.restype = C.c_double
         lib.ref_query_timed.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int,
                                         C.POINTER(C.c_uint64)]
@@ -125,6 +129,29 @@ def oracle_frame(scene, fp, materials, lights, rgba=None, nthreads=0, counters=N
     return rgba
 
 
+def oracle_frame_matrix(scene, fp, view, proj, materials, lights, rgba=None, depth=None, want_depth=True, nthreads=0):
+    """vso_frame_matrix: sched_params with view / proj matrices (16 floats, column-major); returns (rgba, depth)."""
+    w, h = fp.width, fp.height
+    if rgba is None:
+        rgba = np.zeros((h, w, 4), dtype=np.float32)
+    if depth is None and want_depth:
+        depth = np.zeros((h, w), dtype=np.float32)
+    view = np.ascontiguousarray(view, dtype=np.float32).reshape(16)
+    proj = np.ascontiguousarray(proj, dtype=np.float32).reshape(16)
+    b = make_bvh(scene)
+    c = Counters()
+    oracle_lib().vso_frame_matrix(C.byref(fp), _p(view), _p(proj), C.byref(b), _p(scene.normals), _p(materials),
+                                  _p(lights), _p(rgba), _p(depth), C.byref(c), nthreads or (os.cpu_count() or 1))
+    return rgba, depth
+
+
+def oracle_mat4_inverse(m):
+    m = np.ascontiguousarray(m, dtype=np.float32).reshape(16)
+    out = np.zeros(16, dtype=np.float32)
+    oracle_lib().vso_mat4_inverse(_p(m), _p(out))
+    return out
+
+
 def oracle_max_depth(scene) -> int:
     b = make_bvh(scene)
     return int(oracle_lib().vso_bvh_max_depth(C.byref(b)))
@@ -163,6 +190,30 @@ def ref_frame(scene, fp, materials, lights, rgba=None, nthreads=0, mode=0, reps=
                                    _p(materials), _p(lights), _p(rgba), nthreads or (os.cpu_count() or 1), mode, reps,
                                    warmup, _p(basis))
     return rgba, secs, basis
+
+
+def ref_frame_matrix(scene, fp, view, proj, materials, lights, rgba=None, depth=None, want_depth=True, nthreads=0):
+    """Scalar parity driver of the reference headers with matrix sched_params; returns (rgba, depth, inverses[32])."""
+    w, h = fp.width, fp.height
+    if rgba is None:
+        rgba = np.zeros((h, w, 4), dtype=np.float32)
+    if depth is None and want_depth:
+        depth = np.zeros((h, w), dtype=np.float32)
+    view = np.ascontiguousarray(view, dtype=np.float32).reshape(16)
+    proj = np.ascontiguousarray(proj, dtype=np.float32).reshape(16)
+    inv = np.zeros(32, dtype=np.float32)
+    ref_lib().ref_frame_matrix(C.byref(fp), _p(view), _p(proj), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes),
+                               scene.nodes.shape[0], _p(scene.indices), scene.indices.shape[0], _p(scene.normals),
+                               _p(materials), _p(lights), _p(rgba), _p(depth), nthreads or (os.cpu_count() or 1), _p(inv))
+    return rgba, depth, inv
+
+
+def ref_camera_matrices(fp, z_near=0.001, z_far=1000.0):
+    """The reference camera's view / projection matrices for fp's look_at + perspective."""
+    view = np.zeros(16, dtype=np.float32)
+    proj = np.zeros(16, dtype=np.float32)
+    ref_lib().ref_camera_matrices(C.byref(fp), z_near, z_far, _p(view), _p(proj))
+    return view, proj
 
 
 def ref_query_timed(scene, rays, any_hit=False, max_t=3.4028234663852886e38, nthreads=0, reps=1, warmup=0):

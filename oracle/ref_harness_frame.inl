@@ -132,9 +132,14 @@ struct no_sampler_adapter
 };
 
 // Scalar per-pixel driver with the deterministic sampler: the PARITY frame oracle.
+// matrix camera + depth target of the next scalar_frame() call (ref_frame_matrix sets them)
+struct matrix_cam { bool on = false; mat4 view, inv_view, proj, inv_proj; float* depth = nullptr; };
+static matrix_cam g_mcam;
+
 template <typename K>
 void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, float* basis_out)
 {
+    matrix_cam const mc = g_mcam;
     auto cam = make_cam(fp);
     // host-side basis, as the reference schedulers compute it (detail/tiled_sched.inl:296-304)
     auto f = normalize(cam.eye() - cam.center());
@@ -164,13 +169,39 @@ void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, f
                 // make_primary_rays(ssaa_type<N>) (detail/sched_common.h:222-295), then clear +
                 // N x blend(src / N + dst) (detail/sched_common.h:640-698)
                 vec4 acc(0.0f);
+                float zacc = 0.0f;
                 auto run = [&](ray_t const& r, float alpha)
                 {
                     auto res = kernel(r, samp);
                     acc = res.color * alpha + acc * 1.0f;
+                    if (mc.on)
+                    {
+                        float z = res.hit ? detail::depth_transform(res.isect_pos, mc.view, mc.inv_view, mc.proj, mc.inv_proj) : 1.0f;
+                        zacc = z * alpha + zacc * 1.0f;
+                    }
                 };
                 random_sampler<float> unused;
-                if (fp.pixel_sampler == 3)
+                if (mc.on)
+                {
+                    // the same generators with the matrix argument pack (detail/sched_common.h:152-178)
+                    if (fp.pixel_sampler == 3)
+                    {
+                        auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<2>{}, unused, x, y, w, h, mc.view, mc.inv_view, mc.proj, mc.inv_proj);
+                        for (auto const& r : rays) run(r, 1.0f / 2.0f);
+                    }
+                    else if (fp.pixel_sampler == 4)
+                    {
+                        auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<4>{}, unused, x, y, w, h, mc.view, mc.inv_view, mc.proj, mc.inv_proj);
+                        for (auto const& r : rays) run(r, 1.0f / 4.0f);
+                    }
+                    else
+                    {
+                        auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<8>{}, unused, x, y, w, h, mc.view, mc.inv_view, mc.proj, mc.inv_proj);
+                        for (auto const& r : rays) run(r, 1.0f / 8.0f);
+                    }
+                    if (mc.depth) mc.depth[i] = zacc;
+                }
+                else if (fp.pixel_sampler == 3)
                 {
                     auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<2>{}, unused, x, y, w, h, eye, cam_u, cam_v, cam_w);
                     for (auto const& r : rays) run(r, 1.0f / 2.0f);
@@ -195,9 +226,21 @@ void scalar_frame(K kernel, frame_params const& fp, float* rgba, int nthreads, f
                 float jy = samp.next() - 0.5f;
                 px += jx; py += jy;
             }
-            ray_t r = detail::make_primary_ray_impl<ray_t>(px, py, w, h, eye, cam_u, cam_v, cam_w);
+            ray_t r = mc.on ? detail::make_primary_ray_impl<ray_t>(px, py, w, h, mc.view, mc.inv_view, mc.proj, mc.inv_proj)
+                            : detail::make_primary_ray_impl<ray_t>(px, py, w, h, eye, cam_u, cam_v, cam_w);
             auto res = kernel(r, samp);
             vec4 c = res.color;
+            if (mc.on && mc.depth)
+            {
+                // result.depth (detail/sched_common.h:425, :559), stored or blended with the colour
+                float z = res.hit ? detail::depth_transform(res.isect_pos, mc.view, mc.inv_view, mc.proj, mc.inv_proj) : 1.0f;
+                if (fp.pixel_sampler == 2)
+                {
+                    float alpha = 1.0f / float(fp.frame_num);
+                    mc.depth[i] = z * alpha + mc.depth[i] * (1.0f - alpha);
+                }
+                else mc.depth[i] = z;
+            }
             if (fp.pixel_sampler == 2)
             {
                 // jittered_blend: detail/sched_common.h:516-528
@@ -362,6 +405,38 @@ double ref_frame(void const* fp_, void const* prims, size_t n_prims, void const*
     }
     return run(make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(),
                                   s.plastics.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb));
+}
+
+// scalar parity driver with sched_params-style view / projection matrices (column-major 16 floats)
+// and an optional PF_DEPTH32F target; the inverses are the reference's inverse() like the
+// schedulers compute them (detail/tiled_sched.inl:241-242).  inv_out (32 floats) may be NULL.
+void ref_frame_matrix(void const* fp_, float const* view16, float const* proj16, void const* prims, size_t n_prims,
+                      void const* nodes, size_t n_nodes, uint32_t const* indices, size_t n_idx, float const* normals16,
+                      void const* mats_, void const* lights_, float* rgba, float* depth, int nthreads, float* inv_out)
+{
+    g_mcam.on = true;
+    g_mcam.view = mat4(view16); g_mcam.proj = mat4(proj16);
+    g_mcam.inv_view = inverse(g_mcam.view); g_mcam.inv_proj = inverse(g_mcam.proj);
+    g_mcam.depth = depth;
+    if (inv_out)
+    {
+        std::memcpy(inv_out, g_mcam.inv_view.data(), 64);
+        std::memcpy(inv_out + 16, g_mcam.inv_proj.data(), 64);
+    }
+    ref_frame(fp_, prims, n_prims, nodes, n_nodes, indices, n_idx, normals16, mats_, lights_, rgba, nthreads, 0, 1, 0, nullptr);
+    g_mcam = matrix_cam();
+}
+
+// the reference camera's matrices for a frame_params view (detail/camera.inl:10-65), 2 x 16 floats
+void ref_camera_matrices(void const* fp_, float z_near, float z_far, float* view16, float* proj16)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    camera cam;
+    cam.look_at(vec3(fp.eye[0], fp.eye[1], fp.eye[2]), vec3(fp.center[0], fp.center[1], fp.center[2]), vec3(fp.up[0], fp.up[1], fp.up[2]));
+    cam.perspective(fp.fovy, fp.aspect, z_near, z_far);
+    std::memcpy(view16, cam.get_view_matrix().data(), 64);
+    std::memcpy(proj16, cam.get_proj_matrix().data(), 64);
 }
 
 // Timed ray-list baseline: simd::ray8 packets of 8 consecutive rays, all threads.

@@ -96,6 +96,23 @@ void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals
                const vso_material* mats, const vso_point_light* lights, float* rgba,
                vso_counters* counters, int nthreads);
 
+/* matrix camera (sched_params with view_matrix / proj_matrix, scheduler.h:60-96) and the depth
+ * buffer it enables.  Matrices are the reference's matrix<4,4,float>: 16 floats, column-major.
+ *   vso_mat4_inverse      -- math/detail/matrix4.inl:209-244
+ *   vso_primary_ray_matrix -- detail/sched_common.h:152-178
+ *   vso_depth_transform    -- detail/sched_common.h:337-354
+ *   vso_frame_matrix       -- vso_frame() with that camera; depth (width*height floats) may be
+ *                             NULL.  depth = hit ? transform(isect_pos) : 1 (:425), stored /
+ *                             blended / SSAA-accumulated like the colour (:559-575, :713-765) */
+void  vso_mat4_inverse(const float m[16], float out[16]);
+void  vso_primary_ray_matrix(float x, float y, int width, int height, const float inv_view[16],
+                             const float inv_proj[16], vso_ray* out);
+float vso_depth_transform(const float pos[3], const float view[16], const float proj[16]);
+void  vso_frame_matrix(const vso_frame_params* p, const float view[16], const float proj[16],
+                       const vso_bvh* b, const float* normals16, const vso_material* mats,
+                       const vso_point_light* lights, float* rgba, float* depth,
+                       vso_counters* counters, int nthreads);
+
 /* max depth of the BVH2 (root = depth 1); the reference's traversal stack holds 31 entries
  * (detail/stack.h:39-47, detail/bvh/intersect.inl:60) */
 int vso_bvh_max_depth(const vso_bvh* b);

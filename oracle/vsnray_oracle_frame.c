@@ -53,6 +53,9 @@ typedef struct
     const vso_point_light* lights;
     float* rgba;
     float eye[3], cu[3], cv[3], cw[3];
+    int use_matrix;                       /* sched_params carries view / proj matrices */
+    float view[16], inv_view[16], proj[16], inv_proj[16];
+    float* depth;                         /* PF_DEPTH32F target or NULL */
 } frame_ctx;
 
 static void closest(const frame_ctx* f, v3 o, v3 d, vso_hit* h, vso_counters* c)
@@ -310,12 +313,103 @@ static void ssaa_offset(int num, int k, float* dx, float* dy)
     else { *dx = o8x[k]; *dy = o8y[k]; }
 }
 
-static void run_kernel(const frame_ctx* f, float px, float py, uint32_t* samp, float col[4], vso_counters* c)
+/* ---- matrix camera ---------------------------------------------------------------------- */
+
+#define M(m, r, c) ((m)[(c) * 4 + (r)])      /* matrix<4,4,T>::operator()(row, col), column-major */
+static float det2(float m00, float m01, float m10, float m11) { return m00 * m11 - m10 * m01; }   /* math/detail/math.h det2 */
+
+/* inverse(matrix<4,4,T>) -- math/detail/matrix4.inl:209-244 */
+void vso_mat4_inverse(const float m[16], float out[16])
+{
+    float s0 = det2(M(m,0,0), M(m,0,1), M(m,1,0), M(m,1,1));
+    float s1 = det2(M(m,0,0), M(m,0,2), M(m,1,0), M(m,1,2));
+    float s2 = det2(M(m,0,0), M(m,0,3), M(m,1,0), M(m,1,3));
+    float s3 = det2(M(m,0,1), M(m,0,2), M(m,1,1), M(m,1,2));
+    float s4 = det2(M(m,0,1), M(m,0,3), M(m,1,1), M(m,1,3));
+    float s5 = det2(M(m,0,2), M(m,0,3), M(m,1,2), M(m,1,3));
+    float c5 = det2(M(m,2,2), M(m,2,3), M(m,3,2), M(m,3,3));
+    float c4 = det2(M(m,2,1), M(m,2,3), M(m,3,1), M(m,3,3));
+    float c3 = det2(M(m,2,1), M(m,2,2), M(m,3,1), M(m,3,2));
+    float c2 = det2(M(m,2,0), M(m,2,3), M(m,3,0), M(m,3,3));
+    float c1 = det2(M(m,2,0), M(m,2,2), M(m,3,0), M(m,3,2));
+    float c0 = det2(M(m,2,0), M(m,2,1), M(m,3,0), M(m,3,1));
+    float det = s0 * c5 - s1 * c4 + s2 * c3 + s3 * c2 - s4 * c1 + s5 * c0;
+    /* the 16-scalar constructor takes the values column by column (matrix4.inl:28-39) */
+    out[0]  = (+ M(m,1,1) * c5 - M(m,1,2) * c4 + M(m,1,3) * c3) / det;
+    out[1]  = (- M(m,1,0) * c5 + M(m,1,2) * c2 + M(m,1,3) * c1) / det;
+    out[2]  = (+ M(m,1,0) * c4 - M(m,1,1) * c2 + M(m,1,3) * c0) / det;
+    out[3]  = (- M(m,1,0) * c3 + M(m,1,1) * c1 + M(m,1,2) * c0) / det;
+    out[4]  = (- M(m,0,1) * c5 + M(m,0,2) * c4 - M(m,0,3) * c3) / det;
+    out[5]  = (+ M(m,0,0) * c5 - M(m,0,2) * c2 + M(m,0,3) * c1) / det;
+    out[6]  = (- M(m,0,0) * c4 + M(m,0,1) * c2 - M(m,0,3) * c0) / det;
+    out[7]  = (+ M(m,0,0) * c3 - M(m,0,1) * c1 + M(m,0,2) * c0) / det;
+    out[8]  = (+ M(m,3,1) * s5 - M(m,3,2) * s4 + M(m,3,3) * s3) / det;
+    out[9]  = (- M(m,3,0) * s5 + M(m,3,2) * s2 - M(m,3,3) * s1) / det;
+    out[10] = (+ M(m,3,0) * s4 - M(m,3,1) * s2 + M(m,3,3) * s0) / det;
+    out[11] = (- M(m,3,0) * s3 + M(m,3,1) * s1 - M(m,3,2) * s0) / det;
+    out[12] = (- M(m,2,1) * s5 + M(m,2,2) * s4 - M(m,2,3) * s3) / det;
+    out[13] = (+ M(m,2,0) * s5 - M(m,2,2) * s2 + M(m,2,3) * s1) / det;
+    out[14] = (- M(m,2,0) * s4 + M(m,2,1) * s2 - M(m,2,3) * s0) / det;
+    out[15] = (+ M(m,2,0) * s3 - M(m,2,1) * s1 + M(m,2,2) * s0) / det;
+}
+
+/* matrix * vector<4> -- math/detail/matrix4.inl:171-181 */
+static void mat4_mul(const float m[16], const float v[4], float out[4])
+{
+    for (int r = 0; r < 4; ++r) out[r] = M(m,r,0) * v[0] + M(m,r,1) * v[1] + M(m,r,2) * v[2] + M(m,r,3) * v[3];
+}
+
+/* make_primary_ray_impl, matrix overload -- detail/sched_common.h:152-178 */
+void vso_primary_ray_matrix(float x, float y, int width, int height, const float inv_view[16],
+                            const float inv_proj[16], vso_ray* out)
+{
+    float u = 2.0f * (x + 0.5f) / (float)width - 1.0f;
+    float v = 2.0f * (y + 0.5f) / (float)height - 1.0f;
+    float n4[4] = { u, v, -1.0f, 1.0f }, f4[4] = { u, v, 1.0f, 1.0f }, t[4], o[4], d[4];
+    mat4_mul(inv_proj, n4, t); mat4_mul(inv_view, t, o);
+    mat4_mul(inv_proj, f4, t); mat4_mul(inv_view, t, d);
+    v3 ori = v3m(o[0] / o[3], o[1] / o[3], o[2] / o[3]);
+    v3 dir = normalize(sub(v3m(d[0] / d[3], d[1] / d[3], d[2] / d[3]), ori));
+    memset(out, 0, sizeof(*out));
+    out->ori[0] = ori.x; out->ori[1] = ori.y; out->ori[2] = ori.z;
+    out->dir[0] = dir.x; out->dir[1] = dir.y; out->dir[2] = dir.z;
+}
+
+/* depth_transform -- detail/sched_common.h:337-354 */
+float vso_depth_transform(const float pos[3], const float view[16], const float proj[16])
+{
+    float p4[4] = { pos[0], pos[1], pos[2], 1.0f }, t[4], q[4];
+    mat4_mul(view, p4, t); mat4_mul(proj, t, q);
+    return (q[2] / q[3] + 1.0f) * 0.5f;
+}
+#undef M
+
+/* One kernel invocation for the sample at (px, py).  *depth (matrix camera only) receives
+ * result.depth = hit ? depth_transform(isect_pos) : 1 (detail/sched_common.h:425): every built-in
+ * kernel reports the PRIMARY hit and its position (simple.inl:38,66; whitted.inl:241;
+ * pathtracing.inl:68; ao/main.cpp:198-199), so it is evaluated from the primary ray alone. */
+static void run_kernel(const frame_ctx* f, float px, float py, uint32_t* samp, float col[4], float* depth, vso_counters* c)
 {
     const vso_frame_params* p = f->p;
     vso_ray r;
-    vso_primary_ray(px, py, p->width, p->height, f->eye, f->cu, f->cv, f->cw, &r);
+    if (f->use_matrix) vso_primary_ray_matrix(px, py, p->width, p->height, f->inv_view, f->inv_proj, &r);
+    else vso_primary_ray(px, py, p->width, p->height, f->eye, f->cu, f->cv, f->cw, &r);
     v3 o = ld3(r.ori), d = ld3(r.dir);
+    if (depth)
+    {
+        vso_hit h; vso_counters unused = { 0, 0, 0, 0 };
+        *depth = 1.0f;
+        if (!(p->kernel == 3 && p->num_bounces == 0u))
+        {
+            closest(f, o, d, &h, &unused);
+            if (h.hit)
+            {
+                v3 pos = add(o, scale(d, h.t));
+                float pp[3] = { pos.x, pos.y, pos.z };
+                *depth = vso_depth_transform(pp, f->view, f->proj);
+            }
+        }
+    }
     switch (p->kernel)
     {
     case 0: kernel_simple(f, o, d, col, c); break;
@@ -335,19 +429,23 @@ static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
         uint32_t samp = vso_sampler_init((uint32_t)i, p->frame_num, p->seed);
         float px = (float)x, py = (float)y;
         float* dst = f->rgba + i * 4;
-        float col[4];
+        float* zdst = f->depth ? f->depth + i : NULL;
+        float col[4], z = 0.0f;
+        float* zp = zdst ? &z : NULL;
         if (p->pixel_sampler >= 3)
         {
             /* ssaa_type<N>: clear, then N x blend(src / N + dst): detail/sched_common.h:640-698 */
             const int num = 2 << (p->pixel_sampler - 3);
             const float alpha = 1.0f / (float)num;
             for (int k = 0; k < 4; ++k) dst[k] = 0.0f;
+            if (zdst) *zdst = 0.0f;
             for (int s = 0; s < num; ++s)
             {
                 float dx, dy;
                 ssaa_offset(num, s, &dx, &dy);
-                run_kernel(f, px + dx, py + dy, &samp, col, c);
+                run_kernel(f, px + dx, py + dy, &samp, col, zp, c);
                 for (int k = 0; k < 4; ++k) dst[k] = col[k] * alpha + dst[k] * 1.0f;
+                if (zdst) *zdst = z * alpha + *zdst * 1.0f;
             }
             continue;
         }
@@ -358,17 +456,19 @@ static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
             float jy = vso_sampler_next(&samp) - 0.5f;
             px += jx; py += jy;
         }
-        run_kernel(f, px, py, &samp, col, c);
+        run_kernel(f, px, py, &samp, col, zp, c);
         if (p->pixel_sampler == 2)
         {
-            /* jittered_blend: detail/sched_common.h:516-528 */
+            /* jittered_blend: detail/sched_common.h:516-528 (with depth: :559-575) */
             float alpha = 1.0f / (float)p->frame_num;
             for (int k = 0; k < 4; ++k) dst[k] = col[k] * alpha + dst[k] * (1.0f - alpha);
+            if (zdst) *zdst = z * alpha + *zdst * (1.0f - alpha);
         }
         else
         {
-            /* uniform / jittered store: detail/pixel_access.h:38-58 */
+            /* uniform / jittered store: detail/pixel_access.h:38-58, :608-658 */
             for (int k = 0; k < 4; ++k) dst[k] = col[k];
+            if (zdst) *zdst = z;
         }
     }
 }
@@ -391,6 +491,8 @@ static void* fworker_main(void* q)
     return NULL;
 }
 
+static void frame_run(frame_ctx* fp, vso_counters* counters, int nthreads);
+
 void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals16,
                const vso_material* mats, const vso_point_light* lights, float* rgba,
                vso_counters* counters, int nthreads)
@@ -399,6 +501,29 @@ void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals
     memset(&f, 0, sizeof(f));
     f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights; f.rgba = rgba;
     vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
+    frame_run(&f, counters, nthreads);
+}
+
+/* the scheduler computes both inverses on the host each frame (detail/tiled_sched.inl:241-242,
+ * detail/cuda_sched.inl:231-234) */
+void vso_frame_matrix(const vso_frame_params* p, const float view[16], const float proj[16],
+                      const vso_bvh* b, const float* normals16, const vso_material* mats,
+                      const vso_point_light* lights, float* rgba, float* depth,
+                      vso_counters* counters, int nthreads)
+{
+    frame_ctx f;
+    memset(&f, 0, sizeof(f));
+    f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights; f.rgba = rgba;
+    f.use_matrix = 1; f.depth = depth;
+    memcpy(f.view, view, 64); memcpy(f.proj, proj, 64);
+    vso_mat4_inverse(view, f.inv_view); vso_mat4_inverse(proj, f.inv_proj);
+    frame_run(&f, counters, nthreads);
+}
+
+static void frame_run(frame_ctx* fp, vso_counters* counters, int nthreads)
+{
+    frame_ctx f = *fp;
+    const vso_frame_params* p = f.p;
     if (nthreads < 1) nthreads = 1;
     if (nthreads > 256) nthreads = 256;
     size_t n = (size_t)p->width * (size_t)p->height, next = 0;

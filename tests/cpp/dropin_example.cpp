@@ -111,6 +111,25 @@ int main(int argc, char** argv)
         for (unsigned frame_num = 1; frame_num <= 3; ++frame_num) sched.frame(pt, sp2, frame_num);
         dump(out + "/frame_pt.bin", host_rt.color(), size_t(w) * h);
 
+        // --- sched_params from the camera's matrices + a depth buffer (the form GL compositing uses):
+        //     SSAA 4x Whitted into RGBA32F + DEPTH32F, host and device targets ---
+        pinhole_camera cam2;
+        cam2.look_at(vec3(0.0f, 0.0f, 3.0f), vec3(0.0f), vec3(0.0f, 1.0f, 0.0f));
+        cam2.perspective(45.0f * 3.14159265358979323846f / 180.0f, float(w) / float(h), 0.1f, 10.0f);
+        simple_buffer_rt<PF_RGBA32F, PF_DEPTH32F> depth_rt;
+        depth_rt.resize(w, h);
+        auto sp3 = make_sched_params(pixel_sampler::ssaa_type<4>{}, cam2.get_view_matrix(), cam2.get_proj_matrix(), depth_rt);
+        sched.frame(kernel, sp3);
+        dump(out + "/frame_matrix_color.bin", depth_rt.color(), size_t(w) * h);
+        dump(out + "/frame_matrix_depth.bin", depth_rt.depth(), size_t(w) * h);
+        gpu_buffer_rt<PF_RGBA32F, PF_DEPTH32F> dev_depth_rt;
+        dev_depth_rt.resize(w, h);
+        auto sp4 = make_sched_params(pixel_sampler::ssaa_type<4>{}, cam2.get_view_matrix(), cam2.get_proj_matrix(), dev_depth_rt);
+        sched.frame(kernel, sp4);
+        std::vector<float> zback(size_t(w) * h);
+        dev_depth_rt.download_depth(zback.data());
+        if (std::memcmp(zback.data(), depth_rt.depth(), zback.size() * sizeof(float)) != 0) { std::cerr << "gpu depth != host depth\n"; return 2; }
+
         std::printf("dropin_example ok: %zu triangles, %zu nodes, %zu rays\n", tris.size(), bvh.num_nodes(), rays.size());
         return 0;
     }

@@ -45,6 +45,12 @@ def main():
     # ssaa_type<4> through the reference's own tiled_sched<simd::ray8> (RNG-free kernel)
     fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=4)
     frames["k1_ssaa4"], _, _ = O.ref_frame(sc, fp, S.default_material(0), S.point_light(eye), mode=1)
+    # sched_params from view / projection matrices + depth buffer (scalar driver over the reference's
+    # make_primary_ray_impl(matrices) / depth_transform); the matrices are the reference camera's
+    fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=3)
+    view, proj = O.ref_camera_matrices(fp, 0.1, 10.0)
+    frames["matrix_view"], frames["matrix_proj"] = view, proj
+    frames["k1_matrix_ssaa2"], frames["k1_matrix_ssaa2_depth"], _ = O.ref_frame_matrix(sc, fp, view, proj, S.default_material(0), S.point_light(eye))
     np.savez_compressed(os.path.join(HERE, "golden_frames.npz"), **frames)
     print("wrote golden_queries.npz, golden_frames.npz")
 

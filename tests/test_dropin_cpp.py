@@ -58,3 +58,11 @@ def test_dropin_program_matches_oracle(gpu):
             O.oracle_frame(sc, fp, S.default_material(1), S.point_light(eye), rgba=acc)
         pt = np.fromfile(os.path.join(d, "frame_pt.bin"), dtype=np.float32).reshape(120, 160, 4)
         assert float((np.abs(pt - acc).max(axis=2) > 1 / 255).mean()) <= 5e-3
+        # matrix sched_params + depth buffer, ssaa_type<4>: the adaptor's camera matrices are the reference camera's
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), pixel_sampler=4, num_bounces=4)
+        view, proj = S.camera_matrices(fp, 0.1, 10.0)
+        want_c, want_z = O.oracle_frame_matrix(sc, fp, view, proj, S.default_material(0), S.point_light(eye))
+        mc = np.fromfile(os.path.join(d, "frame_matrix_color.bin"), dtype=np.float32).reshape(120, 160, 4)
+        mz = np.fromfile(os.path.join(d, "frame_matrix_depth.bin"), dtype=np.float32).reshape(120, 160)
+        assert float((np.abs(mc - want_c).max(axis=2) > 1 / 255).mean()) <= 2e-4
+        assert float(np.abs(mz - want_z).max()) <= 1e-5

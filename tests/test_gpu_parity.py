@@ -245,6 +245,53 @@ def test_progressive_blend_accumulates(gpu, scenes):
     assert float((diff > 1.0 / 255.0).mean()) <= 5e-3
 
 
+@pytest.mark.parametrize("kernel,ps,mat", [(0, 0, 0), (1, 0, 0), (2, 0, 0), (3, 2, 1), (1, 4, 0), (0, 1, 0), (3, 3, 1)])
+def test_matrix_camera_and_depth_target(gpu, scenes, kernel, ps, mat):
+    """sched_params built from view / projection matrices + PF_DEPTH32F target
+    (detail/sched_common.h:152-178,337-354,425): colours within 1/255, depth within 1e-5, for a
+    host render target and a device render target, both traversals."""
+    import torch
+
+    sc, dev = scenes("cfg2_grid", 0.05)
+    eye = (0.3, 1.2, 2.2)
+    w, h = 256, 192
+    amb = (1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0)
+    mats, lights = S.default_material(mat), S.point_light(eye)
+    view, proj = S.camera_matrices(S.frame_params(kernel, w, h, eye, (0, 0, 0)), 0.1, 10.0)
+    frames = (1, 2, 3) if ps == 2 else (1,)
+    want = wz = None
+    for frame_num in frames:
+        fp = S.frame_params(kernel, w, h, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=amb, frame_num=frame_num)
+        want, wz = O.oracle_frame_matrix(sc, fp, view, proj, mats, lights, rgba=want, depth=wz)
+    for trav in (gpu.TRAVERSE_EXACT, gpu.TRAVERSE_WIDE):
+        img = np.zeros((h, w, 4), dtype=np.float32)
+        z = np.zeros((h, w), dtype=np.float32)
+        d_img = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        d_z = torch.zeros((h, w), dtype=torch.float32, device="cuda")
+        for frame_num in frames:
+            fp = S.frame_params(kernel, w, h, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=amb, frame_num=frame_num)
+            gpu.frame(dev, fp, sc.normals, mats, lights, img, traverse=trav, view_matrix=view, proj_matrix=proj, depth=z)
+            gpu.frame(dev, fp, sc.normals, mats, lights, d_img, traverse=trav, view_matrix=view, proj_matrix=proj, depth=d_z)
+        gpu.sync()
+        torch.cuda.synchronize()
+        assert d_img.cpu().numpy().tobytes() == img.tobytes() and d_z.cpu().numpy().tobytes() == z.tobytes()
+        diff = np.abs(img - want).max(axis=2)
+        limit = (0.0 if trav == gpu.TRAVERSE_EXACT else 2e-4) if kernel in (0, 1) else 2e-3
+        assert float((diff > 1.0 / 255.0).mean()) <= limit, (kernel, ps, trav, float(diff.max()))
+        # depth depends on the primary hit only: t is bit-identical for the same primitive and equal on exact ties
+        assert float(np.abs(z - wz).max()) <= 1e-5, (kernel, ps, trav)
+        assert z.max() == 1.0 and 0.5 < z.min() < 1.0
+    # colour only (no depth target) with the matrix camera
+    fp = S.frame_params(kernel, w, h, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=amb, frame_num=1)
+    img2 = np.zeros((h, w, 4), dtype=np.float32)
+    gpu.frame(dev, fp, sc.normals, mats, lights, img2, view_matrix=view, proj_matrix=proj)
+    want2, _ = O.oracle_frame_matrix(sc, fp, view, proj, mats, lights, want_depth=False)
+    assert float((np.abs(img2 - want2).max(axis=2) > 1.0 / 255.0).mean()) <= 2e-3
+    # the reference has no depth transform for camera-basis sched_params: refused, not ignored
+    with pytest.raises(RuntimeError):
+        gpu.frame(dev, fp, sc.normals, mats, lights, img2, depth=np.zeros((h, w), dtype=np.float32))
+
+
 def test_tile_partition_reassembles_the_frame(gpu, scenes):
     """Interleaved 64x64 tiles over 3 'ranks' rendered one after the other on one GPU, then
     de-interleaved: identical to the single-rank frame (what the NCCL all-gather feeds)."""

@@ -118,6 +118,55 @@ def test_oracle_ssaa_matches_reference(kernel, ps):
     assert np.abs(a - u).max() > 1e-3
 
 
+@pytest.mark.parametrize("kernel,ps", [(0, 0), (1, 0), (2, 0), (3, 2), (1, 4), (0, 1), (3, 3)])
+def test_oracle_matrix_camera_and_depth_match_reference(kernel, ps):
+    """sched_params with view / projection matrices (scheduler.h:60-96): primary rays from the
+    inverse matrices (detail/sched_common.h:152-178), depth = hit ? depth_transform(isect_pos) : 1
+    (:337-354, :425), stored / blended / SSAA-accumulated with the colour -- restatement against
+    the reference headers, including the reference's own inverse() of the camera matrices."""
+    if not O.ref_available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    sc = S.make_scene("cfg2_grid", 0.01)
+    eye = (0.3, 1.2, 2.2)
+    amb = (1, 1, 1, 1) if kernel == 3 else (0, 0, 0, 0)
+    mats, lights = S.default_material(1 if kernel == 3 else 0), S.point_light(eye)
+    view, proj = O.ref_camera_matrices(S.frame_params(kernel, 48, 40, eye, (0, 0, 0)), 0.1, 10.0)
+    a = d = b = e = None
+    for frame_num in ((1, 2, 3) if ps == 2 else (1,)):
+        fp = S.frame_params(kernel, 48, 40, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=amb, frame_num=frame_num)
+        a, d = O.oracle_frame_matrix(sc, fp, view, proj, mats, lights, rgba=a, depth=d)
+        b, e, inv = O.ref_frame_matrix(sc, fp, view, proj, mats, lights, rgba=b, depth=e)
+    assert O.oracle_mat4_inverse(view).tobytes() == inv[:16].tobytes()
+    assert O.oracle_mat4_inverse(proj).tobytes() == inv[16:].tobytes()
+    assert np.abs(a - b).max() <= 1e-6
+    assert np.abs(d - e).max() <= 1e-6
+    assert d.min() > 0.5 and d.max() == 1.0 and (d < 1.0).mean() > 0.2      # geometry in front of the far plane, sky at 1
+    # the matrix camera sees what the look_at / perspective camera sees (same view, other arithmetic)
+    if ps == 0:
+        c = O.oracle_frame(sc, S.frame_params(kernel, 48, 40, eye, (0, 0, 0), pixel_sampler=0, num_bounces=4, ambient=amb), mats, lights)
+        if kernel in (0, 1):
+            assert np.mean(np.abs(a - c).max(axis=2) <= 2.0 / 255.0) > 0.97
+    # no depth target: same colours
+    a2, none = O.oracle_frame_matrix(sc, S.frame_params(kernel, 48, 40, eye, (0, 0, 0), pixel_sampler=ps, num_bounces=4, ambient=amb),
+                                     view, proj, mats, lights, want_depth=False)
+    assert none is None
+    if ps != 2:
+        assert a2.tobytes() == a.tobytes()
+
+
+def test_host_camera_matrices_match_reference_camera():
+    """visionaray_b200.scenes.camera_matrices restates camera::look_at / perspective
+    (detail/camera.inl:10-65) bit for bit."""
+    if not O.ref_available():
+        pytest.skip("oracle/_ref not built (no /root/reference here)")
+    for eye, center, up, zn, zf in (((0.3, 1.2, 2.2), (0, 0, 0), (0, 1, 0), 0.1, 10.0),
+                                    ((-2.0, 0.4, 0.1), (0.2, 0.1, -0.3), (0, 0, 1), 0.001, 1000.0)):
+        fp = S.frame_params(0, 64, 48, eye, center, up=up, fovy_deg=37.0)
+        v, p = S.camera_matrices(fp, zn, zf)
+        rv, rp = O.ref_camera_matrices(fp, zn, zf)
+        assert v.tobytes() == rv.tobytes() and p.tobytes() == rp.tobytes()
+
+
 def test_golden_vectors():
     """Fixtures generated from the reference itself by tests/golden/make_golden.py."""
     path = os.path.join(GOLD, "golden_queries.npz")
@@ -144,6 +193,11 @@ def test_golden_vectors():
         fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=4)
         img = O.oracle_frame(sc, fp, S.default_material(0), S.point_light(eye))
         assert np.abs(img - fr["k1_ssaa4"]).max() <= 1.0 / 255.0     # generated by tiled_sched<simd::ray8> (packets)
+    fp = S.frame_params(1, 32, 24, eye, (0, 0, 0), pixel_sampler=3)
+    view, proj = S.camera_matrices(fp, 0.1, 10.0)
+    assert view.tobytes() == fr["matrix_view"].tobytes() and proj.tobytes() == fr["matrix_proj"].tobytes()
+    img, z = O.oracle_frame_matrix(sc, fp, view, proj, S.default_material(0), S.point_light(eye))
+    assert np.abs(img - fr["k1_matrix_ssaa2"]).max() <= 1e-6 and np.abs(z - fr["k1_matrix_ssaa2_depth"]).max() <= 1e-6
 
 
 def test_brute_force_agrees_with_bvh():

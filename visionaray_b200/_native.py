@@ -62,6 +62,7 @@ class FrameDesc(C.Structure):
         ("mem", C.c_int32), ("traverse", C.c_int32), ("tile_rank", C.c_int32), ("tile_nranks", C.c_int32),
         ("ray_count", C.c_void_p),
         ("params_mem", C.c_int32), ("tile_target", C.c_int32),
+        ("camera_kind", C.c_int32), ("view_matrix", C.c_float * 16), ("proj_matrix", C.c_float * 16),
     ]
 
 

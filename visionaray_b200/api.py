@@ -195,11 +195,15 @@ class DeviceBuffer:
 
 
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
-          tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False):
+          tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False, view_matrix=None, proj_matrix=None,
+          depth=None):
     """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
     the call, returns with pixels in place); torch CUDA tensor -> device render target
     (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
-    normals attached to the scene) are host or device buffers independently of the target."""
+    normals attached to the scene) are host or device buffers independently of the target.
+    `view_matrix` / `proj_matrix` (16 floats each, column-major): sched_params built from matrices
+    instead of fp's camera; with them `depth` (float32 per pixel, same kind of buffer as `color`)
+    receives the PF_DEPTH32F target."""
     if isinstance(scenes, Scene):
         scenes = [scenes]
     d = N.FrameDesc()
@@ -214,7 +218,17 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
         return a.ctypes.data if isinstance(a, np.ndarray) else a.data_ptr()
 
     d.normals, d.materials, d.lights, d.color = p(normals), p(materials), p(lights), p(color)
-    d.depth = None
+    d.depth = p(depth)
+    if depth is not None and isinstance(depth, np.ndarray) != host:
+        raise ValueError("color and depth must live in the same memory")
+    if (view_matrix is None) != (proj_matrix is None):
+        raise ValueError("view_matrix and proj_matrix come together")
+    if view_matrix is not None:
+        d.camera_kind = 1
+        v = np.ascontiguousarray(view_matrix, dtype=np.float32).reshape(16)
+        q = np.ascontiguousarray(proj_matrix, dtype=np.float32).reshape(16)
+        for i in range(16):
+            d.view_matrix[i], d.proj_matrix[i] = float(v[i]), float(q[i])
     d.mem = MEM_HOST if host else MEM_DEVICE
     params = [a for a in (normals, materials, lights) if a is not None]
     kinds = {isinstance(a, np.ndarray) for a in params}

@@ -235,6 +235,41 @@ extern "C" int vsb_camera_basis(vsb_frame_desc* d)
     return VSB_OK;
 }
 
+// inverse of a column-major 4x4 by cofactors of 2x2 sub-determinants, in float like the reference
+// scheduler's inverse(sparams.view_matrix) (detail/cuda_sched.inl:231-234; -ffp-contract=off TU)
+static bool mat4_inverse(const float* m, float* out)
+{
+    auto at = [&](int r, int c) { return m[c * 4 + r]; };
+    auto d2 = [](float a, float b, float c, float d) { return a * d - c * b; };
+    float s[6], c[6];
+    const int pr[6][2] = { {0, 1}, {0, 2}, {0, 3}, {1, 2}, {1, 3}, {2, 3} };
+    for (int k = 0; k < 6; ++k)
+    {
+        s[k] = d2(at(0, pr[k][0]), at(0, pr[k][1]), at(1, pr[k][0]), at(1, pr[k][1]));   // rows 0,1
+        c[k] = d2(at(2, pr[k][0]), at(2, pr[k][1]), at(3, pr[k][0]), at(3, pr[k][1]));   // rows 2,3
+    }
+    const float det = s[0] * c[5] - s[1] * c[4] + s[2] * c[3] + s[3] * c[2] - s[4] * c[1] + s[5] * c[0];
+    if (det == 0.0f || det != det) return false;
+    // adjugate: out(col j of the inverse, stored contiguously) from rows of m
+    out[0]  = (+at(1,1) * c[5] - at(1,2) * c[4] + at(1,3) * c[3]) / det;
+    out[1]  = (-at(1,0) * c[5] + at(1,2) * c[2] + at(1,3) * c[1]) / det;
+    out[2]  = (+at(1,0) * c[4] - at(1,1) * c[2] + at(1,3) * c[0]) / det;
+    out[3]  = (-at(1,0) * c[3] + at(1,1) * c[1] + at(1,2) * c[0]) / det;
+    out[4]  = (-at(0,1) * c[5] + at(0,2) * c[4] - at(0,3) * c[3]) / det;
+    out[5]  = (+at(0,0) * c[5] - at(0,2) * c[2] + at(0,3) * c[1]) / det;
+    out[6]  = (-at(0,0) * c[4] + at(0,1) * c[2] - at(0,3) * c[0]) / det;
+    out[7]  = (+at(0,0) * c[3] - at(0,1) * c[1] + at(0,2) * c[0]) / det;
+    out[8]  = (+at(3,1) * s[5] - at(3,2) * s[4] + at(3,3) * s[3]) / det;
+    out[9]  = (-at(3,0) * s[5] + at(3,2) * s[2] - at(3,3) * s[1]) / det;
+    out[10] = (+at(3,0) * s[4] - at(3,1) * s[2] + at(3,3) * s[0]) / det;
+    out[11] = (-at(3,0) * s[3] + at(3,1) * s[1] - at(3,2) * s[0]) / det;
+    out[12] = (-at(2,1) * s[5] + at(2,2) * s[4] - at(2,3) * s[3]) / det;
+    out[13] = (+at(2,0) * s[5] - at(2,2) * s[2] + at(2,3) * s[1]) / det;
+    out[14] = (-at(2,0) * s[4] + at(2,1) * s[2] - at(2,3) * s[0]) / det;
+    out[15] = (+at(2,0) * s[3] - at(2,1) * s[1] + at(2,2) * s[0]) / det;
+    return true;
+}
+
 extern "C" int vsb_tiles_of_rank(int width, int height, int rank, int nranks, int* n_tiles)
 {
     if (!n_tiles || width < 1 || height < 1 || nranks < 1 || rank < 0 || rank >= nranks) return VSB_ERR_BAD_ARG;
@@ -250,17 +285,25 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     const vsb_frame_params& p = d->p;
     if (p.width < 1 || p.height < 1 || p.kernel < 0 || p.kernel > 3 || p.pixel_sampler < 0 || p.pixel_sampler > 5) return VSB_ERR_BAD_ARG;
     if (p.pixel_sampler == VSB_PS_JITTERED_BLEND && p.frame_num == 0) return VSB_ERR_BAD_ARG;
+    if (d->camera_kind != VSB_CAM_BASIS && d->camera_kind != VSB_CAM_MATRIX) return VSB_ERR_BAD_ARG;
+    if (d->depth && d->camera_kind != VSB_CAM_MATRIX) return VSB_ERR_BAD_ARG;   // depth_transform needs the matrices
     if (p.kernel != VSB_KERNEL_AO && (!d->materials || p.n_materials < 1)) return VSB_ERR_BAD_ARG;
     if (p.n_lights > 0 && !d->lights && p.kernel <= VSB_KERNEL_WHITTED) return VSB_ERR_BAD_ARG;
     for (int i = 0; i < n_scenes; ++i) if (!scenes || !scenes[i] || scenes[i]->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
-    struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles, in_place;
+    struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; float* depth; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles, in_place;
              unsigned long long* ray_count; } fl;
     std::memset(&fl, 0, sizeof(fl));
     std::memcpy(&fl.ctx.p, &p, sizeof(p));
     for (int i = 0; i < 3; ++i) { fl.ctx.eye[i] = d->cam_eye[i]; fl.ctx.cu[i] = d->cam_u[i]; fl.ctx.cv[i] = d->cam_v[i]; fl.ctx.cw[i] = d->cam_w[i]; }
+    if (d->camera_kind == VSB_CAM_MATRIX)
+    {
+        fl.ctx.camera_kind = 1;
+        std::memcpy(fl.ctx.view, d->view_matrix, 64); std::memcpy(fl.ctx.proj, d->proj_matrix, 64);
+        if (!mat4_inverse(d->view_matrix, fl.ctx.inv_view) || !mat4_inverse(d->proj_matrix, fl.ctx.inv_proj)) return VSB_ERR_BAD_ARG;
+    }
     const int nranks = d->tile_nranks > 1 ? d->tile_nranks : 1;
     const int rank = d->tile_nranks > 1 ? d->tile_rank : 0;
     if (rank < 0 || rank >= nranks) return VSB_ERR_BAD_ARG;
@@ -309,10 +352,19 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
             VSB_CUDA(cudaMemcpyAsync(e, d->color, color_px * 16, cudaMemcpyHostToDevice, st));   // progressive state lives with the caller
         fl.color = reinterpret_cast<float4*>(e);
+        if (d->depth)
+        {
+            void* z;
+            rc = stage(6, color_px * 4 + 16, &z); if (rc) return rc;
+            if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
+                VSB_CUDA(cudaMemcpyAsync(z, d->depth, color_px * 4, cudaMemcpyHostToDevice, st));
+            fl.depth = reinterpret_cast<float*>(z);
+        }
         if (d->ray_count) d_ray_count = g.d_work + 1;
     }
     else
     {
+        fl.depth = reinterpret_cast<float*>(d->depth);
         fl.color = reinterpret_cast<float4*>(d->color);
         d_ray_count = reinterpret_cast<unsigned long long*>(d->ray_count);
     }
@@ -350,12 +402,14 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     do {                                                                                                     \
         vsb::FrameProgram<K, SS> prog;                                                                       \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
+        prog.depth = fl.depth;                                                                               \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
         if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, true>(prog, tl, st)));                   \
         else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, st)));                  \
     } while (0)
-        switch (p.kernel * 2 + (p.pixel_sampler >= VSB_PS_SSAA2 ? 1 : 0))
+        // extended instantiation: SSAA samplers, matrix camera, depth target (see shade.cuh)
+        switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX) ? 1 : 0))
         {
         case 0: VSB_LAUNCH_FRAME(0, false); break;
         case 1: VSB_LAUNCH_FRAME(0, true); break;
@@ -384,6 +438,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
             VSB_CUDA(cudaStreamWaitEvent(g.copy_stream, g.band_done[band], 0));
             VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * 16, reinterpret_cast<const char*>(fl.color) + px0 * 16,
                                      (px1 - px0) * 16, cudaMemcpyDeviceToHost, g.copy_stream));
+            if (d->depth)
+                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->depth) + px0 * 4, reinterpret_cast<const char*>(fl.depth) + px0 * 4,
+                                         (px1 - px0) * 4, cudaMemcpyDeviceToHost, g.copy_stream));
         }
     }
     if (d->mem == VSB_MEM_HOST)

@@ -62,9 +62,44 @@ struct FrameCtx
     const float4*     normals;     // per-face normals, 16 B each, by prim_id
     const Material*   materials;   // by geom_id
     const PointLight* lights;
+    // sched_params built from matrices (camera_kind == 1): column-major matrix<4,4,float>
+    int   camera_kind;
+    float view[16], inv_view[16], proj[16], inv_proj[16];
 };
 
 VSB_HD V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
+
+// matrix<4,4> * vector<4>, row r -- math/detail/matrix4.inl:171-181
+VSB_HD float mat4_row(const float* m, int r, float x, float y, float z, float w)
+{
+    return rn_add(rn_add(rn_add(rn_mul(m[r], x), rn_mul(m[4 + r], y)), rn_mul(m[8 + r], z)), rn_mul(m[12 + r], w));
+}
+VSB_HD void mat4_mul(const float* m, const float v[4], float out[4])
+{
+    for (int r = 0; r < 4; ++r) out[r] = mat4_row(m, r, v[0], v[1], v[2], v[3]);
+}
+
+// make_primary_ray_impl, matrix overload: detail/sched_common.h:152-178
+VSB_HD void primary_ray_matrix(const FrameCtx& f, float x, float y, V3& ori, V3& dir)
+{
+    const float u = rn_sub(rn_div(rn_mul(2.0f, rn_add(x, 0.5f)), (float)f.p.width), 1.0f);
+    const float v = rn_sub(rn_div(rn_mul(2.0f, rn_add(y, 0.5f)), (float)f.p.height), 1.0f);
+    const float n4[4] = { u, v, -1.0f, 1.0f }, f4[4] = { u, v, 1.0f, 1.0f };
+    float t[4], o[4], d[4];
+    mat4_mul(f.inv_proj, n4, t); mat4_mul(f.inv_view, t, o);
+    mat4_mul(f.inv_proj, f4, t); mat4_mul(f.inv_view, t, d);
+    ori = v3(rn_div(o[0], o[3]), rn_div(o[1], o[3]), rn_div(o[2], o[3]));
+    dir = vnormalize(vsub(v3(rn_div(d[0], d[3]), rn_div(d[1], d[3]), rn_div(d[2], d[3])), ori));
+}
+
+// depth_transform: detail/sched_common.h:337-354
+VSB_HD float depth_transform(const FrameCtx& f, V3 pos)
+{
+    const float p4[4] = { pos.x, pos.y, pos.z, 1.0f };
+    float t[4], q[4];
+    mat4_mul(f.view, p4, t); mat4_mul(f.proj, t, q);
+    return rn_mul(rn_add(rn_div(q[2], q[3]), 1.0f), 0.5f);
+}
 
 // make_primary_ray_impl, pinhole: detail/sched_common.h:130-150
 VSB_HD void primary_ray(const FrameCtx& f, float x, float y, V3& ori, V3& dir)
@@ -210,24 +245,26 @@ struct FrameLane
 };
 
 // common words: destination index, sampler state, phase, pixel index, SSAA sub-sample index + accumulator
-enum { W_DST = 0, W_SAMP = 1, W_PHASE = 2, W_PIX = 3, W_SUB = 4, W_ACC = 5 };   // 3.. only with SSAA
+enum { W_DST = 0, W_SAMP = 1, W_PHASE = 2, W_PIX = 3, W_SUB = 4, W_ACC = 5, W_DEPTH = 9, W_DACC = 10 };   // 3.. only with EXT
 enum { PH_PRIMARY = 0, PH_BOUNCE = 1, PH_SHADOW = 2 };
 
-// SSAA = true adds the sub-sample accumulator to the lane state and the resampling branch to
-// finish(); the common samplers run the leaner instantiation.
-template <int KERNEL, bool SSAA>
+// EXT = true is the instantiation for the less common sched_params: SSAA pixel samplers (sub-sample
+// accumulator in the lane state, resampling branch in finish()), the matrix camera and the depth
+// target.  The common case (camera basis, uniform / jittered samplers, colour only) runs the leaner one.
+template <int KERNEL, bool EXT>
 struct FrameProgram
 {
     FrameCtx ctx;
     int scissor[4];
     float4* color;
+    float* depth;                    // EXT only; may be null
     int tile_rank, tile_nranks;      // tile_nranks == 0: single rank, row-major target
     int tiles_x;
     int in_place;                    // tile_nranks > 1: store into the whole row-major frame (e.g. peer memory)
     int tile_begin;                  // first rank-local tile of this launch (host targets are rendered in bands)
 
     using Lane = FrameLane;
-    static constexpr int K0 = SSAA ? 9 : 3;      // first kernel-specific state word
+    static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
     static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? 17 : (KERNEL == 0 ? 0 : 6));
 
     __device__ void closest(RayReq& r, V3 o, V3 d) const
@@ -270,8 +307,17 @@ struct FrameProgram
             L.u(K0 + 4) = 0u;                       // result.hit
         }
         V3 o, d;
-        primary_ray(ctx, fx, fy, o, d);
+        if (EXT && ctx.camera_kind == 1) primary_ray_matrix(ctx, fx, fy, o, d);
+        else primary_ray(ctx, fx, fy, o, d);
+        if (EXT) L.f(W_DEPTH) = 1.0f;               // result.depth of a sample whose primary ray misses
         closest(req, o, d);
+    }
+
+    // result.hit / result.isect_pos of the built-in kernels are the PRIMARY hit (simple.inl:38,66;
+    // whitted.inl:241; pathtracing.inl:68; ao/main.cpp:198-199): its depth is kept for finish()
+    __device__ void primary_hit(Lane& L, V3 pos) const
+    {
+        if (EXT && depth) L.f(W_DEPTH) = depth_transform(ctx, pos);
     }
 
     // Pixel result of one kernel invocation.  uniform / jittered: store (detail/pixel_access.h:38-58);
@@ -284,15 +330,17 @@ struct FrameProgram
         const size_t dst = L.u(W_DST);
         float4 c = make_float4(r, g, b, a);
         const int ps = ctx.p.pixel_sampler;
-        if (SSAA && ps >= 3)
+        if (EXT && ps >= 3)
         {
             const int num = 2 << (ps - 3);
             const float alpha = rn_div(1.0f, (float)num);
             c.x = rn_add(rn_mul(c.x, alpha), L.f(W_ACC + 0)); c.y = rn_add(rn_mul(c.y, alpha), L.f(W_ACC + 1));
             c.z = rn_add(rn_mul(c.z, alpha), L.f(W_ACC + 2)); c.w = rn_add(rn_mul(c.w, alpha), L.f(W_ACC + 3));
             const uint32_t k = L.u(W_SUB) + 1u;
+            const float z = rn_add(rn_mul(L.f(W_DEPTH), alpha), L.f(W_DACC));
             if ((int)k < num)
             {
+                L.f(W_DACC) = z;
                 L.f(W_ACC + 0) = c.x; L.f(W_ACC + 1) = c.y; L.f(W_ACC + 2) = c.z; L.f(W_ACC + 3) = c.w;
                 L.u(W_SUB) = k;
                 const uint32_t pixel = L.u(W_PIX);
@@ -301,6 +349,7 @@ struct FrameProgram
                 start_sample(L, rn_add((float)(pixel % (uint32_t)ctx.p.width), dx), rn_add((float)(pixel / (uint32_t)ctx.p.width), dy), req);
                 return true;
             }
+            if (depth) depth[dst] = z;
         }
         else if (ps == 2)
         {
@@ -311,7 +360,9 @@ struct FrameProgram
             c.y = rn_add(rn_mul(c.y, alpha), rn_mul(old.y, ia));
             c.z = rn_add(rn_mul(c.z, alpha), rn_mul(old.z, ia));
             c.w = rn_add(rn_mul(c.w, alpha), rn_mul(old.w, ia));
+            if (EXT && depth) depth[dst] = rn_add(rn_mul(L.f(W_DEPTH), alpha), rn_mul(depth[dst], ia));
         }
+        else if (EXT && depth) depth[dst] = L.f(W_DEPTH);
         color[dst] = c;
         return false;
     }
@@ -345,10 +396,11 @@ struct FrameProgram
         if (!inside) return false;
         const uint32_t pixel = (uint32_t)y * (uint32_t)f.p.width + (uint32_t)x;
         L.u(W_DST) = (tile_nranks > 1 && !in_place) ? (uint32_t)(local_tile * (VSB_TILE * VSB_TILE) + ly * VSB_TILE + lx) : pixel;
-        if (SSAA)
+        if (EXT)
         {
             L.u(W_PIX) = pixel; L.u(W_SUB) = 0u;
             L.f(W_ACC + 0) = 0.0f; L.f(W_ACC + 1) = 0.0f; L.f(W_ACC + 2) = 0.0f; L.f(W_ACC + 3) = 0.0f;
+            L.f(W_DACC) = 0.0f;
         }
         uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
         float fx = (float)x, fy = (float)y;
@@ -359,7 +411,7 @@ struct FrameProgram
             const float jy = rn_sub(sampler_next(samp), 0.5f);
             fx = rn_add(fx, jx); fy = rn_add(fy, jy);
         }
-        else if (SSAA && f.p.pixel_sampler >= 3)
+        else if (EXT && f.p.pixel_sampler >= 3)
         {
             float dx, dy;
             ssaa_offset(2 << (f.p.pixel_sampler - 3), 0, dx, dy);
@@ -370,6 +422,7 @@ struct FrameProgram
         {
             // no bounce is traced: every sample returns the background
             color[L.u(W_DST)] = make_float4(f.p.bg[0], f.p.bg[1], f.p.bg[2], f.p.bg[3]);
+            if (EXT && depth) depth[L.u(W_DST)] = 1.0f;
             return false;
         }
         start_sample(L, fx, fy, req);
@@ -391,6 +444,7 @@ struct FrameProgram
         const FrameCtx& f = ctx;
         if (!h.hit) { return finish_bg(L, req); }
         const V3 pos = vadd(o, vscale(d, h.t));
+        primary_hit(L, pos);
         const Material m = f.materials[h.geom_id];
         V3 n = face_normal(h.prim_id);
         V3 shaded = ambient_term(m);
@@ -433,6 +487,7 @@ struct FrameProgram
         else
         {
             if (phase == PH_PRIMARY && !h.hit) { return finish_bg(L, req); }
+            if (EXT && phase == PH_PRIMARY) primary_hit(L, vadd(o, vscale(d, h.t)));   // detail/whitted.inl:238-242
             // while (hit && throughput > epsilon && depth++ < num_bounces)
             const float throughput = L.f(K0 + 6);
             bool go = h.hit && throughput > f.p.epsilon;
@@ -475,6 +530,7 @@ struct FrameProgram
         {
             if (!h.hit) { return finish_bg(L, req); }
             pos = vadd(o, vscale(d, h.t));
+            primary_hit(L, pos);
             prim_id = h.prim_id; clr = 1.0f; i = 0u;
             L.st(K0 + 0, pos); L.u(K0 + 3) = prim_id; L.u(W_PHASE) = PH_SHADOW;
         }
@@ -517,7 +573,7 @@ struct FrameProgram
         }
         else
         {
-            if (bounce == 0u) result_hit = true;
+            if (bounce == 0u) { result_hit = true; primary_hit(L, vadd(o, vscale(d, h.t))); }
             const V3 view = vneg(d);
             const Material m = f.materials[h.geom_id];
             const V3 sn = face_normal(h.prim_id);
