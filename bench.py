@@ -388,6 +388,7 @@ def run_gpu(args):
     api.sync()
     fence()
     e2e_s = time.perf_counter() - t0
+    e2e_trace_ms = api.last_kernel_ms()           # device time of the last e2e frame's trace launches (all bands)
     te = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
     re = torch.tensor([e2e_rays], dtype=torch.int64, device="cuda")
     if world > 1:
@@ -450,7 +451,7 @@ def run_gpu(args):
                        "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "triangles": sc.n_prims},
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "steps": e2e_steps},
+                    "steps": e2e_steps, "ms_per_step": float(te.item()) * 1e3 / e2e_steps, "trace_ms": e2e_trace_ms},
             "gpu_launches": int(launches), "clocks": clk,
         }
         print(json.dumps(line), flush=True)

@@ -441,19 +441,36 @@ def test_banded_host_target_equals_device_target(gpu, scenes):
     gpu.frame(dev, fp, None, d_m, d_l, full)
     gpu.sync()
     want = full.cpu().numpy()
-    for bands in (4, 3, 1, 8):
-        gpu.tune("frame_bands", bands)
-        host = np.full((h, w, 4), -1.0, dtype=np.float32)
-        rc = np.zeros(1, dtype=np.uint64)
-        gpu.frame(dev, fp, None, mats, lights, host, ray_count=rc)
-        assert np.array_equal(host, want), bands
-        assert rc[0] >= w * h
-    gpu.tune("frame_bands", 2)
-    # compact tile buffer of rank 0 of 1-rank-sized partition: nranks = 2 leaves 144 tiles (< 256: one band);
-    # use the whole image as "rank 0 of 1" through the in-tile layout check instead
-    from visionaray_b200 import partition as P
-    per = P.tiles_of_rank(w, h, 0, 2)
-    compact = np.zeros((per, 64 * 64, 4), dtype=np.float32)
-    gpu.frame(dev, fp, None, mats, lights, compact, tile_rank=0, tile_nranks=2)
-    inside = P.pack_tiles(np.ones_like(want), 0, 2)[:per] != 0      # pixel slots of edge tiles outside the image are undefined
-    assert np.array_equal(compact[inside], P.pack_tiles(want, 0, 2)[:per][inside])
+    gpu.tune("band_min_mib", 1)      # small test frame: allow bands below the production size threshold
+    try:
+        for bands, streams in ((4, 2), (3, 2), (1, 2), (8, 1), (16, 2)):
+            gpu.tune("frame_bands", bands)
+            gpu.tune("band_streams", streams)
+            host = np.full((h, w, 4), -1.0, dtype=np.float32)
+            rc = np.zeros(1, dtype=np.uint64)
+            gpu.frame(dev, fp, None, mats, lights, host, ray_count=rc)
+            assert np.array_equal(host, want), bands
+            assert rc[0] >= w * h
+        gpu.tune("band_streams", 2)
+        # compact tile buffer (rank 0 of 2: 144 tiles = 3 band units of 64 tiles, the last one ragged)
+        from visionaray_b200 import partition as P
+        per = P.tiles_of_rank(w, h, 0, 2)
+        inside = P.pack_tiles(np.ones_like(want), 0, 2)[:per] != 0      # pixel slots of edge tiles outside the image are undefined
+        for bands in (1, 2, 3):
+            gpu.tune("frame_bands", bands)
+            compact = np.zeros((per, 64 * 64, 4), dtype=np.float32)
+            gpu.frame(dev, fp, None, mats, lights, compact, tile_rank=0, tile_nranks=2)
+            assert np.array_equal(compact[inside], P.pack_tiles(want, 0, 2)[:per][inside]), bands
+        # progressive blending into a banded host target: the caller's accumulated frame is uploaded band by band
+        gpu.tune("frame_bands", 4)
+        acc_h = np.zeros((h, w, 4), dtype=np.float32)
+        acc_d = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        for frame_num in (1, 2, 3):
+            fpp = S.frame_params(3, w, h, eye, (0, 0, 0), pixel_sampler=2, frame_num=frame_num, num_bounces=3, ambient=(1, 1, 1, 1))
+            gpu.frame(dev, fpp, None, mats, lights, acc_h)
+            gpu.frame(dev, fpp, None, d_m, d_l, acc_d)
+        gpu.sync()
+        assert np.array_equal(acc_h, acc_d.cpu().numpy())
+    finally:
+        gpu.tune("frame_bands", 8)
+        gpu.tune("band_min_mib", 16)

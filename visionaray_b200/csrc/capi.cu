@@ -65,7 +65,11 @@ int g_query_service_min = 4, g_frame_service_min = 0, g_phase_min = 1;
 int g_sort_rays = 1;
 // frame_bands: a host render target is traced in this many bands so that the D2H copy of one band
 // overlaps the tracing of the next (1 = off)
-int g_frame_bands = 2;     // measured on cfg2: 1: 11.7 ms, 2: 9.6 ms, 4: 9.7 ms per 4096^2 frame into pinned host memory
+int g_host_store = 0;      // 1: frames into PINNED host targets are stored by the trace kernel itself (mapped memory, no staging / D2H pass)
+int g_band_min_mib = 16;   // a band carries at least this much of the target (per-launch ramps vs overlap)
+int g_band_trace = 0;      // developer switch: print the band timeline of host-target frames to stderr
+int g_band_streams = 2;    // 2: alternate bands over two streams (tail of band i overlaps the head of band i+1)
+int g_frame_bands = 8;     // cfg2 into pinned host memory: 1 band 11.8 ms, 2: 9.6, 16 interleaved bands on two streams: see DESIGN.md section 5
 
 template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
@@ -170,6 +174,10 @@ extern "C" int vsb_tune(const char* key, int value)
     else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
     else if (!std::strcmp(key, "sort_rays")) g_sort_rays = value;
     else if (!std::strcmp(key, "frame_bands")) g_frame_bands = value;
+    else if (!std::strcmp(key, "host_store")) g_host_store = value;
+    else if (!std::strcmp(key, "band_streams")) g_band_streams = value;
+    else if (!std::strcmp(key, "band_trace")) g_band_trace = value;
+    else if (!std::strcmp(key, "band_min_mib")) g_band_min_mib = value;
     else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
     else return VSB_ERR_BAD_ARG;
     return VSB_OK;
@@ -345,19 +353,40 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         fl.ctx.materials = reinterpret_cast<const vsb::Material*>(d->materials);
         fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(d->lights);
     }
-    if (d->mem == VSB_MEM_HOST)
+    // A pinned (page-locked, mapped) host target can be written by the kernel itself: every finished
+    // pixel goes over PCIe while the other lanes keep traversing, so there is no D2H pass after the
+    // trace.  Pageable targets and progressive blending (which re-reads the target) are staged.
+    bool direct_host = false;
+    if (d->mem == VSB_MEM_HOST && g_host_store && p.pixel_sampler != VSB_PS_JITTERED_BLEND)
+    {
+        cudaPointerAttributes ac, az;
+        void* dev_c = nullptr; void* dev_z = nullptr;
+        bool ok = cudaPointerGetAttributes(&ac, d->color) == cudaSuccess && ac.type == cudaMemoryTypeHost && ac.devicePointer;
+        if (ok) dev_c = ac.devicePointer;
+        if (ok && d->depth)
+        {
+            ok = cudaPointerGetAttributes(&az, d->depth) == cudaSuccess && az.type == cudaMemoryTypeHost && az.devicePointer;
+            if (ok) dev_z = az.devicePointer;
+        }
+        cudaGetLastError();
+        if (ok)
+        {
+            direct_host = true;
+            fl.color = reinterpret_cast<float4*>(dev_c);
+            fl.depth = reinterpret_cast<float*>(dev_z);
+            if (d->ray_count) d_ray_count = g.d_work + 1;
+        }
+    }
+    if (direct_host) {}
+    else if (d->mem == VSB_MEM_HOST)
     {
         void* e;
         rc = stage(5, color_px * 16 + 16, &e); if (rc) return rc;
-        if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
-            VSB_CUDA(cudaMemcpyAsync(e, d->color, color_px * 16, cudaMemcpyHostToDevice, st));   // progressive state lives with the caller
         fl.color = reinterpret_cast<float4*>(e);
         if (d->depth)
         {
             void* z;
             rc = stage(6, color_px * 4 + 16, &z); if (rc) return rc;
-            if (p.pixel_sampler == VSB_PS_JITTERED_BLEND)
-                VSB_CUDA(cudaMemcpyAsync(z, d->depth, color_px * 4, cudaMemcpyHostToDevice, st));
             fl.depth = reinterpret_cast<float*>(z);
         }
         if (d->ray_count) d_ray_count = g.d_work + 1;
@@ -370,7 +399,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     }
     fl.ray_count = d_ray_count;
 
-    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 16 * sizeof(unsigned long long), st));
+    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 64 * sizeof(unsigned long long), st));
     const bool exact = d->traverse == VSB_TRAVERSE_EXACT;
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
@@ -378,25 +407,78 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel == VSB_KERNEL_PATHTRACING ? 16 : 32);
     tl.phase_min = g_phase_min;
 
-    // Host render targets are rendered in bands of whole tile rows (row-major target) or tile ranges
-    // (compact tile buffer): the D2H copy of band i runs on the copy stream while band i+1 is traced.
+    // Host render targets are traced in bands so that the D2H copy of a finished band runs on the
+    // copy stream while the next bands are traced.  A band is every n_bands-th UNIT (a tile row of a
+    // row-major target, 64 consecutive tiles of a compact tile buffer; each contiguous in the
+    // target): sky and geometry are spread over all bands, so bands finish at an even pace and
+    // the copies never queue up behind a burst of cheap bands.
     const bool compact = nranks > 1 && !fl.in_place;
     int n_bands = 1;
-    if (d->mem == VSB_MEM_HOST && fl.n_owned_tiles >= 256) n_bands = g_frame_bands < 1 ? 1 : (g_frame_bands > 8 ? 8 : g_frame_bands);
-    const int units = compact ? fl.n_owned_tiles : fl.tiles_y;               // what a band is made of
+    if (d->mem == VSB_MEM_HOST && !direct_host)
+    {
+        // a band should carry >= 16 MiB of pixels: below that the per-launch ramps cost more than the overlap buys
+        const size_t by_size = (color_px * 16 >> 20) / (size_t)(g_band_min_mib < 1 ? 1 : g_band_min_mib);
+        n_bands = g_frame_bands < 1 ? 1 : (g_frame_bands > 32 ? 32 : g_frame_bands);
+        if ((size_t)n_bands > by_size) n_bands = by_size < 1 ? 1 : (int)by_size;
+    }
+    const int unit_tiles = compact ? 64 : fl.tiles_x;
+    const int units = compact ? (fl.n_owned_tiles + unit_tiles - 1) / unit_tiles : fl.tiles_y;
     if (n_bands > units) n_bands = units;
-    const int per_band = (units + n_bands - 1) / n_bands;
+    auto unit_pixels = [&](int u, size_t& px0, size_t& px1)      // contiguous pixel range of unit u in the target
+    {
+        if (n_bands == 1) { px0 = 0; px1 = color_px; }
+        else if (compact)
+        {
+            px0 = (size_t)u * unit_tiles * VSB_TILE * VSB_TILE; px1 = px0 + (size_t)unit_tiles * VSB_TILE * VSB_TILE;
+            if (px1 > color_px) px1 = color_px;
+        }
+        else
+        {
+            const size_t row0 = (size_t)u * VSB_TILE, row1 = (size_t)(u + 1) * VSB_TILE < (size_t)p.height ? (size_t)(u + 1) * VSB_TILE : (size_t)p.height;
+            px0 = row0 * (size_t)p.width; px1 = row1 * (size_t)p.width;
+        }
+    };
+    // progressive blending: the accumulated frame lives with the caller; it is uploaded band by band
+    // on its own stream (the H2D engine runs ahead of the trace, the D2H engine behind it)
+    const bool upload = d->mem == VSB_MEM_HOST && !direct_host && p.pixel_sampler == VSB_PS_JITTERED_BLEND;
+    if (upload)
+    {
+        VSB_CUDA(cudaEventRecord(g.band_fork, st));
+        VSB_CUDA(cudaStreamWaitEvent(g.upload_stream, g.band_fork, 0));
+        for (int band = 0; band < n_bands; ++band)
+        {
+            for (int u = band; u < units; u += n_bands)
+            {
+                size_t px0, px1;
+                unit_pixels(u, px0, px1);
+                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(fl.color) + px0 * 16, reinterpret_cast<const char*>(d->color) + px0 * 16,
+                                         (px1 - px0) * 16, cudaMemcpyHostToDevice, g.upload_stream));
+                if (d->depth)
+                    VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(fl.depth) + px0 * 4, reinterpret_cast<const char*>(d->depth) + px0 * 4,
+                                             (px1 - px0) * 4, cudaMemcpyHostToDevice, g.upload_stream));
+                if (n_bands == 1) break;
+            }
+            VSB_CUDA(cudaEventRecord(g.band_up[band], g.upload_stream));
+        }
+    }
 
+    cudaEvent_t tr_k[32], tr_c[32];
     VSB_CUDA(cudaEventRecord(g.ev0, st));
+    // bands alternate between the caller's stream and a second one: the persistent CTAs of band
+    // i+1 are dispatched as those of band i retire, so no SM idles in a band's tail
+    const bool two_streams = n_bands > 1 && g_band_streams > 1;
+    if (two_streams)
+    {
+        VSB_CUDA(cudaEventRecord(g.band_fork, st));
+        VSB_CUDA(cudaStreamWaitEvent(g.band_stream, g.band_fork, 0));
+    }
     for (int band = 0; band < n_bands; ++band)
     {
-        const int u0 = band * per_band, u1 = (band + 1) * per_band < units ? (band + 1) * per_band : units;
-        if (u0 >= u1) break;
-        const int t0 = compact ? u0 : u0 * fl.tiles_x, t1 = compact ? u1 : u1 * fl.tiles_x;   // rank-local tile range
-        // (row-major multi-rank in-place targets are device memory: n_bands == 1 there, t0..t1 = all owned tiles)
-        const int tile_begin = n_bands == 1 ? 0 : t0;
-        const int tile_count = n_bands == 1 ? fl.n_owned_tiles : t1 - t0;
-        tl.n_items = (unsigned long long)tile_count * VSB_TILE * VSB_TILE;
+        cudaStream_t bs = (two_streams && (band & 1)) ? g.band_stream : st;
+        if (upload) VSB_CUDA(cudaStreamWaitEvent(bs, g.band_up[band], 0));
+        const int units_in_band = (units - band + n_bands - 1) / n_bands;
+        const int tile_begin = n_bands == 1 ? 0 : band * unit_tiles;
+        tl.n_items = (unsigned long long)(n_bands == 1 ? fl.n_owned_tiles : units_in_band * unit_tiles) * VSB_TILE * VSB_TILE;
         tl.work_counter = n_bands == 1 ? g.d_work : g.d_work + 2 + band;
 #define VSB_LAUNCH_FRAME(K, SS)                                                                                \
     do {                                                                                                     \
@@ -405,8 +487,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         prog.depth = fl.depth;                                                                               \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
-        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, true>(prog, tl, st)));                   \
-        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, st)));                  \
+        prog.unit_tiles = unit_tiles; prog.unit_stride = n_bands; prog.n_local_tiles = fl.n_owned_tiles;     \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, true>(prog, tl, bs)));                   \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, bs)));                  \
     } while (0)
         // extended instantiation: SSAA samplers, matrix camera, depth target (see shade.cuh)
         switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX) ? 1 : 0))
@@ -423,31 +506,45 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
 #undef VSB_LAUNCH_FRAME
         ++g.launches;
         VSB_CUDA(cudaGetLastError());
-        if (d->mem == VSB_MEM_HOST)
+        if (direct_host) VSB_CUDA(cudaEventRecord(g.ev1, st));
+        else if (d->mem == VSB_MEM_HOST)
         {
-            size_t px0, px1;
-            if (compact) { px0 = (size_t)t0 * VSB_TILE * VSB_TILE; px1 = (size_t)t1 * VSB_TILE * VSB_TILE; }
-            else
-            {
-                const size_t row0 = (size_t)u0 * VSB_TILE, row1 = (size_t)u1 * VSB_TILE < (size_t)p.height ? (size_t)u1 * VSB_TILE : (size_t)p.height;
-                px0 = row0 * (size_t)p.width; px1 = row1 * (size_t)p.width;
-            }
-            if (n_bands == 1) { px0 = 0; px1 = color_px; }
-            if (band == n_bands - 1) VSB_CUDA(cudaEventRecord(g.ev1, st));
-            VSB_CUDA(cudaEventRecord(g.band_done[band], st));
+            VSB_CUDA(cudaEventRecord(g.band_done[band], bs));
+            if (g_band_trace) { cudaEventCreate(&tr_k[band]); cudaEventRecord(tr_k[band], bs); }
             VSB_CUDA(cudaStreamWaitEvent(g.copy_stream, g.band_done[band], 0));
-            VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * 16, reinterpret_cast<const char*>(fl.color) + px0 * 16,
-                                     (px1 - px0) * 16, cudaMemcpyDeviceToHost, g.copy_stream));
-            if (d->depth)
-                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->depth) + px0 * 4, reinterpret_cast<const char*>(fl.depth) + px0 * 4,
-                                         (px1 - px0) * 4, cudaMemcpyDeviceToHost, g.copy_stream));
+            for (int u = band; u < units; u += n_bands)
+            {
+                size_t px0, px1;
+                unit_pixels(u, px0, px1);
+                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * 16, reinterpret_cast<const char*>(fl.color) + px0 * 16,
+                                         (px1 - px0) * 16, cudaMemcpyDeviceToHost, g.copy_stream));
+                if (d->depth)
+                    VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->depth) + px0 * 4, reinterpret_cast<const char*>(fl.depth) + px0 * 4,
+                                             (px1 - px0) * 4, cudaMemcpyDeviceToHost, g.copy_stream));
+                if (n_bands == 1) break;
+            }
+            if (g_band_trace) { cudaEventCreate(&tr_c[band]); cudaEventRecord(tr_c[band], g.copy_stream); }
         }
     }
+    if (two_streams)
+    {
+        VSB_CUDA(cudaEventRecord(g.band_join, g.band_stream));
+        VSB_CUDA(cudaStreamWaitEvent(st, g.band_join, 0));
+    }
+    if (d->mem == VSB_MEM_HOST && !direct_host) VSB_CUDA(cudaEventRecord(g.ev1, st));
     if (d->mem == VSB_MEM_HOST)
     {
         if (d->ray_count) VSB_CUDA(cudaMemcpyAsync(d->ray_count, d_ray_count, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
         VSB_CUDA(cudaStreamSynchronize(st));
         VSB_CUDA(cudaStreamSynchronize(g.copy_stream));   // host-visible target: frame() returns with pixels in place
+        if (g_band_trace && !direct_host)
+            for (int b = 0; b < n_bands; ++b)
+            {
+                float a = 0.0f, c = 0.0f;
+                cudaEventElapsedTime(&a, g.ev0, tr_k[b]); cudaEventElapsedTime(&c, g.ev0, tr_c[b]);
+                std::fprintf(stderr, "band %2d traced at %7.3f ms, on the host at %7.3f ms\n", b, a, c);
+                cudaEventDestroy(tr_k[b]); cudaEventDestroy(tr_c[b]);
+            }
     }
     else VSB_CUDA(cudaEventRecord(g.ev1, st));
     return VSB_OK;

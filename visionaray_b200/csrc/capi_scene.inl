@@ -10,7 +10,10 @@ struct Context
     int          sm_count = 0;
     cudaStream_t stream = nullptr;          // internal stream for uploads / encode
     cudaStream_t copy_stream = nullptr;     // D2H of finished frame bands, overlapping the next band's kernel
-    cudaEvent_t  band_done[8] = {};
+    cudaStream_t band_stream = nullptr;     // odd bands are traced here, so a band's tail overlaps the next band's start
+    cudaStream_t upload_stream = nullptr;   // H2D of the caller's progressive frame, band by band ahead of the trace
+    cudaEvent_t  band_done[32] = {}, band_up[32] = {};
+    cudaEvent_t  band_fork = nullptr, band_join = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     unsigned long long* d_work = nullptr;   // persistent-kernel work counter
     vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
@@ -147,10 +150,15 @@ extern "C" int vsb_init(int device)
     g.sm_count = prop.multiProcessorCount;
     VSB_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     VSB_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
-    for (int i = 0; i < 8; ++i) VSB_CUDA(cudaEventCreateWithFlags(&g.band_done[i], cudaEventDisableTiming));
+    for (int i = 0; i < 32; ++i) VSB_CUDA(cudaEventCreateWithFlags(&g.band_done[i], cudaEventDisableTiming));
+    VSB_CUDA(cudaStreamCreateWithFlags(&g.band_stream, cudaStreamNonBlocking));
+    VSB_CUDA(cudaStreamCreateWithFlags(&g.upload_stream, cudaStreamNonBlocking));
+    for (int i = 0; i < 32; ++i) VSB_CUDA(cudaEventCreateWithFlags(&g.band_up[i], cudaEventDisableTiming));
+    VSB_CUDA(cudaEventCreateWithFlags(&g.band_fork, cudaEventDisableTiming));
+    VSB_CUDA(cudaEventCreateWithFlags(&g.band_join, cudaEventDisableTiming));
     VSB_CUDA(cudaEventCreate(&g.ev0));
     VSB_CUDA(cudaEventCreate(&g.ev1));
-    VSB_CUDA(cudaMalloc(&g.d_work, 16 * sizeof(unsigned long long)));   // [0] queue, [1] ray count, [2..9] band queues
+    VSB_CUDA(cudaMalloc(&g.d_work, 64 * sizeof(unsigned long long)));   // [0] queue, [1] ray count, [2..33] band queues
     VSB_CUDA(cudaMalloc(&g.d_scenes, sizeof(vsb::DeviceScene) * MAX_SCENES));
     g.inited = true;
     return VSB_OK;
@@ -168,7 +176,12 @@ extern "C" int vsb_shutdown(void)
     if (g.ev1) cudaEventDestroy(g.ev1);
     if (g.stream) cudaStreamDestroy(g.stream);
     if (g.copy_stream) cudaStreamDestroy(g.copy_stream);
-    for (int i = 0; i < 8; ++i) if (g.band_done[i]) cudaEventDestroy(g.band_done[i]);
+    if (g.band_stream) cudaStreamDestroy(g.band_stream);
+    if (g.upload_stream) cudaStreamDestroy(g.upload_stream);
+    for (int i = 0; i < 32; ++i) if (g.band_up[i]) cudaEventDestroy(g.band_up[i]);
+    if (g.band_fork) cudaEventDestroy(g.band_fork);
+    if (g.band_join) cudaEventDestroy(g.band_join);
+    for (int i = 0; i < 32; ++i) if (g.band_done[i]) cudaEventDestroy(g.band_done[i]);
     g = Context();
     return VSB_OK;
 }

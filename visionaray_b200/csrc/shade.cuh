@@ -262,6 +262,8 @@ struct FrameProgram
     int tiles_x;
     int in_place;                    // tile_nranks > 1: store into the whole row-major frame (e.g. peer memory)
     int tile_begin;                  // first rank-local tile of this launch (host targets are rendered in bands)
+    int unit_tiles, unit_stride;     // a band = every unit_stride-th run of unit_tiles tiles, so bands cost alike (0: one launch)
+    int n_local_tiles;
 
     using Lane = FrameLane;
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
@@ -385,7 +387,12 @@ struct FrameProgram
         const FrameCtx& f = ctx;
         const int nr = tile_nranks > 1 ? tile_nranks : 1;
         const int rk = tile_nranks > 1 ? tile_rank : 0;
-        const int local_tile = tile_begin + (int)(item / (VSB_TILE * VSB_TILE));
+        int local_tile = (int)(item / (VSB_TILE * VSB_TILE));
+        if (unit_stride > 1)
+        {
+            local_tile = tile_begin + (local_tile / unit_tiles) * (unit_stride * unit_tiles) + local_tile % unit_tiles;
+            if (local_tile >= n_local_tiles) return false;
+        }
         const int in_tile = (int)(item % (VSB_TILE * VSB_TILE));
         const int block = in_tile / 64, p = in_tile % 64;
         const int lx = (block % 8) * 8 + (p & 7), ly = (block / 8) * 8 + (p >> 3);
