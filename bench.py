@@ -540,7 +540,7 @@ def run_gpu_raylist(args):
     hit_frac = float((d_hits[0][:, 0] != 0).float().mean().item())
 
     # e2e: host ray list in, host hit records out (pinned), H2D + D2H inside the call
-    n_e2e = min(n_batch, 1 << 22)
+    n_e2e = n_batch
     h_rays = torch.from_numpy(rays_h[0][:n_e2e].copy()).pin_memory().numpy()
     h_hits = torch.zeros((n_e2e, 8), dtype=torch.int32).pin_memory().numpy().view(api.N.HIT_DTYPE).reshape(-1)
     fn(dev, h_rays, hits=h_hits, traverse=trav)
@@ -554,6 +554,7 @@ def run_gpu_raylist(args):
     if world > 1:
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_value = n_e2e * e2e_steps * world / float(te.item()) / 1e6
+    e2e_trace_ms = api.last_kernel_ms()           # device time from the first to the last piece's trace of the last call
 
     if rank == 0:
         from oracle import bindings as O              # checker / CPU baseline only
@@ -594,7 +595,8 @@ def run_gpu_raylist(args):
                          "roofline_mrays_s": peak * 1e9 / b_ray / 1e6},
             "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": n_e2e * 32 * world,
-                    "d2h_bytes_per_step": n_e2e * 32 * world, "steps": e2e_steps, "rays_per_step": n_e2e},
+                    "d2h_bytes_per_step": n_e2e * 32 * world, "steps": e2e_steps, "rays_per_step": n_e2e,
+                    "ms_per_step": float(te.item()) * 1e3 / e2e_steps, "trace_ms": e2e_trace_ms},
             "gpu_launches": int(launches), "clocks": clk,
         }
         print(json.dumps(line), flush=True)

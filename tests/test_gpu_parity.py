@@ -425,6 +425,26 @@ def test_scheduling_knobs_do_not_change_results(gpu, scenes):
         gpu.tune("no_such_knob", 1)
 
 
+def test_host_ray_lists_in_pieces(gpu, scenes):
+    """Host ray lists are uploaded, traced and read back piece by piece (H2D / trace / D2H overlapped):
+    same hit records as one piece, ragged last piece, per-ray max_t, both traversals and any-hit."""
+    sc, dev = scenes("cfg3_cubes", 0.004)
+    rays = scene_rays(sc, 300_001, 92)
+    mt = (np.random.default_rng(5).random(rays.shape[0]) * 2.0 + 0.05).astype(np.float32)
+    try:
+        gpu.tune("list_piece_krays", 1 << 20)
+        one = [gpu.closest_hit(dev, rays), gpu.closest_hit(dev, rays, max_t_per_ray=mt),
+               gpu.any_hit(dev, rays, max_t_per_ray=mt, traverse=gpu.TRAVERSE_EXACT), gpu.closest_hit(dev, rays, traverse=gpu.TRAVERSE_EXACT)]
+        gpu.tune("list_piece_krays", 64)
+        many = [gpu.closest_hit(dev, rays), gpu.closest_hit(dev, rays, max_t_per_ray=mt),
+                gpu.any_hit(dev, rays, max_t_per_ray=mt, traverse=gpu.TRAVERSE_EXACT), gpu.closest_hit(dev, rays, traverse=gpu.TRAVERSE_EXACT)]
+        for a, b in zip(one, many):
+            assert a.tobytes() == b.tobytes()
+        assert one[3].tobytes() == O.oracle_query(sc, rays, False).tobytes()
+    finally:
+        gpu.tune("list_piece_krays", 1024)
+
+
 def test_banded_host_target_equals_device_target(gpu, scenes):
     """Host render targets with >= 256 tiles are traced in bands with the D2H of one band overlapping
     the next band's kernel: same pixels as the one-launch device target; also for a compact tile buffer."""

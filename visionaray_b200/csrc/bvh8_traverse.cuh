@@ -38,14 +38,44 @@ struct NodeRegs { uint32_t w[20]; };
 // Loads n16 (2, 3 or 5) 128-bit words of a 16-byte aligned record: a BVH8 node (5), a leaf-order
 // triangle (3) or sphere (2).  One code path for nodes and primitives, so a warp whose lanes are
 // in different phases still issues all its loads together.
+#ifndef VSB_L2_HINT
+#define VSB_L2_HINT 0            // 1: L2 eviction priority by record kind (nodes evict_last, primitives evict_first)
+#endif
+
+#if defined(__CUDA_ARCH__) && VSB_L2_HINT
+__device__ __forceinline__ uint4 ldg_hint(const uint4* p, unsigned long long policy)
+{
+    uint4 v;
+    asm("ld.global.nc.L2::cache_hint.v4.u32 {%0, %1, %2, %3}, [%4], %5;" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p), "l"(policy));
+    return v;
+}
+__device__ __forceinline__ unsigned long long l2_policy(bool keep)
+{
+    unsigned long long pol;
+    if (keep) asm("createpolicy.fractional.L2::evict_last.b64 %0, 1.0;" : "=l"(pol));
+    else      asm("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+#endif
+
 VSB_HD void load_record(const void* __restrict__ addr, int n16, NodeRegs& n)
 {
 #if defined(__CUDA_ARCH__)
     const uint4* p = reinterpret_cast<const uint4*>(addr);
+#if VSB_L2_HINT
+    // the node array (10 % of the scene bytes, re-visited by every ray) should outlive the
+    // leaf-order primitives (visited once in a while) in L2
+    const unsigned long long pol = n16 > 3 ? l2_policy(true) : l2_policy(false);
+    const uint4 a = ldg_hint(p, pol), b = ldg_hint(p + 1, pol);
+    uint4 c = make_uint4(0u, 0u, 0u, 0u), d = c, e = c;
+    if (n16 > 2) c = ldg_hint(p + 2, pol);
+    if (n16 > 3) { d = ldg_hint(p + 3, pol); e = ldg_hint(p + 4, pol); }
+#else
     const uint4 a = __ldg(p), b = __ldg(p + 1);
     uint4 c = make_uint4(0u, 0u, 0u, 0u), d = c, e = c;
     if (n16 > 2) c = __ldg(p + 2);
     if (n16 > 3) { d = __ldg(p + 3); e = __ldg(p + 4); }
+#endif
     n.w[0] = a.x; n.w[1] = a.y; n.w[2] = a.z; n.w[3] = a.w;
     n.w[4] = b.x; n.w[5] = b.y; n.w[6] = b.z; n.w[7] = b.w;
     n.w[8] = c.x; n.w[9] = c.y; n.w[10] = c.z; n.w[11] = c.w;

@@ -66,6 +66,7 @@ int g_sort_rays = 1;
 // frame_bands: a host render target is traced in this many bands so that the D2H copy of one band
 // overlaps the tracing of the next (1 = off)
 int g_host_store = 0;      // 1: frames into PINNED host targets are stored by the trace kernel itself (mapped memory, no staging / D2H pass)
+int g_list_piece_krays = 1024;   // host ray lists are staged, traced and read back in pieces of this many Ki rays
 int g_band_min_mib = 16;   // a band carries at least this much of the target (per-launch ramps vs overlap)
 int g_band_trace = 0;      // developer switch: print the band timeline of host-target frames to stderr
 int g_band_streams = 2;    // 2: alternate bands over two streams (tail of band i overlaps the head of band i+1)
@@ -91,74 +92,110 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
-    const float4* d_rays = reinterpret_cast<const float4*>(rays);
-    uint4* d_hits = reinterpret_cast<uint4*>(hits);
-    const float* d_mt = max_t_per_ray;
-    if (mem == VSB_MEM_HOST)
-    {
-        void *a, *b, *c = nullptr;
-        rc = stage(0, n_rays * sizeof(vsb_ray), &a); if (rc) return rc;
-        rc = stage(1, n_rays * sizeof(vsb_hit), &b); if (rc) return rc;
-        VSB_CUDA(cudaMemcpyAsync(a, rays, n_rays * sizeof(vsb_ray), cudaMemcpyHostToDevice, st));
-        if (max_t_per_ray)
-        {
-            rc = stage(2, n_rays * sizeof(float), &c); if (rc) return rc;
-            VSB_CUDA(cudaMemcpyAsync(c, max_t_per_ray, n_rays * sizeof(float), cudaMemcpyHostToDevice, st));
-        }
-        d_rays = reinterpret_cast<const float4*>(a); d_hits = reinterpret_cast<uint4*>(b); d_mt = reinterpret_cast<const float*>(c);
-    }
-    else if (mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
-
-    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, sizeof(unsigned long long), st));
+    if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
-    // coherence sort (order only: rays are gathered and hits scattered by index, so results land in
-    // the caller's order)
-    const uint32_t* d_order = nullptr;
-    if (g_sort_rays && !exact && n_rays >= (1u << 16) && n_rays < 0x7fffffffull)
+
+    // sort (optional) + trace of one contiguous range of the list, all on `st`
+    auto trace_range = [&](const float4* d_rays, uint4* d_hits, const float* d_mt, size_t n_range, unsigned long long* counter,
+                           cudaStream_t st, int slot_off) -> int
     {
-        void *k0, *k1, *i0, *i1, *tmp;
-        const uint32_t n = (uint32_t)n_rays;
-        rc = stage(6, (size_t)n * 4, &k0); if (rc) return rc;
-        rc = stage(7, (size_t)n * 4, &k1); if (rc) return rc;
-        rc = stage(8, (size_t)n * 4, &i0); if (rc) return rc;
-        rc = stage(9, (size_t)n * 4, &i1); if (rc) return rc;
-        size_t tmp_bytes = 0;
-        VSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, 27, st));
-        rc = stage(10, tmp_bytes, &tmp); if (rc) return rc;
-        const vsb_scene* s0 = scenes[0];
-        float3 lo = make_float3(s0->lo[0], s0->lo[1], s0->lo[2]);
-        float3 inv = make_float3(1.0f / fmaxf(s0->hi[0] - s0->lo[0], 1e-30f), 1.0f / fmaxf(s0->hi[1] - s0->lo[1], 1e-30f),
-                                 1.0f / fmaxf(s0->hi[2] - s0->lo[2], 1e-30f));
-        vsb::ray_key_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rays, n, lo, inv, (uint32_t*)k0, (uint32_t*)i0);
+        // coherence sort (order only: rays are gathered and hits scattered by index, so results land in
+        // the caller's order)
+        const uint32_t* d_order = nullptr;
+        if (g_sort_rays && !exact && n_range >= (1u << 16) && n_range < 0x7fffffffull)
+        {
+            void *k0, *k1, *i0, *i1, *tmp;
+            const uint32_t n = (uint32_t)n_range;
+            int rc2;
+            rc2 = stage(6 + slot_off, (size_t)n * 4, &k0); if (rc2) return rc2;
+            rc2 = stage(7 + slot_off, (size_t)n * 4, &k1); if (rc2) return rc2;
+            rc2 = stage(8 + slot_off, (size_t)n * 4, &i0); if (rc2) return rc2;
+            rc2 = stage(9 + slot_off, (size_t)n * 4, &i1); if (rc2) return rc2;
+            size_t tmp_bytes = 0;
+            VSB_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, VSB_SORT_KEY_BITS, st));
+            rc2 = stage(10 + slot_off, tmp_bytes, &tmp); if (rc2) return rc2;
+            const vsb_scene* s0 = scenes[0];
+            float3 lo = make_float3(s0->lo[0], s0->lo[1], s0->lo[2]);
+            float3 inv = make_float3(1.0f / fmaxf(s0->hi[0] - s0->lo[0], 1e-30f), 1.0f / fmaxf(s0->hi[1] - s0->lo[1], 1e-30f),
+                                     1.0f / fmaxf(s0->hi[2] - s0->lo[2], 1e-30f));
+            vsb::ray_key_kernel<<<(n + 255) / 256, 256, 0, st>>>(d_rays, n, lo, inv, (uint32_t*)k0, (uint32_t*)i0);
+            VSB_CUDA(cudaGetLastError());
+            VSB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, VSB_SORT_KEY_BITS, st));
+            g.launches += 2;
+            d_order = (const uint32_t*)i1;
+        }
+        vsb::RayListProgram prog;
+        prog.order = d_order;
+        prog.rays = d_rays; prog.max_t_per_ray = d_mt; prog.max_t = max_t; prog.hits = d_hits; prog.any = any ? 1 : 0;
+        vsb::TraceLaunch tl;
+        tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_range;
+        tl.work_counter = counter; tl.ray_count = nullptr;
+        tl.service_min = g_query_service_min; tl.phase_min = g_phase_min;
+        {
+            // chunk: ~16 reservations per resident warp, 32..256 rays
+            unsigned long long per = (unsigned long long)n_range / ((unsigned long long)g.sm_count * 32ull * 16ull);
+            per = (per / 32ull) * 32ull;
+            tl.chunk = (unsigned)(per < 32ull ? 32ull : (per > 256ull ? 256ull : per));
+        }
+        if (exact) VSB_CUDA((launch_trace<vsb::RayListProgram, true>(prog, tl, st)));
+        else       VSB_CUDA((launch_trace<vsb::RayListProgram, false>(prog, tl, st)));
+        ++g.launches;
         VSB_CUDA(cudaGetLastError());
-        VSB_CUDA(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, (const uint32_t*)k0, (uint32_t*)k1, (const uint32_t*)i0, (uint32_t*)i1, (int)n, 0, 27, st));
-        g.launches += 2;
-        d_order = (const uint32_t*)i1;
-    }
-    vsb::RayListProgram prog;
-    prog.order = d_order;
-    prog.rays = d_rays; prog.max_t_per_ray = d_mt; prog.max_t = max_t; prog.hits = d_hits; prog.any = any ? 1 : 0;
-    vsb::TraceLaunch tl;
-    tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_rays;
-    tl.work_counter = g.d_work; tl.ray_count = nullptr;
-    tl.service_min = g_query_service_min; tl.phase_min = g_phase_min;
+        return VSB_OK;
+    };
+
+    VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 64 * sizeof(unsigned long long), st));
+    if (mem == VSB_MEM_DEVICE)
     {
-        // chunk: ~16 reservations per resident warp, 32..256 rays
-        unsigned long long per = (unsigned long long)n_rays / ((unsigned long long)g.sm_count * 32ull * 16ull);
-        per = (per / 32ull) * 32ull;
-        tl.chunk = (unsigned)(per < 32ull ? 32ull : (per > 256ull ? 256ull : per));
+        VSB_CUDA(cudaEventRecord(g.ev0, st));
+        rc = trace_range(reinterpret_cast<const float4*>(rays), reinterpret_cast<uint4*>(hits), max_t_per_ray, n_rays, g.d_work, st, 0); if (rc) return rc;
+        VSB_CUDA(cudaEventRecord(g.ev1, st));
+        return VSB_OK;
+    }
+
+    // Host lists: staged in pieces.  The rays of piece i+1 go up (H2D engine, upload stream) and the
+    // hits of piece i-1 come down (D2H engine, copy stream) while piece i is traced.
+    void *a, *b, *c = nullptr;
+    rc = stage(0, n_rays * sizeof(vsb_ray), &a); if (rc) return rc;
+    rc = stage(1, n_rays * sizeof(vsb_hit), &b); if (rc) return rc;
+    if (max_t_per_ray) { rc = stage(2, n_rays * sizeof(float), &c); if (rc) return rc; }
+    size_t piece = (size_t)(g_list_piece_krays < 64 ? 64 : g_list_piece_krays) << 10;
+    if ((n_rays + piece - 1) / piece > 32) piece = (((n_rays + 31) / 32 + 65535) >> 16) << 16;
+    const int n_pieces = (int)((n_rays + piece - 1) / piece);
+    VSB_CUDA(cudaEventRecord(g.band_fork, st));
+    VSB_CUDA(cudaStreamWaitEvent(g.upload_stream, g.band_fork, 0));
+    for (int i = 0; i < n_pieces; ++i)
+    {
+        const size_t r0 = (size_t)i * piece, n = r0 + piece < n_rays ? piece : n_rays - r0;
+        VSB_CUDA(cudaMemcpyAsync((char*)a + r0 * sizeof(vsb_ray), rays + r0, n * sizeof(vsb_ray), cudaMemcpyHostToDevice, g.upload_stream));
+        if (max_t_per_ray) VSB_CUDA(cudaMemcpyAsync((char*)c + r0 * sizeof(float), max_t_per_ray + r0, n * sizeof(float), cudaMemcpyHostToDevice, g.upload_stream));
+        VSB_CUDA(cudaEventRecord(g.band_up[i], g.upload_stream));
     }
     VSB_CUDA(cudaEventRecord(g.ev0, st));
-    if (exact) VSB_CUDA((launch_trace<vsb::RayListProgram, true>(prog, tl, st)));
-    else       VSB_CUDA((launch_trace<vsb::RayListProgram, false>(prog, tl, st)));
-    ++g.launches;
-    VSB_CUDA(cudaGetLastError());
-    VSB_CUDA(cudaEventRecord(g.ev1, st));
-    if (mem == VSB_MEM_HOST)
+    // pieces alternate between two streams (own sort buffers each): the persistent CTAs of piece i+1
+    // are dispatched as those of piece i retire
+    const bool two_streams = n_pieces > 1 && g_band_streams > 1;
+    if (two_streams) VSB_CUDA(cudaStreamWaitEvent(g.band_stream, g.band_fork, 0));
+    for (int i = 0; i < n_pieces; ++i)
     {
-        VSB_CUDA(cudaMemcpyAsync(hits, d_hits, n_rays * sizeof(vsb_hit), cudaMemcpyDeviceToHost, st));
-        VSB_CUDA(cudaStreamSynchronize(st));
+        const size_t r0 = (size_t)i * piece, n = r0 + piece < n_rays ? piece : n_rays - r0;
+        cudaStream_t ps = (two_streams && (i & 1)) ? g.band_stream : st;
+        VSB_CUDA(cudaStreamWaitEvent(ps, g.band_up[i], 0));
+        rc = trace_range(reinterpret_cast<const float4*>(a) + 2 * r0, reinterpret_cast<uint4*>(b) + 2 * r0,
+                         c ? reinterpret_cast<const float*>(c) + r0 : nullptr, n, g.d_work + 2 + i, ps, (two_streams && (i & 1)) ? 6 : 0);
+        if (rc) return rc;
+        VSB_CUDA(cudaEventRecord(g.band_done[i], ps));
+        VSB_CUDA(cudaStreamWaitEvent(g.copy_stream, g.band_done[i], 0));
+        VSB_CUDA(cudaMemcpyAsync(hits + r0, (char*)b + r0 * sizeof(vsb_hit), n * sizeof(vsb_hit), cudaMemcpyDeviceToHost, g.copy_stream));
     }
+    if (two_streams)
+    {
+        VSB_CUDA(cudaEventRecord(g.band_join, g.band_stream));
+        VSB_CUDA(cudaStreamWaitEvent(st, g.band_join, 0));
+    }
+    VSB_CUDA(cudaEventRecord(g.ev1, st));
+    VSB_CUDA(cudaStreamSynchronize(st));
+    VSB_CUDA(cudaStreamSynchronize(g.copy_stream));
     return VSB_OK;
 }
 
@@ -168,7 +205,7 @@ extern "C" int vsb_version(void) { return 100; }
 
 extern "C" int vsb_tune(const char* key, int value)
 {
-    if (!key || value < 0 || value > 64) return VSB_ERR_BAD_ARG;
+    if (!key || value < 0 || value > (1 << 20)) return VSB_ERR_BAD_ARG;
     if (!std::strcmp(key, "query_service_min")) g_query_service_min = value;
     else if (!std::strcmp(key, "frame_service_min")) g_frame_service_min = value;
     else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
@@ -178,6 +215,7 @@ extern "C" int vsb_tune(const char* key, int value)
     else if (!std::strcmp(key, "band_streams")) g_band_streams = value;
     else if (!std::strcmp(key, "band_trace")) g_band_trace = value;
     else if (!std::strcmp(key, "band_min_mib")) g_band_min_mib = value;
+    else if (!std::strcmp(key, "list_piece_krays")) g_list_piece_krays = value;
     else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
     else return VSB_ERR_BAD_ARG;
     return VSB_OK;

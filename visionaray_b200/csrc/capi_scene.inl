@@ -17,8 +17,8 @@ struct Context
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
     unsigned long long* d_work = nullptr;   // persistent-kernel work counter
     vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
-    void*        staging[12] = {};
-    size_t       staging_cap[12] = {};
+    void*        staging[24] = {};
+    size_t       staging_cap[24] = {};
     float        last_ms = 0.0f;
     unsigned long long launches = 0;
 };
@@ -169,7 +169,7 @@ extern "C" int vsb_shutdown(void)
     if (!g.inited) return VSB_OK;
     cudaSetDevice(g.device);
     cudaDeviceSynchronize();
-    for (int i = 0; i < 12; ++i) { if (g.staging[i]) cudaFree(g.staging[i]); g.staging[i] = nullptr; g.staging_cap[i] = 0; }
+    for (int i = 0; i < 24; ++i) { if (g.staging[i]) cudaFree(g.staging[i]); g.staging[i] = nullptr; g.staging_cap[i] = 0; }
     if (g.d_work) cudaFree(g.d_work);
     if (g.d_scenes) cudaFree(g.d_scenes);
     if (g.ev0) cudaEventDestroy(g.ev0);

@@ -261,10 +261,12 @@ trace_kernel(const TraceLaunch tl, const Program prog)
 }
 
 // ---- ray list program: closest_hit()/any_hit() over a ray list ----------------------------------
-// Sort key of a ray for the coherence pre-pass of ray lists: direction octant (3 bits, major) and
-// a 24-bit Morton code of the origin inside the scene bounds (8 bits per axis).  Rays that are
-// neighbours after the sort start close together and head the same way, so the lanes of a warp
-// walk the same part of the tree (L1/L2 hits instead of HBM sector misses).
+// Sort key of a ray for the coherence pre-pass of ray lists: a 21-bit Morton code of the origin
+// inside the scene bounds (7 bits per axis, major) and the direction octant (3 bits, minor).  Rays
+// that are neighbours after the sort start close together and head the same way, so the lanes of a
+// warp walk the same part of the tree (L1/L2 hits instead of HBM sector misses).  Origin-major
+// measured 10 % faster on the random-ray stress than octant-major (short mean free path: where a
+// ray starts decides what it touches); 24 key bits = 3 radix passes.
 __device__ __forceinline__ uint32_t morton_spread8(uint32_t v)
 {
     v = (v | (v << 16)) & 0x030000FFu;
@@ -273,6 +275,17 @@ __device__ __forceinline__ uint32_t morton_spread8(uint32_t v)
     v = (v | (v << 2)) & 0x09249249u;
     return v;
 }
+
+#ifndef VSB_SORT_AXIS_BITS
+#define VSB_SORT_AXIS_BITS 7        // Morton bits per axis of the origin cell (21 + 3 octant bits = 3 radix passes)
+#endif
+#ifndef VSB_SORT_OCT_LOW
+#define VSB_SORT_OCT_LOW 1          // 0: direction octant is the major key; 1: the origin cell is (measured +10 % on cfg5)
+#endif
+#ifndef VSB_SORT_NO_OCT
+#define VSB_SORT_NO_OCT 0
+#endif
+#define VSB_SORT_KEY_BITS (3 * VSB_SORT_AXIS_BITS + (VSB_SORT_NO_OCT ? 0 : 3))
 
 __global__ void ray_key_kernel(const float4* __restrict__ rays, uint32_t n, float3 lo, float3 inv_extent,
                                uint32_t* __restrict__ keys, uint32_t* __restrict__ index)
@@ -283,9 +296,11 @@ __global__ void ray_key_kernel(const float4* __restrict__ rays, uint32_t n, floa
     const float fx = fminf(fmaxf((o.x - lo.x) * inv_extent.x, 0.0f), 0.999f);
     const float fy = fminf(fmaxf((o.y - lo.y) * inv_extent.y, 0.0f), 0.999f);
     const float fz = fminf(fmaxf((o.z - lo.z) * inv_extent.z, 0.0f), 0.999f);
-    const uint32_t qx = (uint32_t)(fx * 256.0f), qy = (uint32_t)(fy * 256.0f), qz = (uint32_t)(fz * 256.0f);
+    const float cells = (float)(1 << VSB_SORT_AXIS_BITS);
+    const uint32_t qx = (uint32_t)(fx * cells), qy = (uint32_t)(fy * cells), qz = (uint32_t)(fz * cells);
     const uint32_t oct = (d.x < 0.0f ? 1u : 0u) | (d.y < 0.0f ? 2u : 0u) | (d.z < 0.0f ? 4u : 0u);
-    keys[i] = (oct << 24) | morton_spread8(qx) | (morton_spread8(qy) << 1) | (morton_spread8(qz) << 2);
+    const uint32_t cell = morton_spread8(qx) | (morton_spread8(qy) << 1) | (morton_spread8(qz) << 2);
+    keys[i] = VSB_SORT_NO_OCT ? cell : VSB_SORT_OCT_LOW ? ((cell << 3) | oct) : ((oct << (3 * VSB_SORT_AXIS_BITS)) | cell);
     index[i] = i;
 }
 
