@@ -9,14 +9,26 @@ def load(path):
         if len(r)>5 and r[0]=="Line No": h=r; continue
         if h and len(r)==len(h) and r[0] not in("","Line No") and r[2]=="-": L.append((fname,int(r[0]),r))
     return h,L
+import os, re
+def _function_starts():
+    """line number of every top-level function of bvh8_traverse.cuh (regions follow the source, not fixed lines)"""
+    path=os.path.join(os.path.dirname(os.path.abspath(__file__)),"..","visionaray_b200","csrc","bvh8_traverse.cuh")
+    out=[]
+    for i,l in enumerate(open(path),1):
+        m=re.match(r"^(?:VSB_HD|__device__ __forceinline__)\s+[\w: ]+?\s+(\w+)\(",l)
+        if m: out.append((i,m.group(1)))
+    return out
+_FN=_function_starts()
+_KIND={"test_node":"node_test","perm_xor8":"node_test","test_prim":"prim_test (record decode, accept)","load_record":"record loads","ldg_hint":"record loads",
+       "ray_ctx_init":"ray_init","stack_push":"stack","stack_pop":"stack","trav_begin":"stack","trav_step":"trav_step control"}
 def region(fn, ln, src):
     if fn=="bvh8_traverse.cuh":
-        if "test_node" in src or 56<=ln<=118: return "node_test"
-        if 119<=ln<=150: return "prim_test"
-        if ln<56: return "ray_init/load_record"
-        return "trav_step control/stack"
+        name=""
+        for start,n in _FN:
+            if start<=ln: name=n
+        return _KIND.get(name,"trav_step control")
     if fn=="bvh8.cuh": return "node_test"
-    if fn=="vsb_common.cuh": return "prim_test / shading arithmetic"
+    if fn=="vsb_common.cuh": return "isect_triangle / rn arithmetic (vsb_common.cuh)"
     if fn=="kernels.cuh": return "kernel loop (service, refill, program)"
     if fn=="shade.cuh": return "shade programs"
     return fn

@@ -199,9 +199,24 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
 #ifndef VSB_STEP_MODE
 #define VSB_STEP_MODE 0     // measured: chaining costs a second exposed latency per step (cfg5 +29 % time)
 #endif
+#ifndef VSB_PREFETCH_PUSH
+#define VSB_PREFETCH_PUSH 0   // 1 / 2: prefetch (L2 / L1) the next sibling of a node group when it is pushed
+#endif
 #ifndef VSB_PREFETCH
 #define VSB_PREFETCH 0     // measured: no gain (the unified loads already overlap); kept as a switch
 #endif
+
+// The deep part of the stack lives in its own (local-memory) object: kept inside TravState, its
+// dynamically indexed arrays dragged the whole struct -- node group, primitive group, stack pointer
+// -- into local memory, one LDL/STL per field access in the traversal loop.
+struct TravSpill
+{
+#if defined(__CUDACC__)
+    uint32_t b[VSB_STACK_SIZE - VSB_SHARED_STACK], m[VSB_STACK_SIZE - VSB_SHARED_STACK];
+#else
+    uint32_t b[VSB_STACK_SIZE], m[VSB_STACK_SIZE];
+#endif
+};
 
 struct TravState
 {
@@ -209,20 +224,24 @@ struct TravState
     uint32_t pg_base, pg_mask;      // current primitive group
     int      sp;
 #if defined(__CUDACC__)
-    uint32_t* sstack;               // this thread's column of the block's shared stack: entry k at [2k*128], [(2k+1)*128]
-    uint32_t stack_b[VSB_STACK_SIZE - VSB_SHARED_STACK], stack_m[VSB_STACK_SIZE - VSB_SHARED_STACK];
-#else
-    uint32_t stack_b[VSB_STACK_SIZE], stack_m[VSB_STACK_SIZE];
+    uint32_t sstack;                // shared-window byte address of this thread's column of the block's stack:
+                                    // entry k at words [2k*128], [(2k+1)*128] (one 32-bit register, no generic pointer)
 #endif
+    TravSpill* spill;               // set by the owner of the state
 };
 
 VSB_HD void stack_push(TravState& t, uint32_t b, uint32_t m)
 {
 #if defined(__CUDACC__)
-    if (t.sp < VSB_SHARED_STACK) { t.sstack[(2 * t.sp) * 128] = b; t.sstack[(2 * t.sp + 1) * 128] = m; }
-    else { t.stack_b[t.sp - VSB_SHARED_STACK] = b; t.stack_m[t.sp - VSB_SHARED_STACK] = m; }
+    if (t.sp < VSB_SHARED_STACK)
+    {
+        const uint32_t a = t.sstack + (uint32_t)t.sp * 1024u;
+        asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(b) : "memory");
+        asm volatile("st.shared.u32 [%0+512], %1;" :: "r"(a), "r"(m) : "memory");
+    }
+    else { t.spill->b[t.sp - VSB_SHARED_STACK] = b; t.spill->m[t.sp - VSB_SHARED_STACK] = m; }
 #else
-    t.stack_b[t.sp] = b; t.stack_m[t.sp] = m;
+    t.spill->b[t.sp] = b; t.spill->m[t.sp] = m;
 #endif
     ++t.sp;
 }
@@ -231,10 +250,15 @@ VSB_HD void stack_pop(TravState& t, uint32_t& b, uint32_t& m)
 {
     --t.sp;
 #if defined(__CUDACC__)
-    if (t.sp < VSB_SHARED_STACK) { b = t.sstack[(2 * t.sp) * 128]; m = t.sstack[(2 * t.sp + 1) * 128]; }
-    else { b = t.stack_b[t.sp - VSB_SHARED_STACK]; m = t.stack_m[t.sp - VSB_SHARED_STACK]; }
+    if (t.sp < VSB_SHARED_STACK)
+    {
+        const uint32_t a = t.sstack + (uint32_t)t.sp * 1024u;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(b) : "r"(a) : "memory");
+        asm volatile("ld.shared.u32 %0, [%1+512];" : "=r"(m) : "r"(a) : "memory");
+    }
+    else { b = t.spill->b[t.sp - VSB_SHARED_STACK]; m = t.spill->m[t.sp - VSB_SHARED_STACK]; }
 #else
-    b = t.stack_b[t.sp]; m = t.stack_m[t.sp];
+    b = t.spill->b[t.sp]; m = t.spill->m[t.sp];
 #endif
 }
 
@@ -273,6 +297,9 @@ VSB_HD void prefetch_prims(const void* prims, uint32_t base, uint32_t mask, uint
 // is finished (stack empty, or `any` and a hit was accepted: exit_traversal.h:49-57).
 VSB_HD bool trav_prim_mode(const TravState& t) { return t.pg_mask != 0u; }
 
+// (A "paired" mode -- a lane down to its last pending primitive takes its next node visit in the same
+// step, both record loads issued together -- was measured at 0.6-0.7x: two live records per lane cost
+// more registers / spills than the saved iterations give back.)
 VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg& best, float& limit, bool any)
 {
     NodeRegs n;
@@ -344,7 +371,23 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
         n16 = 5;
         addr = reinterpret_cast<const char*>(s.nodes + (t.ng_base + rel));
-        if (t.ng_mask & 0xff000000u) stack_push(t, t.ng_base, t.ng_mask);
+        if (t.ng_mask & 0xff000000u)
+        {
+            stack_push(t, t.ng_base, t.ng_mask);
+#if defined(__CUDA_ARCH__) && VSB_PREFETCH_PUSH
+            // the sibling this ray visits after the subtree it is about to enter
+            const int bit2 = find_msb(t.ng_mask);
+            const uint32_t slot2 = ((uint32_t)(bit2 - 24) ^ (r.octinv4 & 0xffu)) & 7u;
+            const char* a2 = reinterpret_cast<const char*>(s.nodes + (t.ng_base + (uint32_t)pop_count(imask & ~(0xffffffffu << slot2))));
+#if VSB_PREFETCH_PUSH == 1
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(a2));
+            asm volatile("prefetch.global.L2 [%0];" :: "l"(a2 + 64));
+#else
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(a2));
+            asm volatile("prefetch.global.L1 [%0];" :: "l"(a2 + 64));
+#endif
+#endif
+        }
     }
 
     load_record(addr, n16, n);
@@ -397,7 +440,9 @@ VSB_HD void trace_wide(const WideScene& s, const RayCtx& r, float max_t, HitReg&
 {
     hit_reset(best);
     float limit = max_t;
+    TravSpill spill;
     TravState t;
+    t.spill = &spill;
     trav_begin(t);
     while (trav_step(s, r, t, best, limit, ANY)) { }
 }

@@ -165,8 +165,10 @@ trace_kernel(const TraceLaunch tl, const Program prog)
     bool any = false;
     int scene_i = 0;
     WideScene sc = tl.scenes[0].wide;
+    TravSpill spill;
     TravState t; trav_begin(t);
-    t.sstack = lane_store_raw + threadIdx.x;
+    t.spill = &spill;
+    t.sstack = (uint32_t)__cvta_generic_to_shared(lane_store_raw + threadIdx.x);
     RayReq req;
 
     for (;;)
