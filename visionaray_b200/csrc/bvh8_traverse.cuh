@@ -164,7 +164,7 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
     if (prim_kind == 0)
     {
         // TriRec: v1 | prim_id, e1 | geom_id, e2 | list_index
-        float t, u, v;
+        float t = -1.0f, u = 0.0f, v = 0.0f;      // initialised: left undefined, u / v were kept in local memory across the early-outs
         if (isect_triangle(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]),
                            u2f(n.w[4]), u2f(n.w[5]), u2f(n.w[6]), u2f(n.w[8]), u2f(n.w[9]), u2f(n.w[10]), t, u, v)
             && t >= 0.0f && t < limit)

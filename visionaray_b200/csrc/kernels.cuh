@@ -145,7 +145,7 @@ __device__ __forceinline__ bool phase_runs(int phase_min, bool prim_mode)
 }
 
 template <typename Program, bool EXACT>
-__global__ void __launch_bounds__(VSB_BLOCK, VSB_MIN_BLOCKS)
+__global__ void __launch_bounds__(VSB_BLOCK, Program::MIN_BLOCKS)
 trace_kernel(const TraceLaunch tl, const Program prog)
 {
     extern __shared__ uint32_t lane_store_raw[];
@@ -321,6 +321,10 @@ struct RayListProgram
         __device__ Lane(uint32_t*, unsigned) : item(0) {}
     };
     static constexpr int STATE_WORDS = 0;
+#ifndef VSB_LIST_MIN_BLOCKS
+#define VSB_LIST_MIN_BLOCKS VSB_MIN_BLOCKS
+#endif
+    static constexpr int MIN_BLOCKS = VSB_LIST_MIN_BLOCKS;
 
     __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
     {

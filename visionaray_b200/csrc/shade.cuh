@@ -266,6 +266,10 @@ struct FrameProgram
     int n_local_tiles;
 
     using Lane = FrameLane;
+#ifndef VSB_FRAME_MIN_BLOCKS
+#define VSB_FRAME_MIN_BLOCKS 6
+#endif
+    static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
     static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? 17 : (KERNEL == 0 ? 0 : 6));
 
