@@ -231,6 +231,18 @@ def run_reference(args):
 # GPU arm
 # ------------------------------------------------------------------------------------------------
 
+def make_device_scene(api, sc, args):
+    """The device scene of the run.  --builder reference (default): the tree of the reference's
+    binned-SAH builder (host, include/visionaray_b200/bvh.h reproduces it byte for byte), uploaded and
+    re-encoded.  --builder gpu: the tree is built on the GPU from the primitives (vsb_scene_build)."""
+    if args.builder == "gpu":
+        dev = api.Scene.build(sc.prim_kind, sc.prims, sc.normals)
+        ms = api.last_build_ms()
+        return dev, {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2),
+                     "iterations": ms["iterations"]}
+    return api.Scene(sc), {"kind": "reference binned SAH (host)"}
+
+
 def run_gpu(args):
     import torch
     import torch.distributed as dist
@@ -251,7 +263,7 @@ def run_gpu(args):
     wl = WORKLOADS[args.workload]
     w, h = frame_shape(wl, world)
     sc = S.make_scene(wl["scene"], args.scale)
-    dev = api.Scene(sc)
+    dev, builder = make_device_scene(api, sc, args)
     stats = dev.stats()
     mats, lights = S.default_material(wl["mat"]), S.point_light(wl["eye"])
     d_mats = torch.from_numpy(mats.view(np.float32).copy()).cuda()
@@ -448,7 +460,8 @@ def run_gpu(args):
                                        "nccl": ", NCCL all-gather + de-interleave per frame on a side stream"}[mode],
                        "assembled_frame_verified": verified,
                        "l2": f"framebuffer {w * h * 16 >> 20} MiB rewritten every step + scene {(stats['wide_node_bytes'] + stats['wide_prim_bytes']) >> 20} MiB (> 126 MB L2 together)",
-                       "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "triangles": sc.n_prims},
+                       "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "triangles": sc.n_prims,
+                       "builder": builder},
             "roofline": roofline, "cpu_baseline": cpu,
             "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "steps": e2e_steps, "ms_per_step": float(te.item()) * 1e3 / e2e_steps, "trace_ms": e2e_trace_ms},
@@ -485,7 +498,7 @@ def run_gpu_raylist(args):
     t0 = time.time()
     sc = S.make_scene("cfg5_soup", args.scale)
     build_s = time.time() - t0
-    dev = api.Scene(sc)
+    dev, builder = make_device_scene(api, sc, args)
     stats = dev.stats()
     n_batch = args.batch
     n_bufs = 4                                            # rotate batches: 4 x (512 MiB rays + 512 MiB hits) >> L2
@@ -586,6 +599,7 @@ def run_gpu_raylist(args):
                                    f"batches of {n_batch} rays per GPU", "traverse": args.traverse, "scale": args.scale,
                        "l2": f"{n_bufs} rotating ray/hit batches ({n_bufs * n_batch * 64 >> 20} MiB) + scene "
                              f"{(stats['wide_node_bytes'] + stats['wide_prim_bytes']) >> 20} MiB, all > 126 MB L2",
+                       "builder": builder,
                        "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "bvh2_depth": stats["bvh2_depth"],
                        "host_build_s": build_s, "hit_fraction": hit_frac},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
@@ -617,6 +631,8 @@ def main():
     ap.add_argument("--any", action="store_true", help="cfg5: any-hit instead of closest-hit")
     ap.add_argument("--batch", type=int, default=1 << 24, help="cfg5: rays per batch")
     ap.add_argument("--traverse", default="wide", choices=["wide", "exact"])
+    ap.add_argument("--builder", default="reference", choices=["reference", "gpu"],
+                    help="whose BVH the scene uses: the reference's host builder, or the GPU builder (vsb_scene_build)")
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--gather", default="peer", choices=["peer", "nccl"], help="N > 1: how the frame is assembled")

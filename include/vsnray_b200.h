@@ -189,6 +189,22 @@ int  vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
                       const vsb_bvh_node* nodes, size_t n_nodes,
                       const uint32_t* indices, size_t n_indices,
                       vsb_scene** out);
+/* The same scene with the BVH BUILT ON THE GPU from the primitives alone: replaces
+ * build<index_bvh<P>>(first, last) (bvh.h:455 -> detail/bvh/build.inl:28-140 -> binned_sah_builder,
+ * detail/bvh/sah.h:150-762; one host thread, recursive) followed by the upload above.  Morton sort +
+ * parallel locally-ordered clustering + SAH leaf collapse (<= 4 primitives per leaf), laid out in
+ * the reference's node / indices format, then re-encoded into the BVH8 like any other tree.  Closest
+ * hits are those of the reference's tree up to t-ties (any valid BVH); any-hit winners and
+ * primitive_list_index follow THIS tree's order.  prims: host or device memory (mem = VSB_MEM_*).
+ * Knobs (vsb_tune): "build_radius" (1..32, default 8), "build_cost_node_x100", "build_cost_prim_x100". */
+int  vsb_scene_build(int prim_kind, const void* prims, size_t n_prims, int mem, vsb_scene** out);
+/* the scene's reference-layout tree back on the host -- what index_bvh<P>::nodes() / indices() hold
+ * (bvh.h:298-403); sizes from vsb_scene_stats (out[5] nodes; indices = n_prims).  Either pointer may be NULL. */
+int  vsb_scene_download_bvh(const vsb_scene* s, vsb_bvh_node* nodes_out, size_t nodes_cap,
+                            uint32_t* indices_out, size_t indices_cap);
+/* device time of the last vsb_scene_build(): ms4[0] total (events on the library stream, host round
+ * trips included), [1] bounds + sort, [2] clustering, [3] layout + wide re-encode; iterations may be NULL */
+int  vsb_last_build_ms(float* ms4, int* iterations);
 int  vsb_scene_destroy(vsb_scene* s);
 /* per-face normals kept on the device with the scene (what a cuda_sched user holds in a thrust
  * device_vector and hands to make_kernel_params, src/viewer/viewer.cpp:507-521); n = n_prims */

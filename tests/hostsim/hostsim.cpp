@@ -9,6 +9,9 @@
 
 #include "../../visionaray_b200/csrc/bvh8_traverse.cuh"
 #include "../../visionaray_b200/csrc/bvh2_exact.cuh"
+#include "../../visionaray_b200/csrc/build_ploc.cuh"
+#include <algorithm>
+#include <numeric>
 
 using namespace vsb;
 
@@ -128,6 +131,66 @@ void hs_query_exact(int prim_kind, int any, const void* prims, const void* nodes
         out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
         out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
     }
+}
+
+// Serial form of the GPU builder (csrc/build_ploc.cuh, driven like capi_build.inl drives the
+// kernels): same element functions, same order of steps, so the tree is the GPU's bit for bit.
+// Returns the number of nodes written (0 if the capacity is too small); info[0] = depth,
+// info[1] = PLOC iterations, info[2] = emitted leaves.
+size_t hs_build_ploc(int prim_kind, const void* prims, size_t n_prims, int radius, float cost_node, float cost_prim,
+                     void* nodes_out, size_t cap_nodes, uint32_t* indices_out, uint32_t* info)
+{
+    const uint32_t n = (uint32_t)n_prims;
+    BuildParams bp{ radius, cost_node, cost_prim };
+    std::vector<BNode> boxes(n), bn(2 * (size_t)n - 1), cl[2];
+    std::vector<BSub> sub(2 * (size_t)n - 1);
+    std::vector<uint32_t> parent(2 * (size_t)n - 1, BN_NONE), nn(n), vals(n);
+    std::vector<uint64_t> keys(n), flags(n), scan(n);
+    float cb[6] = { FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX };
+    for (uint32_t i = 0; i < n; ++i)
+    {
+        boxes[i] = prim_bounds(prim_kind, prims, i);
+        const BNode& b = boxes[i];
+        const float c[3] = { 0.5f * (b.lox + b.hix), 0.5f * (b.loy + b.hiy), 0.5f * (b.loz + b.hiz) };
+        for (int k = 0; k < 3; ++k) { cb[k] = std::min(cb[k], c[k]); cb[3 + k] = std::max(cb[3 + k], c[k]); }
+    }
+    for (uint32_t i = 0; i < n; ++i) { keys[i] = morton_of(boxes[i], cb); vals[i] = i; }
+    std::stable_sort(vals.begin(), vals.end(), [&](uint32_t a, uint32_t b) { return keys[a] < keys[b]; });
+    cl[0].resize(n); cl[1].resize(n);
+    for (uint32_t s = 0; s < n; ++s)
+    {
+        BNode b = boxes[vals[s]];
+        bn[s] = b; sub[s] = leaf_sub(b, bp);
+        b.left = s; b.right = 0u; cl[0][s] = b;
+    }
+    uint32_t m = n, merged = 0, iters = 0; int cur = 0;
+    while (m > 1)
+    {
+        for (uint32_t i = 0; i < m; ++i) nn[i] = ploc_nearest(cl[cur].data(), 0, i, m, radius);
+        uint64_t acc = 0;
+        for (uint32_t i = 0; i < m; ++i) { flags[i] = ploc_flags(nn.data(), i); scan[i] = acc; acc += flags[i]; }
+        for (uint32_t i = 0; i < m; ++i)
+            ploc_emit(cl[cur].data(), nn.data(), scan.data(), i, n, merged, bp, bn.data(), sub.data(), parent.data(), cl[cur ^ 1].data());
+        m = (uint32_t)(acc & 0xffffffffull); merged += (uint32_t)(acc >> 32);
+        cur ^= 1; ++iters;
+    }
+    const uint32_t root = cl[cur][0].left;
+    const size_t n_out = 2 * (size_t)sub[root].lcnt - 1;
+    info[1] = iters; info[2] = sub[root].lcnt;
+    if (n_out > cap_nodes) return 0;
+    Node32* nodes = reinterpret_cast<Node32*>(nodes_out);
+    std::vector<BTask> tasks(1), next(n + 1);
+    tasks[0].node = root; tasks[0].out = 0; tasks[0].prim_off = 0; tasks[0].rank_off = 0;
+    uint32_t levels = 0;
+    while (!tasks.empty())
+    {
+        uint32_t cnt = 0; Alloc a{ &cnt };
+        for (auto const& t : tasks) layout_task(t, bn.data(), sub.data(), nodes, indices_out, next.data(), a);
+        tasks.assign(next.begin(), next.begin() + cnt);
+        ++levels;
+    }
+    info[0] = (sub[root].cnt & BS_LEAF) ? 1u : levels + 1u;
+    return n_out;
 }
 
 } // extern "C"

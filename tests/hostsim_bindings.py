@@ -31,6 +31,8 @@ def lib():
         l.hs_prims.argtypes = [vp]
         l.hs_query_wide.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp, vp]
         l.hs_query_exact.argtypes = [C.c_int, C.c_int, vp, vp, vp, vp, sz, C.c_float, vp, vp]
+        l.hs_build_ploc.restype = sz
+        l.hs_build_ploc.argtypes = [C.c_int, vp, sz, C.c_int, C.c_float, C.c_float, vp, sz, vp, vp]
         _lib = l
     return _lib
 
@@ -81,6 +83,22 @@ def query_exact(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_p
     lib().hs_query_exact(scene.prim_kind, int(any_hit), _p(scene.prims), _p(scene.nodes), _p(scene.indices), _p(rays),
                          rays.shape[0], max_t, _p(max_t_per_ray), _p(hits))
     return hits
+
+
+NODE_DTYPE = np.dtype(
+    [("bbox_min", "<f4", (3,)), ("first", "<u4"), ("bbox_max", "<f4", (3,)), ("num_prims", "<u4")]
+)
+
+
+def build_ploc(prim_kind, prims, radius=8, cost_node=1.0, cost_prim=1.0):
+    """Serial instantiation of the GPU builder (csrc/build_ploc.cuh): (nodes, indices, info)."""
+    n = prims.shape[0]
+    nodes = np.zeros(max(2 * n - 1, 1), dtype=NODE_DTYPE)
+    idx = np.zeros(n, dtype=np.uint32)
+    info = np.zeros(4, dtype=np.uint32)
+    nn = lib().hs_build_ploc(prim_kind, _p(prims), n, radius, cost_node, cost_prim, _p(nodes), nodes.shape[0], _p(idx), _p(info))
+    assert nn > 0
+    return nodes[:nn].copy(), idx, dict(depth=int(info[0]), iterations=int(info[1]), leaves=int(info[2]))
 
 
 def decode_wide_nodes(nodes: np.ndarray):

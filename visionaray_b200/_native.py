@@ -69,7 +69,7 @@ class FrameDesc(C.Structure):
 # every symbol include/vsnray_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
-    "vsb_scene_create", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
+    "vsb_scene_create", "vsb_scene_build", "vsb_scene_download_bvh", "vsb_last_build_ms", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_ipc_export", "vsb_ipc_open", "vsb_ipc_close", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
@@ -111,6 +111,9 @@ def cuda_lib() -> C.CDLL:
                     raise RuntimeError(f"VSB_TUNE: bad setting {kv!r}")
         lib.vsb_scene_create.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, C.POINTER(vp)]
         lib.vsb_scene_destroy.argtypes = [vp]
+        lib.vsb_scene_build.argtypes = [C.c_int, vp, sz, C.c_int, C.POINTER(vp)]
+        lib.vsb_scene_download_bvh.argtypes = [vp, vp, sz, vp, sz]
+        lib.vsb_last_build_ms.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int)]
         lib.vsb_scene_set_normals.argtypes = [vp, vp, sz, C.c_int]
         lib.vsb_scene_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
         lib.vsb_scene_download_wide.argtypes = [vp, vp, sz, vp, sz]

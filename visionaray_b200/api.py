@@ -59,6 +59,14 @@ def launch_count() -> int:
     return n.value
 
 
+def last_build_ms() -> dict:
+    """Device time of the last Scene.build(): total / sort / clustering / layout + re-encode, iterations."""
+    ms = (C.c_float * 4)()
+    it = C.c_int(0)
+    _check(N.cuda_lib().vsb_last_build_ms(ms, C.byref(it)), "vsb_last_build_ms")
+    return dict(total_ms=ms[0], sort_ms=ms[1], cluster_ms=ms[2], layout_encode_ms=ms[3], iterations=it.value)
+
+
 def last_kernel_ms() -> float:
     ms = C.c_float(0)
     _check(N.cuda_lib().vsb_last_kernel_ms(C.byref(ms)), "vsb_last_kernel_ms")
@@ -80,6 +88,36 @@ class Scene:
         self.handle = h
         if host_scene.normals is not None:
             self.set_normals(host_scene.normals)
+
+    @classmethod
+    def build(cls, prim_kind: int, prims, normals=None) -> "Scene":
+        """The BVH is built on the GPU from the primitives alone (vsb_scene_build): replaces
+        build<index_bvh<P>>() (bvh.h:455, detail/bvh/{build.inl,sah.h}) + the upload.
+        prims: numpy array (host) or torch CUDA tensor of 64-byte triangles / 48-byte spheres."""
+        self = cls.__new__(cls)
+        self.host = None
+        h = C.c_void_p(0)
+        if isinstance(prims, np.ndarray):
+            p, n, mem = N.ptr(prims), prims.shape[0], MEM_HOST
+        else:
+            p, n, mem = C.c_void_p(prims.data_ptr()), prims.shape[0], MEM_DEVICE
+        self.handle = None
+        _check(N.cuda_lib().vsb_scene_build(prim_kind, p, n, mem, C.byref(h)), "vsb_scene_build")
+        self.handle = h
+        self.n_prims = n
+        if normals is not None:
+            self.set_normals(normals)
+        return self
+
+    def download_bvh(self):
+        """(nodes, indices) of the scene's reference-layout tree (index_bvh<P>::nodes()/indices())."""
+        st = self.stats()
+        nodes = np.zeros(st["bvh2_nodes"], dtype=N.NODE_DTYPE)
+        n_idx = self.n_prims if self.host is None else (self.host.indices.shape[0] if self.host.indices is not None else 0)
+        idx = np.zeros(n_idx, dtype=np.uint32)
+        _check(N.cuda_lib().vsb_scene_download_bvh(self.handle, N.ptr(nodes), nodes.shape[0],
+                                                   N.ptr(idx) if n_idx else None, n_idx), "vsb_scene_download_bvh")
+        return nodes, idx
 
     def set_normals(self, normals):
         """Per-face normals (n_prims x 4 float32) kept on the device with the scene."""

@@ -10,11 +10,14 @@
 
 #include <cuda_runtime.h>
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
 
 #include "../../include/vsnray_b200.h"
 #include "kernels.cuh"
+#include "build_ploc.cuh"
 
 #include "capi_scene.inl"
+#include "capi_build.inl"
 
 namespace
 {
@@ -39,6 +42,14 @@ int upload_scene_table(const vsb_scene* const* scenes, int n_scenes, cudaStream_
     }
     VSB_CUDA(cudaMemcpyAsync(g.d_scenes, tab, sizeof(vsb::DeviceScene) * n_scenes, cudaMemcpyHostToDevice, st));
     return VSB_OK;
+}
+
+// the reference-order walk keeps its stack in VSB_EXACT_STACK entries; a GPU-built tree may be deeper
+bool exact_supported(const vsb_scene* const* scenes, int n_scenes)
+{
+    for (int i = 0; i < n_scenes; ++i)
+        if (scenes[i]->depth2 > VSB_EXACT_STACK - 1) return false;
+    return true;
 }
 
 // grid = resident CTAs per SM x SM count (persistent warps pull work from the queue), capped by the
@@ -94,6 +105,7 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
 
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
+    if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
 
     // sort (optional) + trace of one contiguous range of the list, all on `st`
     auto trace_range = [&](const float4* d_rays, uint4* d_hits, const float* d_mt, size_t n_range, unsigned long long* counter,
@@ -217,6 +229,9 @@ extern "C" int vsb_tune(const char* key, int value)
     else if (!std::strcmp(key, "band_min_mib")) g_band_min_mib = value;
     else if (!std::strcmp(key, "list_piece_krays")) g_list_piece_krays = value;
     else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
+    else if (!std::strcmp(key, "build_radius")) g_build_radius = value;
+    else if (!std::strcmp(key, "build_cost_node_x100")) g_build_cost_node = 0.01f * (float)value;
+    else if (!std::strcmp(key, "build_cost_prim_x100")) g_build_cost_prim = 0.01f * (float)value;
     else return VSB_ERR_BAD_ARG;
     return VSB_OK;
 }
@@ -439,6 +454,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
 
     VSB_CUDA(cudaMemsetAsync(g.d_work, 0, 64 * sizeof(unsigned long long), st));
     const bool exact = d->traverse == VSB_TRAVERSE_EXACT;
+    if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
     tl.chunk = VSB_FRAME_CHUNK; tl.ray_count = fl.ray_count;

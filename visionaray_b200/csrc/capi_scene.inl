@@ -213,51 +213,15 @@ extern "C" int vsb_scene_destroy(vsb_scene* s)
     return VSB_OK;
 }
 
-extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
-                                const vsb_bvh_node* nodes, size_t n_nodes,
-                                const uint32_t* indices, size_t n_indices, vsb_scene** out)
+namespace
 {
-    int rc = require_init(); if (rc) return rc;
-    if (!prims || !nodes || !out || n_prims == 0 || n_nodes == 0) return VSB_ERR_BAD_ARG;
-    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE) return VSB_ERR_BAD_ARG;
-    if (n_nodes >= 0x7fffffffull || n_prims >= 0x7fffffffull) return VSB_ERR_UNSUPPORTED;
 
-    bool big = false;
-    const int depth = validate_tree(nodes, n_nodes, indices, n_indices, n_prims, &big);
-    if (depth < 0) return depth;
-    if (depth > VSB_EXACT_STACK - 1 || depth > VSB_STACK_SIZE - 1) return VSB_ERR_BAD_TREE;
-
-    vsb_scene* s = new vsb_scene();
-    s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_nodes2 = n_nodes; s->n_idx = indices ? n_indices : 0;
-    s->depth2 = depth;
-    for (int i = 0; i < 3; ++i) { s->lo[i] = nodes[0].bbox_min[i]; s->hi[i] = nodes[0].bbox_max[i]; }
-    const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
-    const size_t rec_bytes = prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
-    const size_t list_len = indices ? n_indices : n_prims;
-
-#define VSB_SCENE_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { vsb_scene_destroy(s); return (int)e__; } } while (0)
-    VSB_SCENE_CUDA(cudaMalloc(&s->d_prims, n_prims * prim_bytes));
-    VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_nodes2, n_nodes * sizeof(vsb::Node32)));
-    if (indices) VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_indices, n_indices * sizeof(uint32_t)));
-    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_prims, prims, n_prims * prim_bytes, cudaMemcpyHostToDevice, g.stream));
-    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_nodes2, nodes, n_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice, g.stream));
-    if (indices) VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_indices, indices, n_indices * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
-
-    // BVH2 used for the encode: the caller's tree, or a normalised copy when it has big leaves
-    vsb::Node32* d_enc_nodes = s->d_nodes2;
-    size_t n_enc_nodes = n_nodes;
-    vsb::Node32* d_norm = nullptr;
-    if (big)
-    {
-        std::vector<vsb_bvh_node> norm(nodes, nodes + n_nodes);
-        normalise_leaves(norm);
-        n_enc_nodes = norm.size();
-        VSB_SCENE_CUDA(cudaMalloc((void**)&d_norm, n_enc_nodes * sizeof(vsb::Node32)));
-        VSB_SCENE_CUDA(cudaMemcpy(d_norm, norm.data(), n_enc_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice));
-        d_enc_nodes = d_norm;
-    }
-
-    // GPU re-encode, level by level
+// GPU re-encode BVH2 -> BVH8 of a scene whose reference-layout arrays (d_prims, d_nodes2, d_indices)
+// are on the device.  d_enc_nodes: the BVH2 to collapse (the scene's own, or a normalised copy with
+// <= 4 primitives per leaf).  On failure the caller destroys the scene.
+int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size_t list_len)
+{
+    const size_t rec_bytes = s->prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
     uint32_t* d_leaf_list = nullptr; vsb::WideTask* d_tasks[2] = { nullptr, nullptr }; uint32_t* d_counters = nullptr;
     uint32_t* d_parent = nullptr; uint32_t* d_arrived = nullptr; vsb::CollapseCost* d_cost = nullptr; vsb::CollapseDec* d_dec = nullptr;
     const size_t wide_cap = n_enc_nodes;   // a wide node consumes >= 1 BVH2 inner node
@@ -268,13 +232,12 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
         if (d_tasks[0]) cudaFree(d_tasks[0]);
         if (d_tasks[1]) cudaFree(d_tasks[1]);
         if (d_counters) cudaFree(d_counters);
-        if (d_norm) cudaFree(d_norm);
         if (d_parent) cudaFree(d_parent);
         if (d_arrived) cudaFree(d_arrived);
         if (d_cost) cudaFree(d_cost);
         if (d_dec) cudaFree(d_dec);
     };
-#define VSB_ENC_CUDA(expr) do { err = (expr); if (err != cudaSuccess) { cleanup(); vsb_scene_destroy(s); return (int)err; } } while (0)
+#define VSB_ENC_CUDA(expr) do { err = (expr); if (err != cudaSuccess) { cleanup(); return (int)err; } } while (0)
     VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, wide_cap * sizeof(vsb::Node80)));
     VSB_ENC_CUDA(cudaMalloc((void**)&d_leaf_list, (list_len + 1) * sizeof(uint32_t)));
     VSB_ENC_CUDA(cudaMalloc((void**)&d_tasks[0], (wide_cap + 1) * sizeof(vsb::WideTask)));
@@ -314,22 +277,75 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
         n_tasks = counters[2];
         cur ^= 1;
         ++s->levels;
-        if (s->levels > 256) { cleanup(); vsb_scene_destroy(s); return VSB_ERR_BAD_TREE; }
+        if (s->levels > 256) { cleanup(); return VSB_ERR_BAD_TREE; }
     }
     s->n_wide = counters[0];
     s->n_wide_prims = counters[1];
-    if (s->n_wide_prims != list_len || s->levels > VSB_STACK_SIZE - 2) { cleanup(); vsb_scene_destroy(s); return VSB_ERR_BAD_TREE; }
+    if (s->n_wide_prims != list_len || s->levels > VSB_STACK_SIZE - 2) { cleanup(); return VSB_ERR_BAD_TREE; }
     VSB_ENC_CUDA(cudaMalloc(&s->d_wide_prims, (size_t)s->n_wide_prims * rec_bytes + 64));
     vsb::fill_prims_kernel<<<(s->n_wide_prims + 255) / 256, 256, 0, g.stream>>>(
-        prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims);
+        s->prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims);
     ++g.launches;
     VSB_ENC_CUDA(cudaGetLastError());
     VSB_ENC_CUDA(cudaStreamSynchronize(g.stream));
     cleanup();
+#undef VSB_ENC_CUDA
 
-    s->dev.wide.nodes = s->d_wide; s->dev.wide.prims = s->d_wide_prims; s->dev.wide.prim_kind = prim_kind;
+    s->dev.wide.nodes = s->d_wide; s->dev.wide.prims = s->d_wide_prims; s->dev.wide.prim_kind = s->prim_kind;
     s->dev.exact.nodes = s->d_nodes2; s->dev.exact.prims = s->d_prims; s->dev.exact.indices = s->d_indices;
-    s->dev.exact.prim_kind = prim_kind;
+    s->dev.exact.prim_kind = s->prim_kind;
+    return VSB_OK;
+}
+
+} // namespace
+
+extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
+                                const vsb_bvh_node* nodes, size_t n_nodes,
+                                const uint32_t* indices, size_t n_indices, vsb_scene** out)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!prims || !nodes || !out || n_prims == 0 || n_nodes == 0) return VSB_ERR_BAD_ARG;
+    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE) return VSB_ERR_BAD_ARG;
+    if (n_nodes >= 0x7fffffffull || n_prims >= 0x7fffffffull) return VSB_ERR_UNSUPPORTED;
+
+    bool big = false;
+    const int depth = validate_tree(nodes, n_nodes, indices, n_indices, n_prims, &big);
+    if (depth < 0) return depth;
+    if (depth > VSB_EXACT_STACK - 1 || depth > VSB_STACK_SIZE - 1) return VSB_ERR_BAD_TREE;
+
+    vsb_scene* s = new vsb_scene();
+    s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_nodes2 = n_nodes; s->n_idx = indices ? n_indices : 0;
+    s->depth2 = depth;
+    for (int i = 0; i < 3; ++i) { s->lo[i] = nodes[0].bbox_min[i]; s->hi[i] = nodes[0].bbox_max[i]; }
+    const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
+    const size_t list_len = indices ? n_indices : n_prims;
+
+#define VSB_SCENE_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { vsb_scene_destroy(s); return (int)e__; } } while (0)
+    VSB_SCENE_CUDA(cudaMalloc(&s->d_prims, n_prims * prim_bytes));
+    VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_nodes2, n_nodes * sizeof(vsb::Node32)));
+    if (indices) VSB_SCENE_CUDA(cudaMalloc((void**)&s->d_indices, n_indices * sizeof(uint32_t)));
+    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_prims, prims, n_prims * prim_bytes, cudaMemcpyHostToDevice, g.stream));
+    VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_nodes2, nodes, n_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice, g.stream));
+    if (indices) VSB_SCENE_CUDA(cudaMemcpyAsync(s->d_indices, indices, n_indices * sizeof(uint32_t), cudaMemcpyHostToDevice, g.stream));
+
+    // BVH2 used for the encode: the caller's tree, or a normalised copy when it has big leaves
+    vsb::Node32* d_enc_nodes = s->d_nodes2;
+    size_t n_enc_nodes = n_nodes;
+    vsb::Node32* d_norm = nullptr;
+    if (big)
+    {
+        std::vector<vsb_bvh_node> norm(nodes, nodes + n_nodes);
+        normalise_leaves(norm);
+        n_enc_nodes = norm.size();
+        VSB_SCENE_CUDA(cudaMalloc((void**)&d_norm, n_enc_nodes * sizeof(vsb::Node32)));
+        cudaError_t e = cudaMemcpy(d_norm, norm.data(), n_enc_nodes * sizeof(vsb::Node32), cudaMemcpyHostToDevice);
+        if (e != cudaSuccess) { cudaFree(d_norm); vsb_scene_destroy(s); return (int)e; }
+        d_enc_nodes = d_norm;
+    }
+#undef VSB_SCENE_CUDA
+    rc = encode_wide(s, d_enc_nodes, n_enc_nodes, list_len);
+    if (d_norm) cudaFree(d_norm);
+    if (rc != VSB_OK) { vsb_scene_destroy(s); return rc; }
     *out = s;
     return VSB_OK;
 }
