@@ -333,11 +333,11 @@ inline void build_tree_impl(std::vector<bvh_node>& nodes, std::vector<unsigned>&
 } // namespace detail
 
 // build<index_bvh<P>>(prims, n[, spatial_splits]) -- bvh.h:455, detail/bvh/build.inl:165-178
+// (index_bvh only: use reorder() for bvh<P>; build<b200_index_bvh<P>>() in scheduler.h builds on the GPU)
 template <typename Tree, typename P>
-Tree build(P const* prims, size_t n, bool spatial_splits = false)
+typename std::enable_if<is_index_bvh<Tree>::value, Tree>::type build(P const* prims, size_t n, bool spatial_splits = false)
 {
     if (spatial_splits) throw std::runtime_error("visionaray_b200::build: spatial splits are not supported");
-    static_assert(is_index_bvh<Tree>::value, "build<>: index_bvh only (use reorder() for bvh<P>)");
     Tree tree(prims, n);
     detail::binned_sah_builder builder;
     auto root = builder.init(prims, n);

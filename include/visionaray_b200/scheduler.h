@@ -123,7 +123,44 @@ public:
     {
         this->create(prims, np, nodes, nn, idx, ni);
     }
+
+    // The tree BUILT ON THE GPU from the primitives alone (vsb_scene_build): what
+    // build<index_bvh<P>>(first, last) + cuda_index_bvh<P>(host_bvh) do in the reference
+    // (bvh.h:455,344-350; detail/bvh/build.inl, sah.h), without the single-threaded host build.
+    // Spelled like the reference's builder: build<b200_index_bvh<P>>(prims, n).
+    static b200_index_bvh build_on_device(P const* prims, size_t np)
+    {
+        detail::ensure_init();
+        b200_index_bvh out;
+        detail::check(vsb_scene_build(detail::prim_kind<P>::value, prims, np, VSB_MEM_HOST, &out.scene_), "vsb_scene_build");
+        uint64_t st[6] = { 0, 0, 0, 0, 0, 0 };
+        detail::check(vsb_scene_stats(out.scene_, st, 6), "vsb_scene_stats");
+        out.n_prims_ = np; out.n_nodes_ = size_t(st[5]);
+        return out;
+    }
+
+    // the device tree back as a host index_bvh<P> in the reference's layout (nodes(), indices());
+    // `prims` are the caller's primitives (the device copy is not read back)
+    index_bvh<P> download(P const* prims) const
+    {
+        index_bvh<P> host(prims, this->n_prims_);
+        host.nodes().resize(this->n_nodes_);
+        host.indices().resize(this->n_prims_);
+        detail::check(vsb_scene_download_bvh(this->scene_, reinterpret_cast<vsb_bvh_node*>(host.nodes().data()), host.nodes().size(),
+                                             host.indices().data(), host.indices().size()), "vsb_scene_download_bvh");
+        return host;
+    }
 };
+
+template <typename T> struct is_b200_index_bvh : std::false_type {};
+template <typename P> struct is_b200_index_bvh<b200_index_bvh<P>> : std::true_type {};
+
+// build<b200_index_bvh<P>>(prims, n): same spelling as build<index_bvh<P>>(prims, n) (bvh.h:455)
+template <typename Tree, typename P>
+typename std::enable_if<is_b200_index_bvh<Tree>::value, Tree>::type build(P const* prims, size_t n)
+{
+    return Tree::build_on_device(prims, n);
+}
 
 template <typename P>
 class b200_bvh : public b200_bvh_base<P, false>

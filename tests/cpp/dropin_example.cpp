@@ -5,6 +5,7 @@
 //
 //   dropin_example <out_dir>      exit 0 ok, 2 known-answer failure, 3 no CUDA device / library error
 #include <cstdio>
+#include <cstring>
 #include <fstream>
 #include <iostream>
 #include <vector>
@@ -63,6 +64,23 @@ int main(int argc, char** argv)
         dump(out + "/hits_wide.bin", wide.data(), wide.size());
         dump(out + "/hits_exact.bin", exact.data(), exact.size());
         dump(out + "/hits_any.bin", occ.data(), occ.size());
+
+        // --- the same mesh with the BVH built on the GPU (replaces the host build + upload) ---
+        {
+            auto g_bvh = build<b200_index_bvh<triangle_type>>(tris.data(), tris.size());
+            b200_bvh_ref gp[1] = { g_bvh.ref() };
+            std::vector<hit_record> built(rays.size());
+            closest_hit(rays.data(), rays.size(), gp, gp + 1, built.data());
+            dump(out + "/hits_gpu_built.bin", built.data(), built.size());
+            index_bvh<triangle_type> back = g_bvh.download(tris.data());      // an ordinary host index_bvh again
+            if (back.num_nodes() != g_bvh.num_nodes() || back.num_indices() != tris.size()) { std::cerr << "download size\n"; return 2; }
+            b200_index_bvh<triangle_type> again(back);                        // ... that uploads like a host-built one
+            b200_bvh_ref ap[1] = { again.ref() };
+            std::vector<hit_record> h1(rays.size()), h2(rays.size());
+            closest_hit(rays.data(), rays.size(), gp, gp + 1, h1.data(), true);
+            closest_hit(rays.data(), rays.size(), ap, ap + 1, h2.data(), true);
+            if (std::memcmp(h1.data(), h2.data(), h1.size() * sizeof(hit_record)) != 0) { std::cerr << "downloaded tree != device tree\n"; return 2; }
+        }
 
         // --- frame(): Whitted kernel, one point light at the eye, plastic material ---
         int w = 160, h = 120;

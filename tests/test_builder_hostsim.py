@@ -123,8 +123,9 @@ def test_ploc_degenerate_inputs():
     nodes, idx, info = build_ploc(0, two)
     sc = S.HostScene(0, two, nodes, idx)
     check_bvh2(sc, nodes, idx)
-    same = np.stack([tri((0, 0, 0), (1, 0, 0), (0, 1, 0), i) for i in range(37)])
+    same = np.stack([tri((0, 0, 0), (1, 0, 0), (0, 1, 0), i) for i in range(301)])
     nodes, idx, info = build_ploc(0, same)
+    assert info["iterations"] <= 12 and info["depth"] <= 12      # ties pair up (0,1)(2,3)..: log2 n passes, not n
     sc = S.HostScene(0, same, nodes, idx)
     check_bvh2(sc, nodes, idx)
     rays = np.zeros((1, 8), dtype=np.float32)

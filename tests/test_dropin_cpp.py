@@ -47,6 +47,8 @@ def test_dropin_program_matches_oracle(gpu):
         assert exact.tobytes() == want.tobytes()
         assert classify_closest(want, wide)["bad"] == 0
         assert (occ["hit"] == O.oracle_query(sc, rays, True, 0.5)["hit"]).all()
+        built = np.fromfile(os.path.join(d, "hits_gpu_built.bin"), dtype=O.HIT_DTYPE)     # build<b200_index_bvh<P>>()
+        assert classify_closest(want, built)["bad"] == 0
         eye = (0.0, 0.0, 3.0)
         fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
         ref = O.oracle_frame(sc, fp, S.default_material(0), S.point_light(eye))

@@ -162,8 +162,10 @@ def test_builder_device_primitives_and_full_size(gpu):
         assert (plo[p] >= nodes["bbox_min"][sel]).all() and (phi[p] <= nodes["bbox_max"][sel]).all()
     ref = gpu.Scene(sc)
     rays = torch.from_numpy(scene_rays(sc, 2_000_000, 54)).cuda()
-    a = gpu.closest_hit(ref, rays).cpu().numpy().view(np.uint8).reshape(-1).view(O.HIT_DTYPE)
-    b = gpu.closest_hit(dev, rays).cpu().numpy().view(np.uint8).reshape(-1).view(O.HIT_DTYPE)
+    ha, hb = gpu.closest_hit(ref, rays), gpu.closest_hit(dev, rays)
+    gpu.sync()                                             # the library's own stream (stream=None)
+    a = ha.cpu().numpy().view(np.uint8).reshape(-1).view(O.HIT_DTYPE)
+    b = hb.cpu().numpy().view(np.uint8).reshape(-1).view(O.HIT_DTYPE)
     assert classify_closest(a, b)["bad"] == 0
     assert (a["t"] == b["t"]).mean() > 0.9999
     ms = gpu.last_build_ms()

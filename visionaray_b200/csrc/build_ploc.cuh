@@ -141,20 +141,30 @@ VSB_HD BSub leaf_sub(const BNode& b, const BuildParams& bp)
 }
 
 // nearest neighbour of cluster i among positions [i - radius, i + radius] of tile[], where
-// tile[k] holds cluster (tile_first + k) and clusters [0, m) exist.  Smallest merged area wins,
-// ties go to the smaller position: with a symmetric distance this guarantees that the globally
-// closest pair is mutual, so every iteration merges at least one pair.
+// tile[k] holds cluster (tile_first + k) and clusters [0, m) exist.  Smallest merged area wins.
+// Equal areas are ordered by a key that is SYMMETRIC in the pair -- position distance, then pairs
+// whose lower position is even, then the lower position -- so the order is a strict total order on
+// unordered pairs: the globally smallest pair is each other's choice and every iteration merges at
+// least one pair, and n identical primitives pair up as (0,1)(2,3).. instead of one merge per pass.
+VSB_HD uint32_t ploc_pair_key(uint32_t i, uint32_t j)
+{
+    const uint32_t lo = i < j ? i : j, d = i < j ? j - i : i - j;
+    return (d << 1) | (lo & 1u);
+}
+
 VSB_HD uint32_t ploc_nearest(const BNode* tile, long tile_first, uint32_t i, uint32_t m, int radius)
 {
     const BNode self = tile[(long)i - tile_first];
-    float best = FLT_MAX; uint32_t bj = i;
+    float best = FLT_MAX; uint32_t bj = i, bkey = 0xffffffffu;
     const long j0 = (long)i - radius < 0 ? 0 : (long)i - radius;
     const long j1 = (long)i + radius > (long)m - 1 ? (long)m - 1 : (long)i + radius;
     for (long j = j0; j <= j1; ++j)
     {
         if (j == (long)i) continue;
         const float a = merged_half_area(self, tile[j - tile_first]);
-        if (a < best) { best = a; bj = (uint32_t)j; }
+        const uint32_t key = ploc_pair_key(i, (uint32_t)j);
+        // same distance and same key bits: j = i - d before j = i + d (the smaller lower position)
+        if (a < best || (a == best && key < bkey)) { best = a; bj = (uint32_t)j; bkey = key; }
     }
     return bj;
 }

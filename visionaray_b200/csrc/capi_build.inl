@@ -10,15 +10,17 @@ float g_build_cost_prim = 1.0f;    // vsb_tune("build_cost_prim_x100", ...)
 float g_last_build_ms[4] = { 0, 0, 0, 0 };   // total, sort + setup, PLOC, layout + wide re-encode
 int   g_last_build_iters = 0;
 
+// scratch from the stream-ordered pool (vsb_init keeps it cached between builds)
 struct BuildScratch
 {
     void* p[16] = {};
     int n = 0;
-    ~BuildScratch() { for (int i = 0; i < n; ++i) if (p[i]) cudaFree(p[i]); }
+    cudaStream_t st = nullptr;
+    ~BuildScratch() { for (int i = 0; i < n; ++i) if (p[i]) cudaFreeAsync(p[i], st); }
     template <typename T> cudaError_t alloc(T** out, size_t count)
     {
         void* q = nullptr;
-        cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 16);
+        cudaError_t e = cudaMallocAsync(&q, count * sizeof(T) + 16, st);
         if (e == cudaSuccess) { p[n++] = q; *out = reinterpret_cast<T*>(q); }
         return e;
     }
@@ -40,6 +42,7 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
     vsb_scene* s = new vsb_scene();
     s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_idx = n_prims;
     BuildScratch scratch;
+    scratch.st = st;
     cudaEvent_t ev[4] = { nullptr, nullptr, nullptr, nullptr };
     auto fail = [&](int code) { for (auto e : ev) if (e) cudaEventDestroy(e); vsb_scene_destroy(s); return code; };
 #define VSB_BUILD_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) return fail((int)e__); } while (0)

@@ -148,6 +148,16 @@ extern "C" int vsb_init(int device)
     VSB_CUDA(cudaGetDeviceProperties(&prop, device));
     g.device = device;
     g.sm_count = prop.multiProcessorCount;
+    {
+        // scratch of scene builds comes from the stream-ordered pool (cudaMallocAsync); keep up to 8 GiB of it
+        // cached between builds so that a rebuild does not pay cudaMalloc / cudaFree round trips
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, device) == cudaSuccess)
+        {
+            unsigned long long keep = 8ull << 30;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+    }
     VSB_CUDA(cudaStreamCreateWithFlags(&g.stream, cudaStreamNonBlocking));
     VSB_CUDA(cudaStreamCreateWithFlags(&g.copy_stream, cudaStreamNonBlocking));
     for (int i = 0; i < 32; ++i) VSB_CUDA(cudaEventCreateWithFlags(&g.band_done[i], cudaEventDisableTiming));
@@ -224,39 +234,36 @@ int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size
     const size_t rec_bytes = s->prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
     uint32_t* d_leaf_list = nullptr; vsb::WideTask* d_tasks[2] = { nullptr, nullptr }; uint32_t* d_counters = nullptr;
     uint32_t* d_parent = nullptr; uint32_t* d_arrived = nullptr; vsb::CollapseCost* d_cost = nullptr; vsb::CollapseDec* d_dec = nullptr;
+    vsb::Node80* d_wide_tmp = nullptr;     // encoded into scratch of the worst-case size, then copied to an exact-size array
     const size_t wide_cap = n_enc_nodes;   // a wide node consumes >= 1 BVH2 inner node
     cudaError_t err = cudaSuccess;
+    cudaStream_t st = g.stream;
     auto cleanup = [&]()
     {
-        if (d_leaf_list) cudaFree(d_leaf_list);
-        if (d_tasks[0]) cudaFree(d_tasks[0]);
-        if (d_tasks[1]) cudaFree(d_tasks[1]);
-        if (d_counters) cudaFree(d_counters);
-        if (d_parent) cudaFree(d_parent);
-        if (d_arrived) cudaFree(d_arrived);
-        if (d_cost) cudaFree(d_cost);
-        if (d_dec) cudaFree(d_dec);
+        void* all[] = { d_leaf_list, d_tasks[0], d_tasks[1], d_counters, d_parent, d_arrived, d_cost, d_dec, d_wide_tmp };
+        for (void* q : all) if (q) cudaFreeAsync(q, st);
     };
 #define VSB_ENC_CUDA(expr) do { err = (expr); if (err != cudaSuccess) { cleanup(); return (int)err; } } while (0)
-    VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, wide_cap * sizeof(vsb::Node80)));
-    VSB_ENC_CUDA(cudaMalloc((void**)&d_leaf_list, (list_len + 1) * sizeof(uint32_t)));
-    VSB_ENC_CUDA(cudaMalloc((void**)&d_tasks[0], (wide_cap + 1) * sizeof(vsb::WideTask)));
-    VSB_ENC_CUDA(cudaMalloc((void**)&d_tasks[1], (wide_cap + 1) * sizeof(vsb::WideTask)));
-    VSB_ENC_CUDA(cudaMalloc((void**)&d_counters, 4 * sizeof(uint32_t)));
+    VSB_ENC_CUDA(cudaMallocAsync((void**)&d_wide_tmp, wide_cap * sizeof(vsb::Node80), st));
+    VSB_ENC_CUDA(cudaMallocAsync((void**)&d_leaf_list, (list_len + 1) * sizeof(uint32_t), st));
+    VSB_ENC_CUDA(cudaMallocAsync((void**)&d_tasks[0], (wide_cap + 1) * sizeof(vsb::WideTask), st));
+    VSB_ENC_CUDA(cudaMallocAsync((void**)&d_tasks[1], (wide_cap + 1) * sizeof(vsb::WideTask), st));
+    VSB_ENC_CUDA(cudaMallocAsync((void**)&d_counters, 4 * sizeof(uint32_t), st));
     {
         vsb::WideTask root; root.bvh2_node = 0; root.wide_index = 0;
         uint32_t init[4] = { 1u, 0u, 0u, 0u };
         VSB_ENC_CUDA(cudaMemcpyAsync(d_tasks[0], &root, sizeof(root), cudaMemcpyHostToDevice, g.stream));
         VSB_ENC_CUDA(cudaMemcpyAsync(d_counters, init, sizeof(init), cudaMemcpyHostToDevice, g.stream));
+        VSB_ENC_CUDA(cudaStreamSynchronize(g.stream));      // `root` / `init` are stack variables
     }
     // optimal collapse: bottom-up DP over the BVH2 (g_optimal_collapse = 0: greedy largest-area-first)
     if (g_optimal_collapse)
     {
         const uint32_t nn = (uint32_t)n_enc_nodes;
-        VSB_ENC_CUDA(cudaMalloc((void**)&d_parent, (size_t)nn * 4));
-        VSB_ENC_CUDA(cudaMalloc((void**)&d_arrived, (size_t)nn * 4));
-        VSB_ENC_CUDA(cudaMalloc((void**)&d_cost, (size_t)nn * sizeof(vsb::CollapseCost)));
-        VSB_ENC_CUDA(cudaMalloc((void**)&d_dec, (size_t)nn * sizeof(vsb::CollapseDec)));
+        VSB_ENC_CUDA(cudaMallocAsync((void**)&d_parent, (size_t)nn * 4, st));
+        VSB_ENC_CUDA(cudaMallocAsync((void**)&d_arrived, (size_t)nn * 4, st));
+        VSB_ENC_CUDA(cudaMallocAsync((void**)&d_cost, (size_t)nn * sizeof(vsb::CollapseCost), st));
+        VSB_ENC_CUDA(cudaMallocAsync((void**)&d_dec, (size_t)nn * sizeof(vsb::CollapseDec), st));
         VSB_ENC_CUDA(cudaMemsetAsync(d_arrived, 0, (size_t)nn * 4, g.stream));
         vsb::bvh2_parents_kernel<<<(nn + 255) / 256, 256, 0, g.stream>>>(d_enc_nodes, nn, d_parent);
         vsb::collapse_dp_kernel<<<(nn + 255) / 256, 256, 0, g.stream>>>(d_enc_nodes, nn, d_parent, d_arrived, d_cost, d_dec);
@@ -269,7 +276,7 @@ int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size
     {
         VSB_ENC_CUDA(cudaMemsetAsync(d_counters + 2, 0, sizeof(uint32_t), g.stream));
         vsb::encode_level_kernel<<<(n_tasks + 127) / 128, 128, 0, g.stream>>>(
-            d_tasks[cur], n_tasks, d_enc_nodes, s->d_wide, d_leaf_list, d_tasks[cur ^ 1], d_counters, d_dec);
+            d_tasks[cur], n_tasks, d_enc_nodes, d_wide_tmp, d_leaf_list, d_tasks[cur ^ 1], d_counters, d_dec);
         ++g.launches;
         VSB_ENC_CUDA(cudaGetLastError());
         VSB_ENC_CUDA(cudaMemcpyAsync(counters, d_counters, sizeof(counters), cudaMemcpyDeviceToHost, g.stream));
@@ -282,6 +289,8 @@ int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size
     s->n_wide = counters[0];
     s->n_wide_prims = counters[1];
     if (s->n_wide_prims != list_len || s->levels > VSB_STACK_SIZE - 2) { cleanup(); return VSB_ERR_BAD_TREE; }
+    VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, (size_t)s->n_wide * sizeof(vsb::Node80) + 64));
+    VSB_ENC_CUDA(cudaMemcpyAsync(s->d_wide, d_wide_tmp, (size_t)s->n_wide * sizeof(vsb::Node80), cudaMemcpyDeviceToDevice, st));
     VSB_ENC_CUDA(cudaMalloc(&s->d_wide_prims, (size_t)s->n_wide_prims * rec_bytes + 64));
     vsb::fill_prims_kernel<<<(s->n_wide_prims + 255) / 256, 256, 0, g.stream>>>(
         s->prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims);
