@@ -30,6 +30,7 @@
 #include <stdexcept>
 #include <string>
 #include <type_traits>
+#include <array>
 #include <vector>
 
 #include "../vsnray_b200.h"
@@ -229,6 +230,32 @@ inline void any_hit(ray const* rays, size_t n, b200_bvh_ref const* begin, b200_b
                     bool reference_order = false)
 {
     detail::query(true, begin, end, rays, n, max_t, nullptr, hits, reference_order ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE);
+}
+
+// multi_hit<N>(r, begin, end) (detail/traverse_linear.inl:325-380): the N closest intersections sorted
+// by t, misses (hit = 0, t = FLT_MAX) behind; N = 1..16 (16 in src/examples/multi_hit/main.cpp:186)
+template <size_t N = 16>
+inline std::array<hit_record, N> multi_hit(ray const& r, b200_bvh_ref const* begin, b200_bvh_ref const* end)
+{
+    static_assert(N >= 1 && N <= 16, "multi_hit<N>: N = 1..16");
+    std::array<hit_record, N> h;
+    std::vector<vsb_scene const*> scenes;
+    for (auto it = begin; it != end; ++it) scenes.push_back(it->scene);
+    detail::check(vsb_multi_hit(scenes.data(), int(scenes.size()), reinterpret_cast<vsb_ray const*>(&r), 1, int(N),
+                                reinterpret_cast<vsb_hit*>(h.data()), VSB_MEM_HOST, VSB_TRAVERSE_WIDE, nullptr), "vsb_multi_hit");
+    return h;
+}
+// ray list (host memory): hits[i * N + k] = multi_hit<N>(rays[i], begin, end)[k]
+template <size_t N = 16>
+inline void multi_hit(ray const* rays, size_t n, b200_bvh_ref const* begin, b200_bvh_ref const* end, hit_record* hits,
+                      bool reference_order = false)
+{
+    static_assert(N >= 1 && N <= 16, "multi_hit<N>: N = 1..16");
+    std::vector<vsb_scene const*> scenes;
+    for (auto it = begin; it != end; ++it) scenes.push_back(it->scene);
+    detail::check(vsb_multi_hit(scenes.data(), int(scenes.size()), reinterpret_cast<vsb_ray const*>(rays), n, int(N),
+                                reinterpret_cast<vsb_hit*>(hits), VSB_MEM_HOST,
+                                reference_order ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE, nullptr), "vsb_multi_hit");
 }
 
 //-------------------------------------------------------------------------------------------------

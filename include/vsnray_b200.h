@@ -227,6 +227,16 @@ int  vsb_any_hit(const vsb_scene* const* scenes, int n_scenes,
                  const vsb_ray* rays, size_t n_rays, float max_t, const float* max_t_per_ray,
                  vsb_hit* hits, int mem, int traverse, void* cuda_stream);
 
+/* multi_hit<N>(r, begin, end) over a ray list (detail/traverse_linear.inl:325-380 ->
+ * intersect<MultiHit, N>(), detail/bvh/intersect.inl:35-134; record handling detail/multi_hit.h):
+ * hits[i * max_hits + k] = the k-th closest intersection of ray i, sorted by t, equal t in visit
+ * order, misses (hit = 0, t = FLT_MAX) behind; max_hits = 1..16 (the reference's template argument,
+ * 16 in src/examples/multi_hit/main.cpp:186).  VSB_TRAVERSE_EXACT: records bit-identical to the
+ * reference's; VSB_TRAVERSE_WIDE: same records except order / survivor among exact t-ties. */
+int  vsb_multi_hit(const vsb_scene* const* scenes, int n_scenes,
+                   const vsb_ray* rays, size_t n_rays, int max_hits,
+                   vsb_hit* hits, int mem, int traverse, void* cuda_stream);
+
 /* ---- frame: replaces cuda_sched<R>::frame(kernel, sched_params, frame_num)
  * (detail/cuda_sched.h:24-40, detail/cuda_sched.inl:307-320) for the built-in kernels
  * simple / whitted / pathtracing (detail/*.inl) and the AO kernel of

@@ -54,6 +54,7 @@ def oracle_lib():
         lib.vso_camera_basis.argtypes = [vp, vp, vp, vp, vp]
         lib.vso_frame_matrix.argtypes = [vp, vp, vp, C.POINTER(Bvh), vp, vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
         lib.vso_mat4_inverse.argtypes = [vp, vp]
+        lib.vso_multi_hit.argtypes = [C.POINTER(Bvh), C.c_int, vp, sz, C.c_int, vp, C.c_int]
         lib.vso_bvh_max_depth.argtypes = [C.POINTER(Bvh)]
         lib.vso_sampler_init.restype = C.c_uint32
         lib.vso_sampler_init.argtypes = [C.c_uint32, C.c_uint32, C.c_uint32]
@@ -81,6 +82,8 @@ def ref_lib(fast: bool = False):
         lib.ref_frame.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
         lib.ref_frame_matrix.argtypes = [vp, vp, vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, vp, C.c_int, vp]
         lib.ref_camera_matrices.argtypes = [vp, C.c_float, C.c_float, vp, vp]
+        if hasattr(lib, "ref_multi_hit"):
+            lib.ref_multi_hit.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, C.c_int]
         lib.ref_query_timed.restype = C.c_double
         lib.ref_query_timed.argtypes = [C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, C.c_int, C.c_int, C.c_int,
                                         C.POINTER(C.c_uint64)]
@@ -108,6 +111,34 @@ def oracle_query(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_
     c = counters if counters is not None else Counters()
     oracle_lib().vso_query(int(any_hit), C.byref(b), _p(rays), rays.shape[0], max_t, _p(max_t_per_ray), _p(hits),
                            C.byref(c), nthreads or (os.cpu_count() or 1))
+    return hits
+
+
+def oracle_multi_hit(scenes, rays, n, nthreads=0):
+    """multi_hit<n>() over a range of bvhs (one HostScene or a list): (n_rays, n) records sorted by t."""
+    if not isinstance(scenes, (list, tuple)):
+        scenes = [scenes]
+    arr = (Bvh * len(scenes))(*[make_bvh(s) for s in scenes])
+    hits = np.zeros((rays.shape[0], n), dtype=HIT_DTYPE)
+    oracle_lib().vso_multi_hit(arr, len(scenes), _p(rays), rays.shape[0], n, _p(hits), nthreads or (os.cpu_count() or 1))
+    return hits
+
+
+def ref_multi_hit(scenes, rays, n, nthreads=0):
+    """The same through the unmodified reference headers (oracle/_ref); n in {1, 2, 4, 5, 8, 16}, <= 2 bvhs."""
+    if not isinstance(scenes, (list, tuple)):
+        scenes = [scenes]
+    hits = np.zeros((rays.shape[0], n), dtype=HIT_DTYPE)
+    a = scenes[0]
+    b = scenes[1] if len(scenes) > 1 else None
+    args = [a.prim_kind, n, _p(a.prims), a.prims.shape[0], _p(a.nodes), a.nodes.shape[0], _p(a.indices), a.indices.shape[0]]
+    if b is not None:
+        args += [_p(b.prims), b.prims.shape[0], _p(b.nodes), b.nodes.shape[0], _p(b.indices), b.indices.shape[0]]
+    else:
+        args += [None, 0, None, 0, None, 0]
+    rc = ref_lib().ref_multi_hit(*args, _p(rays), rays.shape[0], _p(hits), nthreads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError(f"ref_multi_hit: unsupported n = {n}")
     return hits
 
 

@@ -195,10 +195,57 @@ void query_impl(int any, void const* prims, size_t n_prims, void const* nodes, s
     });
 }
 
+// multi_hit<N>(r, begin, end) from the unmodified headers (detail/traverse_linear.inl:325-380),
+// over a range of one or two bvh refs
+template <typename P, size_t N>
+void multi_impl(void const* prims, size_t n_prims, void const* nodes, size_t n_nodes, uint32_t const* indices, size_t n_idx,
+                void const* prims2, size_t n_prims2, void const* nodes2, size_t n_nodes2, uint32_t const* indices2, size_t n_idx2,
+                void const* rays, size_t n_rays, hit32* out, int nthreads)
+{
+    using ref_t = typename index_bvh<P>::bvh_ref;
+    std::vector<ref_t> refs;
+    refs.push_back(make_ref<P>(prims, n_prims, nodes, n_nodes, indices, n_idx));
+    if (prims2) refs.push_back(make_ref<P>(prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2));
+    auto r = reinterpret_cast<ray_t const*>(rays);
+    parallel_for(n_rays, nthreads, [&](size_t b, size_t e)
+    {
+        for (size_t i = b; i < e; ++i)
+        {
+            auto hr = multi_hit<N>(r[i], refs.data(), refs.data() + refs.size());
+            for (size_t k = 0; k < N; ++k) store_hit(out[i * N + k], hr[k]);
+        }
+    });
+}
+
+template <typename P>
+int multi_dispatch(int n, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes, uint32_t const* indices, size_t n_idx,
+                   void const* prims2, size_t n_prims2, void const* nodes2, size_t n_nodes2, uint32_t const* indices2, size_t n_idx2,
+                   void const* rays, size_t n_rays, hit32* out, int nthreads)
+{
+#define VSB_MULTI_CASE(N) case N: multi_impl<P, N>(prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, out, nthreads); return 0;
+    switch (n)
+    {
+    VSB_MULTI_CASE(1) VSB_MULTI_CASE(2) VSB_MULTI_CASE(4) VSB_MULTI_CASE(5) VSB_MULTI_CASE(8) VSB_MULTI_CASE(16)
+    default: return 1;
+    }
+#undef VSB_MULTI_CASE
+}
+
 } // namespace
 
 extern "C"
 {
+
+// n in {1, 2, 4, 5, 8, 16}; the second bvh (prims2 ...) may be NULL.  hits_out: n_rays * n records.
+int ref_multi_hit(int prim_kind, int n,
+                  void const* prims, size_t n_prims, void const* nodes, size_t n_nodes, uint32_t const* indices, size_t n_idx,
+                  void const* prims2, size_t n_prims2, void const* nodes2, size_t n_nodes2, uint32_t const* indices2, size_t n_idx2,
+                  void const* rays, size_t n_rays, void* hits_out, int nthreads)
+{
+    if (prim_kind == 0)
+        return multi_dispatch<tri_t>(n, prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, (hit32*)hits_out, nthreads);
+    return multi_dispatch<sph_t>(n, prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, (hit32*)hits_out, nthreads);
+}
 
 // sizes: {vec3, triangle, sphere, ray, bvh_node, aabb, off(tri.v1), off(tri.e1), off(tri.e2),
 //         off(tri.prim_id), off(tri.geom_id), off(sphere.center), off(sphere.radius)}

@@ -324,6 +324,111 @@ void vso_query(int any, const vso_bvh* b, const vso_ray* rays, size_t n_rays, fl
     parallel_ranges(n_rays, nthreads, query_range, &q, counters);
 }
 
+/* ------------------------------------------------------------------------------------------
+ * multi_hit<N>() -- detail/traverse_linear.inl:325-380 -> intersect<MultiHit, N>()
+ * (detail/bvh/intersect.inl:35-134 with RT = array<HR, N>, detail/multi_hit.h:29-41).
+ *   box:   is_closer(box, result_array, max_t) = OR over the records (multi_hit.h:206-233);
+ *   prim:  same OR, then update_if(array, hr) = algo::insert_sorted(hr, begin, end, is_closer_t())
+ *          (multi_hit.h:163-176, detail/algorithm.h:46-74): before the first record with a larger t,
+ *          records behind it shift by one, the last drops out;
+ *   no early exit (exit_traversal<MultiHit> is the generic "never").
+ * max_t is numeric_limits::max() (multi_hit() has no max_t overload).
+ * ---------------------------------------------------------------------------------------- */
+static int multi_closer_box(int hit, float tnear, float tfar, const vso_hit* res, int n, float max_t)
+{
+    for (int i = 0; i < n; ++i)
+        if (hit && tnear < res[i].t && tfar >= 0.0f && tnear < max_t) return 1;
+    return 0;
+}
+
+static int multi_closer_prim(const vso_hit* hr, const vso_hit* res, int n, float max_t)
+{
+    for (int i = 0; i < n; ++i)
+        if (hr->hit && (hr->t >= 0.0f && hr->t < res[i].t) && hr->t < max_t) return 1;
+    return 0;
+}
+
+static void insert_sorted(const vso_hit* item, vso_hit* first, int n)
+{
+    int pos = n;
+    for (int it = 0; it < n; ++it)
+        if (item->hit && (item->t >= 0.0f && item->t < first[it].t)) { pos = it; break; }
+    for (int it = (pos != n) ? n - 1 : n; it > pos; --it) first[it] = first[it - 1];
+    if (pos != n) first[pos] = *item;
+}
+
+void vso_multi_hit_bvh(const vso_ray* r, const vso_bvh* b, int n, vso_hit* result)
+{
+    const float max_t = FLT_MAX;
+    uint32_t stack[128];
+    int sp = 0;
+    float inv_dir[3] = { 1.0f / r->dir[0], 1.0f / r->dir[1], 1.0f / r->dir[2] };
+    for (int i = 0; i < n; ++i) hit_init(&result[i]);
+    stack[sp++] = 0;
+    while (sp > 0)
+    {
+        const vso_bvh_node* node = &b->nodes[stack[--sp]];
+        int culled = 0;
+        while (node->num_prims == 0)
+        {
+            const vso_bvh_node* ch = &b->nodes[node->first];
+            float tn1, tf1, tn2, tf2;
+            int h1 = vso_intersect_aabb(r, ch[0].bbox_min, ch[0].bbox_max, inv_dir, &tn1, &tf1);
+            int h2 = vso_intersect_aabb(r, ch[1].bbox_min, ch[1].bbox_max, inv_dir, &tn2, &tf2);
+            int b1 = multi_closer_box(h1, tn1, tf1, result, n, max_t);
+            int b2 = multi_closer_box(h2, tn2, tf2, result, n, max_t);
+            if (b1 && b2)
+            {
+                unsigned near_addr = (tn1 < tn2) ? 0u : 1u;
+                stack[sp++] = node->first + !near_addr;
+                node = &ch[near_addr];
+            }
+            else if (b1) node = &ch[0];
+            else if (b2) node = &ch[1];
+            else { culled = 1; break; }
+        }
+        if (culled) continue;
+        for (uint32_t i = node->first; i != node->first + node->num_prims; ++i)
+        {
+            vso_hit hr;
+            isect_prim(r, b, i, &hr);
+            if (!multi_closer_prim(&hr, result, n, max_t)) continue;
+            hr.hit = 1;
+            insert_sorted(&hr, result, n);
+        }
+    }
+}
+
+/* a range of BVHs: traverse() (detail/traverse_linear.inl:71-130) merges the per-BVH arrays with
+ * update_if(array, array) (detail/multi_hit.h:181-202) */
+typedef struct { const vso_bvh* bvhs; int n_bvhs; const vso_ray* rays; int n; vso_hit* hits; } multi_ctx;
+
+static void multi_range(size_t b, size_t e, void* p, vso_counters* c)
+{
+    multi_ctx* q = (multi_ctx*)p;
+    vso_hit tmp[64];
+    (void)c;
+    for (size_t i = b; i < e; ++i)
+    {
+        vso_hit* dst = q->hits + i * (size_t)q->n;
+        for (int k = 0; k < q->n; ++k) hit_init(&dst[k]);
+        for (int s = 0; s < q->n_bvhs; ++s)
+        {
+            vso_multi_hit_bvh(&q->rays[i], &q->bvhs[s], q->n, tmp);
+            if (!dst[0].hit) { memcpy(dst, tmp, sizeof(vso_hit) * (size_t)q->n); continue; }
+            for (int k = 0; k < q->n && tmp[k].hit; ++k) insert_sorted(&tmp[k], dst, q->n);
+        }
+        for (int k = 0; k < q->n; ++k) if (!dst[k].hit) hit_init(&dst[k]);
+    }
+}
+
+void vso_multi_hit(const vso_bvh* bvhs, int n_bvhs, const vso_ray* rays, size_t n_rays, int n, vso_hit* hits, int nthreads)
+{
+    multi_ctx q = { bvhs, n_bvhs, rays, n, hits };
+    if (n < 1 || n > 64) return;
+    parallel_ranges(n_rays, nthreads, multi_range, &q, NULL);
+}
+
 /* brute force in list order -- detail/traverse_linear.inl:26-63 */
 typedef struct
 {

@@ -75,6 +75,11 @@ void vso_intersect_bvh(int any, const vso_ray* r, const vso_bvh* b, float max_t,
 void vso_query(int any, const vso_bvh* b, const vso_ray* rays, size_t n_rays, float max_t,
                const float* max_t_per_ray, vso_hit* hits, vso_counters* counters, int nthreads);
 
+/* multi_hit<N>() over a ray list and a range of bvhs (detail/traverse_linear.inl:325-380,
+ * detail/multi_hit.h): hits[i * n + k] = k-th closest record of ray i, misses (t = FLT_MAX) behind */
+void vso_multi_hit_bvh(const vso_ray* r, const vso_bvh* b, int n, vso_hit* result);
+void vso_multi_hit(const vso_bvh* bvhs, int n_bvhs, const vso_ray* rays, size_t n_rays, int n, vso_hit* hits, int nthreads);
+
 /* brute force over all primitives in list order (detail/traverse_linear.inl:26-63); used to
  * classify t-ties */
 void vso_query_brute(int any, int prim_kind, const void* prims, size_t n_prims,

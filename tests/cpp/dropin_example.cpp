@@ -65,6 +65,17 @@ int main(int argc, char** argv)
         dump(out + "/hits_exact.bin", exact.data(), exact.size());
         dump(out + "/hits_any.bin", occ.data(), occ.size());
 
+        // --- multi_hit<16>: a ray through the centre of the sphere crosses the mesh twice ---
+        {
+            ray through(vec3(0.013f, 0.021f, 3.0f), vec3(0.0f, 0.0f, -1.0f));
+            auto mh = multi_hit<16>(through, prims, prims + 1);
+            if (!mh[0].hit || !mh[1].hit || mh[2].hit || !(mh[0].t < mh[1].t)) { std::cerr << "multi_hit known answer failed\n"; return 2; }
+            if (mh[0].t != closest_hit(through, prims, prims + 1).t) { std::cerr << "multi_hit[0] != closest_hit\n"; return 2; }
+            std::vector<hit_record> all(rays.size() * 4);
+            multi_hit<4>(rays.data(), rays.size(), prims, prims + 1, all.data(), true);
+            dump(out + "/hits_multi4.bin", all.data(), all.size());
+        }
+
         // --- the same mesh with the BVH built on the GPU (replaces the host build + upload) ---
         {
             auto g_bvh = build<b200_index_bvh<triangle_type>>(tris.data(), tris.size());

@@ -13,6 +13,7 @@ sys.path.insert(0, ROOT)
 
 from oracle import bindings as O  # noqa: E402
 from visionaray_b200 import scenes as S  # noqa: E402
+from visionaray_b200._native import NODE_DTYPE  # noqa: E402
 
 FLT_MAX = 3.4028234663852886e38
 HERE = os.path.dirname(os.path.abspath(__file__))
@@ -53,7 +54,24 @@ def main():
     frames["k1_matrix_ssaa2"], frames["k1_matrix_ssaa2_depth"], _ = O.ref_frame_matrix(sc, fp, view, proj, S.default_material(0), S.point_light(eye))
     np.savez_compressed(os.path.join(HERE, "golden_frames.npz"), **frames)
     print("wrote golden_queries.npz, golden_frames.npz")
+    multi_hit_vectors()
+
+
+def multi_hit_vectors():
+    """multi_hit<4> / multi_hit<16> of the reference on the scenes and rays of golden_queries.npz."""
+    g = np.load(os.path.join(HERE, "golden_queries.npz"))
+    out = {}
+    for key, kind in (("tri", 0), ("sph", 1)):
+        sc = S.HostScene(kind, g[f"{key}_prims"], g[f"{key}_nodes"].view(NODE_DTYPE).reshape(-1), g[f"{key}_indices"], None, key)
+        rays = g[f"{key}_rays"][:600]
+        for n in (4, 16):
+            out[f"{key}_multi{n}"] = O.ref_multi_hit(sc, rays, n).view(np.uint8)
+    np.savez_compressed(os.path.join(HERE, "golden_multi_hit.npz"), **out)
+    print("wrote golden_multi_hit.npz")
 
 
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "multi_hit":
+        multi_hit_vectors()          # adds golden_multi_hit.npz without touching the older fixtures
+    else:
+        main()

@@ -10,6 +10,7 @@
 #include "../../visionaray_b200/csrc/bvh8_traverse.cuh"
 #include "../../visionaray_b200/csrc/bvh2_exact.cuh"
 #include "../../visionaray_b200/csrc/build_ploc.cuh"
+#include "../../visionaray_b200/csrc/multi_hit.cuh"
 #include <algorithm>
 #include <numeric>
 
@@ -130,6 +131,35 @@ void hs_query_exact(int prim_kind, int any, const void* prims, const void* nodes
         else     trace_exact<false>(s, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz, mt, b);
         out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
         out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
+    }
+}
+
+// multi_hit<N>: both traversals of csrc/multi_hit.cuh, one ray after the other
+void hs_multi_hit_wide(void* h, const void* rays, size_t n_rays, int max_hits, void* hits)
+{
+    auto* w = reinterpret_cast<HostWide*>(h);
+    WideScene s{ w->nodes.data(), w->prims.data(), w->prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        RayCtx rc;
+        ray_ctx_init(rc, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz);
+        MultiHitSink sink; sink.rec = reinterpret_cast<Hit32*>(hits) + i * (size_t)max_hits; sink.n = max_hits;
+        sink.reset();
+        multi_hit_wide(s, rc, sink);
+    }
+}
+
+void hs_multi_hit_exact(int prim_kind, const void* prims, const void* nodes2, const uint32_t* indices,
+                        const void* rays, size_t n_rays, int max_hits, void* hits)
+{
+    ExactScene s{ reinterpret_cast<const Node32*>(nodes2), prims, indices, prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        MultiHitSink sink; sink.rec = reinterpret_cast<Hit32*>(hits) + i * (size_t)max_hits; sink.n = max_hits;
+        sink.reset();
+        multi_hit_exact(s, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz, sink);
     }
 }
 

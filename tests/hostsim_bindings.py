@@ -31,6 +31,8 @@ def lib():
         l.hs_prims.argtypes = [vp]
         l.hs_query_wide.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp, vp]
         l.hs_query_exact.argtypes = [C.c_int, C.c_int, vp, vp, vp, vp, sz, C.c_float, vp, vp]
+        l.hs_multi_hit_wide.argtypes = [vp, vp, sz, C.c_int, vp]
+        l.hs_multi_hit_exact.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_int, vp]
         l.hs_build_ploc.restype = sz
         l.hs_build_ploc.argtypes = [C.c_int, vp, sz, C.c_int, C.c_float, C.c_float, vp, sz, vp, vp]
         _lib = l
@@ -69,6 +71,11 @@ class HostWide:
         lib().hs_query_wide(self.h, int(any_hit), _p(rays), rays.shape[0], max_t, _p(max_t_per_ray), _p(hits))
         return hits
 
+    def multi_hit(self, rays, max_hits):
+        hits = np.zeros((rays.shape[0], max_hits), dtype=HIT_DTYPE)
+        lib().hs_multi_hit_wide(self.h, _p(rays), rays.shape[0], max_hits, _p(hits))
+        return hits
+
     def close(self):
         if self.h:
             lib().hs_free(self.h)
@@ -82,6 +89,13 @@ def query_exact(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_p
     hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
     lib().hs_query_exact(scene.prim_kind, int(any_hit), _p(scene.prims), _p(scene.nodes), _p(scene.indices), _p(rays),
                          rays.shape[0], max_t, _p(max_t_per_ray), _p(hits))
+    return hits
+
+
+def multi_hit_exact(scene, rays, max_hits):
+    hits = np.zeros((rays.shape[0], max_hits), dtype=HIT_DTYPE)
+    lib().hs_multi_hit_exact(scene.prim_kind, _p(scene.prims), _p(scene.nodes), _p(scene.indices), _p(rays), rays.shape[0],
+                             max_hits, _p(hits))
     return hits
 
 

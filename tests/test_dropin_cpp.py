@@ -47,6 +47,8 @@ def test_dropin_program_matches_oracle(gpu):
         assert exact.tobytes() == want.tobytes()
         assert classify_closest(want, wide)["bad"] == 0
         assert (occ["hit"] == O.oracle_query(sc, rays, True, 0.5)["hit"]).all()
+        multi = np.fromfile(os.path.join(d, "hits_multi4.bin"), dtype=O.HIT_DTYPE).reshape(-1, 4)     # multi_hit<4>(), reference order
+        assert multi.tobytes() == O.oracle_multi_hit(sc, rays, 4).tobytes()
         built = np.fromfile(os.path.join(d, "hits_gpu_built.bin"), dtype=O.HIT_DTYPE)     # build<b200_index_bvh<P>>()
         assert classify_closest(want, built)["bad"] == 0
         eye = (0.0, 0.0, 3.0)

@@ -189,6 +189,29 @@ def any_hit(scenes, rays, max_t=FLT_MAX, max_t_per_ray=None, hits=None, traverse
     return _query(N.cuda_lib().vsb_any_hit, scenes, rays, max_t, max_t_per_ray, hits, traverse, stream)
 
 
+def multi_hit(scenes, rays, max_hits=16, hits=None, traverse=TRAVERSE_WIDE, stream=None):
+    """multi_hit<max_hits>(r, begin, end) over a ray list (detail/traverse_linear.inl:325-380): per ray
+    the max_hits closest intersections sorted by t, misses behind.  numpy rays -> (n, max_hits) HIT_DTYPE
+    array; torch CUDA rays -> (n, max_hits, 8) int32 tensor."""
+    if isinstance(scenes, Scene):
+        scenes = [scenes]
+    arr = _scene_array(scenes)
+    n = rays.shape[0]
+    if isinstance(rays, np.ndarray):
+        if hits is None:
+            hits = np.zeros((n, max_hits), dtype=N.HIT_DTYPE)
+        _check(N.cuda_lib().vsb_multi_hit(arr, len(scenes), N.ptr(rays), n, max_hits, N.ptr(hits), MEM_HOST, traverse, stream),
+               "vsb_multi_hit")
+        return hits
+    import torch
+
+    if hits is None:
+        hits = torch.empty((n, max_hits, 8), dtype=torch.int32, device=rays.device)
+    _check(N.cuda_lib().vsb_multi_hit(arr, len(scenes), C.c_void_p(rays.data_ptr()), n, max_hits,
+                                      C.c_void_p(hits.data_ptr()), MEM_DEVICE, traverse, stream), "vsb_multi_hit")
+    return hits
+
+
 def tiles_of_rank(width, height, rank, nranks) -> int:
     n = C.c_int(0)
     _check(N.cuda_lib().vsb_tiles_of_rank(width, height, rank, nranks, C.byref(n)), "vsb_tiles_of_rank")

@@ -15,6 +15,7 @@
 #include "../../include/vsnray_b200.h"
 #include "kernels.cuh"
 #include "build_ploc.cuh"
+#include "multi_hit.cuh"
 
 #include "capi_scene.inl"
 #include "capi_build.inl"
@@ -260,6 +261,46 @@ extern "C" int vsb_any_hit(const vsb_scene* const* scenes, int n_scenes, const v
                            float max_t, const float* max_t_per_ray, vsb_hit* hits, int mem, int traverse, void* cuda_stream)
 {
     return run_query(true, scenes, n_scenes, rays, n_rays, max_t, max_t_per_ray, hits, mem, traverse, cuda_stream);
+}
+
+// multi_hit<N>() over a ray list: N records per ray, sorted by t (csrc/multi_hit.cuh)
+extern "C" int vsb_multi_hit(const vsb_scene* const* scenes, int n_scenes, const vsb_ray* rays, size_t n_rays,
+                             int max_hits, vsb_hit* hits, int mem, int traverse, void* cuda_stream)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (max_hits < 1 || max_hits > VSB_MULTI_HIT_MAX) return VSB_ERR_BAD_ARG;
+    if (n_rays == 0) return VSB_OK;
+    if (!rays || !hits) return VSB_ERR_BAD_ARG;
+    if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT) return VSB_ERR_BAD_ARG;
+    if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
+    const bool exact = traverse == VSB_TRAVERSE_EXACT;
+    if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
+    const vsb::Ray32* d_rays = reinterpret_cast<const vsb::Ray32*>(rays);
+    vsb::Hit32* d_hits = reinterpret_cast<vsb::Hit32*>(hits);
+    const size_t hit_bytes = n_rays * (size_t)max_hits * sizeof(vsb_hit);
+    if (mem == VSB_MEM_HOST)
+    {
+        void *a = nullptr, *b = nullptr;
+        rc = stage(0, n_rays * sizeof(vsb_ray), &a); if (rc) return rc;
+        rc = stage(1, hit_bytes, &b); if (rc) return rc;
+        VSB_CUDA(cudaMemcpyAsync(a, rays, n_rays * sizeof(vsb_ray), cudaMemcpyHostToDevice, st));
+        d_rays = reinterpret_cast<const vsb::Ray32*>(a); d_hits = reinterpret_cast<vsb::Hit32*>(b);
+    }
+    const unsigned blocks = (unsigned)((n_rays + 127) / 128);
+    VSB_CUDA(cudaEventRecord(g.ev0, st));
+    if (exact) vsb::multi_hit_kernel<true><<<blocks, 128, 0, st>>>(g.d_scenes, n_scenes, d_rays, n_rays, max_hits, d_hits);
+    else       vsb::multi_hit_kernel<false><<<blocks, 128, 0, st>>>(g.d_scenes, n_scenes, d_rays, n_rays, max_hits, d_hits);
+    ++g.launches;
+    VSB_CUDA(cudaGetLastError());
+    VSB_CUDA(cudaEventRecord(g.ev1, st));
+    if (mem == VSB_MEM_HOST)
+    {
+        VSB_CUDA(cudaMemcpyAsync(hits, d_hits, hit_bytes, cudaMemcpyDeviceToHost, st));
+        VSB_CUDA(cudaStreamSynchronize(st));
+    }
+    return VSB_OK;
 }
 
 // Host-side camera basis, exactly the arithmetic of cuda_sched_impl_frame
