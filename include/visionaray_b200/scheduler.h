@@ -11,7 +11,8 @@
 //   hit_record<ray, primitive<unsigned>>    math/intersect.h:88-115, detail/bvh/hit_record.h:30-46   hit_record
 //   pinhole_camera                          pinhole_camera.h   pinhole_camera
 //   plastic<T> / matte<T> / point_light<T>  material.h, point_light.h              same names
-//   make_kernel_params(...)                 kernels.h:328-509  same name (per-face normals overloads)
+//   make_kernel_params(...)                 kernels.h:328-509  same name (normals per face / per vertex, tex coords + textures, colours)
+//   emissive / mirror / generic_material     material.h, generic_material.h  same names; texture_ref2d = texture_ref<vector<4, unorm<8>>, 2>
 //   simple/whitted/pathtracing::kernel<KP>  detail/*.inl       same names (+ ao::kernel, src/examples/ao)
 //   pixel_sampler::*_type                   detail/sched_common.h:29-52            same names
 //   make_sched_params(...)                  scheduler.h:164-242                    same name
@@ -92,6 +93,16 @@ public:
     void set_normals(vec3 const* normals, size_t count)
     {
         detail::check(vsb_scene_set_normals(scene_, reinterpret_cast<float const*>(normals), count, VSB_MEM_HOST), "vsb_scene_set_normals");
+    }
+
+    // normals with their binding, colours, tex coords and textures kept with the device tree (deep copy);
+    // frames whose kernel_params pass nullptr normals then use them
+    template <typename SP /* surface_params */>
+    void set_surface(SP const& sp)
+    {
+        std::vector<vsb_texture> texs;
+        vsb_surface_desc d = sp.flatten(texs);
+        detail::check(vsb_scene_set_surface(scene_, sp.present ? &d : nullptr, VSB_MEM_HOST), "vsb_scene_set_surface");
     }
 
 protected:
@@ -350,6 +361,125 @@ private:
     T ka_ = T(0), kd_ = T(0);
 };
 
+// emissive<T> / mirror<T> (material.h, detail/material/{emissive,mirror}.inl)
+template <typename T = float>
+class emissive
+{
+public:
+    void set_ce(vec3 const& c) { ce_ = c; } vec3 get_ce() const { return ce_; }
+    void set_ls(T ls) { ls_ = ls; } T get_ls() const { return ls_; }
+    vsb_material flatten() const
+    {
+        vsb_material m; std::memset(&m, 0, sizeof(m));
+        for (int i = 0; i < 3; ++i) m.cd[i] = ce_[i];
+        m.kd = ls_; m.kind = VSB_MAT_EMISSIVE;
+        return m;
+    }
+private:
+    vec3 ce_ = vec3(0.0f);
+    T ls_ = T(0);
+};
+
+template <typename T = float>
+class mirror
+{
+public:
+    void set_cr(vec3 const& c) { cr_ = c; } vec3 get_cr() const { return cr_; }
+    void set_kr(T k) { kr_ = k; } T get_kr() const { return kr_; }
+    void set_ior(vec3 const& c) { ior_ = c; } void set_ior(T v) { ior_ = vec3(v); } vec3 get_ior() const { return ior_; }
+    void set_absorption(vec3 const& c) { abs_ = c; } void set_absorption(T v) { abs_ = vec3(v); } vec3 get_absorption() const { return abs_; }
+    vsb_material flatten() const
+    {
+        vsb_material m; std::memset(&m, 0, sizeof(m));
+        for (int i = 0; i < 3; ++i) { m.cs[i] = cr_[i]; m.ca[i] = ior_[i]; m.cd[i] = abs_[i]; }
+        m.ks = kr_; m.kind = VSB_MAT_MIRROR;
+        return m;
+    }
+private:
+    vec3 cr_ = vec3(0.0f), ior_ = vec3(0.0f), abs_ = vec3(0.0f);
+    T kr_ = T(0);
+};
+
+// generic_material<emissive<T>, matte<T>, mirror<T>, plastic<T>> (generic_material.h:22-70): a variant of
+// the four; the flattened record carries the alternative in `kind`
+template <typename ...Ts>
+class generic_material
+{
+public:
+    generic_material() { std::memset(&m_, 0, sizeof(m_)); m_.kind = VSB_MAT_MATTE; }
+    template <typename M, typename = decltype(std::declval<M const&>().flatten())>
+    generic_material(M const& material) : m_(material.flatten()) {}
+    bool is_emissive() const { return m_.kind == VSB_MAT_EMISSIVE; }
+    vsb_material flatten() const { return m_; }
+private:
+    vsb_material m_;
+};
+
+// texture_ref<vector<4, unorm<8>>, 2> (texture/detail/texture2d.h, texture_common.h:36-92,172-215): a
+// non-owning view of RGBA8 texels with filter and address modes
+enum tex_address_mode { Wrap = 0, Mirror, Clamp };
+enum tex_filter_mode { Nearest = 0, Linear };
+struct unorm8x4 { unsigned char x, y, z, w; };
+
+class texture_ref2d
+{
+public:
+    texture_ref2d() = default;
+    texture_ref2d(size_t w, size_t h) : width_(w), height_(h) {}
+    void reset(unorm8x4 const* data) { data_ = data; }
+    unorm8x4 const* data() const { return data_; }
+    size_t width() const { return width_; }
+    size_t height() const { return height_; }
+    void set_address_mode(size_t index, tex_address_mode mode) { address_[index] = mode; }
+    void set_address_mode(tex_address_mode mode) { address_[0] = address_[1] = mode; }
+    tex_address_mode get_address_mode(size_t index) const { return address_[index]; }
+    void set_filter_mode(tex_filter_mode mode) { filter_ = mode; }
+    tex_filter_mode get_filter_mode() const { return filter_; }
+    vsb_texture flatten() const
+    {
+        vsb_texture t; std::memset(&t, 0, sizeof(t));
+        t.data = data_; t.width = int(width_); t.height = int(height_);
+        t.filter = int(filter_); t.address[0] = int(address_[0]); t.address[1] = int(address_[1]);
+        return t;
+    }
+private:
+    unorm8x4 const* data_ = nullptr;
+    size_t width_ = 0, height_ = 0;
+    tex_address_mode address_[2] = { Wrap, Wrap };
+    tex_filter_mode filter_ = Nearest;
+};
+
+// binding tags (tags.h)
+struct normals_per_face_binding   { static const int id = VSB_NORMALS_PER_FACE; };
+struct normals_per_vertex_binding { static const int id = VSB_NORMALS_PER_VERTEX; };
+struct colors_per_face_binding    { static const int id = VSB_COLORS_PER_FACE; };
+struct colors_per_vertex_binding  { static const int id = VSB_COLORS_PER_VERTEX; };
+
+// The members of kernel_params beyond prims / materials / lights (kernels.h:194-319): host arrays.
+// present == false: per-face normals only (the first two make_kernel_params overloads).
+struct surface_params
+{
+    bool present;
+    int normal_binding, color_binding;
+    vec3 const* normals;
+    vec3 const* colors;
+    vec2 const* tex_coords;
+    texture_ref2d const* textures; size_t num_textures;
+
+    vsb_surface_desc flatten(std::vector<vsb_texture>& texs) const
+    {
+        vsb_surface_desc d; std::memset(&d, 0, sizeof(d));
+        d.normal_binding = normal_binding; d.color_binding = color_binding;
+        d.normals = reinterpret_cast<float const*>(normals);
+        d.colors = reinterpret_cast<float const*>(colors);
+        d.tex_coords = reinterpret_cast<float const*>(tex_coords);
+        texs.clear();
+        for (size_t i = 0; i < num_textures; ++i) texs.push_back(textures[i].flatten());
+        d.textures = texs.data(); d.n_textures = int(texs.size());
+        return d;
+    }
+};
+
 template <typename T = float>
 class point_light
 {
@@ -377,8 +507,6 @@ private:
 // Kernel parameters and the built-in kernels (kernels.h:94-509, detail/{simple,whitted,pathtracing}.inl)
 //
 
-struct normals_per_face_binding {};
-
 template <typename Material>
 struct kernel_params
 {
@@ -391,6 +519,10 @@ struct kernel_params
     float epsilon;
     vec4 bg_color;
     vec4 ambient_color;
+    // normals per vertex / colours / tex coords + textures (the later make_kernel_params overloads).  Host
+    // arrays given here are uploaded by every frame(); attach them once with b200_index_bvh::set_surface()
+    // and pass nullptr normals to keep them resident, like the thrust vectors of a cuda_sched user
+    surface_params surface;
 };
 
 // make_kernel_params(normals_per_face_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-409
@@ -403,7 +535,47 @@ auto make_kernel_params(normals_per_face_binding, b200_bvh_ref const* begin, b20
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, normals, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color };
+    return kernel_params<M>{ begin, end, normals, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+                             surface_params{ false, 0, 0, nullptr, nullptr, nullptr, nullptr, 0 } };
+}
+
+// make_kernel_params(normals_per_vertex_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-393
+template <typename Materials>
+auto make_kernel_params(normals_per_vertex_binding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
+                        Materials const& materials, point_light<float> const* lbegin, point_light<float> const* lend,
+                        unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
+                        vec4 const& ambient_color = vec4(0.0f))
+    -> kernel_params<typename std::decay<decltype(materials[0])>::type>
+{
+    using M = typename std::decay<decltype(materials[0])>::type;
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+                             surface_params{ true, VSB_NORMALS_PER_VERTEX, 0, normals, nullptr, nullptr, nullptr, 0 } };
+}
+
+// w/ normals and textures  kernels.h:395-437.  `textures`: contiguous container of texture_ref2d, by geom_id
+template <typename NormalBinding, typename Materials, typename Textures, int = NormalBinding::id>
+auto make_kernel_params(NormalBinding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals, vec2 const* tex_coords,
+                        Materials const& materials, Textures const& textures, point_light<float> const* lbegin,
+                        point_light<float> const* lend, unsigned num_bounces = 5, float epsilon = FLT_EPSILON,
+                        vec4 const& bg_color = vec4(0.0f), vec4 const& ambient_color = vec4(0.0f))
+    -> kernel_params<typename std::decay<decltype(materials[0])>::type>
+{
+    using M = typename std::decay<decltype(materials[0])>::type;
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+                             surface_params{ true, NormalBinding::id, 0, normals, nullptr, tex_coords, &textures[0], textures.size() } };
+}
+
+// w/ normals, colors and textures  kernels.h:440-509
+template <typename NormalBinding, typename ColorBinding, typename Materials, typename Textures, int = NormalBinding::id, int = ColorBinding::id>
+auto make_kernel_params(NormalBinding, ColorBinding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
+                        vec2 const* tex_coords, Materials const& materials, vec3 const* colors, Textures const& textures,
+                        point_light<float> const* lbegin, point_light<float> const* lend, unsigned num_bounces = 5,
+                        float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f), vec4 const& ambient_color = vec4(0.0f))
+    -> kernel_params<typename std::decay<decltype(materials[0])>::type>
+{
+    using M = typename std::decay<decltype(materials[0])>::type;
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+                             surface_params{ true, NormalBinding::id, ColorBinding::id, normals, colors, tex_coords, &textures[0], textures.size() } };
 }
 
 namespace simple      { template <typename KP> struct kernel { KP params; static const int id = VSB_KERNEL_SIMPLE; }; }
@@ -650,6 +822,12 @@ public:
 
         std::vector<vsb_scene const*> scenes;
         for (auto it = kp.prims_begin; it != kp.prims_end; ++it) scenes.push_back(it->scene);
+        if (kp.surface.present && kp.surface.normals && !scenes.empty())
+        {
+            std::vector<vsb_texture> texs;
+            vsb_surface_desc sd = kp.surface.flatten(texs);
+            detail::check(vsb_scene_set_surface(const_cast<vsb_scene*>(scenes[0]), &sd, VSB_MEM_HOST), "vsb_scene_set_surface");
+        }
         detail::check(vsb_frame(scenes.data(), int(scenes.size()), &d, nullptr), "vsb_frame");
 
         sparams.rt.end_frame();

@@ -67,8 +67,10 @@ typedef struct vsb_hit {
     uint32_t pad;
 } vsb_hit;
 
-/* plastic<float> / matte<float> parameters (material.h, detail/material/{plastic,matte}.inl),
- * flattened; the adaptor fills it through the reference's getters. 64 B. */
+/* One member of generic_material<emissive, matte, mirror, plastic> (generic_material.h, material.h,
+ * detail/material/*.inl), flattened; the adaptor fills it through the reference's getters. 64 B.
+ *   VSB_MAT_PLASTIC  ca ka cd kd cs ks spec_exp        VSB_MAT_MATTE    ca ka cd kd
+ *   VSB_MAT_EMISSIVE cd = ce, kd = ls                  VSB_MAT_MIRROR   cs = cr, ks = kr, ca = ior, cd = absorption */
 typedef struct vsb_material {
     float ca[3]; float ka;
     float cd[3]; float kd;
@@ -84,7 +86,37 @@ typedef struct vsb_point_light {
     float att_lin; float att_quad; float pad[2];
 } vsb_point_light;
 
-enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1 };
+enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1, VSB_MAT_EMISSIVE = 2, VSB_MAT_MIRROR = 3 };
+
+/* texture_ref<vector<4, unorm<8>>, 2> (texture/detail/texture2d.h, texture_common.h:36-92): RGBA8
+ * texels, row-major, texel(x, y) = data[y * width + x].  width or height 0 = "no texture" (tex_color 1,
+ * get_surface.h:443-445).  filter: tex_filter_mode Nearest / Linear; address: tex_address_mode per axis
+ * (texture/forward.h:18-34; BSpline / CardinalSpline filters and Border are not supported). */
+enum { VSB_TEX_NEAREST = 0, VSB_TEX_LINEAR = 1 };
+enum { VSB_TEX_WRAP = 0, VSB_TEX_MIRROR = 1, VSB_TEX_CLAMP = 2 };
+typedef struct vsb_texture {
+    const void* data;
+    int32_t width, height;
+    int32_t filter;
+    int32_t address[2];
+} vsb_texture;
+
+/* What get_surface() reads besides the hit record: the members of kernel_params beyond prims /
+ * materials / lights (kernels.h:194-319) with their binding tags (tags.h).  vector<3,float> is
+ * 16 bytes, vector<2,float> 8. */
+enum { VSB_NORMALS_PER_FACE = 0, VSB_NORMALS_PER_VERTEX = 1 };
+enum { VSB_COLORS_NONE = 0, VSB_COLORS_PER_FACE = 1, VSB_COLORS_PER_VERTEX = 2 };
+typedef struct vsb_surface_desc {
+    int32_t normal_binding;       /* per face: normals[prim_id] (get_normal.h:28-37); per vertex: shading normal =
+                                     normalize(lerp(normals[3 prim_id + 0..2], u, v)) (get_shading_normal.h:60-76),
+                                     geometric normal = normalize(cross(e1, e2)) (get_normal.h:96-101) */
+    int32_t color_binding;        /* colors[prim_id] or lerp(colors[3 prim_id + 0..2], u, v) (get_color.h:24-58) */
+    const float* normals;         /* n_prims (per face) or 3 n_prims (per vertex) x 16 B */
+    const float* colors;          /* like normals; NULL with VSB_COLORS_NONE */
+    const float* tex_coords;      /* 3 n_prims x 8 B (get_tex_coord.h:24-40); NULL = params without textures */
+    const vsb_texture* textures;  /* n_textures entries, indexed by geom_id (geom_id >= n_textures: no texture) */
+    int32_t n_textures;
+} vsb_surface_desc;
 enum { VSB_PRIM_TRIANGLE = 0, VSB_PRIM_SPHERE = 1 };
 enum { VSB_KERNEL_SIMPLE = 0, VSB_KERNEL_WHITTED = 1, VSB_KERNEL_AO = 2, VSB_KERNEL_PATHTRACING = 3 };
 enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2,
@@ -165,6 +197,9 @@ typedef struct vsb_frame_desc {
      * matrix<4,4,float> layout: 16 floats, column-major. */
     int32_t  camera_kind;                /* VSB_CAM_BASIS (cam_eye/u/v/w above) or VSB_CAM_MATRIX */
     float    view_matrix[16], proj_matrix[16];
+    int32_t  generic_materials;          /* non-zero: `materials` is a generic_material<emissive, matte, mirror, plastic>
+                                            list, i.e. entries may be VSB_MAT_EMISSIVE / VSB_MAT_MIRROR (pathtracing.inl:93-104,
+                                            whitted.inl:66-122).  Detected automatically when params_mem == VSB_MEM_HOST. */
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;
@@ -209,6 +244,13 @@ int  vsb_scene_destroy(vsb_scene* s);
 /* per-face normals kept on the device with the scene (what a cuda_sched user holds in a thrust
  * device_vector and hands to make_kernel_params, src/viewer/viewer.cpp:507-521); n = n_prims */
 int  vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem);
+/* The surface description of the scene's triangles, deep-copied to the device (arrays and texels;
+ * mem = where desc's arrays live) and used by every later vsb_frame() on this scene in place of the
+ * per-face normals: what a cuda_sched user uploads once into thrust vectors / cuda_texture objects and
+ * hands to make_kernel_params(normal_binding[, color_binding], ..., normals, tex_coords, materials[, colors],
+ * textures, ...) (kernels.h:395-509, src/viewer/viewer.cpp:507-541,797-851).  desc == NULL detaches it.
+ * The AO kernel (src/examples/ao) takes per-face normals only. */
+int  vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc, int mem);
 /* diagnostics: out[0]=wide nodes, out[1]=wide node bytes, out[2]=leaf prim records,
  * out[3]=prim record bytes, out[4]=bvh2 max depth, out[5]=bvh2 nodes */
 int  vsb_scene_stats(const vsb_scene* s, uint64_t* out, int n);

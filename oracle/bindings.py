@@ -32,6 +32,38 @@ class Counters(C.Structure):
     _fields_ = [("n_inner", C.c_uint64), ("n_prim", C.c_uint64), ("n_rays", C.c_uint64), ("n_hits", C.c_uint64)]
 
 
+class Texture(C.Structure):
+    _fields_ = [("data", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("filter", C.c_int32),
+                ("address", C.c_int32 * 2)]
+
+
+class Surface(C.Structure):
+    _fields_ = [("normal_binding", C.c_int32), ("color_binding", C.c_int32), ("normals", C.c_void_p),
+                ("colors", C.c_void_p), ("tex_coords", C.c_void_p), ("textures", C.c_void_p), ("n_textures", C.c_int32)]
+
+
+def make_texture(t) -> Texture:
+    o = Texture()
+    if t is not None:
+        o.data = t.data.ctypes.data; o.height, o.width = t.data.shape[0], t.data.shape[1]
+        o.filter = t.filter; o.address[0], o.address[1] = t.address
+    return o
+
+
+def make_surface(sd):
+    """visionaray_b200.scenes.SurfaceData -> (Surface, keepalive)."""
+    s = Surface()
+    s.normal_binding, s.color_binding = sd.normal_binding, sd.color_binding
+    s.normals = sd.normals.ctypes.data
+    s.colors = sd.colors.ctypes.data if sd.colors is not None else None
+    s.tex_coords = sd.tex_coords.ctypes.data if sd.tex_coords is not None else None
+    texs = None
+    if sd.textures:
+        texs = (Texture * len(sd.textures))(*[make_texture(t) for t in sd.textures])
+        s.textures = C.cast(texs, C.c_void_p); s.n_textures = len(sd.textures)
+    return s, texs
+
+
 def _p(a):
     return C.c_void_p(a.ctypes.data) if a is not None else C.c_void_p(0)
 
@@ -54,6 +86,8 @@ def oracle_lib():
         lib.vso_camera_basis.argtypes = [vp, vp, vp, vp, vp]
         lib.vso_frame_matrix.argtypes = [vp, vp, vp, C.POINTER(Bvh), vp, vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
         lib.vso_mat4_inverse.argtypes = [vp, vp]
+        lib.vso_frame_surface.argtypes = [vp, C.POINTER(Bvh), vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
+        lib.vso_tex2d.argtypes = [vp, C.c_float, C.c_float, vp]
         lib.vso_multi_hit.argtypes = [C.POINTER(Bvh), C.c_int, vp, sz, C.c_int, vp, C.c_int]
         lib.vso_bvh_max_depth.argtypes = [C.POINTER(Bvh)]
         lib.vso_sampler_init.restype = C.c_uint32
@@ -82,6 +116,10 @@ def ref_lib(fast: bool = False):
         lib.ref_frame.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
         lib.ref_frame_matrix.argtypes = [vp, vp, vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, vp, C.c_int, vp]
         lib.ref_camera_matrices.argtypes = [vp, C.c_float, C.c_float, vp, vp]
+        if hasattr(lib, "ref_frame_surface"):
+            lib.ref_frame_surface.argtypes = [vp, vp, sz, vp, sz, vp, sz, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp,
+                                              vp, C.c_int]
+            lib.ref_tex2d.argtypes = [vp, C.c_float, C.c_float, vp]
         if hasattr(lib, "ref_multi_hit"):
             lib.ref_multi_hit.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, sz, vp, C.c_int]
         lib.ref_query_timed.restype = C.c_double
@@ -158,6 +196,48 @@ def oracle_frame(scene, fp, materials, lights, rgba=None, nthreads=0, counters=N
     oracle_lib().vso_frame(C.byref(fp), C.byref(b), _p(scene.normals), _p(materials), _p(lights), _p(rgba),
                            C.byref(c), nthreads or (os.cpu_count() or 1))
     return rgba
+
+
+def oracle_frame_surface(scene, fp, surface, materials, lights, rgba=None, nthreads=0):
+    """vso_frame_surface: kernel_params with a surface description + generic materials."""
+    if rgba is None:
+        rgba = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+    b = make_bvh(scene)
+    s, keep = make_surface(surface)
+    c = Counters()
+    oracle_lib().vso_frame_surface(C.byref(fp), C.byref(b), C.byref(s), _p(materials), _p(lights), _p(rgba), C.byref(c),
+                                   nthreads or (os.cpu_count() or 1))
+    del keep
+    return rgba
+
+
+def ref_frame_surface(scene, fp, surface, materials, lights, rgba=None, nthreads=0):
+    """The same through the unmodified reference headers (make_kernel_params / get_surface / tex2D)."""
+    if rgba is None:
+        rgba = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+    s, keep = make_surface(surface)
+    rc = ref_lib().ref_frame_surface(C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes), scene.nodes.shape[0],
+                                     _p(scene.indices), scene.indices.shape[0], s.normal_binding, s.color_binding,
+                                     s.normals, s.colors, s.tex_coords, s.textures, s.n_textures, _p(materials), _p(lights),
+                                     _p(rgba), nthreads or (os.cpu_count() or 1))
+    del keep
+    if rc != 0:
+        raise ValueError("ref_frame_surface: unsupported kernel")
+    return rgba
+
+
+def oracle_tex2d(tex, s, t):
+    o = make_texture(tex)
+    out = np.zeros(4, dtype=np.float32)
+    oracle_lib().vso_tex2d(C.byref(o), s, t, _p(out))
+    return out
+
+
+def ref_tex2d(tex, s, t):
+    o = make_texture(tex)
+    out = np.zeros(4, dtype=np.float32)
+    ref_lib().ref_tex2d(C.byref(o), s, t, _p(out))
+    return out
 
 
 def oracle_frame_matrix(scene, fp, view, proj, materials, lights, rgba=None, depth=None, want_depth=True, nthreads=0):

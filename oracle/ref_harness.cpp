@@ -38,6 +38,8 @@
 #include <visionaray/detail/tiled_sched.h>
 #include <visionaray/sampling.h>
 #include <visionaray/get_normal.h>
+#include <visionaray/generic_material.h>
+#include <visionaray/texture/texture.h>
 
 using namespace visionaray;
 

@@ -312,6 +312,147 @@ struct ao_tiled_adapter
     auto operator()(R ray, Sampler& s) const -> decltype(k(ray, s)) { return k(ray, s); }
 };
 
+
+// ---- kernel_params with a surface description: generic_material<emissive, matte,
+// mirror, plastic>, normals per face / per vertex, optional colours (per face / per vertex),
+// tex coords and texture_ref<vector<4, unorm<8>>, 2> -- all through the reference's own
+// make_kernel_params / get_surface / tex2D.  Scalar parity driver only.
+
+struct tex_pod { void const* data; int32_t width, height, filter, address[2]; };
+
+using gen_mat_t = generic_material<emissive<float>, matte<float>, mirror<float>, plastic<float>>;
+using tex_ref_t = texture_ref<vector<4, unorm<8>>, 2>;
+
+gen_mat_t make_generic(mat_pod const& m)
+{
+    if (m.kind == 2)
+    {
+        emissive<float> e;
+        e.set_ce(spec3(m.cd)); e.set_ls(m.kd);
+        return gen_mat_t(e);
+    }
+    if (m.kind == 3)
+    {
+        mirror<float> r;
+        r.set_cr(spec3(m.cs)); r.set_kr(m.ks);
+        r.set_ior(spec3(m.ca)); r.set_absorption(spec3(m.cd));
+        return gen_mat_t(r);
+    }
+    if (m.kind == 1)
+    {
+        matte<float> t;
+        t.set_ca(spec3(m.ca)); t.set_ka(m.ka);
+        t.set_cd(spec3(m.cd)); t.set_kd(m.kd);
+        return gen_mat_t(t);
+    }
+    plastic<float> p;
+    p.set_ca(spec3(m.ca)); p.set_ka(m.ka);
+    p.set_cd(spec3(m.cd)); p.set_kd(m.kd);
+    p.set_cs(spec3(m.cs)); p.set_ks(m.ks);
+    p.set_specular_exp(m.spec_exp);
+    return gen_mat_t(p);
+}
+
+template <typename KP>
+void run_surface_kernels(KP kparams, frame_params const& fp, float* rgba, int nthreads)
+{
+    if (fp.kernel == 0)
+    {
+        simple::kernel<KP> k{ kparams };
+        scalar_frame(no_sampler_adapter<simple::kernel<KP>>{ k }, fp, rgba, nthreads, nullptr);
+    }
+    else if (fp.kernel == 1)
+    {
+        whitted::kernel<KP> k{ kparams };
+        scalar_frame(no_sampler_adapter<whitted::kernel<KP>>{ k }, fp, rgba, nthreads, nullptr);
+    }
+    else
+    {
+        pathtracing::kernel<KP> k{ kparams };
+        scalar_frame(k, fp, rgba, nthreads, nullptr);
+    }
+}
+
+} // namespace
+
+extern "C" void ref_tex2d(void const* tex_, float s, float t, float* out4)
+{
+    tex_pod const& tp = *(tex_pod const*)tex_;
+    tex_ref_t tex(size_t(tp.width), size_t(tp.height));
+    tex.reset((vector<4, unorm<8>> const*)tp.data);
+    tex.set_filter_mode(tex_filter_mode(tp.filter));
+    tex.set_address_mode(0, tex_address_mode(tp.address[0]));
+    tex.set_address_mode(1, tex_address_mode(tp.address[1]));
+    vec4 c = tex2D(tex, vec2(s, t));
+    out4[0] = c.x; out4[1] = c.y; out4[2] = c.z; out4[3] = c.w;
+}
+
+extern "C" int ref_frame_surface(void const* fp_, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                                 uint32_t const* indices, size_t n_idx, int normal_binding, int color_binding,
+                                 float const* normals16, float const* colors16, float const* tex_coords,
+                                 void const* textures_, int n_textures, void const* mats_, void const* lights_,
+                                 float* rgba, int nthreads)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    if (fp.kernel == 2) return -1;
+    scene_host s{ make_ref<tri_t>(prims, n_prims, nodes, n_nodes, indices, n_idx) };
+    fill_scene(s, fp, nullptr, 0, (mat_pod const*)mats_, (light_pod const*)lights_);
+    aligned_vector<gen_mat_t> mats;
+    for (int i = 0; i < fp.n_materials; ++i) mats.push_back(make_generic(((mat_pod const*)mats_)[i]));
+    vec3 const* normals = reinterpret_cast<vec3 const*>(normals16);
+    vec3 const* colors  = reinterpret_cast<vec3 const*>(colors16);
+    // params with colours always carry tex coords + textures (kernels.h:271-319): without any, every
+    // texture is empty (tex_color 1, get_surface.h:443-445) and the coordinates are never read
+    aligned_vector<vec2> dummy_tc;
+    vec2 const* tcs = reinterpret_cast<vec2 const*>(tex_coords);
+    aligned_vector<tex_ref_t> texs;
+    bool const with_tex = tex_coords != nullptr;
+    if (!with_tex) { dummy_tc.resize(n_prims * 3, vec2(0.0f)); tcs = dummy_tc.data(); }
+    for (int i = 0; i < fp.n_materials; ++i)
+    {
+        tex_ref_t t(0, 0);
+        if (with_tex && i < n_textures)
+        {
+            tex_pod const& tp = ((tex_pod const*)textures_)[i];
+            t = tex_ref_t(size_t(tp.width), size_t(tp.height));
+            t.reset((vector<4, unorm<8>> const*)tp.data);
+            t.set_filter_mode(tex_filter_mode(tp.filter));
+            t.set_address_mode(0, tex_address_mode(tp.address[0]));
+            t.set_address_mode(1, tex_address_mode(tp.address[1]));
+        }
+        texs.push_back(t);
+    }
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+    auto lb = s.lights.data();
+    auto le = s.lights.data() + s.lights.size();
+    tri_ref_t const* pb = &s.ref;
+    tri_ref_t const* pe = &s.ref + 1;
+
+#define VSB_SURF(NB)                                                                                                         \
+    do {                                                                                                                     \
+        if (color_binding == 1)                                                                                              \
+            run_surface_kernels(make_kernel_params(NB{}, colors_per_face_binding{}, pb, pe, normals, tcs, mats.data(), colors, \
+                                                   texs.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads); \
+        else if (color_binding == 2)                                                                                         \
+            run_surface_kernels(make_kernel_params(NB{}, colors_per_vertex_binding{}, pb, pe, normals, tcs, mats.data(), colors, \
+                                                   texs.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads); \
+        else if (with_tex)                                                                                                   \
+            run_surface_kernels(make_kernel_params(NB{}, pb, pe, normals, tcs, mats.data(), texs.data(), lb, le,             \
+                                                   fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads);                \
+        else                                                                                                                 \
+            run_surface_kernels(make_kernel_params(NB{}, pb, pe, normals, mats.data(), lb, le,                               \
+                                                   fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads);                \
+    } while (0)
+    if (normal_binding == 1) VSB_SURF(normals_per_vertex_binding);
+    else                     VSB_SURF(normals_per_face_binding);
+#undef VSB_SURF
+    return 0;
+}
+
+namespace
+{
 } // namespace
 
 extern "C"

@@ -30,6 +30,8 @@ typedef struct { uint32_t geom_id, prim_id, pad0[2]; float v1[3], pad1, e1[3], p
 typedef struct { uint32_t geom_id, prim_id, pad0[2]; float center[3], pad1, radius, pad2[3]; } vso_sphere;
 typedef struct { float bbox_min[3]; uint32_t first; float bbox_max[3]; uint32_t num_prims; } vso_bvh_node;
 typedef struct { int32_t hit; uint32_t prim_id, geom_id; float t, u, v; uint32_t prim_list_index, pad; } vso_hit;
+/* kind 0 plastic, 1 matte (as before); 2 emissive: cd = ce, kd = ls (material.h emissive<T>);
+ * 3 mirror: cs = cr, ks = kr, ca = ior, cd = absorption (material.h mirror<T>, brdf.h:160-212) */
 typedef struct { float ca[3], ka, cd[3], kd, cs[3], ks, spec_exp; int32_t kind; float pad[2]; } vso_material;
 typedef struct { float pos[3], kl, cl[3], att_const, att_lin, att_quad, pad[2]; } vso_point_light;
 
@@ -116,6 +118,36 @@ float vso_depth_transform(const float pos[3], const float view[16], const float 
 void  vso_frame_matrix(const vso_frame_params* p, const float view[16], const float proj[16],
                        const vso_bvh* b, const float* normals16, const vso_material* mats,
                        const vso_point_light* lights, float* rgba, float* depth,
+                       vso_counters* counters, int nthreads);
+
+/* get_surface() inputs beyond per-face normals (kernels.h:194-319, get_surface.h:330-530).
+ * texture_ref<vector<4, unorm<8>>, 2> (texture/detail/texture2d.h): RGBA8 texels, row-major. */
+typedef struct {
+    const void* data; int32_t width, height;
+    int32_t filter;         /* 0 Nearest, 1 Linear (texture/forward.h tex_filter_mode) */
+    int32_t address[2];     /* 0 Wrap, 1 Mirror, 2 Clamp (tex_address_mode; texture/detail/filter/common.h:24-48) */
+} vso_texture;
+typedef struct {
+    int32_t normal_binding;      /* 0 normals_per_face_binding: normals[prim_id]; 1 normals_per_vertex_binding:
+                                    shading normal = normalize(lerp(normals[3 prim_id + 0..2], u, v))
+                                    (get_shading_normal.h:60-76), geometric normal = normalize(cross(e1, e2)) of
+                                    primitive(primitive_list_index) (get_surface.h:285-328, get_normal.h:96-101) */
+    int32_t color_binding;       /* 0 none, 1 colors_per_face_binding, 2 colors_per_vertex_binding (get_color.h:24-58) */
+    const float* normals;        /* vector<3,float>: 16 B each */
+    const float* colors;         /* vector<3,float>: 16 B each */
+    const float* tex_coords;     /* vector<2,float>: 8 B each, 3 per primitive (get_tex_coord.h:24-40); NULL = none */
+    const vso_texture* textures; /* by geom_id; width or height 0 -> tex_color 1 (get_surface.h:443-445) */
+    int32_t n_textures;
+} vso_surface;
+
+/* tex2D(texture_ref<vector<4, unorm<8>>, 2>, coord) -- texture/detail/sampler2d.h:81-113,
+ * filter/{nearest,linear}.h; out = 4 floats */
+void vso_tex2d(const vso_texture* tex, float s, float t, float out[4]);
+
+/* vso_frame() with kernel_params that carry a surface description and a
+ * generic_material<emissive, matte, mirror, plastic> list (surf may be NULL = vso_frame) */
+void vso_frame_surface(const vso_frame_params* p, const vso_bvh* b, const vso_surface* surf,
+                       const vso_material* mats, const vso_point_light* lights, float* rgba,
                        vso_counters* counters, int nthreads);
 
 /* max depth of the BVH2 (root = depth 1); the reference's traversal stack holds 31 entries

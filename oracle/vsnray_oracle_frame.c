@@ -49,6 +49,7 @@ typedef struct
     const vso_frame_params* p;
     const vso_bvh* b;
     const float* normals;
+    const vso_surface* surf;              /* NULL: per-face normals, no colours / textures */
     const vso_material* mats;
     const vso_point_light* lights;
     float* rgba;
@@ -97,16 +98,162 @@ static v3 blinn_f(const vso_material* m, v3 n, v3 wo, v3 wi)
     return scale(scale(schlick, nfactor), powf(hdotn, m->spec_exp));
 }
 
-/* plastic::shade -- detail/material/plastic.inl:18-37; matte::shade -- matte.inl:18-39 */
-static v3 shade(const vso_material* m, const vso_point_light* l, v3 pos, v3 n, v3 wo, v3 wi)
+/* The surface a kernel shades: get_surface() -- get_surface.h:330-530, surface.h:24-96.
+ * has_tex <=> the kernel_params carry colours / textures, i.e. the shade_record has a
+ * tex_color member and the materials' tex_color overloads are the ones instantiated. */
+typedef struct { v3 gn, sn, tex; int has_tex; const vso_material* m; } surf_t;
+
+/* plastic::shade -- detail/material/plastic.inl:18-37 (+ cd() with tex_color :176-183);
+ * matte::shade -- matte.inl:18-39 (:136-142); emissive::shade -- emissive.inl:22-27,76-90;
+ * mirror::shade -- mirror.inl:22-27 (specular_reflection::f == 0, brdf.h:176-185) */
+static v3 shade(const surf_t* s, const vso_point_light* l, v3 pos, v3 n, v3 wo, v3 wi)
 {
+    const vso_material* m = s->m;
+    if (m->kind == 2)
+    {
+        v3 ce = scale(ld3(m->cd), m->kd);
+        return s->has_tex ? scale(mul(s->tex, ld3(m->cd)), m->kd) : ce;
+    }
+    if (m->kind == 3) return v3m(0.0f, 0.0f, 0.0f);
     float ndotl = fmax0(dot(n, wi));
     v3 f = lambert_f(m);
+    if (s->has_tex) f = mul(s->tex, f);
     if (m->kind == 0) f = add(f, blinn_f(m, n, wo, wi));
     return scale(mul(scale(f, VSO_PI), light_intensity(l, pos)), ndotl);
 }
 
+/* material.ambient(): plastic / matte ca * ka; emissive and mirror 0 (emissive.inl:14-18, mirror.inl:14-18) */
+static v3 ambient_of(const vso_material* m)
+{
+    return m->kind <= 1 ? scale(ld3(m->ca), m->ka) : v3m(0.0f, 0.0f, 0.0f);
+}
+
+/* specular_bounce(): detail/whitted.inl:66-122 -- matte 0, mirror kr, everything else
+ * (plastic, emissive) the fall-through 0.1 */
+static float specular_kr(const vso_material* m)
+{
+    return m->kind == 1 ? 0.0f : (m->kind == 3 ? m->ks : 0.1f);
+}
+
 static v3 rgb_of_rgba(const float c[4]) { return v3m(c[0] * c[3], c[1] * c[3], c[2] * c[3]); }   /* from_rgba, detail/spectrum.inl:375-378 */
+
+
+/* map_tex_coord -- texture/detail/filter/common.h:24-48 */
+static float map_tex_coord(float coord, int texsize, int mode)
+{
+    float N = (float)texsize;
+    switch (mode)
+    {
+    case 1:   /* Mirror */
+        if ((((int)floorf(coord)) & 1) == 1) return (float)(texsize - 1) / (float)texsize - (coord - floorf(coord));
+        return coord - floorf(coord);
+    case 0:   /* Wrap */
+        return coord - floorf(coord);
+    default:  /* Clamp: clamp(coord, 0, 1 - 1/N) */
+    {
+        float hi = 1.0f - 1.0f / N;
+        return coord < 0.0f ? 0.0f : (coord > hi ? hi : coord);   /* max(lo, min(x, hi)) */
+    }
+    }
+}
+
+static inline float lerp1(float a, float b, float x) { return (1.0f - x) * a + x * b; }   /* math/detail/math.h:459-464 */
+
+/* tex2D for vector<4, unorm<8>> texels: filtering runs on the unnormalised integers, the result is
+ * converted to vector<4, int> (truncation) and normalised once, float(u) / double(255)
+ * (texture/detail/sampler2d.h:81-113, math/detail/unorm.inl:26-31);
+ * nearest -- filter/nearest.h:45-66, linear -- filter/linear.h:61-98 */
+void vso_tex2d(const vso_texture* tex, float s, float t, float out[4])
+{
+    const uint8_t* px = (const uint8_t*)tex->data;
+    const int w = tex->width, h = tex->height;
+    int q[4];
+    if (tex->filter == 0)
+    {
+        float cs = map_tex_coord(s, w, tex->address[0]), ct = map_tex_coord(t, h, tex->address[1]);
+        int lx = (int)(cs * (float)w), ly = (int)(ct * (float)h);
+        const uint8_t* e = px + 4 * ((size_t)ly * (size_t)w + (size_t)lx);
+        for (int k = 0; k < 4; ++k) q[k] = e[k];
+    }
+    else
+    {
+        float s1 = map_tex_coord(s - 0.5f / (float)w, w, tex->address[0]), t1 = map_tex_coord(t - 0.5f / (float)h, h, tex->address[1]);
+        float s2 = map_tex_coord(s + 0.5f / (float)w, w, tex->address[0]), t2 = map_tex_coord(t + 0.5f / (float)h, h, tex->address[1]);
+        int lx = (int)(s1 * (float)w), ly = (int)(t1 * (float)h);
+        int hx = (int)(s2 * (float)w), hy = (int)(t2 * (float)h);
+        const uint8_t* e00 = px + 4 * ((size_t)ly * (size_t)w + (size_t)lx);
+        const uint8_t* e10 = px + 4 * ((size_t)ly * (size_t)w + (size_t)hx);
+        const uint8_t* e01 = px + 4 * ((size_t)hy * (size_t)w + (size_t)lx);
+        const uint8_t* e11 = px + 4 * ((size_t)hy * (size_t)w + (size_t)hx);
+        float u = s1 * (float)w - (float)lx, v = t1 * (float)h - (float)ly;
+        for (int k = 0; k < 4; ++k)
+        {
+            float p1 = lerp1((float)e00[k], (float)e10[k], u);
+            float p2 = lerp1((float)e01[k], (float)e11[k], u);
+            q[k] = (int)lerp1(p1, p2, v);
+        }
+    }
+    for (int k = 0; k < 4; ++k) out[k] = (float)((double)(float)(uint32_t)q[k] / (double)255);
+}
+
+/* lerp(a, b, c, u, v) -- math/detail/math.h:466-475: (a (1 - (u + v)) + c v) + b u */
+static v3 lerp3(v3 a, v3 b, v3 c, float u, float v)
+{
+    v3 s2 = scale(c, v), s3 = scale(b, u), s1 = scale(a, 1.0f - (u + v));
+    return add(add(s1, s2), s3);
+}
+
+/* get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530 */
+static void get_surface(const frame_ctx* f, const vso_hit* h, surf_t* S)
+{
+    const vso_surface* sf = f->surf;
+    S->m = &f->mats[h->geom_id];
+    S->has_tex = 0; S->tex = v3m(1.0f, 1.0f, 1.0f);
+    if (!sf)
+    {
+        S->gn = S->sn = ld3(f->normals + 4 * (size_t)h->prim_id);   /* normals[hr.prim_id], get_normal.h:28-37 */
+        return;
+    }
+    if (sf->normal_binding == 0) S->gn = S->sn = ld3(sf->normals + 4 * (size_t)h->prim_id);
+    else
+    {
+        /* params.prims.begin[i].primitive(hr.primitive_list_index), get_surface.h:313-327; bvh.h:226-229 */
+        const vso_bvh* b = f->b;
+        size_t pi = b->indices ? b->indices[h->prim_list_index] : h->prim_list_index;
+        const vso_triangle* tri = (const vso_triangle*)b->prims + pi;
+        S->gn = normalize(cross(ld3(tri->e1), ld3(tri->e2)));
+        const float* n = sf->normals + 12 * (size_t)h->prim_id;
+        S->sn = normalize(lerp3(ld3(n), ld3(n + 4), ld3(n + 8), h->u, h->v));
+    }
+    if (sf->color_binding || sf->tex_coords)
+    {
+        S->has_tex = 1;
+        v3 color = v3m(1.0f, 1.0f, 1.0f);
+        if (sf->color_binding == 1) color = ld3(sf->colors + 4 * (size_t)h->prim_id);
+        else if (sf->color_binding == 2)
+        {
+            const float* c = sf->colors + 12 * (size_t)h->prim_id;
+            color = lerp3(ld3(c), ld3(c + 4), ld3(c + 8), h->u, h->v);
+        }
+        v3 tc = v3m(1.0f, 1.0f, 1.0f);
+        if (sf->tex_coords && sf->textures && (int)h->geom_id < sf->n_textures)
+        {
+            const vso_texture* tex = &sf->textures[h->geom_id];
+            if (tex->width > 0 && tex->height > 0)
+            {
+                const float* t = sf->tex_coords + 6 * (size_t)h->prim_id;
+                /* lerp of vector<2,float>, get_tex_coord.h:24-40 */
+                float w0 = 1.0f - (h->u + h->v);
+                float s_ = (t[0] * w0 + t[4] * h->v) + t[2] * h->u;
+                float t_ = (t[1] * w0 + t[5] * h->v) + t[3] * h->u;
+                float q[4];
+                vso_tex2d(tex, s_, t_, q);
+                tc = v3m(q[0], q[1], q[2]);
+            }
+        }
+        S->tex = sf->color_binding ? mul(color, tc) : tc;
+    }
+}
 
 /* simple::kernel -- detail/simple.inl:25-75 */
 static void kernel_simple(const frame_ctx* f, v3 o, v3 d, float out[4], vso_counters* c)
@@ -116,15 +263,15 @@ static void kernel_simple(const frame_ctx* f, v3 o, v3 d, float out[4], vso_coun
     closest(f, o, d, &h, c);
     if (!h.hit) { memcpy(out, p->bg, 16); return; }
     v3 pos = add(o, scale(d, h.t));
-    const vso_material* m = &f->mats[h.geom_id];
-    v3 n = ld3(f->normals + 4 * (size_t)h.prim_id);   /* normals[hr.prim_id], get_normal.h:28-37 */
-    v3 shaded = mul(scale(ld3(m->ca), m->ka), rgb_of_rgba(p->ambient));
+    surf_t S;
+    get_surface(f, &h, &S);
+    v3 shaded = mul(ambient_of(S.m), rgb_of_rgba(p->ambient));
     v3 view = neg(d);
-    n = faceforward(n, view, n);
+    v3 n = faceforward(S.sn, view, S.gn);
     for (int i = 0; i < p->n_lights; ++i)
     {
         v3 wi = normalize(sub(ld3(f->lights[i].pos), pos));
-        shaded = add(shaded, shade(m, &f->lights[i], pos, n, view, wi));
+        shaded = add(shaded, shade(&S, &f->lights[i], pos, n, view, wi));
     }
     out[0] = shaded.x; out[1] = shaded.y; out[2] = shaded.z; out[3] = 1.0f;
 }
@@ -144,11 +291,13 @@ static void kernel_whitted(const frame_ctx* f, v3 o, v3 d, float out[4], vso_cou
     while (h.hit && throughput > p->epsilon && depth++ < p->num_bounces)
     {
         v3 pos = add(o, scale(d, h.t));
-        const vso_material* m = &f->mats[h.geom_id];
-        v3 sn = ld3(f->normals + 4 * (size_t)h.prim_id);
-        v3 shaded = mul(scale(ld3(m->ca), m->ka), rgb_of_rgba(p->ambient));
+        surf_t S;
+        get_surface(f, &h, &S);
+        const vso_material* m = S.m;
+        v3 sn = S.sn;
+        v3 shaded = mul(ambient_of(m), rgb_of_rgba(p->ambient));
         v3 view = neg(d);
-        v3 n = faceforward(sn, view, sn);
+        v3 n = faceforward(sn, view, S.gn);
         for (int i = 0; i < p->n_lights; ++i)
         {
             v3 lpos = ld3(f->lights[i].pos);
@@ -156,11 +305,11 @@ static void kernel_whitted(const frame_ctx* f, v3 o, v3 d, float out[4], vso_cou
             v3 so = add(pos, scale(wi, p->epsilon));
             float ld = length(sub(pos, lpos));
             if (!occluded(f, so, wi, ld, c))
-                shaded = add(shaded, shade(m, &f->lights[i], pos, n, view, wi));
+                shaded = add(shaded, shade(&S, &f->lights[i], pos, n, view, wi));
         }
         color = add(color, scale(shaded, throughput));
 
-        float kr = (m->kind == 0) ? 0.1f : 0.0f;
+        float kr = specular_kr(m);
         if (kr > 0.0f)
         {
             v3 dir = reflect(view, sn);
@@ -251,20 +400,47 @@ static v3 blinn_sample(const vso_material* m, v3 n, v3 wo, v3* wi, float* pdf, u
     return blinn_f(m, n, wo, *wi);
 }
 
-/* plastic::sample_impl -- detail/material/plastic.inl:186-229; matte::sample_impl -- matte.inl:147-155 */
-static v3 material_sample(const vso_material* m, v3 n, v3 wo, v3* wi, float* pdf, uint32_t* samp)
+/* fresnel_reflectance(conductor_tag, eta, k, cosi) -- fresnel.h:17-35, per channel */
+static float fresnel_conductor(float eta, float k, float cosi)
 {
-    if (m->kind == 1) return lambert_sample(m, n, wi, pdf, samp);
-    float prob_diff = ((m->cd[0] + m->cd[1] + m->cd[2]) / 3.0f) * m->kd;
-    float prob_spec = ((m->cs[0] + m->cs[1] + m->cs[2]) / 3.0f) * m->ks;
-    if (prob_diff == 0.0f && prob_spec == 0.0f) { prob_diff = 0.5f; prob_spec = 0.5f; }
-    prob_diff = prob_diff / (prob_diff + prob_spec);
-    float u = vso_sampler_next(samp);
-    if (u < prob_diff) return lambert_sample(m, n, wi, pdf, samp);
-    return blinn_sample(m, n, wo, wi, pdf, samp);
+    float ek = eta * eta + k * k;
+    float rs2 = (ek - 2.0f * eta * cosi + cosi * cosi) / (ek + 2.0f * eta * cosi + cosi * cosi);
+    float rp2 = (ek * cosi * cosi - 2.0f * eta * cosi + 1.0f) / (ek * cosi * cosi + 2.0f * eta * cosi + 1.0f);
+    return (rs2 + rp2) / 2.0f;
 }
 
-/* pathtracing::kernel -- detail/pathtracing.inl:29-121 (no emissive materials in the subset) */
+/* surface::sample -> material.sample(): plastic::sample_impl -- detail/material/plastic.inl:186-229
+ * (x tex_color :48-63); matte -- matte.inl:147-155 (:50-65); emissive -- emissive.inl:29-44
+ * (pdf 1, refl_dir untouched); mirror -- mirror.inl:29-41 -> specular_reflection::sample_f, brdf.h:187-210 */
+static v3 material_sample(const surf_t* s, v3 n, v3 wo, v3* wi, float* pdf, uint32_t* samp)
+{
+    const vso_material* m = s->m;
+    v3 r;
+    if (m->kind == 2) { *pdf = 1.0f; return shade(s, NULL, v3m(0, 0, 0), n, wo, n); }
+    if (m->kind == 3)
+    {
+        *wi = reflect(wo, n);
+        *pdf = 1.0f;
+        float cosi = fabsf(dot(n, wo)), d = fabsf(dot(n, *wi));
+        return v3m(fresnel_conductor(m->ca[0], m->cd[0], cosi) * (m->cs[0] * m->ks) / d,
+                   fresnel_conductor(m->ca[1], m->cd[1], cosi) * (m->cs[1] * m->ks) / d,
+                   fresnel_conductor(m->ca[2], m->cd[2], cosi) * (m->cs[2] * m->ks) / d);
+    }
+    if (m->kind == 1) r = lambert_sample(m, n, wi, pdf, samp);
+    else
+    {
+        float prob_diff = ((m->cd[0] + m->cd[1] + m->cd[2]) / 3.0f) * m->kd;
+        float prob_spec = ((m->cs[0] + m->cs[1] + m->cs[2]) / 3.0f) * m->ks;
+        if (prob_diff == 0.0f && prob_spec == 0.0f) { prob_diff = 0.5f; prob_spec = 0.5f; }
+        prob_diff = prob_diff / (prob_diff + prob_spec);
+        float u = vso_sampler_next(samp);
+        if (u < prob_diff) r = lambert_sample(m, n, wi, pdf, samp);
+        else               r = blinn_sample(m, n, wo, wi, pdf, samp);
+    }
+    return s->has_tex ? mul(s->tex, r) : r;
+}
+
+/* pathtracing::kernel -- detail/pathtracing.inl:29-121 */
 static void kernel_pathtracing(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, float out[4], vso_counters* c)
 {
     const vso_frame_params* p = f->p;
@@ -280,16 +456,17 @@ static void kernel_pathtracing(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, f
         if (bounce == 0) result_hit = h.hit;
 
         v3 view = neg(d);
-        const vso_material* m = &f->mats[h.geom_id];
-        v3 sn = ld3(f->normals + 4 * (size_t)h.prim_id);
-        v3 n = faceforward(sn, view, sn);
-        v3 refl; float pdf = 0.0f;
-        v3 src = material_sample(m, n, view, &refl, &pdf, samp);
+        surf_t S;
+        get_surface(f, &h, &S);
+        v3 n = faceforward(S.sn, view, S.gn);
+        v3 refl = v3m(0.0f, 0.0f, 0.0f); float pdf = 0.0f;
+        v3 src = material_sample(&S, n, view, &refl, &pdf, samp);
         int zero_pdf = pdf <= 0.0f;
-        src = scale(src, dot(n, refl) / pdf);
+        int emissive = S.m->kind == 2;                       /* has_emissive_material(surf), detail/surface.inl:14-38 */
+        if (!emissive) src = scale(src, dot(n, refl) / pdf);
         if (!zero_pdf) dst = mul(dst, src);
         else           dst = v3m(0.0f, 0.0f, 0.0f);
-        active = active && !zero_pdf;
+        active = active && !emissive && !zero_pdf;
         if (!active) break;
         v3 pos = add(o, scale(d, h.t));
         o = add(pos, scale(refl, p->epsilon));
@@ -500,6 +677,17 @@ void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals
     frame_ctx f;
     memset(&f, 0, sizeof(f));
     f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights; f.rgba = rgba;
+    vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
+    frame_run(&f, counters, nthreads);
+}
+
+void vso_frame_surface(const vso_frame_params* p, const vso_bvh* b, const vso_surface* surf,
+                       const vso_material* mats, const vso_point_light* lights, float* rgba,
+                       vso_counters* counters, int nthreads)
+{
+    frame_ctx f;
+    memset(&f, 0, sizeof(f));
+    f.p = p; f.b = b; f.surf = surf; f.normals = surf ? surf->normals : NULL; f.mats = mats; f.lights = lights; f.rgba = rgba;
     vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
     frame_run(&f, counters, nthreads);
 }

@@ -159,6 +159,73 @@ int main(int argc, char** argv)
         dev_depth_rt.download_depth(zback.data());
         if (std::memcmp(zback.data(), depth_rt.depth(), zback.size() * sizeof(float)) != 0) { std::cerr << "gpu depth != host depth\n"; return 2; }
 
+        // --- kernel_params with a surface description (kernels.h:395-509): normals per vertex, colours per
+        //     vertex, tex coords + one texture_ref per geom_id, generic_material list; Whitted, host target.
+        //     The arrays are dumped so that the test can hand the same ones to the oracle. ---
+        {
+            using material_type = generic_material<emissive<float>, matte<float>, mirror<float>, plastic<float>>;
+            std::vector<triangle_type> st = tris;
+            for (size_t i = 0; i < st.size(); ++i) st[i].geom_id = unsigned((i / 3) % 4);
+            auto sbvh = build<index_bvh<triangle_type>>(st.data(), st.size());
+            b200_index_bvh<triangle_type> d_sbvh(sbvh);
+            b200_bvh_ref sprims[1] = { d_sbvh.ref() };
+
+            std::vector<vec3> vn(st.size() * 3), vc(st.size() * 3);
+            std::vector<vec2> tc(st.size() * 3);
+            for (size_t i = 0; i < st.size(); ++i)
+            {
+                vec3 v[3] = { st[i].v1, st[i].v1 + st[i].e1, st[i].v1 + st[i].e2 };
+                for (int k = 0; k < 3; ++k)
+                {
+                    vn[i * 3 + k] = normalize(v[k]);                                  // the sphere's smooth normal
+                    vc[i * 3 + k] = vec3(0.5f + 0.5f * v[k].x, 0.5f + 0.5f * v[k].y, 0.5f + 0.5f * v[k].z);
+                    tc[i * 3 + k].x = 1.7f * v[k].x + 0.4f * v[k].y; tc[i * 3 + k].y = 1.3f * v[k].z - 0.2f;
+                }
+            }
+            int tw = 24, th = 16;
+            std::vector<unorm8x4> texels(size_t(tw) * th);
+            for (int y = 0; y < th; ++y)
+                for (int x = 0; x < tw; ++x)
+                {
+                    unsigned char c = (unsigned char)(((x / 3 + y / 3) & 1) ? 230 : 70);
+                    texels[size_t(y) * tw + x] = unorm8x4{ c, (unsigned char)(c / 2 + x * 4), (unsigned char)(255 - c + y), 255 };
+                }
+            std::vector<texture_ref2d> textures(4);             // geom_id 2 and 3 stay without a texture
+            textures[0] = texture_ref2d(tw, th); textures[0].reset(texels.data());
+            textures[0].set_filter_mode(Linear); textures[0].set_address_mode(0, Wrap); textures[0].set_address_mode(1, Mirror);
+            textures[1] = texture_ref2d(tw, th); textures[1].reset(texels.data());
+            textures[1].set_filter_mode(Nearest); textures[1].set_address_mode(Clamp);
+
+            plastic<float> pl; pl.set_ca(vec3(0.2f)); pl.set_ka(1.0f); pl.set_cd(vec3(0.8f)); pl.set_kd(1.0f); pl.set_cs(vec3(0.1f)); pl.set_ks(1.0f); pl.set_specular_exp(32.0f);
+            matte<float> ma; ma.set_ca(vec3(0.2f)); ma.set_ka(1.0f); ma.set_cd(vec3(0.7f, 0.5f, 0.3f)); ma.set_kd(1.0f);
+            mirror<float> mi; mi.set_cr(vec3(0.9f, 0.85f, 0.8f)); mi.set_kr(0.8f); mi.set_ior(vec3(0.2f, 0.9f, 1.1f)); mi.set_absorption(vec3(3.9f, 2.4f, 2.2f));
+            emissive<float> em; em.set_ce(vec3(1.0f, 0.9f, 0.7f)); em.set_ls(2.0f);
+            std::vector<material_type> gmats = { material_type(pl), material_type(ma), material_type(mi), material_type(em) };
+            std::vector<vsb_material> flat;
+            for (auto const& m : gmats) flat.push_back(m.flatten());
+
+            auto skp = make_kernel_params(normals_per_vertex_binding{}, colors_per_vertex_binding{}, sprims, sprims + 1, vn.data(),
+                                          tc.data(), gmats, vc.data(), textures, lights.data(), lights.data() + lights.size(),
+                                          4, 1e-3f, vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(0.3f, 0.3f, 0.3f, 1.0f));
+            whitted::kernel<decltype(skp)> sk{ skp };
+            b200_sched<ray> ssched;
+            ssched.set_reference_order(true);
+            ssched.frame(sk, sparams);
+            dump(out + "/surface_whitted.bin", host_rt.color(), size_t(w) * h);
+            // attached once to the device tree, frames pass nullptr: same pixels
+            d_sbvh.set_surface(skp.surface);
+            auto skp2 = skp; skp2.surface.normals = nullptr;
+            whitted::kernel<decltype(skp2)> sk2{ skp2 };
+            std::vector<vec4> first(host_rt.color(), host_rt.color() + size_t(w) * h);
+            ssched.frame(sk2, sparams);
+            if (std::memcmp(first.data(), host_rt.color(), first.size() * sizeof(vec4)) != 0) { std::cerr << "attached surface != per-frame surface\n"; return 2; }
+            dump(out + "/surface_normals.bin", vn.data(), vn.size());
+            dump(out + "/surface_colors.bin", vc.data(), vc.size());
+            dump(out + "/surface_tex_coords.bin", tc.data(), tc.size());
+            dump(out + "/surface_texels.bin", texels.data(), texels.size());
+            dump(out + "/surface_materials.bin", flat.data(), flat.size());
+        }
+
         std::printf("dropin_example ok: %zu triangles, %zu nodes, %zu rays\n", tris.size(), bvh.num_nodes(), rays.size());
         return 0;
     }

@@ -55,6 +55,7 @@ def main():
     np.savez_compressed(os.path.join(HERE, "golden_frames.npz"), **frames)
     print("wrote golden_queries.npz, golden_frames.npz")
     multi_hit_vectors()
+    surface_vectors()
 
 
 def multi_hit_vectors():
@@ -70,8 +71,26 @@ def multi_hit_vectors():
     print("wrote golden_multi_hit.npz")
 
 
+def surface_vectors():
+    """Frames of the reference kernels with kernel_params that carry a surface description
+    (normal / colour bindings, tex coords + textures, generic_material list) and tex2D samples,
+    through the unmodified headers: make_kernel_params / get_surface / tex2D."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import surface_cases as SC
+    out = {}
+    for name in SC.CASES:
+        sc, fp, sd, mats, light = SC.case(name)
+        out[name] = O.ref_frame_surface(sc, fp, sd, mats, light)
+    for key, tex, st in SC.tex_samples():
+        out["tex_" + key] = np.stack([O.ref_tex2d(tex, float(s), float(t)) for s, t in st])
+    np.savez_compressed(os.path.join(HERE, "golden_surface.npz"), **out)
+    print("wrote golden_surface.npz")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "multi_hit":
         multi_hit_vectors()          # adds golden_multi_hit.npz without touching the older fixtures
+    elif len(sys.argv) > 1 and sys.argv[1] == "surface":
+        surface_vectors()
     else:
         main()

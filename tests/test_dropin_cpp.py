@@ -70,3 +70,18 @@ def test_dropin_program_matches_oracle(gpu):
         mz = np.fromfile(os.path.join(d, "frame_matrix_depth.bin"), dtype=np.float32).reshape(120, 160)
         assert float((np.abs(mc - want_c).max(axis=2) > 1 / 255).mean()) <= 2e-4
         assert float(np.abs(mz - want_z).max()) <= 1e-5
+        # kernel_params with normals / colours per vertex, tex coords + textures and a generic_material list:
+        # the program's own arrays go to the oracle
+        from visionaray_b200._native import MATERIAL_DTYPE
+        ss = S.make_scene("cfg1_sphere", (50 / 224) ** 2)
+        ss.prims.view(np.uint32)[:, 0] = (np.arange(ss.n_prims) // 3) % 4
+        texels = np.fromfile(os.path.join(d, "surface_texels.bin"), dtype=np.uint8).reshape(16, 24, 4)
+        sd = S.SurfaceData(1, np.fromfile(os.path.join(d, "surface_normals.bin"), dtype=np.float32).reshape(-1, 4), 2,
+                           np.fromfile(os.path.join(d, "surface_colors.bin"), dtype=np.float32).reshape(-1, 4),
+                           np.fromfile(os.path.join(d, "surface_tex_coords.bin"), dtype=np.float32).reshape(-1, 2),
+                           [S.Texture(texels, 1, (0, 1)), S.Texture(texels, 0, (2, 2)), None, None])
+        mats = np.fromfile(os.path.join(d, "surface_materials.bin"), dtype=MATERIAL_DTYPE)
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4, n_materials=4, ambient=(0.3, 0.3, 0.3, 1.0))
+        want_s = O.oracle_frame_surface(ss, fp, sd, mats, S.point_light(eye))
+        got_s = np.fromfile(os.path.join(d, "surface_whitted.bin"), dtype=np.float32).reshape(120, 160, 4)
+        assert float((np.abs(got_s - want_s).max(axis=2) > 1 / 255).mean()) == 0.0      # reference-order walk

@@ -63,13 +63,28 @@ class FrameDesc(C.Structure):
         ("ray_count", C.c_void_p),
         ("params_mem", C.c_int32), ("tile_target", C.c_int32),
         ("camera_kind", C.c_int32), ("view_matrix", C.c_float * 16), ("proj_matrix", C.c_float * 16),
+        ("generic_materials", C.c_int32),
     ]
+
+
+class Texture(C.Structure):
+    """vsb_texture (include/vsnray_b200.h)."""
+
+    _fields_ = [("data", C.c_void_p), ("width", C.c_int32), ("height", C.c_int32), ("filter", C.c_int32),
+                ("address", C.c_int32 * 2)]
+
+
+class SurfaceDesc(C.Structure):
+    """vsb_surface_desc (include/vsnray_b200.h)."""
+
+    _fields_ = [("normal_binding", C.c_int32), ("color_binding", C.c_int32), ("normals", C.c_void_p),
+                ("colors", C.c_void_p), ("tex_coords", C.c_void_p), ("textures", C.c_void_p), ("n_textures", C.c_int32)]
 
 
 # every symbol include/vsnray_b200.h declares (tests check the library exports them all)
 ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
-    "vsb_scene_create", "vsb_scene_build", "vsb_scene_download_bvh", "vsb_last_build_ms", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_stats", "vsb_scene_download_wide",
+    "vsb_scene_create", "vsb_scene_build", "vsb_scene_download_bvh", "vsb_last_build_ms", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_set_surface", "vsb_scene_stats", "vsb_scene_download_wide",
     "vsb_closest_hit", "vsb_any_hit", "vsb_multi_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_ipc_export", "vsb_ipc_open", "vsb_ipc_close", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
@@ -115,6 +130,7 @@ def cuda_lib() -> C.CDLL:
         lib.vsb_scene_download_bvh.argtypes = [vp, vp, sz, vp, sz]
         lib.vsb_last_build_ms.argtypes = [C.POINTER(C.c_float), C.POINTER(C.c_int)]
         lib.vsb_scene_set_normals.argtypes = [vp, vp, sz, C.c_int]
+        lib.vsb_scene_set_surface.argtypes = [vp, C.POINTER(SurfaceDesc), C.c_int]
         lib.vsb_scene_stats.argtypes = [vp, C.POINTER(C.c_uint64), C.c_int]
         lib.vsb_scene_download_wide.argtypes = [vp, vp, sz, vp, sz]
         for f in (lib.vsb_closest_hit, lib.vsb_any_hit):

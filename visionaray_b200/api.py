@@ -255,9 +255,35 @@ class DeviceBuffer:
             self.ptr = 0
 
 
+def set_surface(scene: "Scene", surface) -> None:
+    """vsb_scene_set_surface: attach a scenes.SurfaceData (host arrays) to the device scene -- the
+    normals / colours / tex coords / textures of make_kernel_params (kernels.h:395-509); None detaches."""
+    if surface is None:
+        _check(N.cuda_lib().vsb_scene_set_surface(scene.handle, None, MEM_HOST), "vsb_scene_set_surface")
+        return
+    d = N.SurfaceDesc()
+    d.normal_binding, d.color_binding = surface.normal_binding, surface.color_binding
+    d.normals = surface.normals.ctypes.data
+    d.colors = surface.colors.ctypes.data if surface.colors is not None else None
+    d.tex_coords = surface.tex_coords.ctypes.data if surface.tex_coords is not None else None
+    texs = None
+    if surface.textures:
+        texs = (N.Texture * len(surface.textures))()
+        for i, t in enumerate(surface.textures):
+            if t is None:
+                continue
+            texs[i].data = t.data.ctypes.data
+            texs[i].height, texs[i].width = t.data.shape[0], t.data.shape[1]
+            texs[i].filter = t.filter
+            texs[i].address[0], texs[i].address[1] = t.address
+        d.textures = C.cast(texs, C.c_void_p)
+        d.n_textures = len(surface.textures)
+    _check(N.cuda_lib().vsb_scene_set_surface(scene.handle, C.byref(d), MEM_HOST), "vsb_scene_set_surface")
+
+
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
           tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False, view_matrix=None, proj_matrix=None,
-          depth=None):
+          depth=None, generic_materials=False):
     """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
     the call, returns with pixels in place); torch CUDA tensor -> device render target
     (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
@@ -299,6 +325,7 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.traverse = traverse
     d.tile_rank, d.tile_nranks = tile_rank, tile_nranks
     d.tile_target = 1 if tiles_in_place else 0
+    d.generic_materials = 1 if generic_materials else 0
     d.ray_count = p(ray_count)
     _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), stream), "vsb_frame")
     return color

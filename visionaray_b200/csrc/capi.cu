@@ -422,8 +422,13 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     unsigned long long* d_ray_count = nullptr;
     if (d->mem != VSB_MEM_HOST && d->mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     if (d->params_mem != VSB_MEM_HOST && d->params_mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
-    if (!d->normals && !scenes[0]->d_normals) return VSB_ERR_BAD_ARG;
+    fl.ctx.surf = scenes[0]->surf;
+    if (fl.ctx.surf.enabled && (n_scenes != 1 || p.kernel == VSB_KERNEL_AO)) return VSB_ERR_UNSUPPORTED;
+    if (!d->normals && !scenes[0]->d_normals && !fl.ctx.surf.enabled) return VSB_ERR_BAD_ARG;
     fl.ctx.normals = d->normals ? reinterpret_cast<const float4*>(d->normals) : scenes[0]->d_normals;
+    bool generic_materials = d->generic_materials != 0;
+    if (d->params_mem == VSB_MEM_HOST && d->materials)
+        for (int i = 0; i < p.n_materials; ++i) generic_materials |= d->materials[i].kind >= VSB_MAT_EMISSIVE;
     if (d->params_mem == VSB_MEM_HOST)
     {
         // small per-frame parameter block: materials | lights (what cuda_sched copies as kernel
@@ -587,7 +592,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, bs)));                  \
     } while (0)
         // extended instantiation: SSAA samplers, matrix camera, depth target (see shade.cuh)
-        switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX) ? 1 : 0))
+        // ... and kernel_params with a surface description or a generic material list
+        switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX ||
+                                 fl.ctx.surf.enabled || generic_materials) ? 1 : 0))
         {
         case 0: VSB_LAUNCH_FRAME(0, false); break;
         case 1: VSB_LAUNCH_FRAME(0, true); break;

@@ -62,6 +62,8 @@ struct vsb_scene
     vsb::Node80* d_wide = nullptr;
     void*    d_wide_prims = nullptr;
     float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
+    vsb::SurfCtx surf = {};              // optional, vsb_scene_set_surface(); device copies listed in surf_allocs
+    std::vector<void*> surf_allocs;
     uint32_t n_wide = 0, n_wide_prims = 0;
     int      levels = 0, depth2 = 0;
     float    lo[3] = { 0, 0, 0 }, hi[3] = { 0, 0, 0 };   // root bounds
@@ -219,6 +221,7 @@ extern "C" int vsb_scene_destroy(vsb_scene* s)
     if (s->d_wide) cudaFree(s->d_wide);
     if (s->d_wide_prims) cudaFree(s->d_wide_prims);
     if (s->d_normals) cudaFree(s->d_normals);
+    for (void* q : s->surf_allocs) cudaFree(q);
     delete s;
     return VSB_OK;
 }
@@ -368,6 +371,78 @@ extern "C" int vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_
     VSB_CUDA(cudaMemcpyAsync(s->d_normals, normals16, n * 16,
                              mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, g.stream));
     VSB_CUDA(cudaStreamSynchronize(g.stream));
+    return VSB_OK;
+}
+
+extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc, int mem)
+{
+    int rc = require_init(); if (rc) return rc;
+    if (!s) return VSB_ERR_BAD_ARG;
+    VSB_CUDA(cudaStreamSynchronize(g.stream));      // frames in flight may still read the old copies
+    for (void* q : s->surf_allocs) cudaFree(q);
+    s->surf_allocs.clear();
+    s->surf = vsb::SurfCtx{};
+    if (!desc) return VSB_OK;
+    if (s->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
+    if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    if (!desc->normals || desc->normal_binding < 0 || desc->normal_binding > 1 || desc->color_binding < 0 || desc->color_binding > 2)
+        return VSB_ERR_BAD_ARG;
+    if (desc->color_binding && !desc->colors) return VSB_ERR_BAD_ARG;
+    if (desc->n_textures < 0 || (desc->n_textures > 0 && !desc->textures)) return VSB_ERR_BAD_ARG;
+    const cudaMemcpyKind kind = mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
+    int err = VSB_OK;
+    auto copy = [&](const void* src, size_t bytes) -> void*
+    {
+        void* q = nullptr;
+        if (err || bytes == 0) return q;
+        cudaError_t e = cudaMalloc(&q, bytes);
+        if (e == cudaSuccess) { s->surf_allocs.push_back(q); e = cudaMemcpyAsync(q, src, bytes, kind, g.stream); }
+        if (e != cudaSuccess) err = (int)e;
+        return q;
+    };
+    vsb::SurfCtx c{};
+    c.normal_binding = desc->normal_binding; c.color_binding = desc->color_binding;
+    const size_t n = s->n_prims;
+    c.normals = (const float4*)copy(desc->normals, (desc->normal_binding ? 3 * n : n) * 16);
+    if (desc->color_binding) c.colors = (const float4*)copy(desc->colors, (desc->color_binding == 2 ? 3 * n : n) * 16);
+    if (desc->tex_coords)
+    {
+        c.tex_coords = (const float2*)copy(desc->tex_coords, 3 * n * 8);
+        // texture descriptors are host structures either way; their texels live where `mem` says
+        std::vector<vsb::DevTexture> tab((size_t)(desc->n_textures > 0 ? desc->n_textures : 1));
+        std::memset(tab.data(), 0, tab.size() * sizeof(vsb::DevTexture));
+        for (int i = 0; i < desc->n_textures && !err; ++i)
+        {
+            const vsb_texture& t = desc->textures[i];
+            if (t.width <= 0 || t.height <= 0 || !t.data) continue;
+            if (t.filter < VSB_TEX_NEAREST || t.filter > VSB_TEX_LINEAR || t.address[0] < 0 || t.address[0] > VSB_TEX_CLAMP ||
+                t.address[1] < 0 || t.address[1] > VSB_TEX_CLAMP) { err = VSB_ERR_UNSUPPORTED; break; }
+            tab[i].data = (const uchar4*)copy(t.data, (size_t)t.width * (size_t)t.height * 4);
+            tab[i].width = t.width; tab[i].height = t.height; tab[i].filter = t.filter;
+            tab[i].addr_s = t.address[0]; tab[i].addr_t = t.address[1];
+        }
+        c.n_textures = desc->n_textures;
+        if (!err)
+        {
+            void* q = nullptr;
+            cudaError_t e = cudaMalloc(&q, tab.size() * sizeof(vsb::DevTexture));
+            if (e == cudaSuccess) { s->surf_allocs.push_back(q); e = cudaMemcpyAsync(q, tab.data(), tab.size() * sizeof(vsb::DevTexture), cudaMemcpyHostToDevice, g.stream); }
+            if (e != cudaSuccess) err = (int)e;
+            c.textures = (const vsb::DevTexture*)q;
+            if (!err) err = (int)cudaStreamSynchronize(g.stream);    // tab is a local
+        }
+    }
+    if (!err) err = (int)cudaStreamSynchronize(g.stream);
+    if (err)
+    {
+        for (void* q : s->surf_allocs) cudaFree(q);
+        s->surf_allocs.clear();
+        return err;
+    }
+    c.ref_prims = reinterpret_cast<const float4*>(s->d_prims);
+    c.indices = s->d_indices;
+    c.enabled = 1;
+    s->surf = c;
     return VSB_OK;
 }
 

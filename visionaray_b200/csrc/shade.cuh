@@ -55,6 +55,22 @@ struct FrameParams   // == vsb_frame_params
     int32_t  n_lights, n_materials;
 };
 
+// texture_ref<vector<4, unorm<8>>, 2> on the device (texture/detail/texture2d.h): RGBA8, row-major
+struct DevTexture { const uchar4* data; int32_t width, height, filter, addr_s, addr_t, pad; };
+
+// What get_surface() reads besides the hit record (kernels.h:194-319, get_surface.h:330-530);
+// attached to the scene by vsb_scene_set_surface().  enabled == 0: per-face normals only.
+struct SurfCtx
+{
+    int32_t enabled, normal_binding, color_binding, n_textures;
+    const float4*     normals;      // per face: [prim_id]; per vertex: [3 prim_id + k]
+    const float4*     colors;       // per face / per vertex like the normals; null without colours
+    const float2*     tex_coords;   // [3 prim_id + k]; null without textures
+    const DevTexture* textures;     // by geom_id
+    const float4*     ref_prims;    // the scene's basic_triangle records (4 x 16 B: ids, v1, e1, e2)
+    const uint32_t*   indices;      // index_bvh indirection (bvh.h:226-229); null for a plain bvh
+};
+
 struct FrameCtx
 {
     FrameParams p;
@@ -65,6 +81,7 @@ struct FrameCtx
     // sched_params built from matrices (camera_kind == 1): column-major matrix<4,4,float>
     int   camera_kind;
     float view[16], inv_view[16], proj[16], inv_proj[16];
+    SurfCtx surf;
 };
 
 VSB_HD V3 ld3(const float* p) { return v3(p[0], p[1], p[2]); }
@@ -209,6 +226,182 @@ VSB_HD V3 material_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, ui
     return blinn_sample(m, n, wo, wi, pdf, samp);
 }
 
+// ---- get_surface() with bindings, colours and textures; generic_material -------------------------
+//
+// Used by the EXT instantiation of the frame programs (kernel_params that carry more than
+// per-face normals and a plastic / matte list).  Normals and everything else that defines a ray
+// keep the reference's operation order with single roundings; so does the texture filter, because
+// its result is TRUNCATED to an integer texel value before normalisation (texture/detail/
+// sampler2d.h:81-113), which would turn an ulp into 1/255.
+
+struct Surface { V3 gn, sn, tex; bool has_tex; };
+
+// lerp(a, b, c, u, v) = (a (1 - (u + v)) + c v) + b u -- math/detail/math.h:466-475
+VSB_HD V3 vlerp3(V3 a, V3 b, V3 c, float u, float v)
+{
+    return vadd(vadd(vscale(a, rn_sub(1.0f, rn_add(u, v))), vscale(c, v)), vscale(b, u));
+}
+VSB_HD float lerp1(float a, float b, float x) { return rn_add(rn_mul(rn_sub(1.0f, x), a), rn_mul(x, b)); }   // :459-464
+
+// map_tex_coord -- texture/detail/filter/common.h:24-48 (0 Wrap, 1 Mirror, 2 Clamp)
+VSB_HD float map_tex_coord(float coord, int texsize, int mode)
+{
+    if (mode == 0) return rn_sub(coord, floorf(coord));
+    if (mode == 1)
+    {
+        const float fl = floorf(coord);
+        if ((((int)fl) & 1) == 1) return rn_sub(rn_div((float)(texsize - 1), (float)texsize), rn_sub(coord, fl));
+        return rn_sub(coord, fl);
+    }
+    const float hi = rn_sub(1.0f, rn_div(1.0f, (float)texsize));
+    return coord < 0.0f ? 0.0f : (coord > hi ? hi : coord);
+}
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ uchar4 texel(const DevTexture& t, int x, int y)
+{
+    // the reference reads out of bounds when a wrapped coordinate rounds up to 1 (coord - floor(coord)
+    // == 1 for tiny negative coord); the index is clamped here instead
+    x = x < 0 ? 0 : (x >= t.width ? t.width - 1 : x);
+    y = y < 0 ? 0 : (y >= t.height ? t.height - 1 : y);
+    return __ldg(t.data + (size_t)y * (size_t)t.width + (size_t)x);
+}
+
+// tex2D(texture_ref<vector<4, unorm<8>>, 2>, coord).xyz -- texture/detail/sampler2d.h:81-151,
+// filter/nearest.h:45-66, filter/linear.h:61-98, math/detail/unorm.inl:26-31
+__device__ inline V3 tex2d_rgb(const DevTexture& t, float s, float tt)
+{
+    const float fw = (float)t.width, fh = (float)t.height;
+    int q[3];
+    if (t.filter == 0)
+    {
+        const float cs = map_tex_coord(s, t.width, t.addr_s), ct = map_tex_coord(tt, t.height, t.addr_t);
+        const uchar4 e = texel(t, __float2int_rz(rn_mul(cs, fw)), __float2int_rz(rn_mul(ct, fh)));
+        q[0] = e.x; q[1] = e.y; q[2] = e.z;
+    }
+    else
+    {
+        const float hs = rn_div(0.5f, fw), ht = rn_div(0.5f, fh);
+        const float s1 = map_tex_coord(rn_sub(s, hs), t.width, t.addr_s), t1 = map_tex_coord(rn_sub(tt, ht), t.height, t.addr_t);
+        const float s2 = map_tex_coord(rn_add(s, hs), t.width, t.addr_s), t2 = map_tex_coord(rn_add(tt, ht), t.height, t.addr_t);
+        const int lx = __float2int_rz(rn_mul(s1, fw)), ly = __float2int_rz(rn_mul(t1, fh));
+        const int hx = __float2int_rz(rn_mul(s2, fw)), hy = __float2int_rz(rn_mul(t2, fh));
+        const uchar4 e00 = texel(t, lx, ly), e10 = texel(t, hx, ly), e01 = texel(t, lx, hy), e11 = texel(t, hx, hy);
+        const float u = rn_sub(rn_mul(s1, fw), (float)lx), v = rn_sub(rn_mul(t1, fh), (float)ly);
+        q[0] = __float2int_rz(lerp1(lerp1((float)e00.x, (float)e10.x, u), lerp1((float)e01.x, (float)e11.x, u), v));
+        q[1] = __float2int_rz(lerp1(lerp1((float)e00.y, (float)e10.y, u), lerp1((float)e01.y, (float)e11.y, u), v));
+        q[2] = __float2int_rz(lerp1(lerp1((float)e00.z, (float)e10.z, u), lerp1((float)e01.z, (float)e11.z, u), v));
+    }
+    return v3(__double2float_rn((double)q[0] / 255.0), __double2float_rn((double)q[1] / 255.0), __double2float_rn((double)q[2] / 255.0));
+}
+
+// get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530
+__device__ inline Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v)
+{
+    const SurfCtx& sf = f.surf;
+    Surface S;
+    S.has_tex = false; S.tex = v3(1.0f, 1.0f, 1.0f);
+    if (!sf.enabled)
+    {
+        const float4 nn = __ldg(f.normals + prim_id);
+        S.gn = S.sn = v3(nn.x, nn.y, nn.z);
+        return S;
+    }
+    if (sf.normal_binding == 0)
+    {
+        const float4 nn = __ldg(sf.normals + prim_id);
+        S.gn = S.sn = v3(nn.x, nn.y, nn.z);
+    }
+    else
+    {
+        // geometric normal of primitive(primitive_list_index) (get_surface.h:313-327, get_normal.h:96-101),
+        // shading normal interpolated (get_shading_normal.h:60-76)
+        const size_t pi = sf.indices ? __ldg(sf.indices + list_index) : list_index;
+        const float4 e1 = __ldg(sf.ref_prims + pi * 4 + 2), e2 = __ldg(sf.ref_prims + pi * 4 + 3);
+        S.gn = vnormalize(vcross(v3(e1.x, e1.y, e1.z), v3(e2.x, e2.y, e2.z)));
+        const float4* n = sf.normals + (size_t)prim_id * 3;
+        const float4 a = __ldg(n), b = __ldg(n + 1), c = __ldg(n + 2);
+        S.sn = vnormalize(vlerp3(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), u, v));
+    }
+    if (sf.color_binding || sf.tex_coords)
+    {
+        S.has_tex = true;
+        V3 tc = v3(1.0f, 1.0f, 1.0f);
+        if (sf.tex_coords && (int)geom_id < sf.n_textures)
+        {
+            const DevTexture t = sf.textures[geom_id];
+            if (t.width > 0 && t.height > 0)
+            {
+                const float2* q = sf.tex_coords + (size_t)prim_id * 3;
+                const float2 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+                const float w0 = rn_sub(1.0f, rn_add(u, v));
+                tc = tex2d_rgb(t, rn_add(rn_add(rn_mul(a.x, w0), rn_mul(c.x, v)), rn_mul(b.x, u)),
+                                  rn_add(rn_add(rn_mul(a.y, w0), rn_mul(c.y, v)), rn_mul(b.y, u)));
+            }
+        }
+        if (sf.color_binding == 1)
+        {
+            const float4 c = __ldg(sf.colors + prim_id);
+            tc = v3(c.x * tc.x, c.y * tc.y, c.z * tc.z);
+        }
+        else if (sf.color_binding == 2)
+        {
+            const float4* q = sf.colors + (size_t)prim_id * 3;
+            const float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+            const V3 col = vlerp3(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), u, v);
+            tc = v3(col.x * tc.x, col.y * tc.y, col.z * tc.z);
+        }
+        S.tex = tc;
+    }
+    return S;
+}
+#endif // __CUDACC__
+
+// generic_material<emissive, matte, mirror, plastic>::shade -- detail/generic_material.inl:36-43 ->
+// plastic.inl:18-37,176-183; matte.inl:18-39,136-142; emissive.inl:22-27,76-90; mirror.inl:22-27
+VSB_HD V3 shade_light_ext(const Material& m, const Surface& S, const PointLight& l, V3 pos, V3 n, V3 wo, V3 wi)
+{
+    if (m.kind == 2) return v3(S.tex.x * m.cd[0] * m.kd, S.tex.y * m.cd[1] * m.kd, S.tex.z * m.cd[2] * m.kd);   // tex == 1 without colours
+    if (m.kind == 3) return v3(0.0f, 0.0f, 0.0f);
+    const float ndotl = max0(vdot(n, wi));
+    V3 f = lambert_f(m);
+    f = v3(f.x * S.tex.x, f.y * S.tex.y, f.z * S.tex.z);
+    if (m.kind == 0) { const V3 s = blinn_f(m, n, wo, wi); f = v3(f.x + s.x, f.y + s.y, f.z + s.z); }
+    const V3 li = light_intensity(l, pos);
+    return v3(f.x * VSB_PI * li.x * ndotl, f.y * VSB_PI * li.y * ndotl, f.z * VSB_PI * li.z * ndotl);
+}
+
+// specular_bounce() -- detail/whitted.inl:66-122: matte 0, mirror kr, everything else 0.1
+VSB_HD float specular_kr(const Material& m) { return m.kind == 1 ? 0.0f : (m.kind == 3 ? m.ks : 0.1f); }
+
+// fresnel_reflectance(conductor_tag, eta, k, cosi) -- fresnel.h:17-35
+VSB_HD float fresnel_conductor(float eta, float k, float cosi)
+{
+    const float ek = eta * eta + k * k;
+    const float rs2 = (ek - 2.0f * eta * cosi + cosi * cosi) / (ek + 2.0f * eta * cosi + cosi * cosi);
+    const float rp2 = (ek * cosi * cosi - 2.0f * eta * cosi + 1.0f) / (ek * cosi * cosi + 2.0f * eta * cosi + 1.0f);
+    return (rs2 + rp2) / 2.0f;
+}
+
+// surface::sample -> generic_material::sample -- surface.h:50-92, detail/generic_material.inl:45-57:
+// emissive pdf 1, direction untouched (emissive.inl:29-44); mirror = specular_reflection::sample_f
+// (brdf.h:187-210); plastic / matte as before, times tex_color when the params carry one
+VSB_HD V3 material_sample_ext(const Material& m, const Surface& S, V3 n, V3 wo, V3& wi, float& pdf, uint32_t& samp)
+{
+    if (m.kind == 2) { pdf = 1.0f; return v3(S.tex.x * m.cd[0] * m.kd, S.tex.y * m.cd[1] * m.kd, S.tex.z * m.cd[2] * m.kd); }
+    if (m.kind == 3)
+    {
+        wi = vreflect(wo, n);
+        pdf = 1.0f;
+        const float cosi = fabsf(vdot(n, wo)), d = fabsf(vdot(n, wi));
+        return v3(fresnel_conductor(m.ca[0], m.cd[0], cosi) * (m.cs[0] * m.ks) / d,
+                  fresnel_conductor(m.ca[1], m.cd[1], cosi) * (m.cs[1] * m.ks) / d,
+                  fresnel_conductor(m.ca[2], m.cd[2], cosi) * (m.cs[2] * m.ks) / d);
+    }
+    const V3 r = material_sample(m, n, wo, wi, pdf, samp);
+    return v3(r.x * S.tex.x, r.y * S.tex.y, r.z * S.tex.z);
+}
+
 // ---- frame programs ------------------------------------------------------------------------------
 //
 // The built-in kernels as CONTINUATIONS around the persistent traversal loop (kernels.cuh,
@@ -271,7 +464,7 @@ struct FrameProgram
 #endif
     static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
-    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? 17 : (KERNEL == 0 ? 0 : 6));
+    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (EXT ? 20 : 17) : (KERNEL == 0 ? 0 : 6));
 
     __device__ void closest(RayReq& r, V3 o, V3 d) const
     {
@@ -376,6 +569,7 @@ struct FrameProgram
 
     __device__ V3 ambient_term(const Material& m) const
     {
+        if (EXT && m.kind >= 2) return v3(0.0f, 0.0f, 0.0f);     // emissive / mirror: detail/material/{emissive,mirror}.inl:14-18
         const float aw = ctx.p.ambient[3];
         return v3(m.ca[0] * m.ka * (ctx.p.ambient[0] * aw), m.ca[1] * m.ka * (ctx.p.ambient[1] * aw), m.ca[2] * m.ka * (ctx.p.ambient[2] * aw));
     }
@@ -457,9 +651,22 @@ struct FrameProgram
         const V3 pos = vadd(o, vscale(d, h.t));
         primary_hit(L, pos);
         const Material m = f.materials[h.geom_id];
-        V3 n = face_normal(h.prim_id);
         V3 shaded = ambient_term(m);
         const V3 view = vneg(d);
+        if (EXT)
+        {
+            const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
+            const V3 n = vfaceforward(S.sn, view, S.gn);
+            for (int i = 0; i < f.p.n_lights; ++i)
+            {
+                const PointLight l = f.lights[i];
+                const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
+                const V3 c = shade_light_ext(m, S, l, pos, n, view, wi);
+                shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
+            }
+            return finish(L, shaded.x, shaded.y, shaded.z, 1.0f, req);
+        }
+        V3 n = face_normal(h.prim_id);
         n = vfaceforward(n, view, n);
         for (int i = 0; i < f.p.n_lights; ++i)
         {
@@ -472,25 +679,35 @@ struct FrameProgram
     }
 
     // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
-    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16
+    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; EXT: u 17, v 18, list_index 19
     __device__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
         const FrameCtx& f = ctx;
         const uint32_t phase = L.u(W_PHASE);
         V3 pos, view, shaded;
-        uint32_t prim_id, geom_id, light;
+        uint32_t prim_id, geom_id, light, list_index = 0u;
+        float hu = 0.0f, hv = 0.0f;
         if (phase == PH_SHADOW)
         {
             pos = L.ld(K0 + 9); view = L.ld(K0 + 12); shaded = L.ld(K0 + 3);
             prim_id = L.u(K0 + 15); geom_id = L.u(K0 + 16); light = L.u(K0 + 8);
+            if (EXT) { hu = L.f(K0 + 17); hv = L.f(K0 + 18); list_index = L.u(K0 + 19); }
             if (!h.hit)
             {
                 const Material m = f.materials[geom_id];
                 const PointLight l = f.lights[light];
-                const V3 sn = face_normal(prim_id);
-                const V3 n = vfaceforward(sn, view, sn);
                 const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
-                const V3 c = shade_light(m, l, pos, n, view, wi);
+                V3 c;
+                if (EXT)
+                {
+                    const Surface S = surface_at(f, prim_id, geom_id, list_index, hu, hv);
+                    c = shade_light_ext(m, S, l, pos, vfaceforward(S.sn, view, S.gn), view, wi);
+                }
+                else
+                {
+                    const V3 sn = face_normal(prim_id);
+                    c = shade_light(m, l, pos, vfaceforward(sn, view, sn), view, wi);
+                }
                 shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
             }
             ++light;
@@ -509,6 +726,7 @@ struct FrameProgram
             prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
             shaded = ambient_term(f.materials[geom_id]);
             L.st(K0 + 9, pos); L.st(K0 + 12, view); L.u(K0 + 15) = prim_id; L.u(K0 + 16) = geom_id;
+            if (EXT) { hu = h.u; hv = h.v; list_index = h.list_index; L.f(K0 + 17) = hu; L.f(K0 + 18) = hv; L.u(K0 + 19) = list_index; }
         }
         if ((int)light < f.p.n_lights)
         {
@@ -521,10 +739,11 @@ struct FrameProgram
         const float throughput = L.f(K0 + 6);
         V3 color = L.ld(K0 + 0);
         color = v3(color.x + shaded.x * throughput, color.y + shaded.y * throughput, color.z + shaded.z * throughput);
-        const float kr = (f.materials[geom_id].kind == 0) ? 0.1f : 0.0f;   // specular_bounce, detail/whitted.inl:79-110
+        const float kr = EXT ? specular_kr(f.materials[geom_id])
+                             : ((f.materials[geom_id].kind == 0) ? 0.1f : 0.0f);   // specular_bounce, detail/whitted.inl:66-122
         if (kr > 0.0f)
         {
-            const V3 dir = vreflect(view, face_normal(prim_id));
+            const V3 dir = vreflect(view, EXT ? surface_at(f, prim_id, geom_id, list_index, hu, hv).sn : face_normal(prim_id));
             closest(req, vadd(pos, vscale(dir, f.p.epsilon)), dir);
             L.st(K0 + 0, color); L.f(K0 + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
             return true;
@@ -587,14 +806,30 @@ struct FrameProgram
             if (bounce == 0u) { result_hit = true; primary_hit(L, vadd(o, vscale(d, h.t))); }
             const V3 view = vneg(d);
             const Material m = f.materials[h.geom_id];
-            const V3 sn = face_normal(h.prim_id);
-            const V3 n = vfaceforward(sn, view, sn);
             V3 refl = v3(0.0f, 0.0f, 0.0f);
             float pdf = 0.0f;
             uint32_t samp = L.u(W_SAMP);
-            const V3 src = material_sample(m, n, view, refl, pdf, samp);
+            V3 n, src;
+            if (EXT)
+            {
+                const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
+                n = vfaceforward(S.sn, view, S.gn);
+                src = material_sample_ext(m, S, n, view, refl, pdf, samp);
+            }
+            else
+            {
+                const V3 sn = face_normal(h.prim_id);
+                n = vfaceforward(sn, view, sn);
+                src = material_sample(m, n, view, refl, pdf, samp);
+            }
             L.u(W_SAMP) = samp;
             if (pdf <= 0.0f) { dst = v3(0.0f, 0.0f, 0.0f); finished = true; }
+            else if (EXT && m.kind == 2)
+            {
+                // has_emissive_material(surf): the path ends here with its throughput times ce * ls (detail/pathtracing.inl:93-104)
+                dst = v3(dst.x * src.x, dst.y * src.y, dst.z * src.z);
+                finished = true;
+            }
             else
             {
                 const float w = vdot(n, refl) / pdf;

@@ -24,6 +24,8 @@
 #include <cstring>
 struct float4 { float x, y, z, w; };
 struct uint4 { uint32_t x, y, z, w; };
+struct float2 { float x, y; };
+struct uchar4 { unsigned char x, y, z, w; };
 #endif
 
 namespace vsb
