@@ -10,7 +10,7 @@
 // The builder restates the reference's binned-SAH algorithm (detail/bvh/sah.h:150-428,
 // 615-762: 16 bins, longest centroid axis, leaf <= 4, leaf if split cost > 3*size, right
 // subtree first) so that trees built here have the same shape and quality as the
-// reference's; spatial splits (SBVH) are not implemented.
+// reference's, with and without spatial splits (SBVH, detail/bvh/sah.h:428-615).
 #pragma once
 #ifndef VISIONARAY_B200_BVH_H
 #define VISIONARAY_B200_BVH_H 1
@@ -190,7 +190,68 @@ template <typename P> struct is_any_bvh<bvh_ref_t<P>> : std::true_type {};
 namespace detail
 {
 
-// Binned-SAH builder; restates detail/bvh/sah.h (object splits only).
+// Where a primitive crosses an axis-aligned plane: bounds of its part on either side
+// (split_primitive customisation point, detail/bvh/sah.h:23-128).  Triangles: every edge contributes
+// its end points to the side(s) they lie on and, when it crosses, the crossing point (its coordinate
+// on the axis set to the plane).
+inline void split_edge(aabb& L, aabb& R, vec3 const& a, vec3 const& b, float plane, int axis)
+{
+    float ta = a[size_t(axis)], tb = b[size_t(axis)];
+    if (ta <= plane) L.insert(a);
+    if (ta >= plane) R.insert(a);
+    if ((ta < plane && plane < tb) || (tb < plane && plane < ta))
+    {
+        float w = (plane - ta) / (tb - ta);
+        vec3 x = a * (1.0f - w) + b * w;              // lerp(a, b, w), math/detail/math.h:459-464
+        x[size_t(axis)] = plane;
+        L.insert(x);
+        R.insert(x);
+    }
+}
+
+template <typename T>
+inline void split_primitive(aabb& L, aabb& R, float plane, int axis, basic_triangle<3, T> const& tri)
+{
+    vec3 a = tri.v1, b = a + tri.e1, c = a + tri.e2;
+    L.invalidate(); R.invalidate();
+    split_edge(L, R, a, b, plane, axis);
+    split_edge(L, R, b, c, plane, axis);
+    split_edge(L, R, c, a, plane, axis);
+}
+
+// Spheres: the two caps' bounds (detail/bvh/sah.h:66-126)
+template <typename T>
+inline void split_primitive(aabb& L, aabb& R, float plane, int axis, basic_sphere<T> const& sph)
+{
+    vec3 cen = sph.center;
+    float rad = sph.radius;
+    size_t ax = size_t(axis);
+    L.invalidate(); R.invalidate();
+    if (plane < cen[ax] - rad)      { R.min = cen - vec3(rad); R.max = cen + vec3(rad); }
+    else if (plane > cen[ax] + rad) { L.min = cen - vec3(rad); L.max = cen + vec3(rad); }
+    else
+    {
+        float del = cen[ax] - plane;
+        float da = 0.5f * (rad - del), sa = 0.5f * (rad + del);
+        float r1 = std::sqrt(rad * rad - del * del), r2 = rad;
+        if (del < 0) std::swap(r1, r2);
+        vec3 c = cen, h = vec3(r1);
+        c[ax] -= sa; h[ax] = da;
+        L.insert(c - h); L.insert(c + h);
+        c = cen; h = vec3(r2);
+        c[ax] += da; h[ax] = sa;
+        R.insert(c - h); R.insert(c + h);
+    }
+}
+
+inline aabb intersect(aabb const& a, aabb const& b)      // math/detail/aabb.inl:168-173
+{
+    aabb r; r.min = max(a.min, b.min); r.max = min(a.max, b.max);
+    return r;
+}
+
+// Binned-SAH builder; restates detail/bvh/sah.h: object splits over the centroid bounds and,
+// when enabled, spatial splits over the primitive bounds (SBVH, :428-615).
 class binned_sah_builder
 {
 public:
@@ -198,6 +259,9 @@ public:
 
     struct prim_ref { aabb bounds; int index; };
     struct leaf_info { aabb prim_bounds; aabb cent_bounds; int first; };
+
+    void enable_spatial_splits(bool enable) { use_spatial_splits_ = enable; }
+    void set_alpha(float value) { alpha_ = value; }
 
     template <typename P>
     leaf_info init(P const* prims, size_t n)
@@ -214,6 +278,7 @@ public:
             root.prim_bounds.insert(refs_[i].bounds);
             root.cent_bounds.insert(refs_[i].bounds.center());
         }
+        sa_threshold_ = alpha_ * (2 * safe_half_surface_area(root.prim_bounds));     // sah.h:651
         return root;
     }
 
@@ -226,44 +291,100 @@ public:
         return leaf_size;
     }
 
-    bool split(leaf_info childs[2], leaf_info const& leaf, int max_leaf_size)
+    template <typename P>
+    bool split(leaf_info childs[2], leaf_info const& leaf, P const* prims, int max_leaf_size)
     {
         int leaf_size = int(refs_.size()) - leaf.first;
         if (leaf_size <= max_leaf_size) return false;
 
         vec3 size = leaf.cent_bounds.size();
-        size_t axis = size[1] < size[0] ? 0 : 1;          // max_index, math/detail/vector.inl:811-821
-        axis = size[2] < size[axis] ? axis : 2;
+        size_t axis = max_index(size);
         if (size[axis] <= 0.0f) return false;
 
-        float k0 = leaf.cent_bounds.min[axis];
-        float k1 = float(NumBins) / (leaf.cent_bounds.max[axis] - k0);
-        auto project_unsafe = [&](vec3 const& v) { return static_cast<int>(k1 * (v[axis] - k0)); };
-
-        struct bin { aabb prim_bounds; aabb cent_bounds; int enter; int leave; };
-        std::array<bin, NumBins> bins;
-        for (auto& b : bins) { b.prim_bounds.invalidate(); b.cent_bounds.invalidate(); b.enter = 0; b.leave = 0; }
-
+        // object split: every reference goes to the bin of its centroid (sah.h:374-405)
+        projection pr(leaf.cent_bounds, int(axis));
+        bin_list bins;
+        for (auto& b : bins) b.clear();
         for (size_t r = size_t(leaf.first); r < refs_.size(); ++r)
         {
             vec3 cen = refs_[r].bounds.center();
-            int i = project_unsafe(cen);
-            i = i < 0 ? 0 : (i > NumBins - 1 ? NumBins - 1 : i);
-            bins[size_t(i)].prim_bounds.insert(refs_[r].bounds);
-            bins[size_t(i)].cent_bounds.insert(cen);
-            bins[size_t(i)].enter++;
-            bins[size_t(i)].leave++;
+            bin& b = bins[size_t(pr.project(cen))];
+            b.prim_bounds.insert(refs_[r].bounds);
+            b.cent_bounds.insert(cen);
+            b.enter++;
+            b.leave++;
+        }
+        split_result sr;
+        if (!find_split(sr, bins, leaf.prim_bounds)) return false;       // degenerate (NaN costs); the reference asserts
+
+        // spatial split: tried when the children of the object split overlap (sah.h:708-736)
+        bool spatial = false;
+        if (use_spatial_splits_)
+        {
+            float sa = 2 * safe_half_surface_area(intersect(sr.prim_bounds[0], sr.prim_bounds[1]));
+            if (sa > sa_threshold_)
+            {
+                size = leaf.prim_bounds.size();
+                axis = max_index(size);
+                if (size[axis] <= 0.0f) return false;
+                projection pr2(leaf.prim_bounds, int(axis));
+                for (auto& b : bins) b.clear();
+                for (size_t r = size_t(leaf.first); r < refs_.size(); ++r) bin_chopped(bins, refs_[r], pr2, prims);
+                split_result sr2;
+                if (find_split(sr2, bins, leaf.prim_bounds) && sr2.cost < sr.cost) { spatial = true; pr = pr2; sr = sr2; }
+            }
         }
 
+        if (sr.cost > 3.0f * leaf_size) return false;       // a leaf is cheaper
+
+        if (spatial) { partition_spatial(childs, sr, leaf, pr, prims); return true; }
+
+        childs[0].prim_bounds = sr.prim_bounds[0]; childs[0].cent_bounds = sr.cent_bounds[0];
+        childs[1].prim_bounds = sr.prim_bounds[1]; childs[1].cent_bounds = sr.cent_bounds[1];
+        auto pivot = std::partition(refs_.begin() + leaf.first, refs_.end(),
+                                    [&](prim_ref const& x) { return pr.project_unsafe(x.bounds.center()) < sr.index; });
+        childs[0].first = leaf.first;
+        childs[1].first = int(pivot - refs_.begin());
+        return true;
+    }
+
+private:
+    struct bin
+    {
+        aabb prim_bounds; aabb cent_bounds; int enter; int leave;
+        void clear() { prim_bounds.invalidate(); cent_bounds.invalidate(); enter = 0; leave = 0; }
+    };
+    using bin_list = std::array<bin, NumBins>;
+
+    // bin index of a point along the split axis, and the left plane of a bin (sah.h:230-275)
+    struct projection
+    {
+        float k0, k1; int axis;
+        projection(aabb const& bounds, int ax) : k0(bounds.min[size_t(ax)]), k1(float(NumBins) / (bounds.max[size_t(ax)] - k0)), axis(ax) {}
+        int project_unsafe(vec3 const& v) const { return static_cast<int>(k1 * (v[size_t(axis)] - k0)); }
+        int project(vec3 const& v) const { int i = project_unsafe(v); return i < 0 ? 0 : (i > NumBins - 1 ? NumBins - 1 : i); }
+        float unproject(int i) const { return float(i) / k1 + k0; }
+    };
+
+    struct split_result { aabb prim_bounds[2]; aabb cent_bounds[2]; float cost; int index; };
+
+    static size_t max_index(vec3 const& v)          // math/detail/vector.inl:811-821
+    {
+        size_t a = v[1] < v[0] ? 0 : 1;
+        return v[2] < v[a] ? a : 2;
+    }
+
+    // sweep over the bin boundaries for the cheapest one (sah.h:305-368)
+    static bool find_split(split_result& sr, bin_list const& bins, aabb const& bounds)
+    {
         auto merge = [](bin l, bin const& r)
         {
             l.prim_bounds.insert(r.prim_bounds); l.cent_bounds.insert(r.cent_bounds);
             l.enter += r.enter; l.leave += r.leave;
             return l;
         };
-
-        float hsa_parent = safe_half_surface_area(leaf.prim_bounds);
-        std::array<bin, NumBins> acc_l, acc_r;
+        float hsa_parent = safe_half_surface_area(bounds);
+        bin_list acc_l, acc_r;
         acc_l[0] = bins[0];
         for (int i = 1; i < NumBins; ++i) acc_l[size_t(i)] = merge(acc_l[size_t(i - 1)], bins[size_t(i)]);
         acc_r[NumBins - 1] = bins[NumBins - 1];
@@ -279,30 +400,95 @@ public:
             float cost = 1.0f + (hl / hsa_parent) * (3.0f * L.enter) + (hr / hsa_parent) * (3.0f * R.leave);
             if (cost < best_cost) { best_cost = cost; best_index = i; }
         }
-        if (best_index < 0) return false;            // degenerate (NaN costs); the reference asserts
-        if (best_cost > 3.0f * leaf_size) return false;
-
+        if (best_index < 0) return false;
         bin const& L = acc_l[size_t(best_index - 1)];
         bin const& R = acc_r[size_t(best_index)];
-        childs[0].prim_bounds = L.prim_bounds; childs[0].cent_bounds = L.cent_bounds;
-        childs[1].prim_bounds = R.prim_bounds; childs[1].cent_bounds = R.cent_bounds;
-
-        auto pivot = std::partition(refs_.begin() + leaf.first, refs_.end(),
-                                    [&](prim_ref const& x) { return project_unsafe(x.bounds.center()) < best_index; });
-        childs[0].first = leaf.first;
-        childs[1].first = int(pivot - refs_.begin());
+        sr.prim_bounds[0] = L.prim_bounds; sr.cent_bounds[0] = L.cent_bounds;
+        sr.prim_bounds[1] = R.prim_bounds; sr.cent_bounds[1] = R.cent_bounds;
+        sr.cost = best_cost; sr.index = best_index;
         return true;
     }
 
-private:
+    // spatial binning: the reference is chopped at every bin plane it spans; each piece's bounds
+    // (clipped to what is left of the reference) go to the piece's bin; it "enters" in its first bin
+    // and "leaves" in its last (sah.h:446-487)
+    template <typename P>
+    static void bin_chopped(bin_list& bins, prim_ref const& ref, projection const& pr, P const* prims)
+    {
+        int imin = pr.project(ref.bounds.min), imax = pr.project(ref.bounds.max);
+        aabb rest = ref.bounds;
+        for (int i = imin; i < imax; ++i)
+        {
+            aabb L, R;
+            split_primitive(L, R, pr.unproject(i + 1), pr.axis, prims[ref.index]);
+            L = intersect(L, rest);
+            rest = intersect(R, rest);
+            bins[size_t(i)].prim_bounds.insert(L);
+            bins[size_t(i)].cent_bounds.insert(L.center());
+        }
+        bins[size_t(imax)].prim_bounds.insert(rest);
+        bins[size_t(imax)].cent_bounds.insert(rest.center());
+        bins[size_t(imin)].enter++;
+        bins[size_t(imax)].leave++;
+    }
+
+    // references left of the plane move to the front, those right of it stay, a straddling one is
+    // replaced by its right part and its left part is appended, then swapped to the front block
+    // (sah.h:489-615; no reference unsplitting there either)
+    template <typename P>
+    void partition_spatial(leaf_info childs[2], split_result const& sr, leaf_info const& leaf, projection const& pr, P const* prims)
+    {
+        float plane = pr.unproject(sr.index);
+        size_t ax = size_t(pr.axis);
+        int pivot = leaf.first, i = leaf.first, last = int(refs_.size());
+        for (int k = 0; k < 2; ++k) { childs[k].prim_bounds.invalidate(); childs[k].cent_bounds.invalidate(); }
+        for (; i != last; ++i)
+        {
+            prim_ref& cur = refs_[size_t(i)];
+            if (cur.bounds.max[ax] <= plane)
+            {
+                childs[0].prim_bounds.insert(cur.bounds);
+                childs[0].cent_bounds.insert(cur.bounds.center());
+                if (i != pivot) std::swap(refs_[size_t(pivot)], cur);
+                ++pivot;
+            }
+            else if (cur.bounds.min[ax] >= plane)
+            {
+                childs[1].prim_bounds.insert(cur.bounds);
+                childs[1].cent_bounds.insert(cur.bounds.center());
+            }
+            else
+            {
+                prim_ref L, R;
+                split_primitive(L.bounds, R.bounds, plane, pr.axis, prims[cur.index]);
+                L.bounds = intersect(L.bounds, cur.bounds);
+                R.bounds = intersect(R.bounds, cur.bounds);
+                L.index = R.index = cur.index;
+                childs[0].prim_bounds.insert(L.bounds);
+                childs[0].cent_bounds.insert(L.bounds.center());
+                childs[1].prim_bounds.insert(R.bounds);
+                childs[1].cent_bounds.insert(R.bounds.center());
+                refs_[size_t(i)] = R;
+                refs_.push_back(L);                      // may reallocate: `cur` is dead from here on
+                std::swap(refs_[size_t(pivot)], refs_.back());
+                ++pivot;
+            }
+        }
+        childs[0].first = leaf.first;
+        childs[1].first = pivot;
+    }
+
     std::vector<prim_ref> refs_;
+    float sa_threshold_ = 1.0e+38f, alpha_ = 1.0e-5f;
+    bool use_spatial_splits_ = false;
 };
 
 // detail/bvh/build.inl:28-81, made iterative (explicit work stack) so that 20M-primitive
 // trees cannot overflow the C++ call stack; the visiting order is the same (right subtree
 // fully built before the left one).
+template <typename P>
 inline void build_tree_impl(std::vector<bvh_node>& nodes, std::vector<unsigned>& indices,
-                            binned_sah_builder& b, binned_sah_builder::leaf_info const& root, int max_leaf_size)
+                            binned_sah_builder& b, binned_sah_builder::leaf_info const& root, P const* prims, int max_leaf_size)
 {
     struct job { int index; binned_sah_builder::leaf_info leaf; };
     std::vector<job> work;
@@ -312,7 +498,7 @@ inline void build_tree_impl(std::vector<bvh_node>& nodes, std::vector<unsigned>&
         job j = work.back();
         work.pop_back();
         binned_sah_builder::leaf_info childs[2];
-        if (b.split(childs, j.leaf, max_leaf_size))
+        if (b.split(childs, j.leaf, prims, max_leaf_size))
         {
             int first_child = int(nodes.size());
             nodes[size_t(j.index)].set_inner(j.leaf.prim_bounds, unsigned(first_child));
@@ -337,14 +523,15 @@ inline void build_tree_impl(std::vector<bvh_node>& nodes, std::vector<unsigned>&
 template <typename Tree, typename P>
 typename std::enable_if<is_index_bvh<Tree>::value, Tree>::type build(P const* prims, size_t n, bool spatial_splits = false)
 {
-    if (spatial_splits) throw std::runtime_error("visionaray_b200::build: spatial splits are not supported");
     Tree tree(prims, n);
     detail::binned_sah_builder builder;
+    builder.enable_spatial_splits(spatial_splits);
+    builder.set_alpha(1.0e-5f);
     auto root = builder.init(prims, n);
     tree.clear(2 * (n / 4));
     if (n == 0) return tree;
     tree.nodes().emplace_back();
-    detail::build_tree_impl(tree.nodes(), tree.indices(), builder, root, 4);
+    detail::build_tree_impl(tree.nodes(), tree.indices(), builder, root, prims, 4);
     return tree;
 }
 

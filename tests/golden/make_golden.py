@@ -56,6 +56,7 @@ def main():
     print("wrote golden_queries.npz, golden_frames.npz")
     multi_hit_vectors()
     surface_vectors()
+    sbvh_vectors()
 
 
 def multi_hit_vectors():
@@ -87,10 +88,42 @@ def surface_vectors():
     print("wrote golden_surface.npz")
 
 
+def sbvh_scene_prims():
+    """Long thin triangles (a soup stretched 30x along x): the case spatial splits exist for."""
+    t = S.gen_triangles(5, 3000, 0, 31, 0.05).copy()
+    for o in (4, 8, 12):
+        t[:, o] *= 30.0
+    return t
+
+
+def sbvh_rays(n=6000):
+    rays = S.random_rays(n, 5, -0.2, 1.2)
+    rays[:, 0] *= 30.0
+    return rays
+
+
+def sbvh_vectors():
+    """A tree of the reference's builder WITH spatial splits (build<index_bvh<P>>(first, last, true),
+    detail/bvh/sah.h:430-615: primitives referenced from several leaves, indices > primitives) and the
+    reference's closest_hit / any_hit / multi_hit<16> records on it."""
+    tris, rays = sbvh_scene_prims(), sbvh_rays()
+    nodes, idx = O.ref_build(0, tris, True)
+    assert idx.shape[0] > tris.shape[0] * 3 // 2
+    sc = S.HostScene(0, tris, nodes, idx, None, "sbvh")
+    out = {"nodes": nodes.view(np.uint8), "indices": idx,
+           "closest": O.ref_query(sc, rays, False, FLT_MAX).view(np.uint8),
+           "any": O.ref_query(sc, rays, True, 0.5).view(np.uint8),
+           "multi16": O.ref_multi_hit(sc, rays[:1500], 16).view(np.uint8)}
+    np.savez_compressed(os.path.join(HERE, "golden_sbvh.npz"), **out)
+    print("wrote golden_sbvh.npz:", nodes.shape[0], "nodes,", idx.shape[0], "indices for", tris.shape[0], "triangles")
+
+
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "multi_hit":
         multi_hit_vectors()          # adds golden_multi_hit.npz without touching the older fixtures
     elif len(sys.argv) > 1 and sys.argv[1] == "surface":
         surface_vectors()
+    elif len(sys.argv) > 1 and sys.argv[1] == "sbvh":
+        sbvh_vectors()
     else:
         main()

@@ -11,7 +11,9 @@
 //     what is already there), the last record drops out;
 //   * no early exit (exit_traversal is any-hit only).
 // Two traversals, as for closest_hit: the reference-order BVH2 walk (bit-identical records, tie
-// order included) and the BVH8 walk (same records except the order / survivor among exact t-ties).
+// order included) and the BVH8 walk (same records except the order / survivor among exact t-ties;
+// on trees with spatial splits it reports a primitive once where the reference may report the
+// references it happens to visit, see MultiHitSink::contains).
 // The records live in the caller's output array (32-byte vsb_hit each, N per ray): a thread only
 // ever touches its own N records.
 #pragma once
@@ -39,6 +41,21 @@ struct MultiHitSink
             rec[k] = h;
         }
         limit = FLT_MAX;
+    }
+
+    // Is this primitive already recorded at this t?  A tree built with spatial splits (SBVH,
+    // detail/bvh/sah.h:430-615) references a primitive from several leaves; the BVH8 walk may reach a
+    // different subset of those references than the reference-order walk does, so it reports every
+    // primitive once (the records are sorted: the scan stops at the first larger t).
+    VSB_HD bool contains(float t, uint32_t prim_id, uint32_t geom_id) const
+    {
+        for (int k = 0; k < n; ++k)
+        {
+            const float tk = rec[k].t;
+            if (tk > t) return false;
+            if (tk == t && rec[k].prim_id == prim_id && rec[k].geom_id == geom_id) return true;
+        }
+        return false;
     }
 
     // caller has checked t >= 0 && t < limit
@@ -129,14 +146,14 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
                 float t = -1.0f, u = 0.0f, v = 0.0f;
                 if (isect_triangle(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]),
                                    u2f(n.w[4]), u2f(n.w[5]), u2f(n.w[6]), u2f(n.w[8]), u2f(n.w[9]), u2f(n.w[10]), t, u, v)
-                    && t >= 0.0f && t < out.limit)
+                    && t >= 0.0f && t < out.limit && !out.contains(t, n.w[3], n.w[7]))
                     out.insert(t, u, v, n.w[3], n.w[7], n.w[11]);
             }
             else
             {
                 float t;
                 if (isect_sphere(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]), u2f(n.w[3]), t)
-                    && t >= 0.0f && t < out.limit)
+                    && t >= 0.0f && t < out.limit && !out.contains(t, n.w[4], n.w[5]))
                     out.insert(t, 0.0f, 0.0f, n.w[4], n.w[5], n.w[6]);
             }
             if (pg_mask) continue;
