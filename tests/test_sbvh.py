@@ -82,6 +82,30 @@ def test_host_instantiation_on_split_tree(sbvh):
     w.close()
 
 
+def test_host_builder_with_spatial_splits_reproduces_the_fixture(sbvh):
+    """build<index_bvh<P>>(prims, n, true) of include/visionaray_b200/bvh.h == the reference builder's
+    tree, byte for byte (nodes and indices)."""
+    sc, rays, gold = sbvh
+    nodes, idx = S.build_bvh(0, sc.prims, spatial_splits=True)
+    assert nodes.tobytes() == sc.nodes.tobytes() and idx.tobytes() == sc.indices.tobytes()
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref is only built where /root/reference exists")
+@pytest.mark.parametrize("kind,gen", [
+    (0, lambda: S.gen_triangles(5, 4000, 0, 31, 0.1)),
+    (0, lambda: S.gen_triangles(5, 1500, 0, 33, 1.0)),
+    (0, lambda: S.gen_triangles(3, 300, 0, 3)),
+    (0, lambda: S.gen_triangles(2, 60, 0, 2, 0.15)),
+    (1, lambda: S.gen_spheres(3000, 7, 0.02, 0.2)),
+    (1, lambda: S.gen_spheres(2000, 9, 0.005, 0.5)),
+])
+def test_host_builder_with_spatial_splits_matches_reference_builder(kind, gen):
+    prims = gen()
+    nodes, idx = S.build_bvh(kind, prims, spatial_splits=True)
+    rn, ri = O.ref_build(kind, prims, True)
+    assert nodes.tobytes() == rn.tobytes() and idx.tobytes() == ri.tobytes()
+
+
 def check_unique_multi(ref, got):
     want = unique_records(ref)
     full = (ref["hit"] != 0).all(axis=1)       # the reference's window was full: a duplicate may have pushed a hit out

@@ -168,6 +168,7 @@ def host_lib() -> C.CDLL:
         lib.vsbh_face_normals.argtypes = [vp, sz, vp]
         lib.vsbh_primary_rays.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, vp]
         lib.vsbh_build_bvh.argtypes = [C.c_int, vp, sz, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        lib.vsbh_build_bvh_ex.argtypes = [C.c_int, vp, sz, C.c_int, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
         _host_lib = lib
     return _host_lib
 

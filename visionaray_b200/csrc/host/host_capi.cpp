@@ -55,14 +55,25 @@ void vsbh_face_normals(const void* tris, size_t n, void* normals16)
 
 // build<index_bvh<P>>(); prim_kind 0 triangles, 1 spheres.  nodes_out needs 2n-1 entries,
 // idx_out n entries.
+int vsbh_build_bvh_ex(int prim_kind, const void* prims, size_t n, int spatial_splits, void* nodes_out, size_t nodes_cap,
+                      size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx);
+
 int vsbh_build_bvh(int prim_kind, const void* prims, size_t n, void* nodes_out, size_t nodes_cap,
                    size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx)
+{
+    return vsbh_build_bvh_ex(prim_kind, prims, n, 0, nodes_out, nodes_cap, n_nodes, idx_out, idx_cap, n_idx);
+}
+
+// ... with the reference's third argument: build<index_bvh<P>>(first, last, enable_spatial_splits).
+// A split tree has more indices than primitives (and up to 2 * indices - 1 nodes): size the outputs for it.
+int vsbh_build_bvh_ex(int prim_kind, const void* prims, size_t n, int spatial_splits, void* nodes_out, size_t nodes_cap,
+                      size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx)
 {
     try
     {
         if (prim_kind == 0)
         {
-            auto t = build<index_bvh<basic_triangle<3, float>>>(reinterpret_cast<basic_triangle<3, float> const*>(prims), n);
+            auto t = build<index_bvh<basic_triangle<3, float>>>(reinterpret_cast<basic_triangle<3, float> const*>(prims), n, spatial_splits != 0);
             *n_nodes = t.num_nodes(); *n_idx = t.num_indices();
             if (*n_nodes > nodes_cap || *n_idx > idx_cap) return 1;
             std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
@@ -70,7 +81,7 @@ int vsbh_build_bvh(int prim_kind, const void* prims, size_t n, void* nodes_out, 
         }
         else
         {
-            auto t = build<index_bvh<basic_sphere<float>>>(reinterpret_cast<basic_sphere<float> const*>(prims), n);
+            auto t = build<index_bvh<basic_sphere<float>>>(reinterpret_cast<basic_sphere<float> const*>(prims), n, spatial_splits != 0);
             *n_nodes = t.num_nodes(); *n_idx = t.num_indices();
             if (*n_nodes > nodes_cap || *n_idx > idx_cap) return 1;
             std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
