@@ -439,8 +439,20 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         s->surf_allocs.clear();
         return err;
     }
-    c.ref_prims = reinterpret_cast<const float4*>(s->d_prims);
-    c.indices = s->d_indices;
+    if (desc->normal_binding == VSB_NORMALS_PER_VERTEX)
+    {
+        const size_t n_list = s->d_indices ? s->n_idx : s->n_prims;
+        float4* gn = nullptr;
+        cudaError_t e = cudaMalloc((void**)&gn, n_list * sizeof(float4));
+        if (e != cudaSuccess) { for (void* q : s->surf_allocs) cudaFree(q); s->surf_allocs.clear(); return (int)e; }
+        s->surf_allocs.push_back(gn);
+        vsb::surface_geo_normals_kernel<<<(unsigned)((n_list + 255) / 256), 256, 0, g.stream>>>(
+            reinterpret_cast<const float4*>(s->d_prims), s->d_indices, n_list, gn);
+        ++g.launches;
+        e = cudaStreamSynchronize(g.stream);
+        if (e != cudaSuccess) { for (void* q : s->surf_allocs) cudaFree(q); s->surf_allocs.clear(); return (int)e; }
+        c.geo_normals = gn;
+    }
     c.enabled = 1;
     s->surf = c;
     return VSB_OK;

@@ -67,8 +67,9 @@ struct SurfCtx
     const float4*     colors;       // per face / per vertex like the normals; null without colours
     const float2*     tex_coords;   // [3 prim_id + k]; null without textures
     const DevTexture* textures;     // by geom_id
-    const float4*     ref_prims;    // the scene's basic_triangle records (4 x 16 B: ids, v1, e1, e2)
-    const uint32_t*   indices;      // index_bvh indirection (bvh.h:226-229); null for a plain bvh
+    const float4*     geo_normals;  // per vertex binding: normalize(cross(e1, e2)) of primitive(i), by primitive_list_index i
+                                    // (precomputed by surface_geo_normals_kernel: one load at the hit instead of
+                                    // indices[i] -> 64-byte triangle -> cross -> normalize)
 };
 
 struct FrameCtx
@@ -295,6 +296,20 @@ __device__ inline V3 tex2d_rgb(const DevTexture& t, float s, float tt)
     return v3(__double2float_rn((double)q[0] / 255.0), __double2float_rn((double)q[1] / 255.0), __double2float_rn((double)q[2] / 255.0));
 }
 
+// get_normal(hr, triangle) = normalize(cross(e1, e2)) (get_normal.h:96-101) of primitive(i) =
+// prims[indices[i]] (bvh.h:226-229) for every position i of the primitive list, same single-rounding
+// arithmetic as at shading time
+__global__ void surface_geo_normals_kernel(const float4* __restrict__ ref_prims, const uint32_t* __restrict__ indices,
+                                           size_t n_list, float4* __restrict__ out)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_list) return;
+    const size_t pi = indices ? indices[i] : i;
+    const float4 e1 = ref_prims[pi * 4 + 2], e2 = ref_prims[pi * 4 + 3];
+    const V3 g = vnormalize(vcross(v3(e1.x, e1.y, e1.z), v3(e2.x, e2.y, e2.z)));
+    out[i] = make_float4(g.x, g.y, g.z, 0.0f);
+}
+
 // get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530
 __device__ inline Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v)
 {
@@ -316,9 +331,8 @@ __device__ inline Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32
     {
         // geometric normal of primitive(primitive_list_index) (get_surface.h:313-327, get_normal.h:96-101),
         // shading normal interpolated (get_shading_normal.h:60-76)
-        const size_t pi = sf.indices ? __ldg(sf.indices + list_index) : list_index;
-        const float4 e1 = __ldg(sf.ref_prims + pi * 4 + 2), e2 = __ldg(sf.ref_prims + pi * 4 + 3);
-        S.gn = vnormalize(vcross(v3(e1.x, e1.y, e1.z), v3(e2.x, e2.y, e2.z)));
+        const float4 g = __ldg(sf.geo_normals + list_index);
+        S.gn = v3(g.x, g.y, g.z);
         const float4* n = sf.normals + (size_t)prim_id * 3;
         const float4 a = __ldg(n), b = __ldg(n + 1), c = __ldg(n + 2);
         S.sn = vnormalize(vlerp3(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), u, v));
@@ -464,7 +478,7 @@ struct FrameProgram
 #endif
     static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
-    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (EXT ? 20 : 17) : (KERNEL == 0 ? 0 : 6));
+    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (EXT ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
 
     __device__ void closest(RayReq& r, V3 o, V3 d) const
     {
@@ -679,19 +693,18 @@ struct FrameProgram
     }
 
     // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
-    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; EXT: u 17, v 18, list_index 19
+    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; EXT: the surface of the current hit,
+    // evaluated once -- shading normal (faceforwarded) 17..19, tex_color 20..22, reflection direction 23..25
     __device__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
         const FrameCtx& f = ctx;
         const uint32_t phase = L.u(W_PHASE);
         V3 pos, view, shaded;
-        uint32_t prim_id, geom_id, light, list_index = 0u;
-        float hu = 0.0f, hv = 0.0f;
+        uint32_t prim_id, geom_id, light;
         if (phase == PH_SHADOW)
         {
             pos = L.ld(K0 + 9); view = L.ld(K0 + 12); shaded = L.ld(K0 + 3);
             prim_id = L.u(K0 + 15); geom_id = L.u(K0 + 16); light = L.u(K0 + 8);
-            if (EXT) { hu = L.f(K0 + 17); hv = L.f(K0 + 18); list_index = L.u(K0 + 19); }
             if (!h.hit)
             {
                 const Material m = f.materials[geom_id];
@@ -700,8 +713,9 @@ struct FrameProgram
                 V3 c;
                 if (EXT)
                 {
-                    const Surface S = surface_at(f, prim_id, geom_id, list_index, hu, hv);
-                    c = shade_light_ext(m, S, l, pos, vfaceforward(S.sn, view, S.gn), view, wi);
+                    Surface S;
+                    S.tex = L.ld(K0 + 20);
+                    c = shade_light_ext(m, S, l, pos, L.ld(K0 + 17), view, wi);
                 }
                 else
                 {
@@ -726,7 +740,12 @@ struct FrameProgram
             prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
             shaded = ambient_term(f.materials[geom_id]);
             L.st(K0 + 9, pos); L.st(K0 + 12, view); L.u(K0 + 15) = prim_id; L.u(K0 + 16) = geom_id;
-            if (EXT) { hu = h.u; hv = h.v; list_index = h.list_index; L.f(K0 + 17) = hu; L.f(K0 + 18) = hv; L.u(K0 + 19) = list_index; }
+            if (EXT)
+            {
+                const Surface S = surface_at(f, prim_id, geom_id, h.list_index, h.u, h.v);
+                L.st(K0 + 17, vfaceforward(S.sn, view, S.gn)); L.st(K0 + 20, S.tex);
+                L.st(K0 + 23, vreflect(view, S.sn));          // specular_bounce(material, view_dir, surf.shading_normal)
+            }
         }
         if ((int)light < f.p.n_lights)
         {
@@ -743,7 +762,7 @@ struct FrameProgram
                              : ((f.materials[geom_id].kind == 0) ? 0.1f : 0.0f);   // specular_bounce, detail/whitted.inl:66-122
         if (kr > 0.0f)
         {
-            const V3 dir = vreflect(view, EXT ? surface_at(f, prim_id, geom_id, list_index, hu, hv).sn : face_normal(prim_id));
+            const V3 dir = EXT ? L.ld(K0 + 23) : vreflect(view, face_normal(prim_id));
             closest(req, vadd(pos, vscale(dir, f.p.epsilon)), dir);
             L.st(K0 + 0, color); L.f(K0 + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
             return true;
