@@ -647,17 +647,39 @@ sched_params_matrix<RT, pixel_sampler::uniform_type> make_sched_params(mat4 cons
 
 //-------------------------------------------------------------------------------------------------
 // Render targets (render_target.h:45-101, simple_buffer_rt.h:21-52, gpu_buffer_rt.h:16-48).
-// PF_RGBA32F colour, depth PF_UNSPECIFIED (none) or PF_DEPTH32F: buffer[y * width + x], y up,
-// pitch = width.
+// Colour PF_RGBA32F, PF_RGBA8, PF_RGB32F or PF_RGB8 (pixel_format.h, pixel_traits.h), depth PF_UNSPECIFIED
+// (none) or PF_DEPTH32F: buffer[y * width + x], y up, pitch = width.
 //
 
-enum pixel_format { PF_UNSPECIFIED = 0, PF_RGBA32F = 1, PF_DEPTH32F = 2 };
+enum pixel_format { PF_UNSPECIFIED = 0, PF_RGBA32F = 1, PF_DEPTH32F = 2, PF_RGBA8 = 3, PF_RGB32F = 4, PF_RGB8 = 5 };
+
+struct unorm8x3 { unsigned char x, y, z; };
+
+// pixel_traits<PF>::type (pixel_traits.h): the element type of a colour buffer of that format and its
+// VSB_PF_* id.  vector<3,float> is 16-byte aligned in the reference, hence a PF_RGB32F pixel is a vec3.
+template <pixel_format PF> struct pixel_traits;
+template <> struct pixel_traits<PF_RGBA32F> { using type = vec4;     static const int id = VSB_PF_RGBA32F; };
+template <> struct pixel_traits<PF_RGBA8>   { using type = unorm8x4; static const int id = VSB_PF_RGBA8; };
+template <> struct pixel_traits<PF_RGB32F>  { using type = vec3;     static const int id = VSB_PF_RGB32F; };
+template <> struct pixel_traits<PF_RGB8>    { using type = unorm8x3; static const int id = VSB_PF_RGB8; };
+
+namespace detail
+{
+// convert(target, vec4) of pixel_access::store (detail/color_conversion.h:213-247, math/detail/unorm.inl:18-24)
+inline unsigned char to_unorm8(float f) { f = f < 0.0f ? 0.0f : (f > 1.0f ? 1.0f : f); return (unsigned char)(unsigned)(f * 255.0); }
+template <typename T> T to_pixel(vec4 const& c);
+template <> inline vec4 to_pixel<vec4>(vec4 const& c) { return c; }
+template <> inline unorm8x4 to_pixel<unorm8x4>(vec4 const& c) { return unorm8x4{ to_unorm8(c.x), to_unorm8(c.y), to_unorm8(c.z), to_unorm8(c.w) }; }
+template <> inline vec3 to_pixel<vec3>(vec4 const& c) { return vec3(c.x * c.w, c.y * c.w, c.z * c.w); }
+template <> inline unorm8x3 to_pixel<unorm8x3>(vec4 const& c) { return unorm8x3{ to_unorm8(c.x * c.w), to_unorm8(c.y * c.w), to_unorm8(c.z * c.w) }; }
+} // namespace detail
 
 template <pixel_format CF, pixel_format DF>
 struct render_target_ref
 {
-    vec4* color_; float* depth_; int width_, height_;
-    vec4* color() const { return color_; }
+    using color_type = typename pixel_traits<CF>::type;
+    color_type* color_; float* depth_; int width_, height_;
+    color_type* color() const { return color_; }
     float* depth() const { return depth_; }
     int width() const { return width_; }
     int height() const { return height_; }
@@ -667,31 +689,32 @@ struct render_target_ref
 template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
 class simple_buffer_rt
 {
-    static_assert(CF == PF_RGBA32F && (DF == PF_UNSPECIFIED || DF == PF_DEPTH32F), "the path writes RGBA32F colour and DEPTH32F depth");
+    static_assert(DF == PF_UNSPECIFIED || DF == PF_DEPTH32F, "the path writes DEPTH32F depth");
 public:
-    using color_type = vec4;
+    using color_type = typename pixel_traits<CF>::type;
     using depth_type = float;
     using ref_type = render_target_ref<CF, DF>;
     static const int memory = VSB_MEM_HOST;
+    static const int color_format = pixel_traits<CF>::id;
 
     color_type* color() { return color_.data(); }
     color_type const* color() const { return color_.data(); }
     depth_type* depth() { return DF == PF_DEPTH32F ? depth_.data() : nullptr; }
     depth_type const* depth() const { return DF == PF_DEPTH32F ? depth_.data() : nullptr; }
     ref_type ref() { return ref_type{ color(), depth(), int(width_), int(height_) }; }
-    void clear_color_buffer(vec4 const& c = vec4(0.0f)) { for (auto& p : color_) p = c; }
+    void clear_color_buffer(vec4 const& c = vec4(0.0f)) { color_type q = detail::to_pixel<color_type>(c); for (auto& p : color_) p = q; }
     void clear_depth_buffer(float d = 1.0f) { for (auto& p : depth_) p = d; }
     void begin_frame() {}
     void end_frame() {}
     void resize(size_t w, size_t h)
     {
-        width_ = w; height_ = h; color_.assign(w * h, vec4(0.0f));
+        width_ = w; height_ = h; color_.assign(w * h, detail::to_pixel<color_type>(vec4(0.0f)));
         if (DF == PF_DEPTH32F) depth_.assign(w * h, 0.0f);
     }
     size_t width() const { return width_; }
     size_t height() const { return height_; }
 private:
-    std::vector<vec4> color_;
+    std::vector<color_type> color_;
     std::vector<float> depth_;
     size_t width_ = 0, height_ = 0;
 };
@@ -702,12 +725,13 @@ using cpu_buffer_rt = simple_buffer_rt<CF, DF>;   // cpu_buffer_rt minus display
 template <pixel_format CF = PF_RGBA32F, pixel_format DF = PF_UNSPECIFIED>
 class gpu_buffer_rt
 {
-    static_assert(CF == PF_RGBA32F && (DF == PF_UNSPECIFIED || DF == PF_DEPTH32F), "the path writes RGBA32F colour and DEPTH32F depth");
+    static_assert(DF == PF_UNSPECIFIED || DF == PF_DEPTH32F, "the path writes DEPTH32F depth");
 public:
-    using color_type = vec4;
+    using color_type = typename pixel_traits<CF>::type;
     using depth_type = float;
     using ref_type = render_target_ref<CF, DF>;
     static const int memory = VSB_MEM_DEVICE;
+    static const int color_format = pixel_traits<CF>::id;
 
     gpu_buffer_rt() = default;
     gpu_buffer_rt(gpu_buffer_rt const&) = delete;
@@ -731,8 +755,8 @@ public:
     }
     void clear_color_buffer(vec4 const& c = vec4(0.0f))
     {
-        std::vector<vec4> tmp(width_ * height_, c);
-        detail::check(vsb_device_copy(color_, tmp.data(), tmp.size() * sizeof(vec4), VSB_MEM_DEVICE, VSB_MEM_HOST), "vsb_device_copy");
+        std::vector<color_type> tmp(width_ * height_, detail::to_pixel<color_type>(c));
+        detail::check(vsb_device_copy(color_, tmp.data(), tmp.size() * sizeof(color_type), VSB_MEM_DEVICE, VSB_MEM_HOST), "vsb_device_copy");
     }
     void begin_frame() {}
     void end_frame() {}
@@ -742,8 +766,8 @@ public:
         if (color_) { vsb_device_free(color_); color_ = nullptr; }
         width_ = w; height_ = h;
         void* p = nullptr;
-        detail::check(vsb_device_alloc(w * h * sizeof(vec4), &p), "vsb_device_alloc");
-        color_ = static_cast<vec4*>(p);
+        detail::check(vsb_device_alloc(w * h * sizeof(color_type), &p), "vsb_device_alloc");
+        color_ = static_cast<color_type*>(p);
         clear_color_buffer();
         if (depth_) { vsb_device_free(depth_); depth_ = nullptr; }
         if (DF == PF_DEPTH32F)
@@ -756,12 +780,12 @@ public:
     size_t width() const { return width_; }
     size_t height() const { return height_; }
     // read back (the reference's users go through GL or thrust copies)
-    void download(vec4* dst) const
+    void download(color_type* dst) const
     {
-        detail::check(vsb_device_copy(dst, color_, width_ * height_ * sizeof(vec4), VSB_MEM_HOST, VSB_MEM_DEVICE), "vsb_device_copy");
+        detail::check(vsb_device_copy(dst, color_, width_ * height_ * sizeof(color_type), VSB_MEM_HOST, VSB_MEM_DEVICE), "vsb_device_copy");
     }
 private:
-    vec4* color_ = nullptr;
+    color_type* color_ = nullptr;
     float* depth_ = nullptr;
     size_t width_ = 0, height_ = 0;
 };
@@ -817,6 +841,7 @@ public:
         d.color = sparams.rt.color();
         d.depth = d.camera_kind == VSB_CAM_MATRIX ? sparams.rt.depth() : nullptr;   // the reference's depth path needs the matrices
         d.mem = std::remove_reference<decltype(sparams.rt)>::type::memory;
+        d.color_format = std::remove_reference<decltype(sparams.rt)>::type::color_format;
         d.traverse = traverse_;
         d.tile_rank = tile_rank_; d.tile_nranks = tile_nranks_;
 

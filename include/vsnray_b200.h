@@ -122,6 +122,13 @@ enum { VSB_KERNEL_SIMPLE = 0, VSB_KERNEL_WHITTED = 1, VSB_KERNEL_AO = 2, VSB_KER
 enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2,
        VSB_PS_SSAA2 = 3, VSB_PS_SSAA4 = 4, VSB_PS_SSAA8 = 5 };   /* ssaa_type<2|4|8>, detail/sched_common.h:222-295,640-698 */
 
+/* colour format of the render target = what pixel_access::store / get / blend convert to and from
+ * (pixel_format.h, pixel_traits.h, detail/pixel_access.h:38-58,668-689,1153-1175, detail/color_conversion.h:168-265,
+ * math/detail/unorm.inl:18-31).  Bytes per pixel: 16, 4, 16 (vector<3,float> is 16-byte aligned in the reference;
+ * the 4th word is never written), 3.  unorm8 = (uint32)(clamp(f, 0, 1) * 255.0) (truncation); RGBA -> RGB multiplies
+ * by alpha, RGB -> RGBA (blend, SSAA) reads alpha 1; blends and SSAA accumulate THROUGH the format like the reference. */
+enum { VSB_PF_RGBA32F = 0, VSB_PF_RGBA8 = 1, VSB_PF_RGB32F = 2, VSB_PF_RGB8 = 3 };
+
 /* traversal engine: the wide quantised BVH8 (default, fast) or the reference-order BVH2 walk
  * (bit-exact with detail/bvh/intersect.inl:35-134 including tie order and any-hit winner). */
 enum { VSB_TRAVERSE_WIDE = 0, VSB_TRAVERSE_EXACT = 1 };
@@ -172,7 +179,7 @@ typedef struct vsb_frame_desc {
                                             normals attached to scenes[0] by vsb_scene_set_normals() */
     const vsb_material*    materials;    /* indexed by geom_id */
     const vsb_point_light* lights;
-    void*    color;                      /* PF_RGBA32F, buffer[y*width+x] (pixel_access.h:38-58) */
+    void*    color;                      /* buffer[y*width+x] (pixel_access.h:38-58), pixels of `color_format` (PF_RGBA32F by default) */
     void*    depth;                      /* PF_DEPTH32F, buffer[y*width+x], same memory (and tile layout) as color;
                                             may be NULL.  depth = hit ? ((proj*view*isect_pos).z/w + 1)/2 : 1
                                             (depth_transform, detail/sched_common.h:337-354,425); needs
@@ -197,6 +204,8 @@ typedef struct vsb_frame_desc {
      * matrix<4,4,float> layout: 16 floats, column-major. */
     int32_t  camera_kind;                /* VSB_CAM_BASIS (cam_eye/u/v/w above) or VSB_CAM_MATRIX */
     float    view_matrix[16], proj_matrix[16];
+    int32_t  color_format;               /* VSB_PF_*: format of `color` (default VSB_PF_RGBA32F).  Compact multi-rank tile
+                                            buffers (VSB_TILES_COMPACT with tile_nranks > 1) are RGBA32F only. */
     int32_t  generic_materials;          /* non-zero: `materials` is a generic_material<emissive, matte, mirror, plastic>
                                             list, i.e. entries may be VSB_MAT_EMISSIVE / VSB_MAT_MIRROR (pathtracing.inl:93-104,
                                             whitted.inl:66-122).  Detected automatically when params_mem == VSB_MEM_HOST. */

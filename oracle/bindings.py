@@ -86,6 +86,7 @@ def oracle_lib():
         lib.vso_camera_basis.argtypes = [vp, vp, vp, vp, vp]
         lib.vso_frame_matrix.argtypes = [vp, vp, vp, C.POINTER(Bvh), vp, vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
         lib.vso_mat4_inverse.argtypes = [vp, vp]
+        lib.vso_frame_format.argtypes = [vp, C.POINTER(Bvh), vp, vp, vp, vp, C.c_int, C.POINTER(Counters), C.c_int]
         lib.vso_frame_surface.argtypes = [vp, C.POINTER(Bvh), vp, vp, vp, vp, C.POINTER(Counters), C.c_int]
         lib.vso_tex2d.argtypes = [vp, C.c_float, C.c_float, vp]
         lib.vso_multi_hit.argtypes = [C.POINTER(Bvh), C.c_int, vp, sz, C.c_int, vp, C.c_int]
@@ -116,6 +117,8 @@ def ref_lib(fast: bool = False):
         lib.ref_frame.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int, C.c_int, C.c_int, vp]
         lib.ref_frame_matrix.argtypes = [vp, vp, vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, vp, C.c_int, vp]
         lib.ref_camera_matrices.argtypes = [vp, C.c_float, C.c_float, vp, vp]
+        if hasattr(lib, "ref_frame_format"):
+            lib.ref_frame_format.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, C.c_int, C.c_int]
         if hasattr(lib, "ref_frame_surface"):
             lib.ref_frame_surface.argtypes = [vp, vp, sz, vp, sz, vp, sz, C.c_int, C.c_int, vp, vp, vp, vp, C.c_int, vp, vp,
                                               vp, C.c_int]
@@ -196,6 +199,41 @@ def oracle_frame(scene, fp, materials, lights, rgba=None, nthreads=0, counters=N
     oracle_lib().vso_frame(C.byref(fp), C.byref(b), _p(scene.normals), _p(materials), _p(lights), _p(rgba),
                            C.byref(c), nthreads or (os.cpu_count() or 1))
     return rgba
+
+
+# colour formats of the render target: name -> (id, bytes per pixel, numpy element type, channels stored)
+PIXEL_FORMATS = {"PF_RGBA32F": (0, 16, np.float32, 4), "PF_RGBA8": (1, 4, np.uint8, 4),
+                 "PF_RGB32F": (2, 16, np.float32, 4), "PF_RGB8": (3, 3, np.uint8, 3)}
+
+
+def format_buffer(fmt: str, width: int, height: int) -> np.ndarray:
+    """A zeroed colour buffer of that format: (h, w, channels stored); PF_RGB32F pixels are 16 bytes
+    (vector<3,float> is 16-byte aligned in the reference), the 4th word is never written."""
+    _, _, dt, ch = PIXEL_FORMATS[fmt]
+    return np.zeros((height, width, ch), dtype=dt)
+
+
+def oracle_frame_format(scene, fp, materials, lights, fmt: str, color=None, nthreads=0):
+    """vso_frame_format: the frame into a colour buffer of format `fmt` (store / blend / SSAA through it)."""
+    if color is None:
+        color = format_buffer(fmt, fp.width, fp.height)
+    b = make_bvh(scene)
+    c = Counters()
+    oracle_lib().vso_frame_format(C.byref(fp), C.byref(b), _p(scene.normals), _p(materials), _p(lights), _p(color),
+                                  PIXEL_FORMATS[fmt][0], C.byref(c), nthreads or (os.cpu_count() or 1))
+    return color
+
+
+def ref_frame_format(scene, fp, materials, lights, fmt: str, color=None, nthreads=0):
+    """The same through the reference's own pixel_access::store / blend and colour conversion."""
+    if color is None:
+        color = format_buffer(fmt, fp.width, fp.height)
+    rc = ref_lib().ref_frame_format(C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes), scene.nodes.shape[0],
+                                    _p(scene.indices), scene.indices.shape[0], _p(scene.normals), _p(materials), _p(lights),
+                                    _p(color), PIXEL_FORMATS[fmt][0], nthreads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError("ref_frame_format: unsupported kernel / format")
+    return color
 
 
 def oracle_frame_surface(scene, fp, surface, materials, lights, rgba=None, nthreads=0):

@@ -453,6 +453,127 @@ extern "C" int ref_frame_surface(void const* fp_, void const* prims, size_t n_pr
 
 namespace
 {
+
+// ---- render targets of other colour formats: the reference's own pixel_access::store / blend
+// (detail/pixel_access.h) and colour conversion, driven per pixel like sample_pixel_impl does
+// (detail/sched_common.h:361-528 store, :516-528 blend, :640-698 SSAA = clear + N x blend)
+
+template <pixel_format CF, typename K>
+void scalar_frame_format(K kernel, frame_params const& fp, void* color, int nthreads)
+{
+    using color_t = typename pixel_traits<CF>::type;
+    color_t* buf = reinterpret_cast<color_t*>(color);
+    auto cam = make_cam(fp);
+    auto f = normalize(cam.eye() - cam.center());
+    auto s = normalize(cross(cam.up(), f));
+    auto u = cross(f, s);
+    vec3 eye   = cam.eye();
+    vec3 cam_u = s * tan(cam.fovy() / 2.0f) * cam.aspect();
+    vec3 cam_v = u * tan(cam.fovy() / 2.0f);
+    vec3 cam_w = -f;
+    int w = fp.width, h = fp.height;
+    pixel_format_constant<CF> dst_format;
+    pixel_format_constant<PF_RGBA32F> src_format;
+    parallel_for(size_t(w) * h, nthreads, [&](size_t b, size_t e)
+    {
+        for (size_t i = b; i < e; ++i)
+        {
+            int x = int(i % size_t(w)), y = int(i / size_t(w));
+            det_sampler samp((uint32_t)i, fp.frame_num, fp.seed);
+            float px = float(x), py = float(y);
+            if (fp.pixel_sampler >= 3)
+            {
+                random_sampler<float> unused;
+                detail::pixel_access::store(dst_format, src_format, x, y, w, h, vec4(0.0f), buf);
+                auto run = [&](ray_t const& r, float alpha)
+                {
+                    auto res = kernel(r, samp);
+                    detail::pixel_access::blend(dst_format, src_format, x, y, w, h, res.color, buf, alpha, 1.0f);
+                };
+                if (fp.pixel_sampler == 3)
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<2>{}, unused, unsigned(x), unsigned(y), w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 2.0f);
+                }
+                else if (fp.pixel_sampler == 4)
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<4>{}, unused, unsigned(x), unsigned(y), w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 4.0f);
+                }
+                else
+                {
+                    auto rays = detail::make_primary_rays(ray_t{}, pixel_sampler::ssaa_type<8>{}, unused, unsigned(x), unsigned(y), w, h, eye, cam_u, cam_v, cam_w);
+                    for (auto const& r : rays) run(r, 1.0f / 8.0f);
+                }
+                continue;
+            }
+            if (fp.pixel_sampler != 0)
+            {
+                float jx = samp.next() - 0.5f;
+                float jy = samp.next() - 0.5f;
+                px += jx; py += jy;
+            }
+            ray_t r = detail::make_primary_ray_impl<ray_t>(px, py, w, h, eye, cam_u, cam_v, cam_w);
+            auto res = kernel(r, samp);
+            if (fp.pixel_sampler == 2)
+            {
+                float alpha = 1.0f / float(fp.frame_num);
+                detail::pixel_access::blend(dst_format, src_format, x, y, w, h, res.color, buf, alpha, 1.0f - alpha);
+            }
+            else detail::pixel_access::store(dst_format, src_format, x, y, w, h, res.color, buf);
+        }
+    });
+}
+
+template <typename K>
+int scalar_frame_any_format(K kernel, frame_params const& fp, void* color, int format, int nthreads)
+{
+    switch (format)
+    {
+    case 0: scalar_frame_format<PF_RGBA32F>(kernel, fp, color, nthreads); return 0;
+    case 1: scalar_frame_format<PF_RGBA8>(kernel, fp, color, nthreads); return 0;
+    case 2: scalar_frame_format<PF_RGB32F>(kernel, fp, color, nthreads); return 0;
+    case 3: scalar_frame_format<PF_RGB8>(kernel, fp, color, nthreads); return 0;
+    default: return -1;
+    }
+}
+
+} // namespace
+
+// scalar parity driver into a colour buffer of `format` (0 PF_RGBA32F, 1 PF_RGBA8, 2 PF_RGB32F, 3 PF_RGB8);
+// plastic or matte material list, per-face normals, kernels simple / whitted / pathtracing
+extern "C" int ref_frame_format(void const* fp_, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                                uint32_t const* indices, size_t n_idx, float const* normals16, void const* mats_,
+                                void const* lights_, void* color, int format, int nthreads)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    if (fp.kernel == 2) return -1;
+    scene_host s{ make_ref<tri_t>(prims, n_prims, nodes, n_nodes, indices, n_idx) };
+    fill_scene(s, fp, normals16, n_prims, (mat_pod const*)mats_, (light_pod const*)lights_);
+    bool use_matte = fp.n_materials > 0 && ((mat_pod const*)mats_)[0].kind == 1;
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+    auto lb = s.lights.data();
+    auto le = s.lights.data() + s.lights.size();
+    tri_ref_t const* pb = &s.ref;
+    tri_ref_t const* pe = &s.ref + 1;
+    auto run = [&](auto kparams) -> int
+    {
+        using KP = decltype(kparams);
+        if (fp.kernel == 0) return scalar_frame_any_format(no_sampler_adapter<simple::kernel<KP>>{ { kparams } }, fp, color, format, nthreads);
+        if (fp.kernel == 1) return scalar_frame_any_format(no_sampler_adapter<whitted::kernel<KP>>{ { kparams } }, fp, color, format, nthreads);
+        return scalar_frame_any_format(pathtracing::kernel<KP>{ kparams }, fp, color, format, nthreads);
+    };
+    if (use_matte)
+        return run(make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(), s.mattes.data(), lb, le,
+                                      fp.num_bounces, fp.epsilon, bg, amb));
+    return run(make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(), s.plastics.data(), lb, le,
+                                  fp.num_bounces, fp.epsilon, bg, amb));
+}
+
+namespace
+{
 } // namespace
 
 extern "C"

@@ -150,6 +150,17 @@ void vso_frame_surface(const vso_frame_params* p, const vso_bvh* b, const vso_su
                        const vso_material* mats, const vso_point_light* lights, float* rgba,
                        vso_counters* counters, int nthreads);
 
+/* Colour formats of the render target (pixel_format.h): what pixel_access::store / get / blend convert to
+ * and from (detail/pixel_access.h:38-58,668-689,1153-1175; detail/color_conversion.h:168-265;
+ * math/detail/unorm.inl:18-31): 0 PF_RGBA32F (16 B), 1 PF_RGBA8 (4 B), 2 PF_RGB32F (16 B: vector<3,float> is 16-byte aligned, last word
+ * unused), 3 PF_RGB8 (3 B).
+ * vso_frame_format(): vso_frame() into a buffer of that format (blend and SSAA accumulate THROUGH the format). */
+void vso_store_pixel(int format, const float rgba[4], void* dst);
+void vso_get_pixel(int format, const void* src, float rgba[4]);
+void vso_frame_format(const vso_frame_params* p, const vso_bvh* b, const float* normals16,
+                      const vso_material* mats, const vso_point_light* lights, void* color, int format,
+                      vso_counters* counters, int nthreads);
+
 /* max depth of the BVH2 (root = depth 1); the reference's traversal stack holds 31 entries
  * (detail/stack.h:39-47, detail/bvh/intersect.inl:60) */
 int vso_bvh_max_depth(const vso_bvh* b);

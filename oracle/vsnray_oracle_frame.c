@@ -53,6 +53,8 @@ typedef struct
     const vso_material* mats;
     const vso_point_light* lights;
     float* rgba;
+    int color_format;                     /* 0 PF_RGBA32F (rgba above), else `color` in that format */
+    void* color;
     float eye[3], cu[3], cv[3], cw[3];
     int use_matrix;                       /* sched_params carries view / proj matrices */
     float view[16], inv_view[16], proj[16], inv_proj[16];
@@ -596,8 +598,93 @@ static void run_kernel(const frame_ctx* f, float px, float py, uint32_t* samp, f
     }
 }
 
+/* float_to_unorm<8> / unorm_to_float<8> -- math/detail/unorm.inl:18-31 */
+static uint8_t to_unorm8(float f)
+{
+    f = f < 0.0f ? 0.0f : (f > 1.0f ? 1.0f : f);      /* clamp (color_conversion.h:224), saturate */
+    return (uint8_t)(uint32_t)(f * (double)255);
+}
+static float from_unorm8(uint8_t u) { return (float)((float)u / (double)255); }
+
+static const int vso_bpp[4] = { 16, 4, 16, 3 };   /* pixel_traits<PF_RGB32F>::type is vector<3,float>: 16 bytes, last word unused */
+
+/* pixel_access::store -> convert(): detail/color_conversion.h:213-247 (RGBA -> RGB multiplies by alpha) */
+void vso_store_pixel(int format, const float c[4], void* dst)
+{
+    if (format == 0) memcpy(dst, c, 16);
+    else if (format == 1) { uint8_t* q = (uint8_t*)dst; for (int k = 0; k < 4; ++k) q[k] = to_unorm8(c[k]); }
+    else
+    {
+        float rgb[3] = { c[0] * c[3], c[1] * c[3], c[2] * c[3] };
+        if (format == 2) memcpy(dst, rgb, 12);
+        else { uint8_t* q = (uint8_t*)dst; for (int k = 0; k < 3; ++k) q[k] = to_unorm8(rgb[k]); }
+    }
+}
+
+/* pixel_access::get -> convert(): RGB -> RGBA sets alpha 1 (detail/color_conversion.h:249-265) */
+void vso_get_pixel(int format, const void* src, float c[4])
+{
+    if (format == 0) memcpy(c, src, 16);
+    else if (format == 1) { const uint8_t* q = (const uint8_t*)src; for (int k = 0; k < 4; ++k) c[k] = from_unorm8(q[k]); }
+    else if (format == 2) { memcpy(c, src, 12); c[3] = 1.0f; }
+    else { const uint8_t* q = (const uint8_t*)src; for (int k = 0; k < 3; ++k) c[k] = from_unorm8(q[k]); c[3] = from_unorm8(to_unorm8(1.0f)); }
+}
+
+/* store / blend of one kernel result into a formatted target: detail/pixel_access.h:1153-1175 */
+static void blend_pixel(int format, void* dst, const float col[4], float sfactor, float dfactor)
+{
+    float d[4];
+    vso_get_pixel(format, dst, d);
+    for (int k = 0; k < 4; ++k) d[k] = col[k] * sfactor + d[k] * dfactor;
+    vso_store_pixel(format, d, dst);
+}
+
+static void frame_range_format(frame_ctx* f, size_t b, size_t e, vso_counters* c)
+{
+    const vso_frame_params* p = f->p;
+    const int fmt = f->color_format;
+    size_t w = (size_t)p->width;
+    for (size_t i = b; i < e; ++i)
+    {
+        unsigned x = (unsigned)(i % w), y = (unsigned)(i / w);
+        uint32_t samp = vso_sampler_init((uint32_t)i, p->frame_num, p->seed);
+        float px = (float)x, py = (float)y;
+        char* dst = (char*)f->color + i * (size_t)vso_bpp[fmt];
+        float col[4];
+        if (p->pixel_sampler >= 3)
+        {
+            const int num = 2 << (p->pixel_sampler - 3);
+            const float alpha = 1.0f / (float)num;
+            const float zero[4] = { 0.0f, 0.0f, 0.0f, 0.0f };
+            vso_store_pixel(fmt, zero, dst);
+            for (int s = 0; s < num; ++s)
+            {
+                float dx, dy;
+                ssaa_offset(num, s, &dx, &dy);
+                run_kernel(f, px + dx, py + dy, &samp, col, NULL, c);
+                blend_pixel(fmt, dst, col, alpha, 1.0f);
+            }
+            continue;
+        }
+        if (p->pixel_sampler != 0)
+        {
+            float jx = vso_sampler_next(&samp) - 0.5f;
+            float jy = vso_sampler_next(&samp) - 0.5f;
+            px += jx; py += jy;
+        }
+        run_kernel(f, px, py, &samp, col, NULL, c);
+        if (p->pixel_sampler == 2)
+        {
+            float alpha = 1.0f / (float)p->frame_num;
+            blend_pixel(fmt, dst, col, alpha, 1.0f - alpha);
+        }
+        else vso_store_pixel(fmt, col, dst);
+    }
+}
+
 static void frame_range(frame_ctx* f, size_t b, size_t e, vso_counters* c)
 {
+    if (f->color_format != 0) { frame_range_format(f, b, e, c); return; }
     const vso_frame_params* p = f->p;
     size_t w = (size_t)p->width;
     for (size_t i = b; i < e; ++i)
@@ -677,6 +764,18 @@ void vso_frame(const vso_frame_params* p, const vso_bvh* b, const float* normals
     frame_ctx f;
     memset(&f, 0, sizeof(f));
     f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights; f.rgba = rgba;
+    vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
+    frame_run(&f, counters, nthreads);
+}
+
+void vso_frame_format(const vso_frame_params* p, const vso_bvh* b, const float* normals16,
+                      const vso_material* mats, const vso_point_light* lights, void* color, int format,
+                      vso_counters* counters, int nthreads)
+{
+    frame_ctx f;
+    memset(&f, 0, sizeof(f));
+    f.p = p; f.b = b; f.normals = normals16; f.mats = mats; f.lights = lights;
+    f.rgba = (float*)color; f.color = color; f.color_format = format;
     vso_camera_basis(p, f.eye, f.cu, f.cv, f.cw);
     frame_run(&f, counters, nthreads);
 }

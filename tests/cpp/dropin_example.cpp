@@ -159,6 +159,24 @@ int main(int argc, char** argv)
         dev_depth_rt.download_depth(zback.data());
         if (std::memcmp(zback.data(), depth_rt.depth(), zback.size() * sizeof(float)) != 0) { std::cerr << "gpu depth != host depth\n"; return 2; }
 
+        // --- other colour formats: the same Whitted frame into PF_RGBA8 (host) and PF_RGB8 (device) targets ---
+        {
+            simple_buffer_rt<PF_RGBA8, PF_UNSPECIFIED> rt8;
+            rt8.resize(w, h);
+            auto sp8 = make_sched_params(pixel_sampler::uniform_type{}, cam, rt8);
+            b200_sched<ray> s8;
+            s8.set_reference_order(true);
+            s8.frame(kernel, sp8);
+            dump(out + "/frame_whitted_rgba8.bin", rt8.color(), size_t(w) * h);
+            gpu_buffer_rt<PF_RGB8, PF_UNSPECIFIED> rt3;
+            rt3.resize(w, h);
+            auto sp3b = make_sched_params(pixel_sampler::ssaa_type<2>{}, cam, rt3);
+            s8.frame(kernel, sp3b);
+            std::vector<unorm8x3> px(size_t(w) * h);
+            rt3.download(px.data());
+            dump(out + "/frame_whitted_ssaa2_rgb8.bin", px.data(), px.size());
+        }
+
         // --- kernel_params with a surface description (kernels.h:395-509): normals per vertex, colours per
         //     vertex, tex coords + one texture_ref per geom_id, generic_material list; Whitted, host target.
         //     The arrays are dumped so that the test can hand the same ones to the oracle. ---

@@ -57,6 +57,7 @@ def main():
     multi_hit_vectors()
     surface_vectors()
     sbvh_vectors()
+    format_vectors()
 
 
 def multi_hit_vectors():
@@ -86,6 +87,32 @@ def surface_vectors():
         out["tex_" + key] = np.stack([O.ref_tex2d(tex, float(s), float(t)) for s, t in st])
     np.savez_compressed(os.path.join(HERE, "golden_surface.npz"), **out)
     print("wrote golden_surface.npz")
+
+
+FORMAT_CASES = [(0, 0, 0), (1, 0, 0), (1, 4, 0), (3, 2, 1), (1, 5, 0)]     # (kernel, pixel sampler, material kind)
+
+
+def format_case(kernel, ps, mat, width=40, height=28):
+    sc = S.make_scene("cfg2_grid", 0.004)
+    fp = S.frame_params(kernel, width, height, (0.9, 0.75, 1.3), (0, 0, 0), pixel_sampler=ps, num_bounces=4,
+                        ambient=(1, 1, 1, 1) if kernel == 3 else (0.1, 0.1, 0.1, 1.0), bg=(0.1, 0.4, 1.0, 0.8))
+    return sc, fp, S.default_material(mat), S.point_light((0.4, 1.2, 0.6))
+
+
+def format_vectors():
+    """Frames into PF_RGBA8 / PF_RGB32F / PF_RGB8 targets through the reference's own pixel_access::store /
+    blend and colour conversion (3 accumulated frames for jittered_blend)."""
+    out = {}
+    for fmt in ("PF_RGBA8", "PF_RGB32F", "PF_RGB8"):
+        for kernel, ps, mat in FORMAT_CASES:
+            sc, fp, mats, light = format_case(kernel, ps, mat)
+            buf = O.format_buffer(fmt, fp.width, fp.height)
+            for fn in ((1, 2, 3) if ps == 2 else (1,)):
+                fp.frame_num = fn
+                O.ref_frame_format(sc, fp, mats, light, fmt, buf)
+            out[f"{fmt}_k{kernel}_ps{ps}"] = buf
+    np.savez_compressed(os.path.join(HERE, "golden_formats.npz"), **out)
+    print("wrote golden_formats.npz")
 
 
 def sbvh_scene_prims():
@@ -125,5 +152,7 @@ if __name__ == "__main__":
         surface_vectors()
     elif len(sys.argv) > 1 and sys.argv[1] == "sbvh":
         sbvh_vectors()
+    elif len(sys.argv) > 1 and sys.argv[1] == "formats":
+        format_vectors()
     else:
         main()

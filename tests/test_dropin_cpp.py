@@ -85,3 +85,12 @@ def test_dropin_program_matches_oracle(gpu):
         want_s = O.oracle_frame_surface(ss, fp, sd, mats, S.point_light(eye))
         got_s = np.fromfile(os.path.join(d, "surface_whitted.bin"), dtype=np.float32).reshape(120, 160, 4)
         assert float((np.abs(got_s - want_s).max(axis=2) > 1 / 255).mean()) == 0.0      # reference-order walk
+        # PF_RGBA8 host target and PF_RGB8 device target (SSAA 2x), reference-order walk: byte for byte
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
+        want8 = O.oracle_frame_format(sc, fp, S.default_material(0), S.point_light(eye), "PF_RGBA8")
+        got8 = np.fromfile(os.path.join(d, "frame_whitted_rgba8.bin"), dtype=np.uint8).reshape(120, 160, 4)
+        assert int(np.abs(got8.astype(np.int32) - want8.astype(np.int32)).max()) <= 1 and float((got8 != want8).mean()) <= 1e-3
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), pixel_sampler=3, num_bounces=4)
+        want3 = O.oracle_frame_format(sc, fp, S.default_material(0), S.point_light(eye), "PF_RGB8")
+        got3 = np.fromfile(os.path.join(d, "frame_whitted_ssaa2_rgb8.bin"), dtype=np.uint8).reshape(120, 160, 3)
+        assert int(np.abs(got3.astype(np.int32) - want3.astype(np.int32)).max()) <= 1 and float((got3 != want3).mean()) <= 1e-3

@@ -63,7 +63,7 @@ class FrameDesc(C.Structure):
         ("ray_count", C.c_void_p),
         ("params_mem", C.c_int32), ("tile_target", C.c_int32),
         ("camera_kind", C.c_int32), ("view_matrix", C.c_float * 16), ("proj_matrix", C.c_float * 16),
-        ("generic_materials", C.c_int32),
+        ("color_format", C.c_int32), ("generic_materials", C.c_int32),
     ]
 
 

@@ -418,6 +418,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     const size_t n_normals = scenes[0]->n_prims;
     fl.in_place = (nranks > 1 && d->tile_target == VSB_TILES_IN_PLACE) ? 1 : 0;
     if (fl.in_place && (d->mem != VSB_MEM_DEVICE || p.pixel_sampler == VSB_PS_JITTERED_BLEND)) return VSB_ERR_UNSUPPORTED;
+    if (d->color_format < VSB_PF_RGBA32F || d->color_format > VSB_PF_RGB8) return VSB_ERR_BAD_ARG;
+    if (d->color_format != VSB_PF_RGBA32F && nranks > 1 && !fl.in_place) return VSB_ERR_UNSUPPORTED;   // compact tile buffers + de-interleave are RGBA32F
+    const size_t bpp = d->color_format == VSB_PF_RGBA8 ? 4 : (d->color_format == VSB_PF_RGB8 ? 3 : 16);
     const size_t color_px = (nranks > 1 && !fl.in_place) ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
     unsigned long long* d_ray_count = nullptr;
     if (d->mem != VSB_MEM_HOST && d->mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
@@ -480,7 +483,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     else if (d->mem == VSB_MEM_HOST)
     {
         void* e;
-        rc = stage(5, color_px * 16 + 16, &e); if (rc) return rc;
+        rc = stage(5, color_px * bpp + 16, &e); if (rc) return rc;
         fl.color = reinterpret_cast<float4*>(e);
         if (d->depth)
         {
@@ -517,7 +520,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     if (d->mem == VSB_MEM_HOST && !direct_host)
     {
         // a band should carry >= 16 MiB of pixels: below that the per-launch ramps cost more than the overlap buys
-        const size_t by_size = (color_px * 16 >> 20) / (size_t)(g_band_min_mib < 1 ? 1 : g_band_min_mib);
+        const size_t by_size = (color_px * bpp >> 20) / (size_t)(g_band_min_mib < 1 ? 1 : g_band_min_mib);
         n_bands = g_frame_bands < 1 ? 1 : (g_frame_bands > 32 ? 32 : g_frame_bands);
         if ((size_t)n_bands > by_size) n_bands = by_size < 1 ? 1 : (int)by_size;
     }
@@ -540,7 +543,9 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     };
     // progressive blending: the accumulated frame lives with the caller; it is uploaded band by band
     // on its own stream (the H2D engine runs ahead of the trace, the D2H engine behind it)
-    const bool upload = d->mem == VSB_MEM_HOST && !direct_host && p.pixel_sampler == VSB_PS_JITTERED_BLEND;
+    // (a PF_RGB32F pixel has a 4th word the path never writes: it makes the same round trip)
+    const bool upload = d->mem == VSB_MEM_HOST && !direct_host &&
+                        (p.pixel_sampler == VSB_PS_JITTERED_BLEND || d->color_format == VSB_PF_RGB32F);
     if (upload)
     {
         VSB_CUDA(cudaEventRecord(g.band_fork, st));
@@ -551,8 +556,8 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
             {
                 size_t px0, px1;
                 unit_pixels(u, px0, px1);
-                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(fl.color) + px0 * 16, reinterpret_cast<const char*>(d->color) + px0 * 16,
-                                         (px1 - px0) * 16, cudaMemcpyHostToDevice, g.upload_stream));
+                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(fl.color) + px0 * bpp, reinterpret_cast<const char*>(d->color) + px0 * bpp,
+                                         (px1 - px0) * bpp, cudaMemcpyHostToDevice, g.upload_stream));
                 if (d->depth)
                     VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(fl.depth) + px0 * 4, reinterpret_cast<const char*>(d->depth) + px0 * 4,
                                              (px1 - px0) * 4, cudaMemcpyHostToDevice, g.upload_stream));
@@ -583,7 +588,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
 #define VSB_LAUNCH_FRAME(K, SS)                                                                                \
     do {                                                                                                     \
         vsb::FrameProgram<K, SS> prog;                                                                       \
-        prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; \
+        prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; prog.color_format = d->color_format; \
         prog.depth = fl.depth;                                                                               \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
@@ -594,7 +599,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         // extended instantiation: SSAA samplers, matrix camera, depth target (see shade.cuh)
         // ... and kernel_params with a surface description or a generic material list
         switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX ||
-                                 fl.ctx.surf.enabled || generic_materials) ? 1 : 0))
+                                 fl.ctx.surf.enabled || generic_materials || d->color_format != VSB_PF_RGBA32F) ? 1 : 0))
         {
         case 0: VSB_LAUNCH_FRAME(0, false); break;
         case 1: VSB_LAUNCH_FRAME(0, true); break;
@@ -618,8 +623,8 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
             {
                 size_t px0, px1;
                 unit_pixels(u, px0, px1);
-                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * 16, reinterpret_cast<const char*>(fl.color) + px0 * 16,
-                                         (px1 - px0) * 16, cudaMemcpyDeviceToHost, g.copy_stream));
+                VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->color) + px0 * bpp, reinterpret_cast<const char*>(fl.color) + px0 * bpp,
+                                         (px1 - px0) * bpp, cudaMemcpyDeviceToHost, g.copy_stream));
                 if (d->depth)
                     VSB_CUDA(cudaMemcpyAsync(reinterpret_cast<char*>(d->depth) + px0 * 4, reinterpret_cast<const char*>(fl.depth) + px0 * 4,
                                              (px1 - px0) * 4, cudaMemcpyDeviceToHost, g.copy_stream));

@@ -416,6 +416,70 @@ VSB_HD V3 material_sample_ext(const Material& m, const Surface& S, V3 n, V3 wo, 
     return v3(r.x * S.tex.x, r.y * S.tex.y, r.z * S.tex.z);
 }
 
+// ---- colour formats of the render target (pixel_access store / get, detail/color_conversion.h) ----
+VSB_HD uint32_t float_to_unorm8(float f)        // math/detail/unorm.inl:18-24, after the clamp of color_conversion.h:224
+{
+    f = f < 0.0f ? 0.0f : (f > 1.0f ? 1.0f : f);
+    return (uint32_t)((double)f * 255.0);
+}
+VSB_HD float unorm8_to_float(uint32_t u) { return (float)((double)(float)u / 255.0); }      // :26-31
+
+#if defined(__CUDACC__)
+__device__ __forceinline__ int pixel_bytes(int format) { return format == 1 ? 4 : (format == 3 ? 3 : 16); }
+
+// store(): RGBA -> RGB multiplies by alpha (color_conversion.h:231-247)
+__device__ inline void store_pixel(int format, void* base, size_t index, float4 c)
+{
+    if (format == 0) { reinterpret_cast<float4*>(base)[index] = c; return; }
+    if (format == 1)
+    {
+        reinterpret_cast<uchar4*>(base)[index] = make_uchar4((unsigned char)float_to_unorm8(c.x), (unsigned char)float_to_unorm8(c.y),
+                                                             (unsigned char)float_to_unorm8(c.z), (unsigned char)float_to_unorm8(c.w));
+        return;
+    }
+    const float r = rn_mul(c.x, c.w), g = rn_mul(c.y, c.w), b = rn_mul(c.z, c.w);
+    if (format == 2)
+    {
+        float* q = reinterpret_cast<float*>(base) + index * 4;       // 16-byte pixels, 4th word untouched
+        q[0] = r; q[1] = g; q[2] = b;
+        return;
+    }
+    unsigned char* q = reinterpret_cast<unsigned char*>(base) + index * 3;
+    q[0] = (unsigned char)float_to_unorm8(r); q[1] = (unsigned char)float_to_unorm8(g); q[2] = (unsigned char)float_to_unorm8(b);
+}
+
+// get(): RGB -> RGBA sets alpha 1 (color_conversion.h:249-265)
+__device__ inline float4 load_pixel(int format, const void* base, size_t index)
+{
+    if (format == 0) return reinterpret_cast<const float4*>(base)[index];
+    if (format == 1)
+    {
+        const uchar4 q = reinterpret_cast<const uchar4*>(base)[index];
+        return make_float4(unorm8_to_float(q.x), unorm8_to_float(q.y), unorm8_to_float(q.z), unorm8_to_float(q.w));
+    }
+    if (format == 2)
+    {
+        const float* q = reinterpret_cast<const float*>(base) + index * 4;
+        return make_float4(q[0], q[1], q[2], 1.0f);
+    }
+    const unsigned char* q = reinterpret_cast<const unsigned char*>(base) + index * 3;
+    return make_float4(unorm8_to_float(q[0]), unorm8_to_float(q[1]), unorm8_to_float(q[2]), 1.0f);
+}
+
+// what a pixel reads back as after it was stored: get(store(c)) without touching memory (the SSAA
+// accumulator of a formatted target lives in the lane state between sub-samples)
+__device__ inline float4 roundtrip_pixel(int format, float4 c)
+{
+    if (format == 0) return c;
+    if (format == 1)
+        return make_float4(unorm8_to_float(float_to_unorm8(c.x)), unorm8_to_float(float_to_unorm8(c.y)),
+                           unorm8_to_float(float_to_unorm8(c.z)), unorm8_to_float(float_to_unorm8(c.w)));
+    const float r = rn_mul(c.x, c.w), g = rn_mul(c.y, c.w), b = rn_mul(c.z, c.w);
+    if (format == 2) return make_float4(r, g, b, 1.0f);
+    return make_float4(unorm8_to_float(float_to_unorm8(r)), unorm8_to_float(float_to_unorm8(g)), unorm8_to_float(float_to_unorm8(b)), 1.0f);
+}
+#endif
+
 // ---- frame programs ------------------------------------------------------------------------------
 //
 // The built-in kernels as CONTINUATIONS around the persistent traversal loop (kernels.cuh,
@@ -463,7 +527,8 @@ struct FrameProgram
 {
     FrameCtx ctx;
     int scissor[4];
-    float4* color;
+    float4* color;                   // pixels of color_format (EXT; the lean instantiation is RGBA32F only)
+    int color_format;
     float* depth;                    // EXT only; may be null
     int tile_rank, tile_nranks;      // tile_nranks == 0: single rank, row-major target
     int tiles_x;
@@ -554,6 +619,7 @@ struct FrameProgram
             if ((int)k < num)
             {
                 L.f(W_DACC) = z;
+                if (color_format != 0) c = roundtrip_pixel(color_format, c);     // the target holds the stored value between blends
                 L.f(W_ACC + 0) = c.x; L.f(W_ACC + 1) = c.y; L.f(W_ACC + 2) = c.z; L.f(W_ACC + 3) = c.w;
                 L.u(W_SUB) = k;
                 const uint32_t pixel = L.u(W_PIX);
@@ -568,7 +634,7 @@ struct FrameProgram
         {
             const float alpha = rn_div(1.0f, (float)ctx.p.frame_num);
             const float ia = rn_sub(1.0f, alpha);
-            const float4 old = color[dst];
+            const float4 old = EXT ? load_pixel(color_format, color, dst) : color[dst];
             c.x = rn_add(rn_mul(c.x, alpha), rn_mul(old.x, ia));
             c.y = rn_add(rn_mul(c.y, alpha), rn_mul(old.y, ia));
             c.z = rn_add(rn_mul(c.z, alpha), rn_mul(old.z, ia));
@@ -576,7 +642,8 @@ struct FrameProgram
             if (EXT && depth) depth[dst] = rn_add(rn_mul(L.f(W_DEPTH), alpha), rn_mul(depth[dst], ia));
         }
         else if (EXT && depth) depth[dst] = L.f(W_DEPTH);
-        color[dst] = c;
+        if (EXT) store_pixel(color_format, color, dst, c);
+        else color[dst] = c;
         return false;
     }
     __device__ bool finish_bg(Lane& L, RayReq& req) const { return finish(L, ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3], req); }
@@ -618,7 +685,8 @@ struct FrameProgram
         if (EXT)
         {
             L.u(W_PIX) = pixel; L.u(W_SUB) = 0u;
-            L.f(W_ACC + 0) = 0.0f; L.f(W_ACC + 1) = 0.0f; L.f(W_ACC + 2) = 0.0f; L.f(W_ACC + 3) = 0.0f;
+            L.f(W_ACC + 0) = 0.0f; L.f(W_ACC + 1) = 0.0f; L.f(W_ACC + 2) = 0.0f;
+            L.f(W_ACC + 3) = color_format >= 2 ? 1.0f : 0.0f;        // a cleared RGB pixel reads back with alpha 1
             L.f(W_DACC) = 0.0f;
         }
         uint32_t samp = sampler_init(pixel, f.p.frame_num, f.p.seed);
@@ -640,8 +708,10 @@ struct FrameProgram
         if (KERNEL == 3 && f.p.num_bounces == 0u)
         {
             // no bounce is traced: every sample returns the background
-            color[L.u(W_DST)] = make_float4(f.p.bg[0], f.p.bg[1], f.p.bg[2], f.p.bg[3]);
-            if (EXT && depth) depth[L.u(W_DST)] = 1.0f;
+            RayReq unused;
+            L.u(W_PHASE) = PH_PRIMARY;
+            if (EXT) L.f(W_DEPTH) = 1.0f;
+            while (finish_bg(L, unused)) { }        // every (sub-)sample returns the background, stored / blended as usual
             return false;
         }
         start_sample(L, fx, fy, req);
