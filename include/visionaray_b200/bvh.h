@@ -244,6 +244,13 @@ inline void split_primitive(aabb& L, aabb& R, float plane, int axis, basic_spher
     }
 }
 
+// generic_primitive: the visitor forwards to the alternative (detail/generic_primitive.inl:72-128)
+inline void split_primitive(aabb& L, aabb& R, float plane, int axis, generic_triangle_sphere const& g)
+{
+    if (g.is_triangle()) split_primitive(L, R, plane, axis, g.as_triangle());
+    else                 split_primitive(L, R, plane, axis, g.as_sphere());
+}
+
 inline aabb intersect(aabb const& a, aabb const& b)      // math/detail/aabb.inl:168-173
 {
     aabb r; r.min = max(a.min, b.min); r.max = min(a.max, b.max);

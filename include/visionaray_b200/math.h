@@ -13,6 +13,7 @@
 #define VISIONARAY_B200_MATH_H 1
 
 #include <cfloat>
+#include <cstring>
 #include <cmath>
 #include <cstddef>
 #include <cstdint>
@@ -169,6 +170,44 @@ inline aabb get_bounds(basic_sphere<float> const& s)
     aabb b; b.invalidate();
     b.insert(s.center - vec3(s.radius)); b.insert(s.center + vec3(s.radius));
     return b;
+}
+
+// generic_primitive<basic_triangle<3,float>, basic_sphere<float>> (generic_primitive.h, variant.h): a
+// variant holding either; the alternative sits in place, its 1-based index follows at +64 (80 bytes,
+// 16-byte aligned -- the reference's layout, so arrays pass unchanged).  geom_id / prim_id are the first
+// two words of either alternative.
+template <typename ...Ts> class generic_primitive;
+
+template <>
+class alignas(16) generic_primitive<basic_triangle<3, float>, basic_sphere<float>>
+{
+public:
+    using triangle_type = basic_triangle<3, float>;
+    using sphere_type = basic_sphere<float>;
+
+    generic_primitive() { std::memset(this, 0, sizeof(*this)); }
+    generic_primitive(triangle_type const& t) { std::memset(this, 0, sizeof(*this)); std::memcpy(storage_, &t, sizeof(t)); which_ = 1; }
+    generic_primitive(sphere_type const& s)   { std::memset(this, 0, sizeof(*this)); std::memcpy(storage_, &s, sizeof(s)); which_ = 2; }
+
+    bool is_triangle() const { return which_ == 1; }
+    bool is_sphere() const { return which_ == 2; }
+    triangle_type const& as_triangle() const { return *reinterpret_cast<triangle_type const*>(storage_); }
+    sphere_type const& as_sphere() const { return *reinterpret_cast<sphere_type const*>(storage_); }
+    unsigned geom_id() const { return reinterpret_cast<unsigned const*>(storage_)[0]; }
+    unsigned prim_id() const { return reinterpret_cast<unsigned const*>(storage_)[1]; }
+
+private:
+    alignas(16) unsigned char storage_[64];
+    unsigned which_;
+    unsigned pad_[3];
+};
+using generic_triangle_sphere = generic_primitive<basic_triangle<3, float>, basic_sphere<float>>;
+static_assert(sizeof(generic_triangle_sphere) == 80, "generic_primitive layout");
+
+// get_bounds through the visitor (detail/generic_primitive.inl:46-70)
+inline aabb get_bounds(generic_triangle_sphere const& g)
+{
+    return g.is_triangle() ? get_bounds(g.as_triangle()) : get_bounds(g.as_sphere());
 }
 
 } // namespace visionaray_b200

@@ -55,6 +55,7 @@ inline void ensure_init()
 template <typename P> struct prim_kind;
 template <> struct prim_kind<basic_triangle<3, float>> { static const int value = VSB_PRIM_TRIANGLE; };
 template <> struct prim_kind<basic_sphere<float>> { static const int value = VSB_PRIM_SPHERE; };
+template <> struct prim_kind<generic_triangle_sphere> { static const int value = VSB_PRIM_GENERIC; };
 } // namespace detail
 
 //-------------------------------------------------------------------------------------------------

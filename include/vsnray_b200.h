@@ -45,6 +45,15 @@ typedef struct vsb_sphere {
     float radius; float pad2[3];
 } vsb_sphere;
 
+/* generic_primitive<basic_triangle<3,float>, basic_sphere<float>> (generic_primitive.h, variant.h): the
+ * alternative stored in place, then its 1-based index (1 triangle, 2 sphere).  80 B, 16-byte aligned.
+ * A leaf of such a tree mixes both kinds; intersect() dispatches on `which` (detail/generic_primitive.inl:20-44). */
+typedef struct vsb_generic_primitive {
+    uint32_t storage[16];      /* a vsb_triangle, or a vsb_sphere in the first 48 bytes */
+    uint32_t which;
+    uint32_t pad[3];
+} vsb_generic_primitive;
+
 /* bvh_node: bvh.h:52-119. inner <=> num_prims == 0; children at first, first+1. 32 B. */
 typedef struct vsb_bvh_node {
     float    bbox_min[3];
@@ -117,7 +126,7 @@ typedef struct vsb_surface_desc {
     const vsb_texture* textures;  /* n_textures entries, indexed by geom_id (geom_id >= n_textures: no texture) */
     int32_t n_textures;
 } vsb_surface_desc;
-enum { VSB_PRIM_TRIANGLE = 0, VSB_PRIM_SPHERE = 1 };
+enum { VSB_PRIM_TRIANGLE = 0, VSB_PRIM_SPHERE = 1, VSB_PRIM_GENERIC = 2 };
 enum { VSB_KERNEL_SIMPLE = 0, VSB_KERNEL_WHITTED = 1, VSB_KERNEL_AO = 2, VSB_KERNEL_PATHTRACING = 3 };
 enum { VSB_PS_UNIFORM = 0, VSB_PS_JITTERED = 1, VSB_PS_JITTERED_BLEND = 2,
        VSB_PS_SSAA2 = 3, VSB_PS_SSAA4 = 4, VSB_PS_SSAA8 = 5 };   /* ssaa_type<2|4|8>, detail/sched_common.h:222-295,640-698 */

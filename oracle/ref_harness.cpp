@@ -39,6 +39,7 @@
 #include <visionaray/sampling.h>
 #include <visionaray/get_normal.h>
 #include <visionaray/generic_material.h>
+#include <visionaray/generic_primitive.h>
 #include <visionaray/texture/texture.h>
 
 using namespace visionaray;
@@ -51,6 +52,7 @@ using sph_t     = basic_sphere<float>;
 using ray_t     = basic_ray<float>;
 using tri_ref_t = index_bvh<tri_t>::bvh_ref;
 using sph_ref_t = index_bvh<sph_t>::bvh_ref;
+using gen_t     = generic_primitive<tri_t, sph_t>;      // 80 bytes: the alternative in place, its 1-based index at +64
 
 // Layout shared with include/vsnray_b200.h (vsb_hit).
 struct hit32
@@ -244,6 +246,8 @@ int ref_multi_hit(int prim_kind, int n,
                   void const* prims2, size_t n_prims2, void const* nodes2, size_t n_nodes2, uint32_t const* indices2, size_t n_idx2,
                   void const* rays, size_t n_rays, void* hits_out, int nthreads)
 {
+    if (prim_kind == 2)
+        return multi_dispatch<gen_t>(n, prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, (hit32*)hits_out, nthreads);
     if (prim_kind == 0)
         return multi_dispatch<tri_t>(n, prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, (hit32*)hits_out, nthreads);
     return multi_dispatch<sph_t>(n, prims, n_prims, nodes, n_nodes, indices, n_idx, prims2, n_prims2, nodes2, n_nodes2, indices2, n_idx2, rays, n_rays, (hit32*)hits_out, nthreads);
@@ -283,13 +287,38 @@ int ref_build_spheres(void const* prims, size_t n, int spatial_splits,
     return build_impl<sph_t>(prims, n, spatial_splits, nodes_out, nodes_cap, n_nodes, idx_out, idx_cap, n_idx);
 }
 
-// prim_kind: 0 triangles, 1 spheres.  any: 0 closest-hit, 1 any-hit.
+int ref_build_generic(void const* prims, size_t n, int spatial_splits,
+                      void* nodes_out, size_t nodes_cap, size_t* n_nodes,
+                      uint32_t* idx_out, size_t idx_cap, size_t* n_idx)
+{
+    return build_impl<gen_t>(prims, n, spatial_splits, nodes_out, nodes_cap, n_nodes, idx_out, idx_cap, n_idx);
+}
+
+// generic_primitive<triangle, sphere> records from a tag array (0 triangle, 1 sphere) and the two payloads
+// (64-byte triangle / 48-byte sphere per entry, the unused one ignored): the reference's own constructors
+// decide the memory layout.  out: n * sizeof(gen_t) bytes.  Returns sizeof(gen_t).
+int ref_make_generic(int const* tags, void const* tris, void const* sphs, size_t n, void* out)
+{
+    auto t = reinterpret_cast<tri_t const*>(tris);
+    auto s = reinterpret_cast<sph_t const*>(sphs);
+    if (out)
+    {
+        std::memset(out, 0, n * sizeof(gen_t));
+        auto o = reinterpret_cast<gen_t*>(out);
+        for (size_t i = 0; i < n; ++i) { if (tags[i] == 0) o[i] = gen_t(t[i]); else o[i] = gen_t(s[i]); }
+    }
+    return int(sizeof(gen_t));
+}
+
+// prim_kind: 0 triangles, 1 spheres, 2 generic_primitive<triangle, sphere>.  any: 0 closest-hit, 1 any-hit.
 void ref_query(int prim_kind, int any,
                void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
                uint32_t const* indices, size_t n_idx, void const* rays, size_t n_rays,
                float max_t, float const* max_t_per_ray, void* hits_out, int nthreads)
 {
-    if (prim_kind == 0)
+    if (prim_kind == 2)
+        query_impl<gen_t>(any, prims, n_prims, nodes, n_nodes, indices, n_idx, rays, n_rays, max_t, max_t_per_ray, (hit32*)hits_out, nthreads);
+    else if (prim_kind == 0)
         query_impl<tri_t>(any, prims, n_prims, nodes, n_nodes, indices, n_idx, rays, n_rays, max_t, max_t_per_ray, (hit32*)hits_out, nthreads);
     else
         query_impl<sph_t>(any, prims, n_prims, nodes, n_nodes, indices, n_idx, rays, n_rays, max_t, max_t_per_ray, (hit32*)hits_out, nthreads);

@@ -125,14 +125,24 @@ void vso_intersect_sphere(const vso_ray* r, const vso_sphere* s, vso_hit* out)
     out->t = valid ? (t1 > t2 ? t2 : t1) : -1.0f;
 }
 
+/* intersect(ray, generic_primitive<triangle, sphere>) -- detail/generic_primitive.inl:20-44: the visitor
+ * calls intersect() of the alternative the variant holds (which = 1-based index, variant.h) */
+void vso_intersect_generic(const vso_ray* r, const vso_generic_primitive* g, vso_hit* out)
+{
+    if (g->which == 1) vso_intersect_triangle(r, (const vso_triangle*)g->storage, out);
+    else               vso_intersect_sphere(r, (const vso_sphere*)g->storage, out);
+}
+
 static inline void isect_prim(const vso_ray* r, const vso_bvh* b, uint32_t i, vso_hit* hr)
 {
     /* index_bvh: primitive(i) = prims[indices[i]] (bvh.h:226-229); bvh: prims[i] (:177-180) */
     uint32_t p = b->indices ? b->indices[i] : i;
     if (b->prim_kind == 0)
         vso_intersect_triangle(r, (const vso_triangle*)b->prims + p, hr);
-    else
+    else if (b->prim_kind == 1)
         vso_intersect_sphere(r, (const vso_sphere*)b->prims + p, hr);
+    else
+        vso_intersect_generic(r, (const vso_generic_primitive*)b->prims + p, hr);
     hr->prim_list_index = i;   /* HR(isect(ray, prim), i), detail/bvh/intersect.inl:112 */
 }
 
@@ -445,8 +455,9 @@ static void brute_range(size_t b, size_t e, void* p, vso_counters* c)
         hit_init(&result);
         for (size_t k = 0; k < q->n_prims; ++k)
         {
-            if (q->prim_kind == 0) vso_intersect_triangle(&q->rays[i], (const vso_triangle*)q->prims + k, &hr);
-            else                   vso_intersect_sphere(&q->rays[i], (const vso_sphere*)q->prims + k, &hr);
+            if (q->prim_kind == 0)      vso_intersect_triangle(&q->rays[i], (const vso_triangle*)q->prims + k, &hr);
+            else if (q->prim_kind == 1) vso_intersect_sphere(&q->rays[i], (const vso_sphere*)q->prims + k, &hr);
+            else                        vso_intersect_generic(&q->rays[i], (const vso_generic_primitive*)q->prims + k, &hr);
             hr.prim_list_index = (uint32_t)k;
             if (hr.hit && hr.t >= 0.0f && hr.t < result.t && hr.t < q->max_t)
             {

@@ -28,6 +28,9 @@ extern "C" {
 typedef struct { float ori[3]; float pad0; float dir[3]; float pad1; } vso_ray;
 typedef struct { uint32_t geom_id, prim_id, pad0[2]; float v1[3], pad1, e1[3], pad2, e2[3], pad3; } vso_triangle;
 typedef struct { uint32_t geom_id, prim_id, pad0[2]; float center[3], pad1, radius, pad2[3]; } vso_sphere;
+/* generic_primitive<basic_triangle<3,float>, basic_sphere<float>> (generic_primitive.h, variant.h): the
+ * alternative stored in place (64 bytes), then its 1-based index (1 triangle, 2 sphere); 80 bytes, 16-aligned */
+typedef struct { uint32_t storage[16]; uint32_t which; uint32_t pad[3]; } vso_generic_primitive;
 typedef struct { float bbox_min[3]; uint32_t first; float bbox_max[3]; uint32_t num_prims; } vso_bvh_node;
 typedef struct { int32_t hit; uint32_t prim_id, geom_id; float t, u, v; uint32_t prim_list_index, pad; } vso_hit;
 /* kind 0 plastic, 1 matte (as before); 2 emissive: cd = ce, kd = ls (material.h emissive<T>);
@@ -52,7 +55,7 @@ typedef struct {
 } vso_frame_params;
 
 typedef struct {
-    int prim_kind;                 /* 0 triangles, 1 spheres */
+    int prim_kind;                 /* 0 triangles, 1 spheres, 2 generic_primitive<triangle, sphere> */
     const void* prims; size_t n_prims;
     const vso_bvh_node* nodes; size_t n_nodes;
     const uint32_t* indices; size_t n_indices;   /* NULL: primitive(i) = prims[i] (bvh.h:177-180) */
@@ -66,6 +69,7 @@ typedef struct { uint64_t n_inner, n_prim, n_rays, n_hits; } vso_counters;
 /* primitives (math/intersect.h) */
 void vso_intersect_triangle(const vso_ray* r, const vso_triangle* tri, vso_hit* out);
 void vso_intersect_sphere(const vso_ray* r, const vso_sphere* s, vso_hit* out);
+void vso_intersect_generic(const vso_ray* r, const vso_generic_primitive* g, vso_hit* out);
 int  vso_intersect_aabb(const vso_ray* r, const float bmin[3], const float bmax[3],
                         const float inv_dir[3], float* tnear, float* tfar);
 

@@ -80,7 +80,7 @@ void* hs_build(int prim_kind, const void* prims, size_t n_prims, const void* nod
         ++w->levels;
     }
     w->nodes.resize(node_count);
-    size_t rec = prim_kind == 0 ? sizeof(TriRec) : sizeof(SphRec);
+    size_t rec = (size_t)wide_rec_words16(prim_kind) * 16;
     w->prims.resize((size_t)prim_count * rec + 16);
     for (uint32_t i = 0; i < prim_count; ++i) make_prim_record(prim_kind, prims, indices, leaf_list[i], w->prims.data(), i);
     return w;
@@ -92,7 +92,7 @@ void hs_stats(void* h, uint64_t* out)
 {
     auto* w = reinterpret_cast<HostWide*>(h);
     out[0] = w->nodes.size();
-    out[1] = w->prims.size() / (w->prim_kind == 0 ? sizeof(TriRec) : sizeof(SphRec));
+    out[1] = w->prims.size() / ((size_t)wide_rec_words16(w->prim_kind) * 16);
     out[2] = (uint64_t)w->levels;
 }
 

@@ -84,9 +84,9 @@ VSB_HD float merged_half_area(const BNode& a, const BNode& b)
 VSB_HD BNode prim_bounds(int prim_kind, const void* prims, uint32_t i)
 {
     BNode b;
-    if (prim_kind == 0)
+    const float* p = reinterpret_cast<const float*>(reinterpret_cast<const char*>(prims) + (size_t)i * prim_stride(prim_kind));
+    if (prim_is_triangle(prim_kind, p))
     {
-        const float* p = reinterpret_cast<const float*>(reinterpret_cast<const char*>(prims) + (size_t)i * 64u);
         const float ax = p[4], ay = p[5], az = p[6];
         const float bx = rn_add(ax, p[8]),  by = rn_add(ay, p[9]),  bz = rn_add(az, p[10]);
         const float cx = rn_add(ax, p[12]), cy = rn_add(ay, p[13]), cz = rn_add(az, p[14]);
@@ -95,7 +95,6 @@ VSB_HD BNode prim_bounds(int prim_kind, const void* prims, uint32_t i)
     }
     else
     {
-        const float* p = reinterpret_cast<const float*>(reinterpret_cast<const char*>(prims) + (size_t)i * 48u);
         const float r = p[8];
         b.lox = rn_sub(p[4], r); b.loy = rn_sub(p[5], r); b.loz = rn_sub(p[6], r);
         b.hix = rn_add(p[4], r); b.hiy = rn_add(p[5], r); b.hiz = rn_add(p[6], r);

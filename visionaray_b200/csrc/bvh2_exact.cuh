@@ -80,9 +80,9 @@ VSB_HD void trace_exact(const ExactScene& s, float ox, float oy, float oz, float
             float t, u = 0.0f, v = 0.0f;
             uint32_t prim_id, geom_id;
             bool hit;
-            if (s.prim_kind == 0)
+            const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * prim_stride(s.prim_kind));
+            if (prim_is_triangle(s.prim_kind, q))
             {
-                const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * 64u);
 #if defined(__CUDA_ARCH__)
                 const float4 h = __ldg(q), a = __ldg(q + 1), b = __ldg(q + 2), c = __ldg(q + 3);
 #else
@@ -93,7 +93,6 @@ VSB_HD void trace_exact(const ExactScene& s, float ox, float oy, float oz, float
             }
             else
             {
-                const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * 48u);
 #if defined(__CUDA_ARCH__)
                 const float4 h = __ldg(q), a = __ldg(q + 1), b = __ldg(q + 2);
 #else

@@ -342,9 +342,18 @@ VSB_HD int collapse_node(const WideTask task, const Node32* __restrict__ nodes2,
 VSB_HD void make_prim_record(int prim_kind, const void* prims, const uint32_t* indices, uint32_t li, void* out, uint32_t slot)
 {
     const uint32_t p = indices ? indices[li] : li;
-    if (prim_kind == 0)
+    const uint32_t* src = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(prims) + (size_t)p * prim_stride(prim_kind));
+    if (prim_kind == 2 && !prim_is_triangle(prim_kind, src))
     {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(prims) + (size_t)p * 64u);
+        // a sphere among 48-byte records: sphere layout in words 0..7, tag in word 11
+        uint32_t* o = reinterpret_cast<uint32_t*>(reinterpret_cast<char*>(out) + (size_t)slot * 48u);
+        o[0] = src[4]; o[1] = src[5]; o[2] = src[6]; o[3] = src[8];
+        o[4] = src[1]; o[5] = src[0]; o[6] = li; o[7] = 0u;
+        o[8] = 0u; o[9] = 0u; o[10] = 0u; o[11] = VSB_GENERIC_SPHERE_TAG;
+        return;
+    }
+    if (prim_kind != 1)
+    {
         TriRec r;
         r.v1x = u2f(src[4]);  r.v1y = u2f(src[5]);  r.v1z = u2f(src[6]);  r.prim_id = src[1];
         r.e1x = u2f(src[8]);  r.e1y = u2f(src[9]);  r.e1z = u2f(src[10]); r.geom_id = src[0];
@@ -353,7 +362,6 @@ VSB_HD void make_prim_record(int prim_kind, const void* prims, const uint32_t* i
     }
     else
     {
-        const uint32_t* src = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(prims) + (size_t)p * 48u);
         SphRec r;
         r.cx = u2f(src[4]); r.cy = u2f(src[5]); r.cz = u2f(src[6]); r.radius = u2f(src[8]);
         r.prim_id = src[1]; r.geom_id = src[0]; r.list_index = li; r.pad = 0u;

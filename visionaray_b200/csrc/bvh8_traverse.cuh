@@ -161,7 +161,7 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
 // (update_if.h:50-56,75-79).  `limit` = min(result.t, max_t).
 VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg& best, float& limit)
 {
-    if (prim_kind == 0)
+    if (prim_kind == 0 || (prim_kind == 2 && !(n.w[11] & VSB_GENERIC_SPHERE_TAG)))
     {
         // TriRec: v1 | prim_id, e1 | geom_id, e2 | list_index
         float t = -1.0f, u = 0.0f, v = 0.0f;      // initialised: left undefined, u / v were kept in local memory across the early-outs
@@ -309,7 +309,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
     // does not spend a whole extra warp iteration before its next node visit.
     if (t.pg_mask)
     {
-        const int n16 = s.prim_kind == 0 ? 3 : 2;
+        const int n16 = wide_rec_words16(s.prim_kind);
 #if defined(__CUDA_ARCH__)
         const int n_enter = __popc(__activemask());
 #endif
@@ -359,7 +359,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         const int bit = find_msb(t.pg_mask);
         t.pg_mask &= ~(1u << bit);
         const uint32_t index = t.pg_base + (uint32_t)bit;
-        n16 = s.prim_kind == 0 ? 3 : 2;
+        n16 = wide_rec_words16(s.prim_kind);
         addr = reinterpret_cast<const char*>(s.prims) + (size_t)index * (size_t)(n16 * 16);
     }
     else
@@ -419,7 +419,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         t.pg_base = n.w[5]; t.pg_mask = ph;
         if (t.pg_mask)
         {
-            if (VSB_PREFETCH) prefetch_prims(s.prims, t.pg_base, t.pg_mask, s.prim_kind == 0 ? 48u : 32u);
+            if (VSB_PREFETCH) prefetch_prims(s.prims, t.pg_base, t.pg_mask, (uint32_t)wide_rec_words16(s.prim_kind) * 16u);
             return true;
         }
     }

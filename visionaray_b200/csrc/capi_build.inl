@@ -32,11 +32,11 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
 {
     int rc = require_init(); if (rc) return rc;
     if (!prims || !out || n_prims == 0) return VSB_ERR_BAD_ARG;
-    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE) return VSB_ERR_BAD_ARG;
+    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE && prim_kind != VSB_PRIM_GENERIC) return VSB_ERR_BAD_ARG;
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     if (n_prims >= 0x3fffffffull) return VSB_ERR_UNSUPPORTED;
     const uint32_t n = (uint32_t)n_prims;
-    const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
+    const size_t prim_bytes = vsb::prim_stride(prim_kind);
     cudaStream_t st = g.stream;
 
     vsb_scene* s = new vsb_scene();

@@ -234,7 +234,7 @@ namespace
 // <= 4 primitives per leaf).  On failure the caller destroys the scene.
 int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size_t list_len)
 {
-    const size_t rec_bytes = s->prim_kind == VSB_PRIM_TRIANGLE ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec);
+    const size_t rec_bytes = (size_t)vsb::wide_rec_words16(s->prim_kind) * 16;
     uint32_t* d_leaf_list = nullptr; vsb::WideTask* d_tasks[2] = { nullptr, nullptr }; uint32_t* d_counters = nullptr;
     uint32_t* d_parent = nullptr; uint32_t* d_arrived = nullptr; vsb::CollapseCost* d_cost = nullptr; vsb::CollapseDec* d_dec = nullptr;
     vsb::Node80* d_wide_tmp = nullptr;     // encoded into scratch of the worst-case size, then copied to an exact-size array
@@ -317,7 +317,7 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
 {
     int rc = require_init(); if (rc) return rc;
     if (!prims || !nodes || !out || n_prims == 0 || n_nodes == 0) return VSB_ERR_BAD_ARG;
-    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE) return VSB_ERR_BAD_ARG;
+    if (prim_kind != VSB_PRIM_TRIANGLE && prim_kind != VSB_PRIM_SPHERE && prim_kind != VSB_PRIM_GENERIC) return VSB_ERR_BAD_ARG;
     if (n_nodes >= 0x7fffffffull || n_prims >= 0x7fffffffull) return VSB_ERR_UNSUPPORTED;
 
     bool big = false;
@@ -329,7 +329,7 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
     s->prim_kind = prim_kind; s->n_prims = n_prims; s->n_nodes2 = n_nodes; s->n_idx = indices ? n_indices : 0;
     s->depth2 = depth;
     for (int i = 0; i < 3; ++i) { s->lo[i] = nodes[0].bbox_min[i]; s->hi[i] = nodes[0].bbox_max[i]; }
-    const size_t prim_bytes = prim_kind == VSB_PRIM_TRIANGLE ? 64 : 48;
+    const size_t prim_bytes = vsb::prim_stride(prim_kind);
     const size_t list_len = indices ? n_indices : n_prims;
 
 #define VSB_SCENE_CUDA(expr) do { cudaError_t e__ = (expr); if (e__ != cudaSuccess) { vsb_scene_destroy(s); return (int)e__; } } while (0)
@@ -462,7 +462,7 @@ extern "C" int vsb_scene_stats(const vsb_scene* s, uint64_t* out, int n)
 {
     if (!s || !out) return VSB_ERR_BAD_ARG;
     uint64_t v[6] = { s->n_wide, (uint64_t)s->n_wide * sizeof(vsb::Node80), s->n_wide_prims,
-                      (uint64_t)s->n_wide_prims * (s->prim_kind == 0 ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec)),
+                      (uint64_t)s->n_wide_prims * ((size_t)vsb::wide_rec_words16(s->prim_kind) * 16),
                       (uint64_t)s->depth2, (uint64_t)s->n_nodes2 };
     for (int i = 0; i < n && i < 6; ++i) out[i] = v[i];
     if (n > 6) out[6] = (uint64_t)s->levels;
@@ -474,7 +474,7 @@ extern "C" int vsb_scene_download_wide(const vsb_scene* s, void* nodes_out, size
 {
     if (!s) return VSB_ERR_BAD_ARG;
     const size_t nb = (size_t)s->n_wide * sizeof(vsb::Node80);
-    const size_t pb = (size_t)s->n_wide_prims * (s->prim_kind == 0 ? sizeof(vsb::TriRec) : sizeof(vsb::SphRec));
+    const size_t pb = (size_t)s->n_wide_prims * ((size_t)vsb::wide_rec_words16(s->prim_kind) * 16);
     if (nodes_out) { if (node_bytes_cap < nb) return VSB_ERR_BAD_ARG; VSB_CUDA(cudaMemcpy(nodes_out, s->d_wide, nb, cudaMemcpyDeviceToHost)); }
     if (prims_out) { if (prim_bytes_cap < pb) return VSB_ERR_BAD_ARG; VSB_CUDA(cudaMemcpy(prims_out, s->d_wide_prims, pb, cudaMemcpyDeviceToHost)); }
     return VSB_OK;

@@ -79,6 +79,14 @@ int vsbh_build_bvh_ex(int prim_kind, const void* prims, size_t n, int spatial_sp
             std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
             std::memcpy(idx_out, t.indices().data(), *n_idx * sizeof(uint32_t));
         }
+        else if (prim_kind == 2)
+        {
+            auto t = build<index_bvh<generic_triangle_sphere>>(reinterpret_cast<generic_triangle_sphere const*>(prims), n, spatial_splits != 0);
+            *n_nodes = t.num_nodes(); *n_idx = t.num_indices();
+            if (*n_nodes > nodes_cap || *n_idx > idx_cap) return 1;
+            std::memcpy(nodes_out, t.nodes().data(), *n_nodes * sizeof(bvh_node));
+            std::memcpy(idx_out, t.indices().data(), *n_idx * sizeof(uint32_t));
+        }
         else
         {
             auto t = build<index_bvh<basic_sphere<float>>>(reinterpret_cast<basic_sphere<float> const*>(prims), n, spatial_splits != 0);

@@ -107,16 +107,15 @@ VSB_HD void multi_hit_exact(const ExactScene& s, float ox, float oy, float oz, f
             float t, u = 0.0f, v = 0.0f;
             uint32_t prim_id, geom_id;
             bool hit;
-            if (s.prim_kind == 0)
+            const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * prim_stride(s.prim_kind));
+            if (prim_is_triangle(s.prim_kind, q))
             {
-                const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * 64u);
                 const float4 h = q[0], a = q[1], b = q[2], c = q[3];
                 geom_id = f2u(h.x); prim_id = f2u(h.y);
                 hit = isect_triangle(ox, oy, oz, dx, dy, dz, a.x, a.y, a.z, b.x, b.y, b.z, c.x, c.y, c.z, t, u, v);
             }
             else
             {
-                const float4* q = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(s.prims) + (size_t)p * 48u);
                 const float4 h = q[0], a = q[1], b = q[2];
                 geom_id = f2u(h.x); prim_id = f2u(h.y);
                 hit = isect_sphere(ox, oy, oz, dx, dy, dz, a.x, a.y, a.z, b.x, t);
@@ -132,7 +131,7 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
     uint32_t sb[VSB_STACK_SIZE], sm[VSB_STACK_SIZE];
     int sp = 0;
     uint32_t ng_base = 0u, ng_mask = 0x80000000u, pg_base = 0u, pg_mask = 0u;     // the root as "child 31 of a virtual group"
-    const int n16 = s.prim_kind == 0 ? 3 : 2;
+    const int n16 = wide_rec_words16(s.prim_kind);
     NodeRegs n;
     for (;;)
     {
@@ -141,7 +140,7 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
             const int bit = find_msb(pg_mask);
             pg_mask &= ~(1u << bit);
             load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
-            if (s.prim_kind == 0)
+            if (s.prim_kind == 0 || (s.prim_kind == 2 && !(n.w[11] & VSB_GENERIC_SPHERE_TAG)))
             {
                 float t = -1.0f, u = 0.0f, v = 0.0f;
                 if (isect_triangle(r.ox, r.oy, r.oz, r.dx, r.dy, r.dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]),

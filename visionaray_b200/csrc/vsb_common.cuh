@@ -129,6 +129,21 @@ VSB_HD float u2f(uint32_t u)
 }
 
 // ---- hit record in registers -------------------------------------------------------------------
+// Primitive kinds (include/vsnray_b200.h VSB_PRIM_*): 0 basic_triangle (64 B), 1 basic_sphere (48 B),
+// 2 generic_primitive<basic_triangle, basic_sphere> (80 B: the alternative in place, then its 1-based
+// index at +64 -- generic_primitive.h, variant.h).  Every reader of the reference-layout array goes
+// through these two.
+VSB_HD uint32_t prim_stride(int kind) { return kind == 0 ? 64u : (kind == 1 ? 48u : 80u); }
+VSB_HD bool prim_is_triangle(int kind, const void* rec)
+{
+    return kind == 0 || (kind == 2 && reinterpret_cast<const uint32_t*>(rec)[16] == 1u);
+}
+// leaf-order records of the wide BVH: 48 B (3 x 128 bit) for triangles and for the generic kind, 32 B for
+// spheres.  In a generic scene a sphere keeps the 32-byte sphere layout in the first two words and
+// marks itself with bit 31 of word 11 (a triangle's list_index lives there, < 2^31).
+#define VSB_GENERIC_SPHERE_TAG 0x80000000u
+VSB_HD int wide_rec_words16(int kind) { return kind == 1 ? 2 : 3; }
+
 struct HitReg
 {
     float    t;          // FLT_MAX while no hit (math/intersect.h:95-103)
