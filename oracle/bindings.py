@@ -110,7 +110,7 @@ def ref_lib(fast: bool = False):
         lib = C.CDLL(path)
         vp, sz = C.c_void_p, C.c_size_t
         lib.ref_layout.argtypes = [C.POINTER(C.c_int)]
-        for f in (lib.ref_build_triangles, lib.ref_build_spheres):
+        for f in (lib.ref_build_triangles, lib.ref_build_spheres) + ((lib.ref_build_generic,) if hasattr(lib, "ref_build_generic") else ()):
             f.argtypes = [vp, sz, C.c_int, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
         lib.ref_query.argtypes = [C.c_int, C.c_int, vp, sz, vp, sz, vp, sz, vp, sz, C.c_float, vp, vp, C.c_int]
         lib.ref_frame.restype = C.c_double
@@ -313,11 +313,22 @@ def ref_build(prim_kind, prims, spatial_splits=False):
         [("bbox_min", "<f4", (3,)), ("first", "<u4"), ("bbox_max", "<f4", (3,)), ("num_prims", "<u4")]))
     idx = np.zeros(max(n, 1) * (4 if spatial_splits else 1), dtype=np.uint32)
     nn, ni = C.c_size_t(0), C.c_size_t(0)
-    f = lib.ref_build_triangles if prim_kind == 0 else lib.ref_build_spheres
+    f = lib.ref_build_triangles if prim_kind == 0 else (lib.ref_build_spheres if prim_kind == 1 else lib.ref_build_generic)
     rc = f(_p(prims), n, int(spatial_splits), _p(nodes), nodes.shape[0], C.byref(nn), _p(idx), idx.shape[0], C.byref(ni))
     if rc != 0:
         raise RuntimeError("ref_build: capacity")
     return nodes[: nn.value].copy(), idx[: ni.value].copy()
+
+
+def ref_make_generic(tags, tris, sphs):
+    """generic_primitive records built by the reference's own constructors (pins the 80-byte layout)."""
+    lib = ref_lib()
+    lib.ref_make_generic.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]
+    n = tags.shape[0]
+    size = lib.ref_make_generic(_p(tags), _p(tris), _p(sphs), n, None)
+    out = np.zeros((n, size // 4), dtype=np.float32)
+    lib.ref_make_generic(_p(tags), _p(tris), _p(sphs), n, _p(out))
+    return out
 
 
 def ref_query(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_per_ray=None, nthreads=0):

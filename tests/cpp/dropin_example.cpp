@@ -44,6 +44,22 @@ int main(int argc, char** argv)
             if (any_hit(r, refs, refs + 1, 0.5f).hit) { std::cerr << "any_hit max_t failed\n"; return 2; }
         }
 
+        // --- generic_primitive<triangle, sphere>: one tree, both kinds (src/examples/generic_primitive) ---
+        {
+            using generic_type = generic_primitive<basic_triangle<3, float>, basic_sphere<float>>;
+            triangle_type tri = scenes::make_tri(vec3(-1, -1, 1), vec3(1, -1, 1), vec3(1, 1, 1), 0, 0);
+            basic_sphere<float> sph(vec3(0.0f, 0.0f, -2.0f), 1.0f);
+            sph.prim_id = 1; sph.geom_id = 1;
+            std::vector<generic_type> gp = { generic_type(tri), generic_type(sph) };
+            auto gbvh = build<index_bvh<generic_type>>(gp.data(), gp.size());
+            b200_index_bvh<generic_type> d_gbvh(gbvh);
+            b200_bvh_ref grefs[1] = { d_gbvh.ref() };
+            auto h0 = closest_hit(ray(vec3(0.5f, -0.5f, 5.0f), vec3(0.0f, 0.0f, -1.0f)), grefs, grefs + 1);
+            auto h1 = closest_hit(ray(vec3(-0.5f, 0.5f, 5.0f), vec3(0.0f, 0.0f, -1.0f)), grefs, grefs + 1);
+            if (!h0.hit || h0.prim_id != 0 || h0.t != 4.0f) { std::cerr << "generic primitive: triangle known answer failed\n"; return 2; }
+            if (!h1.hit || h1.prim_id != 1 || !(h1.t > 6.29f && h1.t < 6.30f)) { std::cerr << "generic primitive: sphere known answer failed\n"; return 2; }
+        }
+
         // --- scene: UV sphere, binned-SAH index_bvh on the host, upload + GPU re-encode ---
         std::vector<triangle_type> tris;
         scenes::uv_sphere(tris, 50, 50, 1.0f);

@@ -58,6 +58,7 @@ def main():
     surface_vectors()
     sbvh_vectors()
     format_vectors()
+    generic_vectors()
 
 
 def multi_hit_vectors():
@@ -115,6 +116,25 @@ def format_vectors():
     print("wrote golden_formats.npz")
 
 
+def generic_vectors():
+    """index_bvh<generic_primitive<basic_triangle, basic_sphere>>: records laid out by the reference's own
+    constructors, tree by its builder, closest_hit / any_hit / multi_hit<8> records by its traversal."""
+    sc = S.make_scene("generic", 0.05)
+    w = sc.prims.view(np.uint32)
+    tags = (w[:, 16] == 2).astype(np.int32)
+    rec = O.ref_make_generic(tags, np.ascontiguousarray(sc.prims[:, :16]), np.ascontiguousarray(sc.prims[:, :12]))
+    nodes, idx = O.ref_build(2, sc.prims)
+    ref = S.HostScene(2, sc.prims, nodes, idx, None, "generic")
+    lo, hi = ref.bounds()
+    rays = S.random_rays(6000, 9, float(lo.min()) - 0.1, float(hi.max()) + 0.1)
+    out = {"ref_records": rec.view(np.uint32), "nodes": nodes.view(np.uint8), "indices": idx, "rays": rays,
+           "closest": O.ref_query(ref, rays, False, FLT_MAX).view(np.uint8),
+           "any": O.ref_query(ref, rays, True, 0.3).view(np.uint8),
+           "multi8": O.ref_multi_hit(ref, rays[:1500], 8).view(np.uint8)}
+    np.savez_compressed(os.path.join(HERE, "golden_generic.npz"), **out)
+    print("wrote golden_generic.npz:", sc.n_prims, "primitives,", int(tags.sum()), "spheres")
+
+
 def sbvh_scene_prims():
     """Long thin triangles (a soup stretched 30x along x): the case spatial splits exist for."""
     t = S.gen_triangles(5, 3000, 0, 31, 0.05).copy()
@@ -152,6 +172,8 @@ if __name__ == "__main__":
         surface_vectors()
     elif len(sys.argv) > 1 and sys.argv[1] == "sbvh":
         sbvh_vectors()
+    elif len(sys.argv) > 1 and sys.argv[1] == "generic":
+        generic_vectors()
     elif len(sys.argv) > 1 and sys.argv[1] == "formats":
         format_vectors()
     else:
