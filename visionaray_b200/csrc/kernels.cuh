@@ -146,7 +146,7 @@ __device__ __forceinline__ bool phase_runs(int phase_min, bool prim_mode)
 
 template <typename Program, bool EXACT>
 __global__ void __launch_bounds__(VSB_BLOCK, Program::MIN_BLOCKS)
-trace_kernel(const TraceLaunch tl, const Program prog)
+trace_kernel(const TraceLaunch tl, const __grid_constant__ Program prog)
 {
     extern __shared__ uint32_t lane_store_raw[];
     const unsigned lane = threadIdx.x & 31u;

@@ -311,7 +311,9 @@ __global__ void surface_geo_normals_kernel(const float4* __restrict__ ref_prims,
 }
 
 // get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530
-__device__ inline Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v)
+// (inlined at its single call site per program; as an out-of-line call -- measured -- the path tracer, which
+// evaluates it at every bounce, lost 18 %: the 10-word result goes through local memory)
+__device__ __forceinline__ Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v)
 {
     const SurfCtx& sf = f.surf;
     Surface S;
@@ -603,7 +605,20 @@ struct FrameProgram
     // ssaa<N>: clear, then N x { dst = src/N + dst } (detail/sched_common.h:640-698) -- the
     // accumulator lives in the lane state and the next sub-sample's primary ray is emitted.
     // Returns true when the pixel continues with another ray (req).
-    __device__ bool finish(Lane& L, float r, float g, float b, float a, RayReq& req) const
+    // finish() is reached from several places of a program.  In the EXT Whitted program its body (formats,
+    // SSAA resampling, depth) is ONE out-of-line copy: 6.6 k -> 4.8 k instructions, stall_no_instruction was on
+    // top of that kernel's profile (profiles/r1_surface_whitted_v0.txt); plain inputs 7.61 -> 7.13 ms, full
+    // surface 12.77 -> 11.55 ms on cfg2.  The path tracer measured 5 % slower that way and keeps it inline.
+    __device__ __noinline__ bool finish_ext(Lane& L, float r, float g, float b, float a, RayReq& req) const
+    {
+        return finish_body(L, r, g, b, a, req);
+    }
+    __device__ __forceinline__ bool finish(Lane& L, float r, float g, float b, float a, RayReq& req) const
+    {
+        if (EXT && KERNEL == 1) return finish_ext(L, r, g, b, a, req);
+        return finish_body(L, r, g, b, a, req);
+    }
+    __device__ __forceinline__ bool finish_body(Lane& L, float r, float g, float b, float a, RayReq& req) const
     {
         const size_t dst = L.u(W_DST);
         float4 c = make_float4(r, g, b, a);
