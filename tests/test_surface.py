@@ -104,6 +104,23 @@ def test_gpu_frames_match_oracle(gpu, name):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("name,ps", [("whitted_vertex_cvert_tex", 4), ("simple_face_tex_linear", 3), ("path_vertex_tex", 5)])
+def test_gpu_surface_with_ssaa(gpu, name, ps):
+    """Surface description AND an SSAA pixel sampler: the instantiation that carries both extensions."""
+    sc, fp, sd, mats, light = SC.case(name, 128, 96)
+    fp.pixel_sampler = ps
+    want = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    dev = gpu.Scene(sc)
+    try:
+        gpu.set_surface(dev, sd)
+        img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+        gpu.frame(dev, fp, None, mats, light, img, traverse=gpu.TRAVERSE_EXACT)
+        assert _frac_bad(img, want) <= (0.0 if fp.kernel in (0, 1) else 4e-3)
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
 def test_gpu_generic_materials_without_surface(gpu):
     """A generic_material list with the plain per-face normals (no vsb_scene_set_surface): device
     materials need the generic_materials flag, host materials are detected."""

@@ -1,5 +1,5 @@
 """Frame rate of the built-in kernels with and without a surface description on the
-cfg2 scene and view: plain (plastic, per-face normals, lean instantiation), the same inputs through the
+cfg2 scene and view: plain (plastic, per-face normals, lean instantiation), the same inputs through the SURF
 extended instantiation (generic material list), and the full surface (normals + colours per vertex,
 tex coords + RGBA8 textures, generic_material<emissive, matte, mirror, plastic>).  Device render target,
 CUDA events of the library around the launch.  Also: multi_hit<N> and split-tree rates on random rays.
@@ -45,7 +45,7 @@ for kernel, name in ((1, "whitted"), (3, "pathtracing"), (0, "simple")):
     r = {}
     api.set_surface(dev, None)
     r["plain"] = rate(fp, plastic, False)
-    r["plain_ext_instantiation"] = rate(fp, plastic, True)
+    r["plain_inputs_surf_instantiation"] = rate(fp, plastic, True)
     r["generic_materials"] = rate(fp, S.generic_materials(), True)
     # the face normal at all three vertices: the same rays as `plain`, so the difference is the surface fetch alone
     flat = S.SurfaceData(1, np.ascontiguousarray(np.repeat(sc.normals, 3, axis=0)))

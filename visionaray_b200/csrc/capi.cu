@@ -585,30 +585,39 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         const int tile_begin = n_bands == 1 ? 0 : band * unit_tiles;
         tl.n_items = (unsigned long long)(n_bands == 1 ? fl.n_owned_tiles : units_in_band * unit_tiles) * VSB_TILE * VSB_TILE;
         tl.work_counter = n_bands == 1 ? g.d_work : g.d_work + 2 + band;
-#define VSB_LAUNCH_FRAME(K, SS)                                                                                \
+#define VSB_LAUNCH_FRAME(K, SS, SF)                                                                                \
     do {                                                                                                     \
-        vsb::FrameProgram<K, SS> prog;                                                                       \
+        vsb::FrameProgram<K, SS, SF> prog;                                                                       \
         prog.ctx = fl.ctx; std::memcpy(prog.scissor, fl.scissor, sizeof(prog.scissor)); prog.color = fl.color; prog.color_format = d->color_format; \
         prog.depth = fl.depth;                                                                               \
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
         prog.unit_tiles = unit_tiles; prog.unit_stride = n_bands; prog.n_local_tiles = fl.n_owned_tiles;     \
-        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, true>(prog, tl, bs)));                   \
-        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS>, false>(prog, tl, bs)));                  \
+        if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS, SF>, true>(prog, tl, bs)));                   \
+        else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS, SF>, false>(prog, tl, bs)));                  \
     } while (0)
-        // extended instantiation: SSAA samplers, matrix camera, depth target (see shade.cuh)
-        // ... and kernel_params with a surface description or a generic material list
-        switch (p.kernel * 2 + ((p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX ||
-                                 fl.ctx.surf.enabled || generic_materials || d->color_format != VSB_PF_RGBA32F) ? 1 : 0))
+        // EXT instantiation: SSAA samplers, matrix camera, depth target, colour formats; SURF instantiation:
+        // kernel_params with a surface description or a generic material list (see shade.cuh)
         {
-        case 0: VSB_LAUNCH_FRAME(0, false); break;
-        case 1: VSB_LAUNCH_FRAME(0, true); break;
-        case 2: VSB_LAUNCH_FRAME(1, false); break;
-        case 3: VSB_LAUNCH_FRAME(1, true); break;
-        case 4: VSB_LAUNCH_FRAME(2, false); break;
-        case 5: VSB_LAUNCH_FRAME(2, true); break;
-        case 6: VSB_LAUNCH_FRAME(3, false); break;
-        default: VSB_LAUNCH_FRAME(3, true); break;
+            const bool ext = p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX || d->color_format != VSB_PF_RGBA32F;
+            const bool surf = p.kernel != VSB_KERNEL_AO && (fl.ctx.surf.enabled || generic_materials);
+            switch (p.kernel * 4 + (ext ? 2 : 0) + (surf ? 1 : 0))
+            {
+            case 0:  VSB_LAUNCH_FRAME(0, false, false); break;
+            case 1:  VSB_LAUNCH_FRAME(0, false, true); break;
+            case 2:  VSB_LAUNCH_FRAME(0, true, false); break;
+            case 3:  VSB_LAUNCH_FRAME(0, true, true); break;
+            case 4:  VSB_LAUNCH_FRAME(1, false, false); break;
+            case 5:  VSB_LAUNCH_FRAME(1, false, true); break;
+            case 6:  VSB_LAUNCH_FRAME(1, true, false); break;
+            case 7:  VSB_LAUNCH_FRAME(1, true, true); break;
+            case 8:  VSB_LAUNCH_FRAME(2, false, false); break;
+            case 10: VSB_LAUNCH_FRAME(2, true, false); break;
+            case 12: VSB_LAUNCH_FRAME(3, false, false); break;
+            case 13: VSB_LAUNCH_FRAME(3, false, true); break;
+            case 14: VSB_LAUNCH_FRAME(3, true, false); break;
+            default: VSB_LAUNCH_FRAME(3, true, true); break;
+            }
         }
 #undef VSB_LAUNCH_FRAME
         ++g.launches;

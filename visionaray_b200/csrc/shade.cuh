@@ -229,7 +229,7 @@ VSB_HD V3 material_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, ui
 
 // ---- get_surface() with bindings, colours and textures; generic_material -------------------------
 //
-// Used by the EXT instantiation of the frame programs (kernel_params that carry more than
+// Used by the SURF instantiations of the frame programs (kernel_params that carry more than
 // per-face normals and a plastic / matte list).  Normals and everything else that defines a ray
 // keep the reference's operation order with single roundings; so does the texture filter, because
 // its result is TRUNCATED to an integer texel value before normalisation (texture/detail/
@@ -524,7 +524,10 @@ enum { PH_PRIMARY = 0, PH_BOUNCE = 1, PH_SHADOW = 2 };
 // EXT = true is the instantiation for the less common sched_params: SSAA pixel samplers (sub-sample
 // accumulator in the lane state, resampling branch in finish()), the matrix camera and the depth
 // target.  The common case (camera basis, uniform / jittered samplers, colour only) runs the leaner one.
-template <int KERNEL, bool EXT>
+// SURF = true adds what the later make_kernel_params overloads carry: get_surface() with bindings, colours
+// and textures, and the generic material list.  Separate from EXT so that neither pays for the
+// other's code: these programs are instruction-fetch sensitive.
+template <int KERNEL, bool EXT, bool SURF = false>
 struct FrameProgram
 {
     FrameCtx ctx;
@@ -545,7 +548,7 @@ struct FrameProgram
 #endif
     static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
-    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (EXT ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
+    static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (SURF ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
 
     __device__ void closest(RayReq& r, V3 o, V3 d) const
     {
@@ -665,7 +668,7 @@ struct FrameProgram
 
     __device__ V3 ambient_term(const Material& m) const
     {
-        if (EXT && m.kind >= 2) return v3(0.0f, 0.0f, 0.0f);     // emissive / mirror: detail/material/{emissive,mirror}.inl:14-18
+        if (SURF && m.kind >= 2) return v3(0.0f, 0.0f, 0.0f);     // emissive / mirror: detail/material/{emissive,mirror}.inl:14-18
         const float aw = ctx.p.ambient[3];
         return v3(m.ca[0] * m.ka * (ctx.p.ambient[0] * aw), m.ca[1] * m.ka * (ctx.p.ambient[1] * aw), m.ca[2] * m.ka * (ctx.p.ambient[2] * aw));
     }
@@ -752,7 +755,7 @@ struct FrameProgram
         const Material m = f.materials[h.geom_id];
         V3 shaded = ambient_term(m);
         const V3 view = vneg(d);
-        if (EXT)
+        if (SURF)
         {
             const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
             const V3 n = vfaceforward(S.sn, view, S.gn);
@@ -778,7 +781,7 @@ struct FrameProgram
     }
 
     // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
-    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; EXT: the surface of the current hit,
+    // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; SURF: the surface of the current hit,
     // evaluated once -- shading normal (faceforwarded) 17..19, tex_color 20..22, reflection direction 23..25
     __device__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
     {
@@ -796,7 +799,7 @@ struct FrameProgram
                 const PointLight l = f.lights[light];
                 const V3 wi = vnormalize(vsub(ld3(l.pos), pos));
                 V3 c;
-                if (EXT)
+                if (SURF)
                 {
                     Surface S;
                     S.tex = L.ld(K0 + 20);
@@ -825,7 +828,7 @@ struct FrameProgram
             prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
             shaded = ambient_term(f.materials[geom_id]);
             L.st(K0 + 9, pos); L.st(K0 + 12, view); L.u(K0 + 15) = prim_id; L.u(K0 + 16) = geom_id;
-            if (EXT)
+            if (SURF)
             {
                 const Surface S = surface_at(f, prim_id, geom_id, h.list_index, h.u, h.v);
                 L.st(K0 + 17, vfaceforward(S.sn, view, S.gn)); L.st(K0 + 20, S.tex);
@@ -843,11 +846,11 @@ struct FrameProgram
         const float throughput = L.f(K0 + 6);
         V3 color = L.ld(K0 + 0);
         color = v3(color.x + shaded.x * throughput, color.y + shaded.y * throughput, color.z + shaded.z * throughput);
-        const float kr = EXT ? specular_kr(f.materials[geom_id])
+        const float kr = SURF ? specular_kr(f.materials[geom_id])
                              : ((f.materials[geom_id].kind == 0) ? 0.1f : 0.0f);   // specular_bounce, detail/whitted.inl:66-122
         if (kr > 0.0f)
         {
-            const V3 dir = EXT ? L.ld(K0 + 23) : vreflect(view, face_normal(prim_id));
+            const V3 dir = SURF ? L.ld(K0 + 23) : vreflect(view, face_normal(prim_id));
             closest(req, vadd(pos, vscale(dir, f.p.epsilon)), dir);
             L.st(K0 + 0, color); L.f(K0 + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
             return true;
@@ -914,7 +917,7 @@ struct FrameProgram
             float pdf = 0.0f;
             uint32_t samp = L.u(W_SAMP);
             V3 n, src;
-            if (EXT)
+            if (SURF)
             {
                 const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
                 n = vfaceforward(S.sn, view, S.gn);
@@ -928,7 +931,7 @@ struct FrameProgram
             }
             L.u(W_SAMP) = samp;
             if (pdf <= 0.0f) { dst = v3(0.0f, 0.0f, 0.0f); finished = true; }
-            else if (EXT && m.kind == 2)
+            else if (SURF && m.kind == 2)
             {
                 // has_emissive_material(surf): the path ends here with its throughput times ce * ls (detail/pathtracing.inl:93-104)
                 dst = v3(dst.x * src.x, dst.y * src.y, dst.z * src.z);
