@@ -540,6 +540,21 @@ auto make_kernel_params(normals_per_face_binding, b200_bvh_ref const* begin, b20
                              surface_params{ false, 0, 0, nullptr, nullptr, nullptr, nullptr, 0 } };
 }
 
+// make_kernel_params(prims b/e, materials, lights b/e, ...)  kernels.h:328-366 -- no normals: the kernels take
+// get_normal(hr, primitive), i.e. normalize(cross(e1, e2)) for triangles and (isect_pos - center) / radius for
+// spheres; the form that works for a sphere bvh (simple / whitted kernels)
+template <typename Materials, typename = decltype(std::declval<Materials const&>()[0].flatten())>
+auto make_kernel_params(b200_bvh_ref const* begin, b200_bvh_ref const* end, Materials const& materials,
+                        point_light<float> const* lbegin, point_light<float> const* lend,
+                        unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
+                        vec4 const& ambient_color = vec4(0.0f))
+    -> kernel_params<typename std::decay<decltype(materials[0])>::type>
+{
+    using M = typename std::decay<decltype(materials[0])>::type;
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+                             surface_params{ true, VSB_NORMALS_FROM_PRIMITIVE, 0, nullptr, nullptr, nullptr, nullptr, 0 } };
+}
+
 // make_kernel_params(normals_per_vertex_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-393
 template <typename Materials>
 auto make_kernel_params(normals_per_vertex_binding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
@@ -848,7 +863,7 @@ public:
 
         std::vector<vsb_scene const*> scenes;
         for (auto it = kp.prims_begin; it != kp.prims_end; ++it) scenes.push_back(it->scene);
-        if (kp.surface.present && kp.surface.normals && !scenes.empty())
+        if (kp.surface.present && (kp.surface.normals || kp.surface.normal_binding == VSB_NORMALS_FROM_PRIMITIVE) && !scenes.empty())
         {
             std::vector<vsb_texture> texs;
             vsb_surface_desc sd = kp.surface.flatten(texs);

@@ -113,12 +113,16 @@ typedef struct vsb_texture {
 /* What get_surface() reads besides the hit record: the members of kernel_params beyond prims /
  * materials / lights (kernels.h:194-319) with their binding tags (tags.h).  vector<3,float> is
  * 16 bytes, vector<2,float> 8. */
-enum { VSB_NORMALS_PER_FACE = 0, VSB_NORMALS_PER_VERTEX = 1 };
+enum { VSB_NORMALS_PER_FACE = 0, VSB_NORMALS_PER_VERTEX = 1, VSB_NORMALS_FROM_PRIMITIVE = 2 };
 enum { VSB_COLORS_NONE = 0, VSB_COLORS_PER_FACE = 1, VSB_COLORS_PER_VERTEX = 2 };
 typedef struct vsb_surface_desc {
     int32_t normal_binding;       /* per face: normals[prim_id] (get_normal.h:28-37); per vertex: shading normal =
                                      normalize(lerp(normals[3 prim_id + 0..2], u, v)) (get_shading_normal.h:60-76),
-                                     geometric normal = normalize(cross(e1, e2)) (get_normal.h:96-101) */
+                                     geometric normal = normalize(cross(e1, e2)) (get_normal.h:96-101); from primitive =
+                                     kernel_params WITHOUT normals (the default make_kernel_params overload, kernels.h:328-366):
+                                     get_normal(hr, primitive) -- triangle normalize(cross(e1, e2)), sphere
+                                     (isect_pos - center) / radius (get_normal.h:96-118); `normals` may be NULL.  The
+                                     only binding of a sphere scene (frames: simple / whitted kernels) */
     int32_t color_binding;        /* colors[prim_id] or lerp(colors[3 prim_id + 0..2], u, v) (get_color.h:24-58) */
     const float* normals;         /* n_prims (per face) or 3 n_prims (per vertex) x 16 B */
     const float* colors;          /* like normals; NULL with VSB_COLORS_NONE */

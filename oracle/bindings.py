@@ -54,7 +54,7 @@ def make_surface(sd):
     """visionaray_b200.scenes.SurfaceData -> (Surface, keepalive)."""
     s = Surface()
     s.normal_binding, s.color_binding = sd.normal_binding, sd.color_binding
-    s.normals = sd.normals.ctypes.data
+    s.normals = sd.normals.ctypes.data if sd.normals is not None else None
     s.colors = sd.colors.ctypes.data if sd.colors is not None else None
     s.tex_coords = sd.tex_coords.ctypes.data if sd.tex_coords is not None else None
     texs = None
@@ -261,6 +261,22 @@ def ref_frame_surface(scene, fp, surface, materials, lights, rgba=None, nthreads
     del keep
     if rc != 0:
         raise ValueError("ref_frame_surface: unsupported kernel")
+    return rgba
+
+
+def ref_frame_prim_normals(scene, fp, materials, lights, rgba=None, nthreads=0):
+    """The reference kernels with kernel_params that carry NO normals (default make_kernel_params overload):
+    the normal comes from the primitive.  Triangle and sphere scenes; simple / whitted (+ pathtracing for triangles)."""
+    if rgba is None:
+        rgba = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+    lib = ref_lib()
+    lib.ref_frame_prim_normals.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p, C.c_size_t, C.c_void_p,
+                                           C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
+    rc = lib.ref_frame_prim_normals(scene.prim_kind, C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes),
+                                    scene.nodes.shape[0], _p(scene.indices), scene.indices.shape[0], _p(materials), _p(lights),
+                                    _p(rgba), nthreads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError("ref_frame_prim_normals: unsupported kernel / primitive kind")
     return rgba
 
 

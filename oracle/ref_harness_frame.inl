@@ -373,6 +373,43 @@ void run_surface_kernels(KP kparams, frame_params const& fp, float* rgba, int nt
     }
 }
 
+// kernel_params WITHOUT normals (the default make_kernel_params overload, kernels.h:328-366): the normal comes from
+// the primitive -- get_normal(hr, triangle | sphere | generic_primitive) -- for any primitive type
+template <typename P>
+int frame_prim_normals(frame_params const& fp, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                       uint32_t const* indices, size_t n_idx, void const* mats_, void const* lights_, float* rgba, int nthreads)
+{
+    auto ref = make_ref<P>(prims, n_prims, nodes, n_nodes, indices, n_idx);
+    scene_host s{ tri_ref_t() };
+    fill_scene(s, fp, nullptr, 0, (mat_pod const*)mats_, (light_pod const*)lights_);
+    aligned_vector<gen_mat_t> mats;
+    for (int i = 0; i < fp.n_materials; ++i) mats.push_back(make_generic(((mat_pod const*)mats_)[i]));
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+    auto lb = s.lights.data();
+    auto le = s.lights.data() + s.lights.size();
+    run_surface_kernels(make_kernel_params(&ref, &ref + 1, mats.data(), lb, le, fp.num_bounces, fp.epsilon, bg, amb),
+                        fp, rgba, nthreads);
+    return 0;
+}
+
+} // namespace
+
+extern "C" int ref_frame_prim_normals(int prim_kind, void const* fp_, void const* prims, size_t n_prims, void const* nodes,
+                                      size_t n_nodes, uint32_t const* indices, size_t n_idx, void const* mats_,
+                                      void const* lights_, float* rgba, int nthreads)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    if (fp.kernel == 2) return -1;
+    if (fp.kernel == 3 && prim_kind != 0) return -1;     // pathtracing.inl reads isect_pos before it is set: triangles only
+    if (prim_kind == 0) return frame_prim_normals<tri_t>(fp, prims, n_prims, nodes, n_nodes, indices, n_idx, mats_, lights_, rgba, nthreads);
+    if (prim_kind == 1) return frame_prim_normals<sph_t>(fp, prims, n_prims, nodes, n_nodes, indices, n_idx, mats_, lights_, rgba, nthreads);
+    return -1;     // get_surface() does not instantiate for a generic_primitive without a normals array (get_surface.h:218-245)
+}
+
+namespace
+{
 } // namespace
 
 extern "C" void ref_tex2d(void const* tex_, float s, float t, float* out4)

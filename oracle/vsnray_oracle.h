@@ -132,7 +132,9 @@ typedef struct {
     int32_t address[2];     /* 0 Wrap, 1 Mirror, 2 Clamp (tex_address_mode; texture/detail/filter/common.h:24-48) */
 } vso_texture;
 typedef struct {
-    int32_t normal_binding;      /* 0 normals_per_face_binding: normals[prim_id]; 1 normals_per_vertex_binding:
+    int32_t normal_binding;      /* 2 = the params carry NO normals: get_normal(hr, primitive) -- triangle
+                                    normalize(cross(e1, e2)), sphere (isect_pos - center) / radius (get_normal.h:96-118);
+                                    0 normals_per_face_binding: normals[prim_id]; 1 normals_per_vertex_binding:
                                     shading normal = normalize(lerp(normals[3 prim_id + 0..2], u, v))
                                     (get_shading_normal.h:60-76), geometric normal = normalize(cross(e1, e2)) of
                                     primitive(primitive_list_index) (get_surface.h:285-328, get_normal.h:96-101) */

@@ -206,7 +206,31 @@ static v3 lerp3(v3 a, v3 b, v3 c, float u, float v)
 }
 
 /* get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530 */
-static void get_surface(const frame_ctx* f, const vso_hit* h, surf_t* S)
+/* get_normal(hr, primitive) -- the kernel_params carry no normals (kernels.h:94-140, 328-366):
+ * get_surface.h:133-150 -> get_normal.h:96-101 triangle normalize(cross(e1, e2)); :113-118 sphere
+ * (isect_pos - center) / radius; generic_primitive: the alternative's rule (detail/generic_primitive_get_normal.h) */
+static v3 primitive_normal(const vso_bvh* b, uint32_t list_index, v3 pos)
+{
+    size_t pi = b->indices ? b->indices[list_index] : list_index;
+    const void* rec; int tri;
+    if (b->prim_kind == 0)      { rec = (const vso_triangle*)b->prims + pi; tri = 1; }
+    else if (b->prim_kind == 1) { rec = (const vso_sphere*)b->prims + pi; tri = 0; }
+    else
+    {
+        const vso_generic_primitive* g = (const vso_generic_primitive*)b->prims + pi;
+        rec = g->storage; tri = g->which == 1;
+    }
+    if (tri)
+    {
+        const vso_triangle* t = (const vso_triangle*)rec;
+        return normalize(cross(ld3(t->e1), ld3(t->e2)));
+    }
+    const vso_sphere* sp = (const vso_sphere*)rec;
+    v3 d = sub(pos, ld3(sp->center));
+    return v3m(d.x / sp->radius, d.y / sp->radius, d.z / sp->radius);
+}
+
+static void get_surface(const frame_ctx* f, const vso_hit* h, v3 pos, surf_t* S)
 {
     const vso_surface* sf = f->surf;
     S->m = &f->mats[h->geom_id];
@@ -217,6 +241,7 @@ static void get_surface(const frame_ctx* f, const vso_hit* h, surf_t* S)
         return;
     }
     if (sf->normal_binding == 0) S->gn = S->sn = ld3(sf->normals + 4 * (size_t)h->prim_id);
+    else if (sf->normal_binding == 2) S->gn = S->sn = primitive_normal(f->b, h->prim_list_index, pos);
     else
     {
         /* params.prims.begin[i].primitive(hr.primitive_list_index), get_surface.h:313-327; bvh.h:226-229 */
@@ -266,7 +291,7 @@ static void kernel_simple(const frame_ctx* f, v3 o, v3 d, float out[4], vso_coun
     if (!h.hit) { memcpy(out, p->bg, 16); return; }
     v3 pos = add(o, scale(d, h.t));
     surf_t S;
-    get_surface(f, &h, &S);
+    get_surface(f, &h, pos, &S);
     v3 shaded = mul(ambient_of(S.m), rgb_of_rgba(p->ambient));
     v3 view = neg(d);
     v3 n = faceforward(S.sn, view, S.gn);
@@ -294,7 +319,7 @@ static void kernel_whitted(const frame_ctx* f, v3 o, v3 d, float out[4], vso_cou
     {
         v3 pos = add(o, scale(d, h.t));
         surf_t S;
-        get_surface(f, &h, &S);
+        get_surface(f, &h, pos, &S);
         const vso_material* m = S.m;
         v3 sn = S.sn;
         v3 shaded = mul(ambient_of(m), rgb_of_rgba(p->ambient));
@@ -459,7 +484,10 @@ static void kernel_pathtracing(const frame_ctx* f, v3 o, v3 d, uint32_t* samp, f
 
         v3 view = neg(d);
         surf_t S;
-        get_surface(f, &h, &S);
+        /* hit_rec.isect_pos is assigned only AFTER get_surface() here (detail/pathtracing.inl:74,107): a sphere's
+         * normal (isect_pos - center) / radius would read an unset position in the reference, so binding 2 is
+         * restricted to triangle scenes for this kernel (vsb_frame returns VSB_ERR_UNSUPPORTED otherwise) */
+        get_surface(f, &h, add(o, scale(d, h.t)), &S);
         v3 n = faceforward(S.sn, view, S.gn);
         v3 refl = v3m(0.0f, 0.0f, 0.0f); float pdf = 0.0f;
         v3 src = material_sample(&S, n, view, &refl, &pdf, samp);

@@ -175,6 +175,27 @@ int main(int argc, char** argv)
         dev_depth_rt.download_depth(zback.data());
         if (std::memcmp(zback.data(), depth_rt.depth(), zback.size() * sizeof(float)) != 0) { std::cerr << "gpu depth != host depth\n"; return 2; }
 
+        // --- a sphere bvh rendered with kernel_params that carry no normals (get_normal(hr, sphere)) ---
+        {
+            std::vector<basic_sphere<float>> balls(64);
+            for (size_t i = 0; i < balls.size(); ++i)
+            {
+                balls[i] = basic_sphere<float>(vec3(-1.4f + 0.4f * float(i % 8), -1.4f + 0.4f * float(i / 8), 0.1f * float(i % 3)), 0.17f);
+                balls[i].prim_id = unsigned(i); balls[i].geom_id = 0;
+            }
+            auto sb = build<index_bvh<basic_sphere<float>>>(balls.data(), balls.size());
+            b200_index_bvh<basic_sphere<float>> d_sb(sb);
+            b200_bvh_ref sp[1] = { d_sb.ref() };
+            auto skp = make_kernel_params(sp, sp + 1, materials, lights.data(), lights.data() + lights.size(), 4, 1e-3f,
+                                          vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(0.0f));
+            whitted::kernel<decltype(skp)> sk{ skp };
+            b200_sched<ray> s2;
+            s2.set_reference_order(true);
+            s2.frame(sk, sparams);
+            dump(out + "/frame_spheres.bin", host_rt.color(), size_t(w) * h);
+            dump(out + "/spheres.bin", balls.data(), balls.size());
+        }
+
         // --- other colour formats: the same Whitted frame into PF_RGBA8 (host) and PF_RGB8 (device) targets ---
         {
             simple_buffer_rt<PF_RGBA8, PF_UNSPECIFIED> rt8;

@@ -84,6 +84,10 @@ def surface_vectors():
     for name in SC.CASES:
         sc, fp, sd, mats, light = SC.case(name)
         out[name] = O.ref_frame_surface(sc, fp, sd, mats, light)
+    import test_surface as TS
+    for name, kernel in TS.PRIM_NORMAL_CASES:            # kernel_params without normals, triangle and sphere scenes
+        sc, fp, sd, mats, light = TS.prim_normal_frame(name, kernel, 40, 28)
+        out[f"primnormal_{name}_k{kernel}"] = O.ref_frame_prim_normals(sc, fp, mats, light)
     for key, tex, st in SC.tex_samples():
         out["tex_" + key] = np.stack([O.ref_tex2d(tex, float(s), float(t)) for s, t in st])
     np.savez_compressed(os.path.join(HERE, "golden_surface.npz"), **out)

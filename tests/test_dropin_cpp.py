@@ -94,3 +94,11 @@ def test_dropin_program_matches_oracle(gpu):
         want3 = O.oracle_frame_format(sc, fp, S.default_material(0), S.point_light(eye), "PF_RGB8")
         got3 = np.fromfile(os.path.join(d, "frame_whitted_ssaa2_rgb8.bin"), dtype=np.uint8).reshape(120, 160, 3)
         assert int(np.abs(got3.astype(np.int32) - want3.astype(np.int32)).max()) <= 1 and float((got3 != want3).mean()) <= 1e-3
+        # sphere bvh, kernel_params without normals: the program's spheres through the oracle
+        balls = np.fromfile(os.path.join(d, "spheres.bin"), dtype=np.float32).reshape(-1, 12)
+        nodes, idx = S.build_bvh(1, balls)
+        ssc = S.HostScene(1, balls, nodes, idx, None, "balls")
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
+        want_b = O.oracle_frame_surface(ssc, fp, S.SurfaceData(2, None), S.default_material(0), S.point_light(eye))
+        got_b = np.fromfile(os.path.join(d, "frame_spheres.bin"), dtype=np.float32).reshape(120, 160, 4)
+        assert float((np.abs(got_b - want_b).max(axis=2) > 1 / 255).mean()) == 0.0 and want_b[..., 0].std() > 0.05

@@ -71,6 +71,44 @@ def test_oracle_matches_reference_headers(kernel, nb, cb, tex):
     assert np.abs(got - want).max() <= 1e-6
 
 
+def prim_normal_scene(name):
+    if name == "spheres":
+        sc = S.make_scene("spheres", 0.02)
+        eye, light = (0.0, 0.3, 3.2), S.point_light((1.0, 2.0, 3.0))
+    else:
+        sc = S.make_scene("cfg2_grid", 0.004)
+        eye, light = (0.9, 0.75, 1.3), S.point_light((0.4, 1.2, 0.6))
+    sc.prims.view(np.uint32)[:, 0] = (np.arange(sc.n_prims) // 3) % SC.N_GEOMS
+    return sc, eye, light
+
+
+PRIM_NORMAL_CASES = [("cfg2_grid", 0), ("cfg2_grid", 1), ("cfg2_grid", 3), ("spheres", 0), ("spheres", 1)]
+
+
+def prim_normal_frame(name, kernel, w, h):
+    sc, eye, light = prim_normal_scene(name)
+    fp = S.frame_params(kernel, w, h, eye, (0, 0, 0), pixel_sampler=2 if kernel == 3 else 0, n_materials=SC.N_GEOMS,
+                        num_bounces=4, ambient=(1, 1, 1, 1) if kernel == 3 else (0.3, 0.3, 0.3, 1.0))
+    return sc, fp, S.SurfaceData(2, None), S.generic_materials(), light
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref is only built where /root/reference exists")
+@pytest.mark.parametrize("name,kernel", PRIM_NORMAL_CASES)
+def test_normals_from_the_primitive_match_reference_headers(name, kernel):
+    """kernel_params without normals (default make_kernel_params overload): get_normal(hr, triangle | sphere)."""
+    sc, fp, sd, mats, light = prim_normal_frame(name, kernel, 96, 64)
+    got = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    want = O.ref_frame_prim_normals(sc, fp, mats, light)
+    assert np.abs(got - want).max() <= 1e-6 and want[..., :3].std() > 0.05
+
+
+@pytest.mark.parametrize("name,kernel", PRIM_NORMAL_CASES)
+def test_normals_from_the_primitive_fixture(golden, name, kernel):
+    sc, fp, sd, mats, light = prim_normal_frame(name, kernel, 40, 28)
+    got = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    assert np.abs(got - golden[f"primnormal_{name}_k{kernel}"]).max() <= 1e-6
+
+
 # ---- GPU ------------------------------------------------------------------------------------------
 
 def _frac_bad(img, want):
@@ -116,6 +154,28 @@ def test_gpu_surface_with_ssaa(gpu, name, ps):
         img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
         gpu.frame(dev, fp, None, mats, light, img, traverse=gpu.TRAVERSE_EXACT)
         assert _frac_bad(img, want) <= (0.0 if fp.kernel in (0, 1) else 4e-3)
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,kernel", PRIM_NORMAL_CASES)
+def test_gpu_normals_from_the_primitive(gpu, name, kernel):
+    """Triangle and SPHERE scenes through vsb_frame with kernel_params that carry no normals."""
+    sc, fp, sd, mats, light = prim_normal_frame(name, kernel, 160, 112)
+    want = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    dev = gpu.Scene(sc)
+    try:
+        gpu.set_surface(dev, sd)
+        for trav in (gpu.TRAVERSE_EXACT, gpu.TRAVERSE_WIDE):
+            img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+            gpu.frame(dev, fp, None, mats, light, img, traverse=trav)
+            limit = (0.0 if trav == gpu.TRAVERSE_EXACT else 1e-3) if kernel in (0, 1) else 4e-3
+            assert _frac_bad(img, want) <= limit, (name, kernel, trav)
+        if name == "spheres":
+            fp.kernel = 3          # the reference's path tracer has no defined sphere normal (isect_pos unset)
+            with pytest.raises(RuntimeError):
+                gpu.frame(dev, fp, None, mats, light, img)
     finally:
         dev.close()
 

@@ -263,7 +263,7 @@ def set_surface(scene: "Scene", surface) -> None:
         return
     d = N.SurfaceDesc()
     d.normal_binding, d.color_binding = surface.normal_binding, surface.color_binding
-    d.normals = surface.normals.ctypes.data
+    d.normals = surface.normals.ctypes.data if surface.normals is not None else None
     d.colors = surface.colors.ctypes.data if surface.colors is not None else None
     d.tex_coords = surface.tex_coords.ctypes.data if surface.tex_coords is not None else None
     texs = None

@@ -391,7 +391,16 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     if (d->depth && d->camera_kind != VSB_CAM_MATRIX) return VSB_ERR_BAD_ARG;   // depth_transform needs the matrices
     if (p.kernel != VSB_KERNEL_AO && (!d->materials || p.n_materials < 1)) return VSB_ERR_BAD_ARG;
     if (p.n_lights > 0 && !d->lights && p.kernel <= VSB_KERNEL_WHITTED) return VSB_ERR_BAD_ARG;
-    for (int i = 0; i < n_scenes; ++i) if (!scenes || !scenes[i] || scenes[i]->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
+    for (int i = 0; i < n_scenes; ++i)
+    {
+        if (!scenes || !scenes[i]) return VSB_ERR_BAD_ARG;
+        // a sphere scene shades with get_normal(hr, sphere) (surface attached with VSB_NORMALS_FROM_PRIMITIVE); the
+        // reference's path tracer reads isect_pos before setting it there (detail/pathtracing.inl:74,107), so
+        // simple / whitted only
+        const bool sphere_ok = scenes[i]->prim_kind == VSB_PRIM_SPHERE && scenes[i]->surf.enabled &&
+                               scenes[i]->surf.normal_binding == VSB_NORMALS_FROM_PRIMITIVE && p.kernel <= VSB_KERNEL_WHITTED;
+        if (scenes[i]->prim_kind != VSB_PRIM_TRIANGLE && !sphere_ok) return VSB_ERR_UNSUPPORTED;
+    }
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 

@@ -383,10 +383,16 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
     s->surf_allocs.clear();
     s->surf = vsb::SurfCtx{};
     if (!desc) return VSB_OK;
-    if (s->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
-    if (!desc->normals || desc->normal_binding < 0 || desc->normal_binding > 1 || desc->color_binding < 0 || desc->color_binding > 2)
+    if (desc->normal_binding < 0 || desc->normal_binding > VSB_NORMALS_FROM_PRIMITIVE || desc->color_binding < 0 || desc->color_binding > 2)
         return VSB_ERR_BAD_ARG;
+    if (!desc->normals && desc->normal_binding != VSB_NORMALS_FROM_PRIMITIVE) return VSB_ERR_BAD_ARG;
+    // spheres: only get_normal(hr, sphere) applies (bindings, lerped colours and tex coords are triangle rules); a
+    // generic_primitive needs a normals array in the reference too (get_surface.h:218-245) and has no rule here
+    if (s->prim_kind == VSB_PRIM_GENERIC) return VSB_ERR_UNSUPPORTED;
+    if (s->prim_kind == VSB_PRIM_SPHERE &&
+        (desc->normal_binding != VSB_NORMALS_FROM_PRIMITIVE || desc->color_binding == VSB_COLORS_PER_VERTEX || desc->tex_coords))
+        return VSB_ERR_UNSUPPORTED;
     if (desc->color_binding && !desc->colors) return VSB_ERR_BAD_ARG;
     if (desc->n_textures < 0 || (desc->n_textures > 0 && !desc->textures)) return VSB_ERR_BAD_ARG;
     const cudaMemcpyKind kind = mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
@@ -403,7 +409,8 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
     vsb::SurfCtx c{};
     c.normal_binding = desc->normal_binding; c.color_binding = desc->color_binding;
     const size_t n = s->n_prims;
-    c.normals = (const float4*)copy(desc->normals, (desc->normal_binding ? 3 * n : n) * 16);
+    if (desc->normal_binding != VSB_NORMALS_FROM_PRIMITIVE)
+        c.normals = (const float4*)copy(desc->normals, (desc->normal_binding ? 3 * n : n) * 16);
     if (desc->color_binding) c.colors = (const float4*)copy(desc->colors, (desc->color_binding == 2 ? 3 * n : n) * 16);
     if (desc->tex_coords)
     {
@@ -439,7 +446,12 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         s->surf_allocs.clear();
         return err;
     }
-    if (desc->normal_binding == VSB_NORMALS_PER_VERTEX)
+    if (s->prim_kind == VSB_PRIM_SPHERE)
+    {
+        c.ref_spheres = reinterpret_cast<const float4*>(s->d_prims);
+        c.indices = s->d_indices;
+    }
+    else if (desc->normal_binding != VSB_NORMALS_PER_FACE)
     {
         const size_t n_list = s->d_indices ? s->n_idx : s->n_prims;
         float4* gn = nullptr;

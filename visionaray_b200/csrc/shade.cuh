@@ -67,7 +67,9 @@ struct SurfCtx
     const float4*     colors;       // per face / per vertex like the normals; null without colours
     const float2*     tex_coords;   // [3 prim_id + k]; null without textures
     const DevTexture* textures;     // by geom_id
-    const float4*     geo_normals;  // per vertex binding: normalize(cross(e1, e2)) of primitive(i), by primitive_list_index i
+    const float4*     ref_spheres;  // binding "none" on a sphere scene: the basic_sphere records (3 x 16 B) ...
+    const uint32_t*   indices;      // ... and the index_bvh indirection (null for a plain bvh)
+    const float4*     geo_normals;  // triangles, per vertex / no binding: normalize(cross(e1, e2)) of primitive(i), by primitive_list_index i
                                     // (precomputed by surface_geo_normals_kernel: one load at the hit instead of
                                     // indices[i] -> 64-byte triangle -> cross -> normalize)
 };
@@ -313,7 +315,7 @@ __global__ void surface_geo_normals_kernel(const float4* __restrict__ ref_prims,
 // get_surface(hit_rec, params) for an index_bvh of triangles -- get_surface.h:330-530
 // (inlined at its single call site per program; as an out-of-line call -- measured -- the path tracer, which
 // evaluates it at every bounce, lost 18 %: the 10-word result goes through local memory)
-__device__ __forceinline__ Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v)
+__device__ __forceinline__ Surface surface_at(const FrameCtx& f, uint32_t prim_id, uint32_t geom_id, uint32_t list_index, float u, float v, V3 pos)
 {
     const SurfCtx& sf = f.surf;
     Surface S;
@@ -328,6 +330,21 @@ __device__ __forceinline__ Surface surface_at(const FrameCtx& f, uint32_t prim_i
     {
         const float4 nn = __ldg(sf.normals + prim_id);
         S.gn = S.sn = v3(nn.x, nn.y, nn.z);
+    }
+    else if (sf.normal_binding == 2)
+    {
+        // kernel_params without normals: get_normal(hr, primitive) (get_surface.h:133-150, get_normal.h:96-118)
+        if (sf.ref_spheres)
+        {
+            const size_t pi = sf.indices ? __ldg(sf.indices + list_index) : list_index;
+            const float4 c = __ldg(sf.ref_spheres + pi * 3 + 1), r = __ldg(sf.ref_spheres + pi * 3 + 2);
+            S.gn = S.sn = v3(rn_div(rn_sub(pos.x, c.x), r.x), rn_div(rn_sub(pos.y, c.y), r.x), rn_div(rn_sub(pos.z, c.z), r.x));
+        }
+        else
+        {
+            const float4 g = __ldg(sf.geo_normals + list_index);
+            S.gn = S.sn = v3(g.x, g.y, g.z);
+        }
     }
     else
     {
@@ -757,7 +774,7 @@ struct FrameProgram
         const V3 view = vneg(d);
         if (SURF)
         {
-            const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
+            const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v, pos);
             const V3 n = vfaceforward(S.sn, view, S.gn);
             for (int i = 0; i < f.p.n_lights; ++i)
             {
@@ -830,7 +847,7 @@ struct FrameProgram
             L.st(K0 + 9, pos); L.st(K0 + 12, view); L.u(K0 + 15) = prim_id; L.u(K0 + 16) = geom_id;
             if (SURF)
             {
-                const Surface S = surface_at(f, prim_id, geom_id, h.list_index, h.u, h.v);
+                const Surface S = surface_at(f, prim_id, geom_id, h.list_index, h.u, h.v, pos);
                 L.st(K0 + 17, vfaceforward(S.sn, view, S.gn)); L.st(K0 + 20, S.tex);
                 L.st(K0 + 23, vreflect(view, S.sn));          // specular_bounce(material, view_dir, surf.shading_normal)
             }
@@ -919,7 +936,7 @@ struct FrameProgram
             V3 n, src;
             if (SURF)
             {
-                const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v);
+                const Surface S = surface_at(f, h.prim_id, h.geom_id, h.list_index, h.u, h.v, vadd(o, vscale(d, h.t)));
                 n = vfaceforward(S.sn, view, S.gn);
                 src = material_sample_ext(m, S, n, view, refl, pdf, samp);
             }
