@@ -625,17 +625,11 @@ struct FrameProgram
     // ssaa<N>: clear, then N x { dst = src/N + dst } (detail/sched_common.h:640-698) -- the
     // accumulator lives in the lane state and the next sub-sample's primary ray is emitted.
     // Returns true when the pixel continues with another ray (req).
-    // finish() is reached from several places of a program.  In the EXT Whitted program its body (formats,
-    // SSAA resampling, depth) is ONE out-of-line copy: 6.6 k -> 4.8 k instructions, stall_no_instruction was on
-    // top of that kernel's profile (profiles/r1_surface_whitted_v0.txt); plain inputs 7.61 -> 7.13 ms, full
-    // surface 12.77 -> 11.55 ms on cfg2.  The path tracer measured 5 % slower that way and keeps it inline.
-    __device__ __noinline__ bool finish_ext(Lane& L, float r, float g, float b, float a, RayReq& req) const
-    {
-        return finish_body(L, r, g, b, a, req);
-    }
+    // finish() has ONE call site per program (done(), below).
+    // It used to be inlined at every exit of a kernel: 6.6 k SASS instructions for the extended Whitted program and
+    // stall_no_instruction on top of its profile (profiles/r1_surface_whitted_v0.txt).
     __device__ __forceinline__ bool finish(Lane& L, float r, float g, float b, float a, RayReq& req) const
     {
-        if (EXT && KERNEL == 1) return finish_ext(L, r, g, b, a, req);
         return finish_body(L, r, g, b, a, req);
     }
     __device__ __forceinline__ bool finish_body(Lane& L, float r, float g, float b, float a, RayReq& req) const
@@ -740,15 +734,6 @@ struct FrameProgram
             fx = rn_add(fx, dx); fy = rn_add(fy, dy);
         }
         L.u(W_SAMP) = samp;
-        if (KERNEL == 3 && f.p.num_bounces == 0u)
-        {
-            // no bounce is traced: every sample returns the background
-            RayReq unused;
-            L.u(W_PHASE) = PH_PRIMARY;
-            if (EXT) L.f(W_DEPTH) = 1.0f;
-            while (finish_bg(L, unused)) { }        // every (sub-)sample returns the background, stored / blended as usual
-            return false;
-        }
         start_sample(L, fx, fy, req);
         return true;
     }
@@ -756,17 +741,23 @@ struct FrameProgram
     __device__ bool done(Lane& L, const HitReg& h, float ox, float oy, float oz, float dx, float dy, float dz, RayReq& req) const
     {
         const V3 o = v3(ox, oy, oz), d = v3(dx, dy, dz);
-        if (KERNEL == 0) return done_simple(L, h, o, d, req);
-        if (KERNEL == 1) return done_whitted(L, h, o, d, req);
-        if (KERNEL == 2) return done_ao(L, h, o, d, req);
-        return done_pathtracing(L, h, o, d, req);
+        // the kernels report a finished pixel through `px`; finish() -- store / blend / formats / SSAA resampling -- is
+        // instantiated HERE only, however many exits a kernel has (these programs are instruction-fetch sensitive)
+        float4 px;
+        const bool more = KERNEL == 0 ? done_simple(L, h, o, d, req, px)
+                        : KERNEL == 1 ? done_whitted(L, h, o, d, req, px)
+                        : KERNEL == 2 ? done_ao(L, h, o, d, req, px) : done_pathtracing(L, h, o, d, req, px);
+        if (more) return true;
+        return finish(L, px.x, px.y, px.z, px.w, req);
     }
+    __device__ __forceinline__ bool pixel(float4& px, float r, float g, float b, float a) const { px = make_float4(r, g, b, a); return false; }
+    __device__ __forceinline__ bool pixel_bg(float4& px) const { px = make_float4(ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3]); return false; }
 
     // simple::kernel -- detail/simple.inl:25-75
-    __device__ bool done_simple(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
+    __device__ __forceinline__ bool done_simple(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req, float4& px) const
     {
         const FrameCtx& f = ctx;
-        if (!h.hit) { return finish_bg(L, req); }
+        if (!h.hit) { return pixel_bg(px); }
         const V3 pos = vadd(o, vscale(d, h.t));
         primary_hit(L, pos);
         const Material m = f.materials[h.geom_id];
@@ -783,7 +774,7 @@ struct FrameProgram
                 const V3 c = shade_light_ext(m, S, l, pos, n, view, wi);
                 shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
             }
-            return finish(L, shaded.x, shaded.y, shaded.z, 1.0f, req);
+            return pixel(px, shaded.x, shaded.y, shaded.z, 1.0f);
         }
         V3 n = face_normal(h.prim_id);
         n = vfaceforward(n, view, n);
@@ -794,13 +785,13 @@ struct FrameProgram
             const V3 c = shade_light(m, l, pos, n, view, wi);
             shaded = v3(shaded.x + c.x, shaded.y + c.y, shaded.z + c.z);
         }
-        return finish(L, shaded.x, shaded.y, shaded.z, 1.0f, req);
+        return pixel(px, shaded.x, shaded.y, shaded.z, 1.0f);
     }
 
     // whitted::kernel -- detail/whitted.inl:227-323.  State: color 0..2, shaded 3..5, throughput 6,
     // depth 7, light 8, pos 9..11, view 12..14, prim_id 15, geom_id 16; SURF: the surface of the current hit,
     // evaluated once -- shading normal (faceforwarded) 17..19, tex_color 20..22, reflection direction 23..25
-    __device__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
+    __device__ __forceinline__ bool done_whitted(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req, float4& px) const
     {
         const FrameCtx& f = ctx;
         const uint32_t phase = L.u(W_PHASE);
@@ -833,13 +824,13 @@ struct FrameProgram
         }
         else
         {
-            if (phase == PH_PRIMARY && !h.hit) { return finish_bg(L, req); }
+            if (phase == PH_PRIMARY && !h.hit) { return pixel_bg(px); }
             if (EXT && phase == PH_PRIMARY) primary_hit(L, vadd(o, vscale(d, h.t)));   // detail/whitted.inl:238-242
             // while (hit && throughput > epsilon && depth++ < num_bounces)
             const float throughput = L.f(K0 + 6);
             bool go = h.hit && throughput > f.p.epsilon;
             if (go) { const uint32_t depth = L.u(K0 + 7); go = depth < f.p.num_bounces; L.u(K0 + 7) = depth + 1u; }
-            if (!go) { const V3 c = L.ld(K0 + 0); return finish(L, c.x, c.y, c.z, 1.0f, req); }
+            if (!go) { const V3 c = L.ld(K0 + 0); return pixel(px, c.x, c.y, c.z, 1.0f); }
             pos = vadd(o, vscale(d, h.t));
             view = vneg(d);
             prim_id = h.prim_id; geom_id = h.geom_id; light = 0u;
@@ -872,17 +863,17 @@ struct FrameProgram
             L.st(K0 + 0, color); L.f(K0 + 6) = rn_mul(throughput, kr); L.u(W_PHASE) = PH_BOUNCE;
             return true;
         }
-        return finish(L, color.x, color.y, color.z, 1.0f, req);    // throughput * 0 ends the loop
+        return pixel(px, color.x, color.y, color.z, 1.0f);    // throughput * 0 ends the loop
     }
 
     // AO kernel -- src/examples/ao/main.cpp:183-246.  State: pos 0..2, prim_id 3, clr 4, i 5
-    __device__ bool done_ao(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
+    __device__ __forceinline__ bool done_ao(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req, float4& px) const
     {
         const FrameCtx& f = ctx;
         V3 pos; uint32_t prim_id, i; float clr;
         if (L.u(W_PHASE) == PH_PRIMARY)
         {
-            if (!h.hit) { return finish_bg(L, req); }
+            if (!h.hit) { return pixel_bg(px); }
             pos = vadd(o, vscale(d, h.t));
             primary_hit(L, pos);
             prim_id = h.prim_id; clr = 1.0f; i = 0u;
@@ -908,13 +899,16 @@ struct FrameProgram
             L.f(K0 + 4) = clr; L.u(K0 + 5) = i;
             return true;
         }
-        return finish(L, clr, clr, clr, 1.0f, req);
+        return pixel(px, clr, clr, clr, 1.0f);
     }
 
     // pathtracing::kernel -- detail/pathtracing.inl:29-121.  State: dst 0..2, bounce 3, result.hit 4
-    __device__ bool done_pathtracing(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req) const
+    __device__ __forceinline__ bool done_pathtracing(Lane& L, const HitReg& h, V3 o, V3 d, RayReq& req, float4& px) const
     {
         const FrameCtx& f = ctx;
+        // num_bounces == 0: the loop of the reference kernel never runs and every sample returns the background
+        // (the primary ray traced for it is wasted; not a case worth a second copy of finish())
+        if (f.p.num_bounces == 0u) return pixel_bg(px);
         V3 dst = L.ld(K0 + 0);
         uint32_t bounce = L.u(K0 + 3);
         bool result_hit = L.u(K0 + 4) != 0u;
@@ -967,7 +961,7 @@ struct FrameProgram
                 }
             }
         }
-        if (finished) return result_hit ? finish(L, dst.x, dst.y, dst.z, 1.0f, req) : finish_bg(L, req);
+        if (finished) return result_hit ? pixel(px, dst.x, dst.y, dst.z, 1.0f) : pixel_bg(px);
         L.st(K0 + 0, dst); L.u(K0 + 3) = bounce; L.u(K0 + 4) = result_hit ? 1u : 0u;
         return true;
     }
