@@ -181,6 +181,31 @@ def test_gpu_normals_from_the_primitive(gpu, name, kernel):
 
 
 @pytest.mark.gpu
+def test_gpu_ids_are_checked_against_array_sizes(gpu):
+    """prim_id indexes normals / colours / tex coords, geom_id the materials: the reference trusts them, the
+    library computes the scene's largest ids once and refuses arrays they would leave."""
+    sc, fp, sd, mats, light = SC.case("simple_vertex", 64, 48)
+    img = np.zeros((48, 64, 4), dtype=np.float32)
+    dev = gpu.Scene(sc)
+    try:
+        with pytest.raises(RuntimeError):
+            gpu.frame(dev, S.frame_params(0, 64, 48, (0.3, 0.5, 3.0), (0, 0, 0), n_materials=2), None, mats[:2], light, img)   # geom ids reach 3
+    finally:
+        dev.close()
+    bad = S.HostScene(sc.prim_kind, sc.prims.copy(), sc.nodes, sc.indices, None, "bad")
+    bad.prims.view(np.uint32)[5, 1] = sc.n_prims + 7          # a prim_id past the per-primitive arrays
+    dev = gpu.Scene(bad)
+    try:
+        with pytest.raises(RuntimeError):
+            gpu.set_surface(dev, sd)
+        with pytest.raises(RuntimeError):
+            dev.set_normals(sc.normals)
+        assert gpu.closest_hit(dev, S.random_rays(100, 1, -1.5, 1.5)).shape[0] == 100     # ray queries do not care
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
 def test_gpu_generic_materials_without_surface(gpu):
     """A generic_material list with the plain per-face normals (no vsb_scene_set_surface): device
     materials need the generic_materials flag, host materials are detected."""

@@ -401,6 +401,12 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
                                scenes[i]->surf.normal_binding == VSB_NORMALS_FROM_PRIMITIVE && p.kernel <= VSB_KERNEL_WHITTED;
         if (scenes[i]->prim_kind != VSB_PRIM_TRIANGLE && !sphere_ok) return VSB_ERR_UNSUPPORTED;
     }
+    for (int i = 0; i < n_scenes; ++i)
+    {
+        rc = scene_id_range(scenes[i]); if (rc) return rc;
+        if (p.kernel != VSB_KERNEL_AO && scenes[i]->max_geom_id >= (uint32_t)p.n_materials) return VSB_ERR_BAD_ARG;   // materials[geom_id]
+    }
+    if (n_scenes == 1 && scenes[0]->max_prim_id >= scenes[0]->n_prims) return VSB_ERR_BAD_ARG;                      // normals[prim_id]
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 

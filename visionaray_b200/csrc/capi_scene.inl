@@ -62,6 +62,8 @@ struct vsb_scene
     vsb::Node80* d_wide = nullptr;
     void*    d_wide_prims = nullptr;
     float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
+    mutable int id_range_known = 0;      // largest prim_id / geom_id of the primitives, computed on first use
+    mutable uint32_t max_prim_id = 0, max_geom_id = 0;
     vsb::SurfCtx surf = {};              // optional, vsb_scene_set_surface(); device copies listed in surf_allocs
     std::vector<void*> surf_allocs;
     uint32_t n_wide = 0, n_wide_prims = 0;
@@ -362,11 +364,37 @@ extern "C" int vsb_scene_create(int prim_kind, const void* prims, size_t n_prims
     return VSB_OK;
 }
 
+namespace
+{
+// prim_id indexes the per-primitive arrays (normals, colours, tex coords), geom_id the materials and textures:
+// the reference trusts them; here the scene's largest ids are computed once and every consumer checks its array sizes
+int scene_id_range(const vsb_scene* s)
+{
+    if (s->id_range_known) return VSB_OK;
+    uint32_t* d2 = nullptr;
+    VSB_CUDA(cudaMalloc((void**)&d2, 8));
+    cudaError_t e = cudaMemsetAsync(d2, 0, 8, g.stream);
+    if (e == cudaSuccess)
+    {
+        vsb::id_range_kernel<<<(unsigned)(g.sm_count * 8), 256, 0, g.stream>>>(s->prim_kind, s->d_prims, s->n_prims, d2);
+        ++g.launches;
+        uint32_t h[2] = { 0u, 0u };
+        e = cudaMemcpyAsync(h, d2, 8, cudaMemcpyDeviceToHost, g.stream);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(g.stream);
+        if (e == cudaSuccess) { s->max_prim_id = h[0]; s->max_geom_id = h[1]; s->id_range_known = 1; }
+    }
+    cudaFree(d2);
+    return e == cudaSuccess ? VSB_OK : (int)e;
+}
+} // namespace
+
 extern "C" int vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem)
 {
     int rc = require_init(); if (rc) return rc;
     if (!s || !normals16 || n != s->n_prims) return VSB_ERR_BAD_ARG;
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    rc = scene_id_range(s); if (rc) return rc;
+    if (s->max_prim_id >= n) return VSB_ERR_BAD_ARG;          // normals[prim_id] would leave the array
     if (!s->d_normals) VSB_CUDA(cudaMalloc((void**)&s->d_normals, n * 16));
     VSB_CUDA(cudaMemcpyAsync(s->d_normals, normals16, n * 16,
                              mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, g.stream));
@@ -395,6 +423,8 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         return VSB_ERR_UNSUPPORTED;
     if (desc->color_binding && !desc->colors) return VSB_ERR_BAD_ARG;
     if (desc->n_textures < 0 || (desc->n_textures > 0 && !desc->textures)) return VSB_ERR_BAD_ARG;
+    rc = scene_id_range(s); if (rc) return rc;
+    if (s->max_prim_id >= s->n_prims) return VSB_ERR_BAD_ARG;  // normals / colours / tex coords are indexed by prim_id
     const cudaMemcpyKind kind = mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice;
     int err = VSB_OK;
     auto copy = [&](const void* src, size_t bytes) -> void*

@@ -96,6 +96,25 @@ __global__ void fill_prims_kernel(int prim_kind, const void* __restrict__ prims,
     make_prim_record(prim_kind, prims, indices, leaf_list[i], out, i);
 }
 
+// largest prim_id / geom_id of a primitive array (ids are caller data: per-primitive arrays are indexed by
+// prim_id, materials and textures by geom_id -- checked once per scene instead of trusted)
+__global__ void id_range_kernel(int prim_kind, const void* __restrict__ prims, size_t n, uint32_t* __restrict__ out2)
+{
+    uint32_t mp = 0u, mg = 0u;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+    {
+        const uint32_t* rec = reinterpret_cast<const uint32_t*>(reinterpret_cast<const char*>(prims) + i * prim_stride(prim_kind));
+        mg = rec[0] > mg ? rec[0] : mg;
+        mp = rec[1] > mp ? rec[1] : mp;
+    }
+    for (int o = 16; o > 0; o >>= 1)
+    {
+        const uint32_t a = __shfl_xor_sync(0xffffffffu, mp, o), b = __shfl_xor_sync(0xffffffffu, mg, o);
+        mp = a > mp ? a : mp; mg = b > mg ? b : mg;
+    }
+    if ((threadIdx.x & 31u) == 0u) { atomicMax(out2, mp); atomicMax(out2 + 1, mg); }
+}
+
 // ---- the persistent trace kernel ----------------------------------------------------------------
 //
 // Work items (rays of a list, pixels of a frame) are handed out in two levels: a warp reserves a
