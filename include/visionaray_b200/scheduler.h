@@ -504,9 +504,53 @@ private:
     T kl_ = T(1), att_const_ = T(1), att_lin_ = T(0), att_quad_ = T(0);
 };
 
+// spot_light<T> (spot_light.h, detail/spot_light.inl): set_spot_direction takes a unit vector, set_spot_cutoff an
+// angle and keeps its cosine
+template <typename T = float>
+class spot_light
+{
+public:
+    vec3 position() const { return position_; }
+    void set_cl(vec3 const& cl) { cl_ = cl; }
+    void set_kl(T kl) { kl_ = kl; }
+    void set_position(vec3 const& pos) { position_ = pos; }
+    void set_spot_direction(vec3 const& dir) { spot_direction_ = dir; }
+    void set_spot_cutoff(T cutoff) { spot_cutoff_ = cutoff; spot_cos_cutoff_ = std::cos(cutoff); }
+    void set_spot_exponent(T e) { spot_exponent_ = e; }
+    void set_constant_attenuation(T att) { att_const_ = att; }
+    void set_linear_attenuation(T att) { att_lin_ = att; }
+    void set_quadratic_attenuation(T att) { att_quad_ = att; }
+    vec3 spot_direction() const { return spot_direction_; }
+    T spot_cutoff() const { return spot_cutoff_; }
+    T spot_exponent() const { return spot_exponent_; }
+    vsb_point_light flatten() const
+    {
+        vsb_point_light l; std::memset(&l, 0, sizeof(l));
+        for (int i = 0; i < 3; ++i) { l.pos[i] = position_[i]; l.cl[i] = cl_[i]; l.spot_dir[i] = spot_direction_[i]; }
+        l.kl = kl_; l.att_const = att_const_; l.att_lin = att_lin_; l.att_quad = att_quad_;
+        l.kind = VSB_LIGHT_SPOT; l.spot_exponent = spot_exponent_; l.spot_cos_cutoff = spot_cos_cutoff_;
+        return l;
+    }
+private:
+    vec3 cl_ = vec3(1.0f), position_ = vec3(0.0f), spot_direction_ = vec3(0.0f, 0.0f, -1.0f);
+    T kl_ = T(1), spot_cutoff_ = T(0), spot_cos_cutoff_ = T(1), spot_exponent_ = T(0);
+    T att_const_ = T(1), att_lin_ = T(0), att_quad_ = T(0);
+};
+
 //-------------------------------------------------------------------------------------------------
 // Kernel parameters and the built-in kernels (kernels.h:94-509, detail/{simple,whitted,pathtracing}.inl)
 //
+
+namespace detail
+{
+template <typename Light>
+inline std::vector<vsb_point_light> flatten_lights(Light const* b, Light const* e)
+{
+    std::vector<vsb_point_light> out;
+    for (; b != e; ++b) out.push_back(b->flatten());
+    return out;
+}
+} // namespace detail
 
 template <typename Material>
 struct kernel_params
@@ -515,7 +559,7 @@ struct kernel_params
     b200_bvh_ref const* prims_end;
     vec3 const* normals;             // host per-face normals, or nullptr = the normals attached to the device tree
     Material const* materials;  size_t num_materials;     // indexed by geom_id
-    point_light<float> const* lights_begin; point_light<float> const* lights_end;
+    std::vector<vsb_point_light> lights;          // point_light<T> / spot_light<T> list, flattened when the params are made
     unsigned num_bounces;
     float epsilon;
     vec4 bg_color;
@@ -528,69 +572,69 @@ struct kernel_params
 
 // make_kernel_params(normals_per_face_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-409
 // `materials` is a contiguous container (std::vector<plastic<float>>, ...), as the reference's callers pass.
-template <typename Materials>
+template <typename Materials, typename Light>
 auto make_kernel_params(normals_per_face_binding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
-                        Materials const& materials, point_light<float> const* lbegin, point_light<float> const* lend,
+                        Materials const& materials, Light const* lbegin, Light const* lend,
                         unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
                         vec4 const& ambient_color = vec4(0.0f))
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, normals, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+    return kernel_params<M>{ begin, end, normals, &materials[0], materials.size(), detail::flatten_lights(lbegin, lend), num_bounces, epsilon, bg_color, ambient_color,
                              surface_params{ false, 0, 0, nullptr, nullptr, nullptr, nullptr, 0 } };
 }
 
 // make_kernel_params(prims b/e, materials, lights b/e, ...)  kernels.h:328-366 -- no normals: the kernels take
 // get_normal(hr, primitive), i.e. normalize(cross(e1, e2)) for triangles and (isect_pos - center) / radius for
 // spheres; the form that works for a sphere bvh (simple / whitted kernels)
-template <typename Materials, typename = decltype(std::declval<Materials const&>()[0].flatten())>
+template <typename Materials, typename Light, typename = decltype(std::declval<Materials const&>()[0].flatten())>
 auto make_kernel_params(b200_bvh_ref const* begin, b200_bvh_ref const* end, Materials const& materials,
-                        point_light<float> const* lbegin, point_light<float> const* lend,
+                        Light const* lbegin, Light const* lend,
                         unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
                         vec4 const& ambient_color = vec4(0.0f))
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), detail::flatten_lights(lbegin, lend), num_bounces, epsilon, bg_color, ambient_color,
                              surface_params{ true, VSB_NORMALS_FROM_PRIMITIVE, 0, nullptr, nullptr, nullptr, nullptr, 0 } };
 }
 
 // make_kernel_params(normals_per_vertex_binding, prims b/e, normals, materials, lights b/e, ...)  kernels.h:371-393
-template <typename Materials>
+template <typename Materials, typename Light>
 auto make_kernel_params(normals_per_vertex_binding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
-                        Materials const& materials, point_light<float> const* lbegin, point_light<float> const* lend,
+                        Materials const& materials, Light const* lbegin, Light const* lend,
                         unsigned num_bounces = 5, float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f),
                         vec4 const& ambient_color = vec4(0.0f))
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), detail::flatten_lights(lbegin, lend), num_bounces, epsilon, bg_color, ambient_color,
                              surface_params{ true, VSB_NORMALS_PER_VERTEX, 0, normals, nullptr, nullptr, nullptr, 0 } };
 }
 
 // w/ normals and textures  kernels.h:395-437.  `textures`: contiguous container of texture_ref2d, by geom_id
-template <typename NormalBinding, typename Materials, typename Textures, int = NormalBinding::id>
+template <typename NormalBinding, typename Materials, typename Textures, typename Light, int = NormalBinding::id>
 auto make_kernel_params(NormalBinding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals, vec2 const* tex_coords,
-                        Materials const& materials, Textures const& textures, point_light<float> const* lbegin,
-                        point_light<float> const* lend, unsigned num_bounces = 5, float epsilon = FLT_EPSILON,
+                        Materials const& materials, Textures const& textures, Light const* lbegin,
+                        Light const* lend, unsigned num_bounces = 5, float epsilon = FLT_EPSILON,
                         vec4 const& bg_color = vec4(0.0f), vec4 const& ambient_color = vec4(0.0f))
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), detail::flatten_lights(lbegin, lend), num_bounces, epsilon, bg_color, ambient_color,
                              surface_params{ true, NormalBinding::id, 0, normals, nullptr, tex_coords, &textures[0], textures.size() } };
 }
 
 // w/ normals, colors and textures  kernels.h:440-509
-template <typename NormalBinding, typename ColorBinding, typename Materials, typename Textures, int = NormalBinding::id, int = ColorBinding::id>
+template <typename NormalBinding, typename ColorBinding, typename Materials, typename Textures, typename Light, int = NormalBinding::id, int = ColorBinding::id>
 auto make_kernel_params(NormalBinding, ColorBinding, b200_bvh_ref const* begin, b200_bvh_ref const* end, vec3 const* normals,
                         vec2 const* tex_coords, Materials const& materials, vec3 const* colors, Textures const& textures,
-                        point_light<float> const* lbegin, point_light<float> const* lend, unsigned num_bounces = 5,
+                        Light const* lbegin, Light const* lend, unsigned num_bounces = 5,
                         float epsilon = FLT_EPSILON, vec4 const& bg_color = vec4(0.0f), vec4 const& ambient_color = vec4(0.0f))
     -> kernel_params<typename std::decay<decltype(materials[0])>::type>
 {
     using M = typename std::decay<decltype(materials[0])>::type;
-    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), lbegin, lend, num_bounces, epsilon, bg_color, ambient_color,
+    return kernel_params<M>{ begin, end, nullptr, &materials[0], materials.size(), detail::flatten_lights(lbegin, lend), num_bounces, epsilon, bg_color, ambient_color,
                              surface_params{ true, NormalBinding::id, ColorBinding::id, normals, colors, tex_coords, &textures[0], textures.size() } };
 }
 
@@ -845,8 +889,7 @@ public:
         set_ao(d, kernel);
         std::vector<vsb_material> mats(kp.num_materials);
         for (size_t i = 0; i < kp.num_materials; ++i) mats[i] = kp.materials[i].flatten();
-        std::vector<vsb_point_light> lights;
-        for (auto l = kp.lights_begin; l != kp.lights_end; ++l) lights.push_back(l->flatten());
+        std::vector<vsb_point_light> const& lights = kp.lights;
         d.p.n_materials = int(mats.size()); d.p.n_lights = int(lights.size());
         if (d.camera_kind == VSB_CAM_BASIS) detail::check(vsb_camera_basis(&d), "vsb_camera_basis");
         d.scissor[0] = sparams.scissor_box.x; d.scissor[1] = sparams.scissor_box.y;

@@ -88,11 +88,16 @@ typedef struct vsb_material {
     float pad[2];
 } vsb_material;
 
-/* point_light<float> (point_light.h:58-64). 48 B. */
+/* point_light<float> (point_light.h:58-64) or spot_light<float> (spot_light.h, detail/spot_light.inl:14-38),
+ * flattened; a light list is homogeneous in the reference (the Lights iterator type) but may mix here. 64 B.
+ * Spot: intensity = cl kl att spot, spot = dot(spot_dir, normalize(pos - position)) > spot_cos_cutoff ?
+ * pow(spot, spot_exponent) : 0; spot_dir must be a unit vector. */
+enum { VSB_LIGHT_POINT = 0, VSB_LIGHT_SPOT = 1 };
 typedef struct vsb_point_light {
     float pos[3]; float kl;
     float cl[3];  float att_const;
-    float att_lin; float att_quad; float pad[2];
+    float att_lin; float att_quad; int32_t kind; float spot_exponent;
+    float spot_dir[3]; float spot_cos_cutoff;
 } vsb_point_light;
 
 enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1, VSB_MAT_EMISSIVE = 2, VSB_MAT_MIRROR = 3 };
@@ -222,6 +227,8 @@ typedef struct vsb_frame_desc {
     int32_t  generic_materials;          /* non-zero: `materials` is a generic_material<emissive, matte, mirror, plastic>
                                             list, i.e. entries may be VSB_MAT_EMISSIVE / VSB_MAT_MIRROR (pathtracing.inl:93-104,
                                             whitted.inl:66-122).  Detected automatically when params_mem == VSB_MEM_HOST. */
+    int32_t  spot_lights;                /* non-zero: `lights` may hold VSB_LIGHT_SPOT entries.  Detected automatically when
+                                            params_mem == VSB_MEM_HOST. */
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;

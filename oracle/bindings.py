@@ -280,6 +280,22 @@ def ref_frame_prim_normals(scene, fp, materials, lights, rgba=None, nthreads=0):
     return rgba
 
 
+def ref_frame_spot(scene, fp, materials, lights, cutoff_angles, rgba=None, nthreads=0):
+    """simple / whitted through the reference headers with a spot_light<float> list."""
+    if rgba is None:
+        rgba = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+    lib = ref_lib()
+    vp, sz = C.c_void_p, C.c_size_t
+    lib.ref_frame_spot.argtypes = [vp, vp, sz, vp, sz, vp, sz, vp, vp, vp, vp, vp, C.c_int]
+    ang = np.ascontiguousarray(cutoff_angles, dtype=np.float32)
+    rc = lib.ref_frame_spot(C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes), scene.nodes.shape[0],
+                            _p(scene.indices), scene.indices.shape[0], _p(scene.normals), _p(materials), _p(lights), _p(ang),
+                            _p(rgba), nthreads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError("ref_frame_spot: unsupported kernel")
+    return rgba
+
+
 def oracle_tex2d(tex, s, t):
     o = make_texture(tex)
     out = np.zeros(4, dtype=np.float32)

@@ -32,6 +32,7 @@
 #include <visionaray/kernels.h>
 #include <visionaray/material.h>
 #include <visionaray/point_light.h>
+#include <visionaray/spot_light.h>
 #include <visionaray/scheduler.h>
 #include <visionaray/simple_buffer_rt.h>
 #include <visionaray/camera.h>
@@ -80,7 +81,8 @@ struct light_pod
 {
     float pos[3]; float kl;
     float cl[3];  float att_const;
-    float att_lin; float att_quad; float pad[2];
+    float att_lin; float att_quad; int32_t kind; float spot_exponent;   // kind: 0 point_light, 1 spot_light
+    float spot_dir[3]; float spot_cos_cutoff;
 };
 
 // Deterministic counter-based sampler (PCG-RXS-M-XS-32); the same generator is restated in

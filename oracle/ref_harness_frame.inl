@@ -412,6 +412,45 @@ namespace
 {
 } // namespace
 
+// spot_light<float> list (spot_light.h): plastic materials, per-face normals, simple / whitted kernels.
+// cutoff_angles: the angles the lights were set up with (the class keeps cos(cutoff) itself).
+extern "C" int ref_frame_spot(void const* fp_, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                              uint32_t const* indices, size_t n_idx, float const* normals16, void const* mats_,
+                              void const* lights_, float const* cutoff_angles, float* rgba, int nthreads)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    if (fp.kernel > 1) return -1;
+    scene_host s{ make_ref<tri_t>(prims, n_prims, nodes, n_nodes, indices, n_idx) };
+    fill_scene(s, fp, normals16, n_prims, (mat_pod const*)mats_, (light_pod const*)lights_);
+    aligned_vector<spot_light<float>> spots;
+    light_pod const* lp = (light_pod const*)lights_;
+    for (int i = 0; i < fp.n_lights; ++i)
+    {
+        spot_light<float> l;
+        l.set_cl(vec3(lp[i].cl[0], lp[i].cl[1], lp[i].cl[2]));
+        l.set_kl(lp[i].kl);
+        l.set_position(vec3(lp[i].pos[0], lp[i].pos[1], lp[i].pos[2]));
+        l.set_spot_direction(vec3(lp[i].spot_dir[0], lp[i].spot_dir[1], lp[i].spot_dir[2]));
+        l.set_spot_cutoff(cutoff_angles[i]);
+        l.set_spot_exponent(lp[i].spot_exponent);
+        l.set_constant_attenuation(lp[i].att_const);
+        l.set_linear_attenuation(lp[i].att_lin);
+        l.set_quadratic_attenuation(lp[i].att_quad);
+        spots.push_back(l);
+    }
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+    tri_ref_t const* pb = &s.ref;
+    tri_ref_t const* pe = &s.ref + 1;
+    auto kp = make_kernel_params(normals_per_face_binding{}, pb, pe, s.normals.data(), s.plastics.data(),
+                                 spots.data(), spots.data() + spots.size(), fp.num_bounces, fp.epsilon, bg, amb);
+    using KP = decltype(kp);
+    if (fp.kernel == 0) scalar_frame(no_sampler_adapter<simple::kernel<KP>>{ { kp } }, fp, rgba, nthreads, nullptr);
+    else                scalar_frame(no_sampler_adapter<whitted::kernel<KP>>{ { kp } }, fp, rgba, nthreads, nullptr);
+    return 0;
+}
+
 extern "C" void ref_tex2d(void const* tex_, float s, float t, float* out4)
 {
     tex_pod const& tp = *(tex_pod const*)tex_;

@@ -36,7 +36,8 @@ typedef struct { int32_t hit; uint32_t prim_id, geom_id; float t, u, v; uint32_t
 /* kind 0 plastic, 1 matte (as before); 2 emissive: cd = ce, kd = ls (material.h emissive<T>);
  * 3 mirror: cs = cr, ks = kr, ca = ior, cd = absorption (material.h mirror<T>, brdf.h:160-212) */
 typedef struct { float ca[3], ka, cd[3], kd, cs[3], ks, spec_exp; int32_t kind; float pad[2]; } vso_material;
-typedef struct { float pos[3], kl, cl[3], att_const, att_lin, att_quad, pad[2]; } vso_point_light;
+/* kind 0 point_light, 1 spot_light (detail/spot_light.inl:14-38) */
+typedef struct { float pos[3], kl, cl[3], att_const, att_lin, att_quad; int32_t kind; float spot_exponent, spot_dir[3], spot_cos_cutoff; } vso_point_light;
 
 typedef struct {
     int32_t  kernel;          /* 0 simple, 1 whitted, 2 ao, 3 pathtracing */

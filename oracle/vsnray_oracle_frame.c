@@ -80,6 +80,14 @@ static v3 light_intensity(const vso_point_light* l, v3 pos)
 {
     float dist = length(sub(ld3(l->pos), pos));
     float att = 1.0f / (l->att_const + l->att_lin * dist + l->att_quad * dist * dist);
+    if (l->kind == 1)
+    {
+        /* spot_light::intensity -- detail/spot_light.inl:14-38: (cl kl) att spot */
+        v3 light_dir = sub(ld3(l->pos), pos);
+        float spot = dot(ld3(l->spot_dir), normalize(neg(light_dir)));
+        spot = spot > l->spot_cos_cutoff ? powf(spot, l->spot_exponent) : 0.0f;
+        return scale(scale(scale(ld3(l->cl), l->kl), att), spot);
+    }
     return scale(scale(ld3(l->cl), l->kl), att);
 }
 

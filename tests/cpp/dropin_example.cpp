@@ -196,6 +196,26 @@ int main(int argc, char** argv)
             dump(out + "/spheres.bin", balls.data(), balls.size());
         }
 
+        // --- a spot_light list instead of point lights (spot_light.h) ---
+        {
+            std::vector<spot_light<float>> spots(1);
+            spots[0].set_position(vec3(0.5f, 1.0f, 3.0f));
+            vec3 dir = normalize(vec3(0.0f) - vec3(0.5f, 1.0f, 3.0f));
+            spots[0].set_spot_direction(dir);
+            spots[0].set_spot_cutoff(0.3f);
+            spots[0].set_spot_exponent(6.0f);
+            auto kp_s = make_kernel_params(normals_per_face_binding{}, prims, prims + 1, (vec3 const*)nullptr, materials,
+                                           spots.data(), spots.data() + spots.size(), 4, 1e-3f,
+                                           vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(0.0f));
+            whitted::kernel<decltype(kp_s)> ks{ kp_s };
+            b200_sched<ray> s3;
+            s3.set_reference_order(true);
+            s3.frame(ks, sparams);
+            dump(out + "/frame_spot.bin", host_rt.color(), size_t(w) * h);
+            vsb_point_light fl = spots[0].flatten();
+            dump(out + "/spot_light.bin", &fl, 1);
+        }
+
         // --- other colour formats: the same Whitted frame into PF_RGBA8 (host) and PF_RGB8 (device) targets ---
         {
             simple_buffer_rt<PF_RGBA8, PF_UNSPECIFIED> rt8;

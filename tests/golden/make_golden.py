@@ -88,6 +88,11 @@ def surface_vectors():
     for name, kernel in TS.PRIM_NORMAL_CASES:            # kernel_params without normals, triangle and sphere scenes
         sc, fp, sd, mats, light = TS.prim_normal_frame(name, kernel, 40, 28)
         out[f"primnormal_{name}_k{kernel}"] = O.ref_frame_prim_normals(sc, fp, mats, light)
+    import math
+    import test_lights as TL
+    for kernel in (0, 1):                                # spot_light list
+        sc, fp, mats, lights = TL.case(kernel, 40, 28)
+        out[f"spot_k{kernel}"] = O.ref_frame_spot(sc, fp, mats, lights, [math.radians(a) for a in TL.ANGLES])
     for key, tex, st in SC.tex_samples():
         out["tex_" + key] = np.stack([O.ref_tex2d(tex, float(s), float(t)) for s, t in st])
     np.savez_compressed(os.path.join(HERE, "golden_surface.npz"), **out)

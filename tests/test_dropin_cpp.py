@@ -102,3 +102,11 @@ def test_dropin_program_matches_oracle(gpu):
         want_b = O.oracle_frame_surface(ssc, fp, S.SurfaceData(2, None), S.default_material(0), S.point_light(eye))
         got_b = np.fromfile(os.path.join(d, "frame_spheres.bin"), dtype=np.float32).reshape(120, 160, 4)
         assert float((np.abs(got_b - want_b).max(axis=2) > 1 / 255).mean()) == 0.0 and want_b[..., 0].std() > 0.05
+        # a spot_light list: the program's flattened light through the oracle
+        from visionaray_b200._native import LIGHT_DTYPE
+        spot = np.fromfile(os.path.join(d, "spot_light.bin"), dtype=LIGHT_DTYPE)
+        assert spot["kind"][0] == 1
+        fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
+        want_sp = O.oracle_frame(sc, fp, S.default_material(0), spot)
+        got_sp = np.fromfile(os.path.join(d, "frame_spot.bin"), dtype=np.float32).reshape(120, 160, 4)
+        assert float((np.abs(got_sp - want_sp).max(axis=2) > 1 / 255).mean()) <= 1e-3 and want_sp[..., 0].std() > 0.02

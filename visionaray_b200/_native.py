@@ -31,10 +31,10 @@ MATERIAL_DTYPE = np.dtype(
 )
 LIGHT_DTYPE = np.dtype(
     [("pos", "<f4", (3,)), ("kl", "<f4"), ("cl", "<f4", (3,)), ("att_const", "<f4"), ("att_lin", "<f4"),
-     ("att_quad", "<f4"), ("pad", "<f4", (2,))]
+     ("att_quad", "<f4"), ("kind", "<i4"), ("spot_exponent", "<f4"), ("spot_dir", "<f4", (3,)), ("spot_cos_cutoff", "<f4")]
 )
 assert HIT_DTYPE.itemsize == 32 and NODE_DTYPE.itemsize == 32
-assert MATERIAL_DTYPE.itemsize == 64 and LIGHT_DTYPE.itemsize == 48
+assert MATERIAL_DTYPE.itemsize == 64 and LIGHT_DTYPE.itemsize == 64
 
 
 class FrameParams(C.Structure):
@@ -63,7 +63,7 @@ class FrameDesc(C.Structure):
         ("ray_count", C.c_void_p),
         ("params_mem", C.c_int32), ("tile_target", C.c_int32),
         ("camera_kind", C.c_int32), ("view_matrix", C.c_float * 16), ("proj_matrix", C.c_float * 16),
-        ("color_format", C.c_int32), ("generic_materials", C.c_int32),
+        ("color_format", C.c_int32), ("generic_materials", C.c_int32), ("spot_lights", C.c_int32),
     ]
 
 
@@ -168,6 +168,8 @@ def host_lib() -> C.CDLL:
         lib.vsbh_face_normals.argtypes = [vp, sz, vp]
         lib.vsbh_primary_rays.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, vp]
         lib.vsbh_build_bvh.argtypes = [C.c_int, vp, sz, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        lib.vsbh_spot_cos_cutoff.restype = C.c_float
+        lib.vsbh_spot_cos_cutoff.argtypes = [C.c_float]
         lib.vsbh_build_bvh_ex.argtypes = [C.c_int, vp, sz, C.c_int, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
         _host_lib = lib
     return _host_lib

@@ -283,7 +283,7 @@ def set_surface(scene: "Scene", surface) -> None:
 
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
           tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False, view_matrix=None, proj_matrix=None,
-          depth=None, generic_materials=False, color_format=0):
+          depth=None, generic_materials=False, color_format=0, spot_lights=False):
     """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
     the call, returns with pixels in place); torch CUDA tensor -> device render target
     (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
@@ -326,6 +326,7 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.tile_rank, d.tile_nranks = tile_rank, tile_nranks
     d.tile_target = 1 if tiles_in_place else 0
     d.generic_materials = 1 if generic_materials else 0
+    d.spot_lights = 1 if spot_lights else 0
     d.color_format = color_format          # PF_RGBA32F 0, PF_RGBA8 1, PF_RGB32F 2 (16-byte pixels), PF_RGB8 3
     d.ray_count = p(ray_count)
     _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), stream), "vsb_frame")

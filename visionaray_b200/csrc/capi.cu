@@ -25,9 +25,9 @@ namespace
 
 static_assert(sizeof(vsb_ray) == 32 && sizeof(vsb_hit) == 32 && sizeof(vsb_bvh_node) == 32, "ABI layouts");
 static_assert(sizeof(vsb_triangle) == 64 && sizeof(vsb_sphere) == 48, "ABI layouts");
-static_assert(sizeof(vsb_material) == 64 && sizeof(vsb_point_light) == 48, "ABI layouts");
+static_assert(sizeof(vsb_material) == 64 && sizeof(vsb_point_light) == 64, "ABI layouts");
 static_assert(sizeof(vsb_frame_params) == sizeof(vsb::FrameParams), "frame params layout");
-static_assert(sizeof(vsb::Material) == 64 && sizeof(vsb::PointLight) == 48, "device layouts");
+static_assert(sizeof(vsb::Material) == 64 && sizeof(vsb::PointLight) == 64, "device layouts");
 static_assert(sizeof(vsb::Node80) == 80 && sizeof(vsb::TriRec) == 48 && sizeof(vsb::SphRec) == 32, "wide layouts");
 
 const int BLOCK = 128;
@@ -447,6 +447,10 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     bool generic_materials = d->generic_materials != 0;
     if (d->params_mem == VSB_MEM_HOST && d->materials)
         for (int i = 0; i < p.n_materials; ++i) generic_materials |= d->materials[i].kind >= VSB_MAT_EMISSIVE;
+    // spot lights ride on the same (SURF) instantiations as the generic material list
+    bool spot_lights = d->spot_lights != 0;
+    if (d->params_mem == VSB_MEM_HOST && d->lights)
+        for (int i = 0; i < p.n_lights; ++i) spot_lights |= d->lights[i].kind == VSB_LIGHT_SPOT;
     if (d->params_mem == VSB_MEM_HOST)
     {
         // small per-frame parameter block: materials | lights (what cuda_sched copies as kernel
@@ -458,10 +462,10 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
             VSB_CUDA(cudaMemcpyAsync(a, d->normals, n_normals * 16, cudaMemcpyHostToDevice, st));
             fl.ctx.normals = reinterpret_cast<const float4*>(a);
         }
-        rc = stage(4, (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64 + (size_t)(p.n_lights > 0 ? p.n_lights : 1) * 48 + 64, &b); if (rc) return rc;
+        rc = stage(4, (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64 + (size_t)(p.n_lights > 0 ? p.n_lights : 1) * sizeof(vsb_point_light) + 64, &b); if (rc) return rc;
         if (d->materials) VSB_CUDA(cudaMemcpyAsync(b, d->materials, (size_t)p.n_materials * 64, cudaMemcpyHostToDevice, st));
         c = (char*)b + (size_t)(p.n_materials > 0 ? p.n_materials : 1) * 64;
-        if (d->lights && p.n_lights > 0) VSB_CUDA(cudaMemcpyAsync(c, d->lights, (size_t)p.n_lights * 48, cudaMemcpyHostToDevice, st));
+        if (d->lights && p.n_lights > 0) VSB_CUDA(cudaMemcpyAsync(c, d->lights, (size_t)p.n_lights * sizeof(vsb_point_light), cudaMemcpyHostToDevice, st));
         fl.ctx.materials = reinterpret_cast<const vsb::Material*>(b);
         fl.ctx.lights = reinterpret_cast<const vsb::PointLight*>(c);
     }
@@ -615,7 +619,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         // kernel_params with a surface description or a generic material list (see shade.cuh)
         {
             const bool ext = p.pixel_sampler >= VSB_PS_SSAA2 || d->camera_kind == VSB_CAM_MATRIX || d->color_format != VSB_PF_RGBA32F;
-            const bool surf = p.kernel != VSB_KERNEL_AO && (fl.ctx.surf.enabled || generic_materials);
+            const bool surf = p.kernel != VSB_KERNEL_AO && (fl.ctx.surf.enabled || generic_materials || spot_lights);
             switch (p.kernel * 4 + (ext ? 2 : 0) + (surf ? 1 : 0))
             {
             case 0:  VSB_LAUNCH_FRAME(0, false, false); break;

@@ -58,6 +58,9 @@ void vsbh_face_normals(const void* tris, size_t n, void* normals16)
 int vsbh_build_bvh_ex(int prim_kind, const void* prims, size_t n, int spatial_splits, void* nodes_out, size_t nodes_cap,
                       size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx);
 
+// spot_light<T>::set_spot_cutoff keeps cos(cutoff) (detail/spot_light.inl:143-149): the host's cosf, as the adaptor's setter
+float vsbh_spot_cos_cutoff(float cutoff_radians) { return std::cos(cutoff_radians); }
+
 int vsbh_build_bvh(int prim_kind, const void* prims, size_t n, void* nodes_out, size_t nodes_cap,
                    size_t* n_nodes, uint32_t* idx_out, size_t idx_cap, size_t* n_idx)
 {

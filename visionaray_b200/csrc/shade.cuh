@@ -40,7 +40,7 @@ VSB_HD float max0(float x) { return 0.0f < x ? x : 0.0f; }
 #define VSB_INV_PI  0.31830988618379067154f
 
 struct Material { float ca[3], ka, cd[3], kd, cs[3], ks, spec_exp; int32_t kind; float pad[2]; };
-struct PointLight { float pos[3], kl, cl[3], att_const, att_lin, att_quad, pad[2]; };
+struct PointLight { float pos[3], kl, cl[3], att_const, att_lin, att_quad; int32_t kind; float spot_exponent, spot_dir[3], spot_cos_cutoff; };
 
 struct FrameParams   // == vsb_frame_params
 {
@@ -131,10 +131,20 @@ VSB_HD void primary_ray(const FrameCtx& f, float x, float y, V3& ori, V3& dir)
 }
 
 // point_light::intensity -- detail/point_light.inl:11-27
+// SPOT: the instantiation handles spot lights (the lean frame programs are point-light only: the cone costs the
+// cfg2 frame 2 % even when no light uses it)
+template <bool SPOT>
 VSB_HD V3 light_intensity(const PointLight& l, V3 pos)
 {
     const float dist = vlength(vsub(ld3(l.pos), pos));
-    const float att = 1.0f / (l.att_const + l.att_lin * dist + l.att_quad * dist * dist);
+    float att = 1.0f / (l.att_const + l.att_lin * dist + l.att_quad * dist * dist);
+    if (SPOT && l.kind == 1)
+    {
+        // spot_light::intensity -- detail/spot_light.inl:14-38
+        const V3 to = vnormalize(vsub(pos, ld3(l.pos)));
+        const float spot = vdot(ld3(l.spot_dir), to);
+        att *= spot > l.spot_cos_cutoff ? powf(spot, l.spot_exponent) : 0.0f;
+    }
     return v3(l.cl[0] * l.kl * att, l.cl[1] * l.kl * att, l.cl[2] * l.kl * att);
 }
 
@@ -160,7 +170,7 @@ VSB_HD V3 shade_light(const Material& m, const PointLight& l, V3 pos, V3 n, V3 w
     const float ndotl = max0(vdot(n, wi));
     V3 f = lambert_f(m);
     if (m.kind == 0) { const V3 s = blinn_f(m, n, wo, wi); f = v3(f.x + s.x, f.y + s.y, f.z + s.z); }
-    const V3 li = light_intensity(l, pos);
+    const V3 li = light_intensity<false>(l, pos);
     return v3(f.x * VSB_PI * li.x * ndotl, f.y * VSB_PI * li.y * ndotl, f.z * VSB_PI * li.z * ndotl);
 }
 
@@ -400,7 +410,7 @@ VSB_HD V3 shade_light_ext(const Material& m, const Surface& S, const PointLight&
     V3 f = lambert_f(m);
     f = v3(f.x * S.tex.x, f.y * S.tex.y, f.z * S.tex.z);
     if (m.kind == 0) { const V3 s = blinn_f(m, n, wo, wi); f = v3(f.x + s.x, f.y + s.y, f.z + s.z); }
-    const V3 li = light_intensity(l, pos);
+    const V3 li = light_intensity<true>(l, pos);
     return v3(f.x * VSB_PI * li.x * ndotl, f.y * VSB_PI * li.y * ndotl, f.z * VSB_PI * li.z * ndotl);
 }
 
