@@ -157,7 +157,10 @@ VSB_HD V3 blinn_f(const Material& m, V3 n, V3 wo, V3 wi)
     const float hdotn = max0(vdot(h, n));
     float sat = vdot(wi, h);
     sat = sat < 0.0f ? 0.0f : (sat > 1.0f ? 1.0f : sat);
-    const float sch = powf(1.0f - sat, 5.0f);
+    // pow(1 - sat, 5) of brdf.h:113 as four multiplications: within 2 ulp of powf, and ~150 instructions less in
+    // every frame program (colour arithmetic: pixel parity is a 1/255 tolerance)
+    const float om = 1.0f - sat, om2 = om * om;
+    const float sch = om2 * om2 * om;
     const float nfactor = (m.spec_exp + 2.0f) / (8.0f * VSB_PI);
     const float ph = powf(hdotn, m.spec_exp) * nfactor;
     const float sx = m.cs[0] * m.ks, sy = m.cs[1] * m.ks, sz = m.cs[2] * m.ks;
