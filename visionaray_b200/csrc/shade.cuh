@@ -162,7 +162,13 @@ VSB_HD V3 blinn_f(const Material& m, V3 n, V3 wo, V3 wi)
     const float om = 1.0f - sat, om2 = om * om;
     const float sch = om2 * om2 * om;
     const float nfactor = (m.spec_exp + 2.0f) / (8.0f * VSB_PI);
+    // pow(hdotn, exp) with hdotn in [0, 1]: exp2(exp * log2(hdotn)) on the SFU (relative error ~1e-6 * exp, far
+    // inside the 1/255 pixel tolerance) instead of the ~150-instruction powf; 0^0 = 1 kept
+#if defined(__CUDA_ARCH__)
+    const float ph = (m.spec_exp == 0.0f ? 1.0f : __powf(hdotn, m.spec_exp)) * nfactor;
+#else
     const float ph = powf(hdotn, m.spec_exp) * nfactor;
+#endif
     const float sx = m.cs[0] * m.ks, sy = m.cs[1] * m.ks, sz = m.cs[2] * m.ks;
     return v3((sx + (1.0f - sx) * sch) * ph, (sy + (1.0f - sy) * sch) * ph, (sz + (1.0f - sz) * sch) * ph);
 }
