@@ -174,6 +174,11 @@ extern "C" int vsb_init(int device)
     VSB_CUDA(cudaEventCreate(&g.ev1));
     VSB_CUDA(cudaMalloc(&g.d_work, 64 * sizeof(unsigned long long)));   // [0] queue, [1] ray count, [2..33] band queues
     VSB_CUDA(cudaMalloc(&g.d_scenes, sizeof(vsb::DeviceScene) * MAX_SCENES));
+    {
+        float table[256];
+        for (int u = 0; u < 256; ++u) table[u] = (float)((double)(float)u / 255.0);      // unorm_to_float<8>, math/detail/unorm.inl:26-31
+        VSB_CUDA(cudaMemcpyToSymbol(vsb::c_unorm8_to_float, table, sizeof(table)));
+    }
     g.inited = true;
     return VSB_OK;
 }

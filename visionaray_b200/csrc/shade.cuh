@@ -39,6 +39,27 @@ VSB_HD float max0(float x) { return 0.0f < x ? x : 0.0f; }
 #define VSB_TWO_PI  6.28318530717958647692f
 #define VSB_INV_PI  0.31830988618379067154f
 
+// unorm<8> <-> float (math/detail/unorm.inl:18-31): texels and 8-bit render targets
+VSB_HD uint32_t float_to_unorm8(float f)        // math/detail/unorm.inl:18-24, after the clamp of color_conversion.h:224
+{
+    f = f < 0.0f ? 0.0f : (f > 1.0f ? 1.0f : f);
+    return (uint32_t)((double)f * 255.0);
+}
+#if defined(__CUDACC__)
+// float(u) / double(255) for u = 0..255 (math/detail/unorm.inl:26-31), tabulated by vsb_init(): the exact values
+// without three or four inlined fp64 divisions per texel / pixel in programs that are sensitive to code size
+__constant__ float c_unorm8_to_float[256];
+#endif
+VSB_HD float unorm8_to_float(uint32_t u)
+{
+#if defined(__CUDA_ARCH__)
+    return c_unorm8_to_float[u & 255u];
+#else
+    return (float)((double)(float)u / 255.0);
+#endif
+}
+
+
 struct Material { float ca[3], ka, cd[3], kd, cs[3], ks, spec_exp; int32_t kind; float pad[2]; };
 struct PointLight { float pos[3], kl, cl[3], att_const, att_lin, att_quad; int32_t kind; float spot_exponent, spot_dir[3], spot_cos_cutoff; };
 
@@ -314,7 +335,7 @@ __device__ inline V3 tex2d_rgb(const DevTexture& t, float s, float tt)
         q[1] = __float2int_rz(lerp1(lerp1((float)e00.y, (float)e10.y, u), lerp1((float)e01.y, (float)e11.y, u), v));
         q[2] = __float2int_rz(lerp1(lerp1((float)e00.z, (float)e10.z, u), lerp1((float)e01.z, (float)e11.z, u), v));
     }
-    return v3(__double2float_rn((double)q[0] / 255.0), __double2float_rn((double)q[1] / 255.0), __double2float_rn((double)q[2] / 255.0));
+    return v3(unorm8_to_float((uint32_t)q[0]), unorm8_to_float((uint32_t)q[1]), unorm8_to_float((uint32_t)q[2]));
 }
 
 // get_normal(hr, triangle) = normalize(cross(e1, e2)) (get_normal.h:96-101) of primitive(i) =
@@ -455,13 +476,6 @@ VSB_HD V3 material_sample_ext(const Material& m, const Surface& S, V3 n, V3 wo, 
 }
 
 // ---- colour formats of the render target (pixel_access store / get, detail/color_conversion.h) ----
-VSB_HD uint32_t float_to_unorm8(float f)        // math/detail/unorm.inl:18-24, after the clamp of color_conversion.h:224
-{
-    f = f < 0.0f ? 0.0f : (f > 1.0f ? 1.0f : f);
-    return (uint32_t)((double)f * 255.0);
-}
-VSB_HD float unorm8_to_float(uint32_t u) { return (float)((double)(float)u / 255.0); }      // :26-31
-
 #if defined(__CUDACC__)
 __device__ __forceinline__ int pixel_bytes(int format) { return format == 1 ? 4 : (format == 3 ? 3 : 16); }
 
