@@ -217,7 +217,9 @@ VSB_HD V3 cosine_sample_hemisphere(float u1, float u2)
 {
     const float r = rn_sqrt(u1);
     const float theta = rn_mul(VSB_TWO_PI, u2);
-    return v3(rn_mul(r, cosf(theta)), rn_mul(r, sinf(theta)), rn_sqrt(max0(rn_sub(1.0f, u1))));
+    float sn, cs;
+    sincosf(theta, &sn, &cs);          // one range reduction for both (same values as sinf / cosf)
+    return v3(rn_mul(r, cs), rn_mul(r, sn), rn_sqrt(max0(rn_sub(1.0f, u1))));
 }
 
 VSB_HD V3 hemisphere_dir(V3 u, V3 v, V3 w, V3 sp)
@@ -249,7 +251,9 @@ VSB_HD V3 blinn_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, uint3
     const float phi = rn_mul(u2, VSB_TWO_PI);
     V3 u, v;
     ortho_basis(u, v, n);
-    const V3 h = vnormalize(vadd(vadd(vscale(u, rn_mul(sintheta, cosf(phi))), vscale(v, rn_mul(sintheta, sinf(phi)))), vscale(n, costheta)));
+    float sp, cp;
+    sincosf(phi, &sp, &cp);
+    const V3 h = vnormalize(vadd(vadd(vscale(u, rn_mul(sintheta, cp)), vscale(v, rn_mul(sintheta, sp))), vscale(n, costheta)));
     wi = vreflect(wo, h);
     const float vdoth = vdot(wo, h);
     pdf = ((e + 1.0f) * powf(costheta, e)) / (2.0f * VSB_PI * 4.0f * vdoth);
@@ -259,13 +263,17 @@ VSB_HD V3 blinn_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, uint3
 // plastic::sample_impl -- detail/material/plastic.inl:186-229; matte -- matte.inl:147-155
 VSB_HD V3 material_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, uint32_t& samp)
 {
-    if (m.kind == 1) return lambert_sample(m, n, wi, pdf, samp);
-    float prob_diff = ((m.cd[0] + m.cd[1] + m.cd[2]) / 3.0f) * m.kd;
-    float prob_spec = ((m.cs[0] + m.cs[1] + m.cs[2]) / 3.0f) * m.ks;
-    if (prob_diff == 0.0f && prob_spec == 0.0f) { prob_diff = 0.5f; prob_spec = 0.5f; }
-    prob_diff = prob_diff / (prob_diff + prob_spec);
-    const float u = sampler_next(samp);
-    if (u < prob_diff) return lambert_sample(m, n, wi, pdf, samp);
+    // matte always takes the diffuse lobe; plastic draws u and picks (one copy of each lobe's code)
+    bool diffuse = true;
+    if (m.kind != 1)
+    {
+        float prob_diff = ((m.cd[0] + m.cd[1] + m.cd[2]) / 3.0f) * m.kd;
+        float prob_spec = ((m.cs[0] + m.cs[1] + m.cs[2]) / 3.0f) * m.ks;
+        if (prob_diff == 0.0f && prob_spec == 0.0f) { prob_diff = 0.5f; prob_spec = 0.5f; }
+        prob_diff = prob_diff / (prob_diff + prob_spec);
+        diffuse = sampler_next(samp) < prob_diff;
+    }
+    if (diffuse) return lambert_sample(m, n, wi, pdf, samp);
     return blinn_sample(m, n, wo, wi, pdf, samp);
 }
 
