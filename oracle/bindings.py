@@ -296,6 +296,21 @@ def ref_frame_spot(scene, fp, materials, lights, cutoff_angles, rgba=None, nthre
     return rgba
 
 
+def ref_frame_generic(scene, fp, surface, materials, lights, rgba=None, nthreads=0):
+    """simple / whitted over an index_bvh<generic_primitive<triangle, sphere>> with a normals array."""
+    if rgba is None:
+        rgba = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+    lib = ref_lib()
+    vp, sz = C.c_void_p, C.c_size_t
+    lib.ref_frame_generic.argtypes = [vp, vp, sz, vp, sz, vp, sz, C.c_int, vp, vp, vp, vp, C.c_int]
+    rc = lib.ref_frame_generic(C.byref(fp), _p(scene.prims), scene.prims.shape[0], _p(scene.nodes), scene.nodes.shape[0],
+                               _p(scene.indices), scene.indices.shape[0], surface.normal_binding, _p(surface.normals),
+                               _p(materials), _p(lights), _p(rgba), nthreads or (os.cpu_count() or 1))
+    if rc != 0:
+        raise ValueError("ref_frame_generic: unsupported kernel")
+    return rgba
+
+
 def oracle_tex2d(tex, s, t):
     o = make_texture(tex)
     out = np.zeros(4, dtype=np.float32)

@@ -451,6 +451,34 @@ extern "C" int ref_frame_spot(void const* fp_, void const* prims, size_t n_prims
     return 0;
 }
 
+// index_bvh<generic_primitive<triangle, sphere>> with a normals array (per face / per vertex): the visitor of
+// detail/generic_primitive_get_normal.h picks the alternative's rule.  simple / whitted kernels.
+extern "C" int ref_frame_generic(void const* fp_, void const* prims, size_t n_prims, void const* nodes, size_t n_nodes,
+                                 uint32_t const* indices, size_t n_idx, int normal_binding, float const* normals16,
+                                 void const* mats_, void const* lights_, float* rgba, int nthreads)
+{
+    frame_params fp;
+    std::memcpy(&fp, fp_, sizeof(fp));
+    if (fp.kernel > 1) return -1;
+    auto ref = make_ref<gen_t>(prims, n_prims, nodes, n_nodes, indices, n_idx);
+    scene_host s{ tri_ref_t() };
+    fill_scene(s, fp, nullptr, 0, (mat_pod const*)mats_, (light_pod const*)lights_);
+    aligned_vector<gen_mat_t> mats;
+    for (int i = 0; i < fp.n_materials; ++i) mats.push_back(make_generic(((mat_pod const*)mats_)[i]));
+    vec3 const* normals = reinterpret_cast<vec3 const*>(normals16);
+    vec4 bg(fp.bg[0], fp.bg[1], fp.bg[2], fp.bg[3]);
+    vec4 amb(fp.ambient[0], fp.ambient[1], fp.ambient[2], fp.ambient[3]);
+    auto lb = s.lights.data();
+    auto le = s.lights.data() + s.lights.size();
+    if (normal_binding == 1)
+        run_surface_kernels(make_kernel_params(normals_per_vertex_binding{}, &ref, &ref + 1, normals, mats.data(), lb, le,
+                                               fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads);
+    else
+        run_surface_kernels(make_kernel_params(normals_per_face_binding{}, &ref, &ref + 1, normals, mats.data(), lb, le,
+                                               fp.num_bounces, fp.epsilon, bg, amb), fp, rgba, nthreads);
+    return 0;
+}
+
 extern "C" void ref_tex2d(void const* tex_, float s, float t, float* out4)
 {
     tex_pod const& tp = *(tex_pod const*)tex_;

@@ -248,14 +248,23 @@ static void get_surface(const frame_ctx* f, const vso_hit* h, v3 pos, surf_t* S)
         S->gn = S->sn = ld3(f->normals + 4 * (size_t)h->prim_id);   /* normals[hr.prim_id], get_normal.h:28-37 */
         return;
     }
-    if (sf->normal_binding == 0) S->gn = S->sn = ld3(sf->normals + 4 * (size_t)h->prim_id);
+    /* a generic_primitive: the visitor applies the alternative's rule (detail/generic_primitive_get_normal.h) -- a
+     * sphere has no per-primitive normals under any binding (num_normals == 0) and takes get_normal(hr, sphere) */
+    const vso_generic_primitive* gp = NULL;
+    if (f->b->prim_kind == 2)
+    {
+        size_t gi = f->b->indices ? f->b->indices[h->prim_list_index] : h->prim_list_index;
+        gp = (const vso_generic_primitive*)f->b->prims + gi;
+    }
+    if (gp && gp->which != 1) S->gn = S->sn = primitive_normal(f->b, h->prim_list_index, pos);
+    else if (sf->normal_binding == 0) S->gn = S->sn = ld3(sf->normals + 4 * (size_t)h->prim_id);
     else if (sf->normal_binding == 2) S->gn = S->sn = primitive_normal(f->b, h->prim_list_index, pos);
     else
     {
         /* params.prims.begin[i].primitive(hr.primitive_list_index), get_surface.h:313-327; bvh.h:226-229 */
         const vso_bvh* b = f->b;
         size_t pi = b->indices ? b->indices[h->prim_list_index] : h->prim_list_index;
-        const vso_triangle* tri = (const vso_triangle*)b->prims + pi;
+        const vso_triangle* tri = gp ? (const vso_triangle*)gp->storage : (const vso_triangle*)b->prims + pi;
         S->gn = normalize(cross(ld3(tri->e1), ld3(tri->e2)));
         const float* n = sf->normals + 12 * (size_t)h->prim_id;
         S->sn = normalize(lerp3(ld3(n), ld3(n + 4), ld3(n + 8), h->u, h->v));

@@ -140,6 +140,11 @@ def generic_vectors():
            "closest": O.ref_query(ref, rays, False, FLT_MAX).view(np.uint8),
            "any": O.ref_query(ref, rays, True, 0.3).view(np.uint8),
            "multi8": O.ref_multi_hit(ref, rays[:1500], 8).view(np.uint8)}
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import test_generic_primitive as TG
+    for kernel, nb in TG.FRAME_CASES:                  # frames: get_surface() over the variant with a normals array
+        fsc, fp, sd, mats, light = TG.frame_case(kernel, nb, 40, 28)
+        out[f"frame_k{kernel}_nb{nb}"] = O.ref_frame_generic(fsc, fp, sd, mats, light)
     np.savez_compressed(os.path.join(HERE, "golden_generic.npz"), **out)
     print("wrote golden_generic.npz:", sc.n_prims, "primitives,", int(tags.sum()), "spheres")
 

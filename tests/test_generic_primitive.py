@@ -76,6 +76,52 @@ def test_host_instantiation_on_mixed_leaves(gen):
     w.close()
 
 
+def frame_case(kernel, nb, w=96, h=64):
+    sc = S.make_scene("generic", 0.05)
+    sc.prims.view(np.uint32)[:, 0] = (np.arange(sc.n_prims) // 3) % 4
+    fp = S.frame_params(kernel, w, h, (0.5, 0.6, 2.6), (0.5, 0.5, 0.5), n_materials=4, num_bounces=4, ambient=(0.3, 0.3, 0.3, 1.0))
+    sd = S.SurfaceData(nb, S.generic_normals(sc.prims, nb == 1))
+    return sc, fp, sd, S.generic_materials(), S.point_light((1.5, 2.0, 2.5))
+
+
+FRAME_CASES = [(0, 0), (0, 1), (1, 0), (1, 1)]        # (kernel, normal binding)
+
+
+@pytest.mark.skipif(not O.ref_available(), reason="oracle/_ref is only built where /root/reference exists")
+@pytest.mark.parametrize("kernel,nb", FRAME_CASES)
+def test_frames_oracle_matches_reference_headers(kernel, nb):
+    """get_surface() over a variant: triangles follow the normal binding, spheres take get_normal(hr, sphere)
+    (detail/generic_primitive_get_normal.h)."""
+    sc, fp, sd, mats, light = frame_case(kernel, nb)
+    got = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    want = O.ref_frame_generic(sc, fp, sd, mats, light)
+    assert np.abs(got - want).max() <= 1e-6 and want[..., :3].std() > 0.1
+
+
+@pytest.mark.parametrize("kernel,nb", FRAME_CASES)
+def test_frames_oracle_matches_fixture(kernel, nb):
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "golden_generic.npz"))
+    sc, fp, sd, mats, light = frame_case(kernel, nb, 40, 28)
+    assert np.abs(O.oracle_frame_surface(sc, fp, sd, mats, light) - g[f"frame_k{kernel}_nb{nb}"]).max() <= 1e-6
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("kernel,nb", FRAME_CASES)
+def test_gpu_frames_over_mixed_leaves(gpu, kernel, nb):
+    sc, fp, sd, mats, light = frame_case(kernel, nb, 160, 112)
+    want = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    dev = gpu.Scene(sc)
+    try:
+        gpu.set_surface(dev, sd)
+        for trav in (gpu.TRAVERSE_EXACT, gpu.TRAVERSE_WIDE):
+            img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+            gpu.frame(dev, fp, None, mats, light, img, traverse=trav)
+            bad = float((np.abs(img - want).max(axis=2) > 1.0 / 255.0).mean())
+            assert bad <= (0.0 if trav == gpu.TRAVERSE_EXACT else 1e-3), (kernel, nb, trav, bad)
+    finally:
+        dev.close()
+
+
 @pytest.mark.gpu
 def test_gpu_mixed_leaves(gpu, gen):
     sc, rays, gold, rec = gen

@@ -399,7 +399,8 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         // simple / whitted only
         const bool sphere_ok = scenes[i]->prim_kind == VSB_PRIM_SPHERE && scenes[i]->surf.enabled &&
                                scenes[i]->surf.normal_binding == VSB_NORMALS_FROM_PRIMITIVE && p.kernel <= VSB_KERNEL_WHITTED;
-        if (scenes[i]->prim_kind != VSB_PRIM_TRIANGLE && !sphere_ok) return VSB_ERR_UNSUPPORTED;
+        const bool generic_ok = scenes[i]->prim_kind == VSB_PRIM_GENERIC && scenes[i]->surf.enabled && p.kernel <= VSB_KERNEL_WHITTED;
+        if (scenes[i]->prim_kind != VSB_PRIM_TRIANGLE && !sphere_ok && !generic_ok) return VSB_ERR_UNSUPPORTED;
     }
     for (int i = 0; i < n_scenes; ++i)
     {

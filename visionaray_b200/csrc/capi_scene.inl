@@ -422,7 +422,11 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
     if (!desc->normals && desc->normal_binding != VSB_NORMALS_FROM_PRIMITIVE) return VSB_ERR_BAD_ARG;
     // spheres: only get_normal(hr, sphere) applies (bindings, lerped colours and tex coords are triangle rules); a
     // generic_primitive needs a normals array in the reference too (get_surface.h:218-245) and has no rule here
-    if (s->prim_kind == VSB_PRIM_GENERIC) return VSB_ERR_UNSUPPORTED;
+    // generic_primitive: per-face / per-vertex normals for its triangles, get_normal(hr, sphere) for its spheres
+    // (detail/generic_primitive_get_normal.h); no colours / tex coords, and a normals array is required (get_surface.h:218-245)
+    if (s->prim_kind == VSB_PRIM_GENERIC &&
+        (desc->normal_binding == VSB_NORMALS_FROM_PRIMITIVE || desc->color_binding != VSB_COLORS_NONE || desc->tex_coords))
+        return VSB_ERR_UNSUPPORTED;
     if (s->prim_kind == VSB_PRIM_SPHERE &&
         (desc->normal_binding != VSB_NORMALS_FROM_PRIMITIVE || desc->color_binding == VSB_COLORS_PER_VERTEX || desc->tex_coords))
         return VSB_ERR_UNSUPPORTED;
@@ -486,7 +490,12 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         c.ref_spheres = reinterpret_cast<const float4*>(s->d_prims);
         c.indices = s->d_indices;
     }
-    else if (desc->normal_binding != VSB_NORMALS_PER_FACE)
+    if (s->prim_kind == VSB_PRIM_GENERIC)
+    {
+        c.ref_generic = reinterpret_cast<const float4*>(s->d_prims);
+        c.indices = s->d_indices;
+    }
+    if (s->prim_kind != VSB_PRIM_SPHERE && desc->normal_binding != VSB_NORMALS_PER_FACE)
     {
         const size_t n_list = s->d_indices ? s->n_idx : s->n_prims;
         float4* gn = nullptr;
@@ -494,7 +503,7 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         if (e != cudaSuccess) { for (void* q : s->surf_allocs) cudaFree(q); s->surf_allocs.clear(); return (int)e; }
         s->surf_allocs.push_back(gn);
         vsb::surface_geo_normals_kernel<<<(unsigned)((n_list + 255) / 256), 256, 0, g.stream>>>(
-            reinterpret_cast<const float4*>(s->d_prims), s->d_indices, n_list, gn);
+            s->prim_kind, s->d_prims, s->d_indices, n_list, gn);
         ++g.launches;
         e = cudaStreamSynchronize(g.stream);
         if (e != cudaSuccess) { for (void* q : s->surf_allocs) cudaFree(q); s->surf_allocs.clear(); return (int)e; }

@@ -90,6 +90,8 @@ struct SurfCtx
     const DevTexture* textures;     // by geom_id
     const float4*     ref_spheres;  // binding "none" on a sphere scene: the basic_sphere records (3 x 16 B) ...
     const uint32_t*   indices;      // ... and the index_bvh indirection (null for a plain bvh)
+    const float4*     ref_generic;  // generic_primitive scene: the 80-byte variant records (5 x 16 B, `which` in word 16); a
+                                    // sphere alternative takes get_normal(hr, sphere) under every binding
     const float4*     geo_normals;  // triangles, per vertex / no binding: normalize(cross(e1, e2)) of primitive(i), by primitive_list_index i
                                     // (precomputed by surface_geo_normals_kernel: one load at the hit instead of
                                     // indices[i] -> 64-byte triangle -> cross -> normalize)
@@ -349,13 +351,15 @@ __device__ inline V3 tex2d_rgb(const DevTexture& t, float s, float tt)
 // get_normal(hr, triangle) = normalize(cross(e1, e2)) (get_normal.h:96-101) of primitive(i) =
 // prims[indices[i]] (bvh.h:226-229) for every position i of the primitive list, same single-rounding
 // arithmetic as at shading time
-__global__ void surface_geo_normals_kernel(const float4* __restrict__ ref_prims, const uint32_t* __restrict__ indices,
+__global__ void surface_geo_normals_kernel(int prim_kind, const void* __restrict__ prims, const uint32_t* __restrict__ indices,
                                            size_t n_list, float4* __restrict__ out)
 {
     const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_list) return;
     const size_t pi = indices ? indices[i] : i;
-    const float4 e1 = ref_prims[pi * 4 + 2], e2 = ref_prims[pi * 4 + 3];
+    const float4* rec = reinterpret_cast<const float4*>(reinterpret_cast<const char*>(prims) + pi * prim_stride(prim_kind));
+    if (!prim_is_triangle(prim_kind, rec)) { out[i] = make_float4(0.0f, 0.0f, 0.0f, 0.0f); return; }   // a sphere of a generic scene
+    const float4 e1 = rec[2], e2 = rec[3];
     const V3 g = vnormalize(vcross(v3(e1.x, e1.y, e1.z), v3(e2.x, e2.y, e2.z)));
     out[i] = make_float4(g.x, g.y, g.z, 0.0f);
 }
@@ -374,7 +378,21 @@ __device__ __forceinline__ Surface surface_at(const FrameCtx& f, uint32_t prim_i
         S.gn = S.sn = v3(nn.x, nn.y, nn.z);
         return S;
     }
-    if (sf.normal_binding == 0)
+    bool sphere_alternative = false;
+    if (sf.ref_generic)
+    {
+        // detail/generic_primitive_get_normal.h: the visitor applies the rule of the alternative the variant holds
+        const size_t pi = sf.indices ? __ldg(sf.indices + list_index) : list_index;
+        const float4* rec = sf.ref_generic + pi * 5;
+        if (__float_as_uint(__ldg(rec + 4).x) != 1u)
+        {
+            const float4 c = __ldg(rec + 1), r = __ldg(rec + 2);
+            S.gn = S.sn = v3(rn_div(rn_sub(pos.x, c.x), r.x), rn_div(rn_sub(pos.y, c.y), r.x), rn_div(rn_sub(pos.z, c.z), r.x));
+            sphere_alternative = true;
+        }
+    }
+    if (sphere_alternative) { }
+    else if (sf.normal_binding == 0)
     {
         const float4 nn = __ldg(sf.normals + prim_id);
         S.gn = S.sn = v3(nn.x, nn.y, nn.z);
