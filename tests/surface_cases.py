@@ -47,7 +47,7 @@ def tex_samples():
     rng = np.random.default_rng(17)
     out = []
     for filt in (0, 1):
-        for am in ((0, 0), (1, 1), (2, 2), (0, 2), (1, 0)):
+        for am in ((0, 0), (1, 1), (2, 2), (0, 2), (1, 0), (3, 3)):      # 3 = Border: clamps, like the reference
             tex = S.checker_texture(13, 7, 5, filt, am)
             st = rng.uniform(-3.0, 3.0, (64, 2)).astype(np.float32)
             out.append((f"f{filt}_a{am[0]}{am[1]}", tex, st))

@@ -181,6 +181,26 @@ def test_gpu_normals_from_the_primitive(gpu, name, kernel):
 
 
 @pytest.mark.gpu
+def test_gpu_border_addressing_clamps(gpu):
+    """tex_address_mode Border falls through to Clamp in the reference (filter/common.h:41-46)."""
+    sc, fp, sd, mats, light = SC.case("simple_face_tex_linear", 128, 96)
+    for t in sd.textures:
+        if t is not None:
+            t.address = (3, 3)
+    want = O.oracle_frame_surface(sc, fp, sd, mats, light)
+    clamp = S.make_surface(sc, 0, 0, True, n_geoms=SC.N_GEOMS, tex_filter=1, tex_address=(2, 2))
+    assert want.tobytes() == O.oracle_frame_surface(sc, fp, clamp, mats, light).tobytes()
+    dev = gpu.Scene(sc)
+    try:
+        gpu.set_surface(dev, sd)
+        img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
+        gpu.frame(dev, fp, None, mats, light, img, traverse=gpu.TRAVERSE_EXACT)
+        assert _frac_bad(img, want) == 0.0
+    finally:
+        dev.close()
+
+
+@pytest.mark.gpu
 def test_gpu_ids_are_checked_against_array_sizes(gpu):
     """prim_id indexes normals / colours / tex coords, geom_id the materials: the reference trusts them, the
     library computes the scene's largest ids once and refuses arrays they would leave."""
