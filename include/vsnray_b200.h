@@ -105,8 +105,9 @@ enum { VSB_MAT_PLASTIC = 0, VSB_MAT_MATTE = 1, VSB_MAT_EMISSIVE = 2, VSB_MAT_MIR
 /* texture_ref<vector<4, unorm<8>>, 2> (texture/detail/texture2d.h, texture_common.h:36-92): RGBA8
  * texels, row-major, texel(x, y) = data[y * width + x].  width or height 0 = "no texture" (tex_color 1,
  * get_surface.h:443-445).  filter: tex_filter_mode Nearest / Linear; address: tex_address_mode per axis
- * (texture/forward.h:18-34; BSpline / CardinalSpline filters are not supported). */
-enum { VSB_TEX_NEAREST = 0, VSB_TEX_LINEAR = 1 };
+ * (texture/forward.h:18-34). */
+enum { VSB_TEX_NEAREST = 0, VSB_TEX_LINEAR = 1, VSB_TEX_BSPLINE = 2, VSB_TEX_CARDINAL_SPLINE = 4 };   /* tex_filter_mode; 3 =
+     BSplineInterpol needs the reference's host prefilter (texture/detail/prefilter.h) and is not supported */
 enum { VSB_TEX_WRAP = 0, VSB_TEX_MIRROR = 1, VSB_TEX_CLAMP = 2, VSB_TEX_BORDER = 3 };   /* Border falls through to Clamp in the
                                                                                           reference too (filter/common.h:41-46) */
 typedef struct vsb_texture {

@@ -169,39 +169,116 @@ static float map_tex_coord(float coord, int texsize, int mode)
 
 static inline float lerp1(float a, float b, float x) { return (1.0f - x) * a + x * b; }   /* math/detail/math.h:459-464 */
 
+/* spline weights -- texture/detail/filter/common.h:104-192.  The expressions mix float products with double
+ * literals exactly as written there (a is a float; "a * a" alone is a float product, "0.5 * a" a double one). */
+static float bs_w0(float a) { return (float)((1.0 / 6.0) * (-(a * a * a) + 3.0 * a * a - 3.0 * a + 1.0)); }
+static float bs_w1(float a) { return (float)((1.0 / 6.0) * (3.0 * a * a * a - 6.0 * a * a + 4.0)); }
+static float bs_w2(float a) { return (float)((1.0 / 6.0) * (-3.0 * a * a * a + 3.0 * a * a + 3.0 * a + 1.0)); }
+static float bs_w3(float a) { return (float)((1.0 / 6.0) * (a * a * a)); }
+static float cs_w0(float a) { return (float)(-0.5 * a * a * a + a * a - 0.5 * a); }
+static float cs_w1(float a) { return (float)(1.5 * a * a * a - 2.5 * a * a + 1.0); }
+static float cs_w2(float a) { return (float)(-1.5 * a * a * a + 2.0 * a * a + 0.5 * a); }
+static float cs_w3(float a) { return (float)(0.5 * a * a * a - 0.5 * a * a); }
+
+static void tex_point(const vso_texture* tex, int x, int y, float out[4])
+{
+    const uint8_t* e = (const uint8_t*)tex->data + 4 * ((size_t)y * (size_t)tex->width + (size_t)x);
+    for (int k = 0; k < 4; ++k) out[k] = (float)e[k];
+}
+
+/* nearest -- filter/nearest.h:45-66; linear -- filter/linear.h:61-98: the result in the unnormalised integer
+ * domain (ReturnT = vector<4, int>: truncated) */
+static void tex_nearest_q(const vso_texture* tex, float s, float t, int q[4])
+{
+    const int w = tex->width, h = tex->height;
+    float cs = map_tex_coord(s, w, tex->address[0]), ct = map_tex_coord(t, h, tex->address[1]);
+    float e[4];
+    tex_point(tex, (int)(cs * (float)w), (int)(ct * (float)h), e);
+    for (int k = 0; k < 4; ++k) q[k] = (int)e[k];
+}
+
+static void tex_linear_q(const vso_texture* tex, float s, float t, int q[4])
+{
+    const int w = tex->width, h = tex->height;
+    float s1 = map_tex_coord(s - 0.5f / (float)w, w, tex->address[0]), t1 = map_tex_coord(t - 0.5f / (float)h, h, tex->address[1]);
+    float s2 = map_tex_coord(s + 0.5f / (float)w, w, tex->address[0]), t2 = map_tex_coord(t + 0.5f / (float)h, h, tex->address[1]);
+    int lx = (int)(s1 * (float)w), ly = (int)(t1 * (float)h);
+    int hx = (int)(s2 * (float)w), hy = (int)(t2 * (float)h);
+    float e00[4], e10[4], e01[4], e11[4];
+    tex_point(tex, lx, ly, e00); tex_point(tex, hx, ly, e10); tex_point(tex, lx, hy, e01); tex_point(tex, hx, hy, e11);
+    float u = s1 * (float)w - (float)lx, v = t1 * (float)h - (float)ly;
+    for (int k = 0; k < 4; ++k)
+    {
+        float p1 = lerp1(e00[k], e10[k], u);
+        float p2 = lerp1(e01[k], e11[k], u);
+        q[k] = (int)lerp1(p1, p2, v);
+    }
+}
+
+/* cubic_opt (BSpline): four bilinear lookups at the g / h offsets -- filter/cubic_opt.h:58-95 */
+static void tex_bspline_q(const vso_texture* tex, float s, float t, int q[4])
+{
+    const int w = tex->width, h = tex->height;
+    float x = s * (float)w - 0.5f, floorx = floorf(x), fracx = x - floorf(x);
+    float y = t * (float)h - 0.5f, floory = floorf(y), fracy = y - floorf(y);
+    float tmp00 = bs_w1(fracx) / (bs_w0(fracx) + bs_w1(fracx));
+    float h_00 = (floorx - 0.5f + tmp00) / w;
+    float tmp10 = bs_w3(fracx) / (bs_w2(fracx) + bs_w3(fracx));
+    float h_10 = (floorx + 1.5f + tmp10) / w;
+    float tmp01 = bs_w1(fracy) / (bs_w0(fracy) + bs_w1(fracy));
+    float h_01 = (floory - 0.5f + tmp01) / h;
+    float tmp11 = bs_w3(fracy) / (bs_w2(fracy) + bs_w3(fracy));
+    float h_11 = (floory + 1.5f + tmp11) / h;
+    int a[4], b[4], c[4], d[4];
+    tex_linear_q(tex, h_00, h_01, a); tex_linear_q(tex, h_10, h_01, b);
+    tex_linear_q(tex, h_00, h_11, c); tex_linear_q(tex, h_10, h_11, d);
+    float g0x = bs_w0(fracx) + bs_w1(fracx), g1x = bs_w2(fracx) + bs_w3(fracx);
+    float g0y = bs_w0(fracy) + bs_w1(fracy), g1y = bs_w2(fracy) + bs_w3(fracy);
+    for (int k = 0; k < 4; ++k)
+    {
+        float f_0 = g0x * (float)a[k] + g1x * (float)b[k];
+        float f_1 = g0x * (float)c[k] + g1x * (float)d[k];
+        q[k] = (int)(g0y * f_0 + g1y * f_1);
+    }
+}
+
+/* cubic with the cardinal-spline weights (CardinalSpline): 4 x 4 texels -- filter/cubic.h:85-140 */
+static void tex_cardinal_q(const vso_texture* tex, float s, float t, int q[4])
+{
+    const int w = tex->width, h = tex->height;
+    const float off[4] = { -1.5f, -0.5f, 0.5f, 1.5f };
+    float cx[4], cy[4]; int px[4], py[4];
+    for (int i = 0; i < 4; ++i)
+    {
+        cx[i] = map_tex_coord(off[i] < 0 ? s - (-off[i]) / (float)w : s + off[i] / (float)w, w, tex->address[0]);
+        cy[i] = map_tex_coord(off[i] < 0 ? t - (-off[i]) / (float)h : t + off[i] / (float)h, h, tex->address[1]);
+        px[i] = (int)(cx[i] * (float)w); py[i] = (int)(cy[i] * (float)h);
+    }
+    float ux = cx[1] * (float)w - (float)px[1], uy = cy[1] * (float)h - (float)py[1];
+    float wx[4] = { cs_w0(ux), cs_w1(ux), cs_w2(ux), cs_w3(ux) }, wy[4] = { cs_w0(uy), cs_w1(uy), cs_w2(uy), cs_w3(uy) };
+    float f[4][4];
+    for (int j = 0; j < 4; ++j)
+    {
+        float e0[4], e1[4], e2[4], e3[4];
+        tex_point(tex, px[0], py[j], e0); tex_point(tex, px[1], py[j], e1); tex_point(tex, px[2], py[j], e2); tex_point(tex, px[3], py[j], e3);
+        for (int k = 0; k < 4; ++k) f[j][k] = wx[0] * e0[k] + wx[1] * e1[k] + wx[2] * e2[k] + wx[3] * e3[k];
+    }
+    for (int k = 0; k < 4; ++k) q[k] = (int)(wy[0] * f[0][k] + wy[1] * f[1][k] + wy[2] * f[2][k] + wy[3] * f[3][k]);
+}
+
 /* tex2D for vector<4, unorm<8>> texels: filtering runs on the unnormalised integers, the result is
- * converted to vector<4, int> (truncation) and normalised once, float(u) / double(255)
- * (texture/detail/sampler2d.h:81-113, math/detail/unorm.inl:26-31);
- * nearest -- filter/nearest.h:45-66, linear -- filter/linear.h:61-98 */
+ * converted to vector<4, int> (truncation) and normalised once, float(uint32(q)) / double(255) -- a spline's
+ * undershoot below 0 wraps through uint32 like in the reference
+ * (texture/detail/sampler2d.h:81-113, math/detail/unorm.inl:26-31, filter.h:22-80) */
 void vso_tex2d(const vso_texture* tex, float s, float t, float out[4])
 {
-    const uint8_t* px = (const uint8_t*)tex->data;
-    const int w = tex->width, h = tex->height;
     int q[4];
-    if (tex->filter == 0)
+    switch (tex->filter)
     {
-        float cs = map_tex_coord(s, w, tex->address[0]), ct = map_tex_coord(t, h, tex->address[1]);
-        int lx = (int)(cs * (float)w), ly = (int)(ct * (float)h);
-        const uint8_t* e = px + 4 * ((size_t)ly * (size_t)w + (size_t)lx);
-        for (int k = 0; k < 4; ++k) q[k] = e[k];
-    }
-    else
-    {
-        float s1 = map_tex_coord(s - 0.5f / (float)w, w, tex->address[0]), t1 = map_tex_coord(t - 0.5f / (float)h, h, tex->address[1]);
-        float s2 = map_tex_coord(s + 0.5f / (float)w, w, tex->address[0]), t2 = map_tex_coord(t + 0.5f / (float)h, h, tex->address[1]);
-        int lx = (int)(s1 * (float)w), ly = (int)(t1 * (float)h);
-        int hx = (int)(s2 * (float)w), hy = (int)(t2 * (float)h);
-        const uint8_t* e00 = px + 4 * ((size_t)ly * (size_t)w + (size_t)lx);
-        const uint8_t* e10 = px + 4 * ((size_t)ly * (size_t)w + (size_t)hx);
-        const uint8_t* e01 = px + 4 * ((size_t)hy * (size_t)w + (size_t)lx);
-        const uint8_t* e11 = px + 4 * ((size_t)hy * (size_t)w + (size_t)hx);
-        float u = s1 * (float)w - (float)lx, v = t1 * (float)h - (float)ly;
-        for (int k = 0; k < 4; ++k)
-        {
-            float p1 = lerp1((float)e00[k], (float)e10[k], u);
-            float p2 = lerp1((float)e01[k], (float)e11[k], u);
-            q[k] = (int)lerp1(p1, p2, v);
-        }
+    case 1:  tex_linear_q(tex, s, t, q); break;
+    case 2:  tex_bspline_q(tex, s, t, q); break;      /* BSpline */
+    case 4:  tex_cardinal_q(tex, s, t, q); break;     /* CardinalSpline */
+    default: tex_nearest_q(tex, s, t, q); break;      /* Nearest; BSplineInterpol (3) needs the prefilter, not restated */
     }
     for (int k = 0; k < 4; ++k) out[k] = (float)((double)(float)(uint32_t)q[k] / (double)255);
 }

@@ -15,6 +15,8 @@ CASES = {
     "whitted_face_generic":   ("grid",   1, 0, 0, False, 0),
     "whitted_vertex_tex_nearest": ("sphere", 1, 1, 0, True, 0),
     "path_vertex_tex":        ("grid",   3, 1, 0, True,  1),
+    "whitted_face_tex_bspline": ("grid", 1, 0, 0, True,  2),
+    "simple_vertex_tex_cardinal": ("sphere", 0, 1, 1, True, 4),
     "path_face_cvert":        ("sphere", 3, 0, 2, False, 0),
 }
 
@@ -46,7 +48,7 @@ def tex_samples():
     """(texture, coords) pairs for the tex2D known-answer vectors: every filter x address mode."""
     rng = np.random.default_rng(17)
     out = []
-    for filt in (0, 1):
+    for filt in (0, 1, 2, 4):
         for am in ((0, 0), (1, 1), (2, 2), (0, 2), (1, 0), (3, 3)):      # 3 = Border: clamps, like the reference
             tex = S.checker_texture(13, 7, 5, filt, am)
             st = rng.uniform(-3.0, 3.0, (64, 2)).astype(np.float32)

@@ -461,7 +461,7 @@ extern "C" int vsb_scene_set_surface(vsb_scene* s, const vsb_surface_desc* desc,
         {
             const vsb_texture& t = desc->textures[i];
             if (t.width <= 0 || t.height <= 0 || !t.data) continue;
-            if (t.filter < VSB_TEX_NEAREST || t.filter > VSB_TEX_LINEAR || t.address[0] < 0 || t.address[0] > VSB_TEX_BORDER ||
+            if (t.filter < VSB_TEX_NEAREST || t.filter > VSB_TEX_CARDINAL_SPLINE || t.filter == 3 /* BSplineInterpol: needs the prefilter */ || t.address[0] < 0 || t.address[0] > VSB_TEX_BORDER ||
                 t.address[1] < 0 || t.address[1] > VSB_TEX_BORDER) { err = VSB_ERR_UNSUPPORTED; break; }
             tab[i].data = (const uchar4*)copy(t.data, (size_t)t.width * (size_t)t.height * 4);
             tab[i].width = t.width; tab[i].height = t.height; tab[i].filter = t.filter;

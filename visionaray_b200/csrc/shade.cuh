@@ -322,8 +322,99 @@ __device__ __forceinline__ uchar4 texel(const DevTexture& t, int x, int y)
 
 // tex2D(texture_ref<vector<4, unorm<8>>, 2>, coord).xyz -- texture/detail/sampler2d.h:81-151,
 // filter/nearest.h:45-66, filter/linear.h:61-98, math/detail/unorm.inl:26-31
+// ---- BSpline / CardinalSpline filters (texture/detail/filter/{cubic_opt,cubic}.h, weights filter/common.h:104-192).
+// Rare and bulky, so ONE out-of-line function that tex2d_rgb() only calls for those filter modes.  The weights mix
+// float products with double literals exactly as the reference's expressions do (single roundings spelled out: the
+// filtered value is truncated to an integer texel value afterwards).
+__device__ __forceinline__ double dmul(double a, double b) { return __dmul_rn(a, b); }
+__device__ __forceinline__ double dadd(double a, double b) { return __dadd_rn(a, b); }
+__device__ __forceinline__ float a3f(float a) { return rn_mul(rn_mul(a, a), a); }                      // a * a * a in float
+__device__ __forceinline__ double a3d(double c, float a) { return dmul(dmul(dmul(c, a), a), a); }       // c * a * a * a in double
+__device__ __forceinline__ double a2d(double c, float a) { return dmul(dmul(c, a), a); }                // c * a * a
+__device__ __forceinline__ float bs_w0(float a) { return (float)dmul(1.0 / 6.0, dadd(dadd(dadd((double)(-a3f(a)), a2d(3.0, a)), -dmul(3.0, a)), 1.0)); }
+__device__ __forceinline__ float bs_w1(float a) { return (float)dmul(1.0 / 6.0, dadd(dadd(a3d(3.0, a), -a2d(6.0, a)), 4.0)); }
+__device__ __forceinline__ float bs_w2(float a) { return (float)dmul(1.0 / 6.0, dadd(dadd(dadd(a3d(-3.0, a), a2d(3.0, a)), dmul(3.0, a)), 1.0)); }
+__device__ __forceinline__ float bs_w3(float a) { return (float)dmul(1.0 / 6.0, (double)a3f(a)); }
+__device__ __forceinline__ float cs_w0(float a) { return (float)dadd(dadd(a3d(-0.5, a), (double)rn_mul(a, a)), -dmul(0.5, a)); }
+__device__ __forceinline__ float cs_w1(float a) { return (float)dadd(dadd(a3d(1.5, a), -a2d(2.5, a)), 1.0); }
+__device__ __forceinline__ float cs_w2(float a) { return (float)dadd(dadd(a3d(-1.5, a), a2d(2.0, a)), dmul(0.5, a)); }
+__device__ __forceinline__ float cs_w3(float a) { return (float)dadd(a3d(0.5, a), -a2d(0.5, a)); }
+
+__device__ __forceinline__ void tex_linear_q(const DevTexture& t, float s, float tt, int q[3])
+{
+    const float fw = (float)t.width, fh = (float)t.height;
+    const float hs = rn_div(0.5f, fw), ht = rn_div(0.5f, fh);
+    const float s1 = map_tex_coord(rn_sub(s, hs), t.width, t.addr_s), t1 = map_tex_coord(rn_sub(tt, ht), t.height, t.addr_t);
+    const float s2 = map_tex_coord(rn_add(s, hs), t.width, t.addr_s), t2 = map_tex_coord(rn_add(tt, ht), t.height, t.addr_t);
+    const int lx = __float2int_rz(rn_mul(s1, fw)), ly = __float2int_rz(rn_mul(t1, fh));
+    const int hx = __float2int_rz(rn_mul(s2, fw)), hy = __float2int_rz(rn_mul(t2, fh));
+    const uchar4 e00 = texel(t, lx, ly), e10 = texel(t, hx, ly), e01 = texel(t, lx, hy), e11 = texel(t, hx, hy);
+    const float u = rn_sub(rn_mul(s1, fw), (float)lx), v = rn_sub(rn_mul(t1, fh), (float)ly);
+    q[0] = __float2int_rz(lerp1(lerp1((float)e00.x, (float)e10.x, u), lerp1((float)e01.x, (float)e11.x, u), v));
+    q[1] = __float2int_rz(lerp1(lerp1((float)e00.y, (float)e10.y, u), lerp1((float)e01.y, (float)e11.y, u), v));
+    q[2] = __float2int_rz(lerp1(lerp1((float)e00.z, (float)e10.z, u), lerp1((float)e01.z, (float)e11.z, u), v));
+}
+
+__device__ __noinline__ V3 tex2d_cubic_rgb(const DevTexture& t, float s, float tt)
+{
+    const float fw = (float)t.width, fh = (float)t.height;
+    int q[3];
+    if (t.filter == 2)
+    {
+        // cubic_opt: four bilinear lookups at the g / h offsets (filter/cubic_opt.h:58-95)
+        const float x = rn_sub(rn_mul(s, fw), 0.5f), floorx = floorf(x), fracx = rn_sub(x, floorx);
+        const float y = rn_sub(rn_mul(tt, fh), 0.5f), floory = floorf(y), fracy = rn_sub(y, floory);
+        const float w0x = bs_w0(fracx), w1x = bs_w1(fracx), w2x = bs_w2(fracx), w3x = bs_w3(fracx);
+        const float w0y = bs_w0(fracy), w1y = bs_w1(fracy), w2y = bs_w2(fracy), w3y = bs_w3(fracy);
+        const float g0x = rn_add(w0x, w1x), g1x = rn_add(w2x, w3x), g0y = rn_add(w0y, w1y), g1y = rn_add(w2y, w3y);
+        const float h_00 = rn_div(rn_add(rn_sub(floorx, 0.5f), rn_div(w1x, g0x)), fw);
+        const float h_10 = rn_div(rn_add(rn_add(floorx, 1.5f), rn_div(w3x, g1x)), fw);
+        const float h_01 = rn_div(rn_add(rn_sub(floory, 0.5f), rn_div(w1y, g0y)), fh);
+        const float h_11 = rn_div(rn_add(rn_add(floory, 1.5f), rn_div(w3y, g1y)), fh);
+        int a[3], b[3], c[3], d[3];
+        tex_linear_q(t, h_00, h_01, a); tex_linear_q(t, h_10, h_01, b); tex_linear_q(t, h_00, h_11, c); tex_linear_q(t, h_10, h_11, d);
+        for (int k = 0; k < 3; ++k)
+        {
+            const float f_0 = rn_add(rn_mul(g0x, (float)a[k]), rn_mul(g1x, (float)b[k]));
+            const float f_1 = rn_add(rn_mul(g0x, (float)c[k]), rn_mul(g1x, (float)d[k]));
+            q[k] = __float2int_rz(rn_add(rn_mul(g0y, f_0), rn_mul(g1y, f_1)));
+        }
+    }
+    else
+    {
+        // cubic with the cardinal-spline weights: 4 x 4 texels (filter/cubic.h:85-140)
+        const float off[4] = { 1.5f, 0.5f, 0.5f, 1.5f };
+        float cx[4], cy[4]; int px[4], py[4];
+        for (int i = 0; i < 4; ++i)
+        {
+            const float ds = rn_div(off[i], fw), dt = rn_div(off[i], fh);
+            cx[i] = map_tex_coord(i < 2 ? rn_sub(s, ds) : rn_add(s, ds), t.width, t.addr_s);
+            cy[i] = map_tex_coord(i < 2 ? rn_sub(tt, dt) : rn_add(tt, dt), t.height, t.addr_t);
+            px[i] = __float2int_rz(rn_mul(cx[i], fw)); py[i] = __float2int_rz(rn_mul(cy[i], fh));
+        }
+        const float ux = rn_sub(rn_mul(cx[1], fw), (float)px[1]), uy = rn_sub(rn_mul(cy[1], fh), (float)py[1]);
+        const float wx[4] = { cs_w0(ux), cs_w1(ux), cs_w2(ux), cs_w3(ux) }, wy[4] = { cs_w0(uy), cs_w1(uy), cs_w2(uy), cs_w3(uy) };
+        float acc[3] = { 0.0f, 0.0f, 0.0f };
+        for (int j = 0; j < 4; ++j)
+        {
+            const uchar4 e0 = texel(t, px[0], py[j]), e1 = texel(t, px[1], py[j]), e2 = texel(t, px[2], py[j]), e3 = texel(t, px[3], py[j]);
+            const float fj[3] = {
+                rn_add(rn_add(rn_add(rn_mul(wx[0], (float)e0.x), rn_mul(wx[1], (float)e1.x)), rn_mul(wx[2], (float)e2.x)), rn_mul(wx[3], (float)e3.x)),
+                rn_add(rn_add(rn_add(rn_mul(wx[0], (float)e0.y), rn_mul(wx[1], (float)e1.y)), rn_mul(wx[2], (float)e2.y)), rn_mul(wx[3], (float)e3.y)),
+                rn_add(rn_add(rn_add(rn_mul(wx[0], (float)e0.z), rn_mul(wx[1], (float)e1.z)), rn_mul(wx[2], (float)e2.z)), rn_mul(wx[3], (float)e3.z)) };
+            // w0 f0 + w1 f1 + w2 f2 + w3 f3, left to right
+            for (int k = 0; k < 3; ++k) acc[k] = j == 0 ? rn_mul(wy[0], fj[k]) : rn_add(acc[k], rn_mul(wy[j], fj[k]));
+        }
+        for (int k = 0; k < 3; ++k) q[k] = __float2int_rz(acc[k]);
+    }
+    // a spline can leave [0, 255]: normalised through uint32 like the reference, not through the 8-bit table
+    return v3((float)((double)(float)(uint32_t)q[0] / 255.0), (float)((double)(float)(uint32_t)q[1] / 255.0),
+              (float)((double)(float)(uint32_t)q[2] / 255.0));
+}
+
 __device__ inline V3 tex2d_rgb(const DevTexture& t, float s, float tt)
 {
+    if (t.filter >= 2) return tex2d_cubic_rgb(t, s, tt);
     const float fw = (float)t.width, fh = (float)t.height;
     int q[3];
     if (t.filter == 0)
