@@ -4,12 +4,14 @@
  * Scalar restatement of the frame() path: per pixel ray generation, the built-in kernels
  * (simple / whitted / pathtracing) with the plastic / matte + point-light subset, the AO
  * kernel of src/examples/ao/main.cpp, and the store / blend rules.  Paths cited are relative
- * to /root/reference/include/visionaray/.  Shading uses libm (tanf/powf/sinf/cosf), so frame
+ * to /root/reference/include/visionaray/.  Colour arithmetic uses libm (tanf/powf), so frame
  * parity is a tolerance (1/255 per channel), not bit-exactness; the ray queries inside go
- * through vso_intersect_bvh and are bit-exact.
+ * through vso_intersect_bvh and are bit-exact, and the sin / cos / pow that define SAMPLED
+ * DIRECTIONS go through vso_raymath.h (correctly rounded, the same bits as the device code).
  */
 #define _GNU_SOURCE 1
 #include "vsnray_oracle.h"
+#include "vso_raymath.h"
 
 #include <float.h>
 #include <math.h>
@@ -456,8 +458,10 @@ static v3 cosine_sample_hemisphere(float u1, float u2)
 {
     float r = sqrtf(u1);
     float theta = VSO_TWO_PI * u2;
-    float x = r * cosf(theta);
-    float y = r * sinf(theta);
+    float sn, cs;
+    vso_sincosf(theta, &sn, &cs);             /* std::cos / std::sin of the reference, correctly rounded (vso_raymath.h) */
+    float x = r * cs;
+    float y = r * sn;
     float z = sqrtf(fmax0(1.0f - u1));
     return v3m(x, y, z);
 }
@@ -509,12 +513,14 @@ static v3 blinn_sample(const vso_material* m, v3 n, v3 wo, v3* wi, float* pdf, u
     float u1 = vso_sampler_next(samp);
     float u2 = vso_sampler_next(samp);
     float e = m->spec_exp;
-    float costheta = powf(u1, 1.0f / (e + 1.0f));
+    float costheta = vso_powf(u1, 1.0f / (e + 1.0f));   /* defines the sampled direction: vso_raymath.h */
     float sintheta = sqrtf(fmax0(1.0f - costheta * costheta));
     float phi = u2 * VSO_TWO_PI;
     v3 u, v;
     ortho_basis(&u, &v, n);
-    v3 h = normalize(add(add(scale(u, sintheta * cosf(phi)), scale(v, sintheta * sinf(phi))), scale(n, costheta)));
+    float sp, cp;
+    vso_sincosf(phi, &sp, &cp);
+    v3 h = normalize(add(add(scale(u, sintheta * cp), scale(v, sintheta * sp)), scale(n, costheta)));
     *wi = reflect(wo, h);
     float vdoth = dot(wo, h);
     *pdf = ((e + 1.0f) * powf(costheta, e)) / (2.0f * VSO_PI * 4.0f * vdoth);
@@ -953,4 +959,14 @@ static void frame_run(frame_ctx* fp, vso_counters* counters, int nthreads)
             counters->n_rays += ws[i].c.n_rays;   counters->n_hits += ws[i].c.n_hits;
         }
     free(ws); free(ts);
+}
+
+/* vso_raymath.h through the library, for tests/test_raymath.py */
+void vso_ray_sincosf(const float* x, size_t n, float* s, float* c)
+{
+    for (size_t i = 0; i < n; ++i) vso_sincosf(x[i], s + i, c + i);
+}
+void vso_ray_powf(const float* x, const float* y, size_t n, float* out)
+{
+    for (size_t i = 0; i < n; ++i) out[i] = vso_powf(x[i], y[i]);
 }

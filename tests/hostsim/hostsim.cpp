@@ -11,6 +11,7 @@
 #include "../../visionaray_b200/csrc/bvh2_exact.cuh"
 #include "../../visionaray_b200/csrc/build_ploc.cuh"
 #include "../../visionaray_b200/csrc/multi_hit.cuh"
+#include "../../visionaray_b200/csrc/shade.cuh"
 #include <algorithm>
 #include <numeric>
 
@@ -221,6 +222,17 @@ size_t hs_build_ploc(int prim_kind, const void* prims, size_t n_prims, int radiu
     }
     info[0] = (sub[root].cnt & BS_LEAF) ? 1u : levels + 1u;
     return n_out;
+}
+
+// the product's ray_sincosf / ray_powf (csrc/shade.cuh), host instantiation: compared bit for bit with the oracle's
+// restatement (oracle/vso_raymath.h) in tests/test_raymath.py
+void hs_ray_sincosf(const float* x, size_t n, float* s, float* c)
+{
+    for (size_t i = 0; i < n; ++i) ray_sincosf(x[i], s[i], c[i]);
+}
+void hs_ray_powf(const float* x, const float* y, size_t n, float* out)
+{
+    for (size_t i = 0; i < n; ++i) out[i] = ray_powf(x[i], y[i]);
 }
 
 } // extern "C"

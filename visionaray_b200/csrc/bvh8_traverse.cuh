@@ -188,6 +188,36 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
     }
 }
 
+// The primitive test on a loaded leaf-order record as a pure function (the queue kernel tests a
+// primitive for ANOTHER lane's ray): true when the reference's test hits, t = its distance
+// (no range test).  Same arithmetic as test_prim().
+VSB_HD bool prim_candidate(int prim_kind, const NodeRegs& n, float ox, float oy, float oz, float dx, float dy, float dz, float& t)
+{
+    if (prim_kind == 0 || (prim_kind == 2 && !(n.w[11] & VSB_GENERIC_SPHERE_TAG)))
+    {
+        float u = 0.0f, v = 0.0f;
+        t = -1.0f;
+        return isect_triangle(ox, oy, oz, dx, dy, dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]),
+                              u2f(n.w[4]), u2f(n.w[5]), u2f(n.w[6]), u2f(n.w[8]), u2f(n.w[9]), u2f(n.w[10]), t, u, v);
+    }
+    return isect_sphere(ox, oy, oz, dx, dy, dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]), u2f(n.w[3]), t);
+}
+
+// The hit record of leaf-order record `rec` for a ray: the test is evaluated again (bit-identical
+// t / u / v), ids come from the record.  Used once per ray, when the queue kernel hands the
+// winner of its (t, record) key to the program.
+VSB_HD void hit_from_record(const WideScene& s, uint32_t rec, float ox, float oy, float oz, float dx, float dy, float dz, HitReg& best)
+{
+    NodeRegs n;
+    const int n16 = wide_rec_words16(s.prim_kind);
+    load_record(reinterpret_cast<const char*>(s.prims) + (size_t)rec * (size_t)(n16 * 16), n16, n);
+    hit_reset(best);
+    RayCtx r;
+    r.ox = ox; r.oy = oy; r.oz = oz; r.dx = dx; r.dy = dy; r.dz = dz; r.ix = r.iy = r.iz = 0.0f; r.octinv4 = 0u;
+    float limit = FLT_MAX;
+    test_prim(s.prim_kind, n, r, best, limit);   // accepted candidates have 0 <= t < min(max_t, FLT_MAX): always a hit here
+}
+
 #define VSB_STACK_SIZE 48
 
 // Per-ray traversal state.  Stack entries are node GROUPS (base index, mask): hit bits in
@@ -209,10 +239,15 @@ VSB_HD void test_prim(int prim_kind, const NodeRegs& n, const RayCtx& r, HitReg&
 // The deep part of the stack lives in its own (local-memory) object: kept inside TravState, its
 // dynamically indexed arrays dragged the whole struct -- node group, primitive group, stack pointer
 // -- into local memory, one LDL/STL per field access in the traversal loop.
+#ifndef VSB_Q_SHARED_STACK
+#define VSB_Q_SHARED_STACK 12   // shared entries per thread in the queue kernel (trace_kernel_q): leaves room for its ray / key / queue arrays
+#endif
+#define VSB_MIN_SHARED_STACK (VSB_Q_SHARED_STACK < VSB_SHARED_STACK ? VSB_Q_SHARED_STACK : VSB_SHARED_STACK)
+
 struct TravSpill
 {
 #if defined(__CUDACC__)
-    uint32_t b[VSB_STACK_SIZE - VSB_SHARED_STACK], m[VSB_STACK_SIZE - VSB_SHARED_STACK];
+    uint32_t b[VSB_STACK_SIZE - VSB_MIN_SHARED_STACK], m[VSB_STACK_SIZE - VSB_MIN_SHARED_STACK];
 #else
     uint32_t b[VSB_STACK_SIZE], m[VSB_STACK_SIZE];
 #endif
@@ -230,33 +265,35 @@ struct TravState
     TravSpill* spill;               // set by the owner of the state
 };
 
+template <int SS = VSB_SHARED_STACK>
 VSB_HD void stack_push(TravState& t, uint32_t b, uint32_t m)
 {
 #if defined(__CUDACC__)
-    if (t.sp < VSB_SHARED_STACK)
+    if (t.sp < SS)
     {
         const uint32_t a = t.sstack + (uint32_t)t.sp * 1024u;
         asm volatile("st.shared.u32 [%0], %1;" :: "r"(a), "r"(b) : "memory");
         asm volatile("st.shared.u32 [%0+512], %1;" :: "r"(a), "r"(m) : "memory");
     }
-    else { t.spill->b[t.sp - VSB_SHARED_STACK] = b; t.spill->m[t.sp - VSB_SHARED_STACK] = m; }
+    else { t.spill->b[t.sp - SS] = b; t.spill->m[t.sp - SS] = m; }
 #else
     t.spill->b[t.sp] = b; t.spill->m[t.sp] = m;
 #endif
     ++t.sp;
 }
 
+template <int SS = VSB_SHARED_STACK>
 VSB_HD void stack_pop(TravState& t, uint32_t& b, uint32_t& m)
 {
     --t.sp;
 #if defined(__CUDACC__)
-    if (t.sp < VSB_SHARED_STACK)
+    if (t.sp < SS)
     {
         const uint32_t a = t.sstack + (uint32_t)t.sp * 1024u;
         asm volatile("ld.shared.u32 %0, [%1];" : "=r"(b) : "r"(a) : "memory");
         asm volatile("ld.shared.u32 %0, [%1+512];" : "=r"(m) : "r"(a) : "memory");
     }
-    else { b = t.spill->b[t.sp - VSB_SHARED_STACK]; m = t.spill->m[t.sp - VSB_SHARED_STACK]; }
+    else { b = t.spill->b[t.sp - SS]; m = t.spill->m[t.sp - SS]; }
 #else
     b = t.spill->b[t.sp]; m = t.spill->m[t.sp];
 #endif

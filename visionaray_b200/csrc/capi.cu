@@ -84,9 +84,22 @@ int g_band_trace = 0;      // developer switch: print the band timeline of host-
 int g_band_streams = 2;    // 2: alternate bands over two streams (tail of band i overlaps the head of band i+1)
 int g_frame_bands = 8;     // cfg2 into pinned host memory: 1 band 11.8 ms, 2: 9.6, 16 interleaved bands on two streams: see DESIGN.md section 5
 
+// trace_queue: 1 = single-bvh BVH8 launches run trace_kernel_q (primitive tests shared by the warp), 0 = trace_kernel
+int g_trace_queue = 1, g_drain_min = 32, g_pend_min = 8;
+
 template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
 {
+    tl.drain_min = g_drain_min < 1 ? 1 : (g_drain_min > 32 ? 32 : g_drain_min);
+    tl.pend_min = g_pend_min < 1 ? 1 : g_pend_min;
+    if (!EXACT && g_trace_queue && tl.n_scenes == 1)
+    {
+        auto kernel = vsb::trace_kernel_q<Program>;
+        const size_t smem = vsb::trace_q_smem_words<Program>() * sizeof(uint32_t);
+        const int grid = grid_for(kernel, smem, tl.n_items, tl.chunk);
+        kernel<<<grid, BLOCK, smem, st>>>(tl, prog);
+        return cudaGetLastError();
+    }
     auto kernel = vsb::trace_kernel<Program, EXACT>;
     const size_t smem = (size_t)(Program::STATE_WORDS + 2 * VSB_SHARED_STACK) * BLOCK * sizeof(uint32_t);
     const int grid = grid_for(kernel, smem, tl.n_items, tl.chunk);
@@ -222,6 +235,9 @@ extern "C" int vsb_tune(const char* key, int value)
     if (!std::strcmp(key, "query_service_min")) g_query_service_min = value;
     else if (!std::strcmp(key, "frame_service_min")) g_frame_service_min = value;
     else if (!std::strcmp(key, "phase_min")) g_phase_min = value;
+    else if (!std::strcmp(key, "trace_queue")) g_trace_queue = value;
+    else if (!std::strcmp(key, "drain_min")) g_drain_min = value;
+    else if (!std::strcmp(key, "pend_min")) g_pend_min = value;
     else if (!std::strcmp(key, "sort_rays")) g_sort_rays = value;
     else if (!std::strcmp(key, "frame_bands")) g_frame_bands = value;
     else if (!std::strcmp(key, "host_store")) g_host_store = value;

@@ -140,6 +140,7 @@ struct TraceLaunch
     unsigned long long* ray_count;        // optional: += rays traced
     int service_min;                      // lanes that must be idle before continuations / refill run
     int phase_min;                        // phase vote threshold (phase_runs)
+    int drain_min, pend_min;              // trace_kernel_q: pairs that trigger a drain; lanes waiting on their pairs that force one
 };
 
 #define VSB_BLOCK 128
@@ -281,6 +282,234 @@ trace_kernel(const TraceLaunch tl, const __grid_constant__ Program prog)
     }
 }
 
+// ---- the queue kernel: node visits per lane, primitive tests shared by the warp -------------------
+//
+// Same persistent loop, programs and work queue as trace_kernel, but a lane no longer tests its own
+// primitives.  Every iteration all traversing lanes take ONE NODE VISIT; the primitives the node test
+// selects are appended as (leaf-order record, owner) pairs to a per-warp ring in shared memory, and
+// when the ring holds 32 pairs (or nothing else can run) ALL 32 LANES test one pair each: record loaded
+// from global memory, the owner's ray from shared memory, result merged into the owner's 64-bit key
+// (t bits << 32 | record) with atomicMin.  The primitive test thus runs at (nearly) full warp width
+// however few lanes found primitives in a given step -- it ran at 9.4 of 32 lanes in trace_kernel
+// (profiles/r1_cfg2_instruction_regions_v8.txt) -- and the node test is no longer skipped by lanes that
+// are busy with primitives.  Cost: an owner's cull bound lags its pending pairs by an iteration or two.
+// Replaces the leaf loop of detail/bvh/intersect.inl:104-130.
+//
+// Lane states: TRAVERSING (node work left), PENDING (node work done, pairs of this lane still queued:
+// it is finished when the ring's head has passed the lane's last pair), WAITING / EMPTY / DEAD as above.
+// Ties: the key orders (t, record), so among equal t the smallest leaf-order record wins -- a fixed
+// rule, independent of scheduling (tie candidates are never culled: the node test is conservative).
+// Any-hit lanes leave as soon as their key holds a hit; pairs they leave behind are tested against
+// whatever ray the lane holds then, which is a valid (ray, primitive) test of the same scene.
+// One bvh per launch, BVH8 walk only: ranges of bvhs and the reference-order walk stay on trace_kernel.
+
+#ifndef VSB_QCAP
+#define VSB_QCAP 64               // pairs per warp ring (power of two, >= 64: a full ring always drains 32)
+#endif
+#define LANE_PENDING 4
+#define VSB_KEY_NONE 0xffffffffu
+
+// shared memory of trace_kernel_q in 32-bit words per CTA: stack | program state | ray (6) | key (2) | rings
+template <typename Program>
+__host__ __device__ constexpr size_t trace_q_smem_words()
+{
+    return (size_t)(2 * VSB_Q_SHARED_STACK + Program::STATE_WORDS + 8) * VSB_BLOCK + (size_t)(VSB_BLOCK / 32) * VSB_QCAP * 2;
+}
+
+template <typename Program>
+__global__ void __launch_bounds__(VSB_BLOCK, Program::MIN_BLOCKS_Q)
+trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
+{
+    extern __shared__ uint32_t lane_store_raw[];
+    const unsigned lane = threadIdx.x & 31u;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    uint32_t* const prog_state = lane_store_raw + 2 * VSB_Q_SHARED_STACK * VSB_BLOCK;
+    typename Program::Lane L(prog_state, threadIdx.x);
+    float* const ray_s = reinterpret_cast<float*>(prog_state + Program::STATE_WORDS * VSB_BLOCK);        // [6][VSB_BLOCK]
+    unsigned long long* const key_s = reinterpret_cast<unsigned long long*>(ray_s + 6 * VSB_BLOCK);      // [VSB_BLOCK]
+    uint2* const ring = reinterpret_cast<uint2*>(key_s + VSB_BLOCK) + (threadIdx.x >> 5) * VSB_QCAP;     // this warp's pairs
+
+    unsigned long long chunk_next = 0, chunk_end = 0;     // warp-uniform
+    bool exhausted = false;                               // warp-uniform
+    unsigned q_head = 0u, q_tail = 0u;                    // warp-uniform pair sequence numbers (ring index = seq % VSB_QCAP)
+    int state = LANE_EMPTY;
+    unsigned n_rays = 0, my_seq = 0u;
+
+    RayCtx rc; rc.ox = rc.oy = rc.oz = rc.dx = rc.dy = rc.dz = 0.0f; rc.ix = rc.iy = rc.iz = 0.0f; rc.octinv4 = 0u;
+    float limit = 0.0f;
+    bool any = false, live = false;                       // live: max_t > 0 (a ray with max_t <= 0 cannot hit and is not traced)
+    const WideScene sc = tl.scenes[0].wide;
+    const int n16 = wide_rec_words16(sc.prim_kind);
+    TravSpill spill;
+    TravState t; trav_begin(t);
+    t.spill = &spill;
+    t.sstack = (uint32_t)__cvta_generic_to_shared(lane_store_raw + threadIdx.x);
+    RayReq req;
+
+    // one batch of up to 32 pairs, one per lane
+    auto drain = [&]()
+    {
+        const unsigned n = q_tail - q_head < 32u ? q_tail - q_head : 32u;
+        if (lane < n)
+        {
+            const uint2 e = ring[(q_head + lane) & (VSB_QCAP - 1u)];
+            NodeRegs r;
+            load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)e.x * (size_t)(n16 * 16), n16, r);
+            const float* o = ray_s + e.y;
+            float tt;
+            if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
+            {
+                const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | e.x;
+                if (cand < key_s[e.y]) atomicMin(key_s + e.y, cand);
+            }
+        }
+        q_head += n;
+        __syncwarp();
+    };
+
+    for (;;)
+    {
+        const unsigned not_trav = __ballot_sync(0xffffffffu, state == LANE_WAITING || state == LANE_EMPTY);
+        const unsigned trav = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING || state == LANE_PENDING);
+        if (not_trav != 0u && (__popc(not_trav) >= tl.service_min || trav == 0u))
+        {
+            // ---- continuations of finished rays ----
+            bool start = false;
+            if (state == LANE_WAITING)
+            {
+                const float* o = ray_s + threadIdx.x;
+                const float ox = o[0], oy = o[VSB_BLOCK], oz = o[2 * VSB_BLOCK], dx = o[3 * VSB_BLOCK], dy = o[4 * VSB_BLOCK], dz = o[5 * VSB_BLOCK];
+                const uint32_t rec = (uint32_t)key_s[threadIdx.x];
+                HitReg best;
+                if (live && rec != VSB_KEY_NONE) hit_from_record(sc, rec, ox, oy, oz, dx, dy, dz, best);
+                else hit_reset(best);
+                if (prog.done(L, best, ox, oy, oz, dx, dy, dz, req)) start = true;
+                else state = LANE_EMPTY;
+            }
+            // ---- refill empty lanes from the warp's chunk ----
+            unsigned empty = __ballot_sync(0xffffffffu, state == LANE_EMPTY);
+            while (empty != 0u && !exhausted)
+            {
+                if (chunk_next >= chunk_end)
+                {
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(tl.work_counter, (unsigned long long)tl.chunk);
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    if (base >= tl.n_items) { exhausted = true; break; }
+                    chunk_next = base;
+                    chunk_end = base + tl.chunk < tl.n_items ? base + tl.chunk : tl.n_items;
+                }
+                const unsigned long long item = chunk_next + (unsigned long long)__popc(empty & lt_mask);
+                if (state == LANE_EMPTY && item < chunk_end)
+                {
+                    if (prog.begin(L, item, req)) { start = true; state = LANE_WAITING; }
+                }
+                const unsigned long long taken = (unsigned long long)__popc(empty);
+                chunk_next = chunk_next + taken < chunk_end ? chunk_next + taken : chunk_end;
+                empty = __ballot_sync(0xffffffffu, state == LANE_EMPTY);
+            }
+            if (exhausted && state == LANE_EMPTY) state = LANE_DEAD;
+            if (start)
+            {
+                ++n_rays;
+                any = req.any;
+                float* o = ray_s + threadIdx.x;
+                o[0] = req.ox; o[VSB_BLOCK] = req.oy; o[2 * VSB_BLOCK] = req.oz;
+                o[3 * VSB_BLOCK] = req.dx; o[4 * VSB_BLOCK] = req.dy; o[5 * VSB_BLOCK] = req.dz;
+                // key: a candidate (t, rec) is accepted iff it is smaller; t < max_t strictly <=> bits(t) <= bits(max_t) - 1,
+                // and t < FLT_MAX as against the reference's empty record (math/intersect.h:95-103)
+                live = req.max_t > 0.0f;
+                const float mt = req.max_t < FLT_MAX ? req.max_t : FLT_MAX;
+                const uint32_t hi = live ? __float_as_uint(mt) - 1u : 0u;
+                key_s[threadIdx.x] = ((unsigned long long)hi << 32) | (live ? VSB_KEY_NONE : 0u);
+                limit = __uint_as_float(hi);
+                ray_ctx_init(rc, req.ox, req.oy, req.oz, req.dx, req.dy, req.dz);
+                trav_begin(t);
+                state = live ? LANE_TRAVERSING : LANE_WAITING;
+            }
+            __syncwarp();
+            if (__all_sync(0xffffffffu, state == LANE_DEAD)) break;
+        }
+
+        // ---- node phase: one node visit per traversing lane ----
+        if (state == LANE_TRAVERSING && (t.ng_mask >> 24) != 0u)
+        {
+            const int bit = find_msb(t.ng_mask);
+            t.ng_mask &= ~(1u << bit);
+            const uint32_t imask = t.ng_mask & 0xffu;
+            const uint32_t slot = ((uint32_t)(bit - 24) ^ (rc.octinv4 & 0xffu)) & 7u;
+            const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
+            const char* addr = reinterpret_cast<const char*>(sc.nodes + (t.ng_base + rel));
+            if (t.ng_mask & 0xff000000u) stack_push<VSB_Q_SHARED_STACK>(t, t.ng_base, t.ng_mask);
+            NodeRegs n;
+            load_record(addr, 5, n);
+            uint32_t ph;
+            const uint32_t nh = test_node(n, rc, limit, ph);
+            t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
+            t.pg_base = n.w[5]; t.pg_mask = ph;
+            if ((t.ng_mask >> 24) == 0u)
+            {
+                if (t.sp == 0) t.ng_mask = 0u;
+                else stack_pop<VSB_Q_SHARED_STACK>(t, t.ng_base, t.ng_mask);
+            }
+        }
+
+        // ---- append the selected primitives to the warp's ring; drain when it is full ----
+        bool drained = false;
+        for (;;)
+        {
+            const int c = state == LANE_TRAVERSING ? __popc(t.pg_mask) : 0;
+            if (__ballot_sync(0xffffffffu, c != 0) == 0u) break;
+            int incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
+            {
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if ((int)lane >= o) incl += v;
+            }
+            const unsigned total = (unsigned)__shfl_sync(0xffffffffu, incl, 31);
+            const unsigned space = VSB_QCAP - (q_tail - q_head);
+            unsigned off = (unsigned)(incl - c);
+            while (t.pg_mask != 0u && off < space)
+            {
+                const int bit = find_msb(t.pg_mask);
+                t.pg_mask &= ~(1u << bit);
+                ring[(q_tail + off) & (VSB_QCAP - 1u)] = make_uint2(t.pg_base + (uint32_t)bit, threadIdx.x);
+                ++off;
+            }
+            q_tail += total < space ? total : space;
+            __syncwarp();
+            if (total <= space) break;
+            drain(); drained = true;           // the ring is full
+        }
+
+        // ---- lanes out of node work wait for their pairs; drain when worthwhile ----
+        if (state == LANE_TRAVERSING && (t.ng_mask >> 24) == 0u) { state = LANE_PENDING; my_seq = q_tail; }
+        {
+            const unsigned node_work = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);
+            const int n_pend = __popc(__ballot_sync(0xffffffffu, state == LANE_PENDING && (int)(q_head - my_seq) < 0));
+            while (q_tail - q_head >= (unsigned)tl.drain_min || (q_tail != q_head && (node_work == 0u || n_pend >= tl.pend_min)))
+            {
+                drain(); drained = true;
+            }
+        }
+        if (drained && (state == LANE_TRAVERSING || state == LANE_PENDING))
+        {
+            const unsigned long long k = key_s[threadIdx.x];
+            limit = __uint_as_float((uint32_t)(k >> 32));
+            if (any && live && (uint32_t)k != VSB_KEY_NONE) state = LANE_WAITING;
+        }
+        if (state == LANE_PENDING && (int)(q_head - my_seq) >= 0) state = LANE_WAITING;
+    }
+
+    if (tl.ray_count)
+    {
+        unsigned n = n_rays;
+        for (int o = 16; o > 0; o >>= 1) n += __shfl_down_sync(0xffffffffu, n, o);
+        if (lane == 0 && n) atomicAdd(tl.ray_count, (unsigned long long)n);
+    }
+}
+
 // ---- ray list program: closest_hit()/any_hit() over a ray list ----------------------------------
 // Sort key of a ray for the coherence pre-pass of ray lists: a 21-bit Morton code of the origin
 // inside the scene bounds (7 bits per axis, major) and the direction octant (3 bits, minor).  Rays
@@ -344,6 +573,10 @@ struct RayListProgram
 #define VSB_LIST_MIN_BLOCKS VSB_MIN_BLOCKS
 #endif
     static constexpr int MIN_BLOCKS = VSB_LIST_MIN_BLOCKS;
+#ifndef VSB_LIST_MIN_BLOCKS_Q
+#define VSB_LIST_MIN_BLOCKS_Q 6
+#endif
+    static constexpr int MIN_BLOCKS_Q = VSB_LIST_MIN_BLOCKS_Q;
 
     __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
     {

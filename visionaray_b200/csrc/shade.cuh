@@ -6,8 +6,9 @@
 //
 // Everything that DEFINES A RAY (primary rays, hit positions, light / reflection / sampled
 // directions, offsets) uses single-rounding arithmetic in the reference's operation order, so
-// secondary rays are the same rays the reference traces (up to libm-vs-CUDA sinf/cosf/powf
-// ulps).  Colour arithmetic is free to use FMAs: pixel parity is a 1/255 tolerance.
+// secondary rays are the same rays the oracle traces; sin / cos / pow of sampled directions are
+// correctly rounded on both sides (ray_sincosf / ray_powf below), where the reference's libm is
+// within one ulp.  Colour arithmetic is free to use FMAs: pixel parity is a 1/255 tolerance.
 #pragma once
 
 #include "vsb_common.cuh"
@@ -214,13 +215,121 @@ VSB_HD void ortho_basis(V3& u, V3& v, V3 w)
     u = vcross(v, w);
 }
 
+// ---- sin / cos / pow of the values that define a sampled direction --------------------------------
+// The reference calls std::sin / std::cos / std::pow (libm).  CUDA's sinf / cosf / powf are a few ulps
+// away from libm's, which forks a path at a triangle edge once in a few thousand bounces; so these three
+// are evaluated in double with a FIXED sequence of single-rounding operations and rounded to float once
+// -- the same sequence as the oracle's (oracle/vso_raymath.h restates it in C), i.e. the same bits, and
+// the correctly rounded value in all but ~2^-22 of arguments.
+#if defined(__CUDA_ARCH__)
+VSB_D double d_mul(double a, double b) { return __dmul_rn(a, b); }
+VSB_D double d_add(double a, double b) { return __dadd_rn(a, b); }
+VSB_D double d_sub(double a, double b) { return __dsub_rn(a, b); }
+VSB_D double d_div(double a, double b) { return __ddiv_rn(a, b); }
+VSB_D double bits_to_double(uint64_t b) { return __longlong_as_double((long long)b); }
+VSB_D uint64_t double_to_bits(double d) { return (uint64_t)__double_as_longlong(d); }
+#else
+VSB_HD double d_mul(double a, double b) { return a * b; }            // host build: -ffp-contract=off
+VSB_HD double d_add(double a, double b) { return a + b; }
+VSB_HD double d_sub(double a, double b) { return a - b; }
+VSB_HD double d_div(double a, double b) { return a / b; }
+VSB_HD double bits_to_double(uint64_t b) { double d; memcpy(&d, &b, 8); return d; }
+VSB_HD uint64_t double_to_bits(double d) { uint64_t b; memcpy(&b, &d, 8); return b; }
+#endif
+VSB_HD double d_horner(double p, double x, double c) { return d_add(d_mul(p, x), c); }
+
+// |x| < 2^20
+VSB_HD void ray_sincosf(float x, float& s, float& c)
+{
+    const double PIO2_HI = 1.5707963267341256e+00, PIO2_LO = 6.0771005065061922e-11, TWO_OVER_PI = 6.3661977236758138e-01;
+    const double xd = (double)x;
+    const double kd = rint(d_mul(xd, TWO_OVER_PI));
+    const double r = d_sub(d_sub(xd, d_mul(kd, PIO2_HI)), d_mul(kd, PIO2_LO));
+    const double r2 = d_mul(r, r);
+    double ps = -1.0 / 355687428096000.0;
+    ps = d_horner(ps, r2, 1.0 / 1307674368000.0);
+    ps = d_horner(ps, r2, -1.0 / 6227020800.0);
+    ps = d_horner(ps, r2, 1.0 / 39916800.0);
+    ps = d_horner(ps, r2, -1.0 / 362880.0);
+    ps = d_horner(ps, r2, 1.0 / 5040.0);
+    ps = d_horner(ps, r2, -1.0 / 120.0);
+    ps = d_horner(ps, r2, 1.0 / 6.0);
+    const double sn = d_sub(r, d_mul(d_mul(r, r2), ps));
+    double pc = 1.0 / 6402373705728000.0;
+    pc = d_horner(pc, r2, -1.0 / 20922789888000.0);
+    pc = d_horner(pc, r2, 1.0 / 87178291200.0);
+    pc = d_horner(pc, r2, -1.0 / 479001600.0);
+    pc = d_horner(pc, r2, 1.0 / 3628800.0);
+    pc = d_horner(pc, r2, -1.0 / 40320.0);
+    pc = d_horner(pc, r2, 1.0 / 720.0);
+    pc = d_horner(pc, r2, -1.0 / 24.0);
+    pc = d_horner(pc, r2, 0.5);
+    const double cs = d_sub(1.0, d_mul(r2, pc));
+    const int q = (int)((long long)kd & 3);
+    const double so = (q & 1) ? cs : sn, co = (q & 1) ? sn : cs;
+    s = (float)((q & 2) ? -so : so);
+    c = (float)(((q + 1) & 2) ? -co : co);
+}
+
+// x^y, x >= 0 (x < 0 -> NaN)
+VSB_HD float ray_powf(float x, float y)
+{
+    const double LN2_HI = 6.9314718036912382e-01, LN2_LO = 1.9082149292705877e-10, INV_LN2 = 1.4426950408889634e+00;
+    if (y == 0.0f) return 1.0f;
+    if (x != x || y != y || x < 0.0f) return u2f(0x7fc00000u);
+    if (x == 0.0f) return y > 0.0f ? 0.0f : u2f(0x7f800000u);
+    if (x == 1.0f) return 1.0f;
+    if (x == u2f(0x7f800000u)) return y > 0.0f ? x : 0.0f;
+    uint64_t b = double_to_bits((double)x);
+    int k = (int)((b >> 52) & 0x7ffu) - 1023;
+    double m = bits_to_double((b & 0x000fffffffffffffull) | 0x3ff0000000000000ull);
+    if (m > 1.4142135623730951) { m = d_mul(m, 0.5); k = k + 1; }
+    const double s = d_div(d_sub(m, 1.0), d_add(m, 1.0));
+    const double s2 = d_mul(s, s);
+    double p = 1.0 / 21.0;
+    p = d_horner(p, s2, 1.0 / 19.0);
+    p = d_horner(p, s2, 1.0 / 17.0);
+    p = d_horner(p, s2, 1.0 / 15.0);
+    p = d_horner(p, s2, 1.0 / 13.0);
+    p = d_horner(p, s2, 1.0 / 11.0);
+    p = d_horner(p, s2, 1.0 / 9.0);
+    p = d_horner(p, s2, 1.0 / 7.0);
+    p = d_horner(p, s2, 1.0 / 5.0);
+    p = d_horner(p, s2, 1.0 / 3.0);
+    const double ts = d_mul(2.0, s);
+    const double lnm = d_add(ts, d_mul(ts, d_mul(s2, p)));
+    const double kd = (double)k;
+    const double lnx = d_add(d_mul(kd, LN2_HI), d_add(d_mul(kd, LN2_LO), lnm));
+    const double z = d_mul((double)y, lnx);
+    if (z > 89.0) return u2f(0x7f800000u);
+    if (z < -104.0) return 0.0f;
+    const double nd = rint(d_mul(z, INV_LN2));
+    const double r = d_sub(d_sub(z, d_mul(nd, LN2_HI)), d_mul(nd, LN2_LO));
+    double e = 1.0 / 6227020800.0;
+    e = d_horner(e, r, 1.0 / 479001600.0);
+    e = d_horner(e, r, 1.0 / 39916800.0);
+    e = d_horner(e, r, 1.0 / 3628800.0);
+    e = d_horner(e, r, 1.0 / 362880.0);
+    e = d_horner(e, r, 1.0 / 40320.0);
+    e = d_horner(e, r, 1.0 / 5040.0);
+    e = d_horner(e, r, 1.0 / 720.0);
+    e = d_horner(e, r, 1.0 / 120.0);
+    e = d_horner(e, r, 1.0 / 24.0);
+    e = d_horner(e, r, 1.0 / 6.0);
+    e = d_horner(e, r, 0.5);
+    e = d_horner(e, r, 1.0);
+    e = d_horner(e, r, 1.0);
+    const double sc = bits_to_double((uint64_t)((long long)nd + 1023) << 52);
+    return (float)d_mul(e, sc);
+}
+
 // cosine_sample_hemisphere -- sampling.h:61-71
 VSB_HD V3 cosine_sample_hemisphere(float u1, float u2)
 {
     const float r = rn_sqrt(u1);
     const float theta = rn_mul(VSB_TWO_PI, u2);
     float sn, cs;
-    sincosf(theta, &sn, &cs);          // one range reduction for both (same values as sinf / cosf)
+    ray_sincosf(theta, sn, cs);
     return v3(rn_mul(r, cs), rn_mul(r, sn), rn_sqrt(max0(rn_sub(1.0f, u1))));
 }
 
@@ -248,13 +357,13 @@ VSB_HD V3 blinn_sample(const Material& m, V3 n, V3 wo, V3& wi, float& pdf, uint3
     const float u1 = sampler_next(samp);
     const float u2 = sampler_next(samp);
     const float e = m.spec_exp;
-    const float costheta = powf(u1, 1.0f / (e + 1.0f));
+    const float costheta = ray_powf(u1, rn_div(1.0f, rn_add(e, 1.0f)));
     const float sintheta = rn_sqrt(max0(rn_sub(1.0f, rn_mul(costheta, costheta))));
     const float phi = rn_mul(u2, VSB_TWO_PI);
     V3 u, v;
     ortho_basis(u, v, n);
     float sp, cp;
-    sincosf(phi, &sp, &cp);
+    ray_sincosf(phi, sp, cp);
     const V3 h = vnormalize(vadd(vadd(vscale(u, rn_mul(sintheta, cp)), vscale(v, rn_mul(sintheta, sp))), vscale(n, costheta)));
     wi = vreflect(wo, h);
     const float vdoth = vdot(wo, h);
@@ -714,6 +823,10 @@ struct FrameProgram
 #define VSB_FRAME_MIN_BLOCKS 6
 #endif
     static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
+#ifndef VSB_FRAME_MIN_BLOCKS_Q
+#define VSB_FRAME_MIN_BLOCKS_Q 6
+#endif
+    static constexpr int MIN_BLOCKS_Q = VSB_FRAME_MIN_BLOCKS_Q; // the same for trace_kernel_q
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
     static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (SURF ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
 
