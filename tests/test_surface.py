@@ -129,7 +129,7 @@ def test_gpu_frames_match_oracle(gpu, name):
             bad = _frac_bad(img, want)
             # RNG-free kernels on the reference-order walk reproduce every pixel; the wide walk may take
             # the other triangle of an exact t-tie on a shared edge, the path tracer may fork on an ulp
-            limit = (0.0 if trav == gpu.TRAVERSE_EXACT else 1e-3) if fp.kernel in (0, 1) else 3e-3
+            limit = 0.0 if trav == gpu.TRAVERSE_EXACT else (1e-3 if fp.kernel in (0, 1) else 3e-3)
             assert bad <= limit, (name, trav, bad, float(np.abs(img - want).max()))
         # detaching restores the per-face path
         gpu.set_surface(dev, None)
@@ -170,7 +170,7 @@ def test_gpu_normals_from_the_primitive(gpu, name, kernel):
         for trav in (gpu.TRAVERSE_EXACT, gpu.TRAVERSE_WIDE):
             img = np.zeros((fp.height, fp.width, 4), dtype=np.float32)
             gpu.frame(dev, fp, None, mats, light, img, traverse=trav)
-            limit = (0.0 if trav == gpu.TRAVERSE_EXACT else 1e-3) if kernel in (0, 1) else 4e-3
+            limit = 0.0 if trav == gpu.TRAVERSE_EXACT else (1e-3 if kernel in (0, 1) else 4e-3)
             assert _frac_bad(img, want) <= limit, (name, kernel, trav)
         if name == "spheres":
             fp.kernel = 3          # the reference's path tracer has no defined sphere normal (isect_pos unset)
