@@ -15,6 +15,9 @@
 #pragma once
 
 #include "vsb_common.cuh"
+#if defined(__CUDACC__)
+#include <cuda_fp16.h>
+#endif
 
 namespace vsb
 {
@@ -75,10 +78,52 @@ VSB_HD float fma_f(float a, float b, float c)
 #endif
 }
 
-// byte k of `w` as the float 1 + b * 2^-15 (exact): one PRMT, no int->float conversion
-VSB_HD float byte_as_unit_float(uint32_t w, int k)
+// byte k of `w` as the float 1 + b * 2^-15 (exact): one PRMT, no int->float conversion.  `one` is
+// 0x3F800000 read from the constant bank (unit_float_bits()): PRMT has one immediate slot, and with the
+// constant as the immediate ptxas put the four selectors into registers and re-materialised them with a
+// MOV per use (~48 of the node test's ~280 instructions, found in the SASS).
+#if defined(__CUDACC__)
+__constant__ uint32_t c_unit_float_bits = 0x3F800000u;        // a constant-bank value: opaque to ptxas's constant propagation
+__constant__ uint32_t c_half_bias_bits = 0x64646464u;
+#endif
+VSB_HD uint32_t unit_float_bits()
 {
-    return u2f(byte_perm(w, 0x3F800000u, 0x7604u | ((uint32_t)k << 4)));
+#if defined(__CUDA_ARCH__)
+    return c_unit_float_bits;
+#else
+    return 0x3F800000u;
+#endif
+}
+VSB_HD float byte_as_unit_float(uint32_t w, int k, uint32_t one)
+{
+    return u2f(byte_perm(w, one, 0x7604u | ((uint32_t)k << 4)));
+}
+
+// VSB_NODE_HALFCVT = 1: a quantised plane byte enters the slab test as the float 1024 + b instead: ONE PRMT
+// builds the half2 (0x6400 | b_k, 0x6400 | b_k+1) = (1024 + b_k, 1024 + b_k+1) for two children, two HADD2.F32
+// widen it.  Per byte: half a PRMT on the alu pipe (the saturated one: 80 % of its peak on the cfg2 frame,
+// profiles/r2_cfg2_q1) and one conversion on the fma pipe (21 %), against one PRMT.
+#ifndef VSB_NODE_HALFCVT
+#define VSB_NODE_HALFCVT 0
+#endif
+VSB_HD uint32_t half_bias_bits()
+{
+#if defined(__CUDA_ARCH__)
+    return c_half_bias_bits;
+#else
+    return 0x64646464u;
+#endif
+}
+VSB_HD float byte_as_biased_float(uint32_t w, int k, uint32_t bias)
+{
+#if defined(__CUDA_ARCH__)
+    const uint32_t h2 = byte_perm(w, bias, (k & 2) ? 0x4342u : 0x4140u);
+    const __half2 h = *reinterpret_cast<const __half2*>(&h2);
+    return (k & 1) ? __high2float(h) : __low2float(h);
+#else
+    (void)bias;
+    return 1024.0f + (float)((w >> (8 * k)) & 0xffu);
+#endif
 }
 
 // ---- collapse of one BVH2 subtree root into one BVH8 node ----------------------------------

@@ -103,6 +103,27 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
 {
     const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
     const uint32_t e = n.w[3];
+#if VSB_NODE_HALFCVT
+    // the byte b enters as f = 1024 + b (byte_as_biased_float), so t = f * S + O with S = s * idir,
+    // O = (p - o) * idir - 1024 S
+    const float sxs = u2f((e & 0xffu) << 23) * r.ix;
+    const float sys = u2f(((e >> 8) & 0xffu) << 23) * r.iy;
+    const float szs = u2f(((e >> 16) & 0xffu) << 23) * r.iz;
+    const float oxs = (px - r.ox) * r.ix;
+    const float oys = (py - r.oy) * r.iy;
+    const float ozs = (pz - r.oz) * r.iz;
+    // error bound of this evaluation + of the reference's own slab arithmetic (see bvh8.cuh):
+    // 2^-20 * (|O| + 255 |s idir|) + 2^-12 |s idir| (the rounding of O - 1024 S is 2^-14 |S|)
+    const float k1 = 9.5367431640625e-07f;                 // 2^-20
+    const float k2 = 255.0f * 9.5367431640625e-07f + 0.000244140625f;
+    const float mx = fma_f(fabsf(sxs), k2, fabsf(oxs) * k1);
+    const float my = fma_f(fabsf(sys), k2, fabsf(oys) * k1);
+    const float mz = fma_f(fabsf(szs), k2, fabsf(ozs) * k1);
+    const float bx = fma_f(sxs, -1024.0f, oxs), by = fma_f(sys, -1024.0f, oys), bz = fma_f(szs, -1024.0f, ozs);
+    const float onx = bx - mx, ofx = bx + mx;
+    const float ony = by - my, ofy = by + my;
+    const float onz = bz - mz, ofz = bz + mz;
+#else
     // grid scale per axis, pre-multiplied by 2^15 for the byte->float trick: the byte b enters
     // as f = 1 + b * 2^-15, so t = f * S + O with S = s * idir * 2^15, O = (p - o) * idir - S
     const float sxs = u2f(((e & 0xffu) + 15u) << 23) * r.ix;
@@ -122,9 +143,18 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
     const float ony = (oys - sys) - my, ofy = (oys - sys) + my;
     const float onz = (ozs - szs) - mz, ofz = (ozs - szs) + mz;
 
+#endif
+
     // near/far planes by direction sign (selected once per node, not per child)
     const bool nx = r.ix < 0.0f, ny = r.iy < 0.0f, nz = r.iz < 0.0f;
     uint32_t child_hits = 0u, ph = 0u;
+#if VSB_NODE_HALFCVT
+    const uint32_t one = half_bias_bits();
+#define VSB_PLANE_COORD byte_as_biased_float
+#else
+    const uint32_t one = unit_float_bits();
+#define VSB_PLANE_COORD byte_as_unit_float
+#endif
 #pragma unroll
     for (int half = 0; half < 2; ++half)
     {
@@ -137,12 +167,12 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
 #pragma unroll
         for (int k = 0; k < 4; ++k)
         {
-            const float tnx = fma_f(byte_as_unit_float(qnx, k), sxs, onx);
-            const float tny = fma_f(byte_as_unit_float(qny, k), sys, ony);
-            const float tnz = fma_f(byte_as_unit_float(qnz, k), szs, onz);
-            const float tfx = fma_f(byte_as_unit_float(qfx, k), sxs, ofx);
-            const float tfy = fma_f(byte_as_unit_float(qfy, k), sys, ofy);
-            const float tfz = fma_f(byte_as_unit_float(qfz, k), szs, ofz);
+            const float tnx = fma_f(VSB_PLANE_COORD(qnx, k, one), sxs, onx);
+            const float tny = fma_f(VSB_PLANE_COORD(qny, k, one), sys, ony);
+            const float tnz = fma_f(VSB_PLANE_COORD(qnz, k, one), szs, onz);
+            const float tfx = fma_f(VSB_PLANE_COORD(qfx, k, one), sxs, ofx);
+            const float tfy = fma_f(VSB_PLANE_COORD(qfy, k, one), sys, ofy);
+            const float tfz = fma_f(VSB_PLANE_COORD(qfz, k, one), szs, ofz);
             const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, limit));
             const uint32_t m = (meta4 >> (8 * k)) & 0xffu;       // leaf: count << 5 | offset; inner / empty: 0
@@ -153,6 +183,7 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
             }
         }
     }
+#undef VSB_PLANE_COORD
     prim_hits = ph;
     return perm_xor8(child_hits & (n.w[3] >> 24), r.octinv4 & 7u) << 24;
 }

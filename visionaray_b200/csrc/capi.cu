@@ -85,7 +85,7 @@ int g_band_streams = 2;    // 2: alternate bands over two streams (tail of band 
 int g_frame_bands = 8;     // cfg2 into pinned host memory: 1 band 11.8 ms, 2: 9.6, 16 interleaved bands on two streams: see DESIGN.md section 5
 
 // trace_queue: 1 = single-bvh BVH8 launches run trace_kernel_q (primitive tests shared by the warp), 0 = trace_kernel
-int g_trace_queue = 1, g_drain_min = 32, g_pend_min = 8;
+int g_trace_queue = 1, g_drain_min = 24, g_pend_min = 8;     // drain_min 16..24 measured best (cfg5 +3 % over 32)
 
 template <typename Program, bool EXACT>
 cudaError_t launch_trace(const Program& prog, vsb::TraceLaunch tl, cudaStream_t st)
