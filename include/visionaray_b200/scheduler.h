@@ -868,6 +868,8 @@ public:
     void set_tile_partition(int rank, int nranks) { tile_rank_ = rank; tile_nranks_ = nranks; }
     void set_seed(unsigned seed) { seed_ = seed; }
     void set_reference_order(bool on) { traverse_ = on ? VSB_TRAVERSE_EXACT : VSB_TRAVERSE_WIDE; }
+    // the surface arrays of the kernel params were modified in place: the next frame() uploads them again
+    void surface_changed() { surface_print_.clear(); }
 
     template <typename K, typename SP>
     void frame(K kernel, SP sparams, unsigned frame_num = 0)
@@ -908,9 +910,24 @@ public:
         for (auto it = kp.prims_begin; it != kp.prims_end; ++it) scenes.push_back(it->scene);
         if (kp.surface.present && (kp.surface.normals || kp.surface.normal_binding == VSB_NORMALS_FROM_PRIMITIVE) && !scenes.empty())
         {
+            // The arrays are deep-copied to the device (O(scene) upload + device syncs), so not on every frame: only when
+            // the description handed in differs from the one this scheduler last attached to this scene -- array
+            // addresses, bindings, texture descriptors.  A caller who rewrites the arrays IN PLACE between frames
+            // calls surface_changed() (or b200_index_bvh::set_surface() once, which bypasses this path).
             std::vector<vsb_texture> texs;
             vsb_surface_desc sd = kp.surface.flatten(texs);
-            detail::check(vsb_scene_set_surface(const_cast<vsb_scene*>(scenes[0]), &sd, VSB_MEM_HOST), "vsb_scene_set_surface");
+            std::vector<unsigned char> print(sizeof(void*) + sizeof(sd) + texs.size() * sizeof(vsb_texture));
+            void const* scene0 = scenes[0];
+            sd.textures = nullptr;                            // `texs` is a temporary: its address is not part of the identity
+            std::memcpy(print.data(), &scene0, sizeof(void*));
+            std::memcpy(print.data() + sizeof(void*), &sd, sizeof(sd));
+            if (!texs.empty()) std::memcpy(print.data() + sizeof(void*) + sizeof(sd), texs.data(), texs.size() * sizeof(vsb_texture));
+            sd.textures = texs.data();
+            if (print != surface_print_)
+            {
+                detail::check(vsb_scene_set_surface(const_cast<vsb_scene*>(scenes[0]), &sd, VSB_MEM_HOST), "vsb_scene_set_surface");
+                surface_print_.swap(print);
+            }
         }
         detail::check(vsb_frame(scenes.data(), int(scenes.size()), &d, nullptr), "vsb_frame");
 
@@ -934,6 +951,7 @@ private:
 
     int tile_rank_ = 0, tile_nranks_ = 0, traverse_ = VSB_TRAVERSE_WIDE;
     unsigned seed_ = 1;
+    std::vector<unsigned char> surface_print_;     // identity of the surface description last attached by frame()
 };
 
 } // namespace visionaray_b200

@@ -217,7 +217,11 @@ typedef struct vsb_frame_desc {
     int32_t  tile_target;                /* with tile_nranks > 1: VSB_TILES_COMPACT (default) or VSB_TILES_IN_PLACE =
                                             `color` is the whole row-major frame (width*height pixels), e.g. a peer
                                             GPU's buffer opened with vsb_ipc_open(): the rank's tiles are stored
-                                            straight into it over NVLink, no gather pass (device memory, no blend) */
+                                            straight into it over NVLink, no gather pass (device memory, no blend).
+                                            With mem = VSB_MEM_HOST the frame must be page-locked and mapped
+                                            (cudaHostAlloc / cudaHostRegister with cudaHostRegisterMapped): the
+                                            kernel stores finished pixels straight into it, so the ranks of a
+                                            node assemble ONE host frame in shared memory */
     /* sched_params built from matrices instead of a camera (make_sched_params(view, proj, rt),
      * scheduler.h:60-96,205-242): rays come from the inverse matrices (detail/sched_common.h:152-178;
      * the inverses are computed per frame on the host like detail/cuda_sched.inl:231-234).
@@ -235,7 +239,14 @@ typedef struct vsb_frame_desc {
 
 typedef struct vsb_scene vsb_scene;
 
-/* ---- context ---- */
+/* ---- context ----
+ * One context per process and GPU.  Streams and threads: every query / frame call takes a `cuda_stream`
+ * (NULL = the library's own non-blocking stream, see vsb_sync).  The calls of a context share device-side
+ * state (scene table, work counters, staging buffers), so the library orders them on the device itself: the
+ * stream of a call waits for the work of the previous call, whichever stream that ran on.  Mixing streams is
+ * therefore safe but does not overlap two calls.  Calls with device buffers return asynchronously; order the
+ * consumers of their outputs on the same stream (or synchronise it).  Host THREADS must serialise their calls
+ * into a context, like callers of the reference's frame() (detail/cuda_sched.inl:307-320, not re-entrant). */
 int  vsb_init(int device);                       /* cudaSetDevice + stream/queue state */
 int  vsb_shutdown(void);
 int  vsb_sync(void);                             /* wait for the library's own stream (calls made with cuda_stream == NULL) */
@@ -244,7 +255,8 @@ int  vsb_version(void);
 int  vsb_device_sm_count(int* out);
 /* scheduling knobs of the persistent traversal kernel: "query_service_min", "frame_service_min"
  * (idle lanes of a warp before finished rays are serviced / refilled, 1..32) and "phase_min"
- * (node/primitive phase vote threshold).  Results do not depend on them. */
+ * (node/primitive phase vote threshold); "trace_queue" (1: primitive tests shared by the warp, the default),
+ * "drain_min" / "pend_min" (its batching thresholds).  Results do not depend on them. */
 int  vsb_tune(const char* key, int value);
 
 /* ---- scene: replaces cuda_index_bvh<P>(index_bvh<P> const&) upload (bvh.h:344-350,446-447)
@@ -273,7 +285,10 @@ int  vsb_scene_download_bvh(const vsb_scene* s, vsb_bvh_node* nodes_out, size_t 
 int  vsb_last_build_ms(float* ms4, int* iterations);
 int  vsb_scene_destroy(vsb_scene* s);
 /* per-face normals kept on the device with the scene (what a cuda_sched user holds in a thrust
- * device_vector and hands to make_kernel_params, src/viewer/viewer.cpp:507-521); n = n_prims */
+ * device_vector and hands to make_kernel_params, src/viewer/viewer.cpp:507-521); n = n_prims, or more:
+ * normals[prim_id] is ONE array over all bvhs of a frame's range, so when a frame runs over several scenes
+ * the array attached to scenes[0] (or passed in vsb_frame_desc.normals) must reach the largest prim_id of
+ * all of them (vsb_frame returns VSB_ERR_BAD_ARG otherwise) */
 int  vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem);
 /* The surface description of the scene's triangles, deep-copied to the device (arrays and texels;
  * mem = where desc's arrays live) and used by every later vsb_frame() on this scene in place of the

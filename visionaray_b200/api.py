@@ -153,6 +153,38 @@ class Scene:
             pass
 
 
+def _torch_stream(stream):
+    """Device buffers are torch tensors: unless the caller names a stream, the call runs on torch's CURRENT stream,
+    so it is ordered behind the kernels that produced its inputs and ahead of whatever consumes (or recycles) its
+    outputs.  The legacy default stream has handle 0, which the C ABI reads as "the library's own stream": it is
+    passed as cudaStreamLegacy (0x1) instead."""
+    if stream is not None:
+        return stream
+    import torch
+
+    h = torch.cuda.current_stream().cuda_stream
+    return h if h else 1
+
+
+def _host_array(a, what, dtype=None, itemsize=None):
+    """numpy buffers cross the ABI as raw pointers: they must be C-contiguous and of the expected record type."""
+    if not a.flags["C_CONTIGUOUS"]:
+        raise ValueError(f"{what}: array must be C-contiguous")
+    if dtype is not None and a.dtype != dtype:
+        raise ValueError(f"{what}: dtype {a.dtype} where {dtype} is expected")
+    if itemsize is not None and a.nbytes % itemsize:
+        raise ValueError(f"{what}: {a.nbytes} bytes is not a whole number of {itemsize}-byte records")
+    return a
+
+
+def _device_tensor(a, what, itemsize=None):
+    if not a.is_contiguous():
+        raise ValueError(f"{what}: tensor must be contiguous")
+    if itemsize is not None and (a.numel() * a.element_size()) % itemsize:
+        raise ValueError(f"{what}: not a whole number of {itemsize}-byte records")
+    return a
+
+
 def _scene_array(scenes):
     arr = (C.c_void_p * len(scenes))(*[s.handle for s in scenes])
     return arr
@@ -165,19 +197,37 @@ def _query(fn, scenes, rays, max_t, max_t_per_ray, hits, traverse, stream):
     arr = _scene_array(scenes)
     if isinstance(rays, np.ndarray):
         n = rays.shape[0]
+        _host_array(rays, "rays", itemsize=32)
+        if rays.nbytes != n * 32:
+            raise ValueError("rays: 32-byte records (ori, pad, dir, pad) expected")
         if hits is None:
             hits = np.zeros(n, dtype=N.HIT_DTYPE)
+        _host_array(hits, "hits", itemsize=32)
+        if hits.nbytes < n * 32:
+            raise ValueError("hits: one 32-byte record per ray expected")
+        if max_t_per_ray is not None:
+            _host_array(max_t_per_ray, "max_t_per_ray", dtype=np.float32)
+            if max_t_per_ray.size < n:
+                raise ValueError("max_t_per_ray: one float per ray expected")
         mt = N.ptr(max_t_per_ray) if max_t_per_ray is not None else None
         _check(fn(arr, len(scenes), N.ptr(rays), n, max_t, mt, N.ptr(hits), MEM_HOST, traverse, stream), fn.__name__)
         return hits
     import torch
 
     n = rays.shape[0]
+    _device_tensor(rays, "rays", itemsize=32)
+    if rays.numel() * rays.element_size() != n * 32:
+        raise ValueError("rays: 32-byte records (ori, pad, dir, pad) expected")
     if hits is None:
         hits = torch.empty((n, 8), dtype=torch.int32, device=rays.device)
+    _device_tensor(hits, "hits", itemsize=32)
+    if max_t_per_ray is not None:
+        _device_tensor(max_t_per_ray, "max_t_per_ray")
+        if max_t_per_ray.dtype != torch.float32 or max_t_per_ray.numel() < n:
+            raise ValueError("max_t_per_ray: one float32 per ray expected")
     mt = C.c_void_p(max_t_per_ray.data_ptr()) if max_t_per_ray is not None else None
     _check(fn(arr, len(scenes), C.c_void_p(rays.data_ptr()), n, max_t, mt, C.c_void_p(hits.data_ptr()), MEM_DEVICE,
-              traverse, stream), fn.__name__)
+              traverse, _torch_stream(stream)), fn.__name__)
     return hits
 
 
@@ -207,8 +257,9 @@ def multi_hit(scenes, rays, max_hits=16, hits=None, traverse=TRAVERSE_WIDE, stre
 
     if hits is None:
         hits = torch.empty((n, max_hits, 8), dtype=torch.int32, device=rays.device)
+    _device_tensor(rays, "rays", itemsize=32); _device_tensor(hits, "hits", itemsize=32)
     _check(N.cuda_lib().vsb_multi_hit(arr, len(scenes), C.c_void_p(rays.data_ptr()), n, max_hits,
-                                      C.c_void_p(hits.data_ptr()), MEM_DEVICE, traverse, stream), "vsb_multi_hit")
+                                      C.c_void_p(hits.data_ptr()), MEM_DEVICE, traverse, _torch_stream(stream)), "vsb_multi_hit")
     return hits
 
 
@@ -302,7 +353,11 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     def p(a):
         if a is None:
             return None
-        return a.ctypes.data if isinstance(a, np.ndarray) else a.data_ptr()
+        if isinstance(a, np.ndarray):
+            return _host_array(a, "frame buffer / parameter array").ctypes.data
+        if hasattr(a, "is_contiguous"):
+            _device_tensor(a, "frame buffer / parameter tensor")
+        return a.data_ptr()
 
     d.normals, d.materials, d.lights, d.color = p(normals), p(materials), p(lights), p(color)
     d.depth = p(depth)
@@ -329,12 +384,13 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.spot_lights = 1 if spot_lights else 0
     d.color_format = color_format          # PF_RGBA32F 0, PF_RGBA8 1, PF_RGB32F 2 (16-byte pixels), PF_RGB8 3
     d.ray_count = p(ray_count)
-    _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), stream), "vsb_frame")
+    uses_torch = any(hasattr(a, "is_contiguous") for a in (normals, materials, lights, color, depth, ray_count) if a is not None)
+    _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), _torch_stream(stream) if uses_torch else stream), "vsb_frame")
     return color
 
 
 def deinterleave_tiles(gathered, width, height, nranks, tiles_per_rank_padded, image, stream=None):
     _check(N.cuda_lib().vsb_deinterleave_tiles(C.c_void_p(gathered.data_ptr()), width, height, nranks,
-                                               tiles_per_rank_padded, C.c_void_p(image.data_ptr()), stream),
+                                               tiles_per_rank_padded, C.c_void_p(image.data_ptr()), _torch_stream(stream)),
            "vsb_deinterleave_tiles")
     return image

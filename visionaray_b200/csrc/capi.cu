@@ -115,6 +115,7 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
     if (!rays || !hits) return VSB_ERR_BAD_ARG;
     if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT) return VSB_ERR_BAD_ARG;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    CallOrder order(st);
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
@@ -290,6 +291,7 @@ extern "C" int vsb_multi_hit(const vsb_scene* const* scenes, int n_scenes, const
     if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT) return VSB_ERR_BAD_ARG;
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    CallOrder order(st);
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
     if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
@@ -423,8 +425,13 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         rc = scene_id_range(scenes[i]); if (rc) return rc;
         if (p.kernel != VSB_KERNEL_AO && scenes[i]->max_geom_id >= (uint32_t)p.n_materials) return VSB_ERR_BAD_ARG;   // materials[geom_id]
     }
-    if (n_scenes == 1 && scenes[0]->max_prim_id >= scenes[0]->n_prims) return VSB_ERR_BAD_ARG;                      // normals[prim_id]
+    // normals[prim_id] is ONE array over all bvhs of the range (get_normal.h:28-37): it must cover the largest prim_id
+    size_t normals_needed = 0;
+    for (int i = 0; i < n_scenes; ++i)
+        if ((size_t)scenes[i]->max_prim_id + 1 > normals_needed) normals_needed = (size_t)scenes[i]->max_prim_id + 1;
+    if (n_scenes == 1 && normals_needed > scenes[0]->n_prims) return VSB_ERR_BAD_ARG;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
+    CallOrder order(st);
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
     struct { vsb::FrameCtx ctx; int scissor[4]; float4* color; float* depth; int tile_rank, tile_nranks, tiles_x, tiles_y, n_owned_tiles, in_place;
@@ -447,9 +454,11 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     std::memcpy(fl.scissor, d->scissor, sizeof(fl.scissor));
     if (fl.scissor[2] <= 0 || fl.scissor[3] <= 0) { fl.scissor[0] = 0; fl.scissor[1] = 0; fl.scissor[2] = p.width; fl.scissor[3] = p.height; }
 
-    const size_t n_normals = scenes[0]->n_prims;
+    const size_t n_normals = n_scenes == 1 ? scenes[0]->n_prims : normals_needed;      // what a host `normals` array must hold
     fl.in_place = (nranks > 1 && d->tile_target == VSB_TILES_IN_PLACE) ? 1 : 0;
-    if (fl.in_place && (d->mem != VSB_MEM_DEVICE || p.pixel_sampler == VSB_PS_JITTERED_BLEND)) return VSB_ERR_UNSUPPORTED;
+    // in-place tiles go to device memory (a peer's frame over NVLink) or, for a host frame that several ranks share, to
+    // PINNED + MAPPED host memory the kernel stores into directly (checked below); never with a blend, which re-reads the target
+    if (fl.in_place && p.pixel_sampler == VSB_PS_JITTERED_BLEND) return VSB_ERR_UNSUPPORTED;
     if (d->color_format < VSB_PF_RGBA32F || d->color_format > VSB_PF_RGB8) return VSB_ERR_BAD_ARG;
     if (d->color_format != VSB_PF_RGBA32F && nranks > 1 && !fl.in_place) return VSB_ERR_UNSUPPORTED;   // compact tile buffers + de-interleave are RGBA32F
     const size_t bpp = d->color_format == VSB_PF_RGBA8 ? 4 : (d->color_format == VSB_PF_RGB8 ? 3 : 16);
@@ -460,6 +469,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     fl.ctx.surf = scenes[0]->surf;
     if (fl.ctx.surf.enabled && (n_scenes != 1 || p.kernel == VSB_KERNEL_AO)) return VSB_ERR_UNSUPPORTED;
     if (!d->normals && !scenes[0]->d_normals && !fl.ctx.surf.enabled) return VSB_ERR_BAD_ARG;
+    if (!d->normals && !fl.ctx.surf.enabled && scenes[0]->n_normals < normals_needed) return VSB_ERR_BAD_ARG;   // attached array too small for the range
     fl.ctx.normals = d->normals ? reinterpret_cast<const float4*>(d->normals) : scenes[0]->d_normals;
     bool generic_materials = d->generic_materials != 0;
     if (d->params_mem == VSB_MEM_HOST && d->materials)
@@ -495,7 +505,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     // pixel goes over PCIe while the other lanes keep traversing, so there is no D2H pass after the
     // trace.  Pageable targets and progressive blending (which re-reads the target) are staged.
     bool direct_host = false;
-    if (d->mem == VSB_MEM_HOST && g_host_store && p.pixel_sampler != VSB_PS_JITTERED_BLEND)
+    if (d->mem == VSB_MEM_HOST && (g_host_store || fl.in_place) && p.pixel_sampler != VSB_PS_JITTERED_BLEND)
     {
         cudaPointerAttributes ac, az;
         void* dev_c = nullptr; void* dev_z = nullptr;
@@ -515,6 +525,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
             if (d->ray_count) d_ray_count = g.d_work + 1;
         }
     }
+    if (fl.in_place && d->mem == VSB_MEM_HOST && !direct_host) return VSB_ERR_UNSUPPORTED;   // pageable / unmapped shared frame
     if (direct_host) {}
     else if (d->mem == VSB_MEM_HOST)
     {

@@ -15,6 +15,8 @@ struct Context
     cudaEvent_t  band_done[32] = {}, band_up[32] = {};
     cudaEvent_t  band_fork = nullptr, band_join = nullptr;
     cudaEvent_t  ev0 = nullptr, ev1 = nullptr;
+    cudaEvent_t  call_done = nullptr;       // recorded behind the device work of every query / frame call (CallOrder below)
+    bool         call_done_valid = false;
     unsigned long long* d_work = nullptr;   // persistent-kernel work counter
     vsb::DeviceScene* d_scenes = nullptr;   // scene table handed to kernels (up to MAX_SCENES)
     void*        staging[24] = {};
@@ -34,6 +36,24 @@ int require_init()
     if (!g.inited) return VSB_ERR_NOT_INIT;
     return VSB_OK;
 }
+
+// The scene table, the work counters and the staging slots are per-context device state that every query / frame
+// call rewrites.  Calls may come on different streams (the library's own, the caller's, torch's current one) and
+// device-memory calls return asynchronously, so each call's stream first waits for the work of the previous call:
+// calls on one context are ordered on the device however the caller mixes streams (the reference's frame() is
+// not re-entrant either, detail/cuda_sched.inl:307-320).  Host THREADS must still serialise their calls.
+struct CallOrder
+{
+    cudaStream_t st;
+    explicit CallOrder(cudaStream_t s) : st(s)
+    {
+        if (g.call_done_valid) cudaStreamWaitEvent(st, g.call_done, 0);
+    }
+    ~CallOrder()
+    {
+        if (cudaEventRecord(g.call_done, st) == cudaSuccess) g.call_done_valid = true;
+    }
+};
 
 // grow-only device staging buffer for host-memory callers
 int stage(int slot, size_t bytes, void** out)
@@ -62,6 +82,7 @@ struct vsb_scene
     vsb::Node80* d_wide = nullptr;
     void*    d_wide_prims = nullptr;
     float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
+    size_t   n_normals = 0;              // entries of d_normals (>= max_prim_id + 1; a frame over several bvhs indexes ONE array by prim_id)
     mutable int id_range_known = 0;      // largest prim_id / geom_id of the primitives, computed on first use
     mutable uint32_t max_prim_id = 0, max_geom_id = 0;
     vsb::SurfCtx surf = {};              // optional, vsb_scene_set_surface(); device copies listed in surf_allocs
@@ -86,7 +107,7 @@ int validate_tree(const vsb_bvh_node* nodes, size_t n_nodes, const uint32_t* ind
     std::vector<std::pair<uint32_t, int>> st;
     st.push_back({ 0u, 1 });
     int maxd = 0;
-    size_t visited = 0;
+    size_t visited = 0, leaf_total = 0;
     *big_leaves = false;
     const size_t list_len = indices ? n_idx : n_prims;
     while (!st.empty())
@@ -106,6 +127,8 @@ int validate_tree(const vsb_bvh_node* nodes, size_t n_nodes, const uint32_t* ind
         else
         {
             if ((size_t)n.first + n.num_prims > list_len) return VSB_ERR_BAD_TREE;
+            leaf_total += n.num_prims;
+            if (leaf_total > list_len) return VSB_ERR_BAD_TREE;   // overlapping leaf ranges: the wide encode's scratch holds list_len records
             if (n.num_prims > 4) *big_leaves = true;
             if (indices)
                 for (uint32_t k = 0; k < n.num_prims; ++k)
@@ -172,6 +195,8 @@ extern "C" int vsb_init(int device)
     VSB_CUDA(cudaEventCreateWithFlags(&g.band_join, cudaEventDisableTiming));
     VSB_CUDA(cudaEventCreate(&g.ev0));
     VSB_CUDA(cudaEventCreate(&g.ev1));
+    VSB_CUDA(cudaEventCreateWithFlags(&g.call_done, cudaEventDisableTiming));
+    g.call_done_valid = false;
     VSB_CUDA(cudaMalloc(&g.d_work, 64 * sizeof(unsigned long long)));   // [0] queue, [1] ray count, [2..33] band queues
     VSB_CUDA(cudaMalloc(&g.d_scenes, sizeof(vsb::DeviceScene) * MAX_SCENES));
     {
@@ -193,6 +218,8 @@ extern "C" int vsb_shutdown(void)
     if (g.d_scenes) cudaFree(g.d_scenes);
     if (g.ev0) cudaEventDestroy(g.ev0);
     if (g.ev1) cudaEventDestroy(g.ev1);
+    if (g.call_done) cudaEventDestroy(g.call_done);
+    g.call_done = nullptr; g.call_done_valid = false;
     if (g.stream) cudaStreamDestroy(g.stream);
     if (g.copy_stream) cudaStreamDestroy(g.copy_stream);
     if (g.band_stream) cudaStreamDestroy(g.band_stream);
@@ -396,11 +423,15 @@ int scene_id_range(const vsb_scene* s)
 extern "C" int vsb_scene_set_normals(vsb_scene* s, const float* normals16, size_t n, int mem)
 {
     int rc = require_init(); if (rc) return rc;
-    if (!s || !normals16 || n != s->n_prims) return VSB_ERR_BAD_ARG;
+    // n is normally n_prims; a scene that is ONE of several bvhs of a frame carries the whole range's array
+    // (the reference indexes normals[prim_id] over all bvhs of [begin, end), get_normal.h:28-37)
+    if (!s || !normals16 || n < 1) return VSB_ERR_BAD_ARG;
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
     rc = scene_id_range(s); if (rc) return rc;
     if (s->max_prim_id >= n) return VSB_ERR_BAD_ARG;          // normals[prim_id] would leave the array
+    if (s->d_normals && s->n_normals != n) { cudaFree(s->d_normals); s->d_normals = nullptr; }
     if (!s->d_normals) VSB_CUDA(cudaMalloc((void**)&s->d_normals, n * 16));
+    s->n_normals = n;
     VSB_CUDA(cudaMemcpyAsync(s->d_normals, normals16, n * 16,
                              mem == VSB_MEM_HOST ? cudaMemcpyHostToDevice : cudaMemcpyDeviceToDevice, g.stream));
     VSB_CUDA(cudaStreamSynchronize(g.stream));

@@ -32,6 +32,7 @@ struct MultiHitSink
     Hit32* rec;
     int    n;
     float  limit;      // rec[n - 1].t: what a box / primitive must beat
+    uint32_t scene_tag = 0u;   // index of the bvh being walked (rides in rec[].pad while a ray is in flight, see contains())
 
     VSB_HD void reset()
     {
@@ -46,14 +47,15 @@ struct MultiHitSink
     // Is this primitive already recorded at this t?  A tree built with spatial splits (SBVH,
     // detail/bvh/sah.h:430-615) references a primitive from several leaves; the BVH8 walk may reach a
     // different subset of those references than the reference-order walk does, so it reports every
-    // primitive once (the records are sorted: the scan stops at the first larger t).
+    // primitive once (the records are sorted: the scan stops at the first larger t).  Scoped to the bvh being
+    // walked: the same geometry in two bvhs of a range is two hits, as in the reference.
     VSB_HD bool contains(float t, uint32_t prim_id, uint32_t geom_id) const
     {
         for (int k = 0; k < n; ++k)
         {
             const float tk = rec[k].t;
             if (tk > t) return false;
-            if (tk == t && rec[k].prim_id == prim_id && rec[k].geom_id == geom_id) return true;
+            if (tk == t && rec[k].prim_id == prim_id && rec[k].geom_id == geom_id && rec[k].pad == scene_tag) return true;
         }
         return false;
     }
@@ -64,7 +66,7 @@ struct MultiHitSink
         int pos = 0;
         while (pos < n - 1 && !(t < rec[pos].t)) ++pos;        // first record with a larger t (the last one qualifies: t < limit)
         for (int k = n - 1; k > pos; --k) rec[k] = rec[k - 1];
-        Hit32 h; h.hit = 1; h.prim_id = prim_id; h.geom_id = geom_id; h.t = t; h.u = u; h.v = v; h.prim_list_index = list_index; h.pad = 0u;
+        Hit32 h; h.hit = 1; h.prim_id = prim_id; h.geom_id = geom_id; h.t = t; h.u = u; h.v = v; h.prim_list_index = list_index; h.pad = scene_tag;
         rec[pos] = h;
         limit = rec[n - 1].t;
     }
@@ -198,6 +200,7 @@ __global__ void __launch_bounds__(128) multi_hit_kernel(const SceneTable* __rest
     // a range of BVHs: the records of every BVH merged by t (update_if(array, array), detail/multi_hit.h:181-202)
     for (int k = 0; k < n_scenes; ++k)
     {
+        sink.scene_tag = (uint32_t)k;
         if (EXACT) multi_hit_exact(scenes[k].exact, ray.ox, ray.oy, ray.oz, ray.dx, ray.dy, ray.dz, sink);
         else
         {
@@ -206,6 +209,8 @@ __global__ void __launch_bounds__(128) multi_hit_kernel(const SceneTable* __rest
             multi_hit_wide(scenes[k].wide, rc, sink);
         }
     }
+    if (n_scenes > 1)
+        for (int k = 0; k < max_hits; ++k) sink.rec[k].pad = 0u;      // the tag is scratch: records leave with pad 0
 }
 
 #endif
