@@ -19,8 +19,28 @@ def _function_starts():
         if m: out.append((i,m.group(1)))
     return out
 _FN=_function_starts()
-_KIND={"test_node":"node_test","perm_xor8":"node_test","test_prim":"prim_test (record decode, accept)","load_record":"record loads","ldg_hint":"record loads",
+_KIND={"test_node":"node_test","perm_xor8":"node_test","test_prim":"prim_test (record decode, accept)","prim_candidate":"prim_test (record decode, accept)","hit_from_record":"hit record of the winner (once per ray)","load_record":"record loads","ldg_hint":"record loads",
        "ray_ctx_init":"ray_init","stack_push":"stack","stack_pop":"stack","trav_begin":"stack","trav_step":"trav_step control"}
+def _kernel_markers():
+    """regions of trace_kernel_q (kernels.cuh) by the marker comments of its loop"""
+    path=os.path.join(os.path.dirname(os.path.abspath(__file__)),"..","visionaray_b200","csrc","kernels.cuh")
+    marks=[("auto drain = ","queue: drain (pair fetch, ray from shared, key merge)"),("// ---- continuations of finished rays","kernel loop (service, refill, program)"),
+           ("// ---- node phase","queue: node phase control"),("// ---- append the selected","queue: append + drain decision"),
+           ("if (drained && (state","queue: limit refresh / state"),("if (tl.ray_count)","kernel loop (service, refill, program)")]
+    out=[]; inq=False
+    for i,l in enumerate(open(path),1):
+        if "trace_kernel_q(const TraceLaunch" in l: inq=True
+        if "struct RayListProgram" in l: inq=False
+        if not inq: continue
+        for key,name in marks:
+            if key in l: out.append((i,name))
+    return out
+_KM=_kernel_markers()
+def _kernel_region(ln):
+    name="kernel loop (service, refill, program)"
+    for start,n in _KM:
+        if start<=ln: name=n
+    return name
 def region(fn, ln, src):
     if fn=="bvh8_traverse.cuh":
         name=""
@@ -29,7 +49,7 @@ def region(fn, ln, src):
         return _KIND.get(name,"trav_step control")
     if fn=="bvh8.cuh": return "node_test"
     if fn=="vsb_common.cuh": return "isect_triangle / rn arithmetic (vsb_common.cuh)"
-    if fn=="kernels.cuh": return "kernel loop (service, refill, program)"
+    if fn=="kernels.cuh": return _kernel_region(ln)
     if fn=="shade.cuh": return "shade programs"
     return fn
 path=sys.argv[1]
