@@ -1,0 +1,289 @@
+#!/usr/bin/env python
+"""bench.py -- Mrays/s of the ray-query hot path on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2|cfg1|cfg3|cfg4|cfg5] [--impl reference]
+
+A "step" is one frame() call over the workload's synthetic scene (one pass of ray generation +
+closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.json configs[1]:
+4096x4096 primary rays + Whitted shading vs the 1,002,528-triangle displaced grid.
+
+  value     rays traced / device time of the timed region, scene + parameter arrays + framebuffer
+            resident in HBM (rays are counted by the kernel: primary + shadow + bounce rays)
+  e2e       the same metric through the host-buffer call a user of the reference makes (frame() into a
+            host render target): parameter H2D + framebuffer D2H inside the region.  N > 1: ONE assembled
+            frame in a pinned host buffer that all ranks map (rank 0 reads it)
+  roofline  node-fetch memory roofline of SURVEY.md section 8d: B_ray = 64 N_inner + 68 N_prim + 64
+            bytes per ray on the REFERENCE data layout (N_* counted by the oracle's instrumented
+            traversal of the scene's BVH2 on a down-sampled frame of the same view), against
+            MEASURED_PEAKS.json hbm_gbs.  The kernel is bound by issue slots, not HBM: `bound` says so,
+            `issue` carries the binding figures from the committed ncu capture (profiles/issue.json)
+  cpu_baseline  the reference's own tiled_sched<simd::ray8> (oracle/_ref, unmodified headers) on the
+            host cores, on the SAME frame as the GPU arm
+  extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3
+  strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 (peer stores over NVLink) and
+            cfg4 (progressive path tracer: all-gather + de-interleave), with v_N / (N v_1)
+
+N > 1 (torchrun): the frame is partitioned into interleaved 64x64 tiles (tile k -> rank k % N), the
+scene is replicated.  Headline = weak scaling: the same view at sqrt(N) x the resolution per axis
+(4096^2 pixels per GPU).  The tree is built on the GPU (vsb_scene_build) unless --builder reference.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import math
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SMI_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+             "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+KERNEL_NAMES = {0: "simple", 1: "whitted", 2: "ao", 3: "pathtracing"}
+# name -> (scene, kernel, base width, base height, eye, center, frame kwargs, material kind)
+WORKLOADS = {
+    "cfg1": dict(scene="cfg1_sphere", kernel=0, w=1024, h=1024, eye=(0.0, 0.0, 3.0), mat=0,
+                 desc="1024x1024 primary closest-hit, simple kernel, 99,904-tri UV sphere"),
+    "cfg2": dict(scene="cfg2_grid", kernel=1, w=4096, h=4096, eye=(0.3, 1.2, 2.2), mat=0,
+                 desc="4096x4096 primary + Whitted shading, 1,002,528-tri displaced grid"),
+    "cfg3": dict(scene="cfg3_cubes", kernel=2, w=2048, h=2048, eye=(0.6, 1.4, 2.6), mat=0,
+                 desc="2048x2048 AO any-hit 16 rays/pixel, 5,000,004-tri cube field"),
+    "cfg4": dict(scene="cfg4_terrain", kernel=3, w=4096, h=4096, eye=(0.3, 1.2, 2.2), mat=1,
+                 desc="4096x4096 path tracer 8 diffuse bounces, ~10M-tri terrain"),
+}
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index: int):
+        self.index, self.proc, self.lines = index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={SMI_QUERY}", "--format=csv,noheader,nounits", "-lms", "100"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append((time.time(), line.strip()))
+
+    def stop(self, t0: float, t1: float) -> dict:
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        rows = [l for (t, l) in self.lines if t0 <= t <= t1 + 0.1] or [l for (_, l) in self.lines[-3:]]
+        sm, smax, power, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for l in rows:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1])); smax.append(float(f[2])); power.append(float(f[3]))
+            except ValueError:
+                continue
+            for name, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(smax) if smax else None,
+                "power_w_max": max(power) if power else None, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            with open(path) as f:
+                return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            pass
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+def _profile_json(name: str, key: str):
+    try:
+        with open(os.path.join(ROOT, "profiles", name)) as f:
+            return json.load(f).get(key)
+    except Exception:
+        return None
+
+
+def measured_traffic(key: str):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu capture (profiles/traffic.json), or None."""
+    e = _profile_json("traffic.json", key)
+    return int(e["bytes"]) if e else None
+
+
+def measured_issue(key: str):
+    """What binds the kernel, from the committed ncu capture of the same command (profiles/issue.json):
+    issue-slot utilisation, active threads per instruction, their product, the alu pipe."""
+    return _profile_json("issue.json", key)
+
+
+def frame_shape(wl: dict, n_gpus: int):
+    """Weak scaling: the same view at sqrt(N) x the resolution per axis (rounded to whole 64-pixel
+    tiles), i.e. base-frame pixels per GPU and the same mix of sky / geometry / secondary rays."""
+    if n_gpus <= 1:
+        return wl["w"], wl["h"]
+    f = math.sqrt(n_gpus)
+    return int(round(wl["w"] * f / 64.0)) * 64, int(round(wl["h"] * f / 64.0)) * 64
+
+
+def make_frame_params(S, wl: dict, w: int, h: int, frame_num: int = 1):
+    kernel = wl["kernel"]
+    kw = dict(pixel_sampler=0, num_bounces=4, epsilon=1e-3)
+    if kernel == 3:
+        kw = dict(pixel_sampler=2, num_bounces=8, epsilon=1e-3, ambient=(1.0, 1.0, 1.0, 1.0))
+    if kernel == 2:
+        kw = dict(pixel_sampler=0, ao_samples=16, ao_radius=0.1)
+    return S.frame_params(kernel, w, h, wl["eye"], (0.0, 0.0, 0.0), frame_num=frame_num, **kw)
+
+
+def workload_config(wl: dict, w: int, h: int, scale: float, n_prims: int) -> dict:
+    """The part of `config` that names the workload: identical in the GPU arm and in --impl reference."""
+    return {"workload": wl["desc"], "frame": [w, h], "scale": scale, "kernel": KERNEL_NAMES[wl["kernel"]],
+            "triangles": int(n_prims),
+            "l2": f"inputs larger than L2: framebuffer {w * h * 16 >> 20} MiB rewritten every step + {n_prims * 64 >> 20} MiB of "
+                  f"triangles (126 MB L2)"}
+
+
+def raylist_config(n_prims: int, any_hit: bool, n_batch: int, scale: float) -> dict:
+    return {"workload": f"incoherent random rays vs {n_prims}-tri soup, {'any' if any_hit else 'closest'}-hit, batches of {n_batch} rays per GPU",
+            "scale": scale, "triangles": int(n_prims),
+            "l2": f"inputs larger than L2: 4 rotating ray/hit batches ({4 * n_batch * 64 >> 20} MiB) + {n_prims * 64 >> 20} MiB of triangles (126 MB L2)"}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU side: algorithmic bytes per ray (oracle counters), cpu_baseline, and the --impl reference arm
+# ------------------------------------------------------------------------------------------------
+
+def algorithmic_bytes_per_ray(O, S, sc, wl, mats, lights, sample_wh=(512, 512)):
+    """B_ray = 64 N_inner + 68 N_prim + 64 from the oracle's instrumented scalar
+    traversal of the scene's BVH2 (reference layout) on a down-sampled frame of the same view."""
+    fp = make_frame_params(S, wl, *sample_wh)
+    c = O.Counters()
+    O.oracle_frame(sc, fp, mats, lights, counters=c)
+    n = max(int(c.n_rays), 1)
+    n_inner, n_prim = c.n_inner / n, c.n_prim / n
+    prim_bytes = 68.0 if sc.prim_kind == 0 else 52.0
+    return 64.0 * n_inner + prim_bytes * n_prim + 64.0, dict(n_inner=n_inner, n_prim=n_prim, rays_per_pixel=n / (sample_wh[0] * sample_wh[1]))
+
+
+def cpu_frame_seconds(O, S, sc, wl, mats, lights, w, h, reps, warmup, cores):
+    """Seconds per frame() of the reference's tiled_sched<simd::ray8> (oracle/_ref, unmodified headers, -O3 -mavx2
+    -mfma) on `cores` host threads; the oracle port (scalar C, pthreads) when _ref is absent.  -> (secs, kind)"""
+    fp = make_frame_params(S, wl, w, h)
+    if O.ref_available(fast=True):
+        _, secs, _ = O.ref_frame(sc, fp, mats, lights, mode=1, reps=reps, warmup=warmup, fast=True, nthreads=cores)
+        return secs, "reference"
+    best = None
+    for _ in range(max(reps, 1)):
+        t0 = time.perf_counter()
+        O.oracle_frame(sc, fp, mats, lights)
+        dt = time.perf_counter() - t0
+        best = dt if best is None else min(best, dt)
+    return best, "port"
+
+
+def frame_ray_count(O, S, sc, wl, mats, lights, w, h):
+    """Rays of one frame (primary + shadow + bounce), counted by the oracle on a frame of 1/4 the resolution per axis
+    of the same view and scaled by 16 (the full-frame count is what the GPU arm's kernel counter reports; the CPU
+    side uses this estimate so that counting does not cost more than the timed frames)."""
+    dw, dh = max(w // 4, 64), max(h // 4, 64)
+    c = O.Counters()
+    O.oracle_frame(sc, make_frame_params(S, wl, dw, dh), mats, lights, counters=c)
+    return int(round(int(c.n_rays) * (w * h) / float(dw * dh)))
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path on the host cores, on the SAME frame
+    as the GPU arm at this N (the weak-scaled frame for N > 1; rank 0 alone runs)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    import __graft_entry__ as g
+    g.build_host_only()
+    from oracle import bindings as O
+    from visionaray_b200 import scenes as S
+
+    cores = os.cpu_count() or 1
+    if args.workload == "cfg5":
+        return run_reference_raylist(args, O, S, cores)
+    wl = WORKLOADS[args.workload]
+    w, h = frame_shape(wl, args.gpus)
+    sc = S.make_scene(wl["scene"], args.scale)            # the reference's binned-SAH tree (host builder)
+    mats, lights = S.default_material(wl["mat"]), S.point_light(wl["eye"])
+    rays = frame_ray_count(O, S, sc, wl, mats, lights, w, h)
+    kind = "reference" if O.ref_available(fast=True) else "port"
+    times = []
+    for i in range(args.warmup + args.steps):
+        secs, kind = cpu_frame_seconds(O, S, sc, wl, mats, lights, w, h, reps=1, warmup=0, cores=cores)
+        if i >= args.warmup:
+            times.append(secs)
+    ms = 1e3 * float(np.mean(times))
+    value = rays / (ms * 1e-3) / 1e6
+    how = "tiled_sched<simd::ray8> AVX2 (unmodified headers)" if kind == "reference" else "scalar C port, pthreads"
+    sample = f"the whole {w}x{h} frame per step ({rays} rays, counted on a {max(w // 4, 64)}x{max(h // 4, 64)} frame of the view x 16), {how}"
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(wl, w, h, args.scale, sc.n_prims),
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind, "sample": sample},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def run_reference_raylist(args, O, S, cores):
+    """cfg5 on the host cores: scalar closest_hit()/any_hit() of the unmodified headers over std::threads."""
+    sc = S.make_scene("cfg5_soup", args.scale)
+    n = min(args.batch, 2_000_000)
+    rays = S.random_rays(n, 600)
+    times = []
+    kind = "reference" if O.ref_available(fast=True) else "port"
+    for i in range(args.warmup + args.steps):
+        if kind == "reference":
+            secs, _ = O.ref_query_timed(sc, rays, bool(args.any), nthreads=cores, reps=1, warmup=0)
+        else:
+            t0 = time.perf_counter()
+            O.oracle_query(sc, rays, bool(args.any))
+            secs = time.perf_counter() - t0
+        if i >= args.warmup:
+            times.append(secs)
+    ms = 1e3 * float(np.mean(times))
+    value = n / (ms * 1e-3) / 1e6
+    line = {
+        "impl": "reference", "metric": "Mrays/s", "value": value, "unit": "Mrays/s", "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": raylist_config(sc.n_prims, bool(args.any), args.batch, args.scale),
+        "cpu_baseline": {"value": value, "unit": "Mrays/s", "cores": cores, "kind": kind,
+                         "sample": f"{n} rays of the batch per step, scalar closest_hit()/any_hit() on {cores} threads"},
+        "e2e": {"value": value, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+    return 0
