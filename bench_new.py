@@ -287,3 +287,89 @@ def run_reference_raylist(args, O, S, cores):
     }
     print(json.dumps(line), flush=True)
     return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm: scene preparation and the context every leg shares
+# ------------------------------------------------------------------------------------------------
+
+def prepare_scene(api, S, scene_name: str, scale: float, builder: str):
+    """-> (host scene, device scene, builder info incl. time to a traceable scene).
+    --builder gpu (default): primitives only on the host, the tree is built on the GPU (vsb_scene_build:
+    Morton sort + PLOC + SAH leaf collapse + BVH8 re-encode).  --builder reference: the reference's binned-SAH
+    tree from the host builder (tie-order parity anchor), uploaded and re-encoded."""
+    t0 = time.perf_counter()
+    sc = S.make_scene(scene_name, scale, build_tree=(builder == "reference"))
+    gen_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    if builder == "gpu":
+        dev = api.Scene.build(sc.prim_kind, sc.prims, sc.normals)
+        api.sync()
+        ms = api.last_build_ms()
+        info = {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2),
+                "iterations": ms["iterations"]}
+    else:
+        dev = api.Scene(sc)
+        api.sync()
+        info = {"kind": "reference binned SAH (host builder, inside scene generation)"}
+    info["scene_generation_s"] = round(gen_s, 3)
+    info["upload_and_build_s"] = round(time.perf_counter() - t0, 3)      # H2D of the primitives + build + re-encode, wall clock
+    return sc, dev, info
+
+
+def oracle_scene(S, sc, dev):
+    """The scene with its BVH2 in the reference layout, for the oracle's instrumented traversal (the B_ray
+    counters): the host tree if there is one, else the GPU-built tree downloaded (bvh_node[] + indices[])."""
+    if sc.nodes is not None:
+        return sc
+    nodes, idx = dev.download_bvh()
+    return S.HostScene(sc.prim_kind, sc.prims, nodes, idx, sc.normals, sc.name)
+
+
+class Ctx:
+    """What every GPU leg shares: modules, ranks, the main stream."""
+
+    def __init__(self, args):
+        import torch
+        import torch.distributed as dist
+
+        self.torch, self.dist, self.args = torch, dist, args
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device -- the ray-query path has no CPU fallback")
+        torch.cuda.set_device(self.local_rank)
+        if self.world > 1:
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local_rank))
+        from visionaray_b200 import api, scenes as S
+
+        self.api, self.S = api, S
+        api.init(self.local_rank)
+        # a real (non-legacy) stream: the C ABI treats a NULL stream as "the library's own stream"
+        self.main = torch.cuda.Stream()
+        torch.cuda.set_stream(self.main)
+        self.trav = api.TRAVERSE_EXACT if args.traverse == "exact" else api.TRAVERSE_WIDE
+
+    def fence(self):
+        if self.world > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def max_over_ranks(self, x: float) -> float:
+        t = self.torch.tensor([x], dtype=self.torch.float64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum_over_ranks(self, x: int) -> int:
+        t = self.torch.tensor([x], dtype=self.torch.int64, device="cuda")
+        if self.world > 1:
+            self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return int(t.item())
+
+    def close(self):
+        if self.world > 1:
+            self.dist.barrier()
+            self.dist.destroy_process_group()
