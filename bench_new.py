@@ -373,3 +373,158 @@ class Ctx:
         if self.world > 1:
             self.dist.barrier()
             self.dist.destroy_process_group()
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm: one workload / frame size / assembly mode
+# ------------------------------------------------------------------------------------------------
+
+class FrameRig:
+    """Device-resident buffers and step() of one frame workload.  Modes:
+       single  one GPU renders the whole frame into its own buffer
+       peer    N > 1: every rank stores its tiles straight into rank 0's frame over NVLink peer memory (CUDA IPC)
+               from inside the trace kernel; a 4-byte all-reduce per step is the frame fence
+       nccl    N > 1: compact tile buffers + NCCL all-gather + de-interleave on a side stream, double-buffered
+               (the progressive path tracer: its blend re-reads the rank's own previous frame)"""
+
+    def __init__(self, ctx: Ctx, wl: dict, dev, w: int, h: int, mode: str):
+        torch, api = ctx.torch, ctx.api
+        self.ctx, self.wl, self.dev, self.w, self.h, self.mode = ctx, wl, dev, w, h, mode
+        self.mats, self.lights = ctx.S.default_material(wl["mat"]), ctx.S.point_light(wl["eye"])
+        self.d_mats = torch.from_numpy(self.mats.view(np.float32).copy()).cuda()
+        self.d_lights = torch.from_numpy(self.lights.view(np.float32).copy()).cuda()
+        self.d_rays = torch.zeros(1, dtype=torch.int64, device="cuda")
+        self.per = max(api.tiles_of_rank(w, h, r, ctx.world) for r in range(ctx.world))
+        self.k = 0
+        self.frame_buf = None
+        if mode == "single":
+            self.image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+        elif mode == "peer":
+            handle = [None]
+            if ctx.rank == 0:
+                self.frame_buf = api.DeviceBuffer(w * h * 16)
+                handle[0] = self.frame_buf.export()
+            ctx.dist.broadcast_object_list(handle, src=0)
+            if ctx.rank != 0:
+                self.frame_buf = api.DeviceBuffer.open(handle[0], w * h * 16)
+            self.done_flag = torch.zeros(1, dtype=torch.float32, device="cuda")
+        else:
+            T = api.TILE * api.TILE
+            self.tile_buf = [torch.zeros((self.per, T, 4), dtype=torch.float32, device="cuda") for _ in range(2)]
+            self.gathered = torch.zeros((ctx.world, self.per, T, 4), dtype=torch.float32, device="cuda")
+            self.image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+            self.comm = torch.cuda.Stream()
+            self.rendered = [torch.cuda.Event() for _ in range(2)]
+            self.gathered_done = [torch.cuda.Event() for _ in range(2)]
+
+    def params(self, k: int):
+        return make_frame_params(self.ctx.S, self.wl, self.w, self.h, frame_num=k + 1 if self.wl["kernel"] == 3 else 1)
+
+    def step(self):
+        ctx, api = self.ctx, self.ctx.api
+        k = self.k
+        self.k += 1
+        fp = self.params(k)
+        st = ctx.main.cuda_stream
+        if self.mode == "single":
+            api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.image, traverse=ctx.trav, ray_count=self.d_rays, stream=st)
+        elif self.mode == "peer":
+            api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.frame_buf, traverse=ctx.trav, tile_rank=ctx.rank,
+                      tile_nranks=ctx.world, ray_count=self.d_rays, stream=st, tiles_in_place=True)
+            ctx.dist.all_reduce(self.done_flag)            # frame k is complete on rank 0 once this returns on its stream
+        else:
+            b = k & 1
+            ctx.main.wait_event(self.gathered_done[b])     # buffer b was last read by the gather of frame k-2
+            api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.tile_buf[b], traverse=ctx.trav, tile_rank=ctx.rank,
+                      tile_nranks=ctx.world, ray_count=self.d_rays, stream=st)
+            self.rendered[b].record(ctx.main)
+            self.gather(b)
+
+    def gather(self, b: int):
+        ctx = self.ctx
+        with ctx.torch.cuda.stream(self.comm):
+            self.comm.wait_event(self.rendered[b])
+            ctx.dist.all_gather_into_tensor(self.gathered.view(-1), self.tile_buf[b].view(-1))
+            ctx.api.deinterleave_tiles(self.gathered, self.w, self.h, ctx.world, self.per, self.image, stream=self.comm.cuda_stream)
+            self.gathered_done[b].record(self.comm)
+
+    def end_of_region(self):
+        if self.mode == "nccl":
+            self.ctx.main.wait_stream(self.comm)           # the last gather belongs to the timed region
+
+    def fence_only(self):
+        """The exchange step of one frame WITHOUT the trace: what the assembly costs when nothing hides it."""
+        if self.mode == "peer":
+            self.ctx.dist.all_reduce(self.done_flag)
+        elif self.mode == "nccl":
+            self.rendered[0].record(self.ctx.main)
+            self.gather(0)
+            self.ctx.main.wait_stream(self.comm)
+
+    def assembled(self):
+        """Rank 0: the assembled frame as a device tensor."""
+        torch, api = self.ctx.torch, self.ctx.api
+        if self.mode != "peer":
+            return self.image
+        got = torch.empty((self.h, self.w, 4), dtype=torch.float32, device="cuda")
+        api._check(api.N.cuda_lib().vsb_device_copy(got.data_ptr(), self.frame_buf.data_ptr(), self.w * self.h * 16, 0, 0), "vsb_device_copy")
+        torch.cuda.synchronize()
+        return got
+
+    def close(self):
+        if self.frame_buf is not None:
+            self.ctx.fence()
+            self.frame_buf.close()
+
+
+def time_rig(ctx: Ctx, rig: FrameRig, steps: int, warmup: int, clocks: bool):
+    """W untimed steps, then exactly K steps between barrier + synchronize on both sides, CUDA events on the launching
+    stream, max over ranks.  Then K more steps for the dominant kernel's own launch time (events recorded by the
+    library around each launch), and the exchange step alone."""
+    torch, api = ctx.torch, ctx.api
+    for _ in range(warmup):
+        rig.step()
+    rig.end_of_region()
+    ctx.fence()
+    rig.d_rays.zero_()
+    launches0 = api.launch_count()
+    sampler = ClockSampler(ctx.local_rank) if clocks else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.25)
+        ctx.fence()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tw0 = time.time()
+    e0.record(ctx.main)
+    for _ in range(steps):
+        rig.step()
+    rig.end_of_region()
+    e1.record(ctx.main)
+    ctx.fence()
+    tw1 = time.time()
+    ms_total = ctx.max_over_ranks(e0.elapsed_time(e1))
+    clk = sampler.stop(tw0, tw1) if sampler else None
+    launches = ctx.sum_over_ranks(api.launch_count() - launches0)
+    rays_total = ctx.sum_over_ranks(int(rig.d_rays.item()))
+    kms = []
+    rig.d_rays.zero_()
+    for _ in range(steps):
+        rig.step()
+        kms.append(api.last_kernel_ms())
+    rig.end_of_region()
+    ctx.fence()
+    rays_rank = int(rig.d_rays.item()) / steps
+    fence_ms = None
+    if ctx.world > 1:
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        rig.fence_only()
+        ctx.fence()
+        f0.record(ctx.main)
+        for _ in range(steps):
+            rig.fence_only()
+        f1.record(ctx.main)
+        ctx.fence()
+        fence_ms = ctx.max_over_ranks(f0.elapsed_time(f1)) / steps
+    return {"value": rays_total / (ms_total * 1e-3) / 1e6, "ms_per_step": ms_total / steps, "kernel_ms": float(np.mean(kms)),
+            "rays_per_step": rays_total // steps, "rays_per_step_rank": rays_rank, "launches": launches, "clocks": clk,
+            "exchange_ms": fence_ms}
