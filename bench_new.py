@@ -528,3 +528,91 @@ def time_rig(ctx: Ctx, rig: FrameRig, steps: int, warmup: int, clocks: bool):
     return {"value": rays_total / (ms_total * 1e-3) / 1e6, "ms_per_step": ms_total / steps, "kernel_ms": float(np.mean(kms)),
             "rays_per_step": rays_total // steps, "rays_per_step_rank": rays_rank, "launches": launches, "clocks": clk,
             "exchange_ms": fence_ms}
+
+
+class SharedHostFrame:
+    """ONE host frame for all ranks of the node: a file in /dev/shm mapped by every process and page-locked + mapped
+    into each process's CUDA address space, so that every rank's trace kernel stores its finished tiles straight into
+    the frame the caller (rank 0) reads: no per-rank buffers, no gather, no CPU pass."""
+
+    def __init__(self, ctx: Ctx, w: int, h: int):
+        self.ctx = ctx
+        name = [None]
+        if ctx.rank == 0:
+            name[0] = f"/dev/shm/vsb_frame_{os.getpid()}_{w}x{h}"
+            with open(name[0], "wb") as f:
+                f.truncate(w * h * 16)
+        ctx.dist.broadcast_object_list(name, src=0)
+        self.path = name[0]
+        self.array = np.memmap(self.path, dtype=np.float32, mode="r+", shape=(h, w, 4))
+        self.ptr, self.nbytes = self.array.ctypes.data, w * h * 16
+        rt = ctx.torch.cuda.cudart()
+        err = rt.cudaHostRegister(self.ptr, self.nbytes, 1 | 2)          # portable | mapped
+        if int(err) != 0:
+            raise RuntimeError(f"cudaHostRegister failed: {err}")
+        ctx.fence()
+
+    def close(self):
+        self.ctx.fence()
+        self.ctx.torch.cuda.cudart().cudaHostUnregister(self.ptr)
+        del self.array
+        self.ctx.fence()
+        if self.ctx.rank == 0:
+            try:
+                os.unlink(self.path)
+            except OSError:
+                pass
+
+
+def e2e_frames(ctx: Ctx, wl: dict, dev, w: int, h: int, steps: int, check_against=None):
+    """The same metric through the host-buffer call: frame() into a pinned host render target, parameter H2D and
+    framebuffer D2H inside the timed region (wall clock, max over ranks).  N > 1: ONE assembled frame in a host buffer
+    shared by all ranks (SharedHostFrame); the progressive path tracer keeps per-rank tile buffers, because its blend
+    re-reads the rank's own previous frame."""
+    torch, api, S = ctx.torch, ctx.api, ctx.S
+    mats, lights = S.default_material(wl["mat"]), S.point_light(wl["eye"])
+    world, rank = ctx.world, ctx.rank
+    shared = world > 1 and wl["kernel"] != 3
+    per = max(api.tiles_of_rank(w, h, r, world) for r in range(world))
+    frame = None
+    if shared:
+        frame = SharedHostFrame(ctx, w, h)
+        host_np, n_px = frame.array, w * h // world
+    else:
+        n_px = per * api.TILE * api.TILE if world > 1 else w * h
+        host_np = torch.zeros((n_px, 4), dtype=torch.float32).pin_memory().numpy()
+    h_rays = np.zeros(1, dtype=np.uint64)
+
+    def one(k):
+        fp = make_frame_params(S, wl, w, h, frame_num=k + 1 if wl["kernel"] == 3 else 1)
+        api.frame(dev, fp, None, mats, lights, host_np, traverse=ctx.trav, tile_rank=rank if world > 1 else 0,
+                  tile_nranks=world if world > 1 else 0, ray_count=h_rays, tiles_in_place=shared)
+        return int(h_rays[0])
+
+    one(0)
+    ctx.fence()
+    t0 = time.perf_counter()
+    rays = 0
+    for k in range(steps):
+        rays += one(k)
+    api.sync()
+    ctx.fence()                                       # N > 1: the frame is complete when every rank's call has returned
+    secs = ctx.max_over_ranks(time.perf_counter() - t0)
+    trace_ms = api.last_kernel_ms()
+    rays = ctx.sum_over_ranks(rays)
+    verified = None
+    if shared and check_against is not None and rank == 0:
+        verified = bool(np.array_equal(np.asarray(host_np), check_against.cpu().numpy()))
+    h2d = (mats.nbytes + lights.nbytes + 256) * world
+    if wl["kernel"] == 3:
+        h2d += n_px * 16 * world                       # progressive state lives with the caller
+    d2h = (n_px * 16 + 8) * world
+    out = {"value": rays / secs / 1e6, "unit": "Mrays/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+           "steps": steps, "ms_per_step": secs * 1e3 / steps, "trace_ms": trace_ms,
+           "d2h_gb_s_per_rank": n_px * 16 / (secs / steps) / 1e9,
+           "target": ("one assembled frame in a /dev/shm buffer page-locked and mapped by all ranks; kernels store tiles in place over PCIe"
+                      if shared else ("per-rank compact tile buffers (progressive blend state), pinned" if world > 1 else "pinned host frame, banded D2H overlapping the trace")),
+           "assembled_frame_verified": verified}
+    if frame is not None:
+        frame.close()
+    return out
