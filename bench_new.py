@@ -616,3 +616,102 @@ def e2e_frames(ctx: Ctx, wl: dict, dev, w: int, h: int, steps: int, check_agains
     if frame is not None:
         frame.close()
     return out
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm: ray lists (cfg5)
+# ------------------------------------------------------------------------------------------------
+
+def time_raylist(ctx: Ctx, dev, any_hit: bool, n_batch: int, steps: int, warmup: int, clocks: bool, e2e: bool):
+    """Incoherent random-ray stress: rays uniform in the unit cube with uniform directions vs the triangle soup; a step
+    = one vsb_closest_hit / vsb_any_hit pass over one batch of n_batch rays (4 rotating batches).  N > 1: every rank
+    gets its own batches (contiguous chunks of the global list, different seeds), no collective."""
+    torch, api, S = ctx.torch, ctx.api, ctx.S
+    n_bufs = 4
+    rays_h = [S.random_rays(n_batch, 600 + 16 * ctx.rank + i) for i in range(n_bufs)]
+    d_rays = [torch.from_numpy(r).cuda() for r in rays_h]
+    d_hits = [torch.empty((n_batch, 8), dtype=torch.int32, device="cuda") for _ in range(n_bufs)]
+    fn = api.any_hit if any_hit else api.closest_hit
+    k = [0]
+
+    def step():
+        i = k[0] % n_bufs
+        k[0] += 1
+        fn(dev, d_rays[i], hits=d_hits[i], traverse=ctx.trav, stream=ctx.main.cuda_stream)
+
+    for _ in range(warmup):
+        step()
+    ctx.fence()
+    launches0 = api.launch_count()
+    sampler = ClockSampler(ctx.local_rank) if clocks else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.25)
+        ctx.fence()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    tw0 = time.time()
+    e0.record(ctx.main)
+    for _ in range(steps):
+        step()
+    e1.record(ctx.main)
+    ctx.fence()
+    tw1 = time.time()
+    ms_total = ctx.max_over_ranks(e0.elapsed_time(e1))
+    clk = sampler.stop(tw0, tw1) if sampler else None
+    launches = ctx.sum_over_ranks(api.launch_count() - launches0)
+    kms = []
+    for _ in range(steps):
+        step()
+        kms.append(api.last_kernel_ms())
+    ctx.fence()
+    out = {"value": n_batch * steps * ctx.world / (ms_total * 1e-3) / 1e6, "ms_per_step": ms_total / steps,
+           "kernel_ms": float(np.mean(kms)), "launches": launches, "clocks": clk,
+           "hit_fraction": float((d_hits[0][:, 0] != 0).float().mean().item()), "sample_rays": rays_h[0][:200_000].copy(),
+           "e2e": None}
+    if e2e:
+        # host ray list in, host hit records out (pinned), H2D + D2H inside the call
+        h_rays = torch.from_numpy(rays_h[0].copy()).pin_memory().numpy()
+        h_hits = torch.zeros((n_batch, 8), dtype=torch.int32).pin_memory().numpy().view(api.N.HIT_DTYPE).reshape(-1)
+        fn(dev, h_rays, hits=h_hits, traverse=ctx.trav)
+        ctx.fence()
+        e2e_steps = max(1, min(steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            fn(dev, h_rays, hits=h_hits, traverse=ctx.trav)
+        ctx.fence()
+        secs = ctx.max_over_ranks(time.perf_counter() - t0)
+        out["e2e"] = {"value": n_batch * e2e_steps * ctx.world / secs / 1e6, "unit": "Mrays/s",
+                      "h2d_bytes_per_step": n_batch * 32 * ctx.world, "d2h_bytes_per_step": n_batch * 32 * ctx.world,
+                      "steps": e2e_steps, "rays_per_step": n_batch, "ms_per_step": secs * 1e3 / e2e_steps,
+                      "trace_ms": api.last_kernel_ms()}
+    del d_rays, d_hits
+    return out
+
+
+def raylist_roofline(O, osc, sample, any_hit: bool, n_batch: int, kernel_ms: float, traffic_key):
+    """B_ray from the oracle's instrumented traversal of the scene's BVH2 on 200 k rays of the list."""
+    peak, peak_src = measured_peak_gbs()
+    c = O.Counters()
+    O.oracle_query(osc, sample, any_hit, counters=c)
+    n_inner, n_prim = c.n_inner / c.n_rays, c.n_prim / c.n_rays
+    b_ray = 64.0 * n_inner + 68.0 * n_prim + 64.0
+    achieved = b_ray * n_batch / (kernel_ms * 1e-3) / 1e9
+    return {"bound": "issue", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": measured_traffic(traffic_key) if traffic_key else None,
+            "issue": measured_issue(traffic_key) if traffic_key else None,
+            "kernel": "trace_kernel_q<RayListProgram>", "kernel_ms": kernel_ms, "bytes_per_ray": b_ray,
+            "n_inner_per_ray": n_inner, "n_prim_per_ray": n_prim, "peak_source": peak_src,
+            "roofline_mrays_s": peak * 1e9 / b_ray / 1e6}
+
+
+def frame_roofline(O, S, osc, wl, rig_out: dict, traffic_key):
+    peak, peak_src = measured_peak_gbs()
+    mats, lights = S.default_material(wl["mat"]), S.point_light(wl["eye"])
+    b_ray, visit = algorithmic_bytes_per_ray(O, S, osc, wl, mats, lights)
+    achieved = b_ray * rig_out["rays_per_step_rank"] / (rig_out["kernel_ms"] * 1e-3) / 1e9
+    return {"bound": "issue", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "traffic": measured_traffic(traffic_key) if traffic_key else None,
+            "issue": measured_issue(traffic_key) if traffic_key else None,
+            "kernel": "trace_kernel_q<FrameProgram>", "kernel_ms": rig_out["kernel_ms"], "bytes_per_ray": b_ray,
+            "n_inner_per_ray": visit["n_inner"], "n_prim_per_ray": visit["n_prim"], "peak_source": peak_src,
+            "roofline_mrays_s": peak * 1e9 / b_ray / 1e6}
