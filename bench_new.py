@@ -715,3 +715,143 @@ def frame_roofline(O, S, osc, wl, rig_out: dict, traffic_key):
             "kernel": "trace_kernel_q<FrameProgram>", "kernel_ms": rig_out["kernel_ms"], "bytes_per_ray": b_ray,
             "n_inner_per_ray": visit["n_inner"], "n_prim_per_ray": visit["n_prim"], "peak_source": peak_src,
             "roofline_mrays_s": peak * 1e9 / b_ray / 1e6}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm: the runs
+# ------------------------------------------------------------------------------------------------
+
+def extra_legs(ctx: Ctx, O, args):
+    """N = 1, default run: the incoherent workloads in the same record (short legs, GPU-built trees)."""
+    S, api = ctx.S, ctx.api
+    out = {}
+    steps, warmup = 5, 3
+    sc, dev, info = prepare_scene(api, S, "cfg5_soup", 1.0, "gpu")
+    osc = oracle_scene(S, sc, dev)
+    for name, any_hit in (("cfg5_closest", False), ("cfg5_any", True)):
+        r = time_raylist(ctx, dev, any_hit, 1 << 24, steps, warmup, clocks=False, e2e=False)
+        out[name] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
+                     "steps": steps, "warmup": warmup, "hit_fraction": r["hit_fraction"], "builder": info,
+                     "config": raylist_config(sc.n_prims, any_hit, 1 << 24, 1.0),
+                     "roofline": raylist_roofline(O, osc, r["sample_rays"], any_hit, 1 << 24, r["kernel_ms"], name)}
+    dev.close()
+    del sc, osc
+    wl = WORKLOADS["cfg3"]
+    sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, "gpu")
+    osc = oracle_scene(S, sc, dev)
+    rig = FrameRig(ctx, wl, dev, wl["w"], wl["h"], "single")
+    r = time_rig(ctx, rig, steps, warmup, clocks=False)
+    out["cfg3"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
+                   "steps": steps, "warmup": warmup, "rays_per_step": r["rays_per_step"], "builder": info,
+                   "config": workload_config(wl, wl["w"], wl["h"], 1.0, sc.n_prims),
+                   "roofline": frame_roofline(O, S, osc, wl, r, "cfg3")}
+    rig.close()
+    dev.close()
+    return out
+
+
+def strong_legs(ctx: Ctx, args, cfg2_scene=None):
+    """N > 1: the FIXED 4096^2 frame partitioned over the N GPUs -- cfg2 through peer stores, cfg4 (configs[3]: the
+    progressive path tracer) through all-gather + de-interleave -- against the same frame on one GPU alone, measured
+    in the same run (every rank renders it alone at the same time; rank-local work, max over ranks)."""
+    S, api = ctx.S, ctx.api
+    out = {}
+    steps, warmup = max(5, min(args.steps, 10)), 3
+    for name, mode in (("cfg2", "peer"), ("cfg4", "nccl")):
+        wl = WORKLOADS[name]
+        if name == "cfg2" and cfg2_scene is not None:
+            sc, dev, info, own = cfg2_scene[0], cfg2_scene[1], cfg2_scene[2], False
+        else:
+            sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, args.builder)
+            own = True
+        w, h = wl["w"], wl["h"]
+        alone = FrameRig(ctx, wl, dev, w, h, "single")
+        r1 = time_rig(ctx, alone, steps, warmup, clocks=False)
+        v1 = r1["value"] / ctx.world                              # all ranks ran the same frame alone: per-GPU rate
+        ref_img = alone.image.clone() if name == "cfg2" else None
+        alone.close(); del alone
+        rig = FrameRig(ctx, wl, dev, w, h, mode)
+        rn = time_rig(ctx, rig, steps, warmup, clocks=False)
+        verified = None
+        if name == "cfg2":
+            ctx.fence()
+            if ctx.rank == 0:
+                verified = bool(ctx.torch.equal(rig.assembled(), ref_img))
+            ctx.fence()
+        out[name] = {"frame": [w, h], "assembly": mode, "value": rn["value"], "unit": "Mrays/s", "ms_per_step": rn["ms_per_step"],
+                     "trace_kernel_ms": rn["kernel_ms"], "exchange_alone_ms": rn["exchange_ms"],
+                     "one_gpu_value": v1, "one_gpu_ms_per_step": r1["ms_per_step"], "efficiency": rn["value"] / (ctx.world * v1),
+                     "steps": steps, "warmup": warmup, "assembled_frame_verified": verified,
+                     "triangles": sc.n_prims, "builder": info}
+        rig.close(); del rig
+        if own:
+            dev.close()
+    return out
+
+
+def run_gpu(args):
+    ctx = Ctx(args)
+    S, api = ctx.S, ctx.api
+    wl = WORKLOADS[args.workload]
+    w, h = frame_shape(wl, ctx.world)
+    sc, dev, builder = prepare_scene(api, S, wl["scene"], args.scale, args.builder)
+    stats = dev.stats()
+    mode = "single" if ctx.world == 1 else ("nccl" if (args.gather == "nccl" or wl["kernel"] == 3) else "peer")
+    rig = FrameRig(ctx, wl, dev, w, h, mode)
+    r = time_rig(ctx, rig, args.steps, args.warmup, clocks=True)
+    builder["first_frame_after_build_ms"] = None
+
+    # N > 1: the assembled frame on rank 0 equals the frame one GPU renders alone
+    verified, alone_img = None, None
+    if ctx.world > 1 and wl["kernel"] != 3:
+        ctx.fence()
+        if ctx.rank == 0:
+            alone_img = ctx.torch.zeros((h, w, 4), dtype=ctx.torch.float32, device="cuda")
+            api.frame(dev, rig.params(0), None, rig.d_mats, rig.d_lights, alone_img, traverse=ctx.trav, stream=ctx.main.cuda_stream)
+            ctx.torch.cuda.synchronize()
+            verified = bool(ctx.torch.equal(rig.assembled(), alone_img))
+        ctx.fence()
+    rig.close()
+    e2e = e2e_frames(ctx, wl, dev, w, h, max(1, min(args.steps, 5)), check_against=alone_img)
+    del alone_img
+
+    strong = None
+    if ctx.world > 1 and not args.no_extra and args.workload == "cfg2" and args.scale == 1.0:
+        strong = strong_legs(ctx, args, cfg2_scene=(sc, dev, builder))
+
+    line = None
+    full = ctx.world == 1 and args.scale == 1.0
+    if ctx.rank == 0:
+        from oracle import bindings as O              # checker / CPU baseline only (never on the product path)
+        osc = oracle_scene(S, sc, dev)
+        roofline = frame_roofline(O, S, osc, wl, r, args.workload if full else None)
+        cpu = None
+        if ctx.world == 1 and not args.no_cpu:
+            cores = os.cpu_count() or 1
+            secs, kind = cpu_frame_seconds(O, S, osc if sc.nodes is None else sc, wl, rig.mats, rig.lights, w, h, reps=3, warmup=1, cores=cores)
+            rays = r["rays_per_step"]
+            cpu = {"value": rays / secs / 1e6, "unit": "Mrays/s", "cores": cores, "kind": kind,
+                   "sample": f"the whole {w}x{h} frame ({rays} rays), best of 3 after 1 warm-up, "
+                             + ("tiled_sched<simd::ray8> -O3 -mavx2 -mfma" if kind == "reference" else "scalar C port")
+                             + (", on the GPU-built tree" if sc.nodes is None else "")}
+        cfg = workload_config(wl, w, h, args.scale, sc.n_prims)
+        cfg.update({"rays_per_step": r["rays_per_step"], "traverse": args.traverse,
+                    "partition": f"interleaved 64x64 tiles over {ctx.world} GPU(s), scene replicated"
+                                 + {"single": "", "peer": ", tiles stored in place into rank 0's frame over NVLink peer memory (CUDA IPC) + 1 tiny all-reduce per frame",
+                                    "nccl": ", NCCL all-gather + de-interleave per frame on a side stream"}[mode],
+                    "assembled_frame_verified": verified, "exchange_alone_ms": r["exchange_ms"],
+                    "wide_nodes": stats["wide_nodes"], "bvh2_nodes": stats["bvh2_nodes"], "builder": builder})
+        line = {"metric": "Mrays/s", "value": r["value"], "unit": "Mrays/s", "n_gpus": ctx.world, "steps": args.steps,
+                "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+                "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg, "roofline": roofline,
+                "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(r["launches"]), "clocks": r["clocks"]}
+        if strong is not None:
+            line["strong"] = strong
+    dev.close()
+    if ctx.world == 1 and not args.no_extra and args.workload == "cfg2" and args.scale == 1.0:
+        from oracle import bindings as O
+        line["extra"] = extra_legs(ctx, O, args)
+    if ctx.rank == 0:
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    return 0
