@@ -249,7 +249,8 @@ typedef struct vsb_scene vsb_scene;
  * into a context, like callers of the reference's frame() (detail/cuda_sched.inl:307-320, not re-entrant). */
 int  vsb_init(int device);                       /* cudaSetDevice + stream/queue state */
 int  vsb_shutdown(void);
-int  vsb_sync(void);                             /* wait for the library's own stream (calls made with cuda_stream == NULL) */
+int  vsb_sync(void);                             /* wait for the library's own stream (calls made with cuda_stream == NULL)
+                                                    and for the last query / frame call, whichever stream it ran on */
 const char* vsb_strerror(int code);
 int  vsb_version(void);
 int  vsb_device_sm_count(int* out);

@@ -104,7 +104,7 @@ VSB_HD float byte_as_unit_float(uint32_t w, int k, uint32_t one)
 // widen it.  Per byte: half a PRMT on the alu pipe (the saturated one: 80 % of its peak on the cfg2 frame,
 // profiles/r2_cfg2_q1) and one conversion on the fma pipe (21 %), against one PRMT.
 #ifndef VSB_NODE_HALFCVT
-#define VSB_NODE_HALFCVT 0
+#define VSB_NODE_HALFCVT 1      // measured: cfg2 6306 -> 6394, cfg5/4 1219 -> 1245 Mrays/s (gpurun_out/r2_ab3.log)
 #endif
 VSB_HD uint32_t half_bias_bits()
 {

@@ -747,6 +747,7 @@ extern "C" int vsb_device_copy(void* dst, const void* src, size_t bytes, int dst
     if (!dst || !src) return VSB_ERR_BAD_ARG;
     const cudaMemcpyKind kind = dst_mem == VSB_MEM_DEVICE ? (src_mem == VSB_MEM_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice)
                                                           : (src_mem == VSB_MEM_DEVICE ? cudaMemcpyDeviceToHost : cudaMemcpyHostToHost);
+    if (g.call_done_valid) VSB_CUDA(cudaStreamWaitEvent(g.stream, g.call_done, 0));   // behind the last query / frame call of the context
     VSB_CUDA(cudaMemcpyAsync(dst, src, bytes, kind, g.stream));
     VSB_CUDA(cudaStreamSynchronize(g.stream));
     return VSB_OK;

@@ -236,6 +236,7 @@ extern "C" int vsb_sync(void)
 {
     int rc = require_init(); if (rc) return rc;
     VSB_CUDA(cudaStreamSynchronize(g.stream));
+    if (g.call_done_valid) VSB_CUDA(cudaEventSynchronize(g.call_done));   // the last query / frame call, whichever stream it ran on
     return VSB_OK;
 }
 
