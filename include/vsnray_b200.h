@@ -163,7 +163,8 @@ enum {
     VSB_ERR_BAD_ARG     = -2,
     VSB_ERR_BAD_TREE    = -3,
     VSB_ERR_NOT_INIT    = -4,
-    VSB_ERR_UNSUPPORTED = -5
+    VSB_ERR_UNSUPPORTED = -5,
+    VSB_ERR_TOO_LARGE   = -6        /* a size beyond a stated fixed maximum (vsb_closest_hit_static) */
 };
 
 /* Kernel + scheduler parameters of one frame() call.  Mirrors what cuda_sched<R>::frame()
@@ -315,6 +316,21 @@ int  vsb_closest_hit(const vsb_scene* const* scenes, int n_scenes,
 int  vsb_any_hit(const vsb_scene* const* scenes, int n_scenes,
                  const vsb_ray* rays, size_t n_rays, float max_t, const float* max_t_per_ray,
                  vsb_hit* hits, int mem, int traverse, void* cuda_stream);
+
+/* vsb_closest_hit over ONE scene and a DEVICE ray list, for callers that cannot allocate (code under CUDA graph
+ * capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Same kernels, same hit records as vsb_closest_hit(..., VSB_MEM_DEVICE,
+ * VSB_TRAVERSE_WIDE, stream); but every byte of scratch (scene table, work counter, the coherence sort's keys, order
+ * and radix-sort temporaries) lives in one file-scope __device__ array of VSB_STATIC_SCRATCH_BYTES, so the call
+ * performs no cudaMalloc / cudaFree / allocating library call.  Limits and caveats:
+ *   - n_rays <= VSB_STATIC_MAX_RAYS, else VSB_ERR_TOO_LARGE ("size beyond the fixed maximum");
+ *   - every GPU that loads the library holds the array (24 MiB + 8 KiB) until the process exits;
+ *   - all calls share the array: calls that overlap on the GPU race on it.  Calls of one context are ordered by the
+ *     library; several host threads must serialise their calls. */
+#define VSB_STATIC_MAX_RAYS      (1u << 20)
+#define VSB_STATIC_SCRATCH_BYTES (8192u + 16u * VSB_STATIC_MAX_RAYS + (8u << 20))
+int  vsb_closest_hit_static(const vsb_scene* scene, const vsb_ray* rays, size_t n_rays, float max_t,
+                            vsb_hit* hits, void* cuda_stream);
 
 /* multi_hit<N>(r, begin, end) over a ray list (detail/traverse_linear.inl:325-380 ->
  * intersect<MultiHit, N>(), detail/bvh/intersect.inl:35-134; record handling detail/multi_hit.h):

@@ -85,7 +85,7 @@ class SurfaceDesc(C.Structure):
 ABI_SYMBOLS = [
     "vsb_init", "vsb_shutdown", "vsb_sync", "vsb_strerror", "vsb_version", "vsb_device_sm_count", "vsb_tune",
     "vsb_scene_create", "vsb_scene_build", "vsb_scene_download_bvh", "vsb_last_build_ms", "vsb_scene_destroy", "vsb_scene_set_normals", "vsb_scene_set_surface", "vsb_scene_stats", "vsb_scene_download_wide",
-    "vsb_closest_hit", "vsb_any_hit", "vsb_multi_hit", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
+    "vsb_closest_hit", "vsb_any_hit", "vsb_multi_hit", "vsb_closest_hit_static", "vsb_camera_basis", "vsb_frame", "vsb_tiles_of_rank",
     "vsb_deinterleave_tiles", "vsb_device_alloc", "vsb_device_free", "vsb_device_copy", "vsb_ipc_export", "vsb_ipc_open", "vsb_ipc_close", "vsb_last_kernel_ms", "vsb_launch_count",
 ]
 
@@ -136,6 +136,7 @@ def cuda_lib() -> C.CDLL:
         for f in (lib.vsb_closest_hit, lib.vsb_any_hit):
             f.argtypes = [C.POINTER(vp), C.c_int, vp, sz, C.c_float, vp, vp, C.c_int, C.c_int, vp]
         lib.vsb_multi_hit.argtypes = [C.POINTER(vp), C.c_int, vp, sz, C.c_int, vp, C.c_int, C.c_int, vp]
+        lib.vsb_closest_hit_static.argtypes = [vp, vp, sz, C.c_float, vp, vp]
         lib.vsb_camera_basis.argtypes = [C.POINTER(FrameDesc)]
         lib.vsb_frame.argtypes = [C.POINTER(vp), C.c_int, C.POINTER(FrameDesc), vp]
         lib.vsb_tiles_of_rank.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]

@@ -228,6 +228,8 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
 
 } // namespace
 
+#include "capi_noalloc.inl"
+
 extern "C" int vsb_version(void) { return 100; }
 
 extern "C" int vsb_tune(const char* key, int value)
@@ -264,6 +266,7 @@ extern "C" const char* vsb_strerror(int code)
     case VSB_ERR_BAD_TREE: return "malformed or too deep BVH";
     case VSB_ERR_NOT_INIT: return "vsb_init() has not succeeded";
     case VSB_ERR_UNSUPPORTED: return "unsupported";
+    case VSB_ERR_TOO_LARGE: return "size beyond the fixed maximum of this entry point (vsb_closest_hit_static: VSB_STATIC_MAX_RAYS rays)";
     default: return code > 0 ? cudaGetErrorString((cudaError_t)code) : "unknown error";
     }
 }
