@@ -19,13 +19,15 @@ closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.j
             `issue` carries the binding figures from the committed ncu capture (profiles/issue.json)
   cpu_baseline  the reference's own tiled_sched<simd::ray8> (oracle/_ref, unmodified headers) on the
             host cores, on the SAME frame as the GPU arm
-  extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3
+  extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3;
+            gpu_built_tree: cfg2 and cfg5 on the tree of the GPU builder, with build time and time to first frame
   strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 (peer stores over NVLink) and
             cfg4 (progressive path tracer: all-gather + de-interleave), with v_N / (N v_1)
 
 N > 1 (torchrun): the frame is partitioned into interleaved 64x64 tiles (tile k -> rank k % N), the
 scene is replicated.  Headline = weak scaling: the same view at sqrt(N) x the resolution per axis
-(4096^2 pixels per GPU).  The tree is built on the GPU (vsb_scene_build) unless --builder reference.
+(4096^2 pixels per GPU).  The tree is the reference's binned-SAH tree (host builder) re-encoded on the GPU, as BASELINE's
+configs say; --builder gpu builds it on the GPU instead (extra.gpu_built_tree measures that in the default run).
 """
 from __future__ import annotations
 
@@ -721,32 +723,68 @@ def frame_roofline(O, S, osc, wl, rig_out: dict, traffic_key):
 # GPU arm: the runs
 # ------------------------------------------------------------------------------------------------
 
-def extra_legs(ctx: Ctx, O, args):
-    """N = 1, default run: the incoherent workloads in the same record (short legs, GPU-built trees)."""
+def extra_legs(ctx: Ctx, O, args, cfg2_prims):
+    """N = 1, default run: the incoherent workloads in the same record, measured like the headline (short legs), on the
+    reference's binned-SAH tree (BASELINE configs / north_star: "re-encoded on the GPU from the reference's binned-SAH
+    tree"); and what the GPU builder (vsb_scene_build) gives instead: the same workloads on its tree, with the build time."""
     S, api = ctx.S, ctx.api
     out = {}
     steps, warmup = 5, 3
-    sc, dev, info = prepare_scene(api, S, "cfg5_soup", 1.0, "gpu")
-    osc = oracle_scene(S, sc, dev)
-    for name, any_hit in (("cfg5_closest", False), ("cfg5_any", True)):
-        r = time_raylist(ctx, dev, any_hit, 1 << 24, steps, warmup, clocks=False, e2e=False)
-        out[name] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
-                     "steps": steps, "warmup": warmup, "hit_fraction": r["hit_fraction"], "builder": info,
-                     "config": raylist_config(sc.n_prims, any_hit, 1 << 24, 1.0),
-                     "roofline": raylist_roofline(O, osc, r["sample_rays"], any_hit, 1 << 24, r["kernel_ms"], name)}
+    n_batch = 1 << 24
+
+    def raylist(dev, osc, any_hit, info, key):
+        r = time_raylist(ctx, dev, any_hit, n_batch, steps, warmup, clocks=False, e2e=False)
+        return {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
+                "steps": steps, "warmup": warmup, "hit_fraction": r["hit_fraction"], "builder": info,
+                "config": raylist_config(osc.n_prims, any_hit, n_batch, 1.0),
+                "roofline": raylist_roofline(O, osc, r["sample_rays"], any_hit, n_batch, r["kernel_ms"], key)}
+
+    sc, dev, info = prepare_scene(api, S, "cfg5_soup", 1.0, "reference")
+    out["cfg5_closest"] = raylist(dev, sc, False, info, "cfg5_closest")
+    out["cfg5_any"] = raylist(dev, sc, True, info, "cfg5_any")
     dev.close()
-    del sc, osc
+    gpu_tree = {}
+    t0 = time.perf_counter()
+    dev = api.Scene.build(sc.prim_kind, sc.prims, None)
+    api.sync()
+    ms = api.last_build_ms()
+    binfo = {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"],
+             "upload_and_build_s": round(time.perf_counter() - t0, 3), "host_builder_s": info["scene_generation_s"]}
+    r = time_raylist(ctx, dev, False, n_batch, steps, warmup, clocks=False, e2e=False)
+    gpu_tree["cfg5_closest"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "builder": binfo,
+                                "vs_reference_tree": r["value"] / out["cfg5_closest"]["value"]}
+    dev.close()
+    del sc
+
     wl = WORKLOADS["cfg3"]
-    sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, "gpu")
-    osc = oracle_scene(S, sc, dev)
+    sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, "reference")
     rig = FrameRig(ctx, wl, dev, wl["w"], wl["h"], "single")
     r = time_rig(ctx, rig, steps, warmup, clocks=False)
     out["cfg3"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
                    "steps": steps, "warmup": warmup, "rays_per_step": r["rays_per_step"], "builder": info,
                    "config": workload_config(wl, wl["w"], wl["h"], 1.0, sc.n_prims),
-                   "roofline": frame_roofline(O, S, osc, wl, r, "cfg3")}
+                   "roofline": frame_roofline(O, S, sc, wl, r, "cfg3")}
     rig.close()
     dev.close()
+    del sc
+
+    # the headline frame on the GPU-built tree: generate -> build -> first frame, then the same timing
+    wl = WORKLOADS["cfg2"]
+    t0 = time.perf_counter()
+    dev = api.Scene.build(0, cfg2_prims, S.face_normals(cfg2_prims))
+    api.sync()
+    ms = api.last_build_ms()
+    rig = FrameRig(ctx, wl, dev, wl["w"], wl["h"], "single")
+    rig.step()
+    ctx.torch.cuda.synchronize()
+    first = time.perf_counter() - t0
+    r = time_rig(ctx, rig, steps, warmup, clocks=False)
+    gpu_tree["cfg2"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"],
+                        "builder": {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2),
+                                    "iterations": ms["iterations"], "primitives_to_first_frame_s": round(first, 3)}}
+    rig.close()
+    dev.close()
+    out["gpu_built_tree"] = gpu_tree
     return out
 
 
@@ -854,7 +892,9 @@ def run_gpu(args):
     dev.close()
     if ctx.world == 1 and not args.no_extra and args.workload == "cfg2" and args.scale == 1.0:
         from oracle import bindings as O
-        line["extra"] = extra_legs(ctx, O, args)
+        line["extra"] = extra_legs(ctx, O, args, sc.prims)
+        line["extra"]["gpu_built_tree"]["cfg2"]["vs_reference_tree"] = line["extra"]["gpu_built_tree"]["cfg2"]["value"] / line["value"] \
+            if args.builder == "reference" else None
     if ctx.rank == 0:
         print(json.dumps(line), flush=True)
     ctx.close()
@@ -911,8 +951,9 @@ def main():
     ap.add_argument("--any", action="store_true", help="cfg5: any-hit instead of closest-hit")
     ap.add_argument("--batch", type=int, default=1 << 24, help="cfg5: rays per batch")
     ap.add_argument("--traverse", default="wide", choices=["wide", "exact"])
-    ap.add_argument("--builder", default="gpu", choices=["gpu", "reference"],
-                    help="whose BVH the scene uses: the GPU builder (vsb_scene_build), or the reference's host builder (tie-order parity anchor)")
+    ap.add_argument("--builder", default="reference", choices=["reference", "gpu"],
+                    help="whose BVH the scene uses: the reference's binned-SAH builder (host; what BASELINE's configs name), or the GPU "
+                         "builder (vsb_scene_build: 6.8 ms instead of 0.5 s at 1 M triangles, traces ~10 %% slower)")
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra (N = 1) / strong (N > 1) records of the default run")
