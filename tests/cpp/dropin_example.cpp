@@ -11,6 +11,7 @@
 #include <vector>
 
 #include <visionaray_b200/scheduler.h>
+#include <visionaray_b200/obj_loader.h>
 #include "../../visionaray_b200/csrc/host/scenes.h"
 
 namespace visionaray = visionaray_b200;      // the one-line switch
@@ -299,6 +300,36 @@ int main(int argc, char** argv)
             dump(out + "/surface_tex_coords.bin", tc.data(), tc.size());
             dump(out + "/surface_texels.bin", texels.data(), texels.size());
             dump(out + "/surface_materials.bin", flat.data(), flat.size());
+        }
+
+        // --- a scene from an OBJ file the way the reference's viewer sets it up (src/viewer/viewer.cpp:480-541):
+        //     load_obj -> build<index_bvh> -> make_kernel_params(normals_per_vertex_binding, ..., shading_normals,
+        //     tex_coords, materials, textures, ...) -> whitted kernel -> frame().  argv[2] = the .obj file. ---
+        if (argc > 2)
+        {
+            model mod;
+            load_obj(argv[2], mod);
+            if (mod.shading_normals.size() != 3 * mod.primitives.size()) { std::cerr << "obj: the example needs normals on every face\n"; return 2; }
+            auto obvh = build<index_bvh<triangle_type>>(mod.primitives.data(), mod.primitives.size());
+            b200_index_bvh<triangle_type> d_obvh(obvh);
+            b200_bvh_ref oprims[1] = { d_obvh.ref() };
+            std::vector<point_light<float>> olights(1);
+            olights[0].set_position(vec3(2.5f, 4.0f, 3.0f));
+            auto okp = make_kernel_params(normals_per_vertex_binding{}, oprims, oprims + 1, mod.shading_normals.data(), mod.tex_coords.data(),
+                                          mod.materials, mod.textures, olights.data(), olights.data() + olights.size(), 3, 1e-3f,
+                                          vec4(0.1f, 0.4f, 1.0f, 1.0f), vec4(0.2f, 0.2f, 0.2f, 1.0f));
+            whitted::kernel<decltype(okp)> ok{ okp };
+            pinhole_camera ocam;
+            ocam.look_at(vec3(1.6f, 2.1f, 2.9f), vec3(0.0f, 0.6f, 0.0f));
+            ocam.perspective(45.0f * 3.14159265358979323846f / 180.0f, float(224) / float(160), 0.001f, 1000.0f);
+            simple_buffer_rt<PF_RGBA32F, PF_UNSPECIFIED> ort;
+            ort.resize(224, 160);
+            auto osp = make_sched_params(pixel_sampler::uniform_type{}, ocam, ort);
+            b200_sched<ray> osched;
+            osched.set_reference_order(true);
+            osched.frame(ok, osp);
+            osched.frame(ok, osp);          // second frame: the surface description is not uploaded again (same pixels)
+            dump(out + "/frame_obj.bin", ort.color(), size_t(224) * 160);
         }
 
         std::printf("dropin_example ok: %zu triangles, %zu nodes, %zu rays\n", tris.size(), bvh.num_nodes(), rays.size());

@@ -18,7 +18,8 @@ EXE = os.path.join(ROOT, "tests", "cpp", "dropin_example")
 
 def run(outdir):
     env = dict(os.environ, LD_LIBRARY_PATH=os.path.join(ROOT, "visionaray_b200", "lib") + ":" + os.environ.get("LD_LIBRARY_PATH", ""))
-    return subprocess.run([EXE, outdir], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    obj = os.path.join(ROOT, "tests", "golden", "obj", "smooth.obj")
+    return subprocess.run([EXE, outdir, obj], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
 
 
 def test_builds_and_fails_loudly_without_gpu():
@@ -85,6 +86,15 @@ def test_dropin_program_matches_oracle(gpu):
         want_s = O.oracle_frame_surface(ss, fp, sd, mats, S.point_light(eye))
         got_s = np.fromfile(os.path.join(d, "surface_whitted.bin"), dtype=np.float32).reshape(120, 160, 4)
         assert float((np.abs(got_s - want_s).max(axis=2) > 1 / 255).mean()) == 0.0      # reference-order walk
+        # load_obj -> build -> make_kernel_params(normals_per_vertex_binding, ...) -> frame(): the oracle is fed the arrays
+        # the same loader returns through the host library (tests/test_obj_loader.py pins them)
+        m = S.load_obj(os.path.join(ROOT, "tests", "golden", "obj", "smooth.obj"))
+        osc, osd = m.host_scene(), m.surface()
+        ofp = S.frame_params(1, 224, 160, (1.6, 2.1, 2.9), (0.0, 0.6, 0.0), num_bounces=3, n_materials=len(m.materials),
+                             ambient=(0.2, 0.2, 0.2, 1.0))
+        want_o = O.oracle_frame_surface(osc, ofp, osd, m.materials, S.point_light((2.5, 4.0, 3.0)))
+        got_o = np.fromfile(os.path.join(d, "frame_obj.bin"), dtype=np.float32).reshape(160, 224, 4)
+        assert float(np.abs(got_o - want_o).max()) <= 1 / 255                             # reference-order walk: every pixel
         # PF_RGBA8 host target and PF_RGB8 device target (SSAA 2x), reference-order walk: byte for byte
         fp = S.frame_params(1, 160, 120, eye, (0, 0, 0), num_bounces=4)
         want8 = O.oracle_frame_format(sc, fp, S.default_material(0), S.point_light(eye), "PF_RGBA8")

@@ -169,6 +169,14 @@ def host_lib() -> C.CDLL:
         lib.vsbh_face_normals.argtypes = [vp, sz, vp]
         lib.vsbh_primary_rays.argtypes = [vp, vp, vp, vp, C.c_int, C.c_int, vp]
         lib.vsbh_build_bvh.argtypes = [C.c_int, vp, sz, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        lib.vsbh_obj_load.restype = vp
+        lib.vsbh_obj_load.argtypes = [C.c_char_p]
+        lib.vsbh_obj_free.argtypes = [vp]
+        lib.vsbh_obj_counts.argtypes = [vp, C.POINTER(sz)]
+        lib.vsbh_obj_copy.argtypes = [vp, vp, vp, vp, vp, vp, vp]
+        lib.vsbh_obj_texture.argtypes = [vp, sz, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(vp)]
+        lib.vsbh_obj_warning.restype = sz
+        lib.vsbh_obj_warning.argtypes = [vp, sz, C.c_char_p, sz]
         lib.vsbh_spot_cos_cutoff.restype = C.c_float
         lib.vsbh_spot_cos_cutoff.argtypes = [C.c_float]
         lib.vsbh_build_bvh_ex.argtypes = [C.c_int, vp, sz, C.c_int, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]

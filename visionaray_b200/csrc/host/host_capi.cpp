@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "visionaray_b200/bvh.h"
+#include "visionaray_b200/obj_loader.h"
 #include "scenes.h"
 #include "../shade.cuh"   // host instantiation of primary_ray() (same single-rounding arithmetic as the kernels)
 
@@ -125,6 +126,55 @@ void vsbh_primary_rays(const float* eye, const float* cu, const float* cv, const
             vsb::Ray32& q = r[(size_t)y * width + x];
             q.ox = o.x; q.oy = o.y; q.oz = o.z; q.pad0 = 0.0f; q.dx = d.x; q.dy = d.y; q.dz = d.z; q.pad1 = 0.0f;
         }
+}
+
+// ---- load_obj (include/visionaray_b200/obj_loader.h) for the Python harness -------------------------------------
+void* vsbh_obj_load(const char* path)
+{
+    model* m = new model;
+    try { load_obj(path, *m); }
+    catch (std::exception const&) { delete m; return nullptr; }
+    return m;
+}
+void vsbh_obj_free(void* h) { delete static_cast<model*>(h); }
+// out: primitives, shading normals, geometric normals, tex coords, materials, textures, warnings
+void vsbh_obj_counts(void* h, size_t* out7)
+{
+    model const& m = *static_cast<model*>(h);
+    out7[0] = m.primitives.size(); out7[1] = m.shading_normals.size(); out7[2] = m.geometric_normals.size();
+    out7[3] = m.tex_coords.size(); out7[4] = m.materials.size(); out7[5] = m.textures.size(); out7[6] = m.warnings.size();
+}
+// any pointer may be NULL; normals are 16-byte vec3, tex coords 8-byte vec2, materials 64-byte vsb_material, bbox 2 x vec3 (32 B)
+void vsbh_obj_copy(void* h, void* prims64, void* shading16, void* geometric16, void* tex8, void* materials64, void* bbox32)
+{
+    model const& m = *static_cast<model*>(h);
+    static_assert(sizeof(model::triangle_type) == 64 && sizeof(vec3) == 16 && sizeof(vec2) == 8, "layouts");
+    if (prims64) std::memcpy(prims64, m.primitives.data(), m.primitives.size() * 64);
+    if (shading16) std::memcpy(shading16, m.shading_normals.data(), m.shading_normals.size() * 16);
+    if (geometric16) std::memcpy(geometric16, m.geometric_normals.data(), m.geometric_normals.size() * 16);
+    if (tex8) std::memcpy(tex8, m.tex_coords.data(), m.tex_coords.size() * 8);
+    if (materials64)
+        for (size_t i = 0; i < m.materials.size(); ++i) { vsb_material f = m.materials[i].flatten(); std::memcpy(static_cast<char*>(materials64) + 64 * i, &f, 64); }
+    if (bbox32) { std::memcpy(bbox32, &m.bbox.min, 16); std::memcpy(static_cast<char*>(bbox32) + 16, &m.bbox.max, 16); }
+}
+// texture i: size, modes, texels (RGBA8, owned by the model); returns 0 for an empty ref
+int vsbh_obj_texture(void* h, size_t i, int* width, int* height, int* filter, int* address2, const void** texels)
+{
+    model const& m = *static_cast<model*>(h);
+    if (i >= m.textures.size()) return 0;
+    texture_ref2d const& t = m.textures[i];
+    *width = int(t.width()); *height = int(t.height()); *filter = int(t.get_filter_mode());
+    address2[0] = int(t.get_address_mode(0)); address2[1] = int(t.get_address_mode(1));
+    *texels = t.data();
+    return t.data() != nullptr && t.width() > 0 && t.height() > 0;
+}
+size_t vsbh_obj_warning(void* h, size_t i, char* out, size_t cap)
+{
+    model const& m = *static_cast<model*>(h);
+    if (i >= m.warnings.size() || cap == 0) return 0;
+    size_t n = m.warnings[i].size() < cap - 1 ? m.warnings[i].size() : cap - 1;
+    std::memcpy(out, m.warnings[i].data(), n); out[n] = 0;
+    return n;
 }
 
 } // extern "C"
