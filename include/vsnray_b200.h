@@ -151,7 +151,13 @@ enum { VSB_PF_RGBA32F = 0, VSB_PF_RGBA8 = 1, VSB_PF_RGB32F = 2, VSB_PF_RGB8 = 3 
 
 /* traversal engine: the wide quantised BVH8 (default, fast) or the reference-order BVH2 walk
  * (bit-exact with detail/bvh/intersect.inl:35-134 including tie order and any-hit winner). */
-enum { VSB_TRAVERSE_WIDE = 0, VSB_TRAVERSE_EXACT = 1 };
+enum { VSB_TRAVERSE_WIDE = 0, VSB_TRAVERSE_EXACT = 1,
+       /* opt-in, vsb_closest_hit / vsb_any_hit on triangle scenes: the BVH8 walk with the hit / miss decision of the
+        * watertight test of Woop, Benthin, Wald (JCGT 2013) instead of the reference's Moeller-Trumbore inside test
+        * (math/intersect.h:122-179, which lets rays through on shared edges); t / u / v in the reference's form, so
+        * records equal VSB_TRAVERSE_WIDE's wherever both tests accept.  Not the default: the default reproduces the
+        * reference's decisions.  (csrc/watertight.cuh; DESIGN.md 4.11 counts the rays that change.) */
+       VSB_TRAVERSE_WATERTIGHT = 2 };
 
 /* where the caller's buffers live */
 enum { VSB_MEM_DEVICE = 0, VSB_MEM_HOST = 1 };

@@ -11,6 +11,7 @@
 #include "../../visionaray_b200/csrc/bvh2_exact.cuh"
 #include "../../visionaray_b200/csrc/build_ploc.cuh"
 #include "../../visionaray_b200/csrc/multi_hit.cuh"
+#include "../../visionaray_b200/csrc/watertight.cuh"
 #include "../../visionaray_b200/csrc/shade.cuh"
 #include <algorithm>
 #include <numeric>
@@ -113,6 +114,25 @@ void hs_query_wide(void* h, int any, const void* rays, size_t n_rays, float max_
         HitReg b;
         float mt = max_t_per_ray ? max_t_per_ray[i] : max_t;
         if (any) trace_wide<true>(s, rc, mt, b); else trace_wide<false>(s, rc, mt, b);
+        out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
+        out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
+    }
+}
+
+// VSB_TRAVERSE_WATERTIGHT (csrc/watertight.cuh), host instantiation
+void hs_query_watertight(void* h, int any, const void* rays, size_t n_rays, float max_t, void* hits)
+{
+    auto* w = reinterpret_cast<HostWide*>(h);
+    WideScene s{ w->nodes.data(), w->prims.data(), w->prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    Hit32* out = reinterpret_cast<Hit32*>(hits);
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        RayCtx rc;
+        ray_ctx_init(rc, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz);
+        HitReg b; hit_reset(b);
+        float limit = max_t;
+        if (any) trace_wide_watertight<true>(s, rc, b, limit); else trace_wide_watertight<false>(s, rc, b, limit);
         out[i].hit = b.hit; out[i].prim_id = b.prim_id; out[i].geom_id = b.geom_id; out[i].t = b.t;
         out[i].u = b.u; out[i].v = b.v; out[i].prim_list_index = b.list_index; out[i].pad = 0;
     }

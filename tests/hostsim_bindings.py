@@ -30,6 +30,7 @@ def lib():
         l.hs_prims.restype = vp
         l.hs_prims.argtypes = [vp]
         l.hs_query_wide.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp, vp]
+        l.hs_query_watertight.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp]
         l.hs_query_exact.argtypes = [C.c_int, C.c_int, vp, vp, vp, vp, sz, C.c_float, vp, vp]
         l.hs_multi_hit_wide.argtypes = [vp, vp, sz, C.c_int, vp]
         l.hs_multi_hit_exact.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_int, vp]
@@ -83,6 +84,12 @@ class HostWide:
 
     def __del__(self):
         self.close()
+
+
+def query_watertight(wide: "HostWide", rays, any_hit=False, max_t=3.4028234663852886e38):
+    hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+    lib().hs_query_watertight(wide.h, int(any_hit), _p(rays), rays.shape[0], max_t, _p(hits))
+    return hits
 
 
 def query_exact(scene, rays, any_hit=False, max_t=3.4028234663852886e38, max_t_per_ray=None):

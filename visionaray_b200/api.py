@@ -17,7 +17,7 @@ import numpy as np
 from . import _native as N
 
 FLT_MAX = 3.4028234663852886e38
-TRAVERSE_WIDE, TRAVERSE_EXACT = 0, 1
+TRAVERSE_WIDE, TRAVERSE_EXACT, TRAVERSE_WATERTIGHT = 0, 1, 2
 MEM_DEVICE, MEM_HOST = 0, 1
 KERNEL_SIMPLE, KERNEL_WHITTED, KERNEL_AO, KERNEL_PATHTRACING = 0, 1, 2, 3
 PS_UNIFORM, PS_JITTERED, PS_JITTERED_BLEND = 0, 1, 2

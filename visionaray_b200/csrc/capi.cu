@@ -16,6 +16,7 @@
 #include "kernels.cuh"
 #include "build_ploc.cuh"
 #include "multi_hit.cuh"
+#include "watertight.cuh"
 
 #include "capi_scene.inl"
 #include "capi_build.inl"
@@ -113,12 +114,46 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
     int rc = require_init(); if (rc) return rc;
     if (n_rays == 0) return VSB_OK;
     if (!rays || !hits) return VSB_ERR_BAD_ARG;
-    if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT) return VSB_ERR_BAD_ARG;
+    if (traverse != VSB_TRAVERSE_WIDE && traverse != VSB_TRAVERSE_EXACT && traverse != VSB_TRAVERSE_WATERTIGHT) return VSB_ERR_BAD_ARG;
     cudaStream_t st = cuda_stream ? (cudaStream_t)cuda_stream : g.stream;
     CallOrder order(st);
     rc = upload_scene_table(scenes, n_scenes, st); if (rc) return rc;
 
     if (mem != VSB_MEM_HOST && mem != VSB_MEM_DEVICE) return VSB_ERR_BAD_ARG;
+    if (traverse == VSB_TRAVERSE_WATERTIGHT)
+    {
+        // opt-in mode (csrc/watertight.cuh): one thread per ray, triangle scenes only
+        for (int i = 0; i < n_scenes; ++i) if (scenes[i]->prim_kind != VSB_PRIM_TRIANGLE) return VSB_ERR_UNSUPPORTED;
+        const vsb::Ray32* d_rays = reinterpret_cast<const vsb::Ray32*>(rays);
+        vsb::Hit32* d_hits = reinterpret_cast<vsb::Hit32*>(hits);
+        const float* d_mt = max_t_per_ray;
+        if (mem == VSB_MEM_HOST)
+        {
+            void *a, *b, *c = nullptr;
+            rc = stage(0, n_rays * sizeof(vsb_ray), &a); if (rc) return rc;
+            rc = stage(1, n_rays * sizeof(vsb_hit), &b); if (rc) return rc;
+            VSB_CUDA(cudaMemcpyAsync(a, rays, n_rays * sizeof(vsb_ray), cudaMemcpyHostToDevice, st));
+            if (max_t_per_ray)
+            {
+                rc = stage(2, n_rays * sizeof(float), &c); if (rc) return rc;
+                VSB_CUDA(cudaMemcpyAsync(c, max_t_per_ray, n_rays * sizeof(float), cudaMemcpyHostToDevice, st));
+            }
+            d_rays = reinterpret_cast<const vsb::Ray32*>(a); d_hits = reinterpret_cast<vsb::Hit32*>(b); d_mt = reinterpret_cast<const float*>(c);
+        }
+        const unsigned blocks = (unsigned)((n_rays + 127) / 128);
+        VSB_CUDA(cudaEventRecord(g.ev0, st));
+        if (any) vsb::watertight_kernel<true><<<blocks, 128, 0, st>>>(g.d_scenes, n_scenes, d_rays, n_rays, max_t, d_mt, d_hits);
+        else     vsb::watertight_kernel<false><<<blocks, 128, 0, st>>>(g.d_scenes, n_scenes, d_rays, n_rays, max_t, d_mt, d_hits);
+        ++g.launches;
+        VSB_CUDA(cudaGetLastError());
+        VSB_CUDA(cudaEventRecord(g.ev1, st));
+        if (mem == VSB_MEM_HOST)
+        {
+            VSB_CUDA(cudaMemcpyAsync(hits, d_hits, n_rays * sizeof(vsb_hit), cudaMemcpyDeviceToHost, st));
+            VSB_CUDA(cudaStreamSynchronize(st));
+        }
+        return VSB_OK;
+    }
     const bool exact = traverse == VSB_TRAVERSE_EXACT;
     if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
 
