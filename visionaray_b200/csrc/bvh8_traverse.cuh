@@ -12,6 +12,7 @@ struct WideScene
     const Node80* nodes;      // BVH8 nodes, root = 0
     const void*   prims;      // TriRec[] or SphRec[] in leaf order
     int           prim_kind;  // 0 triangles, 1 spheres
+    const uint32_t* rec_of_list = nullptr;   // primitive_list_index -> leaf-order record (the queue kernel's keys carry the list index)
 };
 
 struct RayCtx
@@ -232,6 +233,13 @@ VSB_HD bool prim_candidate(int prim_kind, const NodeRegs& n, float ox, float oy,
                               u2f(n.w[4]), u2f(n.w[5]), u2f(n.w[6]), u2f(n.w[8]), u2f(n.w[9]), u2f(n.w[10]), t, u, v);
     }
     return isect_sphere(ox, oy, oz, dx, dy, dz, u2f(n.w[0]), u2f(n.w[1]), u2f(n.w[2]), u2f(n.w[3]), t);
+}
+
+// primitive_list_index (position in the reference's indices[]) of a loaded leaf-order record
+VSB_HD uint32_t record_list_index(int prim_kind, const NodeRegs& n)
+{
+    if (prim_kind == 1 || (prim_kind == 2 && (n.w[11] & VSB_GENERIC_SPHERE_TAG))) return n.w[6];
+    return n.w[11];
 }
 
 // The hit record of leaf-order record `rec` for a ray: the test is evaluated again (bit-identical

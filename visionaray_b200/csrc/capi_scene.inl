@@ -81,6 +81,7 @@ struct vsb_scene
     uint32_t* d_indices = nullptr;       // NULL for a non-index bvh
     vsb::Node80* d_wide = nullptr;
     void*    d_wide_prims = nullptr;
+    uint32_t* d_rec_of_list = nullptr;   // primitive_list_index -> leaf-order record
     float4*  d_normals = nullptr;        // optional, vsb_scene_set_normals()
     size_t   n_normals = 0;              // entries of d_normals (>= max_prim_id + 1; a frame over several bvhs indexes ONE array by prim_id)
     mutable int id_range_known = 0;      // largest prim_id / geom_id of the primitives, computed on first use
@@ -255,6 +256,7 @@ extern "C" int vsb_scene_destroy(vsb_scene* s)
     if (s->d_indices) cudaFree(s->d_indices);
     if (s->d_wide) cudaFree(s->d_wide);
     if (s->d_wide_prims) cudaFree(s->d_wide_prims);
+    if (s->d_rec_of_list) cudaFree(s->d_rec_of_list);
     if (s->d_normals) cudaFree(s->d_normals);
     for (void* q : s->surf_allocs) cudaFree(q);
     delete s;
@@ -330,8 +332,9 @@ int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size
     VSB_ENC_CUDA(cudaMalloc((void**)&s->d_wide, (size_t)s->n_wide * sizeof(vsb::Node80) + 64));
     VSB_ENC_CUDA(cudaMemcpyAsync(s->d_wide, d_wide_tmp, (size_t)s->n_wide * sizeof(vsb::Node80), cudaMemcpyDeviceToDevice, st));
     VSB_ENC_CUDA(cudaMalloc(&s->d_wide_prims, (size_t)s->n_wide_prims * rec_bytes + 64));
+    VSB_ENC_CUDA(cudaMalloc((void**)&s->d_rec_of_list, (size_t)s->n_wide_prims * sizeof(uint32_t) + 64));
     vsb::fill_prims_kernel<<<(s->n_wide_prims + 255) / 256, 256, 0, g.stream>>>(
-        s->prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims);
+        s->prim_kind, s->d_prims, s->d_indices, d_leaf_list, s->n_wide_prims, s->d_wide_prims, s->d_rec_of_list);
     ++g.launches;
     VSB_ENC_CUDA(cudaGetLastError());
     VSB_ENC_CUDA(cudaStreamSynchronize(g.stream));
@@ -339,6 +342,7 @@ int encode_wide(vsb_scene* s, vsb::Node32* d_enc_nodes, size_t n_enc_nodes, size
 #undef VSB_ENC_CUDA
 
     s->dev.wide.nodes = s->d_wide; s->dev.wide.prims = s->d_wide_prims; s->dev.wide.prim_kind = s->prim_kind;
+    s->dev.wide.rec_of_list = s->d_rec_of_list;
     s->dev.exact.nodes = s->d_nodes2; s->dev.exact.prims = s->d_prims; s->dev.exact.indices = s->d_indices;
     s->dev.exact.prim_kind = s->prim_kind;
     return VSB_OK;

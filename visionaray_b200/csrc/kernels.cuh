@@ -89,11 +89,12 @@ __global__ void encode_level_kernel(const WideTask* __restrict__ tasks, uint32_t
 }
 
 __global__ void fill_prims_kernel(int prim_kind, const void* __restrict__ prims, const uint32_t* __restrict__ indices,
-                                  const uint32_t* __restrict__ leaf_list, uint32_t n, void* out)
+                                  const uint32_t* __restrict__ leaf_list, uint32_t n, void* out, uint32_t* __restrict__ rec_of_list)
 {
     const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
     make_prim_record(prim_kind, prims, indices, leaf_list[i], out, i);
+    rec_of_list[leaf_list[i]] = i;       // every list position sits in exactly one leaf (validate_tree): a permutation
 }
 
 // largest prim_id / geom_id of a primitive array (ids are caller data: per-primitive arrays are indexed by
@@ -289,7 +290,7 @@ trace_kernel(const TraceLaunch tl, const __grid_constant__ Program prog)
 // selects are appended as (leaf-order record, owner) pairs to a per-warp ring in shared memory, and
 // when the ring holds 32 pairs (or nothing else can run) ALL 32 LANES test one pair each: record loaded
 // from global memory, the owner's ray from shared memory, result merged into the owner's 64-bit key
-// (t bits << 32 | record) with atomicMin.  The primitive test thus runs at (nearly) full warp width
+// (t bits << 32 | primitive_list_index) with atomicMin.  The primitive test thus runs at (nearly) full warp width
 // however few lanes found primitives in a given step -- it ran at 9.4 of 32 lanes in trace_kernel
 // (profiles/r1_cfg2_instruction_regions_v8.txt) -- and the node test is no longer skipped by lanes that
 // are busy with primitives.  Cost: an owner's cull bound lags its pending pairs by an iteration or two.
@@ -297,8 +298,10 @@ trace_kernel(const TraceLaunch tl, const __grid_constant__ Program prog)
 //
 // Lane states: TRAVERSING (node work left), PENDING (node work done, pairs of this lane still queued:
 // it is finished when the ring's head has passed the lane's last pair), WAITING / EMPTY / DEAD as above.
-// Ties: the key orders (t, record), so among equal t the smallest leaf-order record wins -- a fixed
-// rule, independent of scheduling (tie candidates are never culled: the node test is conservative).
+// Ties: the key orders (t, primitive_list_index), so among equal t the smallest position in the reference's
+// primitive list wins -- a fixed rule, independent of scheduling AND of how the BVH8 happened to be laid out
+// (its record order comes from atomic allocation and differs between builds; the first version keyed on it and
+// two GPUs disagreed on tie pixels).  Tie candidates are never culled: the node test is conservative.
 // Any-hit lanes leave as soon as their key holds a hit; pairs they leave behind are tested against
 // whatever ray the lane holds then, which is a valid (ray, primitive) test of the same scene.
 // One bvh per launch, BVH8 walk only: ranges of bvhs and the reference-order walk stay on trace_kernel.
@@ -359,7 +362,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             float tt;
             if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
             {
-                const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | e.x;
+                const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | record_list_index(sc.prim_kind, r);
                 if (cand < key_s[e.y]) atomicMin(key_s + e.y, cand);
             }
         }
@@ -379,9 +382,9 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             {
                 const float* o = ray_s + threadIdx.x;
                 const float ox = o[0], oy = o[VSB_BLOCK], oz = o[2 * VSB_BLOCK], dx = o[3 * VSB_BLOCK], dy = o[4 * VSB_BLOCK], dz = o[5 * VSB_BLOCK];
-                const uint32_t rec = (uint32_t)key_s[threadIdx.x];
+                const uint32_t li = (uint32_t)key_s[threadIdx.x];
                 HitReg best;
-                if (live && rec != VSB_KEY_NONE) hit_from_record(sc, rec, ox, oy, oz, dx, dy, dz, best);
+                if (live && li != VSB_KEY_NONE) hit_from_record(sc, __ldg(sc.rec_of_list + li), ox, oy, oz, dx, dy, dz, best);
                 else hit_reset(best);
                 if (prog.done(L, best, ox, oy, oz, dx, dy, dz, req)) start = true;
                 else state = LANE_EMPTY;
