@@ -21,8 +21,8 @@ closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.j
             host cores, on the SAME frame as the GPU arm
   extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3;
             gpu_built_tree: cfg2 and cfg5 on the tree of the GPU builder, with build time and time to first frame
-  strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 (peer stores over NVLink) and
-            cfg4 (progressive path tracer: all-gather + de-interleave), with v_N / (N v_1)
+  strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 and cfg4 (progressive path tracer), tiles
+            stored into rank 0's frame over NVLink from inside the trace kernel, with v_N / (N v_1)
 
 N > 1 (torchrun): the frame is partitioned into interleaved 64x64 tiles (tile k -> rank k % N), the
 scene is replicated.  Headline = weak scaling: the same view at sqrt(N) x the resolution per axis
@@ -385,9 +385,10 @@ class FrameRig:
     """Device-resident buffers and step() of one frame workload.  Modes:
        single  one GPU renders the whole frame into its own buffer
        peer    N > 1: every rank stores its tiles straight into rank 0's frame over NVLink peer memory (CUDA IPC)
-               from inside the trace kernel; a 4-byte all-reduce per step is the frame fence
+               from inside the trace kernel; a 4-byte all-reduce per step is the frame fence.  The progressive path
+               tracer keeps its blend state in a local compact tile buffer and MIRRORS finished pixels into that frame
        nccl    N > 1: compact tile buffers + NCCL all-gather + de-interleave on a side stream, double-buffered
-               (the progressive path tracer: its blend re-reads the rank's own previous frame)"""
+               (--gather nccl; kept as the comparison)"""
 
     def __init__(self, ctx: Ctx, wl: dict, dev, w: int, h: int, mode: str):
         torch, api = ctx.torch, ctx.api
@@ -399,6 +400,7 @@ class FrameRig:
         self.per = max(api.tiles_of_rank(w, h, r, ctx.world) for r in range(ctx.world))
         self.k = 0
         self.frame_buf = None
+        self.local = None
         if mode == "single":
             self.image = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
         elif mode == "peer":
@@ -410,6 +412,9 @@ class FrameRig:
             if ctx.rank != 0:
                 self.frame_buf = api.DeviceBuffer.open(handle[0], w * h * 16)
             self.done_flag = torch.zeros(1, dtype=torch.float32, device="cuda")
+            # progressive blending re-reads the rank's own accumulated frame: it stays in a local compact tile buffer, and
+            # every finished pixel is mirrored in place into rank 0's frame (vsb_frame_desc.mirror_color)
+            self.local = torch.zeros((self.per, api.TILE * api.TILE, 4), dtype=torch.float32, device="cuda") if wl["kernel"] == 3 else None
         else:
             T = api.TILE * api.TILE
             self.tile_buf = [torch.zeros((self.per, T, 4), dtype=torch.float32, device="cuda") for _ in range(2)]
@@ -431,8 +436,12 @@ class FrameRig:
         if self.mode == "single":
             api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.image, traverse=ctx.trav, ray_count=self.d_rays, stream=st)
         elif self.mode == "peer":
-            api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.frame_buf, traverse=ctx.trav, tile_rank=ctx.rank,
-                      tile_nranks=ctx.world, ray_count=self.d_rays, stream=st, tiles_in_place=True)
+            if self.local is not None:
+                api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.local, traverse=ctx.trav, tile_rank=ctx.rank,
+                          tile_nranks=ctx.world, ray_count=self.d_rays, stream=st, mirror=self.frame_buf)
+            else:
+                api.frame(self.dev, fp, None, self.d_mats, self.d_lights, self.frame_buf, traverse=ctx.trav, tile_rank=ctx.rank,
+                          tile_nranks=ctx.world, ray_count=self.d_rays, stream=st, tiles_in_place=True)
             ctx.dist.all_reduce(self.done_flag)            # frame k is complete on rank 0 once this returns on its stream
         else:
             b = k & 1
@@ -789,13 +798,14 @@ def extra_legs(ctx: Ctx, O, args, cfg2_prims):
 
 
 def strong_legs(ctx: Ctx, args, cfg2_scene=None):
-    """N > 1: the FIXED 4096^2 frame partitioned over the N GPUs -- cfg2 through peer stores, cfg4 (configs[3]: the
-    progressive path tracer) through all-gather + de-interleave -- against the same frame on one GPU alone, measured
+    """N > 1: the FIXED 4096^2 frame partitioned over the N GPUs -- cfg2, and cfg4 (configs[3]: the progressive path
+    tracer), both assembled by peer stores into rank 0's frame -- against the same frame on one GPU alone, measured
     in the same run (every rank renders it alone at the same time; rank-local work, max over ranks)."""
     S, api = ctx.S, ctx.api
     out = {}
     steps, warmup = max(5, min(args.steps, 10)), 3
-    for name, mode in (("cfg2", "peer"), ("cfg4", "nccl")):
+    mode = "nccl" if args.gather == "nccl" else "peer"
+    for name in ("cfg2", "cfg4"):
         wl = WORKLOADS[name]
         if name == "cfg2" and cfg2_scene is not None:
             sc, dev, info, own = cfg2_scene[0], cfg2_scene[1], cfg2_scene[2], False
@@ -806,22 +816,27 @@ def strong_legs(ctx: Ctx, args, cfg2_scene=None):
         alone = FrameRig(ctx, wl, dev, w, h, "single")
         r1 = time_rig(ctx, alone, steps, warmup, clocks=False)
         v1 = r1["value"] / ctx.world                              # all ranks ran the same frame alone: per-GPU rate
-        ref_img = alone.image.clone() if name == "cfg2" else None
         alone.close(); del alone
         rig = FrameRig(ctx, wl, dev, w, h, mode)
         rn = time_rig(ctx, rig, steps, warmup, clocks=False)
+        rig.close(); del rig
+        # the assembled frame equals the frame one GPU renders alone: fresh buffers on both sides, 3 frames each (the
+        # progressive path tracer accumulates frame_num = 1..3)
+        a2, r2 = FrameRig(ctx, wl, dev, w, h, "single"), FrameRig(ctx, wl, dev, w, h, mode)
+        for _ in range(3):
+            a2.step(); r2.step()
+        r2.end_of_region()
+        ctx.fence()
         verified = None
-        if name == "cfg2":
-            ctx.fence()
-            if ctx.rank == 0:
-                verified = bool(ctx.torch.equal(rig.assembled(), ref_img))
-            ctx.fence()
+        if ctx.rank == 0:
+            verified = bool(ctx.torch.equal(r2.assembled(), a2.image))
+        ctx.fence()
+        a2.close(); r2.close(); del a2, r2
         out[name] = {"frame": [w, h], "assembly": mode, "value": rn["value"], "unit": "Mrays/s", "ms_per_step": rn["ms_per_step"],
                      "trace_kernel_ms": rn["kernel_ms"], "exchange_alone_ms": rn["exchange_ms"],
                      "one_gpu_value": v1, "one_gpu_ms_per_step": r1["ms_per_step"], "efficiency": rn["value"] / (ctx.world * v1),
                      "steps": steps, "warmup": warmup, "assembled_frame_verified": verified,
                      "triangles": sc.n_prims, "builder": info}
-        rig.close(); del rig
         if own:
             dev.close()
     return out
@@ -835,7 +850,7 @@ def run_gpu(args):
     t_start = time.perf_counter()
     sc, dev, builder = prepare_scene(api, S, wl["scene"], args.scale, args.builder)
     stats = dev.stats()
-    mode = "single" if ctx.world == 1 else ("nccl" if (args.gather == "nccl" or wl["kernel"] == 3) else "peer")
+    mode = "single" if ctx.world == 1 else ("nccl" if args.gather == "nccl" else "peer")
     rig = FrameRig(ctx, wl, dev, w, h, mode)
     rig.step()                                         # generate -> build -> first frame (one more untimed warm-up step)
     rig.end_of_region()

@@ -242,6 +242,11 @@ typedef struct vsb_frame_desc {
                                             whitted.inl:66-122).  Detected automatically when params_mem == VSB_MEM_HOST. */
     int32_t  spot_lights;                /* non-zero: `lights` may hold VSB_LIGHT_SPOT entries.  Detected automatically when
                                             params_mem == VSB_MEM_HOST. */
+    void*    mirror_color;               /* optional, with compact tile buffers (tile_nranks > 1, VSB_TILES_COMPACT), RGBA32F, device
+                                            memory: every finished pixel is ALSO stored at its row-major position in this whole
+                                            frame (e.g. a peer GPU's buffer opened with vsb_ipc_open()).  Progressive blending
+                                            (jittered_blend) keeps its state in the rank's compact buffer while the assembled frame
+                                            appears in place over NVLink: no all-gather / de-interleave pass */
 } vsb_frame_desc;
 
 typedef struct vsb_scene vsb_scene;

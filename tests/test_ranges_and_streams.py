@@ -127,3 +127,35 @@ def test_overlapping_leaf_ranges_are_rejected(gpu):
     nodes["num_prims"][i] += 1                                         # ... and the total exceeds the list length
     with pytest.raises(RuntimeError):
         gpu.Scene(dataclasses.replace(sc, nodes=nodes))
+
+
+def test_mirror_frame_of_compact_progressive_tiles(gpu):
+    """Progressive blending over 3 'ranks' (one after the other on one GPU): each keeps its accumulation in its compact
+    tile buffer and mirrors every finished pixel into ONE row-major frame (what peers do into rank 0's buffer over
+    NVLink): after 3 accumulated frames the mirror equals the frame one rank accumulates alone, byte for byte."""
+    import torch
+
+    sc = S.make_scene("cfg2_grid", 0.02)
+    dev = gpu.Scene(sc)
+    eye = (0.3, 1.2, 2.2)
+    w, h, nr = 328, 200, 3                             # ragged right / top tiles
+    mats, lights = S.default_material(1), S.point_light(eye)
+    d_m = torch.from_numpy(mats.view(np.float32).copy()).cuda()
+    d_l = torch.from_numpy(lights.view(np.float32).copy()).cuda()
+    alone = torch.zeros((h, w, 4), dtype=torch.float32, device="cuda")
+    per = max(gpu.tiles_of_rank(w, h, r, nr) for r in range(nr))
+    local = [torch.zeros((per, 64 * 64, 4), dtype=torch.float32, device="cuda") for _ in range(nr)]
+    mirror = torch.full((h, w, 4), -1.0, dtype=torch.float32, device="cuda")
+    for frame_num in (1, 2, 3):
+        fp = S.frame_params(3, w, h, eye, (0, 0, 0), pixel_sampler=2, frame_num=frame_num, num_bounces=3, ambient=(1, 1, 1, 1))
+        gpu.frame(dev, fp, None, d_m, d_l, alone)
+        for r in range(nr):
+            gpu.frame(dev, fp, None, d_m, d_l, local[r], tile_rank=r, tile_nranks=nr, mirror=mirror)
+    torch.cuda.synchronize()
+    gpu.sync()
+    assert torch.equal(mirror, alone)
+    fp = S.frame_params(3, w, h, eye, (0, 0, 0), pixel_sampler=2, frame_num=1, num_bounces=3, ambient=(1, 1, 1, 1))
+    with pytest.raises(RuntimeError):                  # a mirror needs compact tile buffers
+        gpu.frame(dev, fp, None, d_m, d_l, alone, mirror=mirror)
+    dev.close()
+

@@ -64,6 +64,7 @@ class FrameDesc(C.Structure):
         ("params_mem", C.c_int32), ("tile_target", C.c_int32),
         ("camera_kind", C.c_int32), ("view_matrix", C.c_float * 16), ("proj_matrix", C.c_float * 16),
         ("color_format", C.c_int32), ("generic_materials", C.c_int32), ("spot_lights", C.c_int32),
+        ("mirror_color", C.c_void_p),
     ]
 
 

@@ -334,7 +334,7 @@ def set_surface(scene: "Scene", surface) -> None:
 
 def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse=TRAVERSE_WIDE, tile_rank=0,
           tile_nranks=0, ray_count=None, stream=None, tiles_in_place=False, view_matrix=None, proj_matrix=None,
-          depth=None, generic_materials=False, color_format=0, spot_lights=False):
+          depth=None, generic_materials=False, color_format=0, spot_lights=False, mirror=None):
     """One frame() call.  `color` (and `ray_count`): numpy array -> host render target (D2H inside
     the call, returns with pixels in place); torch CUDA tensor -> device render target
     (asynchronous on `stream`).  `materials` / `lights` (and `normals`, which may be None to use the
@@ -384,6 +384,7 @@ def frame(scenes, fp: N.FrameParams, normals, materials, lights, color, traverse
     d.spot_lights = 1 if spot_lights else 0
     d.color_format = color_format          # PF_RGBA32F 0, PF_RGBA8 1, PF_RGB32F 2 (16-byte pixels), PF_RGB8 3
     d.ray_count = p(ray_count)
+    d.mirror_color = p(mirror)             # compact tile buffers only: the whole row-major frame every finished pixel is also stored into
     uses_torch = any(hasattr(a, "is_contiguous") for a in (normals, materials, lights, color, depth, ray_count) if a is not None)
     _check(N.cuda_lib().vsb_frame(_scene_array(scenes), len(scenes), C.byref(d), _torch_stream(stream) if uses_torch else stream), "vsb_frame")
     return color

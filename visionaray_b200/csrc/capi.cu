@@ -498,6 +498,8 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     // PINNED + MAPPED host memory the kernel stores into directly (checked below); never with a blend, which re-reads the target
     if (fl.in_place && p.pixel_sampler == VSB_PS_JITTERED_BLEND) return VSB_ERR_UNSUPPORTED;
     if (d->color_format < VSB_PF_RGBA32F || d->color_format > VSB_PF_RGB8) return VSB_ERR_BAD_ARG;
+    // the mirror frame: compact RGBA32F tile buffers in device memory only (the pixel's position is recovered from its compact index)
+    if (d->mirror_color && (nranks < 2 || fl.in_place || d->color_format != VSB_PF_RGBA32F || d->mem != VSB_MEM_DEVICE)) return VSB_ERR_UNSUPPORTED;
     if (d->color_format != VSB_PF_RGBA32F && nranks > 1 && !fl.in_place) return VSB_ERR_UNSUPPORTED;   // compact tile buffers + de-interleave are RGBA32F
     const size_t bpp = d->color_format == VSB_PF_RGBA8 ? 4 : (d->color_format == VSB_PF_RGB8 ? 3 : 16);
     const size_t color_px = (nranks > 1 && !fl.in_place) ? (size_t)fl.n_owned_tiles * VSB_TILE * VSB_TILE : (size_t)p.width * p.height;
@@ -678,6 +680,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
         prog.tile_rank = fl.tile_rank; prog.tile_nranks = fl.tile_nranks; prog.tiles_x = fl.tiles_x;         \
         prog.in_place = fl.in_place; prog.tile_begin = tile_begin;                                           \
         prog.unit_tiles = unit_tiles; prog.unit_stride = n_bands; prog.n_local_tiles = fl.n_owned_tiles;     \
+        prog.mirror = reinterpret_cast<float4*>(d->mirror_color);                                            \
         if (exact) VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS, SF>, true>(prog, tl, bs)));                   \
         else       VSB_CUDA((launch_trace<vsb::FrameProgram<K, SS, SF>, false>(prog, tl, bs)));                  \
     } while (0)

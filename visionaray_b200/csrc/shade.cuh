@@ -817,6 +817,7 @@ struct FrameProgram
     int tile_begin;                  // first rank-local tile of this launch (host targets are rendered in bands)
     int unit_tiles, unit_stride;     // a band = every unit_stride-th run of unit_tiles tiles, so bands cost alike (0: one launch)
     int n_local_tiles;
+    float4* mirror;                  // compact tile buffers: the whole row-major frame finished pixels are ALSO stored into (or null)
 
     using Lane = FrameLane;
 #ifndef VSB_FRAME_MIN_BLOCKS
@@ -936,6 +937,14 @@ struct FrameProgram
         else if (EXT && depth) depth[dst] = L.f(W_DEPTH);
         if (EXT) store_pixel(color_format, color, dst, c);
         else color[dst] = c;
+        if (mirror)
+        {
+            // dst indexes the rank's compact tile buffer: back to the pixel's row-major position in the whole frame
+            const uint32_t lt = (uint32_t)dst / (VSB_TILE * VSB_TILE), in = (uint32_t)dst % (VSB_TILE * VSB_TILE);
+            const uint32_t tile = lt * (uint32_t)tile_nranks + (uint32_t)tile_rank;
+            const uint32_t x = (tile % (uint32_t)tiles_x) * VSB_TILE + (in % VSB_TILE), y = (tile / (uint32_t)tiles_x) * VSB_TILE + (in / VSB_TILE);
+            mirror[(size_t)y * (size_t)ctx.p.width + x] = c;
+        }
         return false;
     }
     __device__ bool finish_bg(Lane& L, RayReq& req) const { return finish(L, ctx.p.bg[0], ctx.p.bg[1], ctx.p.bg[2], ctx.p.bg[3], req); }
