@@ -20,7 +20,8 @@ closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.j
   cpu_baseline  the reference's own tiled_sched<simd::ray8> (oracle/_ref, unmodified headers) on the
             host cores, on the SAME frame as the GPU arm
   extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3;
-            gpu_built_tree: cfg2 and cfg5 on the tree of the GPU builder, with build time and time to first frame
+            gpu_built_tree: cfg2 and cfg5 on the tree of the GPU builder, with build time and time to first frame;
+            naive_gpu: the same frame by the reference's own cuda_sched kernel on this GPU (unmodified headers)
   strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 and cfg4 (progressive path tracer), tiles
             stored into rank 0's frame over NVLink from inside the trace kernel, with v_N / (N v_1)
 
@@ -794,6 +795,22 @@ def extra_legs(ctx: Ctx, O, args, cfg2_prims):
     rig.close()
     dev.close()
     out["gpu_built_tree"] = gpu_tree
+
+    # the same frame by the REFERENCE'S OWN CUDA path on this GPU: cuda_sched<ray>::frame() + whitted::kernel over a
+    # cuda_index_bvh, unmodified headers compiled for sm_100a (oracle/refcuda; none of this repository's kernels)
+    if O.ref_cuda_available():
+        try:
+            wl = WORKLOADS["cfg2"]
+            fp = make_frame_params(S, wl, wl["w"], wl["h"])
+            host = S.HostScene(0, cfg2_prims, None, None, None, "cfg2")
+            _, ms, bms = O.ref_cuda_whitted(host, fp, wl["eye"], reps=steps, warmup=warmup, want_image=False)
+            out["naive_gpu"] = {"impl": "the reference's cuda_sched<basic_ray<float>> + whitted::kernel (one thread per pixel, BVH2, 16x16 blocks)",
+                                "ms_per_step": ms, "frame": [wl["w"], wl["h"]], "steps": steps, "warmup": warmup,
+                                "host_build_and_upload_ms": bms}
+        except Exception as e:                         # a baseline, never a reason to lose the run's line
+            out["naive_gpu"] = {"unavailable": str(e)[:200]}
+    else:
+        out["naive_gpu"] = {"unavailable": "oracle/_ref/libvsnray_ref_cuda.so was not built"}
     return out
 
 
@@ -910,6 +927,12 @@ def run_gpu(args):
         line["extra"] = extra_legs(ctx, O, args, sc.prims)
         line["extra"]["gpu_built_tree"]["cfg2"]["vs_reference_tree"] = line["extra"]["gpu_built_tree"]["cfg2"]["value"] / line["value"] \
             if args.builder == "reference" else None
+        ng = line["extra"].get("naive_gpu") or {}
+        if "ms_per_step" in ng:
+            # the same frame = the same rays (up to tie pixels): this run's kernel counter gives the rate
+            ng["value"] = line["config"]["rays_per_step"] / (ng["ms_per_step"] * 1e-3) / 1e6
+            ng["unit"] = "Mrays/s"
+            ng["this_repo_over_naive_gpu"] = line["value"] / ng["value"]
     if ctx.rank == 0:
         print(json.dumps(line), flush=True)
     ctx.close()

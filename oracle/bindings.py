@@ -430,3 +430,39 @@ def ref_query_timed(scene, rays, any_hit=False, max_t=3.4028234663852886e38, nth
                                          rays.shape[0], max_t, nthreads or (os.cpu_count() or 1), reps, warmup,
                                          C.byref(nh))
     return secs, nh.value
+
+
+# ---- the reference's own CUDA path (oracle/refcuda/ref_cuda_harness.cu -> oracle/_ref/libvsnray_ref_cuda.so) ----
+_ref_cuda = None
+
+
+def ref_cuda_path() -> str:
+    return os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libvsnray_ref_cuda.so")
+
+
+def ref_cuda_available() -> bool:
+    return os.path.exists(ref_cuda_path())
+
+
+def ref_cuda_whitted(scene, fp, light_pos, reps=1, warmup=0, want_image=True):
+    """cuda_sched<basic_ray<float>>::frame() with the stock whitted::kernel on the GPU (needs a CUDA device): returns
+    (rgba or None, ms per frame, build + upload ms).  The tree is the reference's own build<index_bvh>()."""
+    global _ref_cuda
+    if _ref_cuda is None:
+        lib = C.CDLL(ref_cuda_path())
+        lib.ref_cuda_whitted.restype = C.c_float
+        lib.ref_cuda_whitted.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_float), C.POINTER(C.c_float),
+                                         C.c_float, C.POINTER(C.c_float), C.c_uint, C.c_float, C.POINTER(C.c_float), C.c_int, C.c_int,
+                                         C.c_void_p, C.POINTER(C.c_float)]
+        _ref_cuda = lib
+    f3 = lambda v: (C.c_float * 3)(*[float(x) for x in v[:3]])
+    img = np.zeros((fp.height, fp.width, 4), dtype=np.float32) if want_image else None
+    bms = C.c_float(0)
+    bg = (C.c_float * 4)(*[float(fp.bg[i]) for i in range(4)])
+    ms = _ref_cuda.ref_cuda_whitted(_p(scene.prims), scene.prims.shape[0], fp.width, fp.height, f3(fp.eye), f3(fp.center), f3(fp.up),
+                                    fp.fovy, f3(light_pos), fp.num_bounces, fp.epsilon, bg, reps, warmup,
+                                    _p(img) if want_image else None, C.byref(bms))
+    if ms < 0:
+        raise RuntimeError("ref_cuda_whitted: CUDA error")
+    return img, float(ms), float(bms.value)
+
