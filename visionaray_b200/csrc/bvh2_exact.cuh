@@ -65,7 +65,8 @@ VSB_HD void trace_exact(const ExactScene& s, float ox, float oy, float oz, float
             if (b0 && b1)
             {
                 const bool near0 = tn0 < tn1;                 // ties -> child 1 (:86)
-                if (sp < VSB_EXACT_STACK) stack[sp++] = node.first + (near0 ? 1u : 0u);
+                if (sp >= VSB_EXACT_STACK) VSB_STACK_OVERFLOW();
+                stack[sp++] = node.first + (near0 ? 1u : 0u);
                 node = near0 ? c0 : c1;
             }
             else if (b0) node = c0;

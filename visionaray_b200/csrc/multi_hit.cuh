@@ -95,7 +95,8 @@ VSB_HD void multi_hit_exact(const ExactScene& s, float ox, float oy, float oz, f
             if (b0 && b1)
             {
                 const bool near0 = tn0 < tn1;
-                if (sp < VSB_EXACT_STACK) stack[sp++] = node.first + (near0 ? 1u : 0u);
+                if (sp >= VSB_EXACT_STACK) VSB_STACK_OVERFLOW();
+                stack[sp++] = node.first + (near0 ? 1u : 0u);
                 node = near0 ? c0 : c1;
             }
             else if (b0) node = c0;
@@ -166,7 +167,11 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
             const uint32_t imask = ng_mask & 0xffu;
             const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xffu)) & 7u;
             const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
-            if ((ng_mask & 0xff000000u) && sp < VSB_STACK_SIZE) { sb[sp] = ng_base; sm[sp] = ng_mask; ++sp; }
+            if (ng_mask & 0xff000000u)
+            {
+                if (sp >= VSB_STACK_SIZE) VSB_STACK_OVERFLOW();
+                sb[sp] = ng_base; sm[sp] = ng_mask; ++sp;
+            }
             load_record(reinterpret_cast<const char*>(s.nodes + (ng_base + rel)), 5, n);
             uint32_t ph;
             const uint32_t nh = test_node(n, r, out.limit, ph);

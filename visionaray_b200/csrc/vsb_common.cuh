@@ -28,6 +28,16 @@ struct float2 { float x, y; };
 struct uchar4 { unsigned char x, y, z, w; };
 #endif
 
+// A traversal stack that would overflow is a broken invariant (tree depths are checked when a scene is created /
+// before the reference-order walk is chosen), never a case to drop a subtree silently: the kernel traps (the call
+// returns a CUDA error), the host instantiation aborts.
+#if defined(__CUDA_ARCH__)
+#define VSB_STACK_OVERFLOW() __trap()
+#else
+#include <cstdlib>
+#define VSB_STACK_OVERFLOW() std::abort()
+#endif
+
 namespace vsb
 {
 

@@ -127,7 +127,11 @@ VSB_HD void trace_wide_watertight(const WideScene& s, const RayCtx& r, HitReg& b
             const uint32_t imask = ng_mask & 0xffu;
             const uint32_t slot = ((uint32_t)(bit - 24) ^ (r.octinv4 & 0xffu)) & 7u;
             const uint32_t rel = (uint32_t)pop_count(imask & ~(0xffffffffu << slot));
-            if ((ng_mask & 0xff000000u) && sp < VSB_STACK_SIZE) { sb[sp] = ng_base; sm[sp] = ng_mask; ++sp; }
+            if (ng_mask & 0xff000000u)
+            {
+                if (sp >= VSB_STACK_SIZE) VSB_STACK_OVERFLOW();
+                sb[sp] = ng_base; sm[sp] = ng_mask; ++sp;
+            }
             load_record(reinterpret_cast<const char*>(s.nodes + (ng_base + rel)), 5, n);
             uint32_t ph;
             const uint32_t nh = test_node(n, r, limit, ph);
