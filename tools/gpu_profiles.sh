@@ -1,12 +1,23 @@
 #!/bin/bash
-# ncu evidence for profiles/: launch lists (shares) and one full capture of the dominant kernel per workload.
-# Each command has exited 0 WITHOUT ncu in the calls before (gpurun_out/r2_bench_n1c.log).
-mkdir -p gpurun_out
+# ncu evidence for profiles/: launch lists (shares) and one full capture of the dominant kernel per workload, summarised ON
+# the box (gpurun copies at most 64 MiB back).  Each command has exited 0 WITHOUT ncu before (gpurun_out/r2_bench_n1c.log).
+mkdir -p gpurun_out /tmp/reps
 B="python bench.py --steps 2 --warmup 3 --no-cpu --no-extra"
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_launches_cfg2.csv $B > /dev/null 2>&1
 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/r2_launches_cfg5.csv $B --workload cfg5 > /dev/null 2>&1
-ncu --set full --clock-control none --import-source on -k regex:trace_kernel --launch-skip 3 --launch-count 1 -o gpurun_out/r2_cfg2_final -f $B > gpurun_out/ncu_c2.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:trace_kernel --launch-skip 3 --launch-count 1 -o gpurun_out/r2_cfg5_final -f $B --workload cfg5 > gpurun_out/ncu_c5.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:trace_kernel --launch-skip 3 --launch-count 1 -o gpurun_out/r2_cfg5any_final -f $B --workload cfg5 --any > gpurun_out/ncu_c5a.log 2>&1
-ncu --set full --clock-control none --import-source on -k regex:trace_kernel --launch-skip 3 --launch-count 1 -o gpurun_out/r2_cfg3_final -f $B --workload cfg3 > gpurun_out/ncu_c3.log 2>&1
-ls -la gpurun_out/*final*.ncu-rep gpurun_out/r2_launches*.csv
+cap() { name=$1; shift; ncu --set full --clock-control none --import-source on -k regex:trace_kernel --launch-skip 3 --launch-count 1 -o /tmp/reps/$name -f $B "$@" > gpurun_out/ncu_$name.log 2>&1
+  python tools/ncu_summary.py raw /tmp/reps/$name.ncu-rep > gpurun_out/${name}_raw.txt 2>&1
+  python tools/ncu_groups.py /tmp/reps/$name.ncu-rep > gpurun_out/${name}_regions.txt 2>&1
+  python tools/ncu_opcodes.py /tmp/reps/$name.ncu-rep 28 > gpurun_out/${name}_opcodes.txt 2>&1
+  ncu -i /tmp/reps/$name.ncu-rep --page raw --csv 2>/dev/null | python -c "
+import csv,sys
+r=list(csv.reader(sys.stdin)); h,u,row=r[0],r[1],r[2]
+for i,n in enumerate(h):
+    if n.startswith('sm__inst_executed_pipe') and n.endswith('avg.pct_of_peak_sustained_active'): print(n, row[i])
+" > gpurun_out/${name}_pipes.txt; }
+cap r2_cfg2_final
+cap r2_cfg5_final --workload cfg5
+cap r2_cfg5any_final --workload cfg5 --any
+cap r2_cfg3_final --workload cfg3
+cp /tmp/reps/r2_cfg2_final.ncu-rep /tmp/reps/r2_cfg5_final.ncu-rep gpurun_out/
+ls -la gpurun_out/

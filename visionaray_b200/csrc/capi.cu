@@ -191,6 +191,7 @@ int run_query(bool any, const vsb_scene* const* scenes, int n_scenes, const vsb_
         prog.rays = d_rays; prog.max_t_per_ray = d_mt; prog.max_t = max_t; prog.hits = d_hits; prog.any = any ? 1 : 0;
         vsb::TraceLaunch tl;
         tl.scenes = g.d_scenes; tl.n_scenes = n_scenes; tl.n_items = (unsigned long long)n_range;
+        tl.wide0 = scenes[0]->dev.wide;
         tl.work_counter = counter; tl.ray_count = nullptr;
         tl.service_min = g_query_service_min; tl.phase_min = g_phase_min;
         {
@@ -593,6 +594,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     if (exact && !exact_supported(scenes, n_scenes)) return VSB_ERR_UNSUPPORTED;
     vsb::TraceLaunch tl;
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
+    tl.wide0 = scenes[0]->dev.wide;
     tl.chunk = VSB_FRAME_CHUNK; tl.ray_count = fl.ray_count;
     tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel == VSB_KERNEL_PATHTRACING ? 16 : 32);
     tl.phase_min = g_phase_min;

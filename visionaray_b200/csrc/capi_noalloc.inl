@@ -115,6 +115,7 @@ extern "C" int vsb_closest_hit_static(const vsb_scene* scene, const vsb_ray* ray
     prog.rays = d_rays; prog.max_t_per_ray = nullptr; prog.max_t = max_t; prog.hits = reinterpret_cast<uint4*>(hits); prog.any = 0;
     vsb::TraceLaunch tl;
     tl.scenes = table; tl.n_scenes = 1; tl.n_items = (unsigned long long)n_rays;
+    tl.wide0 = scene->dev.wide;
     tl.work_counter = counter; tl.ray_count = nullptr;
     tl.service_min = g_query_service_min; tl.phase_min = g_phase_min;
     {

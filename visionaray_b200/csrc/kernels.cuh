@@ -142,6 +142,9 @@ struct TraceLaunch
     int service_min;                      // lanes that must be idle before continuations / refill run
     int phase_min;                        // phase vote threshold (phase_runs)
     int drain_min, pend_min;              // trace_kernel_q: pairs that trigger a drain; lanes waiting on their pairs that force one
+    WideScene wide0;                      // trace_kernel_q (one bvh per launch): scenes[0].wide BY VALUE, i.e. in the constant bank --
+                                          // as a copy read from the scene table it was spilled, and an LDL.64 of the node
+                                          // array's base sat in front of every node load (profiles/r2_sass_trace_kernels.txt)
 };
 
 #define VSB_BLOCK 128
@@ -341,7 +344,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
     RayCtx rc; rc.ox = rc.oy = rc.oz = rc.dx = rc.dy = rc.dz = 0.0f; rc.ix = rc.iy = rc.iz = 0.0f; rc.octinv4 = 0u;
     float limit = 0.0f;
     bool any = false, live = false;                       // live: max_t > 0 (a ray with max_t <= 0 cannot hit and is not traced)
-    const WideScene sc = tl.scenes[0].wide;
+    const WideScene& sc = tl.wide0;
     const int n16 = wide_rec_words16(sc.prim_kind);
     TravSpill spill;
     TravState t; trav_begin(t);
