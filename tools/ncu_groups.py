@@ -47,7 +47,7 @@ def region(fn, ln, src):
         for start,n in _FN:
             if start<=ln: name=n
         return _KIND.get(name,"trav_step control")
-    if fn=="bvh8.cuh": return "node_test"
+    if fn in ("bvh8.cuh","cuda_fp16.hpp"): return "node_test"      # cuda_fp16.hpp: the half2 -> float conversions of the plane bytes
     if fn=="vsb_common.cuh": return "isect_triangle / rn arithmetic (vsb_common.cuh)"
     if fn=="kernels.cuh": return _kernel_region(ln)
     if fn=="shade.cuh": return "shade programs"
