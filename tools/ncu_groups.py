@@ -25,7 +25,7 @@ def _kernel_markers():
     """regions of trace_kernel_q (kernels.cuh) by the marker comments of its loop"""
     path=os.path.join(os.path.dirname(os.path.abspath(__file__)),"..","visionaray_b200","csrc","kernels.cuh")
     marks=[("auto drain = ","queue: drain (pair fetch, ray from shared, key merge)"),("// ---- continuations of finished rays","kernel loop (service, refill, program)"),
-           ("// ---- node phase","queue: node phase control"),("// ---- append the selected","queue: append + drain decision"),
+           ("// ---- node phase","queue: node phase control"),("// ---- append the selected","queue: append + drain decision"),("// ---- append one GROUP","queue: append + drain decision"),
            ("if (drained && (state","queue: limit refresh / state"),("if (tl.ray_count)","kernel loop (service, refill, program)")]
     out=[]; inq=False
     for i,l in enumerate(open(path),1):

@@ -312,9 +312,6 @@ trace_kernel(const TraceLaunch tl, const __grid_constant__ Program prog)
 #ifndef VSB_QCAP
 #define VSB_QCAP 128              // pairs per warp ring (power of two, >= 64: a full ring always drains 32); 128 measured +2 % on cfg2 over 64
 #endif
-#ifndef VSB_GROUP_RING
-#define VSB_GROUP_RING 0          // 1: ring of (first record, mask, owner) groups expanded at drain time (see trace_kernel_q)
-#endif
 #define LANE_PENDING 4
 #define VSB_KEY_NONE 0xffffffffu
 
@@ -355,73 +352,73 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
     t.sstack = (uint32_t)__cvta_generic_to_shared(lane_store_raw + threadIdx.x);
     RayReq req;
 
-#if VSB_GROUP_RING
-    // GROUP ring: one entry per (lane, node visit) = (first record, primitive mask, owner); a drain takes the leading
+    // Program::GROUP_RING (the AO and path-tracing frame programs; measured +4.8 % cfg3, +3 % cfg4, -1 % cfg2, -2 % cfg5 any-hit):
+    // one entry per (lane, node visit) = (first record, primitive mask, owner); a drain takes the leading
     // groups that hold <= 32 pairs together and expands them to one pair per lane cooperatively
     uint4* const gring = reinterpret_cast<uint4*>(ring);           // VSB_QCAP / 2 groups of 16 bytes in the same 1 KiB per warp
     unsigned q_pairs = 0u;                                         // warp-uniform: pairs in the ring
     auto drain = [&]()
     {
-        const unsigned avail = q_tail - q_head;
-        uint4 e = make_uint4(0u, 0u, 0u, 0u);
-        if (lane < avail) e = gring[(q_head + lane) & (VSB_QCAP / 2 - 1u)];
-        const int c = __popc(e.y);
-        int incl = c;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1)
+        if constexpr (Program::GROUP_RING)
         {
-            const int v = __shfl_up_sync(0xffffffffu, incl, o);
-            if ((int)lane >= o) incl += v;
-        }
-        const int ntake = __popc(__ballot_sync(0xffffffffu, lane < avail && incl <= 32));     // leading groups (incl is monotone), >= 1
-        const int n = __shfl_sync(0xffffffffu, incl, ntake - 1);
-        const int excl = incl - c;
-        const unsigned word = __reduce_or_sync(0xffffffffu, (int)lane < ntake ? 1u << excl : 0u);   // bit at the first pair of every taken group
-        const int g = __popc(word & (0xffffffffu >> (31u - lane))) - 1;                           // the group lane's pair belongs to
-        const uint32_t gb = __shfl_sync(0xffffffffu, e.x, g), go = __shfl_sync(0xffffffffu, e.z, g);
-        uint32_t gm = __shfl_sync(0xffffffffu, e.y, g);
-        int k = (int)lane - __shfl_sync(0xffffffffu, excl, g);
-        if ((int)lane < n)
-        {
-            while (k-- > 0) gm &= gm - 1u;                       // the k-th set bit of the group's mask
-            const uint32_t rec = gb + (uint32_t)(__ffs((int)gm) - 1);
-            NodeRegs r;
-            load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)rec * (size_t)(n16 * 16), n16, r);
-            const float* o = ray_s + go;
-            float tt;
-            if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
+            const unsigned avail = q_tail - q_head;
+            uint4 e = make_uint4(0u, 0u, 0u, 0u);
+            if (lane < avail) e = gring[(q_head + lane) & (VSB_QCAP / 2 - 1u)];
+            const int c = __popc(e.y);
+            int incl = c;
+    #pragma unroll
+            for (int o = 1; o < 32; o <<= 1)
             {
-                const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | record_list_index(sc.prim_kind, r);
-                if (cand < key_s[go]) atomicMin(key_s + go, cand);
+                const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                if ((int)lane >= o) incl += v;
             }
-        }
-        q_head += (unsigned)ntake;
-        q_pairs -= (unsigned)n;
-        __syncwarp();
-    };
-#else
-    // one batch of up to 32 pairs, one per lane
-    auto drain = [&]()
-    {
-        const unsigned n = q_tail - q_head < 32u ? q_tail - q_head : 32u;
-        if (lane < n)
-        {
-            const uint2 e = ring[(q_head + lane) & (VSB_QCAP - 1u)];
-            NodeRegs r;
-            load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)e.x * (size_t)(n16 * 16), n16, r);
-            const float* o = ray_s + e.y;
-            float tt;
-            if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
+            const int ntake = __popc(__ballot_sync(0xffffffffu, lane < avail && incl <= 32));     // leading groups (incl is monotone), >= 1
+            const int n = __shfl_sync(0xffffffffu, incl, ntake - 1);
+            const int excl = incl - c;
+            const unsigned word = __reduce_or_sync(0xffffffffu, (int)lane < ntake ? 1u << excl : 0u);   // bit at the first pair of every taken group
+            const int g = __popc(word & (0xffffffffu >> (31u - lane))) - 1;                           // the group lane's pair belongs to
+            const uint32_t gb = __shfl_sync(0xffffffffu, e.x, g), go = __shfl_sync(0xffffffffu, e.z, g);
+            uint32_t gm = __shfl_sync(0xffffffffu, e.y, g);
+            int k = (int)lane - __shfl_sync(0xffffffffu, excl, g);
+            if ((int)lane < n)
             {
-                const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | record_list_index(sc.prim_kind, r);
-                if (cand < key_s[e.y]) atomicMin(key_s + e.y, cand);
+                while (k-- > 0) gm &= gm - 1u;                       // the k-th set bit of the group's mask
+                const uint32_t rec = gb + (uint32_t)(__ffs((int)gm) - 1);
+                NodeRegs r;
+                load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)rec * (size_t)(n16 * 16), n16, r);
+                const float* o = ray_s + go;
+                float tt;
+                if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
+                {
+                    const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | record_list_index(sc.prim_kind, r);
+                    if (cand < key_s[go]) atomicMin(key_s + go, cand);
+                }
             }
+            q_head += (unsigned)ntake;
+            q_pairs -= (unsigned)n;
+            __syncwarp();
         }
-        q_head += n;
-        __syncwarp();
+        else
+        {
+            // PAIR ring: one batch of up to 32 (record, owner) pairs, one per lane
+            const unsigned n = q_tail - q_head < 32u ? q_tail - q_head : 32u;
+            if (lane < n)
+            {
+                const uint2 e = ring[(q_head + lane) & (VSB_QCAP - 1u)];
+                NodeRegs r;
+                load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)e.x * (size_t)(n16 * 16), n16, r);
+                const float* o = ray_s + e.y;
+                float tt;
+                if (prim_candidate(sc.prim_kind, r, o[0], o[VSB_BLOCK], o[2 * VSB_BLOCK], o[3 * VSB_BLOCK], o[4 * VSB_BLOCK], o[5 * VSB_BLOCK], tt) && tt >= 0.0f)
+                {
+                    const unsigned long long cand = ((unsigned long long)(__float_as_uint(tt) & 0x7fffffffu) << 32) | record_list_index(sc.prim_kind, r);
+                    if (cand < key_s[e.y]) atomicMin(key_s + e.y, cand);
+                }
+            }
+            q_head += n;
+            __syncwarp();
+        }
     };
-
-#endif
 
     for (;;)
     {
@@ -510,78 +507,80 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             }
         }
 
-#if VSB_GROUP_RING
-        // ---- append one GROUP per lane that selected primitives (no per-primitive loop, no scan), drain while worthwhile ----
         bool drained = false;
+        if constexpr (Program::GROUP_RING)
         {
-            const bool mine = state == LANE_TRAVERSING && t.pg_mask != 0u;
-            const unsigned has = __ballot_sync(0xffffffffu, mine);
-            if (has != 0u)
+            // ---- append one GROUP per lane that selected primitives (no per-primitive loop, no scan), drain while worthwhile ----
             {
-                while (q_tail - q_head > VSB_QCAP / 2 - 32u) { drain(); drained = true; }       // room for 32 groups
-                if (mine) gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, 0u);
-                q_pairs += __reduce_add_sync(0xffffffffu, mine ? (unsigned)__popc(t.pg_mask) : 0u);
-                t.pg_mask = 0u;
-                q_tail += (unsigned)__popc(has);
-                __syncwarp();
+                const bool mine = state == LANE_TRAVERSING && t.pg_mask != 0u;
+                const unsigned has = __ballot_sync(0xffffffffu, mine);
+                if (has != 0u)
+                {
+                    while (q_tail - q_head > VSB_QCAP / 2 - 32u) { drain(); drained = true; }       // room for 32 groups
+                    if (mine) gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, 0u);
+                    q_pairs += __reduce_add_sync(0xffffffffu, mine ? (unsigned)__popc(t.pg_mask) : 0u);
+                    t.pg_mask = 0u;
+                    q_tail += (unsigned)__popc(has);
+                    __syncwarp();
+                }
+                if (state == LANE_TRAVERSING && (t.ng_mask >> 24) == 0u) { state = LANE_PENDING; my_seq = q_tail; }
+                while (q_pairs != 0u)
+                {
+                    const unsigned busy = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);
+                    const int n_pend = __popc(__ballot_sync(0xffffffffu, state == LANE_PENDING && (int)(q_head - my_seq) < 0));
+                    if (!(q_pairs >= (unsigned)tl.drain_min || busy == 0u || n_pend >= tl.pend_min)) break;
+                    drain(); drained = true;
+                }
             }
-            if (state == LANE_TRAVERSING && (t.ng_mask >> 24) == 0u) { state = LANE_PENDING; my_seq = q_tail; }
-            while (q_pairs != 0u)
+        }
+        else
+        {
+            // ---- append the selected primitives to the warp's ring, drain while worthwhile (ONE drain site) ----
+            for (;;)
             {
-                const unsigned busy = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);
+                const int c = state == LANE_TRAVERSING ? __popc(t.pg_mask) : 0;
+                const unsigned has = __ballot_sync(0xffffffffu, c != 0);
+                if (has != 0u)
+                {
+                    unsigned off, total;
+                    if (__ballot_sync(0xffffffffu, c > 1) == 0u)
+                    {
+                        off = (unsigned)__popc(has & lt_mask); total = (unsigned)__popc(has);     // one pair per lane: no scan
+                    }
+                    else
+                    {
+                        int incl = c;
+    #pragma unroll
+                        for (int o = 1; o < 32; o <<= 1)
+                        {
+                            const int v = __shfl_up_sync(0xffffffffu, incl, o);
+                            if ((int)lane >= o) incl += v;
+                        }
+                        total = (unsigned)__shfl_sync(0xffffffffu, incl, 31);
+                        off = (unsigned)(incl - c);
+                    }
+                    const unsigned space = VSB_QCAP - (q_tail - q_head);
+                    while (t.pg_mask != 0u && off < space)
+                    {
+                        const int bit = find_msb(t.pg_mask);
+                        t.pg_mask &= ~(1u << bit);
+                        ring[(q_tail + off) & (VSB_QCAP - 1u)] = make_uint2(t.pg_base + (uint32_t)bit, threadIdx.x);
+                        ++off;
+                    }
+                    q_tail += total < space ? total : space;
+                    __syncwarp();
+                }
+                // out of node work and everything appended: wait for the ring's head to pass this lane's last pair
+                if (state == LANE_TRAVERSING && t.pg_mask == 0u && (t.ng_mask >> 24) == 0u) { state = LANE_PENDING; my_seq = q_tail; }
+                const unsigned count = q_tail - q_head;
+                if (count == 0u) break;
+                const unsigned busy = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);                    // node work (or pairs) left
+                const unsigned left = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING && t.pg_mask != 0u); // the ring was full
                 const int n_pend = __popc(__ballot_sync(0xffffffffu, state == LANE_PENDING && (int)(q_head - my_seq) < 0));
-                if (!(q_pairs >= (unsigned)tl.drain_min || busy == 0u || n_pend >= tl.pend_min)) break;
+                if (!(count >= (unsigned)tl.drain_min || left != 0u || busy == 0u || n_pend >= tl.pend_min)) break;
                 drain(); drained = true;
             }
         }
-#else
-        // ---- append the selected primitives to the warp's ring, drain while worthwhile (ONE drain site) ----
-        bool drained = false;
-        for (;;)
-        {
-            const int c = state == LANE_TRAVERSING ? __popc(t.pg_mask) : 0;
-            const unsigned has = __ballot_sync(0xffffffffu, c != 0);
-            if (has != 0u)
-            {
-                unsigned off, total;
-                if (__ballot_sync(0xffffffffu, c > 1) == 0u)
-                {
-                    off = (unsigned)__popc(has & lt_mask); total = (unsigned)__popc(has);     // one pair per lane: no scan
-                }
-                else
-                {
-                    int incl = c;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1)
-                    {
-                        const int v = __shfl_up_sync(0xffffffffu, incl, o);
-                        if ((int)lane >= o) incl += v;
-                    }
-                    total = (unsigned)__shfl_sync(0xffffffffu, incl, 31);
-                    off = (unsigned)(incl - c);
-                }
-                const unsigned space = VSB_QCAP - (q_tail - q_head);
-                while (t.pg_mask != 0u && off < space)
-                {
-                    const int bit = find_msb(t.pg_mask);
-                    t.pg_mask &= ~(1u << bit);
-                    ring[(q_tail + off) & (VSB_QCAP - 1u)] = make_uint2(t.pg_base + (uint32_t)bit, threadIdx.x);
-                    ++off;
-                }
-                q_tail += total < space ? total : space;
-                __syncwarp();
-            }
-            // out of node work and everything appended: wait for the ring's head to pass this lane's last pair
-            if (state == LANE_TRAVERSING && t.pg_mask == 0u && (t.ng_mask >> 24) == 0u) { state = LANE_PENDING; my_seq = q_tail; }
-            const unsigned count = q_tail - q_head;
-            if (count == 0u) break;
-            const unsigned busy = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING);                    // node work (or pairs) left
-            const unsigned left = __ballot_sync(0xffffffffu, state == LANE_TRAVERSING && t.pg_mask != 0u); // the ring was full
-            const int n_pend = __popc(__ballot_sync(0xffffffffu, state == LANE_PENDING && (int)(q_head - my_seq) < 0));
-            if (!(count >= (unsigned)tl.drain_min || left != 0u || busy == 0u || n_pend >= tl.pend_min)) break;
-            drain(); drained = true;
-        }
-#endif
         if (drained && (state == LANE_TRAVERSING || state == LANE_PENDING))
         {
             const unsigned long long k = key_s[threadIdx.x];
@@ -666,6 +665,7 @@ struct RayListProgram
 #define VSB_LIST_MIN_BLOCKS_Q 8     // 64 registers, 32 warps per SM: measured +2 % on the incoherent ray lists (frames: 6 is better)
 #endif
     static constexpr int MIN_BLOCKS_Q = VSB_LIST_MIN_BLOCKS_Q;
+    static constexpr bool GROUP_RING = false;     // pair ring: closest-hit +1 % with groups, any-hit -2 %
 
     __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
     {
