@@ -102,24 +102,39 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
     VSB_BUILD_CUDA(cudaGetLastError());
     VSB_BUILD_CUDA(cudaEventRecord(ev[1], st));
 
-    // 3. PLOC iterations
+    // 3. PLOC iterations, state on the device (build_ploc.cuh), one host sync per chunk of iterations
+    const int MAX_ITERS = 1024, CHUNK = 8;
+    uint32_t* d_state = nullptr;
+    VSB_BUILD_CUDA(scratch.alloc(&d_state, (size_t)2 * (MAX_ITERS + CHUNK + 1)));
+    {
+        const uint32_t init2[2] = { n, 0u };
+        VSB_BUILD_CUDA(cudaMemcpyAsync(d_state, init2, sizeof(init2), cudaMemcpyHostToDevice, st));
+    }
     uint32_t m = n, merged = 0; int cur = 0, iters = 0;
     while (m > 1)
     {
-        const uint32_t b = (m + VSB_PLOC_BLOCK - 1) / VSB_PLOC_BLOCK;
-        vsb::ploc_nn_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_cl[cur], m, bp.radius, d_nn);
-        vsb::ploc_flags_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_nn, m, d_flags);
-        tb = tmp_bytes;
-        VSB_BUILD_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_flags, d_scan, (int)m, st));
-        vsb::ploc_emit_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_cl[cur], d_nn, d_scan, m, n, merged, bp, d_bn, d_sub, d_parent,
-                                                            d_cl[cur ^ 1], d_small + 8);
-        g.launches += 4;
-        uint32_t totals[2] = { 0, 0 };
-        VSB_BUILD_CUDA(cudaMemcpyAsync(totals, d_small + 8, sizeof(totals), cudaMemcpyDeviceToHost, st));
+        if (iters + CHUNK > MAX_ITERS) return fail(VSB_ERR_BAD_TREE);
+        const uint32_t b = (m + VSB_PLOC_BLOCK - 1) / VSB_PLOC_BLOCK;            // m only shrinks within the chunk
+        for (int k = 0; k < CHUNK; ++k)
+        {
+            uint32_t* stt = d_state + 2 * (size_t)(iters + k);
+            vsb::ploc_nn_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_cl[cur], stt, bp.radius, d_nn);
+            vsb::ploc_flags_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_nn, stt, d_flags);
+            tb = tmp_bytes;
+            VSB_BUILD_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_flags, d_scan, (int)m, st));   // entries beyond the live count are never read
+            vsb::ploc_emit_kernel<<<b, VSB_PLOC_BLOCK, 0, st>>>(d_cl[cur], d_nn, d_scan, stt, n, bp, d_bn, d_sub, d_parent, d_cl[cur ^ 1]);
+            g.launches += 4;
+            cur ^= 1;
+        }
+        std::vector<uint32_t> hist(2 * (CHUNK + 1));
+        VSB_BUILD_CUDA(cudaMemcpyAsync(hist.data(), d_state + 2 * (size_t)iters, hist.size() * sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
         VSB_BUILD_CUDA(cudaStreamSynchronize(st));
-        if (totals[1] == 0 || totals[0] != m - totals[1]) return fail(VSB_ERR_BAD_TREE);   // no progress: cannot happen (see ploc_nearest)
-        m = totals[0]; merged += totals[1];
-        cur ^= 1; ++iters;
+        for (int k = 0; k < CHUNK && m > 1; ++k)
+        {
+            const uint32_t m1 = hist[2 * (k + 1)], g1 = hist[2 * (k + 1) + 1];
+            if (g1 == merged || m1 != m - (g1 - merged)) return fail(VSB_ERR_BAD_TREE);   // no progress: cannot happen (see ploc_nearest)
+            m = m1; merged = g1; ++iters;
+        }
     }
     if (merged != n - 1) return fail(VSB_ERR_BAD_TREE);
     VSB_BUILD_CUDA(cudaEventRecord(ev[2], st));
@@ -137,17 +152,34 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
         vsb::BTask t; t.node = root; t.out = 0; t.prim_off = 0; t.rank_off = 0;
         VSB_BUILD_CUDA(cudaMemcpyAsync(d_tasks[0], &t, sizeof(t), cudaMemcpyHostToDevice, st));
     }
+    // task counts per level live on the device; levels are launched in chunks with grids sized for the bound
+    // "tasks double per level" and synced once per chunk
+    const int MAX_LEVELS = 4096, LCHUNK = 8;
+    uint32_t* d_lcount = nullptr;
+    VSB_BUILD_CUDA(scratch.alloc(&d_lcount, (size_t)MAX_LEVELS + LCHUNK + 2));
+    VSB_BUILD_CUDA(cudaMemsetAsync(d_lcount, 0, ((size_t)MAX_LEVELS + LCHUNK + 2) * sizeof(uint32_t), st));
+    {
+        const uint32_t one = 1u;
+        VSB_BUILD_CUDA(cudaMemcpyAsync(d_lcount, &one, sizeof(one), cudaMemcpyHostToDevice, st));
+    }
     uint32_t n_tasks = 1; int levels = 0; cur = 0;
     while (n_tasks > 0)
     {
-        VSB_BUILD_CUDA(cudaMemsetAsync(d_small + 12, 0, sizeof(uint32_t), st));
-        vsb::layout_level_kernel<<<(n_tasks + 127) / 128, 128, 0, st>>>(d_tasks[cur], n_tasks, d_bn, d_sub, s->d_nodes2, s->d_indices,
-                                                                        d_tasks[cur ^ 1], d_small + 12);
-        ++g.launches;
-        VSB_BUILD_CUDA(cudaMemcpyAsync(&n_tasks, d_small + 12, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+        if (levels + LCHUNK > MAX_LEVELS) return fail(VSB_ERR_BAD_TREE);
+        unsigned long long bound = n_tasks;
+        for (int k = 0; k < LCHUNK; ++k)
+        {
+            const uint32_t nb = (uint32_t)(bound < (unsigned long long)n ? bound : (unsigned long long)n);
+            vsb::layout_level_kernel<<<(nb + 127) / 128, 128, 0, st>>>(d_tasks[cur], d_lcount + levels + k, d_bn, d_sub, s->d_nodes2, s->d_indices,
+                                                                    d_tasks[cur ^ 1]);
+            ++g.launches;
+            cur ^= 1;
+            bound *= 2;
+        }
+        uint32_t cnt[LCHUNK + 1];
+        VSB_BUILD_CUDA(cudaMemcpyAsync(cnt, d_lcount + levels, sizeof(cnt), cudaMemcpyDeviceToHost, st));
         VSB_BUILD_CUDA(cudaStreamSynchronize(st));
-        cur ^= 1; ++levels;
-        if (levels > 4096) return fail(VSB_ERR_BAD_TREE);
+        for (int k = 0; k < LCHUNK && n_tasks > 0; ++k) { n_tasks = cnt[k + 1]; ++levels; }
     }
     s->depth2 = (root_sub.cnt & BS_LEAF) ? 1 : levels + 1;
     {
