@@ -84,7 +84,7 @@ typedef struct vsb_material {
     float ca[3]; float ka;
     float cd[3]; float kd;
     float cs[3]; float ks;
-    float spec_exp; int32_t kind;   /* VSB_MAT_PLASTIC | VSB_MAT_MATTE */
+    float spec_exp; int32_t kind;   /* VSB_MAT_PLASTIC | MATTE | EMISSIVE | MIRROR (the last two need generic_materials) */
     float pad[2];
 } vsb_material;
 

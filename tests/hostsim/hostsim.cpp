@@ -119,6 +119,37 @@ void hs_query_wide(void* h, int any, const void* rays, size_t n_rays, float max_
     }
 }
 
+// Work counters of closest_hit on the BVH8 (tools/tree_stats.py): per ray, node visits, leaf groups entered
+// (one ring entry of the group ring / one append batch), primitive tests, and the deepest stack
+void hs_count_wide(void* h, const void* rays, size_t n_rays, uint64_t* out4)
+{
+    auto* w = reinterpret_cast<HostWide*>(h);
+    WideScene s{ w->nodes.data(), w->prims.data(), w->prim_kind };
+    const Ray32* r = reinterpret_cast<const Ray32*>(rays);
+    uint64_t visits = 0, groups = 0, tests = 0, deepest = 0;
+    for (size_t i = 0; i < n_rays; ++i)
+    {
+        RayCtx rc;
+        ray_ctx_init(rc, r[i].ox, r[i].oy, r[i].oz, r[i].dx, r[i].dy, r[i].dz);
+        HitReg best; hit_reset(best);
+        float limit = 3.4028234663852886e38f;
+        TravSpill spill; TravState t; t.spill = &spill;
+        trav_begin(t);
+        for (;;)
+        {
+            const bool prim_mode = trav_prim_mode(t);
+            const uint32_t before = t.pg_mask;
+            if (prim_mode) tests += 1; else visits += 1;
+            const bool more = trav_step(s, rc, t, best, limit, false);
+            if (!prim_mode && t.pg_mask) groups += 1;
+            (void)before;
+            if ((uint64_t)t.sp > deepest) deepest = (uint64_t)t.sp;
+            if (!more) break;
+        }
+    }
+    out4[0] = visits; out4[1] = groups; out4[2] = tests; out4[3] = deepest;
+}
+
 // VSB_TRAVERSE_WATERTIGHT (csrc/watertight.cuh), host instantiation
 void hs_query_watertight(void* h, int any, const void* rays, size_t n_rays, float max_t, void* hits)
 {

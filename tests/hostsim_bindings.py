@@ -31,6 +31,7 @@ def lib():
         l.hs_prims.argtypes = [vp]
         l.hs_query_wide.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp, vp]
         l.hs_query_watertight.argtypes = [vp, C.c_int, vp, sz, C.c_float, vp]
+        l.hs_count_wide.argtypes = [vp, vp, sz, C.POINTER(C.c_uint64)]
         l.hs_query_exact.argtypes = [C.c_int, C.c_int, vp, vp, vp, vp, sz, C.c_float, vp, vp]
         l.hs_multi_hit_wide.argtypes = [vp, vp, sz, C.c_int, vp]
         l.hs_multi_hit_exact.argtypes = [C.c_int, vp, vp, vp, vp, sz, C.c_int, vp]
@@ -71,6 +72,13 @@ class HostWide:
         hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
         lib().hs_query_wide(self.h, int(any_hit), _p(rays), rays.shape[0], max_t, _p(max_t_per_ray), _p(hits))
         return hits
+
+    def work_counters(self, rays):
+        """Per-ray averages of closest_hit's work on this BVH8: node visits, leaf groups entered, primitive tests."""
+        out = (C.c_uint64 * 4)()
+        lib().hs_count_wide(self.h, _p(rays), rays.shape[0], out)
+        n = float(rays.shape[0])
+        return dict(node_visits=out[0] / n, leaf_groups=out[1] / n, prim_tests=out[2] / n, deepest_stack=int(out[3]))
 
     def multi_hit(self, rays, max_hits):
         hits = np.zeros((rays.shape[0], max_hits), dtype=HIT_DTYPE)

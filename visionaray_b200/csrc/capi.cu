@@ -15,6 +15,7 @@
 #include "../../include/vsnray_b200.h"
 #include "kernels.cuh"
 #include "build_ploc.cuh"
+#include "build_sah.cuh"
 #include "multi_hit.cuh"
 #include "watertight.cuh"
 
@@ -285,6 +286,7 @@ extern "C" int vsb_tune(const char* key, int value)
     else if (!std::strcmp(key, "band_min_mib")) g_band_min_mib = value;
     else if (!std::strcmp(key, "list_piece_krays")) g_list_piece_krays = value;
     else if (!std::strcmp(key, "optimal_collapse")) g_optimal_collapse = value;
+    else if (!std::strcmp(key, "build_algorithm")) { if (value != 0 && value != 1) return VSB_ERR_BAD_ARG; g_build_algorithm = value; }
     else if (!std::strcmp(key, "build_radius")) g_build_radius = value;
     else if (!std::strcmp(key, "build_cost_node_x100")) g_build_cost_node = 0.01f * (float)value;
     else if (!std::strcmp(key, "build_cost_prim_x100")) g_build_cost_prim = 0.01f * (float)value;

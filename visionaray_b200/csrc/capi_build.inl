@@ -9,11 +9,12 @@ float g_build_cost_node = 1.0f;    // vsb_tune("build_cost_node_x100", ...)
 float g_build_cost_prim = 1.0f;    // vsb_tune("build_cost_prim_x100", ...)
 float g_last_build_ms[4] = { 0, 0, 0, 0 };   // total, sort + setup, PLOC, layout + wide re-encode
 int   g_last_build_iters = 0;
+int   g_build_algorithm = 0;       // vsb_tune("build_algorithm", 0 = Morton + PLOC, 1 = the reference's binned SAH, level by level)
 
 // scratch from the stream-ordered pool (vsb_init keeps it cached between builds)
 struct BuildScratch
 {
-    void* p[16] = {};
+    void* p[40] = {};
     int n = 0;
     cudaStream_t st = nullptr;
     ~BuildScratch() { for (int i = 0; i < n; ++i) if (p[i]) cudaFreeAsync(p[i], st); }
@@ -27,6 +28,8 @@ struct BuildScratch
 };
 
 } // namespace
+
+#include "capi_build_sah.inl"
 
 extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims, int mem, vsb_scene** out)
 {
@@ -57,6 +60,23 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
     bp.radius = g_build_radius < 1 ? 1 : (g_build_radius > VSB_BUILD_MAX_RADIUS ? VSB_BUILD_MAX_RADIUS : g_build_radius);
     bp.cost_node = g_build_cost_node; bp.cost_prim = g_build_cost_prim;
 
+    int iters = 0;
+    if (g_build_algorithm == 1)
+    {
+        // the reference's own tree (build_sah.cuh)
+        VSB_BUILD_CUDA(cudaEventRecord(ev[0], st));
+        int levels = 0;
+        const int brc = build_tree_sah(s, prim_kind, n, st, scratch, ev, levels);
+        if (brc != VSB_OK) return fail(brc);
+        iters = levels;
+        s->depth2 = levels + 1;
+        vsb::Node32 r;
+        VSB_BUILD_CUDA(cudaMemcpyAsync(&r, s->d_nodes2, sizeof(r), cudaMemcpyDeviceToHost, st));
+        VSB_BUILD_CUDA(cudaStreamSynchronize(st));
+        s->lo[0] = r.min_x; s->lo[1] = r.min_y; s->lo[2] = r.min_z; s->hi[0] = r.max_x; s->hi[1] = r.max_y; s->hi[2] = r.max_z;
+    }
+    else
+    {
     const size_t n_bn = 2 * (size_t)n - 1;
     vsb::BNode *d_bn = nullptr, *d_cl[2] = { nullptr, nullptr };
     vsb::BSub* d_sub = nullptr;
@@ -110,7 +130,7 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
         const uint32_t init2[2] = { n, 0u };
         VSB_BUILD_CUDA(cudaMemcpyAsync(d_state, init2, sizeof(init2), cudaMemcpyHostToDevice, st));
     }
-    uint32_t m = n, merged = 0; int cur = 0, iters = 0;
+    uint32_t m = n, merged = 0; int cur = 0;
     while (m > 1)
     {
         if (iters + CHUNK > MAX_ITERS) return fail(VSB_ERR_BAD_TREE);
@@ -187,10 +207,11 @@ extern "C" int vsb_scene_build(int prim_kind, const void* prims, size_t n_prims,
         VSB_BUILD_CUDA(cudaMemcpy(&r, s->d_nodes2, sizeof(r), cudaMemcpyDeviceToHost));
         s->lo[0] = r.min_x; s->lo[1] = r.min_y; s->lo[2] = r.min_z; s->hi[0] = r.max_x; s->hi[1] = r.max_y; s->hi[2] = r.max_z;
     }
+    }
 #undef VSB_BUILD_CUDA
 
     // 5. the same BVH2 -> BVH8 re-encode as for a host-built tree (leaves already hold <= 4 primitives)
-    rc = encode_wide(s, s->d_nodes2, n_nodes, n_prims);
+    rc = encode_wide(s, s->d_nodes2, s->n_nodes2, n_prims);
     if (rc != VSB_OK) return fail(rc);
     cudaEventRecord(ev[3], st);
     cudaEventSynchronize(ev[3]);
