@@ -20,15 +20,16 @@ closest_hit/any_hit traversal + shading + store).  Default workload = BASELINE.j
   cpu_baseline  the reference's own tiled_sched<simd::ray8> (oracle/_ref, unmodified headers) on the
             host cores, on the SAME frame as the GPU arm
   extra     (N = 1, default run) the incoherent workloads measured the same way: cfg5 closest / any, cfg3;
-            gpu_built_tree: cfg2 and cfg5 on the tree of the GPU builder, with build time and time to first frame;
+            ploc_tree: cfg2 and cfg5 on the tree of the second GPU builder (Morton + PLOC), with build time and time to first frame;
             naive_gpu: the same frame by the reference's own cuda_sched kernel on this GPU (unmodified headers)
   strong    (N > 1) the fixed 4096^2 frame partitioned over the N GPUs: cfg2 and cfg4 (progressive path tracer), tiles
             stored into rank 0's frame over NVLink from inside the trace kernel, with v_N / (N v_1)
 
 N > 1 (torchrun): the frame is partitioned into interleaved 64x64 tiles (tile k -> rank k % N), the
 scene is replicated.  Headline = weak scaling: the same view at sqrt(N) x the resolution per axis
-(4096^2 pixels per GPU).  The tree is the reference's binned-SAH tree (host builder) re-encoded on the GPU, as BASELINE's
-configs say; --builder gpu builds it on the GPU instead (extra.gpu_built_tree measures that in the default run).
+(4096^2 pixels per GPU).  The tree is the reference's binned-SAH tree re-encoded on the GPU as a BVH8, as BASELINE's
+configs say; by default it is BUILT on the GPU too (vsb_scene_build, the host builder's tree node for node; --builder reference
+uses the host builder, extra.ploc_tree measures the Morton + PLOC builder beside it).
 """
 from __future__ import annotations
 
@@ -296,21 +297,26 @@ def run_reference_raylist(args, O, S, cores):
 # GPU arm: scene preparation and the context every leg shares
 # ------------------------------------------------------------------------------------------------
 
+GPU_BUILDERS = {"gpu": (1, "reference binned SAH, built breadth-first on the GPU (vsb_scene_build, build_sah.cuh): the host builder's tree node for node"),
+                "gpu_ploc": (0, "gpu (Morton sort + PLOC + SAH leaf collapse)")}
+
+
 def prepare_scene(api, S, scene_name: str, scale: float, builder: str):
     """-> (host scene, device scene, builder info incl. time to a traceable scene).
-    --builder gpu (default): primitives only on the host, the tree is built on the GPU (vsb_scene_build:
-    Morton sort + PLOC + SAH leaf collapse + BVH8 re-encode).  --builder reference: the reference's binned-SAH
-    tree from the host builder (tie-order parity anchor), uploaded and re-encoded."""
+    --builder gpu (default): primitives only on the host; vsb_scene_build builds the REFERENCE's binned-SAH tree on the
+    GPU (the same nodes and indices as the host builder: tests/test_gpu_sah_builder.py) and re-encodes it as a BVH8.
+    --builder reference: the same tree from the host builder, uploaded and re-encoded.  --builder gpu_ploc: the
+    Morton + PLOC tree (faster to build at >= 5 M primitives, traces ~10 % slower)."""
     t0 = time.perf_counter()
     sc = S.make_scene(scene_name, scale, build_tree=(builder == "reference"))
     gen_s = time.perf_counter() - t0
     t0 = time.perf_counter()
-    if builder == "gpu":
+    if builder in GPU_BUILDERS:
+        api.tune("build_algorithm", GPU_BUILDERS[builder][0])
         dev = api.Scene.build(sc.prim_kind, sc.prims, sc.normals)
         api.sync()
         ms = api.last_build_ms()
-        info = {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2),
-                "iterations": ms["iterations"]}
+        info = {"kind": GPU_BUILDERS[builder][1], "build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"]}
     else:
         dev = api.Scene(sc)
         api.sync()
@@ -736,7 +742,7 @@ def frame_roofline(O, S, osc, wl, rig_out: dict, traffic_key):
 def extra_legs(ctx: Ctx, O, args, cfg2_prims):
     """N = 1, default run: the incoherent workloads in the same record, measured like the headline (short legs), on the
     reference's binned-SAH tree (BASELINE configs / north_star: "re-encoded on the GPU from the reference's binned-SAH
-    tree"); and what the GPU builder (vsb_scene_build) gives instead: the same workloads on its tree, with the build time."""
+    tree"; built by --builder); and the second GPU builder (Morton + PLOC) beside it: build time and traced rate."""
     S, api = ctx.S, ctx.api
     out = {}
     steps, warmup = 5, 3
@@ -749,38 +755,42 @@ def extra_legs(ctx: Ctx, O, args, cfg2_prims):
                 "config": raylist_config(osc.n_prims, any_hit, n_batch, 1.0),
                 "roofline": raylist_roofline(O, osc, r["sample_rays"], any_hit, n_batch, r["kernel_ms"], key)}
 
-    sc, dev, info = prepare_scene(api, S, "cfg5_soup", 1.0, "reference")
-    out["cfg5_closest"] = raylist(dev, sc, False, info, "cfg5_closest")
-    out["cfg5_any"] = raylist(dev, sc, True, info, "cfg5_any")
+    sc, dev, info = prepare_scene(api, S, "cfg5_soup", 1.0, args.builder)
+    osc = oracle_scene(S, sc, dev)
+    out["cfg5_closest"] = raylist(dev, osc, False, info, "cfg5_closest")
+    out["cfg5_any"] = raylist(dev, osc, True, info, "cfg5_any")
     dev.close()
-    gpu_tree = {}
+    del osc
+    ploc = {}
     t0 = time.perf_counter()
+    api.tune("build_algorithm", 0)
     dev = api.Scene.build(sc.prim_kind, sc.prims, None)
     api.sync()
     ms = api.last_build_ms()
-    binfo = {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"],
-             "upload_and_build_s": round(time.perf_counter() - t0, 3), "host_builder_s": info["scene_generation_s"]}
+    binfo = {"kind": GPU_BUILDERS["gpu_ploc"][1], "build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"],
+             "upload_and_build_s": round(time.perf_counter() - t0, 3)}
     r = time_raylist(ctx, dev, False, n_batch, steps, warmup, clocks=False, e2e=False)
-    gpu_tree["cfg5_closest"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "builder": binfo,
-                                "vs_reference_tree": r["value"] / out["cfg5_closest"]["value"]}
+    ploc["cfg5_closest"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "builder": binfo,
+                            "vs_headline_tree": r["value"] / out["cfg5_closest"]["value"]}
     dev.close()
     del sc
 
     wl = WORKLOADS["cfg3"]
-    sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, "reference")
+    sc, dev, info = prepare_scene(api, S, wl["scene"], 1.0, args.builder)
     rig = FrameRig(ctx, wl, dev, wl["w"], wl["h"], "single")
     r = time_rig(ctx, rig, steps, warmup, clocks=False)
     out["cfg3"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"], "ms_per_step": r["ms_per_step"],
                    "steps": steps, "warmup": warmup, "rays_per_step": r["rays_per_step"], "builder": info,
                    "config": workload_config(wl, wl["w"], wl["h"], 1.0, sc.n_prims),
-                   "roofline": frame_roofline(O, S, sc, wl, r, "cfg3")}
+                   "roofline": frame_roofline(O, S, oracle_scene(S, sc, dev), wl, r, "cfg3")}
     rig.close()
     dev.close()
     del sc
 
-    # the headline frame on the GPU-built tree: generate -> build -> first frame, then the same timing
+    # the headline frame on the PLOC tree: primitives -> build -> first frame, then the same timing
     wl = WORKLOADS["cfg2"]
     t0 = time.perf_counter()
+    api.tune("build_algorithm", 0)
     dev = api.Scene.build(0, cfg2_prims, S.face_normals(cfg2_prims))
     api.sync()
     ms = api.last_build_ms()
@@ -789,12 +799,13 @@ def extra_legs(ctx: Ctx, O, args, cfg2_prims):
     ctx.torch.cuda.synchronize()
     first = time.perf_counter() - t0
     r = time_rig(ctx, rig, steps, warmup, clocks=False)
-    gpu_tree["cfg2"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"],
-                        "builder": {"kind": "gpu (Morton sort + PLOC + SAH leaf collapse)", "build_ms": round(ms["total_ms"], 2),
-                                    "iterations": ms["iterations"], "primitives_to_first_frame_s": round(first, 3)}}
+    ploc["cfg2"] = {"value": r["value"], "unit": "Mrays/s", "kernel_ms": r["kernel_ms"],
+                    "builder": {"kind": GPU_BUILDERS["gpu_ploc"][1], "build_ms": round(ms["total_ms"], 2),
+                                "iterations": ms["iterations"], "primitives_to_first_frame_s": round(first, 3)}}
     rig.close()
     dev.close()
-    out["gpu_built_tree"] = gpu_tree
+    api.tune("build_algorithm", 1)
+    out["ploc_tree"] = ploc
 
     # the same frame by the REFERENCE'S OWN CUDA path on this GPU: cuda_sched<ray>::frame() + whitted::kernel over a
     # cuda_index_bvh, unmodified headers compiled for sm_100a (oracle/refcuda; none of this repository's kernels)
@@ -925,8 +936,7 @@ def run_gpu(args):
     if ctx.world == 1 and not args.no_extra and args.workload == "cfg2" and args.scale == 1.0:
         from oracle import bindings as O
         line["extra"] = extra_legs(ctx, O, args, sc.prims)
-        line["extra"]["gpu_built_tree"]["cfg2"]["vs_reference_tree"] = line["extra"]["gpu_built_tree"]["cfg2"]["value"] / line["value"] \
-            if args.builder == "reference" else None
+        line["extra"]["ploc_tree"]["cfg2"]["vs_headline_tree"] = line["extra"]["ploc_tree"]["cfg2"]["value"] / line["value"]
         ng = line["extra"].get("naive_gpu") or {}
         if "ms_per_step" in ng:
             # the same frame = the same rays (up to tie pixels): this run's kernel counter gives the rate
@@ -989,9 +999,10 @@ def main():
     ap.add_argument("--any", action="store_true", help="cfg5: any-hit instead of closest-hit")
     ap.add_argument("--batch", type=int, default=1 << 24, help="cfg5: rays per batch")
     ap.add_argument("--traverse", default="wide", choices=["wide", "exact"])
-    ap.add_argument("--builder", default="reference", choices=["reference", "gpu"],
-                    help="whose BVH the scene uses: the reference's binned-SAH builder (host; what BASELINE's configs name), or the GPU "
-                         "builder (vsb_scene_build: 6.8 ms instead of 0.5 s at 1 M triangles, traces ~10 %% slower)")
+    ap.add_argument("--builder", default="gpu", choices=["gpu", "reference", "gpu_ploc"],
+                    help="who builds the BVH: gpu = the reference's binned-SAH tree built on the GPU (same nodes and indices as the host "
+                         "builder, ~5 ms instead of 0.5 s at 1 M triangles); reference = the host builder; gpu_ploc = Morton + PLOC "
+                         "(another tree: faster to build at >= 5 M primitives, traces ~10 %% slower)")
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra (N = 1) / strong (N > 1) records of the default run")

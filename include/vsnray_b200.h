@@ -282,12 +282,18 @@ int  vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
                       vsb_scene** out);
 /* The same scene with the BVH BUILT ON THE GPU from the primitives alone: replaces
  * build<index_bvh<P>>(first, last) (bvh.h:455 -> detail/bvh/build.inl:28-140 -> binned_sah_builder,
- * detail/bvh/sah.h:150-762; one host thread, recursive) followed by the upload above.  Morton sort +
- * parallel locally-ordered clustering + SAH leaf collapse (<= 4 primitives per leaf), laid out in
- * the reference's node / indices format, then re-encoded into the BVH8 like any other tree.  Closest
- * hits are those of the reference's tree up to t-ties (any valid BVH); any-hit winners and
- * primitive_list_index follow THIS tree's order.  prims: host or device memory (mem = VSB_MEM_*).
- * Knobs (vsb_tune): "build_radius" (1..32, default 8), "build_cost_node_x100", "build_cost_prim_x100". */
+ * detail/bvh/sah.h:150-762; one host thread, recursive) followed by the upload above.
+ *   vsb_tune("build_algorithm", 1) (default): THE REFERENCE'S TREE -- the same binned-SAH decisions, partition order
+ *     and node numbering, evaluated breadth-first (csrc/build_sah.cuh): vsb_scene_download_bvh returns the nodes and
+ *     indices the host builder returns (bounds equal as floats; the sign of a zero may differ), so every result,
+ *     any-hit winners and primitive_list_index included, is that of a scene made from the host builder's tree.
+ *     No spatial splits (build them with the host builder and pass the tree to vsb_scene_create).
+ *   vsb_tune("build_algorithm", 0): Morton sort + parallel locally-ordered clustering + SAH leaf collapse (<= 4
+ *     primitives per leaf; csrc/build_ploc.cuh).  Another valid BVH: closest hits equal up to t-ties, any-hit
+ *     winners and primitive_list_index follow THAT tree's order.  Faster to build from ~5 M primitives up, traces
+ *     ~10 % slower.  Knobs: "build_radius" (1..32, default 8), "build_cost_node_x100", "build_cost_prim_x100".
+ * Both lay the tree out in the reference's node / indices format and re-encode it into the BVH8 like any other
+ * tree.  prims: host or device memory (mem = VSB_MEM_*). */
 int  vsb_scene_build(int prim_kind, const void* prims, size_t n_prims, int mem, vsb_scene** out);
 /* the scene's reference-layout tree back on the host -- what index_bvh<P>::nodes() / indices() hold
  * (bvh.h:298-403); sizes from vsb_scene_stats (out[5] nodes; indices = n_prims).  Either pointer may be NULL. */

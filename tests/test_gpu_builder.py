@@ -24,8 +24,16 @@ FLT_MAX = 3.4028234663852886e38
 SCENES = [("cfg1_sphere", 0.2), ("cfg2_grid", 0.05), ("cfg3_cubes", 0.004), ("cfg5_soup", 0.002), ("spheres", 0.2)]
 
 
+@pytest.fixture(scope="module", autouse=True)
+def ploc_builder(gpu):
+    """This file tests the Morton + PLOC builder; the default of vsb_scene_build is build_sah.cuh (test_gpu_sah_builder.py)."""
+    gpu.tune("build_algorithm", 0)
+    yield
+    gpu.tune("build_algorithm", 1)
+
+
 @pytest.fixture(scope="module")
-def built(gpu):
+def built(gpu, ploc_builder):
     cache = {}
 
     def get(name, scale):

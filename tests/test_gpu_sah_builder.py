@@ -19,7 +19,7 @@ SCENES = [("cfg1_sphere", 0.2), ("cfg2_grid", 0.05), ("cfg3_cubes", 0.004), ("cf
 def sah(gpu):
     gpu.tune("build_algorithm", 1)
     yield gpu
-    gpu.tune("build_algorithm", 0)
+    gpu.tune("build_algorithm", 1)                     # the default
 
 
 def assert_same_tree(nodes, idx, want_nodes, want_idx):

@@ -12,6 +12,7 @@ sys.path.insert(0, ".")
 from visionaray_b200 import api, scenes as S  # noqa: E402
 
 api.init(0)
+api.tune("build_algorithm", 0)          # this tool sweeps the Morton + PLOC builder's knobs (tools/sah_build_bench.py compares both builders)
 jobs = sys.argv[1:] or ["cfg2_grid", "1.0", "cfg5_soup", "0.25"]
 for name, scale in zip(jobs[0::2], jobs[1::2]):
     t0 = time.time()

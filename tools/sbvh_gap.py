@@ -1,7 +1,7 @@
 """Traced-rate gap of the GPU builder (no spatial splits) against the host builder WITH spatial splits
 (detail/bvh/sah.h:428-615) on the case spatial splits exist for: a soup of long thin triangles (the generator of
 tests/golden/make_golden.py:sbvh_scene_prims at N triangles, stretched 30x along x).  Same rays on three trees:
-host SAH without splits, host SAH with splits, GPU (Morton + PLOC).  Usage: python tools/sbvh_gap.py [n_triangles]"""
+host SAH without splits, host SAH with splits, and the two GPU builders (binned SAH = the host tree; Morton + PLOC).  Usage: python tools/sbvh_gap.py [n_triangles]"""
 import json
 import sys
 import time
@@ -46,12 +46,18 @@ for label, split in (("host_sah", False), ("host_sbvh", True)):
     else:
         out[label]["t_equal_to_host_sah"] = bool(np.array_equal(h[:, 3], ref_hits[:, 3]))
     dev.close()
-dev = api.Scene.build(0, torch.from_numpy(tris).cuda())
-ms = api.last_build_ms()
-r, h = rate(dev)
-out["gpu_ploc"] = {"build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"], "mrays": r, "tree": dev.stats(),
-                   "t_equal_to_host_sah": bool(np.array_equal(h[:, 3], ref_hits[:, 3]))}
-dev.close()
+for label, algo in (("gpu_sah", 1), ("gpu_ploc", 0)):
+    api.tune("build_algorithm", algo)
+    for _ in range(2):
+        dev = api.Scene.build(0, torch.from_numpy(tris).cuda())
+        ms = api.last_build_ms()
+        r, h = rate(dev)
+        st = dev.stats()
+        dev.close()
+    out[label] = {"build_ms": round(ms["total_ms"], 2), "iterations": ms["iterations"], "mrays": r, "tree": st,
+                  "t_equal_to_host_sah": bool(np.array_equal(h[:, 3], ref_hits[:, 3]))}
+api.tune("build_algorithm", 1)
 out["gpu_vs_sbvh"] = round(out["gpu_ploc"]["mrays"] / out["host_sbvh"]["mrays"], 3)
 out["gpu_vs_sah"] = round(out["gpu_ploc"]["mrays"] / out["host_sah"]["mrays"], 3)
+out["gpu_sah_vs_sbvh"] = round(out["gpu_sah"]["mrays"] / out["host_sbvh"]["mrays"], 3)
 print(json.dumps(out))

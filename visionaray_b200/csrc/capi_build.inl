@@ -1,5 +1,6 @@
-// capi_build.inl -- vsb_scene_build(): the BVH is built on the GPU (build_ploc.cuh) instead of being
-// handed in from the host builder.  Included by capi.cu after capi_scene.inl.
+// capi_build.inl -- vsb_scene_build(): the BVH is built on the GPU instead of being handed in from the host builder:
+// by default the reference's own binned-SAH tree, breadth-first (build_sah.cuh, capi_build_sah.inl); with
+// vsb_tune("build_algorithm", 0) a Morton + PLOC tree (build_ploc.cuh).  Included by capi.cu after capi_scene.inl.
 
 namespace
 {
@@ -9,7 +10,7 @@ float g_build_cost_node = 1.0f;    // vsb_tune("build_cost_node_x100", ...)
 float g_build_cost_prim = 1.0f;    // vsb_tune("build_cost_prim_x100", ...)
 float g_last_build_ms[4] = { 0, 0, 0, 0 };   // total, sort + setup, PLOC, layout + wide re-encode
 int   g_last_build_iters = 0;
-int   g_build_algorithm = 0;       // vsb_tune("build_algorithm", 0 = Morton + PLOC, 1 = the reference's binned SAH, level by level)
+int   g_build_algorithm = 1;       // vsb_tune("build_algorithm", 0 = Morton + PLOC, 1 = the reference's binned SAH, level by level)
 
 // scratch from the stream-ordered pool (vsb_init keeps it cached between builds)
 struct BuildScratch
