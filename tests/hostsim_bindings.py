@@ -144,7 +144,14 @@ def decode_wide_nodes(nodes: np.ndarray):
     def eight(w0):  # two consecutive words -> 8 bytes
         return np.concatenate([b[:, w0 - 6], b[:, w0 - 5]], axis=1)
 
-    meta = eight(6)
+    # w[6] = `valid`: nibble s = (1 << count) - 1 of the leaf in slot s; records in slot order from prim_base.
+    # Reported as meta = count << 5 | offset (0 for inner children / empty slots).
+    valid = nodes[:, 6].astype(np.uint32)
+    nib = np.stack([(valid >> (4 * k)) & 0xF for k in range(8)], axis=1)
+    assert np.isin(nib, (0, 1, 3, 7, 15)).all() and (nodes[:, 7] == 0).all()
+    count = np.array([0, 1, 0, 2, 0, 0, 0, 3, 0, 0, 0, 0, 0, 0, 0, 4], dtype=np.uint32)[nib]
+    ofs = np.cumsum(count, axis=1) - count
+    meta = np.where(count > 0, (count << 5) | ofs, 0).astype(np.uint32)
     qlo = np.stack([eight(8), eight(10), eight(12)], axis=2).astype(np.float64)
     qhi = np.stack([eight(14), eight(16), eight(18)], axis=2).astype(np.float64)
     lo = p[:, None, :] + qlo * scale[:, None, :]

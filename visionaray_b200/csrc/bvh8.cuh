@@ -338,13 +338,12 @@ VSB_HD int collapse_node(const WideTask task, const Node32* __restrict__ nodes2,
     Node80 out;
     for (int i = 0; i < 20; ++i) out.w[i] = 0u;
     out.w[0] = f2u(lox); out.w[1] = f2u(loy); out.w[2] = f2u(loz);
-    uint32_t imask = 0, inner_rank = 0, prim_ofs = 0;
-    uint8_t meta[8], q[6][8];
+    uint32_t imask = 0, inner_rank = 0, prim_ofs = 0, valid = 0;
+    uint8_t q[6][8];
     for (int s = 0; s < VSB_WIDE; ++s)
     {
-        meta[s] = 0;
         for (int k = 0; k < 6; ++k) q[k][s] = 0;
-        // an empty slot keeps lo = 0 / hi = 0 with meta 0: its bits never enter the hit mask
+        // an empty slot keeps lo = 0 / hi = 0 and an empty nibble in `valid`: its bits never enter the hit mask
         const int ci = child_in_slot[s];
         if (ci < 0) continue;
         const Node32& c = nodes2[child[ci]];
@@ -354,15 +353,14 @@ VSB_HD int collapse_node(const WideTask task, const Node32* __restrict__ nodes2,
         quantise_axis(loz, sz, c.min_z, c.max_z, a, b); q[2][s] = (uint8_t)a; q[5][s] = (uint8_t)b;
         if (c.num_prims == 0)
         {
-            imask |= 1u << s;
-            meta[s] = 0;   // inner children are identified by imask
+            imask |= 1u << s;          // inner children are identified by imask (their nibble of `valid` stays 0)
             next_tasks[task_base + inner_rank].bvh2_node = child[ci];
             next_tasks[task_base + inner_rank].wide_index = child_base + inner_rank;
             ++inner_rank;
         }
         else
         {
-            meta[s] = (uint8_t)((c.num_prims << 5) | prim_ofs);
+            valid |= ((1u << c.num_prims) - 1u) << (4 * s);      // records in slot order: index = prim_base + rank of the bit in `valid`
             for (uint32_t k = 0; k < c.num_prims; ++k) leaf_list[prim_base + prim_ofs + k] = c.first + k;
             prim_ofs += c.num_prims;
         }
@@ -370,8 +368,8 @@ VSB_HD int collapse_node(const WideTask task, const Node32* __restrict__ nodes2,
     out.w[3] = ex | (ey << 8) | (ez << 16) | (imask << 24);
     out.w[4] = child_base;
     out.w[5] = prim_base;
-    out.w[6] = (uint32_t)meta[0] | ((uint32_t)meta[1] << 8) | ((uint32_t)meta[2] << 16) | ((uint32_t)meta[3] << 24);
-    out.w[7] = (uint32_t)meta[4] | ((uint32_t)meta[5] << 8) | ((uint32_t)meta[6] << 16) | ((uint32_t)meta[7] << 24);
+    out.w[6] = valid;
+    out.w[7] = 0u;
     // w[8..9] qlo_x, w[10..11] qlo_y, w[12..13] qlo_z, w[14..15] qhi_x, w[16..17] qhi_y, w[18..19] qhi_z
     for (int k = 0; k < 6; ++k)
     {

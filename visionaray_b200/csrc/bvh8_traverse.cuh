@@ -97,9 +97,36 @@ VSB_HD uint32_t perm_xor8(uint32_t h, uint32_t x)
     return h;
 }
 
+// 8 child bits -> 8 nibbles (bit i -> 0xF << 4 i).  The shifts are multiplications (IMAD: the fma pipe, which has room;
+// the alu pipe is the one the kernel is bound by); no two partial products overlap, so + is |.
+VSB_HD uint32_t expand_nibbles(uint32_t h)
+{
+    uint32_t t = (h * 4097u) & 0x000f000fu;       // bits 0..3 stay, bits 4..7 -> 16..19
+    t = (t * 65u) & 0x03030303u;                  // pairs
+    t = (t * 9u) & 0x11111111u;                   // singles, one per nibble
+    return t * 15u;
+}
+
+// (acc << 1) | sign(d)
+VSB_HD uint32_t funnel_shift_in_sign(uint32_t acc, float d)
+{
+#if defined(__CUDA_ARCH__)
+    return __funnelshift_l(__float_as_uint(d), acc, 1);
+#else
+    return (acc << 1) | (f2u(d) >> 31);
+#endif
+}
+
+// leaf-order record of bit `bit` of a primitive mask (slot space: bit 4 s + j = primitive j of the leaf in slot s)
+VSB_HD uint32_t prim_record(uint32_t prim_base, uint32_t valid, int bit)
+{
+    return prim_base + (uint32_t)pop_count(valid & ((1u << bit) - 1u));
+}
+
 // Tests the 8 children of a node against the ray.  Returns the node hit mask: bits 24..31 = inner
 // children (bit = 24 + (slot ^ octinv), so the highest set bit is the nearest slot); prim_hits
-// gets one bit per leaf primitive of every hit leaf child (up to 8 leaves x 4 primitives).
+// gets one bit per leaf primitive of every hit leaf child, in SLOT space (bit 4 s + j; n.w[6] = the node's
+// `valid` mask maps a bit to its record: prim_record()).
 VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
 {
     const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
@@ -148,7 +175,6 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
 
     // near/far planes by direction sign (selected once per node, not per child)
     const bool nx = r.ix < 0.0f, ny = r.iy < 0.0f, nz = r.iz < 0.0f;
-    uint32_t child_hits = 0u, ph = 0u;
 #if VSB_NODE_HALFCVT
     const uint32_t one = half_bias_bits();
 #define VSB_PLANE_COORD byte_as_biased_float
@@ -156,17 +182,20 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
     const uint32_t one = unit_float_bits();
 #define VSB_PLANE_COORD byte_as_unit_float
 #endif
+    // children 7 .. 0: the sign of tmax - tmin (1 = miss; equal floats give +0, and a difference never rounds across 0)
+    // is shifted into `miss` from the right, so child c ends at bit c -- one funnel shift per child instead of a
+    // compare, a select and an OR (the alu pipe is the kernel's limiter; the subtraction runs on the fma pipe)
+    uint32_t miss = 0u;
 #pragma unroll
-    for (int half = 0; half < 2; ++half)
+    for (int half = 1; half >= 0; --half)
     {
-        const uint32_t meta4 = n.w[6 + half];
         const uint32_t qlox = n.w[8 + half], qloy = n.w[10 + half], qloz = n.w[12 + half];
         const uint32_t qhix = n.w[14 + half], qhiy = n.w[16 + half], qhiz = n.w[18 + half];
         const uint32_t qnx = nx ? qhix : qlox, qfx = nx ? qlox : qhix;
         const uint32_t qny = ny ? qhiy : qloy, qfy = ny ? qloy : qhiy;
         const uint32_t qnz = nz ? qhiz : qloz, qfz = nz ? qloz : qhiz;
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
+        for (int k = 3; k >= 0; --k)
         {
             const float tnx = fma_f(VSB_PLANE_COORD(qnx, k, one), sxs, onx);
             const float tny = fma_f(VSB_PLANE_COORD(qny, k, one), sys, ony);
@@ -176,16 +205,12 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
             const float tfz = fma_f(VSB_PLANE_COORD(qfz, k, one), szs, ofz);
             const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
             const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, limit));
-            const uint32_t m = (meta4 >> (8 * k)) & 0xffu;       // leaf: count << 5 | offset; inner / empty: 0
-            if (tmin <= tmax)
-            {
-                child_hits |= 1u << (4 * half + k);
-                ph |= bit_mask(m & 31u, m >> 5);
-            }
+            miss = funnel_shift_in_sign(miss, tmax - tmin);
         }
     }
+    const uint32_t child_hits = ~miss & 0xffu;
 #undef VSB_PLANE_COORD
-    prim_hits = ph;
+    prim_hits = expand_nibbles(child_hits) & n.w[6];
     return perm_xor8(child_hits & (n.w[3] >> 24), r.octinv4 & 7u) << 24;
 }
 
@@ -271,9 +296,6 @@ VSB_HD void hit_from_record(const WideScene& s, uint32_t rec, float ox, float oy
 #ifndef VSB_PREFETCH_PUSH
 #define VSB_PREFETCH_PUSH 0   // 1 / 2: prefetch (L2 / L1) the next sibling of a node group when it is pushed
 #endif
-#ifndef VSB_PREFETCH
-#define VSB_PREFETCH 0     // measured: no gain (the unified loads already overlap); kept as a switch
-#endif
 
 // The deep part of the stack lives in its own (local-memory) object: kept inside TravState, its
 // dynamically indexed arrays dragged the whole struct -- node group, primitive group, stack pointer
@@ -295,7 +317,8 @@ struct TravSpill
 struct TravState
 {
     uint32_t ng_base, ng_mask;      // current node group
-    uint32_t pg_base, pg_mask;      // current primitive group
+    uint32_t pg_base, pg_mask;      // current primitive group (mask in slot space, see test_node)
+    uint32_t pg_valid;              // the group's node's `valid` mask: prim_record(pg_base, pg_valid, bit)
     int      sp;
 #if defined(__CUDACC__)
     uint32_t sstack;                // shared-window byte address of this thread's column of the block's stack:
@@ -342,26 +365,8 @@ VSB_HD void trav_begin(TravState& t)
 {
     // the root is "inner child at bit 31" of a virtual group with child_base 0 and imask 0
     t.ng_base = 0u; t.ng_mask = 0x80000000u;
-    t.pg_base = 0u; t.pg_mask = 0u;
+    t.pg_base = 0u; t.pg_mask = 0u; t.pg_valid = 0u;
     t.sp = 0;
-}
-
-// Prefetch the leaf-order records of the primitives a node test selected (bits of `mask`, records
-// of `rec_bytes` starting at index `base`): they are tested over the next steps, and by then the
-// lines are in L1 instead of costing one exposed HBM/L2 round trip per primitive.
-VSB_HD void prefetch_prims(const void* prims, uint32_t base, uint32_t mask, uint32_t rec_bytes)
-{
-#if defined(__CUDA_ARCH__)
-    const uint32_t first = (uint32_t)(__ffs((int)mask) - 1), last = (uint32_t)find_msb(mask);
-    const char* a = reinterpret_cast<const char*>(prims) + (size_t)(base + first) * rec_bytes;
-    const char* e = reinterpret_cast<const char*>(prims) + (size_t)(base + last + 1u) * rec_bytes;
-    a = reinterpret_cast<const char*>(reinterpret_cast<uintptr_t>(a) & ~(uintptr_t)127);
-#pragma unroll
-    for (int k = 0; k < 4; ++k)
-        if (a + 128 * k < e) asm volatile("prefetch.global.L1 [%0];" :: "l"(a + 128 * k));
-#else
-    (void)prims; (void)base; (void)mask; (void)rec_bytes;
-#endif
 }
 
 // One traversal step of one ray: EITHER one primitive test (while the lane has primitives
@@ -393,7 +398,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         {
             const int bit = find_msb(t.pg_mask);
             t.pg_mask &= ~(1u << bit);
-            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(t.pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)prim_record(t.pg_base, t.pg_valid, bit) * (size_t)(n16 * 16), n16, n);
             test_prim(s.prim_kind, n, r, best, limit);
             if (any && best.hit) return false;
         }
@@ -421,7 +426,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         uint32_t ph;
         const uint32_t nh = test_node(n, r, limit, ph);
         t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
-        t.pg_base = n.w[5]; t.pg_mask = ph;
+        t.pg_base = n.w[5]; t.pg_mask = ph; t.pg_valid = n.w[6];
         if (t.pg_mask) return true;
     }
 #else
@@ -434,7 +439,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
     {
         const int bit = find_msb(t.pg_mask);
         t.pg_mask &= ~(1u << bit);
-        const uint32_t index = t.pg_base + (uint32_t)bit;
+        const uint32_t index = prim_record(t.pg_base, t.pg_valid, bit);
         n16 = wide_rec_words16(s.prim_kind);
         addr = reinterpret_cast<const char*>(s.prims) + (size_t)index * (size_t)(n16 * 16);
     }
@@ -480,7 +485,7 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         {
             const int bit = find_msb(t.pg_mask);
             t.pg_mask &= ~(1u << bit);
-            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(t.pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)prim_record(t.pg_base, t.pg_valid, bit) * (size_t)(n16 * 16), n16, n);
             test_prim(s.prim_kind, n, r, best, limit);
             if (any && best.hit) return false;
         }
@@ -492,12 +497,8 @@ VSB_HD bool trav_step(const WideScene& s, const RayCtx& r, TravState& t, HitReg&
         uint32_t ph;
         const uint32_t nh = test_node(n, r, limit, ph);
         t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
-        t.pg_base = n.w[5]; t.pg_mask = ph;
-        if (t.pg_mask)
-        {
-            if (VSB_PREFETCH) prefetch_prims(s.prims, t.pg_base, t.pg_mask, (uint32_t)wide_rec_words16(s.prim_kind) * 16u);
-            return true;
-        }
+        t.pg_base = n.w[5]; t.pg_mask = ph; t.pg_valid = n.w[6];
+        if (t.pg_mask) return true;
     }
 #endif
 

@@ -377,13 +377,13 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             const int excl = incl - c;
             const unsigned word = __reduce_or_sync(0xffffffffu, (int)lane < ntake ? 1u << excl : 0u);   // bit at the first pair of every taken group
             const int g = __popc(word & (0xffffffffu >> (31u - lane))) - 1;                           // the group lane's pair belongs to
-            const uint32_t gb = __shfl_sync(0xffffffffu, e.x, g), go = __shfl_sync(0xffffffffu, e.z, g);
+            const uint32_t gb = __shfl_sync(0xffffffffu, e.x, g), go = __shfl_sync(0xffffffffu, e.z, g), gv = __shfl_sync(0xffffffffu, e.w, g);
             uint32_t gm = __shfl_sync(0xffffffffu, e.y, g);
             int k = (int)lane - __shfl_sync(0xffffffffu, excl, g);
             if ((int)lane < n)
             {
                 while (k-- > 0) gm &= gm - 1u;                       // the k-th set bit of the group's mask
-                const uint32_t rec = gb + (uint32_t)(__ffs((int)gm) - 1);
+                const uint32_t rec = prim_record(gb, gv, __ffs((int)gm) - 1);
                 NodeRegs r;
                 load_record(reinterpret_cast<const char*>(sc.prims) + (size_t)rec * (size_t)(n16 * 16), n16, r);
                 const float* o = ray_s + go;
@@ -499,7 +499,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             uint32_t ph;
             const uint32_t nh = test_node(n, rc, limit, ph);
             t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
-            t.pg_base = n.w[5]; t.pg_mask = ph;
+            t.pg_base = n.w[5]; t.pg_mask = ph; t.pg_valid = n.w[6];
             if ((t.ng_mask >> 24) == 0u)
             {
                 if (t.sp == 0) t.ng_mask = 0u;
@@ -517,7 +517,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
                 if (has != 0u)
                 {
                     while (q_tail - q_head > VSB_QCAP / 2 - 32u) { drain(); drained = true; }       // room for 32 groups
-                    if (mine) gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, 0u);
+                    if (mine) gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, t.pg_valid);
                     q_pairs += __reduce_add_sync(0xffffffffu, mine ? (unsigned)__popc(t.pg_mask) : 0u);
                     t.pg_mask = 0u;
                     q_tail += (unsigned)__popc(has);
@@ -564,7 +564,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
                     {
                         const int bit = find_msb(t.pg_mask);
                         t.pg_mask &= ~(1u << bit);
-                        ring[(q_tail + off) & (VSB_QCAP - 1u)] = make_uint2(t.pg_base + (uint32_t)bit, threadIdx.x);
+                        ring[(q_tail + off) & (VSB_QCAP - 1u)] = make_uint2(prim_record(t.pg_base, t.pg_valid, bit), threadIdx.x);
                         ++off;
                     }
                     q_tail += total < space ? total : space;

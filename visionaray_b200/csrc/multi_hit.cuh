@@ -133,7 +133,7 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
 {
     uint32_t sb[VSB_STACK_SIZE], sm[VSB_STACK_SIZE];
     int sp = 0;
-    uint32_t ng_base = 0u, ng_mask = 0x80000000u, pg_base = 0u, pg_mask = 0u;     // the root as "child 31 of a virtual group"
+    uint32_t ng_base = 0u, ng_mask = 0x80000000u, pg_base = 0u, pg_mask = 0u, pg_valid = 0u;     // the root as "child 31 of a virtual group"
     const int n16 = wide_rec_words16(s.prim_kind);
     NodeRegs n;
     for (;;)
@@ -142,7 +142,7 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
         {
             const int bit = find_msb(pg_mask);
             pg_mask &= ~(1u << bit);
-            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(pg_base + (uint32_t)bit) * (size_t)(n16 * 16), n16, n);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)prim_record(pg_base, pg_valid, bit) * (size_t)(n16 * 16), n16, n);
             if (s.prim_kind == 0 || (s.prim_kind == 2 && !(n.w[11] & VSB_GENERIC_SPHERE_TAG)))
             {
                 float t = -1.0f, u = 0.0f, v = 0.0f;
@@ -176,7 +176,7 @@ VSB_HD void multi_hit_wide(const WideScene& s, const RayCtx& r, MultiHitSink& ou
             uint32_t ph;
             const uint32_t nh = test_node(n, r, out.limit, ph);
             ng_base = n.w[4]; ng_mask = nh | (n.w[3] >> 24);
-            pg_base = n.w[5]; pg_mask = ph;
+            pg_base = n.w[5]; pg_mask = ph; pg_valid = n.w[6];
             if (pg_mask) continue;
         }
         if ((ng_mask & 0xff000000u) == 0u)

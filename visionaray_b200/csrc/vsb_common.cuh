@@ -79,11 +79,13 @@ struct SphRec
 
 // ---- BVH8 node: 80 B = 5 x 128-bit records ---------------------------------------------------
 //  q0: origin p (3 x f32) | e_x e_y e_z imask (4 x u8; child box = p + q * 2^(e-127... see below))
-//  q1: child_base (u32) | prim_base (u32) | meta[0..7] (8 x u8)
+//  q1: child_base (u32) | prim_base (u32) | valid (u32) | 0
 //  q2: qlo_x[8] | qlo_y[8]      q3: qlo_z[8] | qhi_x[8]      q4: qhi_y[8] | qhi_z[8]
-// meta[i]: leaf child: (count << 5) | offset, count = 1..4 primitives starting at prim_base + offset
-// (offset 0..28: 8 leaves x 4 primitives = 32 bits of primitive hit mask); inner child (bit i of
-// imask set) or empty slot: 0.  The exponents are
+// valid: nibble i = (1 << count) - 1 for a leaf child in slot i with count = 1..4 primitives, 0 for an inner child (bit i
+// of imask set) or an empty slot.  The node's leaf-order records lie in slot order from prim_base: the record of bit b
+// of `valid` is prim_base + popc(valid & ((1 << b) - 1)).  A node test turns its 8 child hit bits into a primitive mask
+// with one nibble expansion and one AND (round 1 kept count << 5 | offset per child and built the mask child by child:
+// ~40 of the ~180 ALU-pipe instructions of a node visit).  The exponents are
 // biased float exponents: scale = bits_to_float(e << 23).
 struct Node80
 {

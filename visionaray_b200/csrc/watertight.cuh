@@ -96,7 +96,7 @@ VSB_HD void trace_wide_watertight(const WideScene& s, const RayCtx& r, HitReg& b
     wt_ray_init(w, r.dx, r.dy, r.dz);
     uint32_t sb[VSB_STACK_SIZE], sm[VSB_STACK_SIZE];
     int sp = 0;
-    uint32_t ng_base = 0u, ng_mask = 0x80000000u, pg_base = 0u, pg_mask = 0u;
+    uint32_t ng_base = 0u, ng_mask = 0x80000000u, pg_base = 0u, pg_mask = 0u, pg_valid = 0u;
     NodeRegs n;
     for (;;)
     {
@@ -104,7 +104,7 @@ VSB_HD void trace_wide_watertight(const WideScene& s, const RayCtx& r, HitReg& b
         {
             const int bit = find_msb(pg_mask);
             pg_mask &= ~(1u << bit);
-            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)(pg_base + (uint32_t)bit) * 48u, 3, n);
+            load_record(reinterpret_cast<const char*>(s.prims) + (size_t)prim_record(pg_base, pg_valid, bit) * 48u, 3, n);
             const float v1x = u2f(n.w[0]), v1y = u2f(n.w[1]), v1z = u2f(n.w[2]);
             const float e1x = u2f(n.w[4]), e1y = u2f(n.w[5]), e1z = u2f(n.w[6]);
             const float e2x = u2f(n.w[8]), e2y = u2f(n.w[9]), e2z = u2f(n.w[10]);
@@ -136,7 +136,7 @@ VSB_HD void trace_wide_watertight(const WideScene& s, const RayCtx& r, HitReg& b
             uint32_t ph;
             const uint32_t nh = test_node(n, r, limit, ph);
             ng_base = n.w[4]; ng_mask = nh | (n.w[3] >> 24);
-            pg_base = n.w[5]; pg_mask = ph;
+            pg_base = n.w[5]; pg_mask = ph; pg_valid = n.w[6];
             if (pg_mask) continue;
         }
         if ((ng_mask & 0xff000000u) == 0u)
