@@ -5,39 +5,26 @@ Usage: python tools/ncu_region_opcodes.py report.ncu-rep [region-substring]"""
 import re
 import sys
 
-sys.argv, argv = [sys.argv[0], sys.argv[1]], sys.argv
+argv = sys.argv
 import importlib.util, os
 spec = importlib.util.spec_from_file_location("ncu_groups", os.path.join(os.path.dirname(os.path.abspath(__file__)), "ncu_groups.py"))
-import io, contextlib
 G = importlib.util.module_from_spec(spec)
-with contextlib.redirect_stdout(io.StringIO()):
-    spec.loader.exec_module(G)
+spec.loader.exec_module(G)
 want = argv[2] if len(argv) > 2 else "node_test"
 ALU = {"LOP3", "SHF", "PRMT", "FMNMX", "FMNMX3", "ISETP", "SEL", "IADD3", "BMSK", "FSETP", "LEA", "VIADD", "MOV", "POPC", "FLO", "PLOP3", "VIMNMX", "IABS", "FSEL", "SGXT", "R2P", "P2R", "BREV", "VIMNMX3", "HMNMX2", "HSETP2", "IMNMX", "LOP", "FCHK", "FSET"}
 FMA = {"FFMA", "FMUL", "FADD", "IMAD", "HADD2", "HFMA2", "HMUL2"}
-import csv, subprocess
-out = subprocess.run(["ncu", "-i", argv[1], "--page", "source", "--print-source", "cuda,sass", "--csv"], stdout=subprocess.PIPE, text=True).stdout
-rows = list(csv.reader(io.StringIO(out)))
-fname, hdr, cur = "", None, None
+h, L = G.load(argv[1])
+ii = h.index("Instructions Executed"); ti = h.index("Thread Instructions Executed")
+f = lambda v: float(v) if v not in ("", "-") else 0.0
 ops = {}
 total = 0.0
-f = lambda v: float(v) if v not in ("", "-") else 0.0
-for r in rows:
-    if len(r) == 2 and r[0] == "File Path":
-        fname = r[1].split("/")[-1]; continue
-    if len(r) > 5 and r[0] == "Line No":
-        hdr = r; ii = hdr.index("Instructions Executed"); ti = hdr.index("Thread Instructions Executed"); continue
-    if not hdr or len(r) != len(hdr):
+for reg, r in G.dedupe(L):
+    n = f(r[ii]); total += n
+    if want not in reg:
         continue
-    if r[0] not in ("", "Line No") and r[2] == "-":
-        cur = (fname, int(r[0]), r[1]); continue
-    if r[0] == "" and r[2].startswith("0x") and cur:
-        n = f(r[ii]); total += n
-        if want not in G.region(cur[0], cur[1], cur[2]):
-            continue
-        m = re.match(r"\s*(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", r[3])
-        op = m.group(1) if m else "?"
-        a = ops.setdefault(op, [0.0, 0.0]); a[0] += n; a[1] += f(r[ti])
+    m = re.match(r"\s*(?:@!?U?P\d+\s+)?([A-Z0-9_]+)", r[3])
+    op = m.group(1) if m else "?"
+    a = ops.setdefault(op, [0.0, 0.0]); a[0] += n; a[1] += f(r[ti])
 T = sum(a[0] for a in ops.values())
 print(f"# region '{want}': {100 * T / total:.1f} % of {total:.4g} warp instructions")
 pipes = {"alu": 0.0, "fma": 0.0, "other": 0.0}

@@ -127,7 +127,8 @@ VSB_HD uint32_t prim_record(uint32_t prim_base, uint32_t valid, int bit)
 // children (bit = 24 + (slot ^ octinv), so the highest set bit is the nearest slot); prim_hits
 // gets one bit per leaf primitive of every hit leaf child, in SLOT space (bit 4 s + j; n.w[6] = the node's
 // `valid` mask maps a bit to its record: prim_record()).
-VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
+// test_node_slots: the inner-child hits in SLOT space (8 bits); test_node: permuted into traversal order, bits 24..31
+VSB_HD uint32_t test_node_slots(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
 {
     const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
     const uint32_t e = n.w[3];
@@ -182,9 +183,9 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
     const uint32_t one = unit_float_bits();
 #define VSB_PLANE_COORD byte_as_unit_float
 #endif
-    // children 7 .. 0: the sign of tmax - tmin (1 = miss; equal floats give +0, and a difference never rounds across 0)
-    // is shifted into `miss` from the right, so child c ends at bit c -- one funnel shift per child instead of a
-    // compare, a select and an OR (the alu pipe is the kernel's limiter; the subtraction runs on the fma pipe)
+    // children 7 .. 0: the verdict of a child is a sign (1 = miss; equal floats differ by +0, and a difference never
+    // rounds across 0); it is shifted into `miss` from the right, so child c ends at bit c -- one funnel shift per child
+    // instead of a compare, a select and an OR (the alu pipe is the kernel's limiter)
     uint32_t miss = 0u;
 #pragma unroll
     for (int half = 1; half >= 0; --half)
@@ -203,16 +204,38 @@ VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint3
             const float tfx = fma_f(VSB_PLANE_COORD(qfx, k, one), sxs, ofx);
             const float tfy = fma_f(VSB_PLANE_COORD(qfy, k, one), sys, ofy);
             const float tfz = fma_f(VSB_PLANE_COORD(qfz, k, one), szs, ofz);
-            const float tmin = fmaxf(fmaxf(tnx, tny), fmaxf(tnz, 0.0f));
-            const float tmax = fminf(fminf(tfx, tfy), fminf(tfz, limit));
-            miss = funnel_shift_in_sign(miss, tmax - tmin);
+            // max(tn, 0) <= min(tf, limit)  <=>  tn <= tf, tn <= limit, 0 <= tf (limit >= 0): three differences whose
+            // minimum carries the verdict in its sign -- 3 alu-pipe operations per child instead of 4 (the subtractions
+            // run on the fma pipe).  tf is never -0.0: the offsets are sums with a non-negative margin.
+            const float tn = fmaxf(fmaxf(tnx, tny), tnz);
+            const float tf = fminf(fminf(tfx, tfy), tfz);
+            miss = funnel_shift_in_sign(miss, fminf(fminf(tf - tn, limit - tn), tf));
         }
     }
     const uint32_t child_hits = ~miss & 0xffu;
 #undef VSB_PLANE_COORD
     prim_hits = expand_nibbles(child_hits) & n.w[6];
-    return perm_xor8(child_hits & (n.w[3] >> 24), r.octinv4 & 7u) << 24;
+    return child_hits & (n.w[3] >> 24);
 }
+
+VSB_HD uint32_t test_node(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
+{
+    return perm_xor8(test_node_slots(n, r, limit, prim_hits), r.octinv4 & 7u) << 24;
+}
+
+#if defined(__CUDACC__)
+// perm_xor8 as a table in shared memory (8 permutations x 256 masks = 2 KiB per CTA): one LOP3 + one LDS instead of
+// ~10 alu-pipe instructions per node visit.  The CTA fills the table once (perm_lut_fill, then __syncthreads).
+__device__ __forceinline__ void perm_lut_fill(uint8_t* lut)
+{
+    for (unsigned i = threadIdx.x; i < 2048u; i += blockDim.x) lut[i] = (uint8_t)perm_xor8(i & 0xffu, i >> 8);
+}
+__device__ __forceinline__ uint32_t test_node_lut(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits, const uint8_t* lut)
+{
+    const uint32_t h = test_node_slots(n, r, limit, prim_hits);
+    return (uint32_t)lut[(r.octinv4 & 0x700u) | h] * 0x1000000u;
+}
+#endif
 
 // Primitive test on a loaded leaf-order record + is_closer(hr, result, max_t)
 // (update_if.h:50-56,75-79).  `limit` = min(result.t, max_t).

@@ -327,6 +327,9 @@ __global__ void __launch_bounds__(VSB_BLOCK, Program::MIN_BLOCKS_Q)
 trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
 {
     extern __shared__ uint32_t lane_store_raw[];
+    __shared__ uint8_t perm_lut[2048];                    // child-order permutation of a hit mask (test_node_lut)
+    perm_lut_fill(perm_lut);
+    __syncthreads();
     const unsigned lane = threadIdx.x & 31u;
     const unsigned lt_mask = (1u << lane) - 1u;
     uint32_t* const prog_state = lane_store_raw + 2 * VSB_Q_SHARED_STACK * VSB_BLOCK;
@@ -497,7 +500,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
             NodeRegs n;
             load_record(addr, 5, n);
             uint32_t ph;
-            const uint32_t nh = test_node(n, rc, limit, ph);
+            const uint32_t nh = test_node_lut(n, rc, limit, ph, perm_lut);
             t.ng_base = n.w[4]; t.ng_mask = nh | (n.w[3] >> 24);
             t.pg_base = n.w[5]; t.pg_mask = ph; t.pg_valid = n.w[6];
             if ((t.ng_mask >> 24) == 0u)
