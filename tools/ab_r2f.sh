@@ -1,0 +1,9 @@
+#!/bin/bash
+# A/B of ring variants on all four workloads (development)
+mkdir -p gpurun_out
+for v in base gall gnone; do
+  if [ "$v" = base ]; then unset VSB_CUDA_LIB; else export VSB_CUDA_LIB=$PWD/visionaray_b200/lib/variants/libvsnray_b200_$v.so; fi
+  for w in cfg2 cfg3 cfg4; do python bench.py --workload $w --steps 5 --warmup 3 --no-cpu --no-extra 2>/dev/null | python tools/quick.py "$w $v"; done
+  python bench.py --workload cfg5 --steps 5 --warmup 3 --no-cpu 2>/dev/null | python tools/quick.py "cfg5 $v"
+  python bench.py --workload cfg5 --any --steps 5 --warmup 3 --no-cpu 2>/dev/null | python tools/quick.py "cfg5any $v"
+done

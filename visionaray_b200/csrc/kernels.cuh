@@ -355,7 +355,7 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
     t.sstack = (uint32_t)__cvta_generic_to_shared(lane_store_raw + threadIdx.x);
     RayReq req;
 
-    // Program::GROUP_RING (the AO and path-tracing frame programs; measured +4.8 % cfg3, +3 % cfg4, -1 % cfg2, -2 % cfg5 any-hit):
+    // Program::GROUP_RING (ray lists, the AO and path-tracing frame programs; measured +4.5 % cfg3, +5.6 % cfg4, +5 % cfg5, -0.7 % cfg2: gpurun_out/r2_ab6.log):
     // one entry per (lane, node visit) = (first record, primitive mask, owner); a drain takes the leading
     // groups that hold <= 32 pairs together and expands them to one pair per lane cooperatively
     uint4* const gring = reinterpret_cast<uint4*>(ring);           // VSB_QCAP / 2 groups of 16 bytes in the same 1 KiB per warp
@@ -668,7 +668,7 @@ struct RayListProgram
 #define VSB_LIST_MIN_BLOCKS_Q 8     // 64 registers, 32 warps per SM: measured +2 % on the incoherent ray lists (frames: 6 is better)
 #endif
     static constexpr int MIN_BLOCKS_Q = VSB_LIST_MIN_BLOCKS_Q;
-    static constexpr bool GROUP_RING = false;     // pair ring: closest-hit +1 % with groups, any-hit -2 %
+    static constexpr bool GROUP_RING = VSB_GROUP_RING_ALL >= 0;    // group ring: closest-hit +5 %, any-hit +1 % (records addressed by rank since the `valid` node word)
 
     __device__ bool begin(Lane& L, unsigned long long item, RayReq& req) const
     {

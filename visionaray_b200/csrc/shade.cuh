@@ -828,7 +828,7 @@ struct FrameProgram
 #define VSB_FRAME_MIN_BLOCKS_Q 6
 #endif
     static constexpr int MIN_BLOCKS_Q = VSB_FRAME_MIN_BLOCKS_Q; // the same for trace_kernel_q
-    static constexpr bool GROUP_RING = KERNEL >= 2;             // trace_kernel_q's ring holds (record range, mask, owner) groups: AO / path tracing
+    static constexpr bool GROUP_RING = VSB_GROUP_RING_ALL > 0 ? true : (VSB_GROUP_RING_ALL < 0 ? false : KERNEL >= 2);             // trace_kernel_q's ring holds (record range, mask, owner) groups: AO / path tracing
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
     static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (SURF ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
 

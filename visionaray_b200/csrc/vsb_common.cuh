@@ -93,6 +93,9 @@ struct Node80
 };
 
 #define VSB_WIDE 8
+#ifndef VSB_GROUP_RING_ALL
+#define VSB_GROUP_RING_ALL 0      // development switch: 1 / -1 = group ring / pair ring for every program (0: per program)
+#endif
 #define VSB_MAX_LEAF_BITS 32
 
 // ---- exact single-rounding arithmetic ---------------------------------------------------------
