@@ -26,8 +26,9 @@
 //                         node ("segment") that touches its chunk; a segment that lies inside the chunk gets its split
 //                         found right there by a 16-lane group; one that spans chunks is flushed to a global slot
 //   sah_span_split_kernel the split of the spanning segments from their global slots
-//   sah_flag_kernel + cub::DeviceScan + sah_mislist_kernel + sah_swap_kernel      the partition
-//   sah_child_count_kernel + cub::DeviceScan + sah_emit_children_kernel + sah_reassign_kernel   next level's segments
+//   cub::DeviceScan over the predicate (SahFlag, evaluated inside the scan) + sah_mislist_kernel + sah_swap_kernel   the partition
+//   sah_child_count_kernel + cub::DeviceScan + sah_emit_children_kernel   next level's segments (positions move to
+//                         them in the next level's sah_bin_kernel)
 // Spatial splits (sah.h:428-615) stay on the host builder.
 #pragma once
 
@@ -257,16 +258,25 @@ __device__ void sah_find_split(const uint32_t* bins, bool valid, const SahSeg* s
 
 // slots: one set of bins per chunk, for the segment that STARTS in that chunk and reaches beyond it (at most one);
 // span_seg[chunk] names it.  Slots are in the cleared state between levels (sah_span_split_kernel clears what it used).
-__global__ void __launch_bounds__(VSB_SAH_CHUNK) sah_bin_kernel(const SahRef* __restrict__ refs, const uint32_t* __restrict__ seg_of, uint32_t n,
+// prev_child != nullptr: seg_of[] still holds the segments of the level above; every position moves to the child
+// segment it landed in (or to NONE when its segment stayed a leaf) first -- the reassignment pass of the level above,
+// fused into this level's first read of seg_of[].
+__global__ void __launch_bounds__(VSB_SAH_CHUNK) sah_bin_kernel(const SahRef* __restrict__ refs, uint32_t* __restrict__ seg_of, uint32_t n,
                                                                 const SahSeg* __restrict__ segs, SahSplit* splits, uint32_t* slots,
-                                                                uint32_t* __restrict__ span_seg)
+                                                                uint32_t* __restrict__ span_seg, const SahChild* __restrict__ prev_child)
 {
     __shared__ uint32_t sbins[VSB_SAH_MAX_LOCAL * VSB_SAH_SLOT_WORDS];
     __shared__ uint32_t s_lo, s_hi;
     const uint32_t chunk_start = blockIdx.x * VSB_SAH_CHUNK;
     const uint32_t chunk_end = chunk_start + VSB_SAH_CHUNK < n ? chunk_start + VSB_SAH_CHUNK : n;
     const uint32_t p = chunk_start + threadIdx.x;
-    const uint32_t seg = p < n ? seg_of[p] : VSB_SAH_NONE;
+    uint32_t seg = p < n ? seg_of[p] : VSB_SAH_NONE;
+    if (prev_child && seg != VSB_SAH_NONE)
+    {
+        const SahChild c = prev_child[seg];
+        seg = p < c.pivot ? c.lseg : c.rseg;          // a segment that stayed a leaf: lseg = rseg = NONE
+        seg_of[p] = seg;
+    }
     if (threadIdx.x == 0) { s_lo = VSB_SAH_NONE; s_hi = 0u; }
     __syncthreads();
     if (seg != VSB_SAH_NONE) { atomicMin(&s_lo, seg); atomicMax(&s_hi, seg); }
@@ -295,11 +305,16 @@ __global__ void __launch_bounds__(VSB_SAH_CHUNK) sah_bin_kernel(const SahRef* __
         const float c[3] = { sah_center(lo[0], hi[0]), sah_center(lo[1], hi[1]), sah_center(lo[2], hi[2]) };
         const int bin = sah_project(k0, k1, axis == 0 ? c[0] : (axis == 1 ? c[1] : c[2]));
         uint32_t* sb = sbins + (seg - seg_base) * VSB_SAH_SLOT_WORDS + bin;
+        // read before the atomic: once a bin holds a few references most of them extend none of its bounds
+        volatile uint32_t* vb = sb;
 #pragma unroll
         for (int k = 0; k < 3; ++k)
         {
-            atomicMin(sb + k * VSB_SAH_BINS, f2o(lo[k]));        atomicMax(sb + (3 + k) * VSB_SAH_BINS, f2o(hi[k]));
-            atomicMin(sb + (6 + k) * VSB_SAH_BINS, f2o(c[k]));   atomicMax(sb + (9 + k) * VSB_SAH_BINS, f2o(c[k]));
+            const uint32_t l = f2o(lo[k]), h = f2o(hi[k]), m = f2o(c[k]);
+            if (l < vb[k * VSB_SAH_BINS]) atomicMin(sb + k * VSB_SAH_BINS, l);
+            if (h > vb[(3 + k) * VSB_SAH_BINS]) atomicMax(sb + (3 + k) * VSB_SAH_BINS, h);
+            if (m < vb[(6 + k) * VSB_SAH_BINS]) atomicMin(sb + (6 + k) * VSB_SAH_BINS, m);
+            if (m > vb[(9 + k) * VSB_SAH_BINS]) atomicMax(sb + (9 + k) * VSB_SAH_BINS, m);
         }
         atomicAdd(sb + 12 * VSB_SAH_BINS, 1u);
     }
@@ -354,26 +369,20 @@ __global__ void __launch_bounds__(128) sah_span_split_kernel(uint32_t n_chunks, 
 // (bidirectional iterators: Hoare's scheme) leaves the k-th misplaced reference from the left and the k-th misplaced one
 // from the right swapped, everything else where it was.  F = inclusive prefix sum of the predicate over ALL positions.
 
-__global__ void sah_flag_kernel(const SahRef* __restrict__ refs, const uint32_t* __restrict__ seg_of, uint32_t n,
-                                const SahSplit* __restrict__ splits, uint32_t* __restrict__ flags)
+struct SahFlag
 {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    const uint32_t seg = seg_of[p];
-    uint32_t f = 0u;
-    if (seg != VSB_SAH_NONE)
+    const SahRef* refs; const uint32_t* seg_of; const SahSplit* splits;
+    __device__ __forceinline__ uint32_t operator()(uint32_t p) const
     {
+        const uint32_t seg = seg_of[p];
+        if (seg == VSB_SAH_NONE) return 0u;
         const SahSplit* sp = splits + seg;
-        if (sp->do_split)
-        {
-            const int axis = sp->axis;
-            const float* r = reinterpret_cast<const float*>(refs + p);
-            const float c = sah_center(r[axis], r[4 + axis]);
-            f = sah_project_unsafe(sp->k0, sp->k1, c) < sp->index ? 1u : 0u;
-        }
+        if (!sp->do_split) return 0u;
+        const int axis = sp->axis;
+        const float* r = reinterpret_cast<const float*>(refs + p);
+        return sah_project_unsafe(sp->k0, sp->k1, sah_center(r[axis], r[4 + axis])) < sp->index ? 1u : 0u;
     }
-    flags[p] = f;
-}
+};
 
 struct SahRange { uint32_t first, end, pivot, before; };      // before = F[first - 1]
 
@@ -463,7 +472,12 @@ __global__ void sah_emit_children_kernel(uint32_t* state, uint32_t bound, const 
     }
     if (s >= n_open) return;
     const SahSplit* sp = splits + s;
-    if (!sp->do_split) return;                      // stays a leaf: nodes[].left is NONE already
+    if (!sp->do_split)                              // stays a leaf: nodes[].left is NONE already
+    {
+        SahChild c; c.lseg = c.rseg = VSB_SAH_NONE; c.pivot = 0u; c.pad = 0u;
+        child[s] = c;
+        return;
+    }
     const SahSeg* sg = segs + s;
     const SahRange r = sah_range(sg, F);
     uint32_t slot = (uint32_t)(scan[s] & 0xffffffffull);
@@ -494,17 +508,6 @@ __global__ void sah_emit_children_kernel(uint32_t* state, uint32_t bound, const 
         next[slot] = t; c.rseg = slot;
     }
     child[s] = c;
-}
-
-__global__ void sah_reassign_kernel(uint32_t* seg_of, uint32_t n, const SahSplit* __restrict__ splits, const SahChild* __restrict__ child)
-{
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    if (p >= n) return;
-    const uint32_t seg = seg_of[p];
-    if (seg == VSB_SAH_NONE) return;
-    if (!splits[seg].do_split) { seg_of[p] = VSB_SAH_NONE; return; }
-    const SahChild c = child[seg];
-    seg_of[p] = p < c.pivot ? c.lseg : c.rseg;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------

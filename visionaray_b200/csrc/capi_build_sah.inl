@@ -16,23 +16,23 @@ int build_tree_sah(vsb_scene* s, int prim_kind, uint32_t n, cudaStream_t st, Bui
     const int MAX_LEVELS = 4096, CHUNK = 4;
 
     vsb::SahRef* d_refs = nullptr;
-    uint32_t *d_seg_of = nullptr, *d_flags = nullptr, *d_F = nullptr, *d_pos_l = nullptr, *d_pos_r = nullptr;
+    uint32_t *d_seg_of = nullptr, *d_F = nullptr, *d_pos_l = nullptr, *d_pos_r = nullptr;
     vsb::SahSeg* d_segs[2] = { nullptr, nullptr };
     vsb::SahSplit* d_splits = nullptr;
-    vsb::SahChild* d_child = nullptr;
+    vsb::SahChild* d_child[2] = { nullptr, nullptr };
     vsb::SahNode* d_nodes = nullptr;
     uint64_t *d_packed = nullptr, *d_scan = nullptr, *d_keys[2] = { nullptr, nullptr };
     uint32_t *d_vals[2] = { nullptr, nullptr }, *d_rank = nullptr, *d_slots = nullptr, *d_span = nullptr, *d_root = nullptr, *d_state = nullptr;
     VSB_SAH_CUDA(scratch.alloc(&d_refs, (size_t)n));
     VSB_SAH_CUDA(scratch.alloc(&d_seg_of, (size_t)n));
-    VSB_SAH_CUDA(scratch.alloc(&d_flags, (size_t)n));
     VSB_SAH_CUDA(scratch.alloc(&d_F, (size_t)n));
     VSB_SAH_CUDA(scratch.alloc(&d_pos_l, (size_t)n));
     VSB_SAH_CUDA(scratch.alloc(&d_pos_r, (size_t)n));
     VSB_SAH_CUDA(scratch.alloc(&d_segs[0], (size_t)seg_cap));
     VSB_SAH_CUDA(scratch.alloc(&d_segs[1], (size_t)seg_cap));
     VSB_SAH_CUDA(scratch.alloc(&d_splits, (size_t)seg_cap));
-    VSB_SAH_CUDA(scratch.alloc(&d_child, (size_t)seg_cap));
+    VSB_SAH_CUDA(scratch.alloc(&d_child[0], (size_t)seg_cap));
+    VSB_SAH_CUDA(scratch.alloc(&d_child[1], (size_t)seg_cap));
     VSB_SAH_CUDA(scratch.alloc(&d_packed, (size_t)seg_cap));
     VSB_SAH_CUDA(scratch.alloc(&d_scan, (size_t)seg_cap));
     VSB_SAH_CUDA(scratch.alloc(&d_nodes, node_cap));
@@ -46,7 +46,10 @@ int build_tree_sah(vsb_scene* s, int prim_kind, uint32_t n, cudaStream_t st, Bui
     VSB_SAH_CUDA(scratch.alloc(&d_root, (size_t)16));
     VSB_SAH_CUDA(scratch.alloc(&d_state, (size_t)2 * (MAX_LEVELS + CHUNK + 2)));
     size_t t_flag = 0, t_seg = 0, t_sort = 0;
-    VSB_SAH_CUDA(cub::DeviceScan::InclusiveSum(nullptr, t_flag, d_flags, d_F, (int)n, st));
+    using FlagIt = cub::TransformInputIterator<uint32_t, vsb::SahFlag, cub::CountingInputIterator<uint32_t>>;
+    const vsb::SahFlag flag_op{ d_refs, d_seg_of, d_splits };
+    const FlagIt flags(cub::CountingInputIterator<uint32_t>(0u), flag_op);
+    VSB_SAH_CUDA(cub::DeviceScan::InclusiveSum(nullptr, t_flag, flags, d_F, (int)n, st));
     VSB_SAH_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, t_seg, d_packed, d_scan, (int)seg_cap, st));
     VSB_SAH_CUDA(cub::DeviceRadixSort::SortPairs(nullptr, t_sort, d_keys[0], d_keys[1], d_vals[0], d_vals[1], (int)node_cap, 0, 64, st));
     size_t tmp_bytes = t_flag > t_seg ? t_flag : t_seg;
@@ -81,20 +84,19 @@ int build_tree_sah(vsb_scene* s, int prim_kind, uint32_t n, cudaStream_t st, Bui
         {
             const uint32_t sb = (uint32_t)(bound < (unsigned long long)seg_cap ? bound : (unsigned long long)seg_cap);
             uint32_t* stt = d_state + 2 * (size_t)(level + k);
-            vsb::sah_bin_kernel<<<n_chunks, VSB_SAH_CHUNK, 0, st>>>(d_refs, d_seg_of, n, d_segs[cur], d_splits, d_slots, d_span);
+            vsb::sah_bin_kernel<<<n_chunks, VSB_SAH_CHUNK, 0, st>>>(d_refs, d_seg_of, n, d_segs[cur], d_splits, d_slots, d_span,
+                                                                    level + k > 0 ? d_child[cur ^ 1] : nullptr);
             vsb::sah_span_split_kernel<<<(n_chunks * 16 + 127) / 128, 128, 0, st>>>(n_chunks, d_segs[cur], d_splits, d_slots, d_span);
-            vsb::sah_flag_kernel<<<blocks, 256, 0, st>>>(d_refs, d_seg_of, n, d_splits, d_flags);
             size_t tb = tmp_bytes;
-            VSB_SAH_CUDA(cub::DeviceScan::InclusiveSum(d_tmp, tb, d_flags, d_F, (int)n, st));
+            VSB_SAH_CUDA(cub::DeviceScan::InclusiveSum(d_tmp, tb, flags, d_F, (int)n, st));
             vsb::sah_mislist_kernel<<<blocks, 256, 0, st>>>(d_seg_of, n, d_segs[cur], d_splits, d_F, d_pos_l, d_pos_r);
             vsb::sah_swap_kernel<<<blocks, 256, 0, st>>>(d_refs, d_seg_of, n, d_segs[cur], d_splits, d_F, d_pos_l, d_pos_r);
             vsb::sah_child_count_kernel<<<(sb + 127) / 128, 128, 0, st>>>(stt, sb, d_segs[cur], d_splits, d_F, d_packed);
             tb = tmp_bytes;
             VSB_SAH_CUDA(cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_packed, d_scan, (int)sb, st));
             vsb::sah_emit_children_kernel<<<(sb + 127) / 128, 128, 0, st>>>(stt, sb, d_segs[cur], d_splits, d_F, d_packed, d_scan, d_segs[cur ^ 1],
-                                                                             d_nodes, d_child);
-            vsb::sah_reassign_kernel<<<blocks, 256, 0, st>>>(d_seg_of, n, d_splits, d_child);
-            g.launches += 10;
+                                                                             d_nodes, d_child[cur]);
+            g.launches += 8;
             cur ^= 1;
             bound *= 2;
         }

@@ -825,9 +825,11 @@ struct FrameProgram
 #endif
     static constexpr int MIN_BLOCKS = VSB_FRAME_MIN_BLOCKS;     // resident CTAs per SM the register budget is set for
 #ifndef VSB_FRAME_MIN_BLOCKS_Q
-#define VSB_FRAME_MIN_BLOCKS_Q 6
+#define VSB_FRAME_MIN_BLOCKS_Q 0     // 0: per kernel (below); 5 .. 8: every frame program (development)
 #endif
-    static constexpr int MIN_BLOCKS_Q = VSB_FRAME_MIN_BLOCKS_Q; // the same for trace_kernel_q
+    // CTAs of 128 threads per SM for trace_kernel_q: 6 (80 registers) for the simple / Whitted programs, 7 (72 registers) for
+    // AO / path tracing (gpurun_out/r2_ab7.log: 7 everywhere = cfg2 -4 %, cfg3 +3 %, cfg4 +1.5 %; 5 everywhere = -4 ... -6 %)
+    static constexpr int MIN_BLOCKS_Q = VSB_FRAME_MIN_BLOCKS_Q ? VSB_FRAME_MIN_BLOCKS_Q : (KERNEL >= 2 ? 7 : 6);
     static constexpr bool GROUP_RING = VSB_GROUP_RING_ALL > 0 ? true : (VSB_GROUP_RING_ALL < 0 ? false : KERNEL >= 2);             // trace_kernel_q's ring holds (record range, mask, owner) groups: AO / path tracing
     static constexpr int K0 = EXT ? 11 : 3;      // first kernel-specific state word
     static constexpr int STATE_WORDS = K0 + (KERNEL == 1 ? (SURF ? 26 : 17) : (KERNEL == 0 ? 0 : 6));
