@@ -35,7 +35,7 @@ def _function_starts():
         if m: out.append((i,m.group(1)))
     return out
 _FN=_function_starts()
-_KIND={"test_node":"node_test","perm_xor8":"node_test","test_prim":"prim_test (record decode, accept)","prim_candidate":"prim_test (record decode, accept)","hit_from_record":"hit record of the winner (once per ray)","load_record":"record loads","ldg_hint":"record loads",
+_KIND={"test_node":"node_test","perm_xor8":"node_test","test_node_slots":"node_test","test_node_lut":"node_test","expand_nibbles":"node_test","funnel_shift_in_sign":"node_test","perm_lut_fill":"kernel loop (service, refill, program)","prim_record":"queue: append + drain decision","test_prim":"prim_test (record decode, accept)","prim_candidate":"prim_test (record decode, accept)","hit_from_record":"hit record of the winner (once per ray)","load_record":"record loads","ldg_hint":"record loads",
        "ray_ctx_init":"ray_init","stack_push":"stack","stack_pop":"stack","trav_begin":"stack","trav_step":"trav_step control"}
 def _kernel_markers():
     """regions of trace_kernel_q (kernels.cuh) by the marker comments of its loop"""
