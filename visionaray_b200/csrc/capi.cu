@@ -75,8 +75,8 @@ int grid_for(K kernel, size_t smem, unsigned long long items, unsigned chunk)
 //   query_service_min / frame_service_min  lanes that must be idle before continuations + refill run
 //   phase_min                              phase vote threshold
 // frame_service_min 0 = per kernel: 32 (warp-wide lockstep; measured best for the coherent simple /
-// whitted / AO frames) or 16 (path tracing, whose bounces decorrelate the lanes)
-int g_query_service_min = 4, g_frame_service_min = 0, g_phase_min = 1;
+// whitted frames) or 24 (AO and path tracing, whose secondary rays decorrelate the lanes; gpurun_out/r2_ab8.log)
+int g_query_service_min = 8, g_frame_service_min = 0, g_phase_min = 1;     // ray lists: 8 (gpurun_out/r2_ab9.log: 2 / 4 / 8 / 16 = 1156 / 1217 / 1244 / 1196 Mrays/s)
 // sort_rays: 1 = ray lists of >= 64 Ki rays are traced in coherence-sorted order (wide path), 0 = never
 int g_sort_rays = 1;
 // frame_bands: a host render target is traced in this many bands so that the D2H copy of one band
@@ -600,7 +600,7 @@ extern "C" int vsb_frame(const vsb_scene* const* scenes, int n_scenes, const vsb
     tl.scenes = g.d_scenes; tl.n_scenes = n_scenes;
     tl.wide0 = scenes[0]->dev.wide;
     tl.chunk = VSB_FRAME_CHUNK; tl.ray_count = fl.ray_count;
-    tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel == VSB_KERNEL_PATHTRACING ? 16 : 32);
+    tl.service_min = g_frame_service_min > 0 ? g_frame_service_min : (p.kernel >= VSB_KERNEL_AO ? 24 : 32);
     tl.phase_min = g_phase_min;
 
     // Host render targets are traced in bands so that the D2H copy of a finished band runs on the
