@@ -127,9 +127,127 @@ VSB_HD uint32_t prim_record(uint32_t prim_base, uint32_t valid, int bit)
 // children (bit = 24 + (slot ^ octinv), so the highest set bit is the nearest slot); prim_hits
 // gets one bit per leaf primitive of every hit leaf child, in SLOT space (bit 4 s + j; n.w[6] = the node's
 // `valid` mask maps a bit to its record: prim_record()).
+#ifndef VSB_NODE_FHFMA
+#define VSB_NODE_FHFMA 0       // 1: plane * scale + offset as ONE mixed-precision FMA (f16 x f16 + f32, sm_100 FHFMA) -- an experiment, see below
+#endif
+
+#if VSB_NODE_FHFMA
+// d = a.half[AH] * b.half[BH] + c: fma.rn.f32.f16 (SASS FHFMA; the half selectors are operand modifiers).  The product of two
+// halves is exact in f32, so the only rounding is the final one, as in an FFMA.  Host: emulated (tests/hostsim counts
+// node visits with it; the parity tests keep the all-f32 form on the host).
+#if defined(__CUDA_ARCH__)
+template <int AH, int BH>
+__device__ __forceinline__ float fhfma(uint32_t a, uint32_t b, float c)
+{
+    float d;
+    if (AH == 0 && BH == 0) asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.f16 %0, al, bl, %3; }" : "=f"(d) : "r"(a), "r"(b), "f"(c));
+    if (AH == 0 && BH == 1) asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.f16 %0, al, bh, %3; }" : "=f"(d) : "r"(a), "r"(b), "f"(c));
+    if (AH == 1 && BH == 0) asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.f16 %0, ah, bl, %3; }" : "=f"(d) : "r"(a), "r"(b), "f"(c));
+    if (AH == 1 && BH == 1) asm("{ .reg .b16 al, ah, bl, bh; mov.b32 {al, ah}, %1; mov.b32 {bl, bh}, %2; fma.rn.f32.f16 %0, ah, bh, %3; }" : "=f"(d) : "r"(a), "r"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ uint32_t pack_half2(float lo, float hi)
+{
+    uint32_t d;
+    asm("cvt.rn.f16x2.f32 %0, %1, %2;" : "=r"(d) : "f"(hi), "f"(lo));
+    return d;
+}
+#elif defined(VSB_HOSTSIM)
+inline float half_bits_to_float(uint32_t h) { _Float16 x; uint16_t b = (uint16_t)h; memcpy(&x, &b, 2); return (float)x; }
+template <int AH, int BH>
+inline float fhfma(uint32_t a, uint32_t b, float c)
+{
+    const double pa = half_bits_to_float(AH ? a >> 16 : a & 0xffffu), pb = half_bits_to_float(BH ? b >> 16 : b & 0xffffu);
+    return (float)(pa * pb + (double)c);
+}
+inline uint32_t pack_half2(float lo, float hi)
+{
+    const _Float16 l = (_Float16)lo, h = (_Float16)hi;
+    uint16_t bl, bh; memcpy(&bl, &l, 2); memcpy(&bh, &h, 2);
+    return (uint32_t)bl | ((uint32_t)bh << 16);
+}
+#else      // nvcc's host pass: never called
+template <int AH, int BH> inline float fhfma(uint32_t, uint32_t, float c) { return c; }
+inline uint32_t pack_half2(float, float) { return 0u; }
+#endif
+
+// The node test with the plane evaluation in FHFMA.  The byte b is the half 1024 + b (one PRMT per two children, no widening
+// conversion any more: 48 fewer instructions per visit), the scale S = s * idir becomes a half too.  To keep S inside the
+// half's normal range whatever the scene's units and the ray's direction, the node's t axis is rescaled by a power of two
+// K so that the largest |S| lands in [2^7, 2^8): t' = K t, exact, and every comparison of the test is invariant under it.
+// What the half costs: S_h = S' (1 + d), |d| <= 2^-11 (or an absolute 2^-25 where an axis is > 2^21 times faster than the
+// slowest and S' falls into the subnormals).  The offset is formed with the ROUNDED scale, A = O' - 1024 S_h, so the
+// evaluation returns O' + b S_h and the error is |b (S_h - S')| <= 255 * 2^-11 |S'| + 255 * 2^-25: an eighth of a grid cell,
+// added to the margin that already covers the reference's own slab arithmetic.  NaNs (inf - inf in absurd ranges) are
+// ignored by FMNMX, i.e. drop a constraint: conservative.  The host instantiation keeps the all-f32 form; both accept a
+// superset of the reference's exact slab test, and hit records do not depend on which superset.
+VSB_HD uint32_t test_node_slots_fhfma(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
+{
+    const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
+    const uint32_t e = n.w[3];
+    const float sx = u2f((e & 0xffu) << 23) * r.ix, sy = u2f(((e >> 8) & 0xffu) << 23) * r.iy, sz = u2f(((e >> 16) & 0xffu) << 23) * r.iz;
+    const float ms = fmaxf(fmaxf(fabsf(sx), fabsf(sy)), fmaxf(fabsf(sz), 7.888609052210118e-31f));     // >= 2^-100
+    const float K = u2f(0x82800000u - (f2u(ms) & 0x7f800000u));                                          // 2^(7 - floor(log2 ms))
+    const float sxs = sx * K, sys = sy * K, szs = sz * K;
+    const float oxs = (px - r.ox) * r.ix * K, oys = (py - r.oy) * r.iy * K, ozs = (pz - r.oz) * r.iz * K;
+    const float lim = limit * K;
+    const uint32_t sxy = pack_half2(sxs, sys), szz = pack_half2(szs, szs);
+    const uint32_t m1024 = 0xe400e400u;                                                                   // half2(-1024, -1024)
+    const float bx = fhfma<0, 0>(m1024, sxy, oxs), by = fhfma<0, 1>(m1024, sxy, oys), bz = fhfma<0, 0>(m1024, szz, ozs);
+    const float k1 = 9.5367431640625e-07f + 2.384185791015625e-07f;                                       // 2^-20 + 2^-22
+    const float k2 = 255.0f * 9.5367431640625e-07f + 0.000244140625f + 0.1246f;                           // + 255 * 2^-11 (+ slack)
+    const float c0 = 7.62939453125e-06f;                                                                  // 256 * 2^-25
+    const float mx = fma_f(fabsf(sxs), k2, fma_f(fabsf(oxs), k1, c0));
+    const float my = fma_f(fabsf(sys), k2, fma_f(fabsf(oys), k1, c0));
+    const float mz = fma_f(fabsf(szs), k2, fma_f(fabsf(ozs), k1, c0));
+    const float onx = bx - mx, ofx = bx + mx;
+    const float ony = by - my, ofy = by + my;
+    const float onz = bz - mz, ofz = bz + mz;
+    const bool nx = r.ix < 0.0f, ny = r.iy < 0.0f, nz = r.iz < 0.0f;
+    const uint32_t bias = half_bias_bits();
+    uint32_t miss = 0u;
+#pragma unroll
+    for (int half = 1; half >= 0; --half)
+    {
+        const uint32_t qlox = n.w[8 + half], qloy = n.w[10 + half], qloz = n.w[12 + half];
+        const uint32_t qhix = n.w[14 + half], qhiy = n.w[16 + half], qhiz = n.w[18 + half];
+        const uint32_t qnx = nx ? qhix : qlox, qfx = nx ? qlox : qhix;
+        const uint32_t qny = ny ? qhiy : qloy, qfy = ny ? qloy : qhiy;
+        const uint32_t qnz = nz ? qhiz : qloz, qfz = nz ? qloz : qhiz;
+#pragma unroll
+        for (int j = 1; j >= 0; --j)
+        {
+            const uint32_t sel = j ? 0x4342u : 0x4140u;
+            const uint32_t pnx = byte_perm(qnx, bias, sel), pny = byte_perm(qny, bias, sel), pnz = byte_perm(qnz, bias, sel);
+            const uint32_t pfx = byte_perm(qfx, bias, sel), pfy = byte_perm(qfy, bias, sel), pfz = byte_perm(qfz, bias, sel);
+            {
+                const float tn = fmaxf(fmaxf(fhfma<1, 0>(pnx, sxy, onx), fhfma<1, 1>(pny, sxy, ony)), fhfma<1, 0>(pnz, szz, onz));
+                const float tf = fminf(fminf(fhfma<1, 0>(pfx, sxy, ofx), fhfma<1, 1>(pfy, sxy, ofy)), fhfma<1, 0>(pfz, szz, ofz));
+                miss = funnel_shift_in_sign(miss, fminf(fminf(tf - tn, lim - tn), tf));
+            }
+            {
+                const float tn = fmaxf(fmaxf(fhfma<0, 0>(pnx, sxy, onx), fhfma<0, 1>(pny, sxy, ony)), fhfma<0, 0>(pnz, szz, onz));
+                const float tf = fminf(fminf(fhfma<0, 0>(pfx, sxy, ofx), fhfma<0, 1>(pfy, sxy, ofy)), fhfma<0, 0>(pfz, szz, ofz));
+                miss = funnel_shift_in_sign(miss, fminf(fminf(tf - tn, lim - tn), tf));
+            }
+        }
+    }
+    const uint32_t child_hits = ~miss & 0xffu;
+    prim_hits = expand_nibbles(child_hits) & n.w[6];
+    return child_hits & (n.w[3] >> 24);
+}
+#endif
+
+#ifndef VSB_HOST_NODE_FHFMA
+#define VSB_HOST_NODE_FHFMA 0     // hostsim: 1 = the host also uses the FHFMA form (emulated), for visit counts
+#endif
+
 // test_node_slots: the inner-child hits in SLOT space (8 bits); test_node: permuted into traversal order, bits 24..31
 VSB_HD uint32_t test_node_slots(const NodeRegs& n, const RayCtx& r, float limit, uint32_t& prim_hits)
 {
+#if VSB_NODE_FHFMA && (defined(__CUDA_ARCH__) || VSB_HOST_NODE_FHFMA)
+    return test_node_slots_fhfma(n, r, limit, prim_hits);
+#endif
     const float px = u2f(n.w[0]), py = u2f(n.w[1]), pz = u2f(n.w[2]);
     const uint32_t e = n.w[3];
 #if VSB_NODE_HALFCVT
