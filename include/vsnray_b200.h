@@ -266,10 +266,12 @@ int  vsb_sync(void);                             /* wait for the library's own s
 const char* vsb_strerror(int code);
 int  vsb_version(void);
 int  vsb_device_sm_count(int* out);
-/* scheduling knobs of the persistent traversal kernel: "query_service_min", "frame_service_min"
- * (idle lanes of a warp before finished rays are serviced / refilled, 1..32) and "phase_min"
- * (node/primitive phase vote threshold); "trace_queue" (1: primitive tests shared by the warp, the default),
- * "drain_min" / "pend_min" (its batching thresholds).  Results do not depend on them. */
+/* scheduling knobs of the persistent traversal kernel: "query_service_min" (default 8), "frame_service_min"
+ * (0 = per kernel: 32 simple / Whitted, 24 AO / path tracing): idle lanes of a warp before finished rays are
+ * serviced / refilled, 1..32; "phase_min" (node/primitive phase vote threshold of the round-1 loop);
+ * "trace_queue" (1: primitive tests shared by the warp, the default), "drain_min" (24) / "pend_min" (8) (its
+ * batching thresholds); "build_algorithm" and the other builder knobs: see vsb_scene_build.  Results do not
+ * depend on the scheduling knobs. */
 int  vsb_tune(const char* key, int value);
 
 /* ---- scene: replaces cuda_index_bvh<P>(index_bvh<P> const&) upload (bvh.h:344-350,446-447)
