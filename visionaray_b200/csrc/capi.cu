@@ -86,7 +86,7 @@ int g_list_piece_krays = 1024;   // host ray lists are staged, traced and read b
 int g_band_min_mib = 16;   // a band carries at least this much of the target (per-launch ramps vs overlap)
 int g_band_trace = 0;      // developer switch: print the band timeline of host-target frames to stderr
 int g_band_streams = 2;    // 2: alternate bands over two streams (tail of band i overlaps the head of band i+1)
-int g_frame_bands = 8;     // cfg2 into pinned host memory: 1 band 11.8 ms, 2: 9.6, 16 interleaved bands on two streams: see DESIGN.md section 5
+int g_frame_bands = 12;    // cfg2 into pinned host memory: 1 band 11.8 ms, 2: 9.6 (round 1); 8 / 12 / 16 / 24 interleaved bands on two streams: 5.90 / 5.72 / 5.82 / 6.02 ms
 
 // trace_queue: 1 = single-bvh BVH8 launches run trace_kernel_q (primitive tests shared by the warp), 0 = trace_kernel
 int g_trace_queue = 1, g_drain_min = 24, g_pend_min = 8;     // drain_min 16..24 measured best (cfg5 +3 % over 32)
