@@ -520,7 +520,22 @@ trace_kernel_q(const TraceLaunch tl, const __grid_constant__ Program prog)
                 if (has != 0u)
                 {
                     while (q_tail - q_head > VSB_QCAP / 2 - 32u) { drain(); drained = true; }       // room for 32 groups
-                    if (mine) gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, t.pg_valid);
+                    if (mine)
+                    {
+                        gring[(q_tail + (unsigned)__popc(has & lt_mask)) & (VSB_QCAP / 2 - 1u)] = make_uint4(t.pg_base, t.pg_mask, threadIdx.x, t.pg_valid);
+#if VSB_Q_PREFETCH
+                        // the group's records are tested a drain later: start their way up the hierarchy now
+                        const char* a = reinterpret_cast<const char*>(sc.prims) + (size_t)prim_record(t.pg_base, t.pg_valid, __ffs((int)t.pg_mask) - 1) * (size_t)(n16 * 16);
+                        const char* e = reinterpret_cast<const char*>(sc.prims) + (size_t)(prim_record(t.pg_base, t.pg_valid, find_msb(t.pg_mask)) + 1u) * (size_t)(n16 * 16) - 1;
+#if VSB_Q_PREFETCH == 1
+                        asm volatile("prefetch.global.L1 [%0];" :: "l"(a));
+                        if (((uintptr_t)a >> 7) != ((uintptr_t)e >> 7)) asm volatile("prefetch.global.L1 [%0];" :: "l"(e));
+#else
+                        asm volatile("prefetch.global.L2 [%0];" :: "l"(a));
+                        if (((uintptr_t)a >> 7) != ((uintptr_t)e >> 7)) asm volatile("prefetch.global.L2 [%0];" :: "l"(e));
+#endif
+#endif
+                    }
                     q_pairs += __reduce_add_sync(0xffffffffu, mine ? (unsigned)__popc(t.pg_mask) : 0u);
                     t.pg_mask = 0u;
                     q_tail += (unsigned)__popc(has);

@@ -93,6 +93,9 @@ struct Node80
 };
 
 #define VSB_WIDE 8
+#ifndef VSB_Q_PREFETCH
+#define VSB_Q_PREFETCH 0          // group ring: prefetch a group's records when it is appended (1: into L1, 2: into L2)
+#endif
 #ifndef VSB_GROUP_RING_ALL
 #define VSB_GROUP_RING_ALL 0      // development switch: 1 / -1 = group ring / pair ring for every program (0: per program)
 #endif
