@@ -333,12 +333,25 @@ def test_tile_partition_reassembles_the_frame(gpu, scenes):
     buf.close()
 
 
+def _assert_gpu_builder_gives_this_tree(gpu, sc):
+    """The bench's default tree is BUILT on the GPU (vsb_scene_build, csrc/build_sah.cuh): at full size, too, it is the
+    host builder's tree node for node -- so what these tests check on the host tree holds for the bench's scenes."""
+    built = gpu.Scene.build(sc.prim_kind, sc.prims)
+    nodes, idx = built.download_bvh()
+    built.close()
+    assert nodes.shape == sc.nodes.shape
+    assert np.array_equal(nodes["first"], sc.nodes["first"]) and np.array_equal(nodes["num_prims"], sc.nodes["num_prims"])
+    assert np.array_equal(nodes["bbox_min"], sc.nodes["bbox_min"]) and np.array_equal(nodes["bbox_max"], sc.nodes["bbox_max"])
+    assert np.array_equal(idx, sc.indices)
+
+
 def test_full_size_properties_cfg1(gpu):
     """BASELINE configs[0] at full size (99,904 triangles, 1024^2 primary rays): size-independent
     properties -- wide == exact up to ties on every ray; reversing a hit ray from its hit point
     finds the same primitive or a nearer one; any-hit flag == (closest t < max_t)."""
     sc = S.make_scene("cfg1_sphere", 1.0)
     dev = gpu.Scene(sc)
+    _assert_gpu_builder_gives_this_tree(gpu, sc)
     fp = S.frame_params(0, 1024, 1024, (0.0, 0.0, 3.0), (0, 0, 0))
     rays = S.primary_rays(fp)
     exact = gpu.closest_hit(dev, rays, traverse=gpu.TRAVERSE_EXACT)
@@ -363,6 +376,7 @@ def test_full_size_cfg2_frame_wide_vs_reference_order(gpu):
 
     sc = S.make_scene("cfg2_grid", 1.0)
     dev = gpu.Scene(sc)
+    _assert_gpu_builder_gives_this_tree(gpu, sc)
     eye = (0.3, 1.2, 2.2)
     fp = S.frame_params(1, 4096, 4096, eye, (0, 0, 0), num_bounces=4)
     mats, lights = S.default_material(0), S.point_light(eye)
@@ -422,6 +436,7 @@ def test_full_size_cfg3_ao_frame(gpu):
     sc = S.make_scene("cfg3_cubes", 1.0)
     assert sc.n_prims == 5_000_004
     dev = gpu.Scene(sc)
+    _assert_gpu_builder_gives_this_tree(gpu, sc)
     eye = (0.6, 1.4, 2.6)
     fp = S.frame_params(2, 2048, 2048, eye, (0, 0, 0), ao_samples=16, ao_radius=0.1)
     mats, lights = S.default_material(0), S.point_light(eye)
@@ -458,6 +473,7 @@ def test_full_size_cfg4_progressive_path_tracer(gpu):
     sc = S.make_scene("cfg4_terrain", 1.0)
     assert 9_900_000 < sc.n_prims < 10_100_000
     dev = gpu.Scene(sc)
+    _assert_gpu_builder_gives_this_tree(gpu, sc)
     eye = (0.3, 1.2, 2.2)
     mats, lights = S.default_material(1), S.point_light(eye)
     d_m = torch.from_numpy(mats.view(np.float32).copy()).cuda()
@@ -499,6 +515,7 @@ def test_full_size_cfg5_random_ray_stress(gpu):
     sc = S.make_scene("cfg5_soup", 1.0)
     assert sc.n_prims == 20_000_000
     dev = gpu.Scene(sc)
+    _assert_gpu_builder_gives_this_tree(gpu, sc)
     rays = S.random_rays(1 << 24, 600)
     exact = gpu.closest_hit(dev, rays, traverse=gpu.TRAVERSE_EXACT)
     wide = gpu.closest_hit(dev, rays)
