@@ -306,7 +306,7 @@ def prepare_scene(api, S, scene_name: str, scale: float, builder: str):
     --builder gpu (default): primitives only on the host; vsb_scene_build builds the REFERENCE's binned-SAH tree on the
     GPU (the same nodes and indices as the host builder: tests/test_gpu_sah_builder.py) and re-encodes it as a BVH8.
     --builder reference: the same tree from the host builder, uploaded and re-encoded.  --builder gpu_ploc: the
-    Morton + PLOC tree (faster to build at >= 5 M primitives, traces ~10 % slower)."""
+    Morton + PLOC tree (about the same build time, traces 5-14 % slower)."""
     t0 = time.perf_counter()
     sc = S.make_scene(scene_name, scale, build_tree=(builder == "reference"))
     gen_s = time.perf_counter() - t0
@@ -1002,7 +1002,7 @@ def main():
     ap.add_argument("--builder", default="gpu", choices=["gpu", "reference", "gpu_ploc"],
                     help="who builds the BVH: gpu = the reference's binned-SAH tree built on the GPU (same nodes and indices as the host "
                          "builder, ~5 ms instead of 0.5 s at 1 M triangles); reference = the host builder; gpu_ploc = Morton + PLOC "
-                         "(another tree: faster to build at >= 5 M primitives, traces ~10 %% slower)")
+                         "(another tree: about the same build time, traces 5-14 %% slower)")
     ap.add_argument("--scale", type=float, default=1.0, help="scene size factor (1.0 = the BASELINE config)")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--no-extra", action="store_true", help="skip the extra (N = 1) / strong (N > 1) records of the default run")

@@ -292,8 +292,8 @@ int  vsb_scene_create(int prim_kind, const void* prims, size_t n_prims,
  *     No spatial splits (build them with the host builder and pass the tree to vsb_scene_create).
  *   vsb_tune("build_algorithm", 0): Morton sort + parallel locally-ordered clustering + SAH leaf collapse (<= 4
  *     primitives per leaf; csrc/build_ploc.cuh).  Another valid BVH: closest hits equal up to t-ties, any-hit
- *     winners and primitive_list_index follow THAT tree's order.  Faster to build from ~5 M primitives up, traces
- *     ~10 % slower.  Knobs: "build_radius" (1..32, default 8), "build_cost_node_x100", "build_cost_prim_x100".
+ *     winners and primitive_list_index follow THAT tree's order.  Builds in about the same time (8.7 vs 13 ms at 5 M
+ *     primitives, 54 vs 49 ms at 20 M), traces 5-14 % slower.  Knobs: "build_radius" (1..32, default 8), "build_cost_node_x100", "build_cost_prim_x100".
  * Both lay the tree out in the reference's node / indices format and re-encode it into the BVH8 like any other
  * tree.  prims: host or device memory (mem = VSB_MEM_*). */
 int  vsb_scene_build(int prim_kind, const void* prims, size_t n_prims, int mem, vsb_scene** out);
